@@ -1,0 +1,262 @@
+"""Generates tests/golden/*.npz by running the UNMODIFIED reference in this container.
+
+TEST INFRASTRUCTURE ONLY.  Run once here (`python oracle/gen_golden.py`); the
+resulting small fixtures are committed, because `/root/reference` does not exist on
+the GPU box.  Every tensor stored below is an input to, or an output of, the
+reference's own code:
+
+  cp2_step_small.npz   two full `MODEL.forward_cp2` + backward steps (builder.py:1124)
+                       with a one-conv encoder: B=4, 64x64 views, OS16 (P=16), C=128,
+                       K=256 -> composite, losses, grads, EMA'd key weights, queue, ptr.
+  cp2_loss_p196_*.npz  the loss path on given 14x14 feature maps (P=196, C=128,
+                       K=1024) for tau_d in {1.0, 0.2} and include_background on/off.
+  ema.npz              `_momentum_update_key_encoder` (builder.py:557) on odd-sized tensors.
+  enqueue.npz          `_dequeue_and_enqueue` (builder.py:569) incl. wrap-around, K=100.
+  corr.npz             `get_masked_correlation_map` / `calcuate_dense_loss_stats`
+                       (tools/correlation_mapping.py) on the reference's own test cases.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import ref_harness as rh  # noqa: E402
+from oracle.cp2_oracle import synth_views  # noqa: E402
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+def _np(t):
+    return t.detach().cpu().numpy().copy()
+
+
+class _Capture:
+    """Records encoder inputs/outputs and the unshuffle permutation without touching
+    the reference's arithmetic."""
+
+    def __init__(self, model):
+        self.rec = {}
+        model.encoder_q.register_forward_hook(self._q)
+        model.encoder_k.register_forward_hook(self._k)
+        orig = model._batch_shuffle_ddp
+
+        def wrapped(x):
+            y, idx = orig(x)
+            self.rec["idx_unshuffle"] = idx.clone()
+            return y, idx
+
+        model._batch_shuffle_ddp = wrapped
+
+    def _q(self, _m, inp, out):
+        self.rec["img_a_comp"] = inp[0].detach().clone()
+        out.retain_grad()
+        self.rec["q"] = out
+
+    def _k(self, _m, inp, out):
+        self.rec["k_shuffled"] = out.detach().clone()
+
+
+def gen_step_small():
+    torch.manual_seed(0)
+    B, H, C, K = 4, 64, 128, 256
+    _, model = rh.make_reference_model(lambda: rh.PatchEncoder(C, 16), K=K, dim=C,
+                                       dense_logits_temp=0.2)
+    cap = _Capture(model)
+    # make encoder_q differ from encoder_k so the EMA is not a no-op
+    g = torch.Generator().manual_seed(5)
+    with torch.no_grad():
+        for p in model.encoder_q.parameters():
+            p.add_(0.05 * torch.randn(p.shape, generator=g))
+    out = {"queue0": _np(model.queue), "B": B, "H": H, "C": C, "K": K,
+           "temp_local": 0.2, "temp_global": 0.2, "lmbd": 0.2, "m": 0.999}
+    for name, p in model.encoder_q.named_parameters():
+        out[f"q0.{name}"] = _np(p)
+    for name, p in model.encoder_k.named_parameters():
+        out[f"k0.{name}"] = _np(p)
+    opt = torch.optim.SGD(model.encoder_q.parameters(), lr=0.05)
+    for step in range(2):
+        v = synth_views(B, H, H, 16, seed=100 + step)
+        for k_, t in v.items():
+            if "ids" not in k_:      # ids are arange(1, H*W+1) per image (synth_views)
+                out[f"s{step}.{k_}"] = _np(t)
+        opt.zero_grad()
+        loss = model(visualize=False, step=step, new_epoch=False, **v)
+        loss.backward()
+        out[f"s{step}.loss"] = _np(loss)
+        out[f"s{step}.loss_ins"] = np.float32(model.loss_i.val)
+        out[f"s{step}.loss_dense"] = np.float32(model.loss_d.val)
+        out[f"s{step}.acc_ins"] = np.float32(float(model.acc_ins.val))
+        out[f"s{step}.acc_seg"] = np.float32(model.acc_seg.val)
+        out[f"s{step}.img_a_comp"] = _np(cap.rec["img_a_comp"])
+        out[f"s{step}.q"] = _np(cap.rec["q"])
+        out[f"s{step}.grad_q"] = _np(cap.rec["q"].grad)
+        out[f"s{step}.k"] = _np(cap.rec["k_shuffled"][cap.rec["idx_unshuffle"]])
+        out[f"s{step}.queue"] = _np(model.queue)
+        out[f"s{step}.queue_ptr"] = _np(model.queue_ptr)
+        for name, p in model.encoder_k.named_parameters():
+            out[f"s{step}.k.{name}"] = _np(p)
+        for name, p in model.encoder_q.named_parameters():
+            out[f"s{step}.gradw.{name}"] = _np(p.grad)
+        opt.step()
+    np.savez_compressed(os.path.join(OUT, "cp2_step_small.npz"), **out)
+    print("cp2_step_small", out["s0.loss"], out["s1.loss"], out["s1.queue_ptr"])
+
+
+class _FeatEncoder(nn.Module):
+    """Returns a stored feature map whatever the input (identity 'encoder')."""
+
+    class _BB(nn.Module):
+        def forward(self, x):
+            y = torch.zeros(x.shape[0], 1, 14, 14)
+            return (y, y, y, y)
+
+        def init_weights(self):
+            pass
+
+    def __init__(self, B, C, h):
+        super().__init__()
+        self.feat = nn.Parameter(torch.zeros(B, C, h, h))
+        self.backbone = _FeatEncoder._BB()
+
+    def forward(self, x):
+        return self.feat[: x.shape[0]] * 1.0
+
+
+def gen_loss_p196(tag, temp_local, include_background):
+    torch.manual_seed(1)
+    B, C, h, K = 2, 128, 14, 1024
+    _, model = rh.make_reference_model(lambda: _FeatEncoder(B, C, h), K=K, dim=C,
+                                       dense_logits_temp=temp_local,
+                                       include_background=include_background)
+    assert model.output_stride == 16
+    cap = _Capture(model)
+    g = torch.Generator().manual_seed(7)
+    with torch.no_grad():
+        model.encoder_q.feat.copy_(torch.randn(B, C, h, h, generator=g))
+        model.encoder_k.feat.copy_(torch.randn(B, C, h, h, generator=g))
+    v = synth_views(B, 224, 224, 16, seed=42)
+    out = {"queue0": _np(model.queue), "temp_local": temp_local, "temp_global": 0.2,
+           "lmbd": 0.2, "include_background": include_background,
+           "bg0_ch0_zero": _np(v["bg0"][:, 0] == 0), "bg1_ch0_zero": _np(v["bg1"][:, 0] == 0)}
+    loss = model(visualize=False, step=0, new_epoch=False, **v)
+    loss.backward()
+    out["q"] = _np(cap.rec["q"])
+    out["k"] = _np(cap.rec["k_shuffled"][cap.rec["idx_unshuffle"]])
+    out["grad_q"] = _np(model.encoder_q.feat.grad)
+    out["loss"] = _np(loss)
+    out["loss_ins"] = np.float32(model.loss_i.val)
+    out["loss_dense"] = np.float32(model.loss_d.val)
+    out["acc_seg"] = np.float32(model.acc_seg.val)
+    out["acc_ins"] = np.float32(float(model.acc_ins.val))
+    out["queue1_head"] = _np(model.queue[:, :8])   # only columns 0..B-1 changed
+    out["queue_ptr1"] = _np(model.queue_ptr)
+    out["iou"] = np.asarray(model.correlation_ious, dtype=np.float32)
+    out["iou_masked"] = np.asarray(model.masked_correlation_ious, dtype=np.float32)
+    np.savez_compressed(os.path.join(OUT, f"cp2_loss_p196_{tag}.npz"), **out)
+    print("cp2_loss_p196", tag, out["loss"], out["loss_ins"], out["loss_dense"])
+
+
+class _Holder(nn.Module):
+    def __init__(self, shapes, seed):
+        super().__init__()
+        g = torch.Generator().manual_seed(seed)
+        self.ps = nn.ParameterList([nn.Parameter(torch.randn(s, generator=g)) for s in shapes])
+        self.backbone = _FeatEncoder._BB()
+        self.h = nn.Parameter(torch.zeros(1, 1, 14, 14))
+
+    def forward(self, x):
+        return self.h.expand(x.shape[0], 1, 14, 14)
+
+
+def gen_ema():
+    shapes = [(64, 3, 7, 7), (64,), (1,), (257, 33), (5, 1, 3), (100003,), (128, 512, 1, 1), (19,)]
+    seeds = iter([11, 12])
+    _, model = rh.make_reference_model(lambda: _Holder(shapes, next(seeds)), K=16, dim=8)
+    g = torch.Generator().manual_seed(13)
+    with torch.no_grad():
+        for p in model.encoder_k.ps:
+            p.copy_(torch.randn(p.shape, generator=g) * 3.0)
+        # specials: zeros, denormals, negative zero, large
+        model.encoder_q.ps[1][:4] = torch.tensor([0.0, -0.0, 1e-40, 3e38])
+        model.encoder_k.ps[1][:4] = torch.tensor([-0.0, 0.0, -1e-41, 3e38])
+    out = {"m": 0.999, "n": len(shapes)}
+    for i, (pq, pk) in enumerate(zip(model.encoder_q.ps, model.encoder_k.ps)):
+        out[f"q{i}"], out[f"k{i}"] = _np(pq), _np(pk)
+    model._momentum_update_key_encoder()
+    for i, pk in enumerate(model.encoder_k.ps):
+        out[f"k1_{i}"] = _np(pk)
+    model.momentum = 0.99
+    model._momentum_update_key_encoder()
+    for i, pk in enumerate(model.encoder_k.ps):
+        out[f"k2_{i}"] = _np(pk)
+    np.savez_compressed(os.path.join(OUT, "ema.npz"), **out)
+    print("ema ok")
+
+
+def gen_enqueue():
+    _, model = rh.make_reference_model(lambda: _Holder([(2,)], 1), K=100, dim=16)
+    g = torch.Generator().manual_seed(21)
+    out = {"queue0": _np(model.queue)}
+    batches = [32, 32, 32, 32, 7, 100, 1, 29]   # wraps at step 3, exact fill, single row
+    out["batches"] = np.asarray(batches)
+    for i, n in enumerate(batches):
+        keys = torch.randn(n, 16, generator=g)
+        out[f"keys{i}"] = _np(keys)
+        model._dequeue_and_enqueue(keys)
+        out[f"queue{i + 1}"] = _np(model.queue)
+        out[f"ptr{i + 1}"] = _np(model.queue_ptr)
+    np.savez_compressed(os.path.join(OUT, "enqueue.npz"), **out)
+    print("enqueue ok", out[f"ptr{len(batches)}"])
+
+
+def gen_corr():
+    rh.import_reference()
+    from tools.correlation_mapping import (calcuate_dense_loss_stats,
+                                           get_masked_correlation_map)
+    out = {}
+    # reference test case "uniqueIds" (tests/test_correlation_mapping.py:27-76), fixed shuffle
+    bs, hh, ww = 4, 10, 10
+    rng = np.random.RandomState(3)
+    base = torch.arange(1, bs * hh * ww + 1)[torch.from_numpy(rng.permutation(bs * hh * ww))]
+    base = base.reshape(bs, hh, ww)
+    map_a, map_b = base[:, :5, :5], base[:, 1:6, 2:7]
+    mask_a = torch.zeros(bs, 5, 5); mask_a[:, 2:4, 1:3] = 1
+    mask_b = torch.zeros(bs, 5, 5); mask_b[:, 1:3, 0:2] = 1
+    r = get_masked_correlation_map(map_a=map_a, map_b=map_b, mask_a=mask_a, mask_b=mask_b)
+    out.update(u_map_a=_np(map_a), u_map_b=_np(map_b), u_mask_a=_np(mask_a), u_mask_b=_np(mask_b),
+               u_iou=_np(r["iou"]), u_iou_masked=_np(r["iou_masked"]), u_corr=_np(r["corr_map"]))
+    # reference test case "sharedIds" (tests/test_correlation_mapping.py:81-129)
+    base = torch.Tensor([[[1, 2, 2, 3, 4, 5], [6, 2, 2, 3, 3, 3],
+                          [7, 8, 9, 10, 11, 12], [13, 8, 8, 8, 14, 15]]])
+    map_a, map_b = base[:, 0:3, 1:4], base[:, 0:3, 2:5]
+    mask_a = torch.Tensor([[[1, 1, 1], [1, 1, 1], [0, 0, 0]]])
+    mask_b = torch.Tensor([[[1, 0, 0], [1, 0, 0], [1, 0, 0]]])
+    r = get_masked_correlation_map(map_a=map_a, map_b=map_b, mask_a=mask_a, mask_b=mask_b)
+    out.update(s_map_a=_np(map_a), s_map_b=_np(map_b), s_mask_a=_np(mask_a), s_mask_b=_np(mask_b),
+               s_iou=_np(r["iou"]), s_iou_masked=_np(r["iou_masked"]), s_corr=_np(r["corr_map"]))
+    # dense stats
+    g = torch.Generator().manual_seed(9)
+    logits = torch.randn(3, 12, 12, generator=g)
+    labels = (torch.rand(3, 12, generator=g) > 0.4).float()[:, :, None] * \
+             (torch.rand(3, 12, generator=g) > 0.4).float()[:, None, :]
+    st = calcuate_dense_loss_stats(logits, labels)
+    out.update(d_logits=_np(logits), d_labels=_np(labels))
+    for side in ("positive", "negative"):
+        out[f"d_{side}_avg"] = _np(st[side]["average"])
+        out[f"d_{side}_q"] = _np(torch.stack(list(st[side]["quartiles"])))
+    np.savez_compressed(os.path.join(OUT, "corr.npz"), **out)
+    print("corr ok", out["u_iou"][0], out["u_iou_masked"][0], out["s_iou"], out["s_iou_masked"])
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    gen_step_small()
+    gen_loss_p196("t1", 1.0, False)
+    gen_loss_p196("t02", 0.2, False)
+    gen_loss_p196("t02_bg", 0.2, True)
+    gen_ema()
+    gen_enqueue()
+    gen_corr()

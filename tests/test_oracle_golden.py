@@ -1,0 +1,123 @@
+"""CPU: pins oracle/cp2_oracle.py against golden vectors recorded from the unmodified
+reference (oracle/gen_golden.py) and against the constants in the reference's own unit
+tests (tests/test_correlation_mapping.py:73-74,126-127; test_contrastive_metrics.py:53-55)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import T, load_golden
+from oracle import cp2_oracle as O
+
+
+def test_composite_and_subsample_match_reference_bit_exact():
+    g = load_golden("cp2_step_small.npz")
+    for s in (0, 1):
+        out, mask = O.composite(T(g[f"s{s}.img_a"]), T(g[f"s{s}.bg0"]))
+        assert torch.equal(out, T(g[f"s{s}.img_a_comp"]))
+        assert mask.shape == (4, 64, 64)
+        assert O.stride_subsample(mask, 16).shape == (4, 4, 4)
+
+
+@pytest.mark.parametrize("tag", ["t1", "t02", "t02_bg"])
+def test_loss_path_p196(tag):
+    g = load_golden(f"cp2_loss_p196_{tag}.npz")
+    q = T(g["q"]).requires_grad_(True)
+    mask_a = O.stride_subsample(T(g["bg0_ch0_zero"]).float(), 16).reshape(2, -1)
+    mask_b = O.stride_subsample(T(g["bg1_ch0_zero"]).float(), 16).reshape(2, -1)
+    r = O.cp2_loss(q, T(g["k"]), mask_a, mask_b, T(g["queue0"]),
+                   temp_global=float(g["temp_global"]), temp_local=float(g["temp_local"]),
+                   lmbd_dense=float(g["lmbd"]), include_background=bool(g["include_background"]))
+    r["loss"].backward()
+    np.testing.assert_allclose(r["loss"].item(), g["loss"], rtol=1e-6)
+    np.testing.assert_allclose(r["loss_ins"].item(), g["loss_ins"], rtol=1e-6)
+    np.testing.assert_allclose(r["loss_dense"].item(), g["loss_dense"], rtol=1e-6)
+    np.testing.assert_allclose(q.grad.numpy(), g["grad_q"], rtol=1e-4, atol=1e-9)
+    np.testing.assert_allclose(r["acc_dense"].item(), g["acc_seg"], rtol=0, atol=1e-4)
+    np.testing.assert_allclose(r["acc1"].item(), g["acc_ins"], rtol=0, atol=1e-4)
+    queue = T(g["queue0"]).clone()
+    ptr = O.dequeue_and_enqueue(queue, 0, r["k_pos"])
+    assert ptr == int(g["queue_ptr1"][0])
+    np.testing.assert_allclose(queue[:, :8].numpy(), g["queue1_head"], rtol=1e-6, atol=1e-8)
+    ids = torch.arange(1, 224 * 224 + 1).reshape(1, 224, 224).repeat(2, 1, 1)
+    ids = O.stride_subsample(ids, 16)
+    mc = O.masked_correlation(ids, ids, mask_a.reshape(2, 14, 14), mask_b.reshape(2, 14, 14))
+    np.testing.assert_allclose(mc["iou"].numpy(), g["iou"])
+    np.testing.assert_allclose(mc["iou_masked"].numpy(), g["iou_masked"])
+    w = O.cp2_corr_weights(ids, ids, ids, ids, mask_a, mask_b)
+    assert w.dtype == torch.int64 and bool((w == 1).all())
+
+
+def test_full_step_small():
+    g = load_golden("cp2_step_small.npz")
+    queue = T(g["queue0"]).clone()
+    ptr = 0
+    for s in (0, 1):
+        _, ma = O.composite(T(g[f"s{s}.img_a"]), T(g[f"s{s}.bg0"]))
+        _, mb = O.composite(T(g[f"s{s}.img_b"]), T(g[f"s{s}.bg1"]))
+        ma = O.stride_subsample(ma, 16).reshape(4, -1)
+        mb = O.stride_subsample(mb, 16).reshape(4, -1)
+        q = T(g[f"s{s}.q"]).requires_grad_(True)
+        r = O.cp2_loss(q, T(g[f"s{s}.k"]), ma, mb, queue, 0.2, 0.2, 0.2)
+        r["loss"].backward()
+        np.testing.assert_allclose(r["loss"].item(), g[f"s{s}.loss"], rtol=1e-6)
+        np.testing.assert_allclose(q.grad.numpy(), g[f"s{s}.grad_q"], rtol=1e-4, atol=1e-9)
+        ptr = O.dequeue_and_enqueue(queue, ptr, r["k_pos"])
+        assert ptr == int(g[f"s{s}.queue_ptr"][0])
+        np.testing.assert_allclose(queue.numpy(), g[f"s{s}.queue"], rtol=1e-6, atol=1e-8)
+
+
+def test_ema_bit_exact():
+    g = load_golden("ema.npz")
+    n = int(g["n"])
+    q = [T(g[f"q{i}"]) for i in range(n)]
+    k = [T(g[f"k{i}"]) for i in range(n)]
+    k1 = O.ema_update(q, k, 0.999)
+    for i in range(n):
+        assert torch.equal(k1[i].view(torch.int32), T(g[f"k1_{i}"]).view(torch.int32)), i
+    k2 = O.ema_update(q, k1, 0.99)
+    for i in range(n):
+        assert torch.equal(k2[i].view(torch.int32), T(g[f"k2_{i}"]).view(torch.int32)), i
+
+
+def test_enqueue_bit_exact_with_wraparound():
+    g = load_golden("enqueue.npz")
+    queue = T(g["queue0"]).clone()
+    ptr = 0
+    for i, n in enumerate(g["batches"]):
+        ptr = O.dequeue_and_enqueue(queue, ptr, T(g[f"keys{i}"]))
+        assert ptr == int(g[f"ptr{i + 1}"][0])
+        assert torch.equal(queue, T(g[f"queue{i + 1}"]))
+
+
+def test_masked_iou_reference_constants():
+    g = load_golden("corr.npz")
+    for p, iou, ioum in (("u", 12 / 38, 1 / 3), ("s", 4 / 7, 2 / 3)):
+        r = O.masked_correlation(T(g[f"{p}_map_a"]), T(g[f"{p}_map_b"]),
+                                 T(g[f"{p}_mask_a"]), T(g[f"{p}_mask_b"]))
+        assert torch.all(r["iou"] == torch.tensor(iou, dtype=torch.float32))
+        assert torch.all(r["iou_masked"] == torch.tensor(ioum, dtype=torch.float32))
+        np.testing.assert_array_equal(r["iou"].numpy(), g[f"{p}_iou"].reshape(-1))
+        np.testing.assert_array_equal(r["corr_map"].numpy(), g[f"{p}_corr"])
+
+
+def test_dense_stats_and_quantile_semantics():
+    g = load_golden("corr.npz")
+    st = O.dense_loss_stats(T(g["d_logits"]), T(g["d_labels"]))
+    for side in ("positive", "negative"):
+        np.testing.assert_allclose(st[side]["average"].numpy(), g[f"d_{side}_avg"], rtol=1e-6)
+        np.testing.assert_allclose(torch.stack(list(st[side]["quartiles"])).numpy(),
+                                   g[f"d_{side}_q"], rtol=1e-6)
+    # reference tests/test_contrastive_metrics.py:16-57
+    scores = torch.Tensor([[[1, 2, 3], [4, 5, 6]], [[1, 2, 3], [7, 8, 9]]])
+    qt = torch.quantile(scores.flatten(1), q=torch.Tensor([0.25, 0.5, 0.75]), dim=1)
+    assert torch.all(qt == torch.Tensor([[2.25, 2.25], [3.5, 5.0], [4.75, 7.75]]))
+
+
+def test_shuffle_roundtrip():
+    x = torch.arange(24.0).reshape(12, 2)
+    perm = torch.randperm(12, generator=torch.Generator().manual_seed(0))
+    world = 3
+    shuf = [O.batch_shuffle(x, perm, r, world) for r in range(world)]
+    gathered = O.concat_all_gather([s[0] for s in shuf])
+    back = O.concat_all_gather([O.batch_unshuffle(gathered, shuf[0][1], r, world) for r in range(world)])
+    assert torch.equal(back, x)
