@@ -1,0 +1,67 @@
+"""ctypes binding of the C ABI in include/cp2_b200.h (libcp2_b200.so, sm_100a).
+
+There is NO fallback: if the shared library is missing or does not export every
+symbol the header declares, loading raises.  Build it with
+`python -c "import __graft_entry__ as g; g.build()"` or `make -C cp2_b200/csrc`.
+"""
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_int64, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libcp2_b200.so")
+
+# name -> (restype, argtypes); mirrors include/cp2_b200.h one to one
+SIGNATURES = {
+    "cp2_abi_version": (c_int, []),
+    "cp2_last_error": (c_char_p, []),
+    "cp2_composite": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
+    "cp2_prep_tiles": (c_int, [c_int]),
+    "cp2_prep_features": (c_int, [c_void_p] * 7 + [c_int] * 3 + [c_void_p]),
+    "cp2_dense_lse": (c_int, [c_void_p] * 3 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_dense_grad": (c_int, [c_void_p] * 10 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_global_scratch_floats": (c_int64, [c_int, c_int]),
+    "cp2_global_nce": (c_int, [c_void_p] * 5 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_ema": (c_int, [c_void_p] * 5 + [c_int, c_float, c_float, c_void_p]),
+    "cp2_enqueue": (c_int, [c_void_p] * 3 + [c_int] * 3 + [c_void_p]),
+}
+# include/cp2_b200_debug.h — test-only CUDA-core reference kernels
+DEBUG_SIGNATURES = {
+    "cp2_dbg_dense_lse_simt": (c_int, [c_void_p] * 3 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_dbg_dense_grad_simt": (c_int, [c_void_p] * 10 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_dbg_global_nce_simt": (c_int, [c_void_p] * 4 + [c_float] + [c_int] * 3 + [c_void_p]),
+}
+
+EMA_CHUNK = 4096  # CP2_EMA_CHUNK
+
+_lib = None
+
+
+def load():
+    """Loads libcp2_b200.so once; raises if absent or incomplete."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(LIB_PATH):
+        raise RuntimeError(
+            f"cp2_b200: {LIB_PATH} not found. The CUDA extension is mandatory (no CPU or "
+            "PyTorch fallback exists): run `make -C cp2_b200/csrc` or `__graft_entry__.build()`.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for table in (SIGNATURES, DEBUG_SIGNATURES):
+        for name, (res, args) in table.items():
+            try:
+                fn = getattr(lib, name)
+            except AttributeError as e:
+                raise RuntimeError(f"cp2_b200: {LIB_PATH} does not export {name}") from e
+            fn.restype = res
+            fn.argtypes = args
+    if lib.cp2_abi_version() != 1:
+        raise RuntimeError(f"cp2_b200: ABI version {lib.cp2_abi_version()} != 1")
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().cp2_last_error()
+        raise RuntimeError(f"cp2_b200: {what} failed (code {rc}): {msg.decode() if msg else ''}")

@@ -1,0 +1,379 @@
+"""Host-side mirror of the reference's `builder.py` for the CP2 pre-training loss path.
+
+`MODEL` keeps the reference constructor, keyword `forward(...) -> 0-d loss`, buffers
+(`queue`, `queue_ptr`, `queue2`, `queue2_ptr`), sub-modules (`encoder_q`, `encoder_k`),
+meters and method names (builder.py:277-304, 476-482, 543-553, 557-649, 1124-1606), so it
+drops into the reference's `main.py` loop (main.py:390-461, 616-644) and its checkpoints
+interchange.  Everything between the encoder outputs and the scalar loss, plus the
+compositing, the EMA and the enqueue, runs in the sm_100a kernels of libcp2_b200.so
+(include/cp2_b200.h); torch supplies device memory, streams, autograd plumbing and NCCL.
+
+Scope: PretrainType.CP2 with MappingType.CP2 / NegativeType.NONE.  The
+other pre-training modes of the reference raise NotImplementedError here.
+
+Deliberate, documented deviations from the reference (none changes the loss):
+  * no `int(queue_ptr)` / `.item()` / `.cpu()` host syncs on the step: the queue pointer
+    lives on the device and the meters accumulate on the device, syncing only when read;
+  * no `queue.clone()` (builder.py:1396): the global kernel produces the backward's
+    queue-weighted sum in the forward pass, so enqueue may overwrite the queue before
+    `loss.backward()`;
+  * correlation-IoU bookkeeping and dense score quartiles (builder.py:1204-1257, 1298,
+    1401-1403) are loss-neutral in CP2 mode and are skipped (their torch restatements live in
+    the oracle; the IoU lists stay empty);
+  * wandb logging is left to the caller (`rank` is stored, nothing is logged here).
+"""
+from enum import Enum
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops
+
+
+# ---------------------------------------------------------------------------- enums
+class BackboneType(Enum):          # builder.py:30-38
+    DEEPLABV3 = 0
+    UNET_ENCODER_ONLY = 1
+    UNET_TRUNCATED = 2
+
+
+class MappingType(Enum):           # builder.py:41-49
+    CP2 = 0
+    PIXEL_ID = 1
+    REGION_ID = 2
+    PIXEL_REGION_ID = 3
+
+
+class NegativeType(Enum):          # builder.py:140-147
+    NONE = 0
+    FIXED = 1
+    AVERAGE = 2
+    MEDIAN = 3
+    HARD = 4
+
+
+class PretrainType(Enum):          # networks/segment_network.py:14-38
+    RANDOM = 0
+    NONE = 1
+    CP2 = 2
+    MIRROR = 3
+    BYOL = 4
+    MOCO = 5
+    PROPOSED = 6
+    PIXPRO = 7
+    DENSECL_IMGNET = 8
+    DINO_IMGNET = 9
+    BARLOWTWINS_IMGNET = 10
+    VICEREGL_IMGNET = 11
+    MOCO_IMGNET = 12
+    PIXPRO_IMGNET = 13
+    BYOL_IMGNET = 14
+    CP2_IMGNET = 15
+    MOSREP_IMGNET = 16
+    CLOVE_IMGNET = 17
+    DENSECL = 18
+    PROPOSED_V2 = 19
+
+
+# --------------------------------------------------------------------------- meters
+class AverageMeter(object):
+    """builder.py:51-73, with one change: `update` accepts 0-d device tensors and keeps the
+    running sum on the device, so a training step never waits for the GPU.  `val`, `avg`,
+    `sum` read back (and synchronise) only when somebody looks at them."""
+
+    def __init__(self, name, fmt=":f"):
+        self.name = name
+        self.fmt = fmt
+        self.reset()
+
+    def reset(self):
+        self._val = 0
+        self._sum = 0
+        self.count = 0
+
+    def update(self, val, n=1):
+        if torch.is_tensor(val):
+            val = val.detach()
+        self._val = val
+        self._sum = self._sum + val * n
+        self.count += n
+
+    @staticmethod
+    def _f(x):
+        return float(x) if torch.is_tensor(x) else x
+
+    @property
+    def val(self):
+        return self._f(self._val)
+
+    @property
+    def sum(self):
+        return self._f(self._sum)
+
+    @property
+    def avg(self):
+        return self._f(self._sum) / self.count if self.count else 0
+
+    def __str__(self):
+        fmtstr = "{name} {val" + self.fmt + "} ({avg" + self.fmt + "})"
+        return fmtstr.format(name=self.name, val=self.val, avg=self.avg)
+
+
+# ---------------------------------------------------------------------- collectives
+def _world():
+    return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+
+
+def _rank():
+    return dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
+
+
+@torch.no_grad()
+def concat_all_gather(tensor):
+    """builder.py:1710-1722: rank-ordered concatenation along dim 0, no gradient.  One
+    `all_gather_into_tensor` (ncclAllGather over NVLink on the B200 box, gloo on CPU tests)
+    straight into the contiguous output: no per-rank temporaries, no `cat`."""
+    world = _world()
+    if world == 1:
+        return tensor
+    tensor = tensor.contiguous()
+    out = torch.empty((world * tensor.shape[0],) + tuple(tensor.shape[1:]), dtype=tensor.dtype,
+                      device=tensor.device)
+    dist.all_gather_into_tensor(out, tensor)
+    return out
+
+
+def _default_encoder(cfg, dim):
+    """`build_segmentor(cfg.model)` (builder.py:365-371) when mmseg is importable, else the
+    torchvision ResNet-50 (OS16) + ASPP + contrast_conv stand-in of cp2_b200.encoder."""
+    try:
+        from mmseg.models import build_segmentor  # type: ignore
+        return build_segmentor(cfg.model, train_cfg=cfg.get("train_cfg"), test_cfg=cfg.get("test_cfg"))
+    except ImportError:
+        from .encoder import DeepLabV3Encoder
+        return DeepLabV3Encoder(dim=dim)
+
+
+# ---------------------------------------------------------------------------- MODEL
+class MODEL(nn.Module):
+    """Drop-in for the reference's `builder.MODEL` (builder.py:277-1706), CP2 mode.
+
+    Extra keyword-only arguments (not in the reference):
+      encoder_factory : callable returning one segmentor; replaces `build_segmentor(cfg.model)`
+                        (mmseg/mmcv are not installable here).  Called twice (q, k).
+      output_stride   : skip the reference's CPU probe forward (builder.py:392-397) and use
+                        this value.  When None the probe runs exactly as in the reference,
+                        including its side effect on encoder_q's BN running statistics.
+    """
+
+    def __init__(self, cfg, rank, dim=128, K=65536, m=0.999, instance_logits_temp=0.2,
+                 pretrain_from_scratch=False, include_background=False, lmbd_cp2_dense_loss=0.2,
+                 lmbd_pixel_corr_weight=1, lmbd_region_corr_weight=1, lmbd_not_corr_weight=1,
+                 negative_type=NegativeType.NONE, negative_scale=2, pretrain_type=PretrainType.CP2,
+                 backbone_type=BackboneType.DEEPLABV3, mapping_type=MappingType.CP2,
+                 dense_logits_temp=1, unet_truncated_dec_blocks=2, use_predictor=False,
+                 use_avgpool_global=False, use_symmetrical_loss=False, lmbd_coordinate=0,
+                 device=None, *, encoder_factory=None, output_stride=None):
+        super().__init__()
+        self.queue_len = K
+        self.momentum = m
+        self.temp_global = instance_logits_temp
+        self.dim = dim
+        self.include_background = include_background
+        self.lmbd_dense_loss = lmbd_cp2_dense_loss
+        self.device = device
+        self.rank = rank
+        self.epoch = 0
+        self.temp_local = dense_logits_temp
+        self.use_predictor = use_predictor
+        self.use_avgpool_global = use_avgpool_global
+        self.use_symmetrical_loss = use_symmetrical_loss
+        assert 0 <= lmbd_coordinate <= 1, f"{lmbd_coordinate = }"
+        self.lmbd_coordinate = lmbd_coordinate
+
+        # builder.py:325-347 — the same validation, by enum NAME so that the reference's
+        # own enum members (main.py:136-140) are accepted as well
+        mapping_type = MappingType[getattr(mapping_type, "name", mapping_type)]
+        pretrain_type = PretrainType[getattr(pretrain_type, "name", pretrain_type)]
+        negative_type = NegativeType[getattr(negative_type, "name", negative_type)]
+        backbone_type = BackboneType[getattr(backbone_type, "name", backbone_type)]
+        if mapping_type == MappingType.CP2:
+            assert lmbd_pixel_corr_weight == 1
+            assert lmbd_region_corr_weight == 1
+            assert lmbd_not_corr_weight == 1
+        self.mapping_type = mapping_type
+        self.lmbd_pixel_corr_weight = lmbd_pixel_corr_weight
+        self.lmbd_region_corr_weight = lmbd_region_corr_weight
+        self.lmbd_not_corr_weight = lmbd_not_corr_weight
+        self.pretrain_type = pretrain_type
+        self.negative_type = negative_type
+        self.negative_scale = negative_scale
+        self.backbone_type = backbone_type
+        if pretrain_type != PretrainType.CP2:
+            raise NotImplementedError(
+                f"cp2_b200 implements the CP2 pre-training path only ({pretrain_type = }); "
+                "see SURVEY.md section 8(f) for the order in which the other modes follow")
+        assert negative_type == NegativeType.NONE       # builder.py:431-433
+        assert mapping_type == MappingType.CP2
+        if backbone_type != BackboneType.DEEPLABV3 and encoder_factory is None:
+            raise NotImplementedError(f"{backbone_type = } needs an encoder_factory (smp is not installed)")
+
+        make = encoder_factory if encoder_factory is not None else (lambda: _default_encoder(cfg, dim))
+        self.encoder_q = make()
+        self.encoder_k = make()
+        if encoder_factory is None and not pretrain_from_scratch:
+            for enc in (self.encoder_q, self.encoder_k):       # builder.py:375-378
+                if hasattr(enc, "backbone") and hasattr(enc.backbone, "init_weights"):
+                    enc.backbone.init_weights()
+
+        if output_stride is None:                              # builder.py:392-402
+            test_sample = torch.rand(2, 3, 224, 224)
+            self.output_stride = int(test_sample.shape[2] / self.encoder_q(test_sample).shape[2])
+        else:
+            self.output_stride = int(output_stride)
+        self.backbone_output_stride = self.output_stride
+        if output_stride is None and hasattr(self.encoder_q, "backbone"):
+            test_sample = torch.rand(2, 3, 224, 224)
+            shp = self.encoder_q.backbone(test_sample)[3].shape
+            self.backbone_output_stride = int(test_sample.shape[2] / shp[2])
+
+        # builder.py:464-469: parameters only — BN buffers are not copied
+        for param_q, param_k in zip(self.encoder_q.parameters(), self.encoder_k.parameters()):
+            param_k.data.copy_(param_q.data)
+            param_k.requires_grad = False
+
+        # builder.py:476-482 (same RNG draws, same order)
+        self.register_buffer("queue", torch.randn(self.dim, self.queue_len))
+        self.queue = F.normalize(self.queue, dim=0)
+        self.register_buffer("queue_ptr", torch.zeros(1, dtype=torch.long))
+        self.register_buffer("queue2", torch.randn(self.dim, self.queue_len))
+        self.queue2 = F.normalize(self.queue2, dim=0)
+        self.register_buffer("queue2_ptr", torch.zeros(1, dtype=torch.long))
+
+        self.loss_o = AverageMeter("Loss_overall", ":.4f")      # builder.py:543-553
+        self.loss_i = AverageMeter("Loss_ins", ":.4f")
+        self.loss_d = AverageMeter("Loss_den", ":.4f")
+        self.acc_ins = AverageMeter("Acc_ins", ":6.2f")
+        self.acc_seg = AverageMeter("Acc_seg", ":6.2f")
+        self.cross_image_variance_source = AverageMeter("Cross_Image_Variance_Source", ":6.2f")
+        self.cross_image_variance_target = AverageMeter("Cross_Image_Variance_Target", ":6.2f")
+        self.correlation_ious = []
+        self.masked_correlation_ious = []
+        self._ema_plan = None
+
+    # ------------------------------------------------------------------ K4
+    @torch.no_grad()
+    def _momentum_update_key_encoder(self):
+        """builder.py:557-567 as ONE kernel launch over every parameter (bit-exact)."""
+        pq = [p.data for p in self.encoder_q.parameters()]
+        pk = [p.data for p in self.encoder_k.parameters()]
+        if self._ema_plan is None:
+            self._ema_plan = ops.EmaPlan(pq, pk)
+        else:
+            self._ema_plan.rebind(pq, pk)
+        self._ema_plan.apply(self.momentum)
+
+    # ------------------------------------------------------------------ K5
+    @torch.no_grad()
+    def _dequeue_and_enqueue(self, keys):
+        """builder.py:569-587: all-gather, then transposed write at the device-side pointer
+        with wrap-around.  No host sync."""
+        ops.enqueue(concat_all_gather(keys), self.queue, self.queue_ptr)
+
+    @torch.no_grad()
+    def _dequeue_and_enqueue2(self, keys):
+        """builder.py:589-607."""
+        ops.enqueue(concat_all_gather(keys), self.queue2, self.queue2_ptr)
+
+    # ----------------------------------------------------------------- a11
+    @torch.no_grad()
+    def _batch_shuffle_ddp(self, x):
+        """builder.py:609-630.  Same RNG contract: every rank draws a CPU `randperm`, rank
+        0's is broadcast."""
+        batch_size_this = x.shape[0]
+        x_gather = concat_all_gather(x)
+        batch_size_all = x_gather.shape[0]
+        num_gpus = batch_size_all // batch_size_this
+        idx_shuffle = torch.randperm(batch_size_all).to(x.device)
+        if _world() > 1:
+            dist.broadcast(idx_shuffle, src=0)
+        idx_unshuffle = torch.argsort(idx_shuffle)
+        idx_this = idx_shuffle.view(num_gpus, -1)[_rank()]
+        return x_gather[idx_this], idx_unshuffle
+
+    @torch.no_grad()
+    def _batch_unshuffle_ddp(self, x, idx_unshuffle):
+        """builder.py:632-649."""
+        batch_size_this = x.shape[0]
+        x_gather = concat_all_gather(x)
+        num_gpus = x_gather.shape[0] // batch_size_this
+        idx_this = idx_unshuffle.view(num_gpus, -1)[_rank()]
+        return x_gather[idx_this]
+
+    def forward(self, **kwargs):                               # builder.py:651-665
+        return self.forward_cp2(**kwargs)
+
+    # ---------------------------------------------------------- forward_cp2
+    def forward_cp2(self, img_a, img_b, bg0, bg1, visualize=False, step=0, new_epoch=False,
+                    pixel_ids_a=None, pixel_ids_b=None, region_ids_a=None, region_ids_b=None):
+        """builder.py:1124-1606 for MappingType.CP2 / NegativeType.NONE.
+
+        The pixel / region id maps only feed loss-neutral bookkeeping in this mode
+        (corr_weights is all ones, builder.py:329-332, 1238-1243) and are ignored.
+        """
+        os_ = self.output_stride
+        keep = bool(visualize) and self.rank == 0
+        # K1: builder.py:1146-1159 (+ the mask part of the [OS/2::OS] subsample)
+        img_a, mask_a, full_a = ops.composite(img_a, bg0, os_, want_full_mask=keep)
+        img_b, mask_b, full_b = ops.composite(img_b, bg1, os_, want_full_mask=keep)
+        if keep:
+            self.last_visualization = {"img_a": img_a, "img_b": img_b, "mask_a": full_a, "mask_b": full_b}
+        n = img_a.shape[0]
+        mask_a = mask_a.reshape(n, -1)
+        mask_b = mask_b.reshape(n, -1)
+
+        q = self.encoder_q(img_a)                              # builder.py:1260 (cuDNN, out of scope)
+        with torch.no_grad():                                  # builder.py:1271-1277
+            self._momentum_update_key_encoder()
+            img_b, idx_unshuffle = self._batch_shuffle_ddp(img_b)
+            k = self.encoder_k(img_b)
+            k = self._batch_unshuffle_ddp(k, idx_unshuffle)
+
+        # K2a/K2/K3 + autograd: builder.py:1261-1268, 1279-1292, 1392-1397, 1414-1439
+        loss, loss_ins, loss_dense, k_pos, q_pos, stats = ops.cp2_loss(
+            q, k, mask_a, mask_b, self.queue, self.temp_global, self.temp_local, self.lmbd_dense_loss,
+            self.include_background)
+        self._dequeue_and_enqueue(k_pos)                       # builder.py:1426
+
+        if new_epoch and self.rank == 0:
+            self.epoch += 1
+        with torch.no_grad():                                  # builder.py:1553-1563, no syncs
+            self.loss_o.update(loss, n)
+            self.loss_i.update(loss_ins, n)
+            self.loss_d.update(loss_dense, n)
+            self.acc_ins.update(stats["acc_ins"], n)
+            self.acc_seg.update(stats["acc_seg"], n)
+            self.cross_image_variance_source.update(q_pos.std(0).mean(), n)
+            self.cross_image_variance_target.update(k_pos.std(0).mean(), n)
+        return loss
+
+    def on_train_epoch_end(self, step):                        # builder.py:1608
+        return {"train/loss": self.loss_o.avg}
+
+    def reset_metrics(self):
+        for mtr in (self.loss_o, self.loss_i, self.loss_d, self.acc_ins, self.acc_seg,
+                    self.cross_image_variance_source, self.cross_image_variance_target):
+            mtr.reset()
+        self.correlation_ious = []
+        self.masked_correlation_ious = []
+
+    def _accuracy(self, output, target, topk=(1,)):            # builder.py:1690-1706
+        with torch.no_grad():
+            maxk = max(topk)
+            batch_size = target.size(0)
+            _, pred = output.topk(maxk, 1, True, True)
+            correct = pred.t().eq(target.view(1, -1))
+            return [correct[:k_].reshape(-1).float().sum(0, keepdim=True).mul_(100.0 / batch_size)
+                    for k_ in topk]

@@ -1,0 +1,94 @@
+// K1 — copy-paste compositing (reference builder.py:1146-1159).
+// HBM-bound elementwise: 2 reads + 1 write of [B,3,H,W] f32 per view
+// (algorithmic bytes 3*B*3*H*W*4 + B*hs*ws*4).  One thread handles 4 consecutive
+// pixels of all three channels with 128-bit loads/stores; the background's channel 0
+// is read once and yields the mask for all channels.
+#include "common.cuh"
+
+namespace {
+
+template <bool kVec>
+__global__ void __launch_bounds__(256)
+composite_kernel(const float *__restrict__ img, const float *__restrict__ bg, float *__restrict__ out,
+                 float *__restrict__ mask_full, float *__restrict__ mask_ds, int B, int H, int W,
+                 int os, int hs, int ws) {
+  constexpr int V = kVec ? 4 : 1;
+  const long long plane = (long long)H * W;
+  const long long groups_per_img = plane / V;
+  const long long total = (long long)B * groups_per_img;
+  const int o = os / 2;
+  for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < total;
+       g += (long long)gridDim.x * blockDim.x) {
+    const long long b = g / groups_per_img;
+    const long long pix = (g - b * groups_per_img) * V;   // first pixel of the group
+    const long long base = b * 3 * plane + pix;
+    float m[V], bgv[3][V], im[3][V];
+    if constexpr (kVec) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float4 t = __ldcs(reinterpret_cast<const float4 *>(bg + base + c * plane));
+        bgv[c][0] = t.x; bgv[c][1] = t.y; bgv[c][2] = t.z; bgv[c][3] = t.w;
+        const float4 u = __ldcs(reinterpret_cast<const float4 *>(img + base + c * plane));
+        im[c][0] = u.x; im[c][1] = u.y; im[c][2] = u.z; im[c][3] = u.w;
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { bgv[c][0] = bg[base + c * plane]; im[c][0] = img[base + c * plane]; }
+    }
+#pragma unroll
+    for (int v = 0; v < V; ++v) m[v] = (bgv[0][v] == 0.0f) ? 1.0f : 0.0f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      float r[V];
+#pragma unroll
+      for (int v = 0; v < V; ++v) r[v] = im[c][v] * m[v] + bgv[c][v];   // product is exact (m in {0,1})
+      if constexpr (kVec)
+        __stcs(reinterpret_cast<float4 *>(out + base + c * plane), make_float4(r[0], r[1], r[2], r[3]));
+      else
+        out[base + c * plane] = r[0];
+    }
+    if (mask_full != nullptr) {
+      if constexpr (kVec)
+        __stcs(reinterpret_cast<float4 *>(mask_full + b * plane + pix), make_float4(m[0], m[1], m[2], m[3]));
+      else
+        mask_full[b * plane + pix] = m[0];
+    }
+    const int h = (int)(pix / W);
+    if (h >= o && (h - o) % os == 0) {
+      const int w0 = (int)(pix - (long long)h * W);
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        const int w = w0 + v;
+        if (w >= o && (w - o) % os == 0)
+          mask_ds[(b * hs + (h - o) / os) * ws + (w - o) / os] = m[v];
+      }
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" int cp2_composite(const float *img, const float *bg, float *out, float *mask_full,
+                             float *mask_ds, int B, int H, int W, int os, void *stream) {
+  CP2_REQUIRE(img && bg && out && mask_ds, "cp2_composite: null pointer");
+  CP2_REQUIRE(B >= 0 && H > 0 && W > 0 && os > 0, "cp2_composite: bad shape B=%d H=%d W=%d os=%d", B, H, W, os);
+  if (B == 0) return CP2_OK;
+  const int o = os / 2;
+  const int hs = H > o ? (H - o + os - 1) / os : 0;
+  const int ws = W > o ? (W - o + os - 1) / os : 0;
+  auto aligned = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+  const bool vec = (W % 4 == 0) && aligned(img) && aligned(bg) && aligned(out) &&
+                   (mask_full == nullptr || aligned(mask_full));
+  const long long groups = (long long)B * H * W / (vec ? 4 : 1);
+  const int threads = 256;
+  long long blocks = (groups + threads - 1) / threads;
+  const long long cap = (long long)cp2_num_sms() * 16;     // grid-stride; whole waves of 148 SMs
+  if (blocks > cap) blocks = cap;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (vec)
+    composite_kernel<true><<<(unsigned)blocks, threads, 0, st>>>(img, bg, out, mask_full, mask_ds, B, H, W, os, hs, ws);
+  else
+    composite_kernel<false><<<(unsigned)blocks, threads, 0, st>>>(img, bg, out, mask_full, mask_ds, B, H, W, os, hs, ws);
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}

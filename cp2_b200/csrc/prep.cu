@@ -1,0 +1,117 @@
+// K2a — per-pixel L2 normalisation, masked pooling and bf16 transpose
+// (reference builder.py:1261-1268 / 1279-1285).
+// HBM-bound: reads feat [B,C,P] f32 once, writes fhat_t [B,P,C] bf16
+// (algorithmic bytes 6*B*C*P).  A CTA owns 32 consecutive pixels of one image: the
+// loads are coalesced along P (128 B per warp per channel), the tile is transposed
+// through shared memory, and the stores are coalesced along C.  Pooled sums are
+// reduced per tile into scratch and summed over tiles by a second, tiny kernel in a
+// fixed order (deterministic).
+#include "common.cuh"
+
+namespace {
+
+constexpr int PT = 32;   // pixels per CTA
+
+template <int C>
+__global__ void __launch_bounds__(256)
+prep_kernel(const float *__restrict__ feat, const float *__restrict__ mask,
+            __nv_bfloat16 *__restrict__ fhat_t, float *__restrict__ inv_norm,
+            float *__restrict__ scratch, int P, int tiles) {
+  __shared__ float tile[C][PT + 1];
+  __shared__ float ssq[8][PT];
+  __shared__ float den[PT];
+  __shared__ float mk[PT];
+  const int b = blockIdx.y, tl = blockIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int x = tl * PT + lane;
+  const bool valid = x < P;
+  const float *__restrict__ src = feat + (long long)b * C * P + x;
+  float sum = 0.f;
+#pragma unroll 4
+  for (int c = warp; c < C; c += 8) {
+    const float v = valid ? __ldcs(src + (long long)c * P) : 0.f;
+    tile[c][lane] = v;
+    sum = fmaf(v, v, sum);
+  }
+  ssq[warp][lane] = sum;
+  __syncthreads();
+  if (warp == 0) {
+    float tot = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) tot += ssq[w][lane];
+    const float d = fmaxf(sqrtf(tot), 1e-12f);       // F.normalize eps
+    den[lane] = d;
+    mk[lane] = valid ? mask[(long long)b * P + x] : 0.f;
+    if (valid) inv_norm[(long long)b * P + x] = 1.0f / d;
+  }
+  __syncthreads();
+  {
+    const float d = den[lane], m = mk[lane];
+    float *__restrict__ part = scratch + ((long long)(b * tiles + tl) * 2) * C;
+    for (int c = warp; c < C; c += 8) {
+      const float v = tile[c][lane] / d;
+      tile[c][lane] = v;
+      float pos = v * m, neg = valid ? v * (1.0f - m) : 0.f;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        pos += __shfl_xor_sync(0xffffffffu, pos, o);
+        neg += __shfl_xor_sync(0xffffffffu, neg, o);
+      }
+      if (lane == 0) { part[c] = pos; part[C + c] = neg; }
+    }
+  }
+  __syncthreads();
+  // transposed store: warp w writes pixels w*4..w*4+3, 64 channels (128 B) per pass
+#pragma unroll
+  for (int pp = 0; pp < PT / 8; ++pp) {
+    const int p = warp * (PT / 8) + pp;
+    const int xx = tl * PT + p;
+    if (xx < P) {
+      __nv_bfloat162 *dst = reinterpret_cast<__nv_bfloat162 *>(fhat_t + ((long long)b * P + xx) * C);
+#pragma unroll
+      for (int j = 0; j < C / 64; ++j) {
+        const int c = j * 64 + lane * 2;
+        dst[c >> 1] = __floats2bfloat162_rn(tile[c][p], tile[c + 1][p]);
+      }
+    }
+  }
+}
+
+__global__ void prep_reduce_kernel(const float *__restrict__ scratch, float *__restrict__ pos_sum,
+                                   float *__restrict__ neg_sum, int C, int tiles) {
+  const int b = blockIdx.x;
+  for (int t = threadIdx.x; t < 2 * C; t += blockDim.x) {
+    const float *p = scratch + (long long)b * tiles * 2 * C + t;
+    float s = 0.f;
+    for (int tl = 0; tl < tiles; ++tl) s += p[(long long)tl * 2 * C];
+    if (t < C) pos_sum[(long long)b * C + t] = s;
+    else neg_sum[(long long)b * C + (t - C)] = s;
+  }
+}
+
+}  // namespace
+
+extern "C" int cp2_prep_tiles(int P) { return cp2_cdiv(P, PT); }
+
+extern "C" int cp2_prep_features(const float *feat, const float *mask, void *fhat_t, float *inv_norm,
+                                 float *pos_sum, float *neg_sum, float *scratch, int B, int C, int P,
+                                 void *stream) {
+  CP2_REQUIRE(feat && mask && fhat_t && inv_norm && pos_sum && neg_sum && scratch, "cp2_prep_features: null pointer");
+  CP2_REQUIRE(B >= 0 && P > 0, "cp2_prep_features: bad shape B=%d P=%d", B, P);
+  CP2_REQUIRE(C == 64 || C == 128 || C == 192 || C == 256, "cp2_prep_features: C=%d unsupported (64,128,192,256)", C);
+  if (B == 0) return CP2_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int tiles = cp2_prep_tiles(P);
+  dim3 grid(tiles, B);
+  auto *out = static_cast<__nv_bfloat16 *>(fhat_t);
+  switch (C) {
+    case 64: prep_kernel<64><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, P, tiles); break;
+    case 128: prep_kernel<128><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, P, tiles); break;
+    case 192: prep_kernel<192><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, P, tiles); break;
+    default: prep_kernel<256><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, P, tiles); break;
+  }
+  CP2_LAUNCH_CHECK();
+  prep_reduce_kernel<<<B, 256, 0, st>>>(scratch, pos_sum, neg_sum, C, tiles);
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}

@@ -1,0 +1,262 @@
+"""Host-side wrappers: torch tensors in, C-ABI calls on the current CUDA stream.
+
+torch is used for device memory, streams and autograd plumbing only; every op on the
+hot path is a kernel of libcp2_b200.so.  All wrappers raise if their inputs are not
+CUDA tensors — there is no CPU path.
+"""
+import torch
+
+from . import _lib
+
+_EPS = 1e-12   # F.normalize eps
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("cp2_b200 ops need CUDA tensors (B200, sm_100a); there is no CPU fallback")
+
+
+def _f32c(t):
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+# ------------------------------------------------------------------ K1
+def composite(img, bg, output_stride, want_full_mask=False, out=None):
+    """builder.py:1146-1159.  Returns (composited [B,3,H,W], mask_ds [B,hs,ws], mask_full|None)."""
+    _need_cuda(img, bg)
+    img, bg = _f32c(img), _f32c(bg)
+    B, ch, H, W = img.shape
+    assert ch == 3 and bg.shape == img.shape, f"{img.shape = }, {bg.shape = }"
+    o = output_stride // 2
+    hs, ws = len(range(o, H, output_stride)), len(range(o, W, output_stride))
+    out = torch.empty_like(img) if out is None else out
+    mask_ds = torch.empty((B, hs, ws), device=img.device, dtype=torch.float32)
+    mask_full = torch.empty((B, H, W), device=img.device, dtype=torch.float32) if want_full_mask else None
+    lib = _lib.load()
+    _lib.check(lib.cp2_composite(_ptr(img), _ptr(bg), _ptr(out), _ptr(mask_full), _ptr(mask_ds),
+                                 B, H, W, output_stride, _stream()), "cp2_composite")
+    return out, mask_ds, mask_full
+
+
+# ----------------------------------------------------------------- K2a
+def prep_features(feat, mask):
+    """builder.py:1261-1268.  feat [B,C,P] f32, mask [B,P] -> (fhat_t bf16 [B,P,C], inv_norm [B,P],
+    pos_sum [B,C], neg_sum [B,C])."""
+    _need_cuda(feat, mask)
+    feat, mask = _f32c(feat), _f32c(mask)
+    B, C, P = feat.shape
+    lib = _lib.load()
+    dev = feat.device
+    fhat_t = torch.empty((B, P, C), device=dev, dtype=torch.bfloat16)
+    inv_norm = torch.empty((B, P), device=dev, dtype=torch.float32)
+    pos = torch.empty((B, C), device=dev, dtype=torch.float32)
+    neg = torch.empty((B, C), device=dev, dtype=torch.float32)
+    scratch = torch.empty((B, lib.cp2_prep_tiles(P), 2, C), device=dev, dtype=torch.float32)
+    _lib.check(lib.cp2_prep_features(_ptr(feat), _ptr(mask), _ptr(fhat_t), _ptr(inv_norm), _ptr(pos),
+                                     _ptr(neg), _ptr(scratch), B, C, P, _stream()), "cp2_prep_features")
+    return fhat_t, inv_norm, pos, neg
+
+
+# ------------------------------------------------------------------ K2
+def dense_lse(qhat_t, khat_t, inv_tau):
+    """lse[n,y] = log sum_x exp(qhat[n,x].khat[n,y] * inv_tau).  builder.py:1289,1431-1432."""
+    _need_cuda(qhat_t, khat_t)
+    B, P, C = qhat_t.shape
+    lse = torch.empty((B, P), device=qhat_t.device, dtype=torch.float32)
+    _lib.check(_lib.load().cp2_dense_lse(_ptr(qhat_t), _ptr(khat_t), _ptr(lse), float(inv_tau), B, C, P,
+                                        _stream()), "cp2_dense_lse")
+    return lse
+
+
+def dense_grad(qhat_t, khat_t, lse, mask_a, mask_b, inv_norm, alpha, v1, v2, inv_tau):
+    """Fused backward of the dense + global loss w.r.t. the query features -> dq [B,C,P]."""
+    B, P, C = qhat_t.shape
+    dq = torch.empty((B, C, P), device=qhat_t.device, dtype=torch.float32)
+    _lib.check(_lib.load().cp2_dense_grad(_ptr(qhat_t), _ptr(khat_t), _ptr(lse), _ptr(mask_a), _ptr(mask_b),
+                                         _ptr(inv_norm), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(dq),
+                                         float(inv_tau), B, C, P, _stream()), "cp2_dense_grad")
+    return dq
+
+
+# ------------------------------------------------------------------ K3
+def global_nce(q_pos, queue, inv_tau):
+    """One pass over the queue: z[b] = sum_k exp((l-1)/tau), g[b,:] = sum_k exp((l-1)/tau) queue[:,k]."""
+    _need_cuda(q_pos, queue)
+    q_pos = _f32c(q_pos)
+    B, C = q_pos.shape
+    assert queue.dtype == torch.float32 and queue.is_contiguous() and queue.shape[0] == C
+    K = queue.shape[1]
+    lib = _lib.load()
+    dev = q_pos.device
+    z = torch.empty((B,), device=dev, dtype=torch.float32)
+    g = torch.empty((B, C), device=dev, dtype=torch.float32)
+    scratch = torch.empty((max(1, lib.cp2_global_scratch_floats(B, C)),), device=dev, dtype=torch.float32)
+    _lib.check(lib.cp2_global_nce(_ptr(q_pos), _ptr(queue), _ptr(z), _ptr(g), _ptr(scratch), float(inv_tau),
+                                  B, C, K, _stream()), "cp2_global_nce")
+    return z, g
+
+
+# ------------------------------------------------------------------ K4
+class EmaPlan:
+    """Device-side pointer / chunk tables for cp2_ema (built once per model; rebuilt if any
+    parameter storage moves).  builder.py:557-567."""
+
+    def __init__(self, params_q, params_k):
+        self._key = None
+        self.rebind(params_q, params_k)
+        self._build()
+
+    def rebind(self, params_q, params_k):
+        """Points the plan at (possibly re-allocated) parameter tensors; the device tables are
+        rebuilt lazily by `apply` only if an address or size actually changed."""
+        self.params_q = list(params_q)
+        self.params_k = list(params_k)
+        assert len(self.params_q) == len(self.params_k)
+
+    def _signature(self):
+        return tuple((pq.data_ptr(), pk.data_ptr(), pk.numel()) for pq, pk in zip(self.params_q, self.params_k))
+
+    def _build(self):
+        _need_cuda(*self.params_q, *self.params_k)
+        for pq, pk in zip(self.params_q, self.params_k):
+            if pq.dtype != torch.float32 or pk.dtype != torch.float32:
+                raise RuntimeError("cp2_ema: fp32 parameters only")
+            if not (pq.is_contiguous() and pk.is_contiguous()) or pq.shape != pk.shape:
+                raise RuntimeError("cp2_ema: parameters must be contiguous and shape-matched")
+        dev = self.params_k[0].device
+        self.n_params = sum(p.numel() for p in self.params_k)
+        ct, ci = [], []
+        for t, pk in enumerate(self.params_k):
+            n = (pk.numel() + _lib.EMA_CHUNK - 1) // _lib.EMA_CHUNK
+            ct.extend([t] * n)
+            ci.extend(range(n))
+        i64 = dict(device=dev, dtype=torch.int64)
+        self.q_ptrs = torch.tensor([p.data_ptr() for p in self.params_q], **i64)
+        self.k_ptrs = torch.tensor([p.data_ptr() for p in self.params_k], **i64)
+        self.numel = torch.tensor([p.numel() for p in self.params_k], **i64)
+        self.chunk_tensor = torch.tensor(ct, device=dev, dtype=torch.int32)
+        self.chunk_index = torch.tensor(ci, device=dev, dtype=torch.int32)
+        self.n_chunks = len(ct)
+        self._key = self._signature()
+
+    @torch.no_grad()
+    def apply(self, m):
+        if self._signature() != self._key:
+            self._build()
+        # the reference's scalars: m and (1.0 - m) evaluated in double, rounded to fp32 by the op
+        _lib.check(_lib.load().cp2_ema(_ptr(self.q_ptrs), _ptr(self.k_ptrs), _ptr(self.numel),
+                                      _ptr(self.chunk_tensor), _ptr(self.chunk_index), self.n_chunks,
+                                      float(m), float(1.0 - m), _stream()), "cp2_ema")
+
+
+# ------------------------------------------------------------------ K5
+@torch.no_grad()
+def enqueue(keys_all, queue, queue_ptr):
+    """builder.py:574-587 on device: queue[:, (ptr+i) % K] = keys_all[i]; ptr = (ptr+n) % K."""
+    _need_cuda(keys_all, queue, queue_ptr)
+    keys_all = _f32c(keys_all)
+    n, C = keys_all.shape
+    assert queue.dtype == torch.float32 and queue.is_contiguous() and queue.shape[0] == C
+    assert queue_ptr.dtype == torch.int64 and queue_ptr.numel() == 1
+    _lib.check(_lib.load().cp2_enqueue(_ptr(keys_all), _ptr(queue), _ptr(queue_ptr), n, C, queue.shape[1],
+                                      _stream()), "cp2_enqueue")
+
+
+# ------------------------------------------------- fused loss (a5 + a6 + a7 + a12)
+def _unit(s):
+    n = s.norm(dim=1, keepdim=True)
+    d = n.clamp_min(_EPS)
+    return s / d, d, n
+
+
+def _unit_bwd(dy, y, d, n):
+    """Backward of y = s / max(||s||, eps) (F.normalize)."""
+    proj = dy - y * (y * dy).sum(dim=1, keepdim=True)
+    return torch.where(n > _EPS, proj, dy) / d
+
+
+class CP2LossFunction(torch.autograd.Function):
+    """Dense + global CP2 loss from the two encoder outputs (builder.py:1260-1268, 1279-1292,
+    1392-1397, 1414-1439), MappingType.CP2 / NegativeType.NONE.
+
+    forward(q [B,C,h,w], k [B,C,h,w], mask_a [B,P], mask_b [B,P], queue [C,K], ...) ->
+        (loss, loss_ins, loss_dense, k_pos, q_pos, l_pos)
+    Only `loss` carries a gradient, and only to q (keys and queue are detached in the
+    reference, builder.py:1271,1396).  Backward is ONE kernel (cp2_dense_grad): every
+    rank-1 term is folded into per-image vectors computed here on [B,C] tensors.
+    """
+
+    @staticmethod
+    def forward(ctx, q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense, include_background):
+        B, C = q.shape[0], q.shape[1]
+        qf = _f32c(q.detach()).reshape(B, C, -1)
+        kf = _f32c(k.detach()).reshape(B, C, -1)
+        mask_a, mask_b = _f32c(mask_a), _f32c(mask_b)
+        tg, tl = float(temp_global), float(temp_local)
+        qh, q_inv, sq, snq = prep_features(qf, mask_a)
+        kh, _, sk, snk = prep_features(kf, mask_b)
+        q_pos, dq_, nq_ = _unit(sq)
+        k_pos, _, _ = _unit(sk)
+        # ---- global InfoNCE: the queue part is one kernel; the 1-3 extra logits are [B]-sized
+        z, G = global_nce(q_pos, queue, 1.0 / tg)
+        l_pos = (q_pos * k_pos).sum(dim=1)
+        e_pos = torch.exp((l_pos - 1.0) / tg)
+        Z = z + e_pos
+        num = G + e_pos[:, None] * k_pos
+        if include_background:
+            q_neg, dn_, nn_ = _unit(snq)
+            k_neg, _, _ = _unit(snk)
+            e_nq = torch.exp(((q_pos * q_neg).sum(dim=1) - 1.0) / tg)
+            e_nk = torch.exp(((q_pos * k_neg).sum(dim=1) - 1.0) / tg)
+            Z = Z + e_nq + e_nk
+            num = num + e_nq[:, None] * q_neg + e_nk[:, None] * k_neg
+        loss_ins = (torch.log(Z) + (1.0 - l_pos) / tg).mean()
+        # ---- dense InfoNCE: column LSE on the tensor cores, rank-1 positive term here
+        lse = dense_lse(qh, kh, 1.0 / tl)
+        A = mask_a.sum(dim=1)
+        Bm = mask_b.sum(dim=1)
+        dense_n = (mask_b * lse).sum(dim=1) / Bm - (sq * sk).sum(dim=1) / (tl * A * Bm)
+        loss_dense = dense_n.mean()
+        loss = loss_ins + loss_dense * lmbd_dense
+        # ---- backward coefficients for a unit upstream gradient
+        dqpos = (num / Z[:, None] - k_pos) / (B * tg)
+        v1 = _unit_bwd(dqpos, q_pos, dq_, nq_) - (lmbd_dense / B) * sk / (tl * A * Bm)[:, None]
+        v2 = None
+        if include_background:
+            dqneg = (e_nq / Z)[:, None] * q_pos / (B * tg)
+            v2 = _unit_bwd(dqneg, q_neg, dn_, nn_).contiguous()
+        alpha = lmbd_dense / (B * Bm * tl)
+        ctx.save_for_backward(qh, kh, lse, mask_a, mask_b, q_inv, alpha.contiguous(), v1.contiguous(), v2)
+        ctx.inv_tl = 1.0 / tl
+        ctx.q_shape = q.shape
+        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos)
+        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos
+
+    @staticmethod
+    def backward(ctx, g_loss, *_unused):
+        qh, kh, lse, mask_a, mask_b, q_inv, alpha, v1, v2 = ctx.saved_tensors
+        g = g_loss.reshape(())
+        dq = dense_grad(qh, kh, lse, mask_a, mask_b, q_inv, (alpha * g).contiguous(), (v1 * g).contiguous(),
+                        None if v2 is None else (v2 * g).contiguous(), ctx.inv_tl)
+        return dq.reshape(ctx.q_shape), None, None, None, None, None, None, None, None
+
+
+def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_dense=0.2,
+             include_background=False):
+    """-> (loss, loss_ins, loss_dense, k_pos, q_pos, stats); only `loss` has a gradient (to q)."""
+    loss, loss_ins, loss_dense, k_pos, q_pos, l_pos = CP2LossFunction.apply(
+        q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense, include_background)
+    nan = torch.full((), float("nan"), device=loss.device)
+    stats = {"l_pos": l_pos, "acc_ins": nan, "acc_seg": nan}
+    return loss, loss_ins, loss_dense, k_pos, q_pos, stats

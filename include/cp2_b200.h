@@ -1,0 +1,123 @@
+/* cp2_b200 — C ABI of the B200-native CP2 pre-training loss hot path.
+ *
+ * One shared library (cp2_b200/csrc/libcp2_b200.so, sm_100a only) exports exactly the
+ * entry points below.  Each replaces a span of the reference's Python
+ * (kimathikaai/CP2; citations are file:line under /root/reference) that today runs as
+ * a string of ATen/cuBLAS/NCCL library calls.
+ *
+ * Conventions (all entry points)
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless its
+ *     name ends in _host; the caller (torch) owns every buffer, nothing is
+ *     allocated, freed or retained across calls;
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); no
+ *     entry point synchronises the device or the stream;
+ *   - returns 0 on success, a negative CP2_E_* code otherwise and never throws;
+ *     cp2_last_error() then holds a thread-local human-readable message;
+ *   - re-entrant across streams and host threads; no global mutable device state.
+ */
+#ifndef CP2_B200_H_
+#define CP2_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CP2_ABI_VERSION 1
+
+#define CP2_OK 0
+#define CP2_E_INVALID (-1)      /* bad shape / null pointer / unsupported dim          */
+#define CP2_E_CUDA (-2)         /* a CUDA runtime/driver call failed (see last_error)  */
+#define CP2_E_UNSUPPORTED (-3)  /* device is not sm_100 or driver lacks TMA encode     */
+
+int cp2_abi_version(void);
+const char *cp2_last_error(void);
+
+/* K1 — copy-paste compositing of one view.
+ * Replaces builder.py:1146-1152 (mask from channel 0 of the background, img*mask+bg)
+ * and the mask part of the stride subsample builder.py:1155-1159 / 1173-1177.
+ *   img, bg, out : [B,3,H,W] f32 NCHW (out may alias img)
+ *   mask_full    : [B,H,W] f32 or NULL (only the visualisation path needs it)
+ *   mask_ds      : [B,hs,ws] f32, hs = len(range(os/2,H,os)), ws likewise
+ * Bit-exact with the reference. */
+int cp2_composite(const float *img, const float *bg, float *out, float *mask_full,
+                  float *mask_ds, int B, int H, int W, int os, void *stream);
+
+/* K2a — per-pixel L2 normalisation + masked pooling + bf16 transpose.
+ * Replaces builder.py:1261-1268 (query) / 1279-1285 (key): F.normalize(dim=1) and the
+ * two `ncx,nx->nc` einsums (the outer F.normalize of the pooled vectors is left to
+ * the caller: it is [B,C]).
+ *   feat      : [B,C,P] f32 (encoder output, NCHW flattened)
+ *   mask      : [B,P] f32 in {0,1}
+ *   fhat_t    : [B,P,C] bf16, pixel-major unit vectors (operand layout of K2)
+ *   inv_norm  : [B,P] f32, 1/max(||feat_x||, 1e-12)
+ *   pos_sum   : [B,C] f32, sum_x mask_x * fhat_x      (fp32 values, not the bf16 copy)
+ *   neg_sum   : [B,C] f32, sum_x (1-mask_x) * fhat_x
+ *   scratch   : [B, cp2_prep_tiles(P), 2, C] f32 work space (per-tile partial sums)
+ * C must be a multiple of 64 and <= 256. */
+int cp2_prep_tiles(int P);
+int cp2_prep_features(const float *feat, const float *mask, void *fhat_t, float *inv_norm,
+                      float *pos_sum, float *neg_sum, float *scratch, int B, int C, int P,
+                      void *stream);
+
+/* K2 forward — dense pixel InfoNCE, column log-sum-exp.
+ * Replaces builder.py:1289 (einsum ncx,ncy->nxy), :1431 (/T) and the LogSoftmax(dim=1)
+ * of :1432 without materialising [B,P,P]:
+ *   lse[n,y] = log sum_x exp( qhat[n,x,:].khat[n,y,:] * inv_tau )      ([B,P] f32)
+ * tcgen05 (bf16 operands, fp32 accumulate in TMEM), operands fetched by TMA.
+ * C in {128, 256}. */
+int cp2_dense_lse(const void *qhat_t, const void *khat_t, float *lse, float inv_tau, int B,
+                  int C, int P, void *stream);
+
+/* K2 backward — fused gradient of the dense + global loss w.r.t. the query features.
+ * Replaces autograd of builder.py:1261-1268, 1289-1292, 1431-1437:
+ *   acc[x,:]  = sum_y mask_b[y] * exp(S[x,y]*inv_tau - lse[y]) * khat[y,:]   (tcgen05)
+ *   dqhat_x   = alpha[n]*acc[x,:] + mask_a[x]*v1[n,:] + (1-mask_a[x])*v2[n,:]
+ *   dq[n,:,x] = (dqhat_x - qhat_x (qhat_x . dqhat_x)) * inv_norm[n,x]        ([B,C,P] f32)
+ * alpha [B], v1 [B,C], v2 [B,C] (v2 may be NULL = zeros) carry the upstream gradient
+ * and every rank-1 term; the caller computes them on [B,C] tensors. */
+int cp2_dense_grad(const void *qhat_t, const void *khat_t, const float *lse,
+                   const float *mask_a, const float *mask_b, const float *inv_norm,
+                   const float *alpha, const float *v1, const float *v2, float *dq,
+                   float inv_tau, int B, int C, int P, void *stream);
+
+/* K3 — global MoCo InfoNCE against the negative queue, forward and backward in one
+ * pass over the queue.  Replaces builder.py:1396 (q_pos @ queue.clone()) and the
+ * queue part of F.cross_entropy at :1428 and its autograd:
+ *   z[b]   = sum_k exp((l[b,k] - 1) * inv_tau),      l = q_pos @ queue
+ *   g[b,:] = sum_k exp((l[b,k] - 1) * inv_tau) * queue[:,k]
+ * (fixed shift 1: |l| <= 1 for unit vectors, so no running max is needed.)
+ *   q_pos   : [B,C] f32 unit rows; queue : [C,K] f32 (read once, as TF32 by tcgen05)
+ *   z : [B] f32; g : [B,C] f32
+ *   scratch : cp2_global_scratch_floats(B,C) f32
+  * C == 128, K % 4 == 0. */
+int64_t cp2_global_scratch_floats(int B, int C);
+int cp2_global_nce(const float *q_pos, const float *queue, float *z, float *g, float *scratch,
+                   float inv_tau, int B, int C, int K, void *stream);
+
+/* K4 — momentum (EMA) update of the key encoder, all parameters in one launch.
+ * Replaces builder.py:557-567 (3 ATen kernels x ~183 tensors).
+ *   k = fadd_rn(fmul_rn(k, m), fmul_rn(q, one_minus_m)), bit-exact with the reference.
+ *   q_ptrs, k_ptrs : device arrays [n_tensors] of tensor base pointers
+ *   chunk_tensor, chunk_index : device arrays [n_chunks] (int32): chunk i covers
+ *       elements [chunk_index[i]*CP2_EMA_CHUNK, ...) of tensor chunk_tensor[i]
+ *   numel : device array [n_tensors] (int64) */
+#define CP2_EMA_CHUNK 4096
+int cp2_ema(const float *const *q_ptrs, float *const *k_ptrs, const int64_t *numel,
+            const int32_t *chunk_tensor, const int32_t *chunk_index, int n_chunks, float m,
+            float one_minus_m, void *stream);
+
+/* K5 — queue enqueue of the all-gathered keys with wrap-around, device-side pointer.
+ * Replaces builder.py:574-587 (int(queue_ptr) D2H sync, 1-2 transposed slice writes,
+ * pointer update).  The all-gather itself (builder.py:1710-1722) is issued by the
+ * caller as one ncclAllGather into keys_all on the same stream.
+ *   keys_all : [n,C] f32 ; queue : [C,K] f32 ; queue_ptr : [1] int64 (read, then advanced)
+ * Bit-exact with the reference (n <= K). */
+int cp2_enqueue(const float *keys_all, float *queue, int64_t *queue_ptr, int n, int C, int K,
+                void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CP2_B200_H_ */

@@ -1,0 +1,286 @@
+"""GPU parity: every kernel of libcp2_b200.so, called through the C ABI (ctypes), against the
+CPU oracle (oracle/cp2_oracle.py) on the same seeded inputs and against the golden vectors
+recorded from the unmodified reference.
+
+Tolerances (BASELINE.json north_star): composite / EMA / enqueue bit-exact; losses within 1e-4
+relative; gradients of the bf16-operand tensor-core path within rel-L2 2e-2 of the fp32
+reference (measured: ~3e-3), TF32 global path likewise.
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import T, load_golden
+from oracle import cp2_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from cp2_b200 import _lib, ops as _ops
+    _lib.load()
+    return _ops
+
+
+def dev(t):
+    return t.cuda()
+
+
+def rel_l2(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+# --------------------------------------------------------------------------- K1
+@pytest.mark.parametrize("B,H,W,os_", [(4, 64, 64, 16), (3, 224, 224, 16), (2, 30, 45, 8), (1, 17, 19, 4),
+                                        (2, 224, 224, 32), (5, 96, 100, 16)])
+def test_composite_bit_exact(ops, B, H, W, os_):
+    g = torch.Generator().manual_seed(B * 1000 + H)
+    img = torch.rand(B, 3, H, W, generator=g) - 0.3
+    bg = torch.rand(B, 3, H, W, generator=g)
+    bg[:, :, H // 4: H // 2 + 3, W // 5: W // 2 + 1] = 0.0
+    bg[0, 0, 0, :] = 0.0                 # channel 0 only -> still fg, bg added on channels 1,2
+    bg[-1, 1:, -1, :] = 0.0              # channels 1,2 only -> not fg
+    bg[0, 0, 1, 0] = -0.0                # -0.0 == 0 is foreground
+    ref, mask = O.composite(img, bg)
+    out, mds, mfull = ops.composite(dev(img), dev(bg), os_, want_full_mask=True)
+    assert torch.equal(out.cpu().view(torch.int32), ref.view(torch.int32))
+    assert torch.equal(mfull.cpu(), mask)
+    assert torch.equal(mds.cpu(), O.stride_subsample(mask, os_))
+    out2, mds2, none = ops.composite(dev(img), dev(bg), os_)
+    assert none is None and torch.equal(out2, out) and torch.equal(mds2, mds)
+
+
+def test_composite_golden_and_empty(ops):
+    g = load_golden("cp2_step_small.npz")
+    for s in (0, 1):
+        out, mds, _ = ops.composite(dev(T(g[f"s{s}.img_a"])), dev(T(g[f"s{s}.bg0"])), 16)
+        assert torch.equal(out.cpu(), T(g[f"s{s}.img_a_comp"]))
+    out, mds, _ = ops.composite(torch.empty(0, 3, 32, 32).cuda(), torch.empty(0, 3, 32, 32).cuda(), 16)
+    assert out.shape == (0, 3, 32, 32) and mds.shape == (0, 2, 2)
+
+
+def test_composite_unaligned_views(ops):
+    # a non-16-byte-aligned base pointer must take the scalar path and still be exact
+    g = torch.Generator().manual_seed(9)
+    base_i = torch.rand(2 * 3 * 16 * 16 + 1, generator=g).cuda()
+    base_b = torch.rand(2 * 3 * 16 * 16 + 1, generator=g).cuda()
+    img = base_i[1:].view(2, 3, 16, 16)
+    bg = base_b[1:].view(2, 3, 16, 16)
+    bg[:, :, 4:12, 4:12] = 0
+    ref, mask = O.composite(img.cpu(), bg.cpu())
+    out, mds, _ = ops.composite(img, bg, 8)
+    assert torch.equal(out.cpu(), ref) and torch.equal(mds.cpu(), O.stride_subsample(mask, 8))
+
+
+# --------------------------------------------------------------------------- K4
+def test_ema_golden_bit_exact(ops):
+    g = load_golden("ema.npz")
+    n = int(g["n"])
+    q = [dev(T(g[f"q{i}"])) for i in range(n)]
+    k = [dev(T(g[f"k{i}"])) for i in range(n)]
+    plan = ops.EmaPlan(q, k)
+    plan.apply(0.999)
+    for i in range(n):
+        assert torch.equal(k[i].cpu().view(torch.int32), T(g[f"k1_{i}"]).view(torch.int32)), i
+    plan.apply(0.99)
+    for i in range(n):
+        assert torch.equal(k[i].cpu().view(torch.int32), T(g[f"k2_{i}"]).view(torch.int32)), i
+
+
+def test_ema_many_tensors_and_unaligned(ops):
+    g = torch.Generator().manual_seed(4)
+    sizes = [1, 3, 4097, 4096, 8191, 64 * 3 * 7 * 7, 2048 * 512 + 5, 7, 256, 12289]
+    big_q = torch.randn(sum(sizes) + 3, generator=g).cuda()
+    big_k = torch.randn(sum(sizes) + 3, generator=g).cuda()
+    q, k, o = [], [], 1                       # offset 1 float: most slices are not 16 B aligned
+    for s in sizes:
+        q.append(big_q[o:o + s]); k.append(big_k[o:o + s]); o += s
+    ref = O.ema_update([t.cpu() for t in q], [t.cpu() for t in k], 0.999)
+    guard = (big_k[0].item(), big_k[-2:].clone())
+    plan = ops.EmaPlan(q, k)
+    plan.apply(0.999)
+    for a, b in zip(k, ref):
+        assert torch.equal(a.cpu().view(torch.int32), b.view(torch.int32))
+    assert big_k[0].item() == guard[0] and torch.equal(big_k[-2:], guard[1])
+    # storage moves -> tables rebuilt
+    k2 = [t.clone() for t in k]
+    ref2 = O.ema_update([t.cpu() for t in q], [t.cpu() for t in k2], 0.5)
+    plan.rebind(q, k2)
+    plan.apply(0.5)
+    for a, b in zip(k2, ref2):
+        assert torch.equal(a.cpu().view(torch.int32), b.view(torch.int32))
+
+
+# --------------------------------------------------------------------------- K5
+def test_enqueue_golden_wraparound(ops):
+    g = load_golden("enqueue.npz")
+    queue = dev(T(g["queue0"]).clone())
+    ptr = torch.zeros(1, dtype=torch.int64).cuda()
+    for i, _n in enumerate(g["batches"]):
+        ops.enqueue(dev(T(g[f"keys{i}"])), queue, ptr)
+        assert int(ptr.item()) == int(g[f"ptr{i + 1}"][0])
+        assert torch.equal(queue.cpu(), T(g[f"queue{i + 1}"]))
+
+
+@pytest.mark.parametrize("n,C,K,ptr0", [(256, 128, 65536, 65536 - 100), (32, 128, 4096, 0), (33, 128, 100, 90),
+                                         (100, 128, 100, 37), (8, 256, 72, 70), (0, 128, 64, 5)])
+def test_enqueue_random(ops, n, C, K, ptr0):
+    g = torch.Generator().manual_seed(n + K)
+    queue = torch.randn(C, K, generator=g)
+    keys = torch.randn(n, C, generator=g)
+    ref = queue.clone()
+    p = ptr0
+    if n:
+        p = O.dequeue_and_enqueue(ref, ptr0, keys)
+    qd, pd = dev(queue), torch.tensor([ptr0], dtype=torch.int64).cuda()
+    ops.enqueue(dev(keys), qd, pd)
+    assert int(pd.item()) == p and torch.equal(qd.cpu(), ref)
+
+
+# -------------------------------------------------------------------------- K2a
+@pytest.mark.parametrize("B,C,P", [(2, 128, 196), (3, 256, 50), (1, 128, 784), (2, 64, 33)])
+def test_prep_features(ops, B, C, P):
+    g = torch.Generator().manual_seed(P)
+    feat = torch.randn(B, C, P, generator=g) * 3
+    feat[0, :, 1] = 0.0                                   # zero pixel: eps path of F.normalize
+    mask = (torch.rand(B, P, generator=g) < 0.6).float()
+    f_hat, pos, neg = O.normalize_and_pool(feat, mask)
+    fh, inv, ps, ns = ops.prep_features(dev(feat), dev(mask))
+    assert fh.shape == (B, P, C) and fh.dtype == torch.bfloat16
+    want = f_hat.transpose(1, 2)
+    assert torch.allclose(fh.float().cpu(), want, rtol=0, atol=2 ** -8)     # bf16 rounding of |v|<=1
+    assert rel_l2(fh.float(), want) < 3e-3
+    n = feat.norm(dim=1).clamp_min(1e-12)
+    assert torch.allclose(inv.cpu(), 1.0 / n, rtol=2e-6)
+    raw_pos = torch.einsum("ncx,nx->nc", f_hat, mask)
+    raw_neg = torch.einsum("ncx,nx->nc", f_hat, 1 - mask)
+    assert torch.allclose(ps.cpu(), raw_pos, rtol=1e-5, atol=1e-5)
+    assert torch.allclose(ns.cpu(), raw_neg, rtol=1e-5, atol=1e-5)
+    assert torch.allclose(torch.nn.functional.normalize(ps.cpu(), dim=1), pos, rtol=1e-5, atol=1e-6)
+
+
+# ------------------------------------------------------------------- K2 forward
+def _unit_bf16(B, P, C, seed):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.nn.functional.normalize(torch.randn(B, P, C, generator=g), dim=2)
+    return x.to(torch.bfloat16)
+
+
+def _lse_ref(qh, kh, inv_tau):
+    s = torch.einsum("nxc,nyc->nxy", qh.double(), kh.double()) * inv_tau
+    return torch.logsumexp(s, dim=1)
+
+
+@pytest.mark.parametrize("B,C,P,tau", [(2, 128, 196, 0.2), (1, 128, 128, 1.0), (3, 128, 50, 0.2),
+                                       (2, 256, 196, 0.2), (1, 128, 784, 0.2), (1, 256, 300, 1.0),
+                                       (2, 128, 1, 0.2)])
+def test_dense_lse_vs_oracle(ops, B, C, P, tau):
+    qh, kh = _unit_bf16(B, P, C, 1), _unit_bf16(B, P, C, 2)
+    ref = _lse_ref(qh.float(), kh.float(), 1.0 / tau)
+    got = ops.dense_lse(dev(qh), dev(kh), 1.0 / tau)
+    torch.cuda.synchronize()
+    assert torch.allclose(got.double().cpu(), ref, rtol=0, atol=2e-5), float((got.double().cpu() - ref).abs().max())
+
+
+def test_dense_lse_vs_simt_large(ops):
+    from cp2_b200 import _lib
+    lib = _lib.load()
+    B, C, P = 2, 128, 3136
+    qh, kh = dev(_unit_bf16(B, P, C, 3)), dev(_unit_bf16(B, P, C, 4))
+    got = ops.dense_lse(qh, kh, 5.0)
+    ref = torch.empty_like(got)
+    _lib.check(lib.cp2_dbg_dense_lse_simt(qh.data_ptr(), kh.data_ptr(), ref.data_ptr(), 5.0, B, C, P,
+                                          torch.cuda.current_stream().cuda_stream), "simt")
+    torch.cuda.synchronize()
+    assert torch.allclose(got, ref, rtol=0, atol=3e-5), float((got - ref).abs().max())
+
+
+# ------------------------------------------------------------------ K2 backward
+def _grad_ref(qh, kh, lse, ma, mb, inv_norm, alpha, v1, v2, inv_tau):
+    """fp64 restatement of the cp2_dense_grad contract (include/cp2_b200.h)."""
+    qh, kh = qh.double(), kh.double()
+    s = torch.einsum("nxc,nyc->nxy", qh, kh) * inv_tau
+    p = torch.exp(s - lse.double()[:, None, :]) * mb.double()[:, None, :]
+    acc = torch.einsum("nxy,nyc->nxc", p, kh)
+    g = alpha.double()[:, None, None] * acc + ma.double()[:, :, None] * v1.double()[:, None, :]
+    if v2 is not None:
+        g = g + (1 - ma.double())[:, :, None] * v2.double()[:, None, :]
+    d = (g - qh * (qh * g).sum(-1, keepdim=True)) * inv_norm.double()[:, :, None]
+    return d.transpose(1, 2)                                # [B,C,P]
+
+
+@pytest.mark.parametrize("B,C,P,tau,bg", [(2, 128, 196, 0.2, False), (1, 128, 128, 1.0, True),
+                                          (2, 128, 50, 0.2, True), (1, 256, 196, 0.2, False),
+                                          (1, 128, 784, 0.2, True), (1, 256, 300, 1.0, True)])
+def test_dense_grad_vs_oracle(ops, B, C, P, tau, bg):
+    g = torch.Generator().manual_seed(P + C)
+    qh, kh = _unit_bf16(B, P, C, 5), _unit_bf16(B, P, C, 6)
+    ma = (torch.rand(B, P, generator=g) < 0.6).float()
+    mb = (torch.rand(B, P, generator=g) < 0.6).float()
+    inv_norm = torch.rand(B, P, generator=g) + 0.5
+    alpha = torch.rand(B, generator=g) + 0.1
+    v1 = torch.randn(B, C, generator=g) * 0.1
+    v2 = torch.randn(B, C, generator=g) * 0.1 if bg else None
+    lse = _lse_ref(qh.float(), kh.float(), 1.0 / tau).float()
+    ref = _grad_ref(qh.float(), kh.float(), lse, ma, mb, inv_norm, alpha, v1, v2, 1.0 / tau)
+    got = ops.dense_grad(dev(qh), dev(kh), dev(lse), dev(ma), dev(mb), dev(inv_norm), dev(alpha), dev(v1),
+                         None if v2 is None else dev(v2), 1.0 / tau)
+    torch.cuda.synchronize()
+    assert got.shape == (B, C, P)
+    err = rel_l2(got, ref)
+    assert err < 5e-3, err                                   # Ptilde is rounded to bf16 (2^-9)
+
+
+def test_dense_grad_vs_simt_large(ops):
+    from cp2_b200 import _lib
+    lib = _lib.load()
+    B, C, P = 1, 128, 3136
+    g = torch.Generator().manual_seed(11)
+    qh, kh = dev(_unit_bf16(B, P, C, 7)), dev(_unit_bf16(B, P, C, 8))
+    ma = dev((torch.rand(B, P, generator=g) < 0.6).float())
+    mb = dev((torch.rand(B, P, generator=g) < 0.6).float())
+    inv_norm = dev(torch.rand(B, P, generator=g) + 0.5)
+    alpha, v1 = dev(torch.rand(B, generator=g) + 0.1), dev(torch.randn(B, C, generator=g) * 0.01)
+    lse = ops.dense_lse(qh, kh, 5.0)
+    got = ops.dense_grad(qh, kh, lse, ma, mb, inv_norm, alpha, v1, None, 5.0)
+    ref = torch.empty_like(got)
+    st = torch.cuda.current_stream().cuda_stream
+    _lib.check(lib.cp2_dbg_dense_grad_simt(qh.data_ptr(), kh.data_ptr(), lse.data_ptr(), ma.data_ptr(),
+                                           mb.data_ptr(), inv_norm.data_ptr(), alpha.data_ptr(), v1.data_ptr(),
+                                           None, ref.data_ptr(), 5.0, B, C, P, st), "simt")
+    torch.cuda.synchronize()
+    assert rel_l2(got, ref) < 5e-3, rel_l2(got, ref)
+
+
+# --------------------------------------------------------------------------- K3
+@pytest.mark.parametrize("B,K,tau", [(32, 65536, 0.2), (4, 4096, 0.2), (2, 1024, 0.07), (64, 8192, 0.2),
+                                     (100, 4096, 0.2), (7, 1000, 0.2), (1, 256, 1.0)])
+def test_global_nce_vs_oracle(ops, B, K, tau):
+    C = 128
+    g = torch.Generator().manual_seed(B + K)
+    qp = torch.nn.functional.normalize(torch.randn(B, C, generator=g), dim=1)
+    queue = torch.nn.functional.normalize(torch.randn(C, K, generator=g), dim=0)
+    e = torch.exp((qp.double() @ queue.double() - 1.0) / tau)
+    z_ref, g_ref = e.sum(dim=1), e @ queue.double().T
+    z, gg = ops.global_nce(dev(qp), dev(queue), 1.0 / tau)
+    torch.cuda.synchronize()
+    # TF32 operands (10-bit mantissa): logits off by <~1e-3 -> e off by <~1e-3/tau relative
+    assert torch.allclose(z.double().cpu(), z_ref, rtol=2e-3 / tau * 0.2 + 1e-3), (z.cpu(), z_ref)
+    assert rel_l2(gg, g_ref) < 5e-3, rel_l2(gg, g_ref)
+
+
+def test_global_nce_vs_simt(ops):
+    from cp2_b200 import _lib
+    lib = _lib.load()
+    B, C, K = 32, 128, 65536
+    g = torch.Generator().manual_seed(0)
+    qp = dev(torch.nn.functional.normalize(torch.randn(B, C, generator=g), dim=1))
+    queue = dev(torch.nn.functional.normalize(torch.randn(C, K, generator=g), dim=0))
+    z, gg = ops.global_nce(qp, queue, 5.0)
+    z2, g2 = torch.empty_like(z), torch.empty_like(gg)
+    _lib.check(lib.cp2_dbg_global_nce_simt(qp.data_ptr(), queue.data_ptr(), z2.data_ptr(), g2.data_ptr(), 5.0,
+                                           B, C, K, torch.cuda.current_stream().cuda_stream), "simt")
+    torch.cuda.synchronize()
+    assert torch.allclose(z, z2, rtol=2e-3) and rel_l2(gg, g2) < 5e-3
