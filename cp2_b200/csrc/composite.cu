@@ -70,12 +70,13 @@ composite_kernel(const float *__restrict__ img, const float *__restrict__ bg, fl
 
 extern "C" int cp2_composite(const float *img, const float *bg, float *out, float *mask_full,
                              float *mask_ds, int B, int H, int W, int os, void *stream) {
-  CP2_REQUIRE(img && bg && out && mask_ds, "cp2_composite: null pointer");
   CP2_REQUIRE(B >= 0 && H > 0 && W > 0 && os > 0, "cp2_composite: bad shape B=%d H=%d W=%d os=%d", B, H, W, os);
-  if (B == 0) return CP2_OK;
+  if (B == 0) return CP2_OK;                 // empty batch: pointers may be null
+  CP2_REQUIRE(img && bg && out, "cp2_composite: null pointer");
   const int o = os / 2;
   const int hs = H > o ? (H - o + os - 1) / os : 0;
   const int ws = W > o ? (W - o + os - 1) / os : 0;
+  CP2_REQUIRE(mask_ds || hs * ws == 0, "cp2_composite: null mask_ds");
   auto aligned = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
   const bool vec = (W % 4 == 0) && aligned(img) && aligned(bg) && aligned(out) &&
                    (mask_full == nullptr || aligned(mask_full));

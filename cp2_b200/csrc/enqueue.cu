@@ -35,9 +35,9 @@ __global__ void advance_ptr_kernel(int64_t *queue_ptr, int n, int K) {
 
 extern "C" int cp2_enqueue(const float *keys_all, float *queue, int64_t *queue_ptr, int n, int C,
                            int K, void *stream) {
-  CP2_REQUIRE(keys_all && queue && queue_ptr, "cp2_enqueue: null pointer");
   CP2_REQUIRE(n >= 0 && C > 0 && K > 0 && n <= K, "cp2_enqueue: bad shape n=%d C=%d K=%d", n, C, K);
   if (n == 0) return CP2_OK;
+  CP2_REQUIRE(keys_all && queue && queue_ptr, "cp2_enqueue: null pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   dim3 grid(cp2_cdiv(n, 32), cp2_cdiv(C, 32));
   enqueue_kernel<<<grid, 256, 0, st>>>(keys_all, queue, queue_ptr, n, C, K);

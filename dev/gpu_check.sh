@@ -6,7 +6,7 @@ nvidia-smi --query-gpu=name,driver_version,clocks.max.sm --format=csv > gpurun_o
 rc=0
 for f in tests/test_kernels_gpu.py tests/test_loss_gpu.py; do
   n=$(basename $f .py)
-  timeout 600 python -m pytest $f -m gpu -q -x --tb=short -p no:cacheprovider > gpurun_out/$n.log 2>&1
+  timeout 600 python -m pytest $f -m gpu -q --tb=line -p no:cacheprovider > gpurun_out/$n.log 2>&1
   r=$?
   echo "== $f exit $r"; tail -n 40 gpurun_out/$n.log
   [ $r -ne 0 ] && rc=$r

@@ -88,10 +88,11 @@ int cp2_dense_grad(const void *qhat_t, const void *khat_t, const float *lse,
  *   z[b]   = sum_k exp((l[b,k] - 1) * inv_tau),      l = q_pos @ queue
  *   g[b,:] = sum_k exp((l[b,k] - 1) * inv_tau) * queue[:,k]
  * (fixed shift 1: |l| <= 1 for unit vectors, so no running max is needed.)
- *   q_pos   : [B,C] f32 unit rows; queue : [C,K] f32 (read once, as TF32 by tcgen05)
+ *   q_pos   : [B,C] f32 unit rows (used as a bf16 hi+lo pair);
+ *   queue   : [C,K] f32, read once by TMA and converted on chip to a bf16 operand image
  *   z : [B] f32; g : [B,C] f32
  *   scratch : cp2_global_scratch_floats(B,C) f32
-  * C == 128, K % 4 == 0. */
+ * C == 128, K % 4 == 0, queue 16-byte aligned. */
 int64_t cp2_global_scratch_floats(int B, int C);
 int cp2_global_nce(const float *q_pos, const float *queue, float *z, float *g, float *scratch,
                    float inv_tau, int B, int C, int K, void *stream);
