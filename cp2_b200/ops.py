@@ -10,6 +10,51 @@ from . import _lib
 
 _EPS = 1e-12   # F.normalize eps
 
+# ------------------------------------------------------------ launch accounting
+# Every C-ABI call goes through `_call`: it counts the kernels launched (bench.py's
+# `gpu_launches`) and, when a KernelTimer is active, brackets the call with CUDA events on
+# the launching stream (bench.py's per-kernel roofline figures).
+LAUNCHES = 0
+_timer = None
+
+
+class KernelTimer:
+    """with KernelTimer() as t: ...   then t.summary() -> {name: (n_calls, mean_us)}."""
+
+    def __init__(self):
+        self.records = {}
+
+    def __enter__(self):
+        global _timer
+        self._prev, _timer = _timer, self
+        return self
+
+    def __exit__(self, *exc):
+        global _timer
+        _timer = self._prev
+
+    def summary(self):
+        torch.cuda.synchronize()
+        out = {}
+        for name, evs in self.records.items():
+            ms = [a.elapsed_time(b) for a, b in evs]
+            out[name] = (len(ms), 1e3 * sum(ms) / max(1, len(ms)))
+        return out
+
+
+def _call(name, n_kernels, fn, *args):
+    global LAUNCHES
+    LAUNCHES += n_kernels
+    if _timer is None:
+        _lib.check(fn(*args), name)
+        return
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    _lib.check(fn(*args), name)
+    e1.record()
+    _timer.records.setdefault(name, []).append((e0, e1))
+
 
 def _ptr(t):
     return None if t is None else t.data_ptr()
@@ -44,8 +89,8 @@ def composite(img, bg, output_stride, want_full_mask=False, out=None):
     mask_ds = torch.empty((B, hs, ws), device=img.device, dtype=torch.float32)
     mask_full = torch.empty((B, H, W), device=img.device, dtype=torch.float32) if want_full_mask else None
     lib = _lib.load()
-    _lib.check(lib.cp2_composite(_ptr(img), _ptr(bg), _ptr(out), _ptr(mask_full), _ptr(mask_ds),
-                                 B, H, W, output_stride, _stream()), "cp2_composite")
+    _call("cp2_composite", 1, lib.cp2_composite, _ptr(img), _ptr(bg), _ptr(out), _ptr(mask_full), _ptr(mask_ds),
+                                 B, H, W, output_stride, _stream())
     return out, mask_ds, mask_full
 
 
@@ -63,8 +108,8 @@ def prep_features(feat, mask):
     pos = torch.empty((B, C), device=dev, dtype=torch.float32)
     neg = torch.empty((B, C), device=dev, dtype=torch.float32)
     scratch = torch.empty((B, lib.cp2_prep_tiles(P), 2, C), device=dev, dtype=torch.float32)
-    _lib.check(lib.cp2_prep_features(_ptr(feat), _ptr(mask), _ptr(fhat_t), _ptr(inv_norm), _ptr(pos),
-                                     _ptr(neg), _ptr(scratch), B, C, P, _stream()), "cp2_prep_features")
+    _call("cp2_prep_features", 2, lib.cp2_prep_features, _ptr(feat), _ptr(mask), _ptr(fhat_t), _ptr(inv_norm), _ptr(pos),
+                                     _ptr(neg), _ptr(scratch), B, C, P, _stream())
     return fhat_t, inv_norm, pos, neg
 
 
@@ -74,8 +119,8 @@ def dense_lse(qhat_t, khat_t, inv_tau):
     _need_cuda(qhat_t, khat_t)
     B, P, C = qhat_t.shape
     lse = torch.empty((B, P), device=qhat_t.device, dtype=torch.float32)
-    _lib.check(_lib.load().cp2_dense_lse(_ptr(qhat_t), _ptr(khat_t), _ptr(lse), float(inv_tau), B, C, P,
-                                        _stream()), "cp2_dense_lse")
+    _call("cp2_dense_lse", 1, _lib.load().cp2_dense_lse, _ptr(qhat_t), _ptr(khat_t), _ptr(lse), float(inv_tau), B, C, P,
+                                        _stream())
     return lse
 
 
@@ -83,9 +128,9 @@ def dense_grad(qhat_t, khat_t, lse, mask_a, mask_b, inv_norm, alpha, v1, v2, inv
     """Fused backward of the dense + global loss w.r.t. the query features -> dq [B,C,P]."""
     B, P, C = qhat_t.shape
     dq = torch.empty((B, C, P), device=qhat_t.device, dtype=torch.float32)
-    _lib.check(_lib.load().cp2_dense_grad(_ptr(qhat_t), _ptr(khat_t), _ptr(lse), _ptr(mask_a), _ptr(mask_b),
+    _call("cp2_dense_grad", 1, _lib.load().cp2_dense_grad, _ptr(qhat_t), _ptr(khat_t), _ptr(lse), _ptr(mask_a), _ptr(mask_b),
                                          _ptr(inv_norm), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(dq),
-                                         float(inv_tau), B, C, P, _stream()), "cp2_dense_grad")
+                                         float(inv_tau), B, C, P, _stream())
     return dq
 
 
@@ -102,8 +147,8 @@ def global_nce(q_pos, queue, inv_tau):
     z = torch.empty((B,), device=dev, dtype=torch.float32)
     g = torch.empty((B, C), device=dev, dtype=torch.float32)
     scratch = torch.empty((max(1, lib.cp2_global_scratch_floats(B, C)),), device=dev, dtype=torch.float32)
-    _lib.check(lib.cp2_global_nce(_ptr(q_pos), _ptr(queue), _ptr(z), _ptr(g), _ptr(scratch), float(inv_tau),
-                                  B, C, K, _stream()), "cp2_global_nce")
+    _call("cp2_global_nce", 2, lib.cp2_global_nce, _ptr(q_pos), _ptr(queue), _ptr(z), _ptr(g), _ptr(scratch), float(inv_tau),
+                                  B, C, K, _stream())
     return z, g
 
 
@@ -155,9 +200,9 @@ class EmaPlan:
         if self._signature() != self._key:
             self._build()
         # the reference's scalars: m and (1.0 - m) evaluated in double, rounded to fp32 by the op
-        _lib.check(_lib.load().cp2_ema(_ptr(self.q_ptrs), _ptr(self.k_ptrs), _ptr(self.numel),
+        _call("cp2_ema", 1, _lib.load().cp2_ema, _ptr(self.q_ptrs), _ptr(self.k_ptrs), _ptr(self.numel),
                                       _ptr(self.chunk_tensor), _ptr(self.chunk_index), self.n_chunks,
-                                      float(m), float(1.0 - m), _stream()), "cp2_ema")
+                                      float(m), float(1.0 - m), _stream())
 
 
 # ------------------------------------------------------------------ K5
@@ -169,8 +214,8 @@ def enqueue(keys_all, queue, queue_ptr):
     n, C = keys_all.shape
     assert queue.dtype == torch.float32 and queue.is_contiguous() and queue.shape[0] == C
     assert queue_ptr.dtype == torch.int64 and queue_ptr.numel() == 1
-    _lib.check(_lib.load().cp2_enqueue(_ptr(keys_all), _ptr(queue), _ptr(queue_ptr), n, C, queue.shape[1],
-                                      _stream()), "cp2_enqueue")
+    _call("cp2_enqueue", 2, _lib.load().cp2_enqueue, _ptr(keys_all), _ptr(queue), _ptr(queue_ptr), n, C, queue.shape[1],
+                                      _stream())
 
 
 # ------------------------------------------------- fused loss (a5 + a6 + a7 + a12)

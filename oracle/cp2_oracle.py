@@ -307,3 +307,51 @@ def synth_views(batch, height, width, output_stride, seed, fg_lo=0.5, fg_hi=0.8)
     out["region_ids_a"] = out["pixel_ids_a"].clone()
     out["region_ids_b"] = out["pixel_ids_b"].clone()
     return out
+
+
+# ------------------------------------------------- whole pre-training step (CPU port)
+class CP2StepPort:
+    """CPU restatement of ONE reference pre-training iteration: `train()` body
+    main.py:616-644 around `MODEL.forward_cp2` (builder.py:1124-1439) in the order the
+    reference runs it (Appendix A.3 of SURVEY.md): composite both views, encoder_q,
+    EMA, encoder_k, losses against the queue BEFORE enqueue, enqueue, backward, SGD.
+
+    Used only as bench.py's CPU baseline / `--impl reference` arm (kind "port": the
+    reference is pure Python and cannot travel to the GPU box).  World size 1, so the
+    batch shuffle (builder.py:609-649) is the identity up to a permutation that BN
+    batch statistics do not see.  `encoder_factory()` builds one segmentor (the
+    out-of-scope backbone; plain torch on the CPU, as in the reference).
+    """
+
+    def __init__(self, encoder_factory, dim=128, K=65536, m=0.999, temp_global=0.2, temp_local=1.0,
+                 lmbd_dense=0.2, output_stride=16, lr=0.001, seed=0):
+        torch.manual_seed(seed)
+        self.encoder_q = encoder_factory()
+        self.encoder_k = encoder_factory()
+        for pq, pk in zip(self.encoder_q.parameters(), self.encoder_k.parameters()):
+            pk.data.copy_(pq.data)                      # builder.py:464-469
+            pk.requires_grad = False
+        self.queue = F.normalize(torch.randn(dim, K), dim=0)   # builder.py:476-477
+        self.ptr = 0
+        self.m, self.tg, self.tl, self.lmbd, self.os = m, temp_global, temp_local, lmbd_dense, output_stride
+        self.opt = torch.optim.SGD(self.encoder_q.parameters(), lr, momentum=0.9, weight_decay=1e-4)  # main.py:467-471
+
+    def step(self, img_a, img_b, bg0, bg1):
+        img_a, mask_a = composite(img_a, bg0)
+        img_b, mask_b = composite(img_b, bg1)
+        n = img_a.shape[0]
+        mask_a = stride_subsample(mask_a, self.os).reshape(n, -1)
+        mask_b = stride_subsample(mask_b, self.os).reshape(n, -1)
+        q = self.encoder_q(img_a)
+        with torch.no_grad():
+            pq = [p.data for p in self.encoder_q.parameters()]
+            pk = [p.data for p in self.encoder_k.parameters()]
+            for p, new in zip(self.encoder_k.parameters(), ema_update(pq, pk, self.m)):
+                p.data = new
+            k = self.encoder_k(img_b)
+        r = cp2_loss(q, k, mask_a, mask_b, self.queue.clone(), self.tg, self.tl, self.lmbd)  # clone: builder.py:1396
+        self.ptr = dequeue_and_enqueue(self.queue, self.ptr, r["k_pos"])
+        self.opt.zero_grad()
+        r["loss"].backward()
+        self.opt.step()
+        return float(r["loss"].detach())
