@@ -212,8 +212,11 @@ def reference_arm(args):
 def dense_sweep(args, peaks):
     """configs[3]: dense pixel InfoNCE fwd+bwd at B=256 images/GPU, P in {14^2,28^2,56^2}, C in {128,256}.
     Algorithmic work 4*B*P^2*C FLOP (Q^T K forward + dQ backward; the backward's recomputation of Q^T K is
-    not counted).  `us` = cp2_dense_lse + cp2_dense_grad; `us_with_prep` adds the two cp2_prep_features
-    launches (normalise + pool + bf16 transpose of q and k).  L2 is flushed between iterations."""
+    not counted, and background key columns skipped by the compaction are still counted: `frac` is the
+    dense-algorithmic figure, `executed_frac` = share of key columns actually visited).  Two mask variants
+    (SURVEY.md 8d): Bernoulli(0.65) fg masks (CP2's copy-paste masks are 50-80 % foreground) and all-ones
+    (nothing to skip).  `us` = cp2_dense_lse + cp2_dense_grad; `us_with_prep` adds the two
+    cp2_prep_features launches.  L2 is flushed between iterations."""
     import torch
     from cp2_b200 import ops
     dev = torch.device("cuda")
@@ -225,34 +228,42 @@ def dense_sweep(args, peaks):
             g = torch.Generator(device=dev).manual_seed(7)
             q = torch.randn(B, C, P, device=dev, generator=g)
             k = torch.randn(B, C, P, device=dev, generator=g)
-            g8 = torch.Generator(device=dev).manual_seed(8)
-            ma = (torch.rand(B, P, device=dev, generator=g8) < 0.65).float()
-            mb = (torch.rand(B, P, device=dev, generator=g8) < 0.65).float()
             alpha = torch.full((B,), 1.0 / B, device=dev)
             v1 = torch.zeros(B, C, device=dev)
             inv_tau = 1.0 / TAU_D
-            t_core, t_all = [], []
-            for it in range(3 + args.sweep_iters):
-                flush.zero_()
-                e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-                e[0].record()
-                qh, q_inv, _, _ = ops.prep_features(q, ma)
-                kh, _, _, _ = ops.prep_features(k, mb)
-                e[1].record()
-                lse = ops.dense_lse(qh, kh, inv_tau)
-                dq = ops.dense_grad(qh, kh, lse, ma, mb, q_inv, alpha, v1, None, inv_tau)
-                e[2].record()
-                torch.cuda.synchronize()
-                if it >= 3:
-                    t_core.append(e[1].elapsed_time(e[2]) * 1e3)
-                    t_all.append(e[0].elapsed_time(e[2]) * 1e3)
-            us, us_all = statistics.mean(t_core), statistics.mean(t_all)
-            flop = 4.0 * B * P * P * C
-            tf = flop / (us * 1e-6) / 1e12
-            rows.append({"P": P, "C": C, "B": B, "us": round(us, 2), "us_with_prep": round(us_all, 2),
-                         "flop": flop, "tflops": round(tf, 2), "peak": peaks["tf_burst"],
-                         "frac": round(tf / peaks["tf_burst"], 4), "finite": bool(torch.isfinite(dq).all())})
-            del q, k, qh, kh, dq, lse
+            for variant in ("bernoulli(0.65)", "ones"):
+                g8 = torch.Generator(device=dev).manual_seed(8)
+                if variant == "ones":
+                    ma = torch.ones(B, P, device=dev)
+                    mb = torch.ones(B, P, device=dev)
+                else:
+                    ma = (torch.rand(B, P, device=dev, generator=g8) < 0.65).float()
+                    mb = (torch.rand(B, P, device=dev, generator=g8) < 0.65).float()
+                t_core, t_all = [], []
+                for it in range(3 + args.sweep_iters):
+                    flush.zero_()
+                    e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+                    e[0].record()
+                    qh, q_inv, _, _, _ = ops.prep_features(q, ma)
+                    kh, _, _, _, cnt = ops.prep_features(k, mb, compact=True)
+                    e[1].record()
+                    lse = ops.dense_lse(qh, kh, inv_tau, cnt)
+                    dq = ops.dense_grad(qh, kh, lse, ma, None, q_inv, alpha, v1, None, inv_tau, key_count=cnt)
+                    e[2].record()
+                    torch.cuda.synchronize()
+                    if it >= 3:
+                        t_core.append(e[1].elapsed_time(e[2]) * 1e3)
+                        t_all.append(e[0].elapsed_time(e[2]) * 1e3)
+                us, us_all = statistics.mean(t_core), statistics.mean(t_all)
+                flop = 4.0 * B * P * P * C
+                tf = flop / (us * 1e-6) / 1e12
+                rows.append({"P": P, "C": C, "B": B, "masks": variant, "us": round(us, 2),
+                             "us_with_prep": round(us_all, 2), "flop": flop, "tflops": round(tf, 2),
+                             "peak": peaks["tf_burst"], "frac": round(tf / peaks["tf_burst"], 4),
+                             "executed_frac": round(float(cnt.float().mean()) / P, 4),
+                             "finite": bool(torch.isfinite(dq).all())})
+                del qh, kh, dq, lse
+            del q, k
     return rows
 
 

@@ -17,9 +17,10 @@ SIGNATURES = {
     "cp2_last_error": (c_char_p, []),
     "cp2_composite": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "cp2_prep_tiles": (c_int, [c_int]),
-    "cp2_prep_features": (c_int, [c_void_p] * 7 + [c_int] * 3 + [c_void_p]),
-    "cp2_dense_lse": (c_int, [c_void_p] * 3 + [c_float] + [c_int] * 3 + [c_void_p]),
-    "cp2_dense_grad": (c_int, [c_void_p] * 10 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_prep_features": (c_int, [c_void_p] * 8 + [c_int] * 3 + [c_void_p]),
+    "cp2_dense_lse": (c_int, [c_void_p] * 4 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_dense_pad": (c_int, [c_int]),
+    "cp2_dense_grad": (c_int, [c_void_p] * 12 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_global_scratch_floats": (c_int64, [c_int, c_int]),
     "cp2_global_nce": (c_int, [c_void_p] * 5 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_ema": (c_int, [c_void_p] * 5 + [c_int, c_float, c_float, c_void_p]),
@@ -33,6 +34,7 @@ DEBUG_SIGNATURES = {
 }
 
 EMA_CHUNK = 4096  # CP2_EMA_CHUNK
+ABI_VERSION = 2  # CP2_ABI_VERSION
 
 _lib = None
 
@@ -55,8 +57,8 @@ def load():
                 raise RuntimeError(f"cp2_b200: {LIB_PATH} does not export {name}") from e
             fn.restype = res
             fn.argtypes = args
-    if lib.cp2_abi_version() != 1:
-        raise RuntimeError(f"cp2_b200: ABI version {lib.cp2_abi_version()} != 1")
+    if lib.cp2_abi_version() != ABI_VERSION:
+        raise RuntimeError(f"cp2_b200: ABI version {lib.cp2_abi_version()} != {ABI_VERSION}")
     _lib = lib
     return lib
 

@@ -2,21 +2,28 @@
 // 1431-1437 and their autograd).  The [B,P,P] logit matrix never exists in HBM.
 //
 // Operands: qhat_t / khat_t [B,P,C] bf16 (unit pixel vectors, written by cp2_prep_features),
-// fetched by TMA as 128-row x 64-channel boxes with the 128-byte swizzle (16 KB per box,
-// C/64 boxes per 128-pixel tile; rows past P are zero-filled by the TMA unit).
+// fetched by TMA as (rows x 64-channel) boxes with the 128-byte swizzle; rows past P are
+// zero-filled by the TMA unit.  With `key_count` (compacted keys: foreground rows first, zero rows
+// after) only ceil(count/tile) key tiles are visited by either pass: background key pixels carry
+// no loss term (labels = mask_a (x) mask_b) and no gradient (P~ = P . mask_b).
 //
-// Forward  (cp2_dense_lse):  CTA = (image n, 128 key pixels y).  S^T tile = Khat_y . Qhat_x^T
-//   (M = y -> TMEM lanes, N = x -> TMEM columns), so the log-sum-exp over the QUERY axis
-//   (the reference's LogSoftmax(dim=1)) is a per-lane running sum: no cross-lane traffic
-//   and, because |S| <= 1/tau for unit vectors, no running max.
-// Backward (cp2_dense_grad): CTA = (image n, 128 query pixels x).  Per key tile:
-//   S = Qhat_x . Khat_y^T  (M = x) -> softmax warps turn it into Ptilde = mask_b * exp(S - lse_y)
-//   as bf16 *in place in TMEM* -> dQhat += Ptilde . Khat_y with A read from TMEM and B the
-//   same shared-memory key tile addressed MN-major.  The epilogue adds the rank-1 terms,
-//   applies the F.normalize backward and writes dq [B,C,P] coalesced along P.
+// Forward  (cp2_dense_lse):  CTA = (image n, 128 key pixels y), 2 CTAs per SM.  S^T tile =
+//   Khat_y . Qhat_x^T (M = y -> TMEM lanes, N = x -> TMEM columns), so the log-sum-exp over the
+//   QUERY axis (the reference's LogSoftmax(dim=1)) is a per-lane running sum: no cross-lane
+//   traffic and, because |S| <= 1/tau for unit vectors, no running max.
+// Backward (cp2_dense_grad): persistent CTA (one per SM) over work items (image n, 128 query
+//   pixels x).  Per key tile: S = Qhat_x . Khat_y^T (double-buffered in TMEM) -> 8 softmax warps
+//   turn it into P~ = exp2(S*c - lse_y*log2e) as bf16 *in place in TMEM* -> dQhat += P~ . Khat_y
+//   with A read from TMEM and B the same shared-memory key tile addressed MN-major.  While the
+//   softmax warps work on tile j the tensor pipe computes S(j+1) and dQ(j-1).  4 epilogue warps add
+//   the rank-1 terms, apply the F.normalize backward and write dq [B,C,P] coalesced along P while
+//   the next item is already running (dQhat accumulator double-buffered when C = 128).
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
-// warps 2-5 = softmax / epilogue (one TMEM lane quadrant each).
+// The exponentials are the co-bottleneck (16 MUFU ex2 / clk / SM vs 8192 MMA flop / clk / SM at
+// C = 128): PF of every 4 column pairs are evaluated on the FMA pipe instead (Cody-Waite +
+// minimax polynomial, packed FFMA2; umma.cuh), the rest on the MUFU.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "umma.cuh"
 
@@ -24,27 +31,30 @@ using namespace umma;
 
 namespace {
 
-constexpr int TILE = 128;                 // pixels per tile: MMA M and N
-constexpr int BOX_BYTES = TILE * 128;     // one TMA box = 128 rows x 128 B
-constexpr int NTHREADS = 192;
+constexpr int TILE = 128;                 // MMA M (TMEM lanes): key pixels (fwd) / query pixels (bwd)
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
+constexpr float NL_MASKED = -80.0f;       // exp2 argument offset of a masked key column (2^-80 ~ 0)
 
 __device__ __forceinline__ uint8_t *align1024(uint8_t *p) {
   return reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(p) + 1023) & ~uintptr_t(1023));
 }
 
-// K-major operand tile [128 rows][C] in C/64 swizzled boxes: descriptor of the kk-th K=16 slice.
-__device__ __forceinline__ uint64_t kmajor_desc(uint32_t tile_addr, int kk) {
-  return make_sdesc(tile_addr + (kk >> 2) * BOX_BYTES + (kk & 3) * 32, 16, 1024);
+// K-major operand tile [rows][C] stored as C/64 swizzled boxes of `box_bytes`: descriptor of the
+// kk-th K=16 slice (32 bytes inside the 128-byte row).
+__device__ __forceinline__ uint64_t kmajor_desc(uint32_t tile_addr, int kk, int box_bytes) {
+  return make_sdesc(tile_addr + (kk >> 2) * box_bytes + (kk & 3) * 32, 16, 1024);
 }
 
 // ------------------------------------------------------------------ forward
-template <int C, int NST>
-__global__ void __launch_bounds__(NTHREADS)
+constexpr int LSE_THREADS = 192;          // warp 0 TMA, warp 1 MMA + TMEM owner, warps 2-5 softmax
+
+template <int C, int NST, int PF>
+__global__ void __launch_bounds__(LSE_THREADS)
 dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
-                 float *__restrict__ lse, float scale_log2, int P) {
-  constexpr int OPER = (C / 64) * BOX_BYTES;
+                 const int *__restrict__ key_count, float *__restrict__ lse, float scale_log2, int P) {
+  constexpr int BOX = TILE * 128;
+  constexpr int OPER = (C / 64) * BOX;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = align1024(smem_raw);
   uint8_t *sK = smem;
@@ -56,6 +66,12 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.y, y0 = blockIdx.x * TILE;
   const int nx = (P + TILE - 1) / TILE;
+  const int cnt = key_count ? min(max(key_count[b], 0), P) : P;
+  if (y0 >= cnt) {                       // whole tile is background: no loss term reads it
+    const int y = y0 + threadIdx.x;
+    if (threadIdx.x < TILE && y < P) lse[(long long)b * P + y] = 0.f;
+    return;
+  }
 
   if (threadIdx.x == 0) {
     mbar_init(bar_k, 1);
@@ -74,13 +90,13 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
   if (warp == 0) {
     if (lane == 0) {
       mbar_expect_tx(bar_k, OPER);
-      for (int kb = 0; kb < C / 64; ++kb) tma_load_3d(sK + kb * BOX_BYTES, &tm_k, bar_k, kb * 64, y0, b);
+      for (int kb = 0; kb < C / 64; ++kb) tma_load_3d(sK + kb * BOX, &tm_k, bar_k, kb * 64, y0, b);
       for (int i = 0; i < nx; ++i) {
         const int s = i % NST, ph = (i / NST) & 1;
         mbar_wait(&empty[s], ph ^ 1);
         mbar_expect_tx(&full[s], OPER);
         for (int kb = 0; kb < C / 64; ++kb)
-          tma_load_3d(sQ + s * OPER + kb * BOX_BYTES, &tm_q, &full[s], kb * 64, i * TILE, b);
+          tma_load_3d(sQ + s * OPER + kb * BOX, &tm_q, &full[s], kb * 64, i * TILE, b);
       }
     }
   } else if (warp == 1) {
@@ -96,7 +112,7 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         const uint32_t aQ = smem_u32(sQ + s * OPER);
 #pragma unroll
         for (int kk = 0; kk < C / 16; ++kk)
-          mma_f16_ss(tmem + buf * TILE, kmajor_desc(aK, kk), kmajor_desc(aQ, kk), idesc, kk > 0);
+          mma_f16_ss(tmem + buf * TILE, kmajor_desc(aK, kk, BOX), kmajor_desc(aQ, kk, BOX), idesc, kk > 0);
         mma_commit(&empty[s]);
         mma_commit(&tfull[buf]);
       }
@@ -105,7 +121,9 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     const int quad = warp & 3;
     const int y = y0 + quad * 32 + lane;
     const uint32_t lane_base = tmem + (uint32_t(quad * 32) << 16);
-    float sum = 0.f;
+    const f2 scale2 = f2_pack(scale_log2, scale_log2);
+    f2 acc_m = f2_pack(0.f, 0.f), acc_p = f2_pack(0.f, 0.f);
+    float tail = 0.f;
     for (int i = 0; i < nx; ++i) {
       const int buf = i & 1, tph = (i >> 1) & 1;
       mbar_wait(&tfull[buf], tph);
@@ -119,11 +137,20 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
           tmem_wait_ld();
           if ((ch + 1) * 32 <= nvalid) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) sum += ex2_approx(__uint_as_float(r[j]) * scale_log2);
+            for (int pr = 0; pr < 16; ++pr) {
+              const f2 rr = f2_pack_u(r[2 * pr], r[2 * pr + 1]);
+              if ((pr & 3) < PF) {
+                acc_p = f2_add(acc_p, exp2_poly2_scaled<3>(rr, scale2));
+              } else {
+                float a, c;
+                f2_unpack(f2_mul(rr, scale2), a, c);
+                acc_m = f2_add(acc_m, f2_pack(ex2_approx(a), ex2_approx(c)));
+              }
+            }
           } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j)
-              if (ch * 32 + j < nvalid) sum += ex2_approx(__uint_as_float(r[j]) * scale_log2);
+              if (ch * 32 + j < nvalid) tail += ex2_approx(__uint_as_float(r[j]) * scale_log2);
           }
         }
       }
@@ -131,7 +158,9 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[buf]);
     }
-    if (y < P) lse[(long long)b * P + y] = log2f(sum) * LN2;
+    float s0, s1;
+    f2_unpack(f2_add(acc_m, acc_p), s0, s1);
+    if (y < P) lse[(long long)b * P + y] = log2f(s0 + s1 + tail) * LN2;
   }
   tc_fence_before();
   __syncthreads();
@@ -139,178 +168,266 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
 }
 
 // ----------------------------------------------------------------- backward
-template <int C, int NST>
-__global__ void __launch_bounds__(NTHREADS)
+// nl[b, y] = -lse[b,y]*log2(e) for key columns that carry gradient, NL_MASKED otherwise; rows padded
+// to a multiple of 128 so every key tile's slice is one aligned bulk copy.
+__global__ void dense_nl_kernel(const float *__restrict__ lse, const float *__restrict__ mask_b,
+                                const int *__restrict__ key_count, float *__restrict__ nl, int P, int P_pad) {
+  const int b = blockIdx.y;
+  const int y = blockIdx.x * blockDim.x + threadIdx.x;
+  if (y >= P_pad) return;
+  float v = NL_MASKED;
+  if (y < P) {
+    bool on = true;
+    if (mask_b) on = mask_b[(long long)b * P + y] != 0.f;
+    if (key_count) on = on && (y < key_count[b]);
+    if (on) v = -lse[(long long)b * P + y] * LOG2E;
+  }
+  nl[(long long)b * P_pad + y] = v;
+}
+
+constexpr int GRAD_THREADS = 448;   // warp 0 TMA, warp 1 MMA + TMEM owner, warps 2-9 softmax, 10-13 epilogue
+
+template <int C, int TY, int NST, int NQ, int ND>
+struct GradCfg {
+  static constexpr int QBOX = TILE * 128;              // query box: 128 rows x 128 B
+  static constexpr int KBOX = TY * 128;                // key box:   TY rows x 128 B
+  static constexpr int OPER_Q = (C / 64) * QBOX;
+  static constexpr int OPER_K = (C / 64) * KBOX;
+  static constexpr int NBARS = 2 * NQ + 2 * NST + 4 + 2 * ND;
+  static constexpr size_t SMEM = 1024 + (size_t)NQ * OPER_Q + (size_t)NST * OPER_K + (size_t)NST * TY * 4 +
+                                 NBARS * 8 + 16;
+  static_assert(2 * TY + ND * C <= 512, "TMEM budget");
+};
+
+template <int C, int TY, int NST, int NQ, int ND, int PF>
+__global__ void __launch_bounds__(GRAD_THREADS, 1)
 dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
-                  const float *__restrict__ lse, const float *__restrict__ mask_a,
-                  const float *__restrict__ mask_b, const float *__restrict__ inv_norm,
-                  const float *__restrict__ alpha, const float *__restrict__ v1,
-                  const float *__restrict__ v2, float *__restrict__ dq, float scale_log2, int P) {
-  constexpr int OPER = (C / 64) * BOX_BYTES;
-  constexpr uint32_t TMEM_COLS = (C <= 128) ? 256 : 512;   // S/Ptilde 128 cols + dQhat C cols
+                  const __nv_bfloat16 *__restrict__ qhat, const float *__restrict__ nl,
+                  const int *__restrict__ key_count, const float *__restrict__ mask_a,
+                  const float *__restrict__ inv_norm, const float *__restrict__ alpha,
+                  const float *__restrict__ v1, const float *__restrict__ v2, float *__restrict__ dq,
+                  float scale_log2, int B, int P, int P_pad) {
+  using Cfg = GradCfg<C, TY, NST, NQ, ND>;
+  constexpr int W = TY / 2;                              // S columns per softmax warp
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = align1024(smem_raw);
   uint8_t *sQ = smem;
-  uint8_t *sK = smem + OPER;
-  float *nl2 = reinterpret_cast<float *>(sK + NST * OPER);   // [2][TILE]  -lse*log2e, or -inf
-  float *sv1 = nl2 + 2 * TILE;                               // [C]
-  float *sv2 = sv1 + C;                                      // [C]
-  uint64_t *bars = reinterpret_cast<uint64_t *>(sv2 + C);
-  uint64_t *bar_q = bars, *kfull = bars + 1, *kempty = kfull + NST, *s_full = kempty + NST,
-           *p_full = s_full + 1, *dq_full = p_full + 1;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(dq_full + 1);
+  uint8_t *sK = sQ + NQ * Cfg::OPER_Q;
+  float *nlbuf = reinterpret_cast<float *>(sK + NST * Cfg::OPER_K);      // [NST][TY]
+  uint64_t *bars = reinterpret_cast<uint64_t *>(nlbuf + NST * TY);
+  uint64_t *q_full = bars, *q_empty = q_full + NQ, *kfull = q_empty + NQ, *kempty = kfull + NST,
+           *s_full = kempty + NST, *p_full = s_full + 2, *d_full = p_full + 2, *d_empty = d_full + ND;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(d_empty + ND);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b = blockIdx.y, x0 = blockIdx.x * TILE;
-  const int ny = (P + TILE - 1) / TILE;
+  const int nxt = (P + TILE - 1) / TILE;
+  const int items = B * nxt;
 
   if (threadIdx.x == 0) {
-    mbar_init(bar_q, 1);
+    for (int i = 0; i < NQ; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&kfull[s], 1); mbar_init(&kempty[s], 1); }
-    mbar_init(s_full, 1);
-    mbar_init(p_full, 4);
-    mbar_init(dq_full, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 8); }
+    for (int i = 0; i < ND; ++i) { mbar_init(&d_full[i], 1); mbar_init(&d_empty[i], 4); }
     fence_barrier_init();
     prefetch_tmap(&tm_q);
     prefetch_tmap(&tm_k);
   }
-  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const uint32_t tmem_S = tmem, tmem_D = tmem + TILE;
+  const uint32_t tmem_D = tmem + 2 * TY;
+
+  auto key_tiles = [&](int b) {
+    const int cnt = key_count ? min(max(key_count[b], 0), P) : P;
+    return (cnt + TY - 1) / TY;
+  };
 
   if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      mbar_expect_tx(bar_q, OPER);
-      for (int kb = 0; kb < C / 64; ++kb) tma_load_3d(sQ + kb * BOX_BYTES, &tm_q, bar_q, kb * 64, x0, b);
-      for (int j = 0; j < ny; ++j) {
-        const int s = j % NST, ph = (j / NST) & 1;
-        mbar_wait(&kempty[s], ph ^ 1);
-        mbar_expect_tx(&kfull[s], OPER);
+      int g = 0, it = 0;
+      for (int w = blockIdx.x; w < items; w += gridDim.x, ++it) {
+        const int b = w / nxt, x0 = (w % nxt) * TILE, ny = key_tiles(b);
+        const int qb = it % NQ;
+        mbar_wait(&q_empty[qb], ((it / NQ) & 1) ^ 1);
+        mbar_expect_tx(&q_full[qb], Cfg::OPER_Q);
         for (int kb = 0; kb < C / 64; ++kb)
-          tma_load_3d(sK + s * OPER + kb * BOX_BYTES, &tm_k, &kfull[s], kb * 64, j * TILE, b);
+          tma_load_3d(sQ + qb * Cfg::OPER_Q + kb * Cfg::QBOX, &tm_q, &q_full[qb], kb * 64, x0, b);
+        for (int j = 0; j < ny; ++j, ++g) {
+          const int s = g % NST;
+          mbar_wait(&kempty[s], ((g / NST) & 1) ^ 1);
+          mbar_expect_tx(&kfull[s], Cfg::OPER_K + TY * 4);
+          for (int kb = 0; kb < C / 64; ++kb)
+            tma_load_3d(sK + s * Cfg::OPER_K + kb * Cfg::KBOX, &tm_k, &kfull[s], kb * 64, j * TY, b);
+          bulk_load_1d(nlbuf + s * TY, nl + (long long)b * P_pad + j * TY, TY * 4, &kfull[s]);
+        }
       }
     }
   } else if (warp == 1) {
+    // -------------------------------------------------------------- MMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc_s = make_idesc(TILE, TILE, FMT_BF16, FMT_BF16, MAJOR_K, MAJOR_K);
+      constexpr uint32_t idesc_s = make_idesc(TILE, TY, FMT_BF16, FMT_BF16, MAJOR_K, MAJOR_K);
       constexpr uint32_t idesc_d = make_idesc(TILE, C, FMT_BF16, FMT_BF16, MAJOR_K, MAJOR_MN);
-      const uint32_t aQ = smem_u32(sQ);
-      mbar_wait(bar_q, 0);
-      for (int j = 0; j < ny; ++j) {
-        const int s = j % NST, ph = (j / NST) & 1;
-        const uint32_t aK = smem_u32(sK + s * OPER);
-        mbar_wait(&kfull[s], ph);
-        tc_fence_after();
-        // S = Qhat_x . Khat_y^T   (overwrites the previous Ptilde: same-thread MMAs run in order)
+      int g = 0, it = 0;
+      for (int w = blockIdx.x; w < items; w += gridDim.x, ++it) {
+        const int b = w / nxt, ny = key_tiles(b);
+        const int qb = it % NQ, db = it % ND;
+        const uint32_t aQ = smem_u32(sQ + qb * Cfg::OPER_Q);
+        const uint32_t tD = tmem_D + db * C;
+        mbar_wait(&q_full[qb], (it / NQ) & 1);
+        mbar_wait(&d_empty[db], ((it / ND) & 1) ^ 1);
+        auto issue_s = [&](int gi) {                       // S(gi) = Qhat_x . Khat_y^T -> S buffer gi&1
+          const int s = gi % NST;
+          const uint32_t aK = smem_u32(sK + s * Cfg::OPER_K);
+          mbar_wait(&kfull[s], (gi / NST) & 1);
+          tc_fence_after();
 #pragma unroll
-        for (int kk = 0; kk < C / 16; ++kk)
-          mma_f16_ss(tmem_S, kmajor_desc(aQ, kk), kmajor_desc(aK, kk), idesc_s, kk > 0);
-        mma_commit(s_full);
-        mbar_wait(p_full, j & 1);
-        tc_fence_after();
-        // dQhat += Ptilde . Khat_y : A = bf16 pairs in TMEM (8 columns per K=16 slice),
-        // B = the key tile read MN-major: 16 key rows per slice (2 KB), 64-channel chunks 16 KB apart.
+          for (int kk = 0; kk < C / 16; ++kk)
+            mma_f16_ss(tmem + (gi & 1) * TY, kmajor_desc(aQ, kk, Cfg::QBOX), kmajor_desc(aK, kk, Cfg::KBOX),
+                       idesc_s, kk > 0);
+          mma_commit(&s_full[gi & 1]);
+        };
+        if (ny > 0) issue_s(g);
+        for (int j = 0; j < ny; ++j, ++g) {
+          if (j + 1 < ny) issue_s(g + 1);
+          const int s = g % NST;
+          const uint32_t aK = smem_u32(sK + s * Cfg::OPER_K);
+          const uint32_t tS = tmem + (g & 1) * TY;
+          mbar_wait(&p_full[g & 1], (g >> 1) & 1);
+          tc_fence_after();
+          // dQhat += P~ . Khat_y : A = bf16 pairs in TMEM (8 columns per K=16 slice; each softmax warp
+          // packed its W columns at the start of its own region), B = the key tile read MN-major:
+          // 16 key rows (2 KB) per slice, 64-channel chunks KBOX apart.
 #pragma unroll
-        for (int kk = 0; kk < TILE / 16; ++kk)
-          mma_f16_ts(tmem_D, tmem_S + kk * 8, make_sdesc(aK + kk * 2048, BOX_BYTES, 1024), idesc_d,
-                     (j > 0 || kk > 0) ? 1u : 0u);
-        mma_commit(&kempty[s]);
+          for (int kk = 0; kk < TY / 16; ++kk) {
+            const int half = (kk * 16) / W, local = (kk * 16) % W;
+            mma_f16_ts(tD, tS + half * W + local / 2, make_sdesc(aK + kk * 2048, Cfg::KBOX, 1024), idesc_d,
+                       (j > 0 || kk > 0) ? 1u : 0u);
+          }
+          mma_commit(&kempty[s]);
+        }
+        mma_commit(&q_empty[qb]);
+        mma_commit(&d_full[db]);
       }
-      mma_commit(dq_full);
+    }
+  } else if (warp < 10) {
+    // ------------------------------------------------ softmax warps: S -> P~ (bf16, in place)
+    const int quad = warp & 3, half = (warp - 2) >> 2;
+    const uint32_t lane_off = uint32_t(quad * 32) << 16;
+    const f2 scale2 = f2_pack(scale_log2, scale_log2);
+    int g = 0;
+    for (int w = blockIdx.x; w < items; w += gridDim.x) {
+      const int ny = key_tiles(w / nxt);
+      for (int j = 0; j < ny; ++j, ++g) {
+        const int s = g % NST;
+        const uint32_t tS = tmem + (g & 1) * TY + lane_off + half * W;
+        mbar_wait(&kfull[s], (g / NST) & 1);             // nl slice of this tile landed (bulk copy)
+        mbar_wait(&s_full[g & 1], (g >> 1) & 1);
+        tc_fence_after();
+        const float *nlw = nlbuf + s * TY + half * W;
+#pragma unroll
+        for (int ch = 0; ch < W / 32; ++ch) {
+          uint32_t r[32], pk[16];
+          tmem_ld32(tS + ch * 32, r);
+          tmem_wait_ld();
+          const float4 *nl4 = reinterpret_cast<const float4 *>(nlw + ch * 32);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const float4 n4 = nl4[u];
+            const f2 xa = f2_fma(f2_pack_u(r[4 * u], r[4 * u + 1]), scale2, f2_pack(n4.x, n4.y));
+            const f2 xb = f2_fma(f2_pack_u(r[4 * u + 2], r[4 * u + 3]), scale2, f2_pack(n4.z, n4.w));
+            float a0, a1, b0, b1;
+            if (((2 * u) & 3) < PF) {
+              f2_unpack(exp2_poly2<2>(xa), a0, a1);
+            } else {
+              f2_unpack(xa, a0, a1);
+              a0 = ex2_approx(a0); a1 = ex2_approx(a1);
+            }
+            if (((2 * u + 1) & 3) < PF) {
+              f2_unpack(exp2_poly2<2>(xb), b0, b1);
+            } else {
+              f2_unpack(xb, b0, b1);
+              b0 = ex2_approx(b0); b1 = ex2_approx(b1);
+            }
+            pk[2 * u] = pack_bf16x2(a0, a1);
+            pk[2 * u + 1] = pack_bf16x2(b0, b1);
+          }
+          tmem_st16(tS + ch * 16, pk);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[g & 1]);
+      }
     }
   } else {
+    // ---- epilogue warps: rank-1 terms, F.normalize backward, coalesced store along P
     const int quad = warp & 3;
-    const int st = threadIdx.x - 64;                 // 0..127 among softmax threads
     const int row = quad * 32 + lane;
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
-    for (int c = st; c < C; c += 128) {
-      sv1[c] = v1[(long long)b * C + c];
-      sv2[c] = v2 ? v2[(long long)b * C + c] : 0.f;
-    }
-    for (int j = 0; j < ny; ++j) {
-      const int y = j * TILE + st;
-      float nl = -INFINITY;
-      if (y < P && mask_b[(long long)b * P + y] != 0.f) nl = -lse[(long long)b * P + y] * LOG2E;
-      float *nlbuf = nl2 + (j & 1) * TILE;
-      nlbuf[st] = nl;
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      mbar_wait(s_full, j & 1);
+    int it = 0;
+    for (int w = blockIdx.x; w < items; w += gridDim.x, ++it) {
+      const int b = w / nxt, x0 = (w % nxt) * TILE, ny = key_tiles(b);
+      const int db = it % ND;
+      const int x = x0 + row;
+      const bool valid = x < P;
+      const float a = valid ? mask_a[(long long)b * P + x] : 0.f;
+      const float inr = valid ? inv_norm[(long long)b * P + x] : 0.f;
+      const float al = (ny > 0) ? alpha[b] : 0.f;
+      const float *v1b = v1 + (long long)b * C;
+      const float *v2b = v2 ? v2 + (long long)b * C : nullptr;
+      const uint4 *qrow = reinterpret_cast<const uint4 *>(qhat + ((long long)b * P + (valid ? x : 0)) * C);
+      mbar_wait(&d_full[db], (it / ND) & 1);
       tc_fence_after();
-#pragma unroll
-      for (int ch = 0; ch < TILE / 32; ++ch) {
-        uint32_t r[32], pk[16];
-        tmem_ld32(tmem_S + lane_off + ch * 32, r);
-        tmem_wait_ld();
-        const float4 *nl4 = reinterpret_cast<const float4 *>(nlbuf + ch * 32);
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const float4 n4 = nl4[u];
-          const float p0 = ex2_approx(fmaf(__uint_as_float(r[4 * u + 0]), scale_log2, n4.x));
-          const float p1 = ex2_approx(fmaf(__uint_as_float(r[4 * u + 1]), scale_log2, n4.y));
-          const float p2 = ex2_approx(fmaf(__uint_as_float(r[4 * u + 2]), scale_log2, n4.z));
-          const float p3 = ex2_approx(fmaf(__uint_as_float(r[4 * u + 3]), scale_log2, n4.w));
-          pk[2 * u] = pack_bf16x2(p0, p1);
-          pk[2 * u + 1] = pack_bf16x2(p2, p3);
-        }
-        tmem_st16(tmem_S + lane_off + ch * 16, pk);
-      }
-      tmem_wait_st();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(p_full);
-    }
-    // ---- epilogue: rank-1 terms, F.normalize backward, coalesced store along P
-    mbar_wait(bar_q, 0);                        // TMA-written Qhat tile visible to this thread
-    mbar_wait(dq_full, 0);
-    tc_fence_after();
-    const int x = x0 + row;
-    const bool valid = x < P;
-    const float a = valid ? mask_a[(long long)b * P + x] : 0.f;
-    const float inr = valid ? inv_norm[(long long)b * P + x] : 0.f;
-    const float al = alpha[b];
-    const uint8_t *qrow = sQ + row * 128;
-    float dot = 0.f;
+      const uint32_t tD = tmem_D + db * C + lane_off;
+      float dot = 0.f;
 #pragma unroll 1
-    for (int pass = 0; pass < 2; ++pass) {
+      for (int pass = 0; pass < 2; ++pass) {
 #pragma unroll 1
-      for (int ch = 0; ch < C / 32; ++ch) {
-        uint32_t r[32];
-        tmem_ld32(tmem_D + lane_off + ch * 32, r);
-        tmem_wait_ld();
-        const uint8_t *qbox = qrow + (ch >> 1) * BOX_BYTES;
+        for (int ch = 0; ch < C / 32; ++ch) {
+          uint32_t r[32];
+          if (ny > 0) {
+            tmem_ld32(tD + ch * 32, r);
+            tmem_wait_ld();
+          } else {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int jc = (ch & 1) * 4 + u;                       // 16-byte chunk within the 128-byte row
-          const uint4 qv = *reinterpret_cast<const uint4 *>(qbox + ((jc ^ (row & 7)) << 4));
-          const uint32_t qw[4] = {qv.x, qv.y, qv.z, qv.w};
+            for (int i = 0; i < 32; ++i) r[i] = 0u;
+          }
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int c = ch * 32 + u * 8 + e;
-            const float qh = __uint_as_float((e & 1) ? (qw[e >> 1] & 0xffff0000u) : (qw[e >> 1] << 16));
-            const float s2 = sv2[c];
-            const float g = fmaf(al, __uint_as_float(r[u * 8 + e]), fmaf(a, sv1[c] - s2, s2));
-            if (pass == 0) dot = fmaf(qh, g, dot);
-            else if (valid) dq[((long long)b * C + c) * P + x] = (g - qh * dot) * inr;
+          for (int u = 0; u < 4; ++u) {
+            const uint4 qv = __ldg(qrow + ch * 4 + u);
+            const uint32_t qw[4] = {qv.x, qv.y, qv.z, qv.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int c = ch * 32 + u * 8 + e;
+              const float qh = __uint_as_float((e & 1) ? (qw[e >> 1] & 0xffff0000u) : (qw[e >> 1] << 16));
+              const float s2 = v2b ? __ldg(v2b + c) : 0.f;
+              const float gq = fmaf(al, __uint_as_float(r[u * 8 + e]), fmaf(a, __ldg(v1b + c) - s2, s2));
+              if (pass == 0) dot = fmaf(qh, gq, dot);
+              else if (valid) dq[((long long)b * C + c) * P + x] = (gq - qh * dot) * inr;
+            }
           }
         }
       }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&d_empty[db]);
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem, TMEM_COLS);
+  if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
 // ---------------------------------------------------------------------- host
-int make_feature_tmap(CUtensorMap *tm, const void *base, int B, int C, int P) {
+int make_feature_tmap(CUtensorMap *tm, const void *base, int B, int C, int P, int box_rows) {
   EncodeTiledFn enc = get_encode_tiled();
   if (!enc) { cp2_set_error("cuTensorMapEncodeTiled unavailable in this driver"); return CP2_E_UNSUPPORTED; }
   const cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)P, (cuuint64_t)B};
   const cuuint64_t strides[2] = {(cuuint64_t)C * 2, (cuuint64_t)P * C * 2};
-  const cuuint32_t box[3] = {64, TILE, 1};
+  const cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
   const cuuint32_t estr[3] = {1, 1, 1};
   const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void *>(base), dims, strides, box, estr,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -319,70 +436,102 @@ int make_feature_tmap(CUtensorMap *tm, const void *base, int B, int C, int P) {
   return CP2_OK;
 }
 
-template <int C>
-constexpr size_t lse_smem(int nst) { return 1024 + (size_t)(C / 64) * BOX_BYTES * (1 + nst) + 256; }
-template <int C>
-constexpr size_t grad_smem(int nst) {
-  return 1024 + (size_t)(C / 64) * BOX_BYTES * (1 + nst) + sizeof(float) * (2 * TILE + 2 * C) + 256;
+// share of the exponentials evaluated on the FMA pipe, in quarters (0..3); tunable for experiments
+int poly_quarters(const char *env, int dflt) {
+  const char *e = getenv(env);
+  if (!e || !*e) return dflt;
+  const int v = atoi(e);
+  return v < 0 ? 0 : (v > 3 ? 3 : v);
 }
 
-template <int C, int NST>
-int launch_lse(const CUtensorMap &tq, const CUtensorMap &tk, float *lse, float scale_log2, int B, int P,
-               cudaStream_t st) {
+template <int C>
+constexpr size_t lse_smem(int nst) { return 1024 + (size_t)(C / 64) * TILE * 128 * (1 + nst) + 256; }
+
+template <int C, int PF>
+int launch_lse(const CUtensorMap &tq, const CUtensorMap &tk, const int *key_count, float *lse, float scale_log2,
+               int B, int P, cudaStream_t st) {
+  constexpr int NST = 2;
   const size_t smem = lse_smem<C>(NST);
-  CP2_CUDA(cudaFuncSetAttribute(dense_lse_kernel<C, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CP2_CUDA(cudaFuncSetAttribute(dense_lse_kernel<C, NST, PF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(cp2_cdiv(P, TILE), B);
-  dense_lse_kernel<C, NST><<<grid, NTHREADS, smem, st>>>(tq, tk, lse, scale_log2, P);
+  dense_lse_kernel<C, NST, PF><<<grid, LSE_THREADS, smem, st>>>(tq, tk, key_count, lse, scale_log2, P);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }
 
-template <int C, int NST>
-int launch_grad(const CUtensorMap &tq, const CUtensorMap &tk, const float *lse, const float *mask_a,
-                const float *mask_b, const float *inv_norm, const float *alpha, const float *v1,
-                const float *v2, float *dq, float scale_log2, int B, int P, cudaStream_t st) {
-  const size_t smem = grad_smem<C>(NST);
-  CP2_CUDA(cudaFuncSetAttribute(dense_grad_kernel<C, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid(cp2_cdiv(P, TILE), B);
-  dense_grad_kernel<C, NST><<<grid, NTHREADS, smem, st>>>(tq, tk, lse, mask_a, mask_b, inv_norm, alpha, v1, v2, dq,
-                                                          scale_log2, P);
+template <int C, int TY, int NST, int NQ, int ND, int PF>
+int launch_grad(const CUtensorMap &tq, const CUtensorMap &tk, const void *qhat, const float *nl,
+                const int *key_count, const float *mask_a, const float *inv_norm, const float *alpha,
+                const float *v1, const float *v2, float *dq, float scale_log2, int B, int P, int P_pad,
+                cudaStream_t st) {
+  using Cfg = GradCfg<C, TY, NST, NQ, ND>;
+  auto kern = dense_grad_kernel<C, TY, NST, NQ, ND, PF>;
+  CP2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+  const long long items = (long long)B * cp2_cdiv(P, TILE);
+  const int grid = (int)(items < cp2_num_sms() ? items : cp2_num_sms());
+  kern<<<grid, GRAD_THREADS, Cfg::SMEM, st>>>(tq, tk, static_cast<const __nv_bfloat16 *>(qhat), nl, key_count,
+                                              mask_a, inv_norm, alpha, v1, v2, dq, scale_log2, B, P, P_pad);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }
 
 }  // namespace
 
-extern "C" int cp2_dense_lse(const void *qhat_t, const void *khat_t, float *lse, float inv_tau, int B, int C,
-                             int P, void *stream) {
-  CP2_REQUIRE(qhat_t && khat_t && lse, "cp2_dense_lse: null pointer");
+extern "C" int cp2_dense_pad(int P) { return P > 0 ? cp2_cdiv(P, TILE) * TILE : 0; }
+
+extern "C" int cp2_dense_lse(const void *qhat_t, const void *khat_t, const int *key_count, float *lse,
+                             float inv_tau, int B, int C, int P, void *stream) {
   CP2_REQUIRE(C == 128 || C == 256, "cp2_dense_lse: C=%d unsupported (128 or 256)", C);
   CP2_REQUIRE(B >= 0 && P > 0 && B <= 65535, "cp2_dense_lse: bad shape B=%d P=%d", B, P);
+  CP2_REQUIRE(inv_tau > 0.f && inv_tau <= 16.f, "cp2_dense_lse: 1/tau=%g outside (0, 16]", (double)inv_tau);
   if (B == 0) return CP2_OK;
+  CP2_REQUIRE(qhat_t && khat_t && lse, "cp2_dense_lse: null pointer");
   CUtensorMap tq, tk;
   int rc;
-  if ((rc = make_feature_tmap(&tq, qhat_t, B, C, P)) != CP2_OK) return rc;
-  if ((rc = make_feature_tmap(&tk, khat_t, B, C, P)) != CP2_OK) return rc;
+  if ((rc = make_feature_tmap(&tq, qhat_t, B, C, P, TILE)) != CP2_OK) return rc;
+  if ((rc = make_feature_tmap(&tk, khat_t, B, C, P, TILE)) != CP2_OK) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const float scale_log2 = inv_tau * LOG2E;
-  if (C == 128) return launch_lse<128, 2>(tq, tk, lse, scale_log2, B, P, st);
-  return launch_lse<256, 2>(tq, tk, lse, scale_log2, B, P, st);
+  const float sl2 = inv_tau * LOG2E;
+  const int pf = poly_quarters("CP2_DENSE_PF_FWD", 2);
+#define CP2_LSE(CC, PFV) launch_lse<CC, PFV>(tq, tk, key_count, lse, sl2, B, P, st)
+  if (C == 128) {
+    switch (pf) { case 0: return CP2_LSE(128, 0); case 1: return CP2_LSE(128, 1); case 2: return CP2_LSE(128, 2);
+                  default: return CP2_LSE(128, 3); }
+  }
+  switch (pf) { case 0: return CP2_LSE(256, 0); case 1: return CP2_LSE(256, 1); case 2: return CP2_LSE(256, 2);
+                default: return CP2_LSE(256, 3); }
+#undef CP2_LSE
 }
 
-extern "C" int cp2_dense_grad(const void *qhat_t, const void *khat_t, const float *lse, const float *mask_a,
-                              const float *mask_b, const float *inv_norm, const float *alpha, const float *v1,
-                              const float *v2, float *dq, float inv_tau, int B, int C, int P, void *stream) {
-  CP2_REQUIRE(qhat_t && khat_t && lse && mask_a && mask_b && inv_norm && alpha && v1 && dq,
-              "cp2_dense_grad: null pointer");
+extern "C" int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int *key_count, const float *lse,
+                              const float *mask_a, const float *mask_b, const float *inv_norm,
+                              const float *alpha, const float *v1, const float *v2, float *dq,
+                              float *scratch_nl, float inv_tau, int B, int C, int P, void *stream) {
   CP2_REQUIRE(C == 128 || C == 256, "cp2_dense_grad: C=%d unsupported (128 or 256)", C);
   CP2_REQUIRE(B >= 0 && P > 0 && B <= 65535, "cp2_dense_grad: bad shape B=%d P=%d", B, P);
+  CP2_REQUIRE(inv_tau > 0.f && inv_tau <= 16.f, "cp2_dense_grad: 1/tau=%g outside (0, 16]", (double)inv_tau);
   if (B == 0) return CP2_OK;
+  CP2_REQUIRE(qhat_t && khat_t && lse && mask_a && inv_norm && alpha && v1 && dq && scratch_nl,
+              "cp2_dense_grad: null pointer");
+  const int TY = (C == 128) ? 128 : 64;
   CUtensorMap tq, tk;
   int rc;
-  if ((rc = make_feature_tmap(&tq, qhat_t, B, C, P)) != CP2_OK) return rc;
-  if ((rc = make_feature_tmap(&tk, khat_t, B, C, P)) != CP2_OK) return rc;
+  if ((rc = make_feature_tmap(&tq, qhat_t, B, C, P, TILE)) != CP2_OK) return rc;
+  if ((rc = make_feature_tmap(&tk, khat_t, B, C, P, TY)) != CP2_OK) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const float scale_log2 = inv_tau * LOG2E;
-  if (C == 128)
-    return launch_grad<128, 2>(tq, tk, lse, mask_a, mask_b, inv_norm, alpha, v1, v2, dq, scale_log2, B, P, st);
-  return launch_grad<256, 2>(tq, tk, lse, mask_a, mask_b, inv_norm, alpha, v1, v2, dq, scale_log2, B, P, st);
+  const int P_pad = cp2_dense_pad(P);
+  dense_nl_kernel<<<dim3(cp2_cdiv(P_pad, 256), B), 256, 0, st>>>(lse, mask_b, key_count, scratch_nl, P, P_pad);
+  CP2_LAUNCH_CHECK();
+  const float sl2 = inv_tau * LOG2E;
+  const int pf = poly_quarters("CP2_DENSE_PF_BWD", 2);
+#define CP2_GRAD(CC, TYV, NQV, NDV, PFV)                                                                      \
+  launch_grad<CC, TYV, 3, NQV, NDV, PFV>(tq, tk, qhat_t, scratch_nl, key_count, mask_a, inv_norm, alpha, v1, \
+                                         v2, dq, sl2, B, P, P_pad, st)
+  if (C == 128) {
+    switch (pf) { case 0: return CP2_GRAD(128, 128, 2, 2, 0); case 1: return CP2_GRAD(128, 128, 2, 2, 1);
+                  case 2: return CP2_GRAD(128, 128, 2, 2, 2); default: return CP2_GRAD(128, 128, 2, 2, 3); }
+  }
+  switch (pf) { case 0: return CP2_GRAD(256, 64, 1, 1, 0); case 1: return CP2_GRAD(256, 64, 1, 1, 1);
+                case 2: return CP2_GRAD(256, 64, 1, 1, 2); default: return CP2_GRAD(256, 64, 1, 1, 3); }
+#undef CP2_GRAD
 }

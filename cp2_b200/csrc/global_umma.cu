@@ -258,17 +258,38 @@ global_nce_kernel(const __grid_constant__ CUtensorMap tm_queue, const float *__r
   if (warp == 1) tmem_dealloc(tmem, TMEM_COLS);
 }
 
-__global__ void global_finalize_kernel(const float *__restrict__ part_z, const float *__restrict__ part_g,
-                                       float *__restrict__ z, float *__restrict__ g, int NB, int nctas) {
-  const int b = blockIdx.x, chunk = b / ROWS, bl = b % ROWS, c = threadIdx.x;
-  float s = 0.f, sz = 0.f;
-  for (int cta = 0; cta < nctas; ++cta) {
+// Fixed-order reduction of the per-CTA partials: 8 slices of the CTA range are summed in parallel
+// (thread = channel x slice), then combined in slice order -> deterministic, ~19 dependent loads deep.
+constexpr int FIN_SLICES = 8;
+__global__ void __launch_bounds__(CDIM * FIN_SLICES)
+global_finalize_kernel(const float *__restrict__ part_z, const float *__restrict__ part_g,
+                       float *__restrict__ z, float *__restrict__ g, int NB, int nctas) {
+  __shared__ float sg[FIN_SLICES][CDIM];
+  __shared__ float sz[FIN_SLICES];
+  const int b = blockIdx.x, chunk = b / ROWS, bl = b % ROWS;
+  const int c = threadIdx.x % CDIM, sl = threadIdx.x / CDIM;
+  float s = 0.f, szv = 0.f;
+#pragma unroll 4
+  for (int cta = sl; cta < nctas; cta += FIN_SLICES) {
     const long long pb = (long long)(chunk * nctas + cta) * NB + bl;
     s += part_g[pb * CDIM + c];
-    if (c == 0) sz += part_z[pb];
+    if (c == 0) szv += part_z[pb];
   }
-  g[(long long)b * CDIM + c] = s;
-  if (c == 0) z[b] = sz;
+  sg[sl][c] = s;
+  if (c == 0) sz[sl] = szv;
+  __syncthreads();
+  if (sl == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < FIN_SLICES; ++i) t += sg[i][c];
+    g[(long long)b * CDIM + c] = t;
+    if (c == 0) {
+      float tz = 0.f;
+#pragma unroll
+      for (int i = 0; i < FIN_SLICES; ++i) tz += sz[i];
+      z[b] = tz;
+    }
+  }
 }
 
 int pick_nb(int B) { return B <= 16 ? 16 : 32; }
@@ -332,7 +353,7 @@ extern "C" int cp2_global_nce(const float *q_pos, const float *queue, float *z, 
   if (NB == 16) rc = launch_global<16>(tq, q_pos, part_z, part_g, scale_log2, B, K, nctas, chunks, st);
   else rc = launch_global<32>(tq, q_pos, part_z, part_g, scale_log2, B, K, nctas, chunks, st);
   if (rc != CP2_OK) return rc;
-  global_finalize_kernel<<<B, CDIM, 0, st>>>(part_z, part_g, z, g, NB, nctas);
+  global_finalize_kernel<<<B, CDIM * FIN_SLICES, 0, st>>>(part_z, part_g, z, g, NB, nctas);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }

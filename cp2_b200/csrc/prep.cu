@@ -16,16 +16,44 @@ template <int C>
 __global__ void __launch_bounds__(256)
 prep_kernel(const float *__restrict__ feat, const float *__restrict__ mask,
             __nv_bfloat16 *__restrict__ fhat_t, float *__restrict__ inv_norm,
-            float *__restrict__ scratch, int P, int tiles) {
+            float *__restrict__ scratch, int32_t *__restrict__ key_count, int P, int tiles) {
   __shared__ float tile[C][PT + 1];
   __shared__ float ssq[8][PT];
   __shared__ float den[PT];
   __shared__ float mk[PT];
+  __shared__ int dest[PT];          // compact mode: destination row of each pixel of the tile
+  __shared__ int cnt_s[2][8];
   const int b = blockIdx.y, tl = blockIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int x = tl * PT + lane;
   const bool valid = x < P;
   const float *__restrict__ src = feat + (long long)b * C * P + x;
+  if (key_count != nullptr) {
+    // stable partition of the image's pixels: foreground rows first, background rows (zeroed) after
+    int before = 0, total = 0;
+    for (int i = threadIdx.x; i < P; i += 256) {
+      const int on = mask[(long long)b * P + i] != 0.f;
+      total += on;
+      before += on && (i < tl * PT);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      before += __shfl_xor_sync(0xffffffffu, before, o);
+      total += __shfl_xor_sync(0xffffffffu, total, o);
+    }
+    if (lane == 0) { cnt_s[0][warp] = before; cnt_s[1][warp] = total; }
+    __syncthreads();
+    if (warp == 0) {
+      before = 0; total = 0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) { before += cnt_s[0][w]; total += cnt_s[1][w]; }
+      const bool on = valid && mask[(long long)b * P + x] != 0.f;
+      const unsigned fgm = __ballot_sync(0xffffffffu, on);
+      const int fg_lt = __popc(fgm & ((1u << lane) - 1u));
+      dest[lane] = on ? (before + fg_lt) : (total + (x - before - fg_lt));
+      if (tl == 0 && lane == 0) key_count[b] = total;
+    }
+  }
   float sum = 0.f;
 #pragma unroll 4
   for (int c = warp; c < C; c += 8) {
@@ -67,11 +95,13 @@ prep_kernel(const float *__restrict__ feat, const float *__restrict__ mask,
     const int p = warp * (PT / 8) + pp;
     const int xx = tl * PT + p;
     if (xx < P) {
-      __nv_bfloat162 *dst = reinterpret_cast<__nv_bfloat162 *>(fhat_t + ((long long)b * P + xx) * C);
+      const int row = key_count ? dest[p] : xx;
+      const float keep = (key_count && mk[p] == 0.f) ? 0.f : 1.f;
+      __nv_bfloat162 *dst = reinterpret_cast<__nv_bfloat162 *>(fhat_t + ((long long)b * P + row) * C);
 #pragma unroll
       for (int j = 0; j < C / 64; ++j) {
         const int c = j * 64 + lane * 2;
-        dst[c >> 1] = __floats2bfloat162_rn(tile[c][p], tile[c + 1][p]);
+        dst[c >> 1] = __floats2bfloat162_rn(tile[c][p] * keep, tile[c + 1][p] * keep);
       }
     }
   }
@@ -94,8 +124,8 @@ __global__ void prep_reduce_kernel(const float *__restrict__ scratch, float *__r
 extern "C" int cp2_prep_tiles(int P) { return cp2_cdiv(P, PT); }
 
 extern "C" int cp2_prep_features(const float *feat, const float *mask, void *fhat_t, float *inv_norm,
-                                 float *pos_sum, float *neg_sum, float *scratch, int B, int C, int P,
-                                 void *stream) {
+                                 float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count, int B,
+                                 int C, int P, void *stream) {
   CP2_REQUIRE(feat && mask && fhat_t && inv_norm && pos_sum && neg_sum && scratch, "cp2_prep_features: null pointer");
   CP2_REQUIRE(B >= 0 && P > 0, "cp2_prep_features: bad shape B=%d P=%d", B, P);
   CP2_REQUIRE(C == 64 || C == 128 || C == 192 || C == 256, "cp2_prep_features: C=%d unsupported (64,128,192,256)", C);
@@ -105,10 +135,10 @@ extern "C" int cp2_prep_features(const float *feat, const float *mask, void *fha
   dim3 grid(tiles, B);
   auto *out = static_cast<__nv_bfloat16 *>(fhat_t);
   switch (C) {
-    case 64: prep_kernel<64><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, P, tiles); break;
-    case 128: prep_kernel<128><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, P, tiles); break;
-    case 192: prep_kernel<192><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, P, tiles); break;
-    default: prep_kernel<256><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, P, tiles); break;
+    case 64: prep_kernel<64><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, key_count, P, tiles); break;
+    case 128: prep_kernel<128><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, key_count, P, tiles); break;
+    case 192: prep_kernel<192><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, key_count, P, tiles); break;
+    default: prep_kernel<256><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, key_count, P, tiles); break;
   }
   CP2_LAUNCH_CHECK();
   prep_reduce_kernel<<<B, 256, 0, st>>>(scratch, pos_sum, neg_sum, C, tiles);

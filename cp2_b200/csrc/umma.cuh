@@ -186,6 +186,107 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16
       : "memory");
 }
 
+// 1-D bulk copy global -> shared (bytes % 16 == 0, both addresses 16-byte aligned), completes on an mbarrier
+__device__ __forceinline__ void bulk_load_1d(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// ------------------------------------------------------- packed fp32x2 math (FFMA2 / FADD2 / FMUL2)
+struct f2 { unsigned long long v; };
+__device__ __forceinline__ f2 f2_pack(float lo, float hi) {
+  f2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ f2 f2_pack_u(uint32_t lo, uint32_t hi) {
+  f2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(f2 a, float &lo, float &hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v));
+}
+__device__ __forceinline__ void f2_unpack_u(f2 a, uint32_t &lo, uint32_t &hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(a.v));
+}
+__device__ __forceinline__ f2 f2_fma(f2 a, f2 b, f2 c) {
+  f2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v));
+  return r;
+}
+__device__ __forceinline__ f2 f2_add(f2 a, f2 b) {
+  f2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+__device__ __forceinline__ f2 f2_sub(f2 a, f2 b) {
+  f2 r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+__device__ __forceinline__ f2 f2_mul(f2 a, f2 b) {
+  f2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+
+// 2^x for a pair on the FMA/ALU pipes (no MUFU): Cody-Waite split x = n + f, |f| <= 0.5 by the
+// 1.5*2^23 rounding trick, minimax polynomial of degree DEG for 2^f (max rel. error 1.7e-3 / 7.6e-5 /
+// 2.7e-6 for DEG 2 / 3 / 4), exponent spliced in with one shift-add.  Requires -126 <= x <= 126.
+template <int DEG>
+__device__ __forceinline__ f2 exp2_poly2(f2 x) {
+  const f2 magic = f2_pack(12582912.f, 12582912.f);
+  const f2 t = f2_add(x, magic);
+  const f2 f = f2_sub(x, f2_sub(t, magic));
+  f2 p;
+  if constexpr (DEG == 2) {
+    p = f2_fma(f2_pack(0.23840933f, 0.23840933f), f, f2_pack(0.70340872f, 0.70340872f));
+    p = f2_fma(p, f, f2_pack(1.00044143f, 1.00044143f));
+  } else if constexpr (DEG == 3) {
+    p = f2_fma(f2_pack(0.05516955f, 0.05516955f), f, f2_pack(0.24260588f, 0.24260588f));
+    p = f2_fma(p, f, f2_pack(0.69326085f, 0.69326085f));
+    p = f2_fma(p, f, f2_pack(0.99992841f, 0.99992841f));
+  } else {
+    p = f2_fma(f2_pack(0.0095698982f, 0.0095698982f), f, f2_pack(0.055917259f, 0.055917259f));
+    p = f2_fma(p, f, f2_pack(0.24024744f, 0.24024744f));
+    p = f2_fma(p, f, f2_pack(0.69312191f, 0.69312191f));
+    p = f2_fma(p, f, f2_pack(0.99999928f, 0.99999928f));
+  }
+  uint32_t p0, p1, t0, t1;
+  f2_unpack_u(p, p0, p1);
+  f2_unpack_u(t, t0, t1);
+  return f2_pack_u(p0 + (t0 << 23), p1 + (t1 << 23));
+}
+
+// 2^(r*scale) for a pair, the scale folded into the range reduction (saves the separate multiply).
+template <int DEG>
+__device__ __forceinline__ f2 exp2_poly2_scaled(f2 r, f2 scale) {
+  const f2 magic = f2_pack(12582912.f, 12582912.f);
+  const f2 t = f2_fma(r, scale, magic);
+  const f2 f = f2_fma(r, scale, f2_sub(magic, t));
+  f2 p;
+  if constexpr (DEG == 2) {
+    p = f2_fma(f2_pack(0.23840933f, 0.23840933f), f, f2_pack(0.70340872f, 0.70340872f));
+    p = f2_fma(p, f, f2_pack(1.00044143f, 1.00044143f));
+  } else if constexpr (DEG == 3) {
+    p = f2_fma(f2_pack(0.05516955f, 0.05516955f), f, f2_pack(0.24260588f, 0.24260588f));
+    p = f2_fma(p, f, f2_pack(0.69326085f, 0.69326085f));
+    p = f2_fma(p, f, f2_pack(0.99992841f, 0.99992841f));
+  } else {
+    p = f2_fma(f2_pack(0.0095698982f, 0.0095698982f), f, f2_pack(0.055917259f, 0.055917259f));
+    p = f2_fma(p, f, f2_pack(0.24024744f, 0.24024744f));
+    p = f2_fma(p, f, f2_pack(0.69312191f, 0.69312191f));
+    p = f2_fma(p, f, f2_pack(0.99999928f, 0.99999928f));
+  }
+  uint32_t p0, p1, t0, t1;
+  f2_unpack_u(p, p0, p1);
+  f2_unpack_u(t, t0, t1);
+  return f2_pack_u(p0 + (t0 << 23), p1 + (t1 << 23));
+}
+
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));

@@ -15,7 +15,6 @@ Same layer layout and parameter shapes as the reference's segmentor in contrast 
 """
 import torch
 import torch.nn as nn
-import torch.nn.functional as F
 
 
 def _conv_bn_relu(cin, cout, k, dilation=1):
@@ -58,7 +57,8 @@ class ASPPContrastHead(nn.Module):
                                            nn.Conv2d(channels, dim, 1))
 
     def forward(self, x):
-        outs = [F.interpolate(self.image_pool(x), size=x.shape[2:], mode="bilinear", align_corners=False)]
+        # bilinear resize of a 1x1 map (aspp_head.py:105-110) is a broadcast, bit for bit
+        outs = [self.image_pool(x).expand(-1, -1, x.shape[2], x.shape[3])]
         outs.extend(m(x) for m in self.aspp_modules)
         return self.contrast_conv(self.bottleneck(torch.cat(outs, dim=1)))
 

@@ -95,9 +95,10 @@ def composite(img, bg, output_stride, want_full_mask=False, out=None):
 
 
 # ----------------------------------------------------------------- K2a
-def prep_features(feat, mask):
+def prep_features(feat, mask, compact=False):
     """builder.py:1261-1268.  feat [B,C,P] f32, mask [B,P] -> (fhat_t bf16 [B,P,C], inv_norm [B,P],
-    pos_sum [B,C], neg_sum [B,C])."""
+    pos_sum [B,C], neg_sum [B,C], key_count).  compact=True (key side): fhat_t holds the foreground
+    rows first (pixel order) then zero rows, and key_count [B] int32 is their number; else None."""
     _need_cuda(feat, mask)
     feat, mask = _f32c(feat), _f32c(mask)
     B, C, P = feat.shape
@@ -108,29 +109,34 @@ def prep_features(feat, mask):
     pos = torch.empty((B, C), device=dev, dtype=torch.float32)
     neg = torch.empty((B, C), device=dev, dtype=torch.float32)
     scratch = torch.empty((B, lib.cp2_prep_tiles(P), 2, C), device=dev, dtype=torch.float32)
-    _call("cp2_prep_features", 2, lib.cp2_prep_features, _ptr(feat), _ptr(mask), _ptr(fhat_t), _ptr(inv_norm), _ptr(pos),
-                                     _ptr(neg), _ptr(scratch), B, C, P, _stream())
-    return fhat_t, inv_norm, pos, neg
+    count = torch.empty((B,), device=dev, dtype=torch.int32) if compact else None
+    _call("cp2_prep_features", 2, lib.cp2_prep_features, _ptr(feat), _ptr(mask), _ptr(fhat_t), _ptr(inv_norm),
+          _ptr(pos), _ptr(neg), _ptr(scratch), _ptr(count), B, C, P, _stream())
+    return fhat_t, inv_norm, pos, neg, count
 
 
 # ------------------------------------------------------------------ K2
-def dense_lse(qhat_t, khat_t, inv_tau):
-    """lse[n,y] = log sum_x exp(qhat[n,x].khat[n,y] * inv_tau).  builder.py:1289,1431-1432."""
+def dense_lse(qhat_t, khat_t, inv_tau, key_count=None):
+    """lse[n,y] = log sum_x exp(qhat[n,x].khat[n,y] * inv_tau).  builder.py:1289,1431-1432.
+    key_count [B] int32 (compacted keys): rows >= key_count[n] are skipped / meaningless."""
     _need_cuda(qhat_t, khat_t)
     B, P, C = qhat_t.shape
     lse = torch.empty((B, P), device=qhat_t.device, dtype=torch.float32)
-    _call("cp2_dense_lse", 1, _lib.load().cp2_dense_lse, _ptr(qhat_t), _ptr(khat_t), _ptr(lse), float(inv_tau), B, C, P,
-                                        _stream())
+    _call("cp2_dense_lse", 1, _lib.load().cp2_dense_lse, _ptr(qhat_t), _ptr(khat_t), _ptr(key_count), _ptr(lse),
+          float(inv_tau), B, C, P, _stream())
     return lse
 
 
-def dense_grad(qhat_t, khat_t, lse, mask_a, mask_b, inv_norm, alpha, v1, v2, inv_tau):
-    """Fused backward of the dense + global loss w.r.t. the query features -> dq [B,C,P]."""
+def dense_grad(qhat_t, khat_t, lse, mask_a, mask_b, inv_norm, alpha, v1, v2, inv_tau, key_count=None):
+    """Fused backward of the dense + global loss w.r.t. the query features -> dq [B,C,P].
+    mask_b may be None when the keys are compacted (key_count given)."""
     B, P, C = qhat_t.shape
+    lib = _lib.load()
     dq = torch.empty((B, C, P), device=qhat_t.device, dtype=torch.float32)
-    _call("cp2_dense_grad", 1, _lib.load().cp2_dense_grad, _ptr(qhat_t), _ptr(khat_t), _ptr(lse), _ptr(mask_a), _ptr(mask_b),
-                                         _ptr(inv_norm), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(dq),
-                                         float(inv_tau), B, C, P, _stream())
+    nl = torch.empty((B, lib.cp2_dense_pad(P)), device=qhat_t.device, dtype=torch.float32)
+    _call("cp2_dense_grad", 2, lib.cp2_dense_grad, _ptr(qhat_t), _ptr(khat_t), _ptr(key_count), _ptr(lse),
+          _ptr(mask_a), _ptr(mask_b), _ptr(inv_norm), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(dq), _ptr(nl),
+          float(inv_tau), B, C, P, _stream())
     return dq
 
 
@@ -249,8 +255,8 @@ class CP2LossFunction(torch.autograd.Function):
         kf = _f32c(k.detach()).reshape(B, C, -1)
         mask_a, mask_b = _f32c(mask_a), _f32c(mask_b)
         tg, tl = float(temp_global), float(temp_local)
-        qh, q_inv, sq, snq = prep_features(qf, mask_a)
-        kh, _, sk, snk = prep_features(kf, mask_b)
+        qh, q_inv, sq, snq, _ = prep_features(qf, mask_a)
+        kh, _, sk, snk, kcnt = prep_features(kf, mask_b, compact=True)     # fg keys first, zero rows after
         q_pos, dq_, nq_ = _unit(sq)
         k_pos, _, _ = _unit(sk)
         # ---- global InfoNCE: the queue part is one kernel; the 1-3 extra logits are [B]-sized
@@ -268,10 +274,11 @@ class CP2LossFunction(torch.autograd.Function):
             num = num + e_nq[:, None] * q_neg + e_nk[:, None] * k_neg
         loss_ins = (torch.log(Z) + (1.0 - l_pos) / tg).mean()
         # ---- dense InfoNCE: column LSE on the tensor cores, rank-1 positive term here
-        lse = dense_lse(qh, kh, 1.0 / tl)
+        lse = dense_lse(qh, kh, 1.0 / tl, kcnt)                # compact key order: rows < kcnt are fg
         A = mask_a.sum(dim=1)
-        Bm = mask_b.sum(dim=1)
-        dense_n = (mask_b * lse).sum(dim=1) / Bm - (sq * sk).sum(dim=1) / (tl * A * Bm)
+        Bm = kcnt.to(torch.float32)
+        fg = torch.arange(lse.shape[1], device=lse.device)[None, :] < kcnt[:, None]
+        dense_n = torch.where(fg, lse, lse.new_zeros(())).sum(dim=1) / Bm - (sq * sk).sum(dim=1) / (tl * A * Bm)
         loss_dense = dense_n.mean()
         loss = loss_ins + loss_dense * lmbd_dense
         # ---- backward coefficients for a unit upstream gradient
@@ -282,7 +289,7 @@ class CP2LossFunction(torch.autograd.Function):
             dqneg = (e_nq / Z)[:, None] * q_pos / (B * tg)
             v2 = _unit_bwd(dqneg, q_neg, dn_, nn_).contiguous()
         alpha = lmbd_dense / (B * Bm * tl)
-        ctx.save_for_backward(qh, kh, lse, mask_a, mask_b, q_inv, alpha.contiguous(), v1.contiguous(), v2)
+        ctx.save_for_backward(qh, kh, lse, mask_a, kcnt, q_inv, alpha.contiguous(), v1.contiguous(), v2)
         ctx.inv_tl = 1.0 / tl
         ctx.q_shape = q.shape
         ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos)
@@ -290,10 +297,10 @@ class CP2LossFunction(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_loss, *_unused):
-        qh, kh, lse, mask_a, mask_b, q_inv, alpha, v1, v2 = ctx.saved_tensors
+        qh, kh, lse, mask_a, kcnt, q_inv, alpha, v1, v2 = ctx.saved_tensors
         g = g_loss.reshape(())
-        dq = dense_grad(qh, kh, lse, mask_a, mask_b, q_inv, (alpha * g).contiguous(), (v1 * g).contiguous(),
-                        None if v2 is None else (v2 * g).contiguous(), ctx.inv_tl)
+        dq = dense_grad(qh, kh, lse, mask_a, None, q_inv, (alpha * g).contiguous(), (v1 * g).contiguous(),
+                        None if v2 is None else (v2 * g).contiguous(), ctx.inv_tl, key_count=kcnt)
         return dq.reshape(ctx.q_shape), None, None, None, None, None, None, None, None
 
 

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CP2_ABI_VERSION 1
+#define CP2_ABI_VERSION 2
 
 #define CP2_OK 0
 #define CP2_E_INVALID (-1)      /* bad shape / null pointer / unsupported dim          */
@@ -44,7 +44,7 @@ const char *cp2_last_error(void);
 int cp2_composite(const float *img, const float *bg, float *out, float *mask_full,
                   float *mask_ds, int B, int H, int W, int os, void *stream);
 
-/* K2a — per-pixel L2 normalisation + masked pooling + bf16 transpose.
+/* K2a — per-pixel L2 normalisation + masked pooling + bf16 transpose (+ key compaction).
  * Replaces builder.py:1261-1268 (query) / 1279-1285 (key): F.normalize(dim=1) and the
  * two `ncx,nx->nc` einsums (the outer F.normalize of the pooled vectors is left to
  * the caller: it is [B,C]).
@@ -55,32 +55,42 @@ int cp2_composite(const float *img, const float *bg, float *out, float *mask_ful
  *   pos_sum   : [B,C] f32, sum_x mask_x * fhat_x      (fp32 values, not the bf16 copy)
  *   neg_sum   : [B,C] f32, sum_x (1-mask_x) * fhat_x
  *   scratch   : [B, cp2_prep_tiles(P), 2, C] f32 work space (per-tile partial sums)
+ *   key_count : NULL, or [B] int32 OUT.  When given, fhat_t is written COMPACTED: the unit vectors of
+ *               the foreground pixels (mask != 0) first, in pixel order, then zero rows;
+ *               key_count[n] = number of foreground pixels.  Only the key side is compacted:
+ *               background keys have label 0 for every query (builder.py:1291-1292,1435), so they
+ *               enter neither the loss nor the gradient.  inv_norm / pos_sum / neg_sum are unaffected.
  * C must be a multiple of 64 and <= 256. */
 int cp2_prep_tiles(int P);
 int cp2_prep_features(const float *feat, const float *mask, void *fhat_t, float *inv_norm,
-                      float *pos_sum, float *neg_sum, float *scratch, int B, int C, int P,
-                      void *stream);
+                      float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count, int B, int C,
+                      int P, void *stream);
 
 /* K2 forward — dense pixel InfoNCE, column log-sum-exp.
  * Replaces builder.py:1289 (einsum ncx,ncy->nxy), :1431 (/T) and the LogSoftmax(dim=1)
  * of :1432 without materialising [B,P,P]:
  *   lse[n,y] = log sum_x exp( qhat[n,x,:].khat[n,y,:] * inv_tau )      ([B,P] f32)
  * tcgen05 (bf16 operands, fp32 accumulate in TMEM), operands fetched by TMA.
- * C in {128, 256}. */
-int cp2_dense_lse(const void *qhat_t, const void *khat_t, float *lse, float inv_tau, int B,
-                  int C, int P, void *stream);
+ *   key_count : NULL (all P key rows) or [B] int32: only rows y < key_count[n] are meaningful
+ *               (compacted keys); key tiles entirely past it are skipped and their lse set to 0.
+ * C in {128, 256}; 0 < inv_tau <= 16. */
+int cp2_dense_lse(const void *qhat_t, const void *khat_t, const int32_t *key_count, float *lse,
+                  float inv_tau, int B, int C, int P, void *stream);
 
 /* K2 backward — fused gradient of the dense + global loss w.r.t. the query features.
  * Replaces autograd of builder.py:1261-1268, 1289-1292, 1431-1437:
- *   acc[x,:]  = sum_y mask_b[y] * exp(S[x,y]*inv_tau - lse[y]) * khat[y,:]   (tcgen05)
+ *   acc[x,:]  = sum_y on_y * exp(S[x,y]*inv_tau - lse[y]) * khat[y,:]   (tcgen05)
+ *               on_y = (mask_b == NULL || mask_b[y] != 0) && (key_count == NULL || y < key_count[n])
  *   dqhat_x   = alpha[n]*acc[x,:] + mask_a[x]*v1[n,:] + (1-mask_a[x])*v2[n,:]
  *   dq[n,:,x] = (dqhat_x - qhat_x (qhat_x . dqhat_x)) * inv_norm[n,x]        ([B,C,P] f32)
  * alpha [B], v1 [B,C], v2 [B,C] (v2 may be NULL = zeros) carry the upstream gradient
- * and every rank-1 term; the caller computes them on [B,C] tensors. */
-int cp2_dense_grad(const void *qhat_t, const void *khat_t, const float *lse,
-                   const float *mask_a, const float *mask_b, const float *inv_norm,
-                   const float *alpha, const float *v1, const float *v2, float *dq,
-                   float inv_tau, int B, int C, int P, void *stream);
+ * and every rank-1 term; the caller computes them on [B,C] tensors.
+ *   scratch_nl : [B, cp2_dense_pad(P)] f32 work space. */
+int cp2_dense_pad(int P);
+int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int32_t *key_count, const float *lse,
+                   const float *mask_a, const float *mask_b, const float *inv_norm, const float *alpha,
+                   const float *v1, const float *v2, float *dq, float *scratch_nl, float inv_tau, int B,
+                   int C, int P, void *stream);
 
 /* K3 — global MoCo InfoNCE against the negative queue, forward and backward in one
  * pass over the queue.  Replaces builder.py:1396 (q_pos @ queue.clone()) and the

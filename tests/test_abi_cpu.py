@@ -38,18 +38,21 @@ def test_every_declared_symbol_is_exported(lib):
 
 
 def test_abi_version_and_host_helpers(lib):
-    assert lib.cp2_abi_version() == 1
+    assert lib.cp2_abi_version() == 2
     assert lib.cp2_prep_tiles(196) == 7 and lib.cp2_prep_tiles(32) == 1
     assert lib.cp2_global_scratch_floats(0, 128) == 0
+    assert lib.cp2_dense_pad(196) == 256 and lib.cp2_dense_pad(3136) == 3200 and lib.cp2_dense_pad(128) == 128
 
 
 def test_invalid_arguments_are_rejected_before_any_launch(lib):
     # bad shapes / null pointers -> CP2_E_INVALID (-1) and a message; no device is needed for these paths
     assert lib.cp2_composite(None, None, None, None, None, 1, 0, 4, 16, None) == -1
     assert b"cp2_composite" in lib.cp2_last_error()
-    assert lib.cp2_dense_lse(None, None, None, 1.0, 1, 128, 196, None) == -1
-    assert lib.cp2_dense_lse(1, 1, 1, 1.0, 1, 96, 196, None) == -1           # unsupported C
+    assert lib.cp2_dense_lse(None, None, None, None, 1.0, 1, 128, 196, None) == -1
+    assert lib.cp2_dense_lse(1, 1, None, 1, 1.0, 1, 96, 196, None) == -1     # unsupported C
     assert b"C=96" in lib.cp2_last_error()
+    assert lib.cp2_dense_lse(1, 1, None, 1, 50.0, 1, 128, 196, None) == -1    # 1/tau outside (0, 16]
+    assert b"1/tau" in lib.cp2_last_error()
     assert lib.cp2_global_nce(1, 1, 1, 1, 1, 5.0, 4, 64, 4096, None) == -1    # C != 128
     assert lib.cp2_enqueue(1, 1, 1, 10, 128, 5, None) == -1                   # n > K
     assert lib.cp2_ema(None, None, None, None, None, 3, 0.999, 0.001, None) == -1

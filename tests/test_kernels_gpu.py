@@ -147,7 +147,8 @@ def test_prep_features(ops, B, C, P):
     feat[0, :, 1] = 0.0                                   # zero pixel: eps path of F.normalize
     mask = (torch.rand(B, P, generator=g) < 0.6).float()
     f_hat, pos, neg = O.normalize_and_pool(feat, mask)
-    fh, inv, ps, ns = ops.prep_features(dev(feat), dev(mask))
+    fh, inv, ps, ns, cnt = ops.prep_features(dev(feat), dev(mask))
+    assert cnt is None
     assert fh.shape == (B, P, C) and fh.dtype == torch.bfloat16
     want = f_hat.transpose(1, 2)
     assert torch.allclose(fh.float().cpu(), want, rtol=0, atol=2 ** -8)     # bf16 rounding of |v|<=1
@@ -159,6 +160,26 @@ def test_prep_features(ops, B, C, P):
     assert torch.allclose(ps.cpu(), raw_pos, rtol=1e-5, atol=1e-5)
     assert torch.allclose(ns.cpu(), raw_neg, rtol=1e-5, atol=1e-5)
     assert torch.allclose(torch.nn.functional.normalize(ps.cpu(), dim=1), pos, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("B,C,P", [(2, 128, 196), (2, 256, 50), (1, 128, 3136), (3, 128, 33)])
+def test_prep_features_compact_keys(ops, B, C, P):
+    """compact=True: foreground rows first (pixel order), zero rows after, key_count = #fg; everything
+    else identical to the plain call."""
+    g = torch.Generator().manual_seed(P + 1)
+    feat = torch.randn(B, C, P, generator=g)
+    mask = (torch.rand(B, P, generator=g) < 0.6).float()
+    mask[0] = 1.0                                         # all foreground
+    if B > 1:
+        mask[1] = 0.0                                     # no foreground at all
+    fh, inv, ps, ns, _ = ops.prep_features(dev(feat), dev(mask))
+    fc, inv2, ps2, ns2, cnt = ops.prep_features(dev(feat), dev(mask), compact=True)
+    assert torch.equal(inv, inv2) and torch.equal(ps, ps2) and torch.equal(ns, ns2)
+    assert cnt.dtype == torch.int32 and torch.equal(cnt.cpu().long(), mask.sum(1).long())
+    for b in range(B):
+        n = int(cnt[b])
+        assert torch.equal(fc[b, :n], fh[b][mask[b].bool().cuda()])
+        assert not fc[b, n:].any()
 
 
 # ------------------------------------------------------------------- K2 forward
@@ -182,6 +203,19 @@ def test_dense_lse_vs_oracle(ops, B, C, P, tau):
     got = ops.dense_lse(dev(qh), dev(kh), 1.0 / tau)
     torch.cuda.synchronize()
     assert torch.allclose(got.double().cpu(), ref, rtol=0, atol=2e-5), float((got.double().cpu() - ref).abs().max())
+
+
+def test_dense_lse_compact_count(ops):
+    """key_count: rows < count match the full computation, tiles entirely past count are zeroed."""
+    B, C, P = 3, 128, 700
+    qh, kh = dev(_unit_bf16(B, P, C, 21)), dev(_unit_bf16(B, P, C, 22))
+    cnt = torch.tensor([700, 130, 0], dtype=torch.int32).cuda()
+    full = ops.dense_lse(qh, kh, 5.0)
+    got = ops.dense_lse(qh, kh, 5.0, cnt)
+    torch.cuda.synchronize()
+    assert torch.equal(got[0], full[0])
+    assert torch.equal(got[1, :256], full[1, :256]) and not got[1, 256:].any()
+    assert not got[2].any()
 
 
 def test_dense_lse_vs_simt_large(ops):
@@ -231,6 +265,35 @@ def test_dense_grad_vs_oracle(ops, B, C, P, tau, bg):
     assert got.shape == (B, C, P)
     err = rel_l2(got, ref)
     assert err < 5e-3, err                                   # Ptilde is rounded to bf16 (2^-9)
+
+
+@pytest.mark.parametrize("C,P", [(128, 500), (256, 333)])
+def test_dense_grad_compact_equals_masked(ops, C, P):
+    """Compacted keys + key_count give the gradient of the mask_b formulation (same fp64 reference)."""
+    B, tau = 3, 0.2
+    g = torch.Generator().manual_seed(C + P)
+    feat_k = torch.randn(B, C, P, generator=g)
+    qh = _unit_bf16(B, P, C, 31)
+    ma = (torch.rand(B, P, generator=g) < 0.6).float()
+    mb = (torch.rand(B, P, generator=g) < 0.6).float()
+    mb[1] = 0.0                                           # an image without foreground keys
+    mb[2, :P // 2] = 1.0
+    inv_norm = torch.rand(B, P, generator=g) + 0.5
+    alpha = torch.rand(B, generator=g) + 0.1
+    v1 = torch.randn(B, C, generator=g) * 0.1
+    kh_full, _, _, _, _ = ops.prep_features(dev(feat_k), dev(mb))
+    kh_c, _, _, _, cnt = ops.prep_features(dev(feat_k), dev(mb), compact=True)
+    lse_c = ops.dense_lse(dev(qh), kh_c, 1.0 / tau, cnt)
+    got = ops.dense_grad(dev(qh), kh_c, lse_c, dev(ma), None, dev(inv_norm), dev(alpha), dev(v1), None,
+                         1.0 / tau, key_count=cnt)
+    torch.cuda.synchronize()
+    lse = _lse_ref(qh.float(), kh_full.float().cpu(), 1.0 / tau).float()
+    ref = _grad_ref(qh.float(), kh_full.float().cpu(), lse, ma, mb, inv_norm, alpha, v1, None, 1.0 / tau)
+    assert rel_l2(got, ref) < 5e-3, rel_l2(got, ref)
+    # image 1 has no fg keys: only the rank-1 terms remain
+    only_rank1 = _grad_ref(qh[1:2].float(), kh_full[1:2].float().cpu(), lse[1:2], ma[1:2], mb[1:2], inv_norm[1:2],
+                           alpha[1:2] * 0, v1[1:2], None, 1.0 / tau)
+    assert rel_l2(got[1:2], only_rank1) < 1e-5
 
 
 def test_dense_grad_vs_simt_large(ops):
