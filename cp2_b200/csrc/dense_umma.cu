@@ -122,35 +122,40 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     const int y = y0 + quad * 32 + lane;
     const uint32_t lane_base = tmem + (uint32_t(quad * 32) << 16);
     const f2 scale2 = f2_pack(scale_log2, scale_log2);
-    f2 acc_m = f2_pack(0.f, 0.f), acc_p = f2_pack(0.f, 0.f);
+    f2 acc_m = f2_pack(0.f, 0.f), acc_p = f2_pack(0.f, 0.f), acc_m2 = acc_m, acc_p2 = acc_m;
     float tail = 0.f;
     for (int i = 0; i < nx; ++i) {
       const int buf = i & 1, tph = (i >> 1) & 1;
       mbar_wait(&tfull[buf], tph);
       tc_fence_after();
       const int nvalid = min(TILE, P - i * TILE);
+      // software pipeline: the TMEM load of chunk ch+1 is in flight while chunk ch is exponentiated
+      uint32_t r[2][32];
+      tmem_ld32(lane_base + buf * TILE, r[0]);
 #pragma unroll
       for (int ch = 0; ch < TILE / 32; ++ch) {
+        tmem_wait_ld();
+        if (ch + 1 < TILE / 32 && (ch + 1) * 32 < nvalid) tmem_ld32(lane_base + buf * TILE + (ch + 1) * 32, r[(ch + 1) & 1]);
         if (ch * 32 < nvalid) {                    // warp-uniform
-          uint32_t r[32];
-          tmem_ld32(lane_base + buf * TILE + ch * 32, r);
-          tmem_wait_ld();
+          const uint32_t(&rc)[32] = r[ch & 1];
           if ((ch + 1) * 32 <= nvalid) {
 #pragma unroll
             for (int pr = 0; pr < 16; ++pr) {
-              const f2 rr = f2_pack_u(r[2 * pr], r[2 * pr + 1]);
+              const f2 rr = f2_pack_u(rc[2 * pr], rc[2 * pr + 1]);
               if ((pr & 3) < PF) {
-                acc_p = f2_add(acc_p, exp2_poly2_scaled<3>(rr, scale2));
+                if (pr & 4) acc_p = f2_add(acc_p, exp2_poly2_scaled<3>(rr, scale2));
+                else acc_p2 = f2_add(acc_p2, exp2_poly2_scaled<3>(rr, scale2));
               } else {
                 float a, c;
                 f2_unpack(f2_mul(rr, scale2), a, c);
-                acc_m = f2_add(acc_m, f2_pack(ex2_approx(a), ex2_approx(c)));
+                if (pr & 4) acc_m = f2_add(acc_m, f2_pack(ex2_approx(a), ex2_approx(c)));
+                else acc_m2 = f2_add(acc_m2, f2_pack(ex2_approx(a), ex2_approx(c)));
               }
             }
           } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j)
-              if (ch * 32 + j < nvalid) tail += ex2_approx(__uint_as_float(r[j]) * scale_log2);
+              if (ch * 32 + j < nvalid) tail += ex2_approx(__uint_as_float(rc[j]) * scale_log2);
           }
         }
       }
@@ -159,7 +164,7 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       if (lane == 0) mbar_arrive(&tempty[buf]);
     }
     float s0, s1;
-    f2_unpack(f2_add(acc_m, acc_p), s0, s1);
+    f2_unpack(f2_add(f2_add(acc_m, acc_m2), f2_add(acc_p, acc_p2)), s0, s1);
     if (y < P) lse[(long long)b * P + y] = log2f(s0 + s1 + tail) * LN2;
   }
   tc_fence_before();
@@ -290,8 +295,12 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
           mma_commit(&s_full[gi & 1]);
         };
         if (ny > 0) issue_s(g);
+        if (ny <= 1) mma_commit(&q_empty[qb]);             // all S MMAs of the item issued: Qhat tile is free
         for (int j = 0; j < ny; ++j, ++g) {
-          if (j + 1 < ny) issue_s(g + 1);
+          if (j + 1 < ny) {
+            issue_s(g + 1);
+            if (j + 2 == ny) mma_commit(&q_empty[qb]);
+          }
           const int s = g % NST;
           const uint32_t aK = smem_u32(sK + s * Cfg::OPER_K);
           const uint32_t tS = tmem + (g & 1) * TY;
@@ -308,7 +317,6 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
           }
           mma_commit(&kempty[s]);
         }
-        mma_commit(&q_empty[qb]);
         mma_commit(&d_full[db]);
       }
     }
@@ -327,11 +335,14 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
         mbar_wait(&s_full[g & 1], (g >> 1) & 1);
         tc_fence_after();
         const float *nlw = nlbuf + s * TY + half * W;
+        uint32_t rb[2][32];
+        tmem_ld32(tS, rb[0]);
 #pragma unroll
         for (int ch = 0; ch < W / 32; ++ch) {
-          uint32_t r[32], pk[16];
-          tmem_ld32(tS + ch * 32, r);
+          uint32_t pk[16];
           tmem_wait_ld();
+          if (ch + 1 < W / 32) tmem_ld32(tS + (ch + 1) * 32, rb[(ch + 1) & 1]);
+          const uint32_t(&r)[32] = rb[ch & 1];
           const float4 *nl4 = reinterpret_cast<const float4 *>(nlw + ch * 32);
 #pragma unroll
           for (int u = 0; u < 8; ++u) {
@@ -524,14 +535,14 @@ extern "C" int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int 
   CP2_LAUNCH_CHECK();
   const float sl2 = inv_tau * LOG2E;
   const int pf = poly_quarters("CP2_DENSE_PF_BWD", 2);
-#define CP2_GRAD(CC, TYV, NQV, NDV, PFV)                                                                      \
-  launch_grad<CC, TYV, 3, NQV, NDV, PFV>(tq, tk, qhat_t, scratch_nl, key_count, mask_a, inv_norm, alpha, v1, \
+#define CP2_GRAD(CC, TYV, NSTV, NQV, NDV, PFV)                                                                     \
+  launch_grad<CC, TYV, NSTV, NQV, NDV, PFV>(tq, tk, qhat_t, scratch_nl, key_count, mask_a, inv_norm, alpha, v1, \
                                          v2, dq, sl2, B, P, P_pad, st)
   if (C == 128) {
-    switch (pf) { case 0: return CP2_GRAD(128, 128, 2, 2, 0); case 1: return CP2_GRAD(128, 128, 2, 2, 1);
-                  case 2: return CP2_GRAD(128, 128, 2, 2, 2); default: return CP2_GRAD(128, 128, 2, 2, 3); }
+    switch (pf) { case 0: return CP2_GRAD(128, 128, 5, 1, 2, 0); case 1: return CP2_GRAD(128, 128, 5, 1, 2, 1);
+                  case 2: return CP2_GRAD(128, 128, 5, 1, 2, 2); default: return CP2_GRAD(128, 128, 5, 1, 2, 3); }
   }
-  switch (pf) { case 0: return CP2_GRAD(256, 64, 1, 1, 0); case 1: return CP2_GRAD(256, 64, 1, 1, 1);
-                case 2: return CP2_GRAD(256, 64, 1, 1, 2); default: return CP2_GRAD(256, 64, 1, 1, 3); }
+  switch (pf) { case 0: return CP2_GRAD(256, 64, 4, 1, 1, 0); case 1: return CP2_GRAD(256, 64, 4, 1, 1, 1);
+                case 2: return CP2_GRAD(256, 64, 4, 1, 1, 2); default: return CP2_GRAD(256, 64, 4, 1, 1, 3); }
 #undef CP2_GRAD
 }

@@ -57,7 +57,7 @@ class ASPPContrastHead(nn.Module):
                                            nn.Conv2d(channels, dim, 1))
 
     def forward(self, x):
-        # bilinear resize of a 1x1 map (aspp_head.py:105-110) is a broadcast, bit for bit
+        # bilinear resize of a 1x1 map (aspp_head.py:105-110) is a broadcast (equal up to the 1-ulp rounding of w0*x + w1*x)
         outs = [self.image_pool(x).expand(-1, -1, x.shape[2], x.shape[3])]
         outs.extend(m(x) for m in self.aspp_modules)
         return self.contrast_conv(self.bottleneck(torch.cat(outs, dim=1)))
