@@ -30,6 +30,7 @@ SIGNATURES = {
 DEBUG_SIGNATURES = {
     "cp2_dbg_dense_lse_simt": (c_int, [c_void_p] * 3 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_dbg_dense_grad_simt": (c_int, [c_void_p] * 10 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_dbg_dense_trace": (c_int, [c_void_p]),
     "cp2_dbg_global_nce_simt": (c_int, [c_void_p] * 4 + [c_float] + [c_int] * 3 + [c_void_p]),
 }
 

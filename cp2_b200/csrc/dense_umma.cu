@@ -25,6 +25,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "cp2_b200_debug.h"
 #include "umma.cuh"
 
 using namespace umma;
@@ -100,22 +101,28 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(TILE, TILE, FMT_BF16, FMT_BF16, MAJOR_K, MAJOR_K);
-      const uint32_t aK = smem_u32(sK);
-      mbar_wait(bar_k, 0);
-      for (int i = 0; i < nx; ++i) {
-        const int s = i % NST, ph = (i / NST) & 1, buf = i & 1, tph = (i >> 1) & 1;
-        mbar_wait(&full[s], ph);
-        mbar_wait(&tempty[buf], tph ^ 1);
-        tc_fence_after();
-        const uint32_t aQ = smem_u32(sQ + s * OPER);
+    // whole warp converged (loop state stays warp-uniform), one elected lane issues
+    constexpr uint32_t idesc = make_idesc(TILE, TILE, FMT_BF16, FMT_BF16, MAJOR_K, MAJOR_K);
+    const uint64_t dK = make_sdesc(smem_u32(sK), 16, 1024);
+    const uint64_t dQ0 = make_sdesc(smem_u32(sQ), 16, 1024);
+    mbar_wait(bar_k, 0);
+    for (int i = 0; i < nx; ++i) {
+      const int s = i % NST, ph = (i / NST) & 1, buf = i & 1, tph = (i >> 1) & 1;
+      mbar_wait(&full[s], ph);
+      mbar_wait(&tempty[buf], tph ^ 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t dQ = sdesc_advance(dQ0, s * OPER);
+        const uint32_t tacc = tmem + buf * TILE;
 #pragma unroll
-        for (int kk = 0; kk < C / 16; ++kk)
-          mma_f16_ss(tmem + buf * TILE, kmajor_desc(aK, kk, BOX), kmajor_desc(aQ, kk, BOX), idesc, kk > 0);
+        for (int kk = 0; kk < C / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * BOX + (kk & 3) * 32;
+          mma_f16_ss(tacc, sdesc_advance(dK, off), sdesc_advance(dQ, off), idesc, kk > 0);
+        }
         mma_commit(&empty[s]);
         mma_commit(&tfull[buf]);
       }
+      __syncwarp();
     }
   } else {
     const int quad = warp & 3;
@@ -211,8 +218,20 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
                   const int *__restrict__ key_count, const float *__restrict__ mask_a,
                   const float *__restrict__ inv_norm, const float *__restrict__ alpha,
                   const float *__restrict__ v1, const float *__restrict__ v2, float *__restrict__ dq,
-                  float scale_log2, int B, int P, int P_pad) {
+                  float scale_log2, int B, int P, int P_pad, long long *__restrict__ trace) {
   using Cfg = GradCfg<C, TY, NST, NQ, ND>;
+  // optional per-CTA wait-time accounting (test-only; cp2_dbg_dense_trace): slot k of trace[blockIdx.x*16+k]
+  long long tr_a = 0, tr_b = 0, tr_c = 0, tr_d = 0;
+  const long long tr_start = trace ? clock64() : 0;
+  auto twait = [&](uint64_t *bar, uint32_t parity, long long &acc) {
+    if (trace) {
+      const long long t = clock64();
+      mbar_wait(bar, parity);
+      acc += clock64() - t;
+    } else {
+      mbar_wait(bar, parity);
+    }
+  };
   constexpr int W = TY / 2;                              // S columns per softmax warp
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = align1024(smem_raw);
@@ -256,13 +275,13 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       for (int w = blockIdx.x; w < items; w += gridDim.x, ++it) {
         const int b = w / nxt, x0 = (w % nxt) * TILE, ny = key_tiles(b);
         const int qb = it % NQ;
-        mbar_wait(&q_empty[qb], ((it / NQ) & 1) ^ 1);
+        twait(&q_empty[qb], ((it / NQ) & 1) ^ 1, tr_a);
         mbar_expect_tx(&q_full[qb], Cfg::OPER_Q);
         for (int kb = 0; kb < C / 64; ++kb)
           tma_load_3d(sQ + qb * Cfg::OPER_Q + kb * Cfg::QBOX, &tm_q, &q_full[qb], kb * 64, x0, b);
         for (int j = 0; j < ny; ++j, ++g) {
           const int s = g % NST;
-          mbar_wait(&kempty[s], ((g / NST) & 1) ^ 1);
+          twait(&kempty[s], ((g / NST) & 1) ^ 1, tr_b);
           mbar_expect_tx(&kfull[s], Cfg::OPER_K + TY * 4);
           for (int kb = 0; kb < C / 64; ++kb)
             tma_load_3d(sK + s * Cfg::OPER_K + kb * Cfg::KBOX, &tm_k, &kfull[s], kb * 64, j * TY, b);
@@ -272,53 +291,68 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
     }
   } else if (warp == 1) {
     // -------------------------------------------------------------- MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc_s = make_idesc(TILE, TY, FMT_BF16, FMT_BF16, MAJOR_K, MAJOR_K);
-      constexpr uint32_t idesc_d = make_idesc(TILE, C, FMT_BF16, FMT_BF16, MAJOR_K, MAJOR_MN);
-      int g = 0, it = 0;
-      for (int w = blockIdx.x; w < items; w += gridDim.x, ++it) {
-        const int b = w / nxt, ny = key_tiles(b);
-        const int qb = it % NQ, db = it % ND;
-        const uint32_t aQ = smem_u32(sQ + qb * Cfg::OPER_Q);
-        const uint32_t tD = tmem_D + db * C;
-        mbar_wait(&q_full[qb], (it / NQ) & 1);
-        mbar_wait(&d_empty[db], ((it / ND) & 1) ^ 1);
-        auto issue_s = [&](int gi) {                       // S(gi) = Qhat_x . Khat_y^T -> S buffer gi&1
-          const int s = gi % NST;
-          const uint32_t aK = smem_u32(sK + s * Cfg::OPER_K);
-          mbar_wait(&kfull[s], (gi / NST) & 1);
-          tc_fence_after();
+    // The whole warp runs the loop (state stays warp-uniform -> descriptors live in uniform registers and
+    // one MMA costs ~3 instructions to issue); an elected lane issues tcgen05.mma / commit.
+    constexpr uint32_t idesc_s = make_idesc(TILE, TY, FMT_BF16, FMT_BF16, MAJOR_K, MAJOR_K);
+    constexpr uint32_t idesc_d = make_idesc(TILE, C, FMT_BF16, FMT_BF16, MAJOR_K, MAJOR_MN);
+    const uint64_t dQ0 = make_sdesc(smem_u32(sQ), 16, 1024);
+    const uint64_t dK0 = make_sdesc(smem_u32(sK), 16, 1024);               // K-major view (S GEMM)
+    const uint64_t dKmn0 = make_sdesc(smem_u32(sK), Cfg::KBOX, 1024);      // MN-major view (dQ GEMM)
+    int g = 0, it = 0;
+    for (int w = blockIdx.x; w < items; w += gridDim.x, ++it) {
+      const int b = w / nxt, ny = key_tiles(b);
+      const int qb = it % NQ, db = it % ND;
+      const uint64_t dQ = sdesc_advance(dQ0, qb * Cfg::OPER_Q);
+      const uint32_t tD = tmem_D + db * C;
+      twait(&q_full[qb], (it / NQ) & 1, tr_a);
+      twait(&d_empty[db], ((it / ND) & 1) ^ 1, tr_b);
+      auto issue_s = [&](int gi) {                       // S(gi) = Qhat_x . Khat_y^T -> S buffer gi&1
+        const int s = gi % NST;
+        twait(&kfull[s], (gi / NST) & 1, tr_c);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint64_t dK = sdesc_advance(dK0, s * Cfg::OPER_K);
+          const uint32_t tS = tmem + (gi & 1) * TY;
 #pragma unroll
           for (int kk = 0; kk < C / 16; ++kk)
-            mma_f16_ss(tmem + (gi & 1) * TY, kmajor_desc(aQ, kk, Cfg::QBOX), kmajor_desc(aK, kk, Cfg::KBOX),
-                       idesc_s, kk > 0);
+            mma_f16_ss(tS, sdesc_advance(dQ, (kk >> 2) * Cfg::QBOX + (kk & 3) * 32),
+                       sdesc_advance(dK, (kk >> 2) * Cfg::KBOX + (kk & 3) * 32), idesc_s, kk > 0);
           mma_commit(&s_full[gi & 1]);
-        };
-        if (ny > 0) issue_s(g);
-        if (ny <= 1) mma_commit(&q_empty[qb]);             // all S MMAs of the item issued: Qhat tile is free
-        for (int j = 0; j < ny; ++j, ++g) {
-          if (j + 1 < ny) {
-            issue_s(g + 1);
-            if (j + 2 == ny) mma_commit(&q_empty[qb]);
-          }
-          const int s = g % NST;
-          const uint32_t aK = smem_u32(sK + s * Cfg::OPER_K);
+        }
+        __syncwarp();
+      };
+      auto release_q = [&]() {                           // all S MMAs of the item issued: Qhat tile is free
+        if (elect_one()) mma_commit(&q_empty[qb]);
+        __syncwarp();
+      };
+      if (ny > 0) issue_s(g);
+      if (ny <= 1) release_q();
+      for (int j = 0; j < ny; ++j, ++g) {
+        if (j + 1 < ny) {
+          issue_s(g + 1);
+          if (j + 2 == ny) release_q();
+        }
+        const int s = g % NST;
+        twait(&p_full[g & 1], (g >> 1) & 1, tr_d);
+        tc_fence_after();
+        // dQhat += P~ . Khat_y : A = bf16 pairs in TMEM (8 columns per K=16 slice; each softmax warp
+        // packed its W columns at the start of its own region), B = the key tile read MN-major:
+        // 16 key rows (2 KB) per slice, 64-channel chunks KBOX apart.
+        if (elect_one()) {
+          const uint64_t dKmn = sdesc_advance(dKmn0, s * Cfg::OPER_K);
           const uint32_t tS = tmem + (g & 1) * TY;
-          mbar_wait(&p_full[g & 1], (g >> 1) & 1);
-          tc_fence_after();
-          // dQhat += P~ . Khat_y : A = bf16 pairs in TMEM (8 columns per K=16 slice; each softmax warp
-          // packed its W columns at the start of its own region), B = the key tile read MN-major:
-          // 16 key rows (2 KB) per slice, 64-channel chunks KBOX apart.
 #pragma unroll
           for (int kk = 0; kk < TY / 16; ++kk) {
             const int half = (kk * 16) / W, local = (kk * 16) % W;
-            mma_f16_ts(tD, tS + half * W + local / 2, make_sdesc(aK + kk * 2048, Cfg::KBOX, 1024), idesc_d,
+            mma_f16_ts(tD, tS + half * W + local / 2, sdesc_advance(dKmn, kk * 2048), idesc_d,
                        (j > 0 || kk > 0) ? 1u : 0u);
           }
           mma_commit(&kempty[s]);
         }
-        mma_commit(&d_full[db]);
+        __syncwarp();
       }
+      if (elect_one()) mma_commit(&d_full[db]);
+      __syncwarp();
     }
   } else if (warp < 10) {
     // ------------------------------------------------ softmax warps: S -> P~ (bf16, in place)
@@ -331,8 +365,8 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       for (int j = 0; j < ny; ++j, ++g) {
         const int s = g % NST;
         const uint32_t tS = tmem + (g & 1) * TY + lane_off + half * W;
-        mbar_wait(&kfull[s], (g / NST) & 1);             // nl slice of this tile landed (bulk copy)
-        mbar_wait(&s_full[g & 1], (g >> 1) & 1);
+        twait(&kfull[s], (g / NST) & 1, tr_a);           // nl slice of this tile landed (bulk copy)
+        twait(&s_full[g & 1], (g >> 1) & 1, tr_b);
         tc_fence_after();
         const float *nlw = nlbuf + s * TY + half * W;
         uint32_t rb[2][32];
@@ -390,7 +424,7 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       const float *v1b = v1 + (long long)b * C;
       const float *v2b = v2 ? v2 + (long long)b * C : nullptr;
       const uint4 *qrow = reinterpret_cast<const uint4 *>(qhat + ((long long)b * P + (valid ? x : 0)) * C);
-      mbar_wait(&d_full[db], (it / ND) & 1);
+      twait(&d_full[db], (it / ND) & 1, tr_a);
       tc_fence_after();
       const uint32_t tD = tmem_D + db * C + lane_off;
       float dot = 0.f;
@@ -427,6 +461,14 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       if (lane == 0) mbar_arrive(&d_empty[db]);
     }
   }
+  if (trace && lane == 0 && (warp <= 2 || warp == 10)) {
+    const int slot = warp == 0 ? 0 : warp == 1 ? 2 : warp == 2 ? 6 : 8;
+    long long *t = trace + blockIdx.x * 16 + slot;
+    t[0] = tr_a; t[1] = tr_b;
+    if (warp == 1) { t[2] = tr_c; t[3] = tr_d; }
+    if (warp == 0) trace[blockIdx.x * 16 + 10] = clock64() - tr_start;
+    if (warp == 2 || warp == 10) trace[blockIdx.x * 16 + (warp == 2 ? 11 : 12)] = clock64() - tr_start;
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, 512);
@@ -446,6 +488,8 @@ int make_feature_tmap(CUtensorMap *tm, const void *base, int B, int C, int P, in
   if (r != CUDA_SUCCESS) { cp2_set_error("cuTensorMapEncodeTiled(features) failed: CUresult %d", (int)r); return CP2_E_CUDA; }
   return CP2_OK;
 }
+
+long long *g_dense_trace = nullptr;    // test-only: set by cp2_dbg_dense_trace, read by the next cp2_dense_grad
 
 // share of the exponentials evaluated on the FMA pipe, in quarters (0..3); tunable for experiments
 int poly_quarters(const char *env, int dflt) {
@@ -481,12 +525,18 @@ int launch_grad(const CUtensorMap &tq, const CUtensorMap &tk, const void *qhat, 
   const long long items = (long long)B * cp2_cdiv(P, TILE);
   const int grid = (int)(items < cp2_num_sms() ? items : cp2_num_sms());
   kern<<<grid, GRAD_THREADS, Cfg::SMEM, st>>>(tq, tk, static_cast<const __nv_bfloat16 *>(qhat), nl, key_count,
-                                              mask_a, inv_norm, alpha, v1, v2, dq, scale_log2, B, P, P_pad);
+                                              mask_a, inv_norm, alpha, v1, v2, dq, scale_log2, B, P, P_pad,
+                                              g_dense_trace);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }
 
 }  // namespace
+
+extern "C" int cp2_dbg_dense_trace(long long *buf) {   // [n_sms * 16] device counters or NULL (cp2_b200_debug.h)
+  g_dense_trace = buf;
+  return CP2_OK;
+}
 
 extern "C" int cp2_dense_pad(int P) { return P > 0 ? cp2_cdiv(P, TILE) * TILE : 0; }
 

@@ -22,6 +22,12 @@ int cp2_dbg_dense_grad_simt(const void *qhat_t, const void *khat_t, const float 
 int cp2_dbg_global_nce_simt(const float *q_pos, const float *queue, float *z, float *g,
                             float inv_tau, int B, int C, int K, void *stream);
 
+/* Wait-time accounting of the next cp2_dense_grad launches: buf = device array [n_sms*16] of int64 cycle
+ * counters per CTA (0/1 producer waits on q_empty/kempty; 2-5 MMA issuer waits on q_full/d_empty/kfull/
+ * p_full; 6/7 first softmax warp waits on kfull/s_full; 8 epilogue wait on d_full; 10-12 role lifetimes),
+ * or NULL to switch it off. */
+int cp2_dbg_dense_trace(long long *buf);
+
 #ifdef __cplusplus
 }
 #endif
