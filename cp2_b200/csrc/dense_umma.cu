@@ -47,6 +47,105 @@ __device__ __forceinline__ uint64_t kmajor_desc(uint32_t tile_addr, int kk, int 
   return make_sdesc(tile_addr + (kk >> 2) * box_bytes + (kk & 3) * 32, 16, 1024);
 }
 
+// One 32-column chunk of the backward softmax: P~ = exp2(S*scale + nl) packed to bf16 pairs.  Software
+// pipeline over four 8-column groups in explicit program order: X(k) = scale/offset (FFMA2), E(k) = the
+// exponentials (MUFU, or the FMA-pipe polynomial for the first PF pairs of a group), C(k) = bf16 pack.
+template <int PF>
+__device__ __forceinline__ void softmax_chunk_bwd(const uint32_t (&r)[32], uint32_t nl_saddr, f2 scale2,
+                                                  uint32_t (&pk)[16]) {
+  float4 n[8];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) n[u] = lds_f4(nl_saddr + u * 16);
+  f2 x[16];
+  auto X = [&](int k) {
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int j = 4 * k + p;
+      const f2 nlp = (j & 1) ? f2_pack(n[j >> 1].z, n[j >> 1].w) : f2_pack(n[j >> 1].x, n[j >> 1].y);
+      x[j] = f2_fma_v(f2_pack_u(r[2 * j], r[2 * j + 1]), scale2, nlp);
+    }
+  };
+  auto E = [&](int k) {
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int j = 4 * k + p;
+      if (p < PF) {
+        x[j] = exp2_poly2<2>(x[j]);
+      } else {
+        float a, c;
+        f2_unpack(x[j], a, c);
+        a = ex2_approx_v(a);
+        c = ex2_approx_v(c);
+        x[j] = f2_pack(a, c);
+      }
+    }
+  };
+  auto Cv = [&](int k) {
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int j = 4 * k + p;
+      float a, c;
+      f2_unpack(x[j], a, c);
+      pk[j] = pack_bf16x2_v(a, c);
+    }
+  };
+  X(0);
+  X(1);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    E(k);
+    if (k + 2 < 4) X(k + 2);
+    if (k > 0) Cv(k - 1);
+  }
+  Cv(3);
+}
+
+// One full 32-column chunk of the forward: adds sum_j exp2(S_j*scale) into the running pair sums.
+template <int PF>
+__device__ __forceinline__ void softmax_chunk_fwd(const uint32_t (&r)[32], f2 scale2, f2 &acc_m, f2 &acc_m2,
+                                                  f2 &acc_p, f2 &acc_p2) {
+  f2 x[16];
+  auto X = [&](int k) {
+#pragma unroll
+    for (int p = PF; p < 4; ++p) x[4 * k + p] = f2_mul_v(f2_pack_u(r[8 * k + 2 * p], r[8 * k + 2 * p + 1]), scale2);
+  };
+  auto E = [&](int k) {
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int j = 4 * k + p;
+      if (p < PF) {
+        x[j] = exp2_poly2_scaled<3>(f2_pack_u(r[2 * j], r[2 * j + 1]), scale2);
+      } else {
+        float a, c;
+        f2_unpack(x[j], a, c);
+        a = ex2_approx_v(a);
+        c = ex2_approx_v(c);
+        x[j] = f2_pack(a, c);
+      }
+    }
+  };
+  auto A = [&](int k) {
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int j = 4 * k + p;
+      if (p < PF) {
+        if (k & 1) acc_p = f2_add(acc_p, x[j]); else acc_p2 = f2_add(acc_p2, x[j]);
+      } else {
+        if (k & 1) acc_m = f2_add_v(acc_m, x[j]); else acc_m2 = f2_add_v(acc_m2, x[j]);
+      }
+    }
+  };
+  X(0);
+  X(1);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    E(k);
+    if (k + 2 < 4) X(k + 2);
+    if (k > 0) A(k - 1);
+  }
+  A(3);
+}
+
 // ------------------------------------------------------------------ forward
 constexpr int LSE_THREADS = 192;          // warp 0 TMA, warp 1 MMA + TMEM owner, warps 2-5 softmax
 
@@ -146,19 +245,7 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
         if (ch * 32 < nvalid) {                    // warp-uniform
           const uint32_t(&rc)[32] = r[ch & 1];
           if ((ch + 1) * 32 <= nvalid) {
-#pragma unroll
-            for (int pr = 0; pr < 16; ++pr) {
-              const f2 rr = f2_pack_u(rc[2 * pr], rc[2 * pr + 1]);
-              if ((pr & 3) < PF) {
-                if (pr & 4) acc_p = f2_add(acc_p, exp2_poly2_scaled<3>(rr, scale2));
-                else acc_p2 = f2_add(acc_p2, exp2_poly2_scaled<3>(rr, scale2));
-              } else {
-                float a, c;
-                f2_unpack(f2_mul(rr, scale2), a, c);
-                if (pr & 4) acc_m = f2_add(acc_m, f2_pack(ex2_approx(a), ex2_approx(c)));
-                else acc_m2 = f2_add(acc_m2, f2_pack(ex2_approx(a), ex2_approx(c)));
-              }
-            }
+            softmax_chunk_fwd<PF>(rc, scale2, acc_m, acc_m2, acc_p, acc_p2);
           } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j)
@@ -207,7 +294,7 @@ struct GradCfg {
   static constexpr int OPER_K = (C / 64) * KBOX;
   static constexpr int NBARS = 2 * NQ + 2 * NST + 4 + 2 * ND;
   static constexpr size_t SMEM = 1024 + (size_t)NQ * OPER_Q + (size_t)NST * OPER_K + (size_t)NST * TY * 4 +
-                                 NBARS * 8 + 16;
+                                 2 * C * 4 + NBARS * 8 + 16;
   static_assert(2 * TY + ND * C <= 512, "TMEM budget");
 };
 
@@ -238,7 +325,8 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
   uint8_t *sQ = smem;
   uint8_t *sK = sQ + NQ * Cfg::OPER_Q;
   float *nlbuf = reinterpret_cast<float *>(sK + NST * Cfg::OPER_K);      // [NST][TY]
-  uint64_t *bars = reinterpret_cast<uint64_t *>(nlbuf + NST * TY);
+  float *sva = nlbuf + NST * TY, *svb = sva + C;                          // [C] each (epilogue)
+  uint64_t *bars = reinterpret_cast<uint64_t *>(svb + C);
   uint64_t *q_full = bars, *q_empty = q_full + NQ, *kfull = q_empty + NQ, *kempty = kfull + NST,
            *s_full = kempty + NST, *p_full = s_full + 2, *d_full = p_full + 2, *d_empty = d_full + ND;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(d_empty + ND);
@@ -368,7 +456,7 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
         twait(&kfull[s], (g / NST) & 1, tr_a);           // nl slice of this tile landed (bulk copy)
         twait(&s_full[g & 1], (g >> 1) & 1, tr_b);
         tc_fence_after();
-        const float *nlw = nlbuf + s * TY + half * W;
+        const uint32_t nl_saddr = smem_u32(nlbuf + s * TY + half * W);
         uint32_t rb[2][32];
         tmem_ld32(tS, rb[0]);
 #pragma unroll
@@ -377,28 +465,7 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
           tmem_wait_ld();
           if (ch + 1 < W / 32) tmem_ld32(tS + (ch + 1) * 32, rb[(ch + 1) & 1]);
           const uint32_t(&r)[32] = rb[ch & 1];
-          const float4 *nl4 = reinterpret_cast<const float4 *>(nlw + ch * 32);
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const float4 n4 = nl4[u];
-            const f2 xa = f2_fma(f2_pack_u(r[4 * u], r[4 * u + 1]), scale2, f2_pack(n4.x, n4.y));
-            const f2 xb = f2_fma(f2_pack_u(r[4 * u + 2], r[4 * u + 3]), scale2, f2_pack(n4.z, n4.w));
-            float a0, a1, b0, b1;
-            if (((2 * u) & 3) < PF) {
-              f2_unpack(exp2_poly2<2>(xa), a0, a1);
-            } else {
-              f2_unpack(xa, a0, a1);
-              a0 = ex2_approx(a0); a1 = ex2_approx(a1);
-            }
-            if (((2 * u + 1) & 3) < PF) {
-              f2_unpack(exp2_poly2<2>(xb), b0, b1);
-            } else {
-              f2_unpack(xb, b0, b1);
-              b0 = ex2_approx(b0); b1 = ex2_approx(b1);
-            }
-            pk[2 * u] = pack_bf16x2(a0, a1);
-            pk[2 * u + 1] = pack_bf16x2(b0, b1);
-          }
+          softmax_chunk_bwd<PF>(r, nl_saddr + ch * 128, scale2, pk);
           tmem_st16(tS + ch * 16, pk);
         }
         tmem_wait_st();
@@ -421,40 +488,64 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       const float a = valid ? mask_a[(long long)b * P + x] : 0.f;
       const float inr = valid ? inv_norm[(long long)b * P + x] : 0.f;
       const float al = (ny > 0) ? alpha[b] : 0.f;
-      const float *v1b = v1 + (long long)b * C;
-      const float *v2b = v2 ? v2 + (long long)b * C : nullptr;
       const uint4 *qrow = reinterpret_cast<const uint4 *>(qhat + ((long long)b * P + (valid ? x : 0)) * C);
+      // rank-1 vectors of this image -> shared memory: sva = v1 - v2, svb = v2 (read back as broadcasts)
+      const int et = threadIdx.x - 320;                        // 0..127 among the epilogue threads
+      asm volatile("bar.sync 1, 128;" ::: "memory");           // everyone is done with the previous item's copy
+      for (int c = et; c < C; c += 128) {
+        const float b2 = v2 ? v2[(long long)b * C + c] : 0.f;
+        sva[c] = v1[(long long)b * C + c] - b2;
+        svb[c] = b2;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      // software pipeline over the 2 * C/32 (pass, 32-channel chunk) steps: the Qhat row chunk of step s+1 is
+      // loaded while step s computes; the first one is in flight before the accumulator is ready
+      constexpr int NCH = C / 32, NSTEP = 2 * NCH;
+      uint4 qb[2][4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) qb[0][u] = __ldg(qrow + u);
       twait(&d_full[db], (it / ND) & 1, tr_a);
       tc_fence_after();
       const uint32_t tD = tmem_D + db * C + lane_off;
       float dot = 0.f;
 #pragma unroll 1
-      for (int pass = 0; pass < 2; ++pass) {
-#pragma unroll 1
-        for (int ch = 0; ch < C / 32; ++ch) {
-          uint32_t r[32];
-          if (ny > 0) {
-            tmem_ld32(tD + ch * 32, r);
-            tmem_wait_ld();
-          } else {
+      for (int st2 = 0; st2 < NSTEP; st2 += 2) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) r[i] = 0u;
-          }
+      for (int sub = 0; sub < 2; ++sub) {
+        const int st = st2 + sub;
+        const int ch = st % NCH, pass = st / NCH;
+        if (st + 1 < NSTEP) {
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const uint4 qv = __ldg(qrow + ch * 4 + u);
-            const uint32_t qw[4] = {qv.x, qv.y, qv.z, qv.w};
+          for (int u = 0; u < 4; ++u) qb[(sub + 1) & 1][u] = __ldg(qrow + ((st + 1) % NCH) * 4 + u);
+        }
+        uint32_t r[32];
+        if (ny > 0) {
+          tmem_ld32(tD + ch * 32, r);
+          tmem_wait_ld();
+        } else {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const int c = ch * 32 + u * 8 + e;
+          for (int i = 0; i < 32; ++i) r[i] = 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const uint4 qv = qb[sub][u];
+          const uint32_t qw[4] = {qv.x, qv.y, qv.z, qv.w};
+#pragma unroll
+          for (int e4 = 0; e4 < 2; ++e4) {
+            const float4 va = *reinterpret_cast<const float4 *>(sva + ch * 32 + u * 8 + e4 * 4);
+            const float4 vb = *reinterpret_cast<const float4 *>(svb + ch * 32 + u * 8 + e4 * 4);
+            const float vaa[4] = {va.x, va.y, va.z, va.w}, vbb[4] = {vb.x, vb.y, vb.z, vb.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int e = e4 * 4 + i, c = ch * 32 + u * 8 + e;
               const float qh = __uint_as_float((e & 1) ? (qw[e >> 1] & 0xffff0000u) : (qw[e >> 1] << 16));
-              const float s2 = v2b ? __ldg(v2b + c) : 0.f;
-              const float gq = fmaf(al, __uint_as_float(r[u * 8 + e]), fmaf(a, __ldg(v1b + c) - s2, s2));
+              const float gq = fmaf(al, __uint_as_float(r[u * 8 + e]), fmaf(a, vaa[i], vbb[i]));
               if (pass == 0) dot = fmaf(qh, gq, dot);
               else if (valid) dq[((long long)b * C + c) * P + x] = (gq - qh * dot) * inr;
             }
           }
         }
+      }
       }
       tc_fence_before();
       __syncwarp();
@@ -553,7 +644,7 @@ extern "C" int cp2_dense_lse(const void *qhat_t, const void *khat_t, const int *
   if ((rc = make_feature_tmap(&tk, khat_t, B, C, P, TILE)) != CP2_OK) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const float sl2 = inv_tau * LOG2E;
-  const int pf = poly_quarters("CP2_DENSE_PF_FWD", 2);
+  const int pf = poly_quarters("CP2_DENSE_PF_FWD", 1);
 #define CP2_LSE(CC, PFV) launch_lse<CC, PFV>(tq, tk, key_count, lse, sl2, B, P, st)
   if (C == 128) {
     switch (pf) { case 0: return CP2_LSE(128, 0); case 1: return CP2_LSE(128, 1); case 2: return CP2_LSE(128, 2);
@@ -584,7 +675,7 @@ extern "C" int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int 
   dense_nl_kernel<<<dim3(cp2_cdiv(P_pad, 256), B), 256, 0, st>>>(lse, mask_b, key_count, scratch_nl, P, P_pad);
   CP2_LAUNCH_CHECK();
   const float sl2 = inv_tau * LOG2E;
-  const int pf = poly_quarters("CP2_DENSE_PF_BWD", 2);
+  const int pf = poly_quarters("CP2_DENSE_PF_BWD", 1);
 #define CP2_GRAD(CC, TYV, NSTV, NQV, NDV, PFV)                                                                     \
   launch_grad<CC, TYV, NSTV, NQV, NDV, PFV>(tq, tk, qhat_t, scratch_nl, key_count, mask_a, inv_norm, alpha, v1, \
                                          v2, dq, sl2, B, P, P_pad, st)

@@ -314,6 +314,40 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return r;
 }
 
+// "volatile" twins: the compiler keeps volatile asm statements in program order, which is how the softmax
+// loops interleave MUFU work with FMA / conversion work of neighbouring column groups (the two softmax
+// warps that share an SM sub-partition would otherwise run their MUFU phases in lock-step).
+__device__ __forceinline__ float ex2_approx_v(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ f2 f2_fma_v(f2 a, f2 b, f2 c) {
+  f2 r;
+  asm volatile("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v));
+  return r;
+}
+__device__ __forceinline__ f2 f2_mul_v(f2 a, f2 b) {
+  f2 r;
+  asm volatile("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+__device__ __forceinline__ f2 f2_add_v(f2 a, f2 b) {
+  f2 r;
+  asm volatile("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+  return r;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2_v(float lo, float hi) {
+  uint32_t r;
+  asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t saddr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+  return v;
+}
+
 // ------------------------------------------------------- host: tensor-map encode
 // Resolves cuTensorMapEncodeTiled through the runtime (no link-time libcuda dependency).
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,

@@ -24,7 +24,7 @@ if [ "$1" != "nocu" ]; then
   unset CP2_BENCH_CUDA_PROFILER
   SW="python bench.py --sweep-only --sweep-points 3136 --sweep-dims 128 --sweep-iters 1"
   timeout 300 $SW > gpurun_out/plain_sweep.log 2>&1 &&
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'dense_' -s 6 -c 2 \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:"dense_(lse|grad)_kernel" -s 6 -c 2 \
       -o gpurun_out/prof_dense -f $SW > gpurun_out/ncu_dense.log 2>&1
   echo "== ncu dense exit $?"
 fi

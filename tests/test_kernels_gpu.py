@@ -202,7 +202,7 @@ def test_dense_lse_vs_oracle(ops, B, C, P, tau):
     ref = _lse_ref(qh.float(), kh.float(), 1.0 / tau)
     got = ops.dense_lse(dev(qh), dev(kh), 1.0 / tau)
     torch.cuda.synchronize()
-    # half of the exponentials run as a degree-3 polynomial on the FMA pipe (max rel. error 7.6e-5, mean
+    # a quarter of the exponentials run as a degree-3 polynomial on the FMA pipe (max rel. error 7.6e-5, mean
     # bias 5e-6): |d lse| stays below 5e-5, i.e. < 1e-5 relative on a loss whose tolerance is 1e-4
     assert torch.allclose(got.double().cpu(), ref, rtol=0, atol=5e-5), float((got.double().cpu() - ref).abs().max())
 
