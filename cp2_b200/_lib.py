@@ -25,6 +25,10 @@ SIGNATURES = {
     "cp2_global_nce": (c_int, [c_void_p] * 5 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_ema": (c_int, [c_void_p] * 5 + [c_int, c_float, c_float, c_void_p]),
     "cp2_enqueue": (c_int, [c_void_p] * 3 + [c_int] * 3 + [c_void_p]),
+    "cp2_mirror_partials": (c_int, [c_int, c_int64]),
+    "cp2_mirror_loss": (c_int, [c_void_p] * 8 + [c_float, c_float, c_int64, c_int, c_int, c_int64, c_void_p]),
+    "cp2_mirror_up_partials": (c_int, [c_int] * 3),
+    "cp2_mirror_loss_upsampled": (c_int, [c_void_p] * 7 + [c_float, c_float, c_int64] + [c_int] * 6 + [c_void_p]),
 }
 # include/cp2_b200_debug.h — test-only CUDA-core reference kernels
 DEBUG_SIGNATURES = {
@@ -35,7 +39,7 @@ DEBUG_SIGNATURES = {
 }
 
 EMA_CHUNK = 4096  # CP2_EMA_CHUNK
-ABI_VERSION = 2  # CP2_ABI_VERSION
+ABI_VERSION = 3  # CP2_ABI_VERSION
 
 _lib = None
 

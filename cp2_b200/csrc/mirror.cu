@@ -1,0 +1,582 @@
+// a13 / f5 — MirrorModule loss (reference networks/mirror_network.py:40-63, with the
+// bilinear `resize` of networks/segment_network.py:219-231 optionally fused in).
+//
+//   class   = CE(cat(s,t), cat(masks,masks))                  mean over valid pixels
+//   compare = CE(input = softmax(s/T), target = softmax(t/T)) soft-target CE whose *input*
+//             is already a probability map (the reference's double softmax), mean over pixels
+//   loss    = class + lmbd * compare
+//
+// Two kernels, one per-pixel device function:
+//   mirror_full_kernel : logits already at label resolution.  HBM-bound elementwise:
+//                        reads s,t (2*Cls*4 B/px) + labels (8 B/px), writes ds,dt (2*Cls*4 B/px).
+//   mirror_up_kernel   : logits at the decoder's resolution [B,Cls,h,w]; the bilinear
+//                        upsample (align_corners=False) is evaluated on the fly from a
+//                        shared-memory patch and its backward is accumulated on chip, so
+//                        the [B,Cls,H,W] logits and their gradients never exist in HBM:
+//                        algorithmic traffic = the labels (8 B/px).
+// Losses are reduced per CTA and summed in fixed order by mirror_finalize_kernel.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kMaxCls = 8;
+constexpr long long kIgnoreIndex = -100;     // nn.CrossEntropyLoss() default (mirror_network.py:30,32)
+
+struct MirrorScale {
+  float inv_temp;   // 1/T
+  float w_cls;      // 1 / (number of valid class-CE terms)
+  float w_cmp;      // lmbd / (number of pixels)
+};
+
+// One pixel.  s,t: logits; label in [0,CLS) or -1 (ignored).  Adds the un-normalised loss terms to
+// cls_sum / cmp_sum and returns d loss / d s, d loss / d t (already normalised by w_cls / w_cmp).
+template <int CLS, bool HAS_T, bool GRAD>
+__device__ __forceinline__ void mirror_pixel(const float (&s)[CLS], const float (&t)[CLS], int label,
+                                             const MirrorScale &sc, float &cls_sum, float &cmp_sum,
+                                             float (&gs)[CLS], float (&gt)[CLS]) {
+  // ---- class CE on s (and t): lse(x) - x[label]
+  float ms = s[0];
+#pragma unroll
+  for (int c = 1; c < CLS; ++c) ms = fmaxf(ms, s[c]);
+  float es[CLS], zs = 0.f, s_lab = 0.f;
+#pragma unroll
+  for (int c = 0; c < CLS; ++c) {
+    es[c] = __expf(s[c] - ms);
+    zs += es[c];
+    s_lab = (c == label) ? s[c] : s_lab;
+  }
+  const float rzs = __fdividef(1.f, zs);
+  const float valid = label >= 0 ? 1.f : 0.f;
+  cls_sum += valid * (ms + __logf(zs) - s_lab);
+  if constexpr (GRAD) {
+#pragma unroll
+    for (int c = 0; c < CLS; ++c) gs[c] = valid * sc.w_cls * (es[c] * rzs - (c == label ? 1.f : 0.f));
+  }
+  if constexpr (HAS_T) {
+    float mt = t[0];
+#pragma unroll
+    for (int c = 1; c < CLS; ++c) mt = fmaxf(mt, t[c]);
+    float et[CLS], zt = 0.f, t_lab = 0.f;
+#pragma unroll
+    for (int c = 0; c < CLS; ++c) {
+      et[c] = __expf(t[c] - mt);
+      zt += et[c];
+      t_lab = (c == label) ? t[c] : t_lab;
+    }
+    const float rzt = __fdividef(1.f, zt);
+    cls_sum += valid * (mt + __logf(zt) - t_lab);
+    if constexpr (GRAD) {
+#pragma unroll
+      for (int c = 0; c < CLS; ++c) gt[c] = valid * sc.w_cls * (et[c] * rzt - (c == label ? 1.f : 0.f));
+    }
+    // ---- compare: u = softmax(s/T) used as CE *logits*, target tau = softmax(t/T)
+    float u[CLS], tau[CLS], zu = 0.f, ztau = 0.f;
+#pragma unroll
+    for (int c = 0; c < CLS; ++c) {
+      u[c] = __expf((s[c] - ms) * sc.inv_temp);
+      tau[c] = __expf((t[c] - mt) * sc.inv_temp);
+      zu += u[c];
+      ztau += tau[c];
+    }
+    const float rzu = __fdividef(1.f, zu), rztau = __fdividef(1.f, ztau);
+    float e2[CLS], z2 = 0.f;
+#pragma unroll
+    for (int c = 0; c < CLS; ++c) {
+      u[c] *= rzu;
+      tau[c] *= rztau;
+      e2[c] = __expf(u[c]);            // u in [0,1]: no shift needed
+      z2 += e2[c];
+    }
+    const float lse2 = __logf(z2), rz2 = __fdividef(1.f, z2);
+    float cmp = 0.f;
+#pragma unroll
+    for (int c = 0; c < CLS; ++c) cmp -= tau[c] * (u[c] - lse2);
+    cmp_sum += cmp;
+    if constexpr (GRAD) {
+      // d cmp/d u_c = softmax(u)_c - tau_c ;  d cmp/d tau_c = -(u_c - lse2); both through a softmax/T
+      float gu[CLS], gtau[CLS], du = 0.f, dtau = 0.f;
+#pragma unroll
+      for (int c = 0; c < CLS; ++c) {
+        gu[c] = e2[c] * rz2 - tau[c];
+        gtau[c] = lse2 - u[c];
+        du += gu[c] * u[c];
+        dtau += gtau[c] * tau[c];
+      }
+      const float k = sc.w_cmp * sc.inv_temp;
+#pragma unroll
+      for (int c = 0; c < CLS; ++c) {
+        gs[c] += k * u[c] * (gu[c] - du);
+        gt[c] += k * tau[c] * (gtau[c] - dtau);
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ int mirror_label(long long l, int cls) {
+  return (l >= 0 && l < cls) ? (int)l : -1;       // ignore_index (-100) and out-of-range -> ignored
+}
+
+// Block-level sum of three per-thread values -> partial[blockIdx][0..2] (fixed order: deterministic).
+template <int THREADS>
+__device__ __forceinline__ void block_partials(float a, float b, float c, float *partial_row) {
+  __shared__ float red[3][THREADS / 32];
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    a += __shfl_down_sync(0xffffffffu, a, off);
+    b += __shfl_down_sync(0xffffffffu, b, off);
+    c += __shfl_down_sync(0xffffffffu, c, off);
+  }
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) { red[0][wid] = a; red[1][wid] = b; red[2][wid] = c; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float x = 0.f, y = 0.f, z = 0.f;
+    for (int i = 0; i < THREADS / 32; ++i) { x += red[0][i]; y += red[1][i]; z += red[2][i]; }
+    partial_row[0] = x; partial_row[1] = y; partial_row[2] = z;
+  }
+}
+
+// --------------------------------------------------------------------- full resolution
+// s,t,ds,dt: [B,CLS,HW]; labels [B,HW].  One thread = V consecutive pixels, grid-stride.
+template <int CLS, bool HAS_T, bool GRAD, int V>
+__global__ void __launch_bounds__(256)
+mirror_full_kernel(const float *__restrict__ s, const float *__restrict__ t,
+                   const long long *__restrict__ labels, float *__restrict__ partial,
+                   float *__restrict__ ds, float *__restrict__ dt, const float *__restrict__ gscale,
+                   MirrorScale sc, int B, long long HW) {
+  if constexpr (GRAD) {
+    if (gscale != nullptr) { const float g = __ldg(gscale); sc.w_cls *= g; sc.w_cmp *= g; }
+  }
+  const long long groups_per_img = HW / V;
+  const long long total = (long long)B * groups_per_img;
+  float cls_sum = 0.f, cmp_sum = 0.f, n_valid = 0.f;
+  for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < total;
+       g += (long long)gridDim.x * blockDim.x) {
+    const long long b = g / groups_per_img;
+    const long long pix = (g - b * groups_per_img) * V;
+    const long long base = b * CLS * HW + pix;
+    float sv[CLS][V], tv[CLS][V];
+    long long lab[V];
+    if constexpr (V == 4) {
+      const longlong2 l0 = __ldcs(reinterpret_cast<const longlong2 *>(labels + b * HW + pix));
+      const longlong2 l1 = __ldcs(reinterpret_cast<const longlong2 *>(labels + b * HW + pix + 2));
+      lab[0] = l0.x; lab[1] = l0.y; lab[2] = l1.x; lab[3] = l1.y;
+#pragma unroll
+      for (int c = 0; c < CLS; ++c) {
+        const float4 a = __ldcs(reinterpret_cast<const float4 *>(s + base + c * HW));
+        sv[c][0] = a.x; sv[c][1] = a.y; sv[c][2] = a.z; sv[c][3] = a.w;
+        if constexpr (HAS_T) {
+          const float4 q = __ldcs(reinterpret_cast<const float4 *>(t + base + c * HW));
+          tv[c][0] = q.x; tv[c][1] = q.y; tv[c][2] = q.z; tv[c][3] = q.w;
+        }
+      }
+    } else {
+      lab[0] = labels[b * HW + pix];
+#pragma unroll
+      for (int c = 0; c < CLS; ++c) {
+        sv[c][0] = s[base + c * HW];
+        if constexpr (HAS_T) tv[c][0] = t[base + c * HW];
+      }
+    }
+    float gsv[CLS][V], gtv[CLS][V];
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      float sp[CLS], tp[CLS], gs[CLS], gt[CLS];
+#pragma unroll
+      for (int c = 0; c < CLS; ++c) { sp[c] = sv[c][v]; tp[c] = HAS_T ? tv[c][v] : 0.f; }
+      const int label = mirror_label(lab[v], CLS);
+      n_valid += label >= 0 ? 1.f : 0.f;
+      mirror_pixel<CLS, HAS_T, GRAD>(sp, tp, label, sc, cls_sum, cmp_sum, gs, gt);
+      if constexpr (GRAD) {
+#pragma unroll
+        for (int c = 0; c < CLS; ++c) { gsv[c][v] = gs[c]; gtv[c][v] = HAS_T ? gt[c] : 0.f; }
+      }
+    }
+    if constexpr (GRAD) {
+#pragma unroll
+      for (int c = 0; c < CLS; ++c) {
+        if constexpr (V == 4) {
+          __stcs(reinterpret_cast<float4 *>(ds + base + c * HW),
+                 make_float4(gsv[c][0], gsv[c][1], gsv[c][2], gsv[c][3]));
+          if constexpr (HAS_T)
+            __stcs(reinterpret_cast<float4 *>(dt + base + c * HW),
+                   make_float4(gtv[c][0], gtv[c][1], gtv[c][2], gtv[c][3]));
+        } else {
+          ds[base + c * HW] = gsv[c][0];
+          if constexpr (HAS_T) dt[base + c * HW] = gtv[c][0];
+        }
+      }
+    }
+  }
+  block_partials<256>(cls_sum, cmp_sum, n_valid, partial + 3ll * blockIdx.x);
+}
+
+// out[0] = loss, out[1] = class, out[2] = compare (un-weighted), out[3] = valid labelled pixels counted
+__global__ void __launch_bounds__(256)
+mirror_finalize_kernel(const float *__restrict__ partial, int rows, float w_cls, float inv_npix,
+                       float lmbd, float *__restrict__ out) {
+  __shared__ double red[3][256];
+  double a = 0, b = 0, c = 0;
+  for (int i = threadIdx.x; i < rows; i += 256) { a += partial[3 * i]; b += partial[3 * i + 1]; c += partial[3 * i + 2]; }
+  red[0][threadIdx.x] = a; red[1][threadIdx.x] = b; red[2][threadIdx.x] = c;
+  __syncthreads();
+  for (int off = 128; off > 0; off >>= 1) {
+    if (threadIdx.x < off) {
+      red[0][threadIdx.x] += red[0][threadIdx.x + off];
+      red[1][threadIdx.x] += red[1][threadIdx.x + off];
+      red[2][threadIdx.x] += red[2][threadIdx.x + off];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double cls = red[0][0] * (double)w_cls, cmp = red[1][0] * (double)inv_npix;
+    out[0] = (float)(cls + (double)lmbd * cmp);
+    out[1] = (float)cls;
+    out[2] = (float)cmp;
+    out[3] = (float)red[2][0];
+  }
+}
+
+// ------------------------------------------------------------- fused bilinear upsample
+// ATen's upsample_bilinear2d (align_corners=False): src = r*(dst+0.5)-0.5 clamped at 0,
+// i0 = (int)src, i1 = i0 + (i0 < in-1), l1 = src - i0, l0 = 1 - l1, with r = (float)in/out.
+__host__ __device__ __forceinline__ void bilinear_src(int dst, float r, int in, int &i0, int &i1,
+                                                      float &l0, float &l1) {
+  float src = r * ((float)dst + 0.5f) - 0.5f;
+  if (src < 0.f) src = 0.f;
+  i0 = (int)src;
+  if (i0 > in - 1) i0 = in - 1;
+  i1 = i0 + (i0 < in - 1 ? 1 : 0);
+  l1 = src - (float)i0;
+  l0 = 1.f - l1;
+}
+
+constexpr int kUpTW = 128;   // output columns per CTA = threads per CTA
+constexpr int kUpTH = 16;    // output rows per CTA
+
+// s_lo,t_lo,ds_lo,dt_lo: [B,CLS,h,w]; labels [B,H,W].  CTA = kUpTH x kUpTW output pixels of one
+// image, thread = one output column.  Shared memory: the low-resolution patch the tile reads
+// ([2][CLS][PH][PW] values) and, with GRAD, a same-shaped gradient accumulator.
+template <int CLS, bool HAS_T, bool GRAD>
+__global__ void __launch_bounds__(kUpTW)
+mirror_up_kernel(const float *__restrict__ s_lo, const float *__restrict__ t_lo,
+                 const long long *__restrict__ labels, float *__restrict__ partial,
+                 float *__restrict__ ds_lo, float *__restrict__ dt_lo, MirrorScale sc, int h, int w,
+                 int H, int W, float ry, float rx, int PH, int PW) {
+  extern __shared__ float smem[];
+  constexpr int NS = HAS_T ? 2 : 1;
+  const int cell = PH * PW;
+  float *val = smem;                       // [NS][CLS][PH][PW]
+  float *acc = smem + NS * CLS * cell;     // [NS][CLS][PH][PW]  (GRAD only)
+  const int b = blockIdx.z, tid = threadIdx.x, lane = tid & 31;
+  const int x_tile = blockIdx.x * kUpTW, y_tile = blockIdx.y * kUpTH;
+  const int rows = min(kUpTH, H - y_tile);
+
+  int py0, px0, tmp;
+  float f0, f1;
+  bilinear_src(y_tile, ry, h, py0, tmp, f0, f1);
+  bilinear_src(x_tile, rx, w, px0, tmp, f0, f1);
+  for (int i = tid; i < NS * CLS * cell; i += kUpTW) {
+    const int k = i / (CLS * cell), c = (i / cell) % CLS, pi = (i % cell) / PW, pj = i % PW;
+    const int yy = py0 + pi, xx = px0 + pj;
+    const float *src = (k == 0) ? s_lo : t_lo;
+    val[i] = (yy < h && xx < w) ? __ldg(src + (((long long)b * CLS + c) * h + yy) * w + xx) : 0.f;
+    if constexpr (GRAD) acc[i] = 0.f;
+  }
+
+  const int x = x_tile + tid;
+  const bool live = x < W;
+  const int xc = live ? x : W - 1;          // dead lanes keep a sorted key and contribute zeros
+  int ix0, ix1;
+  float l0x, l1x;
+  bilinear_src(xc, rx, w, ix0, ix1, l0x, l1x);
+  ix0 -= px0; ix1 -= px0;
+  // labels of this thread's column: all loads issued before the first use
+  // (then packed to 4-bit codes, label+1, so that the row loop needs no unrolling)
+  long long lab[kUpTH];
+#pragma unroll
+  for (int r = 0; r < kUpTH; ++r)
+    lab[r] = (live && r < rows) ? __ldcs(labels + ((long long)b * H + y_tile + r) * W + x) : kIgnoreIndex;
+  unsigned long long codes = 0;
+#pragma unroll
+  for (int r = 0; r < kUpTH; ++r)
+    codes |= (unsigned long long)(mirror_label(lab[r], CLS) + 1) << (4 * r);
+  // segmented-reduction plan over the (sorted) key ix0 within the warp
+  unsigned same = 0;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const int other = __shfl_down_sync(0xffffffffu, ix0, 1 << i);
+    if (lane + (1 << i) < 32 && other == ix0) same |= 1u << i;
+  }
+  const int prev = __shfl_up_sync(0xffffffffu, ix0, 1);
+  const bool head = lane == 0 || prev != ix0;
+  __syncthreads();
+
+  float top[NS][CLS], bot[NS][CLS], a_top[NS][CLS], a_bot[NS][CLS];
+  int cur0 = -1, cur1 = -1;
+  float cls_sum = 0.f, cmp_sum = 0.f, n_valid = 0.f;
+
+  auto flush = [&]() {
+    if constexpr (GRAD) {
+#pragma unroll
+      for (int k = 0; k < NS; ++k)
+#pragma unroll
+        for (int c = 0; c < CLS; ++c)
+#pragma unroll
+          for (int tb = 0; tb < 2; ++tb) {
+            const float a = tb == 0 ? a_top[k][c] : a_bot[k][c];
+            float v0 = l0x * a, v1 = l1x * a;
+#pragma unroll
+            for (int i = 0; i < 5; ++i) {
+              const float o0 = __shfl_down_sync(0xffffffffu, v0, 1 << i);
+              const float o1 = __shfl_down_sync(0xffffffffu, v1, 1 << i);
+              if (same & (1u << i)) { v0 += o0; v1 += o1; }
+            }
+            if (head) {
+              float *row = acc + (k * CLS + c) * cell + (tb == 0 ? cur0 : cur1) * PW;
+              atomicAdd(row + ix0, v0);
+              atomicAdd(row + ix1, v1);
+            }
+          }
+    }
+  };
+
+#pragma unroll 1
+  for (int r = 0; r < rows; ++r) {            // CTA-uniform trip count and branches
+    int iy0, iy1;
+    float l0y, l1y;
+    bilinear_src(y_tile + r, ry, h, iy0, iy1, l0y, l1y);
+    iy0 -= py0; iy1 -= py0;
+    if (iy0 != cur0) {
+      if (cur0 >= 0) flush();
+      cur0 = iy0; cur1 = iy1;
+#pragma unroll
+      for (int k = 0; k < NS; ++k)
+#pragma unroll
+        for (int c = 0; c < CLS; ++c) {
+          const float *p = val + (k * CLS + c) * cell;
+          top[k][c] = l0x * p[iy0 * PW + ix0] + l1x * p[iy0 * PW + ix1];
+          bot[k][c] = l0x * p[iy1 * PW + ix0] + l1x * p[iy1 * PW + ix1];
+          a_top[k][c] = 0.f; a_bot[k][c] = 0.f;
+        }
+    }
+    float sp[CLS], tp[CLS], gs[CLS], gt[CLS];
+#pragma unroll
+    for (int c = 0; c < CLS; ++c) {
+      sp[c] = l0y * top[0][c] + l1y * bot[0][c];
+      tp[c] = HAS_T ? l0y * top[NS - 1][c] + l1y * bot[NS - 1][c] : 0.f;
+    }
+    const int label = (int)((codes >> (4 * r)) & 15ull) - 1;   // -1: ignored / dead lane
+    float cs = 0.f, cm = 0.f;
+    mirror_pixel<CLS, HAS_T, GRAD>(sp, tp, label, sc, cs, cm, gs, gt);
+    if (live) { cls_sum += cs; cmp_sum += cm; n_valid += label >= 0 ? 1.f : 0.f; }
+    if constexpr (GRAD) {
+      const float m = live ? 1.f : 0.f;
+#pragma unroll
+      for (int c = 0; c < CLS; ++c) {
+        a_top[0][c] += m * l0y * gs[c]; a_bot[0][c] += m * l1y * gs[c];
+        if constexpr (HAS_T) { a_top[1][c] += m * l0y * gt[c]; a_bot[1][c] += m * l1y * gt[c]; }
+      }
+    }
+  }
+  if (cur0 >= 0) flush();
+  if constexpr (GRAD) {
+    __syncthreads();
+    for (int i = tid; i < NS * CLS * cell; i += kUpTW) {
+      const int k = i / (CLS * cell), c = (i / cell) % CLS, pi = (i % cell) / PW, pj = i % PW;
+      const int yy = py0 + pi, xx = px0 + pj;
+      const float v = acc[i];
+      if (yy < h && xx < w && v != 0.f)
+        atomicAdd((k == 0 ? ds_lo : dt_lo) + (((long long)b * CLS + c) * h + yy) * w + xx, v);
+    }
+  }
+  const long long cta = ((long long)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  block_partials<kUpTW>(cls_sum, cmp_sum, n_valid, partial + 3 * cta);
+}
+
+struct UpGeom { int gx, gy, PH, PW; };
+
+UpGeom up_geometry(int h, int w, int H, int W) {
+  UpGeom g;
+  g.gx = cp2_cdiv(W, kUpTW);
+  g.gy = cp2_cdiv(H, kUpTH);
+  const float ry = (float)h / (float)H, rx = (float)w / (float)W;
+  g.PH = 1; g.PW = 1;
+  int a0, a1, b0, b1; float f0, f1;
+  for (int ty = 0; ty < g.gy; ++ty) {
+    bilinear_src(ty * kUpTH, ry, h, a0, a1, f0, f1);
+    const int last = (ty * kUpTH + kUpTH - 1 < H) ? ty * kUpTH + kUpTH - 1 : H - 1;
+    bilinear_src(last, ry, h, b0, b1, f0, f1);
+    if (b1 - a0 + 1 > g.PH) g.PH = b1 - a0 + 1;
+  }
+  for (int tx = 0; tx < g.gx; ++tx) {
+    bilinear_src(tx * kUpTW, rx, w, a0, a1, f0, f1);
+    const int last = (tx * kUpTW + kUpTW - 1 < W) ? tx * kUpTW + kUpTW - 1 : W - 1;
+    bilinear_src(last, rx, w, b0, b1, f0, f1);
+    if (b1 - a0 + 1 > g.PW) g.PW = b1 - a0 + 1;
+  }
+  return g;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------ entry points
+namespace {
+
+int full_blocks(int B, long long HW, bool vec) {
+  const long long groups = (long long)B * HW / (vec ? 4 : 1);
+  long long blocks = (groups + 255) / 256;
+  const long long cap = (long long)cp2_num_sms() * 8;    // grid-stride; whole waves of 148 SMs
+  if (blocks > cap) blocks = cap;
+  return blocks < 1 ? 1 : (int)blocks;
+}
+
+bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+template <int CLS>
+int launch_full(const float *s, const float *t, const long long *labels, float *partial, float *ds,
+                float *dt, const float *gscale, MirrorScale sc, int B, long long HW, bool vec,
+                int blocks, cudaStream_t st) {
+  const bool has_t = t != nullptr, grad = ds != nullptr;
+#define CP2_FULL(HT, GR, VV)                                                                     \
+  mirror_full_kernel<CLS, HT, GR, VV><<<blocks, 256, 0, st>>>(s, t, labels, partial, ds, dt,     \
+                                                               gscale, sc, B, HW)
+  if (vec) {
+    if (has_t) { if (grad) CP2_FULL(true, true, 4); else CP2_FULL(true, false, 4); }
+    else       { if (grad) CP2_FULL(false, true, 4); else CP2_FULL(false, false, 4); }
+  } else {
+    if (has_t) { if (grad) CP2_FULL(true, true, 1); else CP2_FULL(true, false, 1); }
+    else       { if (grad) CP2_FULL(false, true, 1); else CP2_FULL(false, false, 1); }
+  }
+#undef CP2_FULL
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}
+
+template <int CLS>
+int launch_up(const float *s, const float *t, const long long *labels, float *partial, float *ds,
+              float *dt, MirrorScale sc, int B, int h, int w, int H, int W, const UpGeom &g,
+              cudaStream_t st) {
+  const bool has_t = t != nullptr, grad = ds != nullptr;
+  const size_t smem = sizeof(float) * (size_t)(has_t ? 2 : 1) * CLS * g.PH * g.PW * (grad ? 2 : 1);
+  CP2_REQUIRE(smem <= 200 * 1024, "cp2_mirror_loss_upsampled: low-resolution patch of %zu bytes per tile "
+              "does not fit shared memory (h=%d w=%d H=%d W=%d)", smem, h, w, H, W);
+  const float ry = (float)h / (float)H, rx = (float)w / (float)W;
+  const dim3 grid(g.gx, g.gy, B);
+#define CP2_UP(HT, GR)                                                                            \
+  do {                                                                                            \
+    if (smem > 48 * 1024)                                                                         \
+      CP2_CUDA(cudaFuncSetAttribute(mirror_up_kernel<CLS, HT, GR>,                                \
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));     \
+    mirror_up_kernel<CLS, HT, GR><<<grid, kUpTW, smem, st>>>(s, t, labels, partial, ds, dt, sc, h, \
+                                                             w, H, W, ry, rx, g.PH, g.PW);        \
+  } while (0)
+  if (has_t) { if (grad) CP2_UP(true, true); else CP2_UP(true, false); }
+  else       { if (grad) CP2_UP(false, true); else CP2_UP(false, false); }
+#undef CP2_UP
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}
+
+int finalize(const float *partial, int rows, bool has_t, long long n_pix, long long n_valid,
+             float lmbd, float *out, cudaStream_t st) {
+  const float w_cls = 1.0f / (float)((has_t ? 2 : 1) * (double)n_valid);
+  mirror_finalize_kernel<<<1, 256, 0, st>>>(partial, rows, w_cls, 1.0f / (float)n_pix, has_t ? lmbd : 0.f, out);
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}
+
+MirrorScale make_scale(bool has_t, long long n_pix, long long n_valid, float lmbd, float inv_temp) {
+  MirrorScale sc;
+  sc.inv_temp = inv_temp;
+  sc.w_cls = 1.0f / (float)((has_t ? 2 : 1) * (double)n_valid);
+  sc.w_cmp = lmbd / (float)n_pix;
+  return sc;
+}
+
+}  // namespace
+
+extern "C" int cp2_mirror_partials(int B, int64_t HW) {
+  if (B <= 0 || HW <= 0) return 1;
+  return full_blocks(B, HW, HW % 4 == 0);
+}
+
+extern "C" int cp2_mirror_loss(const float *s_logits, const float *t_logits, const int64_t *labels,
+                               float *partial, float *out, float *ds, float *dt, const float *gscale,
+                               float lmbd_compare, float inv_temp, int64_t n_valid, int B, int Cls,
+                               int64_t HW, void *stream) {
+  CP2_REQUIRE(B > 0 && HW > 0, "cp2_mirror_loss: empty input (B=%d HW=%lld): the mean is undefined", B, (long long)HW);
+  CP2_REQUIRE(Cls >= 2 && Cls <= kMaxCls, "cp2_mirror_loss: Cls=%d not in [2,%d]", Cls, kMaxCls);
+  CP2_REQUIRE(s_logits && labels && partial && out, "cp2_mirror_loss: null pointer");
+  CP2_REQUIRE((ds == nullptr) == (dt == nullptr) || t_logits == nullptr, "cp2_mirror_loss: ds and dt go together");
+  CP2_REQUIRE(inv_temp > 0.f, "cp2_mirror_loss: inv_temp=%g", inv_temp);
+  const bool has_t = t_logits != nullptr;
+  const long long n_pix = (long long)B * HW;
+  if (n_valid <= 0) n_valid = n_pix;
+  const bool vec = HW % 4 == 0 && aligned16(s_logits) && (!has_t || aligned16(t_logits)) && aligned16(labels) &&
+                   (ds == nullptr || (aligned16(ds) && (!has_t || aligned16(dt))));
+  // the partial buffer is sized by cp2_mirror_partials (vector geometry): never launch more CTAs
+  int blocks = full_blocks(B, HW, vec);
+  const int cap = cp2_mirror_partials(B, HW);
+  if (blocks > cap) blocks = cap;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const MirrorScale sc = make_scale(has_t, n_pix, n_valid, lmbd_compare, inv_temp);
+  const long long *lab = reinterpret_cast<const long long *>(labels);
+  int rc = CP2_OK;
+#define CP2_CALL_FULL(N) launch_full<N>(s_logits, t_logits, lab, partial, ds, dt, gscale, sc, B, HW, vec, blocks, st)
+  switch (Cls) {
+    case 2: rc = CP2_CALL_FULL(2); break;
+    case 3: rc = CP2_CALL_FULL(3); break;
+    case 4: rc = CP2_CALL_FULL(4); break;
+    case 5: rc = CP2_CALL_FULL(5); break;
+    case 6: rc = CP2_CALL_FULL(6); break;
+    case 7: rc = CP2_CALL_FULL(7); break;
+    default: rc = CP2_CALL_FULL(8); break;
+  }
+#undef CP2_CALL_FULL
+  if (rc != CP2_OK) return rc;
+  return finalize(partial, blocks, has_t, n_pix, n_valid, lmbd_compare, out, st);
+}
+
+extern "C" int cp2_mirror_up_partials(int B, int H, int W) {
+  if (B <= 0 || H <= 0 || W <= 0) return 1;
+  return B * cp2_cdiv(H, kUpTH) * cp2_cdiv(W, kUpTW);
+}
+
+extern "C" int cp2_mirror_loss_upsampled(const float *s_lo, const float *t_lo, const int64_t *labels,
+                                         float *partial, float *out, float *ds_lo, float *dt_lo,
+                                         float lmbd_compare, float inv_temp, int64_t n_valid, int B,
+                                         int Cls, int h, int w, int H, int W, void *stream) {
+  CP2_REQUIRE(B > 0 && h > 0 && w > 0 && H > 0 && W > 0,
+              "cp2_mirror_loss_upsampled: empty input (B=%d h=%d w=%d H=%d W=%d)", B, h, w, H, W);
+  CP2_REQUIRE(Cls >= 2 && Cls <= kMaxCls, "cp2_mirror_loss_upsampled: Cls=%d not in [2,%d]", Cls, kMaxCls);
+  CP2_REQUIRE(s_lo && labels && partial && out, "cp2_mirror_loss_upsampled: null pointer");
+  CP2_REQUIRE((ds_lo == nullptr) == (dt_lo == nullptr) || t_lo == nullptr,
+              "cp2_mirror_loss_upsampled: ds_lo and dt_lo go together");
+  CP2_REQUIRE(inv_temp > 0.f, "cp2_mirror_loss_upsampled: inv_temp=%g", inv_temp);
+  CP2_REQUIRE(B <= 65535, "cp2_mirror_loss_upsampled: B=%d > 65535", B);
+  const bool has_t = t_lo != nullptr;
+  const long long n_pix = (long long)B * H * W;
+  if (n_valid <= 0) n_valid = n_pix;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t lo_bytes = sizeof(float) * (size_t)B * Cls * h * w;
+  if (ds_lo) CP2_CUDA(cudaMemsetAsync(ds_lo, 0, lo_bytes, st));
+  if (dt_lo && has_t) CP2_CUDA(cudaMemsetAsync(dt_lo, 0, lo_bytes, st));
+  const UpGeom g = up_geometry(h, w, H, W);
+  const MirrorScale sc = make_scale(has_t, n_pix, n_valid, lmbd_compare, inv_temp);
+  const long long *lab = reinterpret_cast<const long long *>(labels);
+  int rc = CP2_OK;
+#define CP2_CALL_UP(N) launch_up<N>(s_lo, t_lo, lab, partial, ds_lo, dt_lo, sc, B, h, w, H, W, g, st)
+  switch (Cls) {
+    case 2: rc = CP2_CALL_UP(2); break;
+    case 3: rc = CP2_CALL_UP(3); break;
+    case 4: rc = CP2_CALL_UP(4); break;
+    case 5: rc = CP2_CALL_UP(5); break;
+    case 6: rc = CP2_CALL_UP(6); break;
+    case 7: rc = CP2_CALL_UP(7); break;
+    default: rc = CP2_CALL_UP(8); break;
+  }
+#undef CP2_CALL_UP
+  if (rc != CP2_OK) return rc;
+  return finalize(partial, B * g.gx * g.gy, has_t, n_pix, n_valid, lmbd_compare, out, st);
+}

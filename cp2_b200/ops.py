@@ -312,3 +312,113 @@ def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_
     nan = torch.full((), float("nan"), device=loss.device)
     stats = {"l_pos": l_pos, "acc_ins": nan, "acc_seg": nan}
     return loss, loss_ins, loss_dense, k_pos, q_pos, stats
+
+
+# ------------------------------------------------ mirror variant (a13 / f5)
+def _labels_i64(labels):
+    if labels.dtype != torch.int64:
+        labels = labels.long()
+    return labels if labels.is_contiguous() else labels.contiguous()
+
+
+def mirror_loss_raw(s_logits, t_logits, labels, lmbd_compare, softmax_temp, want_grads, gscale=None, n_valid=None):
+    """One launch of cp2_mirror_loss on full-resolution logits [B,Cls,*spatial] (t_logits may be None:
+    MirrorVariant.NONE).  -> (out [4] = loss, class, compare, n_valid_counted; ds|None; dt|None)."""
+    _need_cuda(s_logits, t_logits, labels)
+    s = _f32c(s_logits)
+    t = None if t_logits is None else _f32c(t_logits)
+    labels = _labels_i64(labels)
+    B, Cls = s.shape[0], s.shape[1]
+    HW = s[0, 0].numel()
+    assert labels.numel() == B * HW and (t is None or t.shape == s.shape), f"{s.shape = } {labels.shape = }"
+    lib = _lib.load()
+    dev = s.device
+    partial = torch.empty((lib.cp2_mirror_partials(B, HW), 3), device=dev, dtype=torch.float32)
+    out = torch.empty((4,), device=dev, dtype=torch.float32)
+    ds = torch.empty_like(s) if want_grads else None
+    dt = torch.empty_like(s) if (want_grads and t is not None) else None
+    _call("cp2_mirror_loss", 2, lib.cp2_mirror_loss, _ptr(s), _ptr(t), _ptr(labels), _ptr(partial), _ptr(out),
+          _ptr(ds), _ptr(dt), _ptr(gscale), float(lmbd_compare), 1.0 / float(softmax_temp),
+          int(n_valid) if n_valid else 0, B, Cls, HW, _stream())
+    return out, ds, dt
+
+
+def mirror_loss_upsampled_raw(s_lo, t_lo, labels, lmbd_compare, softmax_temp, want_grads, n_valid=None):
+    """One launch of cp2_mirror_loss_upsampled: decoder-resolution logits [B,Cls,h,w] against labels
+    [B,H,W]; the bilinear resize (segment_network.py:219-231) happens on chip.
+    -> (out [4]; ds_lo|None; dt_lo|None) for upstream gradient 1."""
+    _need_cuda(s_lo, t_lo, labels)
+    s = _f32c(s_lo)
+    t = None if t_lo is None else _f32c(t_lo)
+    labels = _labels_i64(labels)
+    B, Cls, h, w = s.shape
+    _, H, W = labels.shape
+    assert labels.shape[0] == B and (t is None or t.shape == s.shape), f"{s.shape = } {labels.shape = }"
+    lib = _lib.load()
+    dev = s.device
+    partial = torch.empty((lib.cp2_mirror_up_partials(B, H, W), 3), device=dev, dtype=torch.float32)
+    out = torch.empty((4,), device=dev, dtype=torch.float32)
+    ds = torch.empty_like(s) if want_grads else None
+    dt = torch.empty_like(s) if (want_grads and t is not None) else None
+    n_launch = 2 + (1 if ds is not None else 0) + (1 if dt is not None else 0)     # + memsets of the grads
+    _call("cp2_mirror_loss_upsampled", n_launch, lib.cp2_mirror_loss_upsampled, _ptr(s), _ptr(t), _ptr(labels),
+          _ptr(partial), _ptr(out), _ptr(ds), _ptr(dt), float(lmbd_compare), 1.0 / float(softmax_temp),
+          int(n_valid) if n_valid else 0, B, Cls, h, w, H, W, _stream())
+    return out, ds, dt
+
+
+class MirrorLossFunction(torch.autograd.Function):
+    """loss = class + lmbd * compare on full-resolution logits (mirror_network.py:47-63).
+    Forward = one loss-only pass; backward = one pass that recomputes the per-pixel terms and writes
+    both gradients already multiplied by the upstream gradient (read from device memory)."""
+
+    @staticmethod
+    def forward(ctx, s_logits, t_logits, labels, lmbd_compare, softmax_temp, n_valid):
+        out, _, _ = mirror_loss_raw(s_logits.detach(), None if t_logits is None else t_logits.detach(), labels,
+                                    lmbd_compare, softmax_temp, want_grads=False, n_valid=n_valid)
+        ctx.save_for_backward(s_logits, t_logits, labels)
+        ctx.cfg = (lmbd_compare, softmax_temp, n_valid)
+        aux = out[1:]
+        ctx.mark_non_differentiable(aux)
+        return out[0], aux
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_aux):
+        s_logits, t_logits, labels = ctx.saved_tensors
+        lmbd_compare, softmax_temp, n_valid = ctx.cfg
+        g = g_loss.detach().reshape(1).float().contiguous()
+        _, ds, dt = mirror_loss_raw(s_logits.detach(), None if t_logits is None else t_logits.detach(), labels,
+                                    lmbd_compare, softmax_temp, want_grads=True, gscale=g, n_valid=n_valid)
+        return (ds.reshape(s_logits.shape), None if dt is None else dt.reshape(t_logits.shape),
+                None, None, None, None)
+
+
+class MirrorLossUpsampledFunction(torch.autograd.Function):
+    """The same loss taken directly from the decoder's low-resolution logits: forward computes the
+    loss AND both low-resolution gradients in one pass over the labels; backward only scales the two
+    [B,Cls,h,w] gradients by the upstream gradient."""
+
+    @staticmethod
+    def forward(ctx, s_lo, t_lo, labels, lmbd_compare, softmax_temp, n_valid):
+        need = s_lo.requires_grad or (t_lo is not None and t_lo.requires_grad)
+        out, ds, dt = mirror_loss_upsampled_raw(s_lo.detach(), None if t_lo is None else t_lo.detach(), labels,
+                                                lmbd_compare, softmax_temp, want_grads=need, n_valid=n_valid)
+        ctx.save_for_backward(ds, dt)
+        aux = out[1:]
+        ctx.mark_non_differentiable(aux)
+        return out[0], aux
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_aux):
+        ds, dt = ctx.saved_tensors
+        return (ds * g_loss, None if dt is None else dt * g_loss, None, None, None, None)
+
+
+def mirror_loss(s_logits, t_logits, labels, lmbd_compare=0.01, softmax_temp=2.0, n_valid=None):
+    """-> (loss with autograd to s/t logits, aux [3] = class, compare, valid pixel count)."""
+    return MirrorLossFunction.apply(s_logits, t_logits, labels, lmbd_compare, softmax_temp, n_valid)
+
+
+def mirror_loss_upsampled(s_lo, t_lo, labels, lmbd_compare=0.01, softmax_temp=2.0, n_valid=None):
+    """-> (loss with autograd to the low-resolution logits, aux [3])."""
+    return MirrorLossUpsampledFunction.apply(s_lo, t_lo, labels, lmbd_compare, softmax_temp, n_valid)

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CP2_ABI_VERSION 2
+#define CP2_ABI_VERSION 3
 
 #define CP2_OK 0
 #define CP2_E_INVALID (-1)      /* bad shape / null pointer / unsupported dim          */
@@ -127,6 +127,44 @@ int cp2_ema(const float *const *q_ptrs, float *const *k_ptrs, const int64_t *num
  * Bit-exact with the reference (n <= K). */
 int cp2_enqueue(const float *keys_all, float *queue, int64_t *queue_ptr, int n, int C, int K,
                 void *stream);
+
+/* a13/f5 — MirrorModule loss (networks/mirror_network.py:40-63): class CE on both logit maps +
+ * the "mirror" output-consistency term, forward and backward in one pass.
+ *   class   = CE(cat(s,t), cat(labels,labels))               nn.CrossEntropyLoss(), ignore_index -100
+ *   compare = CE(input = softmax(s/T), target = softmax(t/T)) soft-target CE on a probability map
+ *   loss    = class + lmbd_compare * compare                  (mirror_network.py:62-63)
+ * Replaces the ~10 ATen passes of mirror_network.py:47-63 and their autograd.
+ *   s_logits, t_logits : [B,Cls,HW] f32.  t_logits == NULL selects MirrorVariant.NONE
+ *                        (mirror_network.py:53-55): class CE on s only, compare = 0.
+ *   labels  : [B,HW] int64; -100 (and any value outside [0,Cls)) is ignored by the class term
+ *   partial : [cp2_mirror_partials(B,HW), 3] f32 work space (per-CTA sums, reduced in fixed order)
+ *   out     : [4] f32 = {loss, class, compare, number of valid labelled pixels counted}
+ *   ds, dt  : NULL (loss only) or [B,Cls,HW] f32 OUT: d loss/d s_logits, d loss/d t_logits,
+ *             multiplied by *gscale when gscale != NULL (the upstream gradient, a device scalar)
+ *   n_valid : number of labelled pixels that are not ignored, <= 0 meaning "all B*HW" (the mean of
+ *             the class term divides by it; out[3] reports the counted value for verification)
+ * 2 <= Cls <= 8; inv_temp = 1/T > 0. */
+int cp2_mirror_partials(int B, int64_t HW);
+int cp2_mirror_loss(const float *s_logits, const float *t_logits, const int64_t *labels,
+                    float *partial, float *out, float *ds, float *dt, const float *gscale,
+                    float lmbd_compare, float inv_temp, int64_t n_valid, int B, int Cls, int64_t HW,
+                    void *stream);
+
+/* a13/f5 — the same loss with the bilinear `resize` of SegmentationModule.forward
+ * (networks/segment_network.py:219-231; F.interpolate(mode="bilinear", align_corners=False))
+ * fused in: the kernel reads the decoder's low-resolution logits, interpolates them on chip
+ * and accumulates the upsample's backward on chip, so the [B,Cls,H,W] logits and their gradients
+ * never exist in HBM (algorithmic traffic: the labels).
+ *   s_lo, t_lo   : [B,Cls,h,w] f32 (t_lo == NULL: MirrorVariant.NONE); labels : [B,H,W] int64
+ *   partial      : [cp2_mirror_up_partials(B,H,W), 3] f32 work space; out : [4] f32 as above
+ *   ds_lo, dt_lo : NULL or [B,Cls,h,w] f32 OUT (zeroed here, then accumulated with fp32 atomics:
+ *                  last-bit run-to-run differences, as ATen's own upsample backward)
+ * Gradients are for upstream gradient 1 (they are tiny: scale them on the caller's side). */
+int cp2_mirror_up_partials(int B, int H, int W);
+int cp2_mirror_loss_upsampled(const float *s_lo, const float *t_lo, const int64_t *labels,
+                              float *partial, float *out, float *ds_lo, float *dt_lo,
+                              float lmbd_compare, float inv_temp, int64_t n_valid, int B, int Cls,
+                              int h, int w, int H, int W, void *stream);
 
 #ifdef __cplusplus
 }

@@ -279,6 +279,26 @@ def mirror_loss(s_logits, t_logits, masks, lmbd_compare: float, softmax_temp: fl
     return cls + lmbd_compare * compare, cls, compare
 
 
+def mirror_loss_none(logits, masks):
+    """MirrorVariant.NONE (networks/mirror_network.py:53-55,62-63): class CE only."""
+    cls = F.cross_entropy(logits, masks)
+    return cls, cls, torch.zeros(())
+
+
+def mirror_resize(logits_lo, size):
+    """SegmentationModule.forward's `resize` (networks/segment_network.py:222-228)."""
+    return F.interpolate(logits_lo, size=tuple(size), mode="bilinear", align_corners=False)
+
+
+def mirror_step(s_lo, t_lo, masks, lmbd_compare: float, softmax_temp: float):
+    """shared_step from the segmentor's low-resolution logits: resize then the loss
+    (networks/mirror_network.py:40-63).  t_lo None = MirrorVariant.NONE."""
+    size = masks.shape[-2:]
+    if t_lo is None:
+        return mirror_loss_none(mirror_resize(s_lo, size), masks)
+    return mirror_loss(mirror_resize(s_lo, size), mirror_resize(t_lo, size), masks, lmbd_compare, softmax_temp)
+
+
 # --------------------------------------------------------------- synthetic inputs
 def synth_views(batch, height, width, output_stride, seed, fg_lo=0.5, fg_hi=0.8):
     """Deterministic synthetic inputs of the shape `forward_cp2` takes:

@@ -21,6 +21,7 @@ import sys
 import numpy as np
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import ref_harness as rh  # noqa: E402
@@ -251,6 +252,89 @@ def gen_corr():
     print("corr ok", out["u_iou"][0], out["u_iou_masked"][0], out["s_iou"], out["s_iou_masked"])
 
 
+class _MirrorSelf:
+    """The attributes `MirrorModule.shared_step` (networks/mirror_network.py:40-86) reads.  The
+    reference's own `__init__` cannot run (TypeError at HEAD, SURVEY.md header), so its UNMODIFIED
+    `shared_step` and `SegmentationModule.forward` are called unbound on this holder."""
+
+    def __init__(self, ref_seg, ref_mirror, variant, lo_by_image, image_shape, lmbd, temp):
+        self._seg = ref_seg
+        self.mirror_variant = variant
+        self.image_shape = image_shape
+        self.lmbd_compare_loss = lmbd
+        self.softmax_temp = temp
+        self.class_loss = nn.CrossEntropyLoss()          # mirror_network.py:30-32
+        self.compare_loss = nn.CrossEntropyLoss()
+        self.softmax = nn.Softmax(dim=1)
+        self.logged = {}
+        self._lo = lo_by_image
+        self.model = lambda img: self._lo[id(img)]       # "segmentor": returns the prepared low-res logits
+        self.train_metrics = type("M", (), {"update": lambda *a, **k: None, "items": lambda self_: []})()
+
+    def forward(self, images):                            # segment_network.py:219-231, unmodified
+        return self._seg.SegmentationModule.forward(self, images)
+
+    def log(self, name, value, **_k):
+        self.logged[name] = value
+
+    def log_dict(self, *_a, **_k):
+        pass
+
+
+def gen_mirror():
+    rh.import_reference()
+    import types
+    for name, attrs in (("albumentations", {}),):
+        if name not in sys.modules:
+            m = types.ModuleType(name)
+            m.__dict__.update(attrs)
+            sys.modules[name] = m
+    sys.modules["lightning"].LightningDataModule = object
+    import networks.mirror_network as ref_mirror
+    import networks.segment_network as ref_seg
+    out = {}
+    cases = [  # tag, B, Cls, h, w, H, W, lmbd, T, variant
+        ("a", 2, 2, 4, 4, 64, 64, 0.01, 2.0, "OUTPUT"),        # the reference's defaults (mirror_pretrain.py:50-51), x16
+        ("b", 3, 2, 5, 7, 37, 45, 0.5, 0.7, "OUTPUT"),         # ragged, non-integer scale
+        ("c", 2, 5, 6, 6, 24, 24, 0.1, 1.5, "OUTPUT"),         # multi-class
+        ("d", 2, 3, 8, 8, 8, 8, 0.3, 2.0, "OUTPUT"),           # no resize
+        ("e", 2, 2, 4, 4, 64, 64, 0.01, 2.0, "NONE"),          # MirrorVariant.NONE
+    ]
+    g = torch.Generator().manual_seed(77)
+    for tag, B, Cls, h, w, H, W, lmbd, temp, variant in cases:
+        s_lo = (3.0 * torch.randn(B, Cls, h, w, generator=g)).requires_grad_()
+        t_lo = (3.0 * torch.randn(B, Cls, h, w, generator=g)).requires_grad_()
+        masks = torch.randint(0, Cls, (B, H, W), generator=g)
+        s_img, t_img = torch.zeros(1), torch.zeros(1)
+        holder = _MirrorSelf(ref_seg, ref_mirror, ref_mirror.MirrorVariant[variant],
+                             {id(s_img): s_lo, id(t_img): t_lo}, (3, H, W), lmbd, temp)
+        batch = (s_img, t_img, masks) if variant == "OUTPUT" else (s_img, masks)
+        loss = ref_mirror.MirrorModule.shared_step(holder, batch, ref_seg.Stage.TRAIN)
+        loss.backward()
+        out.update({f"{tag}_s_lo": _np(s_lo), f"{tag}_masks": _np(masks), f"{tag}_loss": _np(loss),
+                    f"{tag}_class": _np(holder.logged["train_class_loss"]),
+                    f"{tag}_ds_lo": _np(s_lo.grad),
+                    f"{tag}_cfg": np.asarray([lmbd, temp], dtype=np.float64),
+                    f"{tag}_variant": np.asarray(variant)})
+        if variant == "OUTPUT":
+            out.update({f"{tag}_t_lo": _np(t_lo), f"{tag}_dt_lo": _np(t_lo.grad),
+                        f"{tag}_compare": _np(holder.logged["train_compare_loss"])})
+        # full-resolution logits and their gradients, for the non-fused kernel
+        s_hi = F.interpolate(s_lo.detach(), size=(H, W), mode="bilinear", align_corners=False).requires_grad_()
+        t_hi = F.interpolate(t_lo.detach(), size=(H, W), mode="bilinear", align_corners=False).requires_grad_()
+        holder2 = _MirrorSelf(ref_seg, ref_mirror, ref_mirror.MirrorVariant[variant], {}, (3, H, W), lmbd, temp)
+        holder2.forward = lambda images, _m={id(s_img): s_hi, id(t_img): t_hi}: (_m[id(images)], None)
+        loss2 = ref_mirror.MirrorModule.shared_step(holder2, batch, ref_seg.Stage.TRAIN)
+        loss2.backward()
+        assert abs(float(loss2) - float(loss)) < 1e-6
+        out[f"{tag}_ds_hi"] = _np(s_hi.grad)
+        if variant == "OUTPUT":
+            out[f"{tag}_dt_hi"] = _np(t_hi.grad)
+        print("mirror", tag, float(loss))
+    out["tags"] = np.asarray([c[0] for c in cases])
+    np.savez_compressed(os.path.join(OUT, "mirror.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     gen_step_small()
@@ -260,3 +344,4 @@ if __name__ == "__main__":
     gen_ema()
     gen_enqueue()
     gen_corr()
+    gen_mirror()

@@ -121,3 +121,22 @@ def test_shuffle_roundtrip():
     gathered = O.concat_all_gather([s[0] for s in shuf])
     back = O.concat_all_gather([O.batch_unshuffle(gathered, shuf[0][1], r, world) for r in range(world)])
     assert torch.equal(back, x)
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c", "d", "e"])
+def test_mirror_step_matches_reference(tag):
+    """oracle.mirror_step vs the unmodified MirrorModule.shared_step + SegmentationModule.forward
+    (networks/mirror_network.py:40-63, segment_network.py:219-231) recorded by gen_golden.gen_mirror."""
+    g = load_golden("mirror.npz")
+    lmbd, temp = (float(v) for v in g[f"{tag}_cfg"])
+    s_lo = T(g[f"{tag}_s_lo"]).requires_grad_(True)
+    none = str(g[f"{tag}_variant"]) == "NONE"
+    t_lo = None if none else T(g[f"{tag}_t_lo"]).requires_grad_(True)
+    loss, cls, cmp = O.mirror_step(s_lo, t_lo, T(g[f"{tag}_masks"]), lmbd, temp)
+    loss.backward()
+    np.testing.assert_allclose(loss.item(), g[f"{tag}_loss"], rtol=1e-6)
+    np.testing.assert_allclose(cls.item(), g[f"{tag}_class"], rtol=1e-6)
+    np.testing.assert_allclose(s_lo.grad.numpy(), g[f"{tag}_ds_lo"], rtol=1e-5, atol=1e-9)
+    if not none:
+        np.testing.assert_allclose(cmp.item(), g[f"{tag}_compare"], rtol=1e-6)
+        np.testing.assert_allclose(t_lo.grad.numpy(), g[f"{tag}_dt_lo"], rtol=1e-5, atol=1e-9)
