@@ -41,6 +41,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=32, help="images per GPU (configs[1]: 32)")
+    ap.add_argument("--nchw", action="store_true",
+                    help="keep the (out-of-scope) cuDNN backbone in NCHW instead of channels_last (NHWC)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the dense-loss microbench sweep")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sweep-only", action="store_true", help="run only the dense-loss sweep (profiling)")
@@ -51,8 +53,9 @@ def parse_args():
     return ap.parse_args()
 
 
-def workload_config(batch, n_gpus):
+def workload_config(batch, n_gpus, nchw=False):
     return {
+        "backbone_memory_format": "NCHW" if nchw else "channels_last (NHWC; fp32 values unchanged)",
         "workload": "BASELINE.json configs[1]: CP2 pretrain, ResNet-50 DeepLabV3 OS16 (torchvision stand-in "
                     "for the mmseg segmentor), 224x224 views (14x14 map), C=128, queue 65536",
         "batch_per_gpu": batch, "global_batch": batch * n_gpus, "image": IMG, "feature_map": IMG // OS_,
@@ -313,6 +316,10 @@ def own_arm(args):
     model = MODEL(None, rank=rank, dim=DIM, K=QUEUE, m=0.999, instance_logits_temp=TAU_G,
                   pretrain_from_scratch=True, lmbd_cp2_dense_loss=LMBD, dense_logits_temp=TAU_D, device=dev,
                   encoder_factory=lambda: DeepLabV3Encoder(dim=DIM), output_stride=OS_).to(dev)
+    if not args.nchw:
+        # cuDNN's tensor-core convolutions are NHWC kernels: NCHW weights/activations cost an
+        # nchwToNhwc / nhwcToNchw transpose around every convolution (11 % of the r01b step)
+        model = model.to(memory_format=torch.channels_last)
     n_params = sum(p.numel() for p in model.encoder_k.parameters())
     net = model
     if world > 1:
@@ -407,7 +414,7 @@ def own_arm(args):
         "metric": METRIC, "value": B * world * args.steps / (ms_value * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_value / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32+bf16",
-        "data": "synthetic", "config": workload_config(B, world),
+        "data": "synthetic", "config": workload_config(B, world, args.nchw),
         "e2e": {"value": B * world * args.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "kernels": kernels,

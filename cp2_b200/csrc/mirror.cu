@@ -28,88 +28,113 @@ struct MirrorScale {
   float w_cmp;      // lmbd / (number of pixels)
 };
 
+__device__ __forceinline__ float ex2_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float lg2_fast(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_fast(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // One pixel.  s,t: logits; label in [0,CLS) or -1 (ignored).  Adds the un-normalised loss terms to
 // cls_sum / cmp_sum and returns d loss / d s, d loss / d t (already normalised by w_cls / w_cmp).
+// All exponentials / logarithms are base-2 MUFU approximations (rel. error ~2^-22) with the
+// log2(e) factors folded into the FFMA that applies the max shift.
 template <int CLS, bool HAS_T, bool GRAD>
 __device__ __forceinline__ void mirror_pixel(const float (&s)[CLS], const float (&t)[CLS], int label,
                                              const MirrorScale &sc, float &cls_sum, float &cmp_sum,
                                              float (&gs)[CLS], float (&gt)[CLS]) {
+  constexpr float kL2E = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
+  const float wv = label >= 0 ? sc.w_cls : 0.f;          // class weight of this pixel (0 if ignored)
+  const float k2 = kL2E * sc.inv_temp;
   // ---- class CE on s (and t): lse(x) - x[label]
   float ms = s[0];
 #pragma unroll
   for (int c = 1; c < CLS; ++c) ms = fmaxf(ms, s[c]);
-  float es[CLS], zs = 0.f, s_lab = 0.f;
+  float es[CLS], zs = 0.f, s_lab = ms;
+  const float nms = -ms * kL2E;
 #pragma unroll
   for (int c = 0; c < CLS; ++c) {
-    es[c] = __expf(s[c] - ms);
+    es[c] = ex2_fast(fmaf(s[c], kL2E, nms));
     zs += es[c];
     s_lab = (c == label) ? s[c] : s_lab;
   }
-  const float rzs = __fdividef(1.f, zs);
-  const float valid = label >= 0 ? 1.f : 0.f;
-  cls_sum += valid * (ms + __logf(zs) - s_lab);
+  float term = fmaf(kLn2, lg2_fast(zs), ms - s_lab);
   if constexpr (GRAD) {
+    const float rzs = rcp_fast(zs) * wv;
 #pragma unroll
-    for (int c = 0; c < CLS; ++c) gs[c] = valid * sc.w_cls * (es[c] * rzs - (c == label ? 1.f : 0.f));
+    for (int c = 0; c < CLS; ++c) gs[c] = fmaf(es[c], rzs, c == label ? -wv : 0.f);
   }
   if constexpr (HAS_T) {
     float mt = t[0];
 #pragma unroll
     for (int c = 1; c < CLS; ++c) mt = fmaxf(mt, t[c]);
-    float et[CLS], zt = 0.f, t_lab = 0.f;
+    float et[CLS], zt = 0.f, t_lab = mt;
+    const float nmt = -mt * kL2E;
 #pragma unroll
     for (int c = 0; c < CLS; ++c) {
-      et[c] = __expf(t[c] - mt);
+      et[c] = ex2_fast(fmaf(t[c], kL2E, nmt));
       zt += et[c];
       t_lab = (c == label) ? t[c] : t_lab;
     }
-    const float rzt = __fdividef(1.f, zt);
-    cls_sum += valid * (mt + __logf(zt) - t_lab);
+    term += fmaf(kLn2, lg2_fast(zt), mt - t_lab);
     if constexpr (GRAD) {
+      const float rzt = rcp_fast(zt) * wv;
 #pragma unroll
-      for (int c = 0; c < CLS; ++c) gt[c] = valid * sc.w_cls * (et[c] * rzt - (c == label ? 1.f : 0.f));
+      for (int c = 0; c < CLS; ++c) gt[c] = fmaf(et[c], rzt, c == label ? -wv : 0.f);
     }
     // ---- compare: u = softmax(s/T) used as CE *logits*, target tau = softmax(t/T)
     float u[CLS], tau[CLS], zu = 0.f, ztau = 0.f;
+    const float nms2 = -ms * k2, nmt2 = -mt * k2;
 #pragma unroll
     for (int c = 0; c < CLS; ++c) {
-      u[c] = __expf((s[c] - ms) * sc.inv_temp);
-      tau[c] = __expf((t[c] - mt) * sc.inv_temp);
+      u[c] = ex2_fast(fmaf(s[c], k2, nms2));
+      tau[c] = ex2_fast(fmaf(t[c], k2, nmt2));
       zu += u[c];
       ztau += tau[c];
     }
-    const float rzu = __fdividef(1.f, zu), rztau = __fdividef(1.f, ztau);
+    const float rzu = rcp_fast(zu), rztau = rcp_fast(ztau);
     float e2[CLS], z2 = 0.f;
 #pragma unroll
     for (int c = 0; c < CLS; ++c) {
       u[c] *= rzu;
       tau[c] *= rztau;
-      e2[c] = __expf(u[c]);            // u in [0,1]: no shift needed
+      e2[c] = ex2_fast(u[c] * kL2E);   // u in [0,1]: no shift needed
       z2 += e2[c];
     }
-    const float lse2 = __logf(z2), rz2 = __fdividef(1.f, z2);
-    float cmp = 0.f;
+    const float lse2 = kLn2 * lg2_fast(z2);
+    // cmp = -sum tau_c (u_c - lse2) = lse2 - sum tau_c u_c   (sum tau = 1)
+    float tu = 0.f;
 #pragma unroll
-    for (int c = 0; c < CLS; ++c) cmp -= tau[c] * (u[c] - lse2);
-    cmp_sum += cmp;
+    for (int c = 0; c < CLS; ++c) tu = fmaf(tau[c], u[c], tu);
+    cmp_sum += lse2 - tu;
     if constexpr (GRAD) {
-      // d cmp/d u_c = softmax(u)_c - tau_c ;  d cmp/d tau_c = -(u_c - lse2); both through a softmax/T
-      float gu[CLS], gtau[CLS], du = 0.f, dtau = 0.f;
+      // d cmp/d u_c = softmax(u)_c - tau_c ;  d cmp/d tau_c = lse2 - u_c; both through a softmax/T
+      const float rz2 = rcp_fast(z2);
+      float gu[CLS], du = 0.f;
 #pragma unroll
       for (int c = 0; c < CLS; ++c) {
-        gu[c] = e2[c] * rz2 - tau[c];
-        gtau[c] = lse2 - u[c];
-        du += gu[c] * u[c];
-        dtau += gtau[c] * tau[c];
+        gu[c] = fmaf(e2[c], rz2, -tau[c]);
+        du = fmaf(gu[c], u[c], du);
       }
+      // sum_c (lse2 - u_c) tau_c = lse2 - tu, so gtau_c - dtau = tu - u_c
       const float k = sc.w_cmp * sc.inv_temp;
 #pragma unroll
       for (int c = 0; c < CLS; ++c) {
-        gs[c] += k * u[c] * (gu[c] - du);
-        gt[c] += k * tau[c] * (gtau[c] - dtau);
+        gs[c] = fmaf(k * u[c], gu[c] - du, gs[c]);
+        gt[c] = fmaf(k * tau[c], tu - u[c], gt[c]);
       }
     }
   }
+  cls_sum += label >= 0 ? term : 0.f;
 }
 
 __device__ __forceinline__ int mirror_label(long long l, int cls) {

@@ -176,15 +176,19 @@ class EmaPlan:
         assert len(self.params_q) == len(self.params_k)
 
     def _signature(self):
-        return tuple((pq.data_ptr(), pk.data_ptr(), pk.numel()) for pq, pk in zip(self.params_q, self.params_k))
+        return tuple((pq.data_ptr(), pk.data_ptr(), pk.numel(), pk.stride())
+                     for pq, pk in zip(self.params_q, self.params_k))
 
     def _build(self):
         _need_cuda(*self.params_q, *self.params_k)
         for pq, pk in zip(self.params_q, self.params_k):
             if pq.dtype != torch.float32 or pk.dtype != torch.float32:
                 raise RuntimeError("cp2_ema: fp32 parameters only")
-            if not (pq.is_contiguous() and pk.is_contiguous()) or pq.shape != pk.shape:
-                raise RuntimeError("cp2_ema: parameters must be contiguous and shape-matched")
+            # elementwise over the storage: any dense layout works (contiguous or channels_last)
+            # as long as both sides use the same one
+            dense = pk.is_contiguous() or (pk.dim() == 4 and pk.is_contiguous(memory_format=torch.channels_last))
+            if not dense or pq.shape != pk.shape or pq.stride() != pk.stride():
+                raise RuntimeError("cp2_ema: parameters must be dense, shape- and stride-matched")
         dev = self.params_k[0].device
         self.n_params = sum(p.numel() for p in self.params_k)
         ct, ci = [], []
