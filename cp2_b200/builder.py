@@ -287,30 +287,60 @@ class MODEL(nn.Module):
         """builder.py:589-607."""
         ops.enqueue(concat_all_gather(keys), self.queue2, self.queue2_ptr)
 
-    # ----------------------------------------------------------------- a11
+    # ----------------------------------------------------------------- a11 / f1
+    @staticmethod
+    def _exchange_rows(x, perm_host):
+        """out_global[i] = in_global[perm[i]] for a batch sharded in rank order, moving ONLY the rows each
+        rank needs (one all_to_all_single = grouped ncclSend/ncclRecv over NVLink) instead of the
+        reference's all-gather of the whole global batch (builder.py:612,635: W x the data).
+        `perm_host` is the full permutation on the HOST, identical on every rank."""
+        W, me, B = _world(), _rank(), x.shape[0]
+        need = perm_host.view(W, B)                              # need[r] = global rows rank r must end up with
+        owner = torch.div(need, B, rounding_mode="floor")
+        # what I send to rank r: my local rows among need[r], in the order they appear in need[r]
+        send_rows = [need[r][owner[r] == me] - me * B for r in range(W)]
+        in_splits = [int(t.numel()) for t in send_rows]
+        # what I receive: grouped by source rank, each group in need[me] order (stable sort by owner)
+        order = torch.sort(owner[me], stable=True).indices       # recv[i] belongs at position order[i]
+        out_splits = torch.bincount(owner[me], minlength=W).tolist()
+        send = x.index_select(0, torch.cat(send_rows).to(x.device, non_blocking=True)).contiguous()
+        recv = torch.empty_like(x)
+        dist.all_to_all_single(recv, send, output_split_sizes=out_splits, input_split_sizes=in_splits)
+        inv = torch.empty_like(order)
+        inv[order] = torch.arange(B)
+        return recv.index_select(0, inv.to(x.device, non_blocking=True))
+
     @torch.no_grad()
     def _batch_shuffle_ddp(self, x):
-        """builder.py:609-630.  Same RNG contract: every rank draws a CPU `randperm`, rank
-        0's is broadcast."""
+        """builder.py:609-630.  Same RNG contract: every rank draws a CPU `randperm`, rank 0's is
+        broadcast.  Returns (x_shuffled_for_this_rank, idx_unshuffle) like the reference; the rows
+        travel by all-to-all."""
         batch_size_this = x.shape[0]
-        x_gather = concat_all_gather(x)
-        batch_size_all = x_gather.shape[0]
-        num_gpus = batch_size_all // batch_size_this
-        idx_shuffle = torch.randperm(batch_size_all).to(x.device)
-        if _world() > 1:
+        W = _world()
+        batch_size_all = batch_size_this * W
+        idx_host = torch.randperm(batch_size_all)                # CPU generator, advanced on every rank
+        idx_shuffle = idx_host.to(x.device)
+        if W > 1:
             dist.broadcast(idx_shuffle, src=0)
+            if _rank() != 0:
+                idx_host = idx_shuffle.cpu()                     # rank 0 already holds the winning draw
         idx_unshuffle = torch.argsort(idx_shuffle)
-        idx_this = idx_shuffle.view(num_gpus, -1)[_rank()]
-        return x_gather[idx_this], idx_unshuffle
+        self._unshuffle_host = (idx_unshuffle, torch.argsort(idx_host))
+        if W == 1:
+            return x[idx_shuffle], idx_unshuffle
+        return self._exchange_rows(x, idx_host), idx_unshuffle
 
     @torch.no_grad()
     def _batch_unshuffle_ddp(self, x, idx_unshuffle):
         """builder.py:632-649."""
-        batch_size_this = x.shape[0]
-        x_gather = concat_all_gather(x)
-        num_gpus = x_gather.shape[0] // batch_size_this
-        idx_this = idx_unshuffle.view(num_gpus, -1)[_rank()]
-        return x_gather[idx_this]
+        if _world() == 1:
+            return x[idx_unshuffle]
+        cached = getattr(self, "_unshuffle_host", None)
+        if cached is not None and cached[0] is idx_unshuffle:
+            perm_host = cached[1]                                # no second device->host read
+        else:
+            perm_host = idx_unshuffle.cpu()
+        return self._exchange_rows(x, perm_host)
 
     def forward(self, **kwargs):                               # builder.py:651-665
         return self.forward_cp2(**kwargs)

@@ -147,10 +147,12 @@ __device__ __forceinline__ void softmax_chunk_fwd(const uint32_t (&r)[32], f2 sc
 }
 
 // ------------------------------------------------------------------ forward
-constexpr int LSE_THREADS = 192;          // warp 0 TMA, warp 1 MMA + TMEM owner, warps 2-5 softmax
-
-template <int C, int NST, int PF>
-__global__ void __launch_bounds__(LSE_THREADS)
+// warp 0 TMA, warp 1 MMA + TMEM owner, warps 2..2+NSW-1 softmax.  NSW = 4: one warp per TMEM lane quadrant
+// takes all 128 query columns of a tile; NSW = 8: two warps per quadrant take 64 columns each.  The
+// FMUL2 -> MUFU -> FADD2 stream of one warp issues in order, so the MUFU pipe only saturates with >= 4
+// such warps per SM sub-partition (dev/mb/microbench.cu: 12.5 ex2/clk/SM with 2 warps, 15.1 with 4).
+template <int C, int NST, int PF, int NSW>
+__global__ void __launch_bounds__(64 + 32 * NSW, 2)
 dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                  const int *__restrict__ key_count, float *__restrict__ lse, float scale_log2, int P) {
   constexpr int BOX = TILE * 128;
@@ -162,6 +164,8 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
   uint64_t *bars = reinterpret_cast<uint64_t *>(sQ + NST * OPER);
   uint64_t *bar_k = bars, *full = bars + 1, *empty = full + NST, *tfull = empty + NST, *tempty = tfull + 2;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 2);
+  float *half_sum = reinterpret_cast<float *>(tmem_slot + 4);      // [TILE] partial sums of the upper column half
+  constexpr int CW = TILE / (NSW / 4);                             // query columns per softmax warp
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.y, y0 = blockIdx.x * TILE;
@@ -176,7 +180,7 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
   if (threadIdx.x == 0) {
     mbar_init(bar_k, 1);
     for (int s = 0; s < NST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], NSW); }
     fence_barrier_init();
     prefetch_tmap(&tm_q);
     prefetch_tmap(&tm_k);
@@ -224,9 +228,9 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       __syncwarp();
     }
   } else {
-    const int quad = warp & 3;
+    const int quad = warp & 3, half = (warp - 2) >> 2, c0 = half * CW;
     const int y = y0 + quad * 32 + lane;
-    const uint32_t lane_base = tmem + (uint32_t(quad * 32) << 16);
+    const uint32_t lane_base = tmem + (uint32_t(quad * 32) << 16) + c0;
     const f2 scale2 = f2_pack(scale_log2, scale_log2);
     f2 acc_m = f2_pack(0.f, 0.f), acc_p = f2_pack(0.f, 0.f), acc_m2 = acc_m, acc_p2 = acc_m;
     float tail = 0.f;
@@ -234,14 +238,14 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
       const int buf = i & 1, tph = (i >> 1) & 1;
       mbar_wait(&tfull[buf], tph);
       tc_fence_after();
-      const int nvalid = min(TILE, P - i * TILE);
+      const int nvalid = min(CW, P - i * TILE - c0);     // valid columns of this warp's slice (may be <= 0)
       // software pipeline: the TMEM load of chunk ch+1 is in flight while chunk ch is exponentiated
       uint32_t r[2][32];
       tmem_ld32(lane_base + buf * TILE, r[0]);
 #pragma unroll
-      for (int ch = 0; ch < TILE / 32; ++ch) {
+      for (int ch = 0; ch < CW / 32; ++ch) {
         tmem_wait_ld();
-        if (ch + 1 < TILE / 32 && (ch + 1) * 32 < nvalid) tmem_ld32(lane_base + buf * TILE + (ch + 1) * 32, r[(ch + 1) & 1]);
+        if (ch + 1 < CW / 32 && (ch + 1) * 32 < nvalid) tmem_ld32(lane_base + buf * TILE + (ch + 1) * 32, r[(ch + 1) & 1]);
         if (ch * 32 < nvalid) {                    // warp-uniform
           const uint32_t(&rc)[32] = r[ch & 1];
           if ((ch + 1) * 32 <= nvalid) {
@@ -259,7 +263,13 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     }
     float s0, s1;
     f2_unpack(f2_add(f2_add(acc_m, acc_m2), f2_add(acc_p, acc_p2)), s0, s1);
-    if (y < P) lse[(long long)b * P + y] = log2f(s0 + s1 + tail) * LN2;
+    float total = s0 + s1 + tail;
+    if constexpr (NSW == 8) {
+      if (half == 1) half_sum[quad * 32 + lane] = total;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (half == 0) total += half_sum[quad * 32 + lane];
+    }
+    if (half == 0 && y < P) lse[(long long)b * P + y] = log2f(total) * LN2;
   }
   tc_fence_before();
   __syncthreads();
@@ -591,16 +601,16 @@ int poly_quarters(const char *env, int dflt) {
 }
 
 template <int C>
-constexpr size_t lse_smem(int nst) { return 1024 + (size_t)(C / 64) * TILE * 128 * (1 + nst) + 256; }
+constexpr size_t lse_smem(int nst) { return 1024 + (size_t)(C / 64) * TILE * 128 * (1 + nst) + 256 + TILE * 4; }
 
-template <int C, int PF>
+template <int C, int PF, int NSW>
 int launch_lse(const CUtensorMap &tq, const CUtensorMap &tk, const int *key_count, float *lse, float scale_log2,
                int B, int P, cudaStream_t st) {
   constexpr int NST = 2;
   const size_t smem = lse_smem<C>(NST);
-  CP2_CUDA(cudaFuncSetAttribute(dense_lse_kernel<C, NST, PF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CP2_CUDA(cudaFuncSetAttribute(dense_lse_kernel<C, NST, PF, NSW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(cp2_cdiv(P, TILE), B);
-  dense_lse_kernel<C, NST, PF><<<grid, LSE_THREADS, smem, st>>>(tq, tk, key_count, lse, scale_log2, P);
+  dense_lse_kernel<C, NST, PF, NSW><<<grid, 64 + 32 * NSW, smem, st>>>(tq, tk, key_count, lse, scale_log2, P);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }
@@ -644,8 +654,13 @@ extern "C" int cp2_dense_lse(const void *qhat_t, const void *khat_t, const int *
   if ((rc = make_feature_tmap(&tk, khat_t, B, C, P, TILE)) != CP2_OK) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const float sl2 = inv_tau * LOG2E;
-  const int pf = poly_quarters("CP2_DENSE_PF_FWD", 1);
-#define CP2_LSE(CC, PFV) launch_lse<CC, PFV>(tq, tk, key_count, lse, sl2, B, P, st)
+  // measured on B200 (dev/tune_dense.py, P=3136): C=128 best at 8 softmax warps + 1/4 of the exponentials on
+  // the FMA pipe; at C=256 (one CTA per SM, MMA twice as long per exponential) the plain MUFU stream wins
+  const int pf = poly_quarters("CP2_DENSE_PF_FWD", C == 128 ? 1 : 0);
+  const char *nsw_env = getenv("CP2_DENSE_NSW_FWD");
+  const bool nsw8 = !(nsw_env && atoi(nsw_env) == 4);
+#define CP2_LSE(CC, PFV) (nsw8 ? launch_lse<CC, PFV, 8>(tq, tk, key_count, lse, sl2, B, P, st) \
+                               : launch_lse<CC, PFV, 4>(tq, tk, key_count, lse, sl2, B, P, st))
   if (C == 128) {
     switch (pf) { case 0: return CP2_LSE(128, 0); case 1: return CP2_LSE(128, 1); case 2: return CP2_LSE(128, 2);
                   default: return CP2_LSE(128, 3); }

@@ -71,6 +71,72 @@ __global__ void __launch_bounds__(512) alu_kernel(long long *cycles, float *sink
   if (r == 1.2345f) sink[0] = r;
 }
 
+// MODE 0: per 8 pairs: 8 FMUL2 + 16 MUFU + 8 FADD2 (the forward's MUFU path, packed fp32x2)
+// MODE 1: same with scalar FMUL/FADD (16 + 16 + 16)
+// MODE 2: MODE 0 in bursts (8 FMUL2, then 16 MUFU, then 8 FADD2)
+template <int MODE>
+__global__ void __launch_bounds__(512) mix_kernel(long long *cycles, float *sink, int iters, float scale) {
+  f2 acc[4];
+  float sa[8];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) acc[j] = f2_pack(0.f, 0.f);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sa[j] = 0.f;
+  f2 src[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) src[j] = f2_pack(0.001f * (threadIdx.x + j), 0.002f * (threadIdx.x + j));
+  const f2 scale2 = f2_pack(scale, scale);
+  __syncthreads();
+  const long long t0 = clock64();
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) src[j].v += 0x0000000100000001ull;      // new inputs every iteration (ALU pipe)
+    if (MODE == 0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        f2 x = f2_mul_v(src[j], scale2);
+        float a, c;
+        f2_unpack(x, a, c);
+        a = ex2_approx_v(a);
+        c = ex2_approx_v(c);
+        acc[j & 3] = f2_add_v(acc[j & 3], f2_pack(a, c));
+      }
+    } else if (MODE == 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float a, c;
+        f2_unpack(src[j], a, c);
+        a = ex2_approx_v(a * scale);
+        c = ex2_approx_v(c * scale);
+        sa[j] += a;
+        sa[(j + 4) & 7] += c;
+      }
+    } else {
+      f2 x[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[j] = f2_mul_v(src[j], scale2);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float a, c;
+        f2_unpack(x[j], a, c);
+        a = ex2_approx_v(a);
+        c = ex2_approx_v(c);
+        x[j] = f2_pack(a, c);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j & 3] = f2_add_v(acc[j & 3], x[j]);
+    }
+  }
+  const long long t1 = clock64();
+  float r = 0.f;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { float x, y; f2_unpack(acc[j], x, y); r += x + y; }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) r += sa[j];
+  if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
+  if (r == 1.2345f) sink[0] = r;
+}
+
 int main() {
   long long *cyc; unsigned *sink; cudaMalloc(&cyc, 148 * 8); cudaMalloc(&sink, 64);
   long long h[148];
@@ -105,6 +171,15 @@ int main() {
     snprintf(nm, 96, "exp2_poly2<3>             warps=%d", warps); report(nm, (double)iters * 8 * 32 * warps, "exp");
     alu_kernel<5><<<148, warps * 32>>>(cyc, (float *)sink, iters);
     snprintf(nm, 96, "cvt.bf16x2                warps=%d", warps); report(nm, (double)iters * 4 * 32 * warps, "cvt");
+  }
+  for (int warps : {4, 8, 16}) {
+    char nm[96];
+    mix_kernel<0><<<148, warps * 32>>>(cyc, (float *)sink, iters, 0.999f);
+    snprintf(nm, 96, "mix FMUL2+2MUFU+FADD2 interleaved warps=%d", warps); report(nm, (double)iters * 16 * 32 * warps, "ex2");
+    mix_kernel<1><<<148, warps * 32>>>(cyc, (float *)sink, iters, 0.999f);
+    snprintf(nm, 96, "mix scalar FMUL+MUFU+FADD        warps=%d", warps); report(nm, (double)iters * 16 * 32 * warps, "ex2");
+    mix_kernel<2><<<148, warps * 32>>>(cyc, (float *)sink, iters, 0.999f);
+    snprintf(nm, 96, "mix bursts 8 FMUL2/16 MUFU/8 FADD2 warps=%d", warps); report(nm, (double)iters * 16 * 32 * warps, "ex2");
   }
   return 0;
 }

@@ -53,6 +53,25 @@ __global__ void __launch_bounds__(64 + 32 * (BG > 0 ? BG : 1)) mma_kernel(long l
             mma_f16_ss(tmem, sdesc_advance(dQ, off), sdesc_advance(dK, off), id256, kk > 0);
           }
         }
+        if (MODE == 4 || MODE == 5) {            // TS S-GEMM: A = stationary tile in TMEM (cols 320..383), B K-major
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk) {
+            const uint32_t off = (kk >> 2) * 16384 + (kk & 3) * 32;
+            mma_f16_ts(tmem + (t & 1) * 128, tmem + 320 + kk * 8, sdesc_advance(dK, off), id128, kk > 0);
+          }
+        }
+        if (MODE == 5) {                         // + TS dQ-GEMM (proposed backward mix)
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk)
+            mma_f16_ts(tmem + 256, tmem + (t & 1) * 128 + kk * 8, sdesc_advance(dKmn, kk * 2048), idmn, 1u);
+        }
+        if (MODE == 6) {                         // TS S-GEMM with N=256
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk) {
+            const uint32_t off = (kk >> 2) * 16384 + (kk & 3) * 32;
+            mma_f16_ts(tmem, tmem + 320 + kk * 8, sdesc_advance(dK, off), id256, kk > 0);
+          }
+        }
         if ((t & 7) == 7 || t == tiles - 1) mma_commit(&bar);
       }
       __syncwarp();
@@ -96,6 +115,9 @@ int main() {
   run<1, 0>("TS  128x128x16 x8 (B MN-major)", 8);
   run<2, 0>("SS x8 + TS x8 (backward mix)", 16);
   run<3, 0>("SS  128x256x16 x8", 8);
+  run<4, 0>("TS  128x128x16 x8 (B K-major; fwd proposal)", 8);
+  run<5, 0>("TS S x8 + TS dQ x8 (bwd proposal)", 16);
+  run<6, 0>("TS  128x256x16 x8 (B K-major)", 8);
   run<0, 8>("SS  128x128x16 x8   + 8 warps LDTM/STTM", 8);
   run<1, 8>("TS  128x128x16 x8   + 8 warps LDTM/STTM", 8);
   run<2, 8>("SS x8 + TS x8       + 8 warps LDTM/STTM", 16);

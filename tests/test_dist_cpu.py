@@ -60,6 +60,19 @@ def _worker(rank, port, out_dir):
     res["unshuffle_oracle"] = torch.equal(
         back, O.batch_unshuffle(torch.cat([O.batch_shuffle(all_imgs, idx_shuffle, r, WORLD)[0] * 2.0
                                            for r in range(WORLD)]), idx_unshuffle, rank, WORLD))
+    # a non-cached idx tensor (e.g. restored by a caller) takes the device->host path and agrees
+    back2 = model._batch_unshuffle_ddp(shuf * 2.0, idx_unshuffle.clone())
+    res["unshuffle_uncached"] = torch.equal(back2, imgs * 2.0)
+    # several more draws with 4-D payloads (ragged per-peer row counts in the all-to-all)
+    ok = True
+    for t in range(6):
+        big = torch.randn(5, 3, 4, 4) + rank
+        all_big = [torch.empty_like(big) for _ in range(WORLD)]
+        dist.all_gather(all_big, big)
+        s5, iu = model._batch_shuffle_ddp(big)
+        ref5, _ = O.batch_shuffle(torch.cat(all_big), torch.argsort(iu), rank, WORLD)
+        ok = ok and torch.equal(s5, ref5) and torch.equal(model._batch_unshuffle_ddp(s5, iu), big)
+    res["shuffle_4d_ok"] = ok
     # a9: the gathered keys every rank would enqueue are identical and rank-ordered -> identical queues
     keys = torch.randn(4, 128)
     keys_all = concat_all_gather(keys)
@@ -76,7 +89,8 @@ def test_world2_gloo_host_logic(tmp_path):
     mp.spawn(_worker, args=(port, str(tmp_path)), nprocs=WORLD, join=True)
     outs = [torch.load(tmp_path / f"r{r}.pt") for r in range(WORLD)]
     for o in outs:
-        for k in ("gather_ok", "shuffle_ok", "same_perm", "unshuffle_ok", "unshuffle_oracle"):
+        for k in ("gather_ok", "shuffle_ok", "same_perm", "unshuffle_ok", "unshuffle_oracle", "unshuffle_uncached",
+                  "shuffle_4d_ok"):
             assert o["res"][k], k
         assert o["res"]["ptr"] == 4
     assert torch.equal(outs[0]["queue"], outs[1]["queue"])
