@@ -324,8 +324,13 @@ def own_arm(args):
     net = model
     if world > 1:
         # queues are identical on every rank by construction -> no per-forward buffer broadcast
-        net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], find_unused_parameters=True,
-                                                        broadcast_buffers=False)
+        # conv_seg never receives a gradient in contrast mode (the reason the reference passes
+        # find_unused_parameters=True, main.py:456-461): freezing it is behaviour-neutral and spares DDP the
+        # per-step graph traversal; gradients are reduced in place in the buckets
+        for p in model.encoder_q.decode_head.conv_seg.parameters():
+            p.requires_grad_(False)
+        net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], find_unused_parameters=False,
+                                                        broadcast_buffers=False, gradient_as_bucket_view=True)
     opt = torch.optim.SGD(model.encoder_q.parameters(), 1e-3, momentum=0.9, weight_decay=1e-4)
 
     B = args.batch

@@ -68,6 +68,16 @@ def _worker(rank, port, out_dir):
     dist.all_gather(perms, idx_unshuffle)
     res["same_perm"] = all(torch.equal(p, perms[0]) for p in perms)
     res["roundtrip"] = torch.equal(model._batch_unshuffle_ddp(y * 3.0, idx_unshuffle), x * 3.0)
+    # the all-to-all row exchange lands exactly the rows the reference's all-gather + index would
+    ok = True
+    for t in range(4):
+        big = torch.randn(6, 3, 8, 8, device=dev) + rank
+        all_big = [torch.empty_like(big) for _ in range(WORLD)]
+        dist.all_gather(all_big, big)
+        yb, iu = model._batch_shuffle_ddp(big)
+        ref, _ = O.batch_shuffle(torch.cat(all_big).cpu(), torch.argsort(iu).cpu(), rank, WORLD)
+        ok = ok and torch.equal(yb.cpu(), ref) and torch.equal(model._batch_unshuffle_ddp(yb, iu), big)
+    res["shuffle_vs_oracle"] = ok
     # ---- two DDP steps: finite loss, gradients all-reduced, queues stay identical across ranks
     ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[rank], broadcast_buffers=False)
     opt = torch.optim.SGD(model.encoder_q.parameters(), 0.01)
@@ -99,6 +109,6 @@ def test_world2_nccl_enqueue_shuffle_ddp(tmp_path):
     mp.spawn(_worker, args=(_free_port(), str(tmp_path)), nprocs=WORLD, join=True)
     for r in range(WORLD):
         res = torch.load(tmp_path / f"r{r}.pt")
-        for k in ("queue_ok", "ptr_ok", "same_perm", "roundtrip", "finite", "queues_equal", "weights_equal"):
+        for k in ("queue_ok", "ptr_ok", "same_perm", "roundtrip", "shuffle_vs_oracle", "finite", "queues_equal", "weights_equal"):
             assert res[k], (r, k)
         assert res["ptr_after"] == (5 * 32 + 2 * 8) % 72
