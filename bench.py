@@ -378,10 +378,29 @@ def own_arm(args):
     launches = ops.LAUNCHES - launches0
     ksum = kt.summary()
 
+    # e2e: every step's inputs come from pinned host memory (77 MB per step) and the loss is read back.
+    # As in a pin_memory data loader, the copy of step i+1 is issued on a copy stream before step i's loss
+    # is waited for, so it overlaps the compute; each timed step still contains exactly one full H2D copy.
+    copy_stream = torch.cuda.Stream(device=dev)
+    pending = {}
+
+    def prefetch(i):
+        with torch.cuda.stream(copy_stream):
+            b = {k: v.to(dev, non_blocking=True) for k, v in host[i % 2].items()}
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        pending["next"] = (b, ev)
+
     def e2e_step(i):
-        batch = {k: v.to(dev, non_blocking=True) for k, v in host[i % 2].items()}
+        batch, ev = pending.pop("next")
+        cur = torch.cuda.current_stream()
+        cur.wait_event(ev)
+        for t in batch.values():
+            t.record_stream(cur)
+        prefetch(i + 1)
         return step(batch).item()           # device -> host read of the step's loss
 
+    prefetch(0)
     for i in range(2):
         e2e_step(i)
     ms_e2e = timed(e2e_step, args.steps)

@@ -163,6 +163,11 @@ class MODEL(nn.Module):
     Extra keyword-only arguments (not in the reference):
       encoder_factory : callable returning one segmentor; replaces `build_segmentor(cfg.model)`
                         (mmseg/mmcv are not installable here).  Called twice (q, k).
+      track_accuracy  : also evaluate the loss-neutral `acc_ins` / `acc_seg` meters (builder.py:1441-1448)
+                        each step.  They need the arg-max over all P x P logits and the top-1 over the
+                        65537 global logits, which the fused kernels never materialise, so this opt-in
+                        branch materialises them with torch ops (the slow "stats"
+                        branch); off by default, the meters then read NaN.
       output_stride   : skip the reference's CPU probe forward (builder.py:392-397) and use
                         this value.  When None the probe runs exactly as in the reference,
                         including its side effect on encoder_q's BN running statistics.
@@ -175,7 +180,7 @@ class MODEL(nn.Module):
                  backbone_type=BackboneType.DEEPLABV3, mapping_type=MappingType.CP2,
                  dense_logits_temp=1, unet_truncated_dec_blocks=2, use_predictor=False,
                  use_avgpool_global=False, use_symmetrical_loss=False, lmbd_coordinate=0,
-                 device=None, *, encoder_factory=None, output_stride=None):
+                 device=None, *, encoder_factory=None, output_stride=None, track_accuracy=False):
         super().__init__()
         self.queue_len = K
         self.momentum = m
@@ -262,6 +267,26 @@ class MODEL(nn.Module):
         self.correlation_ious = []
         self.masked_correlation_ious = []
         self._ema_plan = None
+        self.track_accuracy = bool(track_accuracy)
+
+    @torch.no_grad()
+    def _accuracy_stats(self, q, k, mask_a, mask_b, q_pos, k_pos):
+        """builder.py:1441-1448 (+ :1395-1418 for the logits) with torch ops; opt-in, off the hot path."""
+        n = q.shape[0]
+        qh = F.normalize(q.detach().float().flatten(2), dim=1)
+        kh = F.normalize(k.detach().float().flatten(2), dim=1)
+        P = qh.shape[2]
+        idx = torch.einsum("ncx,ncy->nxy", qh, kh).reshape(n, -1).argmax(dim=1)
+        ar = torch.arange(n, device=q.device)
+        acc_seg = (mask_a[ar, idx // P] * mask_b[ar, idx % P]).float().mean() * 100.0
+        parts = [(q_pos * k_pos).sum(dim=1, keepdim=True), q_pos @ self.queue]
+        if self.include_background:
+            q_neg = F.normalize(torch.einsum("ncx,nx->nc", qh, 1.0 - mask_a), dim=1)
+            k_neg = F.normalize(torch.einsum("ncx,nx->nc", kh, 1.0 - mask_b), dim=1)
+            parts += [(q_pos * q_neg).sum(dim=1, keepdim=True), (q_pos * k_neg).sum(dim=1, keepdim=True)]
+        logits = torch.cat(parts, dim=1)
+        acc1 = self._accuracy(logits, torch.zeros(n, dtype=torch.long, device=q.device), topk=(1,))[0]
+        return acc1.reshape(()), acc_seg
 
     # ------------------------------------------------------------------ K4
     @torch.no_grad()
@@ -375,6 +400,8 @@ class MODEL(nn.Module):
         loss, loss_ins, loss_dense, k_pos, q_pos, stats = ops.cp2_loss(
             q, k, mask_a, mask_b, self.queue, self.temp_global, self.temp_local, self.lmbd_dense_loss,
             self.include_background)
+        if self.track_accuracy:                                # uses the queue BEFORE this step's enqueue
+            stats["acc_ins"], stats["acc_seg"] = self._accuracy_stats(q, k, mask_a, mask_b, q_pos, k_pos)
         self._dequeue_and_enqueue(k_pos)                       # builder.py:1426
 
         if new_epoch and self.rank == 0:

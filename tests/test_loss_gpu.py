@@ -123,7 +123,7 @@ def test_model_two_steps_against_reference_golden(monkeypatch):
     B, H, C, K = int(g["B"]), int(g["H"]), int(g["C"]), int(g["K"])
     dev = torch.device("cuda:0")
     model = MODEL(None, rank=1, dim=C, K=K, dense_logits_temp=0.2, device=dev,
-                  encoder_factory=lambda: _Patch(C, 16), output_stride=16).to(dev)
+                  encoder_factory=lambda: _Patch(C, 16), output_stride=16, track_accuracy=True).to(dev)
     with torch.no_grad():
         model.queue.copy_(T(g["queue0"]))
         for name, p in model.encoder_q.named_parameters():
@@ -142,6 +142,9 @@ def test_model_two_steps_against_reference_golden(monkeypatch):
         np.testing.assert_allclose(model.loss_i.val, g[f"s{s}.loss_ins"], rtol=LOSS_RTOL)
         np.testing.assert_allclose(model.loss_d.val, g[f"s{s}.loss_dense"], rtol=LOSS_RTOL)
         assert int(model.queue_ptr.item()) == int(g[f"s{s}.queue_ptr"][0])
+        # opt-in accuracy meters (builder.py:1441-1448): values of the reference's own meters
+        np.testing.assert_allclose(float(model.acc_ins.val), g[f"s{s}.acc_ins"], atol=1e-3)
+        np.testing.assert_allclose(float(model.acc_seg.val), g[f"s{s}.acc_seg"], atol=1e-3)
         # queue contents: the keys come from a cuDNN conv here vs a CPU conv in the golden run
         np.testing.assert_allclose(model.queue.cpu().numpy(), g[f"s{s}.queue"], rtol=0, atol=2e-5)
         for name, p in model.encoder_k.named_parameters():
