@@ -138,6 +138,14 @@ def synth_batch(batch, seed, pinned=False):
             top = int(torch.randint(0, IMG - rh + 1, (1,), generator=g))
             left = int(torch.randint(0, IMG - rw + 1, (1,), generator=g))
             out[name][i, :, top:top + rh, left:left + rw] = 0.0
+    # pixel / region id maps (main.py:616-628 passes them on every step; CP2 mapping: region ids = pixel ids,
+    # loader.py:84-85): two random crops of one id canvas per image, int64 [B,H,W]
+    pad = 32
+    canvas = torch.arange(1, (IMG + pad) * (IMG + pad) + 1, dtype=torch.int64).reshape(IMG + pad, IMG + pad)
+    off = torch.randint(0, pad + 1, (batch, 4), generator=g)
+    for name, (cy, cx) in (("pixel_ids_a", (0, 1)), ("pixel_ids_b", (2, 3))):
+        out[name] = torch.stack([canvas[int(o[cy]):int(o[cy]) + IMG, int(o[cx]):int(o[cx]) + IMG] for o in off])
+    out["region_ids_a"], out["region_ids_b"] = out["pixel_ids_a"].clone(), out["pixel_ids_b"].clone()
     if pinned:
         out = {k: v.pin_memory() for k, v in out.items()}
     return out
@@ -160,12 +168,12 @@ def cpu_baseline_leg(budget_s=20.0):
     batch = 8
     port, b, threads = _cpu_port(batch)
     t0 = time.perf_counter()
-    port.step(b["img_a"], b["img_b"], b["bg0"], b["bg1"])
+    port.step(**b)
     warm = time.perf_counter() - t0
     n = max(1, min(5, int(budget_s / max(warm, 1e-3))))
     t0 = time.perf_counter()
     for _ in range(n):
-        port.step(b["img_a"], b["img_b"], b["bg0"], b["bg1"])
+        port.step(**b)
     dt = (time.perf_counter() - t0) / n
     return {"value": batch / dt, "unit": UNIT, "cores": threads, "kind": "port",
             "sample": f"{n} timed steps (after 1 warm-up) of the full pre-training step at batch {batch} "
@@ -182,18 +190,18 @@ def reference_arm(args):
     # calibrate at batch 2 (BatchNorm needs > 1 sample), then size each step's sample so the run ends in minutes
     port, b2, threads = _cpu_port(2)
     t0 = time.perf_counter()
-    port.step(b2["img_a"], b2["img_b"], b2["bg0"], b2["bg1"])
-    port.step(b2["img_a"], b2["img_b"], b2["bg0"], b2["bg1"])
+    port.step(**b2)
+    port.step(**b2)
     per_img = (time.perf_counter() - t0) / 4.0
     budget = 150.0
     batch = int(budget / max(total, 1) / max(per_img, 1e-4))
     batch = max(2, min(args.batch, batch))
     b = synth_batch(batch, seed=1234)
     for _ in range(args.warmup):
-        port.step(b["img_a"], b["img_b"], b["bg0"], b["bg1"])
+        port.step(**b)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        port.step(b["img_a"], b["img_b"], b["bg0"], b["bg1"])
+        port.step(**b)
     dt = (time.perf_counter() - t0) / max(args.steps, 1)
     value = batch / dt
     sample = (f"each step = the full pre-training step on {batch} of the {args.batch} images of one GPU's batch "
@@ -282,6 +290,7 @@ def algorithmic_work(batch, n_params, world):
         "cp2_global_nce": ("hbm", 4 * C * QUEUE + 8 * batch * C),
         "cp2_ema": ("hbm", 12 * n_params),
         "cp2_enqueue": ("hbm", 2 * world * batch * C * 4),
+        "cp2_id_iou": ("hbm", 2 * batch * P * (8 + 4)),       # latency-bound: 2P ids + masks per image
     }
 
 

@@ -25,6 +25,7 @@ SIGNATURES = {
     "cp2_global_nce": (c_int, [c_void_p] * 5 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_ema": (c_int, [c_void_p] * 5 + [c_int, c_float, c_float, c_void_p]),
     "cp2_enqueue": (c_int, [c_void_p] * 3 + [c_int] * 3 + [c_void_p]),
+    "cp2_id_iou": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_void_p]),
     "cp2_mirror_partials": (c_int, [c_int, c_int64]),
     "cp2_mirror_loss": (c_int, [c_void_p] * 8 + [c_float, c_float, c_int64, c_int, c_int, c_int64, c_void_p]),
     "cp2_mirror_up_partials": (c_int, [c_int] * 3),
@@ -39,7 +40,7 @@ DEBUG_SIGNATURES = {
 }
 
 EMA_CHUNK = 4096  # CP2_EMA_CHUNK
-ABI_VERSION = 3  # CP2_ABI_VERSION
+ABI_VERSION = 4  # CP2_ABI_VERSION
 
 _lib = None
 

@@ -264,8 +264,7 @@ class MODEL(nn.Module):
         self.acc_seg = AverageMeter("Acc_seg", ":6.2f")
         self.cross_image_variance_source = AverageMeter("Cross_Image_Variance_Source", ":6.2f")
         self.cross_image_variance_target = AverageMeter("Cross_Image_Variance_Target", ":6.2f")
-        self.correlation_ious = []
-        self.masked_correlation_ious = []
+        self._iou_host, self._iou_dev = [[], []], [[], []]      # (all pixels, masked): lists + pending device chunks
         self._ema_plan = None
         self.track_accuracy = bool(track_accuracy)
 
@@ -287,6 +286,21 @@ class MODEL(nn.Module):
         logits = torch.cat(parts, dim=1)
         acc1 = self._accuracy(logits, torch.zeros(n, dtype=torch.long, device=q.device), topk=(1,))[0]
         return acc1.reshape(()), acc_seg
+
+    # ----------------------------------------------------------- a4 (metrics)
+    # builder.py:1252-1257 extends two python lists with per-image IoUs every step, through a .cpu() sync.
+    # Here the per-step [B] results stay on the device and are only read back when the list is looked at
+    # (the reference does so once per epoch, builder.py:1455-1486).
+    def _iou_list(self, which):
+        if self._iou_dev[which]:
+            self._iou_host[which].extend(torch.cat(self._iou_dev[which]).cpu().numpy().tolist())
+            self._iou_dev[which] = []
+        return self._iou_host[which]
+
+    correlation_ious = property(lambda self: self._iou_list(0),
+                                lambda self, v: (self._iou_dev.__setitem__(0, []), self._iou_host.__setitem__(0, list(v)))[0])
+    masked_correlation_ious = property(lambda self: self._iou_list(1),
+                                       lambda self, v: (self._iou_dev.__setitem__(1, []), self._iou_host.__setitem__(1, list(v)))[0])
 
     # ------------------------------------------------------------------ K4
     @torch.no_grad()
@@ -375,8 +389,9 @@ class MODEL(nn.Module):
                     pixel_ids_a=None, pixel_ids_b=None, region_ids_a=None, region_ids_b=None):
         """builder.py:1124-1606 for MappingType.CP2 / NegativeType.NONE.
 
-        The pixel / region id maps only feed loss-neutral bookkeeping in this mode
-        (corr_weights is all ones, builder.py:329-332, 1238-1243) and are ignored.
+        The pixel / region id maps only feed loss-neutral bookkeeping in this mode (corr_weights is
+        all ones, builder.py:329-332, 1238-1243): the region-id IoUs the reference records per step
+        (builder.py:1252-1257) come from `cp2_id_iou`; the pixel-id maps are not needed.
         """
         os_ = self.output_stride
         keep = bool(visualize) and self.rank == 0
@@ -386,6 +401,11 @@ class MODEL(nn.Module):
         if keep:
             self.last_visualization = {"img_a": img_a, "img_b": img_b, "mask_a": full_a, "mask_b": full_b}
         n = img_a.shape[0]
+        if region_ids_a is not None and region_ids_b is not None:
+            # a2 + a4: builder.py:1211-1217, 1252-1257 (the region-id IoUs are the ones the reference keeps)
+            iou, iou_m = ops.id_iou(region_ids_a, region_ids_b, mask_a, mask_b, os_)
+            self._iou_dev[0].append(iou)
+            self._iou_dev[1].append(iou_m)
         mask_a = mask_a.reshape(n, -1)
         mask_b = mask_b.reshape(n, -1)
 

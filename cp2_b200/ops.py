@@ -318,6 +318,23 @@ def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_
     return loss, loss_ins, loss_dense, k_pos, q_pos, stats
 
 
+# ------------------------------------------------------------- a2 + a4
+@torch.no_grad()
+def id_iou(ids_a, ids_b, mask_a_ds, mask_b_ds, output_stride):
+    """tools/correlation_mapping.py:103-138 on the `[OS/2::OS]` subsample of two full-resolution id maps
+    (builder.py:1165-1186, 1203-1217).  ids [B,H,W] int64, masks [B,hs,ws] f32 -> (iou [B], iou_masked [B])."""
+    _need_cuda(ids_a, ids_b, mask_a_ds, mask_b_ds)
+    ids_a, ids_b = _labels_i64(ids_a), _labels_i64(ids_b)
+    mask_a_ds, mask_b_ds = _f32c(mask_a_ds), _f32c(mask_b_ds)
+    B, H, W = ids_a.shape
+    assert ids_b.shape == ids_a.shape and mask_a_ds.shape[0] == B and mask_a_ds.shape == mask_b_ds.shape
+    iou = torch.empty((B,), device=ids_a.device, dtype=torch.float32)
+    iou_m = torch.empty((B,), device=ids_a.device, dtype=torch.float32)
+    _call("cp2_id_iou", 1, _lib.load().cp2_id_iou, _ptr(ids_a), _ptr(ids_b), _ptr(mask_a_ds), _ptr(mask_b_ds),
+          _ptr(iou), _ptr(iou_m), B, H, W, int(output_stride), _stream())
+    return iou, iou_m
+
+
 # ------------------------------------------------ mirror variant (a13 / f5)
 def _labels_i64(labels):
     if labels.dtype != torch.int64:

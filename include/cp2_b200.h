@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CP2_ABI_VERSION 3
+#define CP2_ABI_VERSION 4
 
 #define CP2_OK 0
 #define CP2_E_INVALID (-1)      /* bad shape / null pointer / unsupported dim          */
@@ -127,6 +127,19 @@ int cp2_ema(const float *const *q_ptrs, float *const *k_ptrs, const int64_t *num
  * Bit-exact with the reference (n <= K). */
 int cp2_enqueue(const float *keys_all, float *queue, int64_t *queue_ptr, int n, int C, int K,
                 void *stream);
+
+/* a2 + a4 — sub-sampled id maps and their (masked) correlation IoU.
+ * Replaces builder.py:1165-1186 (the `[OS/2::OS]` subsample of the id maps) and
+ * tools/correlation_mapping.py:103-138 get_masked_iou (a python loop of torch.unique per image
+ * followed by .cpu(), builder.py:1252-1257), for one pair of id maps:
+ *   values   = (id + 1) of both sub-sampled maps, 0 where the sub-sampled mask is 0
+ *   iou[n]   = #distinct values occurring more than once / #distinct values         (all pixels)
+ *   iou_masked[n] likewise over the unmasked pixels only; 0/0 -> NaN (the reference raises)
+ *   ids_a, ids_b : [B,H,W] int64 (full resolution) ; mask_a_ds, mask_b_ds : [B,hs,ws] f32 of K1
+ *   iou, iou_masked : [B] f32.  Bit-exact with the reference. */
+int cp2_id_iou(const int64_t *ids_a, const int64_t *ids_b, const float *mask_a_ds,
+               const float *mask_b_ds, float *iou, float *iou_masked, int B, int H, int W, int os,
+               void *stream);
 
 /* a13/f5 — MirrorModule loss (networks/mirror_network.py:40-63): class CE on both logit maps +
  * the "mirror" output-consistency term, forward and backward in one pass.

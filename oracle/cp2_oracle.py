@@ -353,15 +353,27 @@ class CP2StepPort:
             pk.requires_grad = False
         self.queue = F.normalize(torch.randn(dim, K), dim=0)   # builder.py:476-477
         self.ptr = 0
+        self.correlation_ious, self.masked_correlation_ious = [], []
         self.m, self.tg, self.tl, self.lmbd, self.os = m, temp_global, temp_local, lmbd_dense, output_stride
         self.opt = torch.optim.SGD(self.encoder_q.parameters(), lr, momentum=0.9, weight_decay=1e-4)  # main.py:467-471
 
-    def step(self, img_a, img_b, bg0, bg1):
+    def step(self, img_a, img_b, bg0, bg1, pixel_ids_a=None, pixel_ids_b=None, region_ids_a=None,
+             region_ids_b=None):
         img_a, mask_a = composite(img_a, bg0)
         img_b, mask_b = composite(img_b, bg1)
         n = img_a.shape[0]
-        mask_a = stride_subsample(mask_a, self.os).reshape(n, -1)
-        mask_b = stride_subsample(mask_b, self.os).reshape(n, -1)
+        mask_a = stride_subsample(mask_a, self.os)
+        mask_b = stride_subsample(mask_b, self.os)
+        if region_ids_a is not None:
+            # builder.py:1165-1186, 1203-1217, 1252-1257: both correlation maps and the region-id IoUs
+            pa, pb = stride_subsample(pixel_ids_a, self.os), stride_subsample(pixel_ids_b, self.os)
+            ra, rb = stride_subsample(region_ids_a, self.os), stride_subsample(region_ids_b, self.os)
+            masked_correlation(pa, pb, mask_a, mask_b)
+            reg = masked_correlation(ra, rb, mask_a, mask_b)
+            self.correlation_ious.extend(reg["iou"].tolist())
+            self.masked_correlation_ious.extend(reg["iou_masked"].tolist())
+        mask_a = mask_a.reshape(n, -1)
+        mask_b = mask_b.reshape(n, -1)
         q = self.encoder_q(img_a)
         with torch.no_grad():
             pq = [p.data for p in self.encoder_q.parameters()]

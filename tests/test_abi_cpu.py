@@ -39,7 +39,7 @@ def test_every_declared_symbol_is_exported(lib):
 
 def test_abi_version_and_host_helpers(lib):
     from cp2_b200 import _lib
-    assert lib.cp2_abi_version() == _lib.ABI_VERSION == 3
+    assert lib.cp2_abi_version() == _lib.ABI_VERSION == 4
     assert lib.cp2_mirror_up_partials(2, 512, 512) == 2 * 32 * 4 and lib.cp2_mirror_partials(0, 16) == 1
     assert lib.cp2_prep_tiles(196) == 7 and lib.cp2_prep_tiles(32) == 1
     assert lib.cp2_global_scratch_floats(0, 128) == 0
@@ -62,6 +62,7 @@ def test_invalid_arguments_are_rejected_before_any_launch(lib):
     assert b"Cls=9" in lib.cp2_last_error()
     assert lib.cp2_mirror_loss(1, 1, 1, 1, 1, None, None, None, 0.01, 0.5, 0, 0, 2, 64, None) == -1   # empty mean
     assert lib.cp2_mirror_loss_upsampled(1, 1, None, 1, 1, None, None, 0.01, 0.5, 0, 2, 2, 4, 4, 64, 64, None) == -1
+    assert lib.cp2_id_iou(1, 1, 1, 1, 1, 1, 2, 8, 8, 16, None) == -1          # empty sub-sampled map
     # empty work is a no-op success, as the reference's ops are on empty tensors
     assert lib.cp2_composite(None, None, None, None, None, 0, 8, 8, 16, None) == 0
     assert lib.cp2_enqueue(None, None, None, 0, 128, 16, None) == 0

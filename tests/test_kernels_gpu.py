@@ -349,3 +349,41 @@ def test_global_nce_vs_simt(ops):
                                            B, C, K, torch.cuda.current_stream().cuda_stream), "simt")
     torch.cuda.synchronize()
     assert torch.allclose(z, z2, rtol=2e-3) and rel_l2(gg, g2) < 5e-3
+
+
+# ------------------------------------------------------------------- a2 + a4
+def test_id_iou_reference_cases(ops):
+    """The reference's own unit-test constants (tests/test_correlation_mapping.py:73-74, 126-127) and the
+    golden outputs of get_masked_correlation_map recorded by oracle/gen_golden.gen_corr; output stride 1."""
+    g = load_golden("corr.npz")
+    for p, iou, ioum in (("u", 12 / 38, 1 / 3), ("s", 4 / 7, 2 / 3)):
+        a, b = T(g[f"{p}_map_a"]).long(), T(g[f"{p}_map_b"]).long()
+        r_iou, r_ioum = ops.id_iou(dev(a), dev(b), dev(T(g[f"{p}_mask_a"])), dev(T(g[f"{p}_mask_b"])), 1)
+        assert torch.equal(r_iou.cpu(), T(g[f"{p}_iou"]).reshape(-1))
+        assert torch.equal(r_ioum.cpu(), T(g[f"{p}_iou_masked"]).reshape(-1))
+        assert torch.all(r_iou.cpu() == torch.tensor(iou, dtype=torch.float32))
+        assert torch.all(r_ioum.cpu() == torch.tensor(ioum, dtype=torch.float32))
+
+
+@pytest.mark.parametrize("B,H,W,os_", [(4, 224, 224, 16), (3, 64, 48, 8), (2, 30, 45, 4), (2, 112, 112, 2)])
+def test_id_iou_vs_oracle(ops, B, H, W, os_):
+    """Two crops of one id canvas (pixel ids) and a coarse region-id map with repeated and zero ids,
+    sub-sampled at [OS/2::OS] inside the kernel (builder.py:1165-1186); bit-exact."""
+    gen = torch.Generator().manual_seed(B + H)
+    canvas = torch.arange(1, (H + 9) * (W + 7) + 1).reshape(H + 9, W + 7)
+    offs = torch.randint(0, 7, (B, 4), generator=gen)
+    ids_a = torch.stack([canvas[int(o[0]):int(o[0]) + H, int(o[1]):int(o[1]) + W] for o in offs])
+    ids_b = torch.stack([canvas[int(o[2]):int(o[2]) + H, int(o[3]):int(o[3]) + W] for o in offs])
+    for kind in ("pixel", "region"):
+        if kind == "region":
+            ids_a, ids_b = (ids_a // 97) % 5, (ids_b // 97) % 5        # few distinct ids, zeros included
+        mask_a = (torch.rand(B, H, W, generator=gen) < 0.6).float()
+        mask_b = (torch.rand(B, H, W, generator=gen) < 0.6).float()
+        ma, mb = O.stride_subsample(mask_a, os_), O.stride_subsample(mask_b, os_)
+        ma[:, 0, 0] = 1.0
+        mb[:, 0, 0] = 1.0                                             # at least one unmasked entry per map
+        sa, sb = O.stride_subsample(ids_a, os_), O.stride_subsample(ids_b, os_)
+        ref = O.masked_correlation(sa, sb, ma, mb)
+        iou, ioum = ops.id_iou(dev(ids_a), dev(ids_b), dev(ma), dev(mb), os_)
+        assert torch.equal(iou.cpu(), ref["iou"]), kind
+        assert torch.equal(ioum.cpu(), ref["iou_masked"]), kind

@@ -157,3 +157,9 @@ def test_model_two_steps_against_reference_golden(monkeypatch):
             assert rel_l2(p.grad, want) < GRAD_REL_L2, (name, rel_l2(p.grad, want))
         opt.step()
     assert model.loss_o.count == 2 * B and abs(model.loss_o.val - float(g["s1.loss"])) < 1e-3
+    # region-id IoUs recorded per step (builder.py:1252-1257): identical id maps in both views -> IoU 1,
+    # one entry per image and step; reset_metrics clears them
+    assert len(model.correlation_ious) == 2 * B and len(model.masked_correlation_ious) == 2 * B
+    assert all(v == 1.0 for v in model.correlation_ious)
+    model.reset_metrics()
+    assert model.correlation_ious == [] and model.masked_correlation_ious == []
