@@ -290,6 +290,7 @@ def algorithmic_work(batch, n_params, world):
         "cp2_global_nce": ("hbm", 4 * C * QUEUE + 8 * batch * C),
         "cp2_ema": ("hbm", 12 * n_params),
         "cp2_enqueue": ("hbm", 2 * world * batch * C * 4),
+        "cp2_loss_combine": ("hbm", batch * (9 * C + 2 * P) * 4),   # latency-bound: [B,C] / [B,P] operands once
         "cp2_id_iou": ("hbm", 2 * batch * P * (8 + 4)),       # latency-bound: 2P ids + masks per image
     }
 

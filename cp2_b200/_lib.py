@@ -17,10 +17,11 @@ SIGNATURES = {
     "cp2_last_error": (c_char_p, []),
     "cp2_composite": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "cp2_prep_tiles": (c_int, [c_int]),
-    "cp2_prep_features": (c_int, [c_void_p] * 8 + [c_int] * 3 + [c_void_p]),
+    "cp2_prep_features": (c_int, [c_void_p] * 11 + [c_int] * 3 + [c_void_p]),
     "cp2_dense_lse": (c_int, [c_void_p] * 4 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_dense_pad": (c_int, [c_int]),
-    "cp2_dense_grad": (c_int, [c_void_p] * 12 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_dense_grad": (c_int, [c_void_p] * 13 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_loss_combine": (c_int, [c_void_p] * 18 + [c_float] * 3 + [c_int] * 3 + [c_void_p]),
     "cp2_global_scratch_floats": (c_int64, [c_int, c_int]),
     "cp2_global_nce": (c_int, [c_void_p] * 5 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_ema": (c_int, [c_void_p] * 5 + [c_int, c_float, c_float, c_void_p]),
@@ -40,7 +41,7 @@ DEBUG_SIGNATURES = {
 }
 
 EMA_CHUNK = 4096  # CP2_EMA_CHUNK
-ABI_VERSION = 4  # CP2_ABI_VERSION
+ABI_VERSION = 5  # CP2_ABI_VERSION
 
 _lib = None
 

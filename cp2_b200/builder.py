@@ -432,8 +432,8 @@ class MODEL(nn.Module):
             self.loss_d.update(loss_dense, n)
             self.acc_ins.update(stats["acc_ins"], n)
             self.acc_seg.update(stats["acc_seg"], n)
-            self.cross_image_variance_source.update(q_pos.std(0).mean(), n)
-            self.cross_image_variance_target.update(k_pos.std(0).mean(), n)
+            self.cross_image_variance_source.update(stats["std_q_pos"], n)    # q_pos.std(0).mean()
+            self.cross_image_variance_target.update(stats["std_k_pos"], n)
         return loss
 
     def on_train_epoch_end(self, step):                        # builder.py:1608

@@ -1,0 +1,167 @@
+// a5/a7/a12 glue — everything of the CP2 loss that lives on [B,C] / [B] tensors, in two launches:
+// the global InfoNCE's positive (and optional background) logits and its cross-entropy
+// (reference builder.py:1395, 1414-1418, 1428), the rank-1 positive term and the masked mean of the
+// dense loss (builder.py:1431-1437), the loss combination (builder.py:1439), and the per-image
+// coefficient vectors the one-kernel backward (cp2_dense_grad) consumes: the global loss's gradient
+// pushed through the outer F.normalize of the pooled query vectors (builder.py:1264,1268), plus the
+// dense loss's rank-1 term.  The [B,P,P] work is done by cp2_dense_lse and the queue pass by
+// cp2_global_nce; this kernel only combines their [B,P] / [B,C] results, replacing ~40 tiny ATen
+// launches of the eager formulation.
+#include "common.cuh"
+
+namespace {
+
+constexpr float kEps = 1e-12f;     // F.normalize eps
+
+template <int N>
+__device__ __forceinline__ void block_sum(float (&v)[N], float *red /* [N][4] */) {
+#pragma unroll
+  for (int k = 0; k < N; ++k)
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v[k] += __shfl_down_sync(0xffffffffu, v[k], off);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  __syncthreads();                                   // red may still be read from a previous round
+  if (lane == 0)
+#pragma unroll
+    for (int k = 0; k < N; ++k) red[k * 4 + wid] = v[k];
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < N; ++k) v[k] = red[k * 4] + red[k * 4 + 1] + red[k * 4 + 2] + red[k * 4 + 3];
+}
+
+// One CTA (128 threads) per image.
+__global__ void __launch_bounds__(128)
+loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k_pos,
+                    const float *__restrict__ q_neg, const float *__restrict__ k_neg,
+                    const float *__restrict__ sq, const float *__restrict__ sk,
+                    const float *__restrict__ norms_q, const float *__restrict__ z,
+                    const float *__restrict__ G, const float *__restrict__ lse,
+                    const int *__restrict__ key_count, const float *__restrict__ mask_a,
+                    float *__restrict__ terms, float *__restrict__ l_pos_out, float *__restrict__ alpha,
+                    float *__restrict__ v1, float *__restrict__ v2, float inv_tg, float inv_tl, float lmbd,
+                    int B, int C, int P) {
+  __shared__ float red[6 * 4];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const bool bg = q_neg != nullptr;
+  const long long row = (long long)b * C;
+  const int cnt = min(max(key_count[b], 0), P);
+  // ---- round 1: the dot products and the [P]-sized sums
+  float r1[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};     // l_pos, q_pos.q_neg, q_pos.k_neg, sq.sk, A, sum lse
+  for (int c = tid; c < C; c += 128) {
+    const float qp = q_pos[row + c];
+    r1[0] = fmaf(qp, k_pos[row + c], r1[0]);
+    if (bg) { r1[1] = fmaf(qp, q_neg[row + c], r1[1]); r1[2] = fmaf(qp, k_neg[row + c], r1[2]); }
+    r1[3] = fmaf(sq[row + c], sk[row + c], r1[3]);
+  }
+  for (int x = tid; x < P; x += 128) {
+    r1[4] += mask_a[(long long)b * P + x];
+    if (x < cnt) r1[5] += lse[(long long)b * P + x];   // compacted keys: rows < cnt are the foreground ones
+  }
+  block_sum<6>(r1, red);
+  const float l_pos = r1[0], A = r1[4], Bm = (float)cnt;
+  // shift 1 as in cp2_global_nce: |l| <= 1 for unit vectors
+  const float e_pos = expf((l_pos - 1.f) * inv_tg);
+  float Z = z[b] + e_pos, e_nq = 0.f, e_nk = 0.f;
+  if (bg) {
+    e_nq = expf((r1[1] - 1.f) * inv_tg);
+    e_nk = expf((r1[2] - 1.f) * inv_tg);
+    Z += e_nq + e_nk;
+  }
+  const float rZ = 1.f / Z, invB = 1.f / (float)B;
+  const float dense_scale = inv_tl / (A * Bm);       // 1 / (tau_d * A * Bm); 0/0 -> NaN as the reference
+  // ---- round 2: projections of the outer-normalize backward
+  const float nq = norms_q[2 * b], nnq = norms_q[2 * b + 1];
+  float r2[2] = {0.f, 0.f};
+  for (int c = tid; c < C; c += 128) {
+    const float qp = q_pos[row + c], kp = k_pos[row + c];
+    float num = fmaf(e_pos, kp, G[row + c]);
+    if (bg) num = fmaf(e_nq, q_neg[row + c], fmaf(e_nk, k_neg[row + c], num));
+    const float dqpos = (num * rZ - kp) * invB * inv_tg;
+    r2[0] = fmaf(qp, dqpos, r2[0]);
+    if (bg) r2[1] = fmaf(q_neg[row + c], e_nq * rZ * qp * invB * inv_tg, r2[1]);
+  }
+  block_sum<2>(r2, red);
+  const float dq_d = 1.f / fmaxf(nq, kEps), dn_d = 1.f / fmaxf(nnq, kEps);
+  for (int c = tid; c < C; c += 128) {
+    const float qp = q_pos[row + c], kp = k_pos[row + c];
+    float num = fmaf(e_pos, kp, G[row + c]);
+    if (bg) num = fmaf(e_nq, q_neg[row + c], fmaf(e_nk, k_neg[row + c], num));
+    const float dqpos = (num * rZ - kp) * invB * inv_tg;
+    const float proj = nq > kEps ? dqpos - qp * r2[0] : dqpos;
+    v1[row + c] = proj * dq_d - lmbd * invB * sk[row + c] * dense_scale;
+    if (bg) {
+      const float qn = q_neg[row + c];
+      const float dqneg = e_nq * rZ * qp * invB * inv_tg;
+      v2[row + c] = (nnq > kEps ? dqneg - qn * r2[1] : dqneg) * dn_d;
+    }
+  }
+  if (tid == 0) {
+    terms[2 * b] = logf(Z) + (1.f - l_pos) * inv_tg;                 // -log softmax at the positive
+    terms[2 * b + 1] = r1[5] / Bm - r1[3] * dense_scale;               // loss_dense of this image
+    l_pos_out[b] = l_pos;
+    alpha[b] = lmbd * invB * inv_tl / Bm;
+  }
+}
+
+// out = {loss, loss_ins, loss_dense, mean_c std_b(q_pos), mean_c std_b(k_pos)}; fixed summation order.
+__global__ void __launch_bounds__(256)
+loss_finalize_kernel(const float *__restrict__ terms, const float *__restrict__ q_pos,
+                     const float *__restrict__ k_pos, float *__restrict__ out, float lmbd, int B, int C) {
+  __shared__ float red[2 * 4 * 2];
+  float sd[2] = {0.f, 0.f};
+  for (int c = threadIdx.x; c < C; c += 256) {
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+      const float *src = w == 0 ? q_pos : k_pos;
+      float m = 0.f;
+      for (int b = 0; b < B; ++b) m += src[(long long)b * C + c];
+      m /= (float)B;
+      float var = 0.f;
+      for (int b = 0; b < B; ++b) { const float d = src[(long long)b * C + c] - m; var = fmaf(d, d, var); }
+      sd[w] += sqrtf(var / (float)(B - 1));                             // torch.std: unbiased; B = 1 -> NaN
+    }
+  }
+#pragma unroll
+  for (int w = 0; w < 2; ++w)
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) sd[w] += __shfl_down_sync(0xffffffffu, sd[w], off);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) { red[wid] = sd[0]; red[8 + wid] = sd[1]; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, d = 0.f, s0 = 0.f, s1 = 0.f;
+    for (int b = 0; b < B; ++b) { a += terms[2 * b]; d += terms[2 * b + 1]; }
+    for (int w = 0; w < 8; ++w) { s0 += red[w]; s1 += red[8 + w]; }
+    a /= (float)B;
+    d /= (float)B;
+    out[0] = a + d * lmbd;
+    out[1] = a;
+    out[2] = d;
+    out[3] = s0 / (float)C;
+    out[4] = s1 / (float)C;
+  }
+}
+
+}  // namespace
+
+extern "C" int cp2_loss_combine(const float *q_pos, const float *k_pos, const float *q_neg, const float *k_neg,
+                                const float *sq, const float *sk, const float *norms_q, const float *z,
+                                const float *G, const float *lse, const int32_t *key_count,
+                                const float *mask_a, float *out, float *l_pos, float *alpha, float *v1,
+                                float *v2, float *scratch, float inv_tau_global, float inv_tau_dense,
+                                float lmbd_dense, int B, int C, int P, void *stream) {
+  CP2_REQUIRE(B > 0 && C > 0 && P > 0, "cp2_loss_combine: bad shape B=%d C=%d P=%d", B, C, P);
+  CP2_REQUIRE(q_pos && k_pos && sq && sk && norms_q && z && G && lse && key_count && mask_a && out && l_pos &&
+              alpha && v1 && scratch, "cp2_loss_combine: null pointer");
+  CP2_REQUIRE((q_neg == nullptr) == (k_neg == nullptr) && (q_neg == nullptr) == (v2 == nullptr),
+              "cp2_loss_combine: q_neg, k_neg and v2 go together (include_background)");
+  CP2_REQUIRE(inv_tau_global > 0.f && inv_tau_dense > 0.f, "cp2_loss_combine: bad temperature");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  loss_combine_kernel<<<B, 128, 0, st>>>(q_pos, k_pos, q_neg, k_neg, sq, sk, norms_q, z, G, lse, key_count, mask_a,
+                                         scratch, l_pos, alpha, v1, v2, inv_tau_global, inv_tau_dense, lmbd_dense,
+                                         B, C, P);
+  CP2_LAUNCH_CHECK();
+  loss_finalize_kernel<<<1, 256, 0, st>>>(scratch, q_pos, k_pos, out, lmbd_dense, B, C);
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}

@@ -314,7 +314,8 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
                   const __nv_bfloat16 *__restrict__ qhat, const float *__restrict__ nl,
                   const int *__restrict__ key_count, const float *__restrict__ mask_a,
                   const float *__restrict__ inv_norm, const float *__restrict__ alpha,
-                  const float *__restrict__ v1, const float *__restrict__ v2, float *__restrict__ dq,
+                  const float *__restrict__ v1, const float *__restrict__ v2,
+                  const float *__restrict__ gscale, float *__restrict__ dq,
                   float scale_log2, int B, int P, int P_pad, long long *__restrict__ trace) {
   using Cfg = GradCfg<C, TY, NST, NQ, ND>;
   // optional per-CTA wait-time accounting (test-only; cp2_dbg_dense_trace): slot k of trace[blockIdx.x*16+k]
@@ -489,6 +490,7 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
     const int quad = warp & 3;
     const int row = quad * 32 + lane;
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
+    const float gup = gscale ? __ldg(gscale) : 1.f;          // upstream gradient (device scalar)
     int it = 0;
     for (int w = blockIdx.x; w < items; w += gridDim.x, ++it) {
       const int b = w / nxt, x0 = (w % nxt) * TILE, ny = key_tiles(b);
@@ -497,14 +499,14 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       const bool valid = x < P;
       const float a = valid ? mask_a[(long long)b * P + x] : 0.f;
       const float inr = valid ? inv_norm[(long long)b * P + x] : 0.f;
-      const float al = (ny > 0) ? alpha[b] : 0.f;
+      const float al = (ny > 0) ? alpha[b] * gup : 0.f;
       const uint4 *qrow = reinterpret_cast<const uint4 *>(qhat + ((long long)b * P + (valid ? x : 0)) * C);
       // rank-1 vectors of this image -> shared memory: sva = v1 - v2, svb = v2 (read back as broadcasts)
       const int et = threadIdx.x - 320;                        // 0..127 among the epilogue threads
       asm volatile("bar.sync 1, 128;" ::: "memory");           // everyone is done with the previous item's copy
       for (int c = et; c < C; c += 128) {
-        const float b2 = v2 ? v2[(long long)b * C + c] : 0.f;
-        sva[c] = v1[(long long)b * C + c] - b2;
+        const float b2 = v2 ? v2[(long long)b * C + c] * gup : 0.f;
+        sva[c] = v1[(long long)b * C + c] * gup - b2;
         svb[c] = b2;
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -618,15 +620,15 @@ int launch_lse(const CUtensorMap &tq, const CUtensorMap &tk, const int *key_coun
 template <int C, int TY, int NST, int NQ, int ND, int PF>
 int launch_grad(const CUtensorMap &tq, const CUtensorMap &tk, const void *qhat, const float *nl,
                 const int *key_count, const float *mask_a, const float *inv_norm, const float *alpha,
-                const float *v1, const float *v2, float *dq, float scale_log2, int B, int P, int P_pad,
-                cudaStream_t st) {
+                const float *v1, const float *v2, const float *gscale, float *dq, float scale_log2, int B, int P,
+                int P_pad, cudaStream_t st) {
   using Cfg = GradCfg<C, TY, NST, NQ, ND>;
   auto kern = dense_grad_kernel<C, TY, NST, NQ, ND, PF>;
   CP2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
   const long long items = (long long)B * cp2_cdiv(P, TILE);
   const int grid = (int)(items < cp2_num_sms() ? items : cp2_num_sms());
   kern<<<grid, GRAD_THREADS, Cfg::SMEM, st>>>(tq, tk, static_cast<const __nv_bfloat16 *>(qhat), nl, key_count,
-                                              mask_a, inv_norm, alpha, v1, v2, dq, scale_log2, B, P, P_pad,
+                                              mask_a, inv_norm, alpha, v1, v2, gscale, dq, scale_log2, B, P, P_pad,
                                               g_dense_trace);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
@@ -672,8 +674,8 @@ extern "C" int cp2_dense_lse(const void *qhat_t, const void *khat_t, const int *
 
 extern "C" int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int *key_count, const float *lse,
                               const float *mask_a, const float *mask_b, const float *inv_norm,
-                              const float *alpha, const float *v1, const float *v2, float *dq,
-                              float *scratch_nl, float inv_tau, int B, int C, int P, void *stream) {
+                              const float *alpha, const float *v1, const float *v2, const float *gscale,
+                              float *dq, float *scratch_nl, float inv_tau, int B, int C, int P, void *stream) {
   CP2_REQUIRE(C == 128 || C == 256, "cp2_dense_grad: C=%d unsupported (128 or 256)", C);
   CP2_REQUIRE(B >= 0 && P > 0 && B <= 65535, "cp2_dense_grad: bad shape B=%d P=%d", B, P);
   CP2_REQUIRE(inv_tau > 0.f && inv_tau <= 16.f, "cp2_dense_grad: 1/tau=%g outside (0, 16]", (double)inv_tau);
@@ -693,7 +695,7 @@ extern "C" int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int 
   const int pf = poly_quarters("CP2_DENSE_PF_BWD", 1);
 #define CP2_GRAD(CC, TYV, NSTV, NQV, NDV, PFV)                                                                     \
   launch_grad<CC, TYV, NSTV, NQV, NDV, PFV>(tq, tk, qhat_t, scratch_nl, key_count, mask_a, inv_norm, alpha, v1, \
-                                         v2, dq, sl2, B, P, P_pad, st)
+                                         v2, gscale, dq, sl2, B, P, P_pad, st)
   if (C == 128) {
     switch (pf) { case 0: return CP2_GRAD(128, 128, 5, 1, 2, 0); case 1: return CP2_GRAD(128, 128, 5, 1, 2, 1);
                   case 2: return CP2_GRAD(128, 128, 5, 1, 2, 2); default: return CP2_GRAD(128, 128, 5, 1, 2, 3); }

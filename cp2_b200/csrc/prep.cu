@@ -107,16 +107,44 @@ prep_kernel(const float *__restrict__ feat, const float *__restrict__ mask,
   }
 }
 
-__global__ void prep_reduce_kernel(const float *__restrict__ scratch, float *__restrict__ pos_sum,
-                                   float *__restrict__ neg_sum, int C, int tiles) {
+// Fixed-order reduction of the per-tile partial sums -> pos_sum / neg_sum [B,C]; optionally also the outer
+// F.normalize of builder.py:1264,1268 (x / max(||x||, 1e-12)) -> pos_unit / neg_unit [B,C] and the raw norms.
+__global__ void __launch_bounds__(256)
+prep_reduce_kernel(const float *__restrict__ scratch, float *__restrict__ pos_sum, float *__restrict__ neg_sum,
+                   float *__restrict__ pos_unit, float *__restrict__ neg_unit, float *__restrict__ norms, int C,
+                   int tiles) {
+  __shared__ float sums[512];
+  __shared__ float red[2][8];
   const int b = blockIdx.x;
+  float sq_pos = 0.f, sq_neg = 0.f;
   for (int t = threadIdx.x; t < 2 * C; t += blockDim.x) {
     const float *p = scratch + (long long)b * tiles * 2 * C + t;
     float s = 0.f;
     for (int tl = 0; tl < tiles; ++tl) s += p[(long long)tl * 2 * C];
-    if (t < C) pos_sum[(long long)b * C + t] = s;
-    else neg_sum[(long long)b * C + (t - C)] = s;
+    sums[t] = s;
+    if (t < C) { pos_sum[(long long)b * C + t] = s; sq_pos = fmaf(s, s, sq_pos); }
+    else { neg_sum[(long long)b * C + (t - C)] = s; sq_neg = fmaf(s, s, sq_neg); }
   }
+  if (pos_unit == nullptr) return;
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    sq_pos += __shfl_down_sync(0xffffffffu, sq_pos, off);
+    sq_neg += __shfl_down_sync(0xffffffffu, sq_neg, off);
+  }
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) { red[0][wid] = sq_pos; red[1][wid] = sq_neg; }
+  __syncthreads();
+  float np = 0.f, nn = 0.f;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) { np += red[0][w]; nn += red[1][w]; }
+  np = sqrtf(np);
+  nn = sqrtf(nn);
+  const float ip = 1.f / fmaxf(np, 1e-12f), in = 1.f / fmaxf(nn, 1e-12f);
+  for (int t = threadIdx.x; t < 2 * C; t += blockDim.x) {
+    if (t < C) pos_unit[(long long)b * C + t] = sums[t] * ip;
+    else neg_unit[(long long)b * C + (t - C)] = sums[t] * in;
+  }
+  if (threadIdx.x == 0) { norms[2 * b] = np; norms[2 * b + 1] = nn; }
 }
 
 }  // namespace
@@ -124,10 +152,13 @@ __global__ void prep_reduce_kernel(const float *__restrict__ scratch, float *__r
 extern "C" int cp2_prep_tiles(int P) { return cp2_cdiv(P, PT); }
 
 extern "C" int cp2_prep_features(const float *feat, const float *mask, void *fhat_t, float *inv_norm,
-                                 float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count, int B,
-                                 int C, int P, void *stream) {
+                                 float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count,
+                                 float *pos_unit, float *neg_unit, float *norms, int B, int C, int P,
+                                 void *stream) {
   CP2_REQUIRE(feat && mask && fhat_t && inv_norm && pos_sum && neg_sum && scratch, "cp2_prep_features: null pointer");
   CP2_REQUIRE(B >= 0 && P > 0, "cp2_prep_features: bad shape B=%d P=%d", B, P);
+  CP2_REQUIRE((pos_unit == nullptr) == (neg_unit == nullptr) && (pos_unit == nullptr) == (norms == nullptr),
+              "cp2_prep_features: pos_unit, neg_unit and norms go together");
   CP2_REQUIRE(C == 64 || C == 128 || C == 192 || C == 256, "cp2_prep_features: C=%d unsupported (64,128,192,256)", C);
   if (B == 0) return CP2_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -141,7 +172,7 @@ extern "C" int cp2_prep_features(const float *feat, const float *mask, void *fha
     default: prep_kernel<256><<<grid, 256, 0, st>>>(feat, mask, out, inv_norm, scratch, key_count, P, tiles); break;
   }
   CP2_LAUNCH_CHECK();
-  prep_reduce_kernel<<<B, 256, 0, st>>>(scratch, pos_sum, neg_sum, C, tiles);
+  prep_reduce_kernel<<<B, 256, 0, st>>>(scratch, pos_sum, neg_sum, pos_unit, neg_unit, norms, C, tiles);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }

@@ -95,10 +95,12 @@ def composite(img, bg, output_stride, want_full_mask=False, out=None):
 
 
 # ----------------------------------------------------------------- K2a
-def prep_features(feat, mask, compact=False):
+def prep_features(feat, mask, compact=False, unit=False):
     """builder.py:1261-1268.  feat [B,C,P] f32, mask [B,P] -> (fhat_t bf16 [B,P,C], inv_norm [B,P],
     pos_sum [B,C], neg_sum [B,C], key_count).  compact=True (key side): fhat_t holds the foreground
-    rows first (pixel order) then zero rows, and key_count [B] int32 is their number; else None."""
+    rows first (pixel order) then zero rows, and key_count [B] int32 is their number; else None.
+    unit=True appends (pos_unit [B,C], neg_unit [B,C], norms [B,2]): the outer F.normalize of the pooled
+    vectors (builder.py:1264,1268) and the raw norms its backward needs."""
     _need_cuda(feat, mask)
     feat, mask = _f32c(feat), _f32c(mask)
     B, C, P = feat.shape
@@ -110,8 +112,13 @@ def prep_features(feat, mask, compact=False):
     neg = torch.empty((B, C), device=dev, dtype=torch.float32)
     scratch = torch.empty((B, lib.cp2_prep_tiles(P), 2, C), device=dev, dtype=torch.float32)
     count = torch.empty((B,), device=dev, dtype=torch.int32) if compact else None
+    pu = torch.empty((B, C), device=dev, dtype=torch.float32) if unit else None
+    nu = torch.empty((B, C), device=dev, dtype=torch.float32) if unit else None
+    norms = torch.empty((B, 2), device=dev, dtype=torch.float32) if unit else None
     _call("cp2_prep_features", 2, lib.cp2_prep_features, _ptr(feat), _ptr(mask), _ptr(fhat_t), _ptr(inv_norm),
-          _ptr(pos), _ptr(neg), _ptr(scratch), _ptr(count), B, C, P, _stream())
+          _ptr(pos), _ptr(neg), _ptr(scratch), _ptr(count), _ptr(pu), _ptr(nu), _ptr(norms), B, C, P, _stream())
+    if unit:
+        return fhat_t, inv_norm, pos, neg, count, pu, nu, norms
     return fhat_t, inv_norm, pos, neg, count
 
 
@@ -127,16 +134,17 @@ def dense_lse(qhat_t, khat_t, inv_tau, key_count=None):
     return lse
 
 
-def dense_grad(qhat_t, khat_t, lse, mask_a, mask_b, inv_norm, alpha, v1, v2, inv_tau, key_count=None):
+def dense_grad(qhat_t, khat_t, lse, mask_a, mask_b, inv_norm, alpha, v1, v2, inv_tau, key_count=None, gscale=None):
     """Fused backward of the dense + global loss w.r.t. the query features -> dq [B,C,P].
-    mask_b may be None when the keys are compacted (key_count given)."""
+    mask_b may be None when the keys are compacted (key_count given); gscale: None or a 1-element f32
+    device tensor, the upstream gradient multiplied into alpha / v1 / v2 inside the kernel."""
     B, P, C = qhat_t.shape
     lib = _lib.load()
     dq = torch.empty((B, C, P), device=qhat_t.device, dtype=torch.float32)
     nl = torch.empty((B, lib.cp2_dense_pad(P)), device=qhat_t.device, dtype=torch.float32)
     _call("cp2_dense_grad", 2, lib.cp2_dense_grad, _ptr(qhat_t), _ptr(khat_t), _ptr(key_count), _ptr(lse),
-          _ptr(mask_a), _ptr(mask_b), _ptr(inv_norm), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(dq), _ptr(nl),
-          float(inv_tau), B, C, P, _stream())
+          _ptr(mask_a), _ptr(mask_b), _ptr(inv_norm), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(gscale), _ptr(dq),
+          _ptr(nl), float(inv_tau), B, C, P, _stream())
     return dq
 
 
@@ -229,16 +237,25 @@ def enqueue(keys_all, queue, queue_ptr):
 
 
 # ------------------------------------------------- fused loss (a5 + a6 + a7 + a12)
-def _unit(s):
-    n = s.norm(dim=1, keepdim=True)
-    d = n.clamp_min(_EPS)
-    return s / d, d, n
-
-
-def _unit_bwd(dy, y, d, n):
-    """Backward of y = s / max(||s||, eps) (F.normalize)."""
-    proj = dy - y * (y * dy).sum(dim=1, keepdim=True)
-    return torch.where(n > _EPS, proj, dy) / d
+def loss_combine(q_pos, k_pos, q_neg, k_neg, sq, sk, norms_q, z, G, lse, key_count, mask_a, temp_global,
+                 temp_local, lmbd_dense):
+    """cp2_loss_combine: the [B,C]/[B]-sized remainder of the loss (2 launches).
+    -> out [5] = (loss, loss_ins, loss_dense, std meter of q_pos, std meter of k_pos), l_pos [B],
+       alpha [B], v1 [B,C], v2 [B,C]|None (inputs of cp2_dense_grad for upstream gradient 1)."""
+    B, C = q_pos.shape
+    P = lse.shape[1]
+    dev = q_pos.device
+    out = torch.empty((5,), device=dev, dtype=torch.float32)
+    l_pos = torch.empty((B,), device=dev, dtype=torch.float32)
+    alpha = torch.empty((B,), device=dev, dtype=torch.float32)
+    v1 = torch.empty((B, C), device=dev, dtype=torch.float32)
+    v2 = torch.empty((B, C), device=dev, dtype=torch.float32) if q_neg is not None else None
+    scratch = torch.empty((B, 2), device=dev, dtype=torch.float32)
+    _call("cp2_loss_combine", 2, _lib.load().cp2_loss_combine, _ptr(q_pos), _ptr(k_pos), _ptr(q_neg), _ptr(k_neg),
+          _ptr(sq), _ptr(sk), _ptr(norms_q), _ptr(z), _ptr(G), _ptr(lse), _ptr(key_count), _ptr(mask_a), _ptr(out),
+          _ptr(l_pos), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(scratch), 1.0 / float(temp_global),
+          1.0 / float(temp_local), float(lmbd_dense), B, C, P, _stream())
+    return out, l_pos, alpha, v1, v2
 
 
 class CP2LossFunction(torch.autograd.Function):
@@ -246,10 +263,11 @@ class CP2LossFunction(torch.autograd.Function):
     1392-1397, 1414-1439), MappingType.CP2 / NegativeType.NONE.
 
     forward(q [B,C,h,w], k [B,C,h,w], mask_a [B,P], mask_b [B,P], queue [C,K], ...) ->
-        (loss, loss_ins, loss_dense, k_pos, q_pos, l_pos)
+        (loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters [2])
     Only `loss` carries a gradient, and only to q (keys and queue are detached in the
-    reference, builder.py:1271,1396).  Backward is ONE kernel (cp2_dense_grad): every
-    rank-1 term is folded into per-image vectors computed here on [B,C] tensors.
+    reference, builder.py:1271,1396).  Forward = cp2_prep_features x 2, cp2_global_nce, cp2_dense_lse,
+    cp2_loss_combine; backward = cp2_dense_grad alone, reading the upstream gradient from device memory.
+    No ATen arithmetic in between: torch only allocates the buffers.
     """
 
     @staticmethod
@@ -259,62 +277,38 @@ class CP2LossFunction(torch.autograd.Function):
         kf = _f32c(k.detach()).reshape(B, C, -1)
         mask_a, mask_b = _f32c(mask_a), _f32c(mask_b)
         tg, tl = float(temp_global), float(temp_local)
-        qh, q_inv, sq, snq, _ = prep_features(qf, mask_a)
-        kh, _, sk, snk, kcnt = prep_features(kf, mask_b, compact=True)     # fg keys first, zero rows after
-        q_pos, dq_, nq_ = _unit(sq)
-        k_pos, _, _ = _unit(sk)
-        # ---- global InfoNCE: the queue part is one kernel; the 1-3 extra logits are [B]-sized
-        z, G = global_nce(q_pos, queue, 1.0 / tg)
-        l_pos = (q_pos * k_pos).sum(dim=1)
-        e_pos = torch.exp((l_pos - 1.0) / tg)
-        Z = z + e_pos
-        num = G + e_pos[:, None] * k_pos
-        if include_background:
-            q_neg, dn_, nn_ = _unit(snq)
-            k_neg, _, _ = _unit(snk)
-            e_nq = torch.exp(((q_pos * q_neg).sum(dim=1) - 1.0) / tg)
-            e_nk = torch.exp(((q_pos * k_neg).sum(dim=1) - 1.0) / tg)
-            Z = Z + e_nq + e_nk
-            num = num + e_nq[:, None] * q_neg + e_nk[:, None] * k_neg
-        loss_ins = (torch.log(Z) + (1.0 - l_pos) / tg).mean()
-        # ---- dense InfoNCE: column LSE on the tensor cores, rank-1 positive term here
-        lse = dense_lse(qh, kh, 1.0 / tl, kcnt)                # compact key order: rows < kcnt are fg
-        A = mask_a.sum(dim=1)
-        Bm = kcnt.to(torch.float32)
-        fg = torch.arange(lse.shape[1], device=lse.device)[None, :] < kcnt[:, None]
-        dense_n = torch.where(fg, lse, lse.new_zeros(())).sum(dim=1) / Bm - (sq * sk).sum(dim=1) / (tl * A * Bm)
-        loss_dense = dense_n.mean()
-        loss = loss_ins + loss_dense * lmbd_dense
-        # ---- backward coefficients for a unit upstream gradient
-        dqpos = (num / Z[:, None] - k_pos) / (B * tg)
-        v1 = _unit_bwd(dqpos, q_pos, dq_, nq_) - (lmbd_dense / B) * sk / (tl * A * Bm)[:, None]
-        v2 = None
-        if include_background:
-            dqneg = (e_nq / Z)[:, None] * q_pos / (B * tg)
-            v2 = _unit_bwd(dqneg, q_neg, dn_, nn_).contiguous()
-        alpha = lmbd_dense / (B * Bm * tl)
-        ctx.save_for_backward(qh, kh, lse, mask_a, kcnt, q_inv, alpha.contiguous(), v1.contiguous(), v2)
+        qh, q_inv, sq, _, _, q_pos, q_neg, norms_q = prep_features(qf, mask_a, unit=True)
+        # key side compacted: fg keys first, zero rows after
+        kh, _, sk, _, kcnt, k_pos, k_neg, _ = prep_features(kf, mask_b, compact=True, unit=True)
+        z, G = global_nce(q_pos, queue, 1.0 / tg)              # one pass over the queue: fwd + bwd sums
+        lse = dense_lse(qh, kh, 1.0 / tl, kcnt)                # column LSE on the tensor cores
+        bg = bool(include_background)
+        out, l_pos, alpha, v1, v2 = loss_combine(q_pos, k_pos, q_neg if bg else None, k_neg if bg else None,
+                                                 sq, sk, norms_q, z, G, lse, kcnt, mask_a, tg, tl, lmbd_dense)
+        ctx.save_for_backward(qh, kh, lse, mask_a, kcnt, q_inv, alpha, v1, v2)
         ctx.inv_tl = 1.0 / tl
         ctx.q_shape = q.shape
-        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos)
-        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos
+        loss, loss_ins, loss_dense, meters = out[0], out[1], out[2], out[3:]
+        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters)
+        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters
 
     @staticmethod
     def backward(ctx, g_loss, *_unused):
         qh, kh, lse, mask_a, kcnt, q_inv, alpha, v1, v2 = ctx.saved_tensors
-        g = g_loss.reshape(())
-        dq = dense_grad(qh, kh, lse, mask_a, None, q_inv, (alpha * g).contiguous(), (v1 * g).contiguous(),
-                        None if v2 is None else (v2 * g).contiguous(), ctx.inv_tl, key_count=kcnt)
+        g = g_loss.detach().reshape(1)
+        if g.dtype != torch.float32 or not g.is_contiguous():
+            g = g.float().contiguous()
+        dq = dense_grad(qh, kh, lse, mask_a, None, q_inv, alpha, v1, v2, ctx.inv_tl, key_count=kcnt, gscale=g)
         return dq.reshape(ctx.q_shape), None, None, None, None, None, None, None, None
 
 
 def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_dense=0.2,
              include_background=False):
     """-> (loss, loss_ins, loss_dense, k_pos, q_pos, stats); only `loss` has a gradient (to q)."""
-    loss, loss_ins, loss_dense, k_pos, q_pos, l_pos = CP2LossFunction.apply(
+    loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters = CP2LossFunction.apply(
         q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense, include_background)
-    nan = torch.full((), float("nan"), device=loss.device)
-    stats = {"l_pos": l_pos, "acc_ins": nan, "acc_seg": nan}
+    nan = float("nan")       # the arg-max / top-1 meters need the materialised logits: MODEL(track_accuracy=True)
+    stats = {"l_pos": l_pos, "acc_ins": nan, "acc_seg": nan, "std_q_pos": meters[0], "std_k_pos": meters[1]}
     return loss, loss_ins, loss_dense, k_pos, q_pos, stats
 
 

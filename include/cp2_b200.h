@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CP2_ABI_VERSION 4
+#define CP2_ABI_VERSION 5
 
 #define CP2_OK 0
 #define CP2_E_INVALID (-1)      /* bad shape / null pointer / unsupported dim          */
@@ -60,11 +60,14 @@ int cp2_composite(const float *img, const float *bg, float *out, float *mask_ful
  *               key_count[n] = number of foreground pixels.  Only the key side is compacted:
  *               background keys have label 0 for every query (builder.py:1291-1292,1435), so they
  *               enter neither the loss nor the gradient.  inv_norm / pos_sum / neg_sum are unaffected.
+ *   pos_unit, neg_unit, norms : all NULL, or OUT [B,C], [B,C], [B,2]: the outer F.normalize of the pooled
+ *               vectors (builder.py:1264,1268,1282,1285), x / max(||x||, 1e-12), and the raw norms
+ *               (||pos_sum||, ||neg_sum||) the normalisation's backward needs.
  * C must be a multiple of 64 and <= 256. */
 int cp2_prep_tiles(int P);
 int cp2_prep_features(const float *feat, const float *mask, void *fhat_t, float *inv_norm,
-                      float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count, int B, int C,
-                      int P, void *stream);
+                      float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count,
+                      float *pos_unit, float *neg_unit, float *norms, int B, int C, int P, void *stream);
 
 /* K2 forward — dense pixel InfoNCE, column log-sum-exp.
  * Replaces builder.py:1289 (einsum ncx,ncy->nxy), :1431 (/T) and the LogSoftmax(dim=1)
@@ -83,14 +86,15 @@ int cp2_dense_lse(const void *qhat_t, const void *khat_t, const int32_t *key_cou
  *               on_y = (mask_b == NULL || mask_b[y] != 0) && (key_count == NULL || y < key_count[n])
  *   dqhat_x   = alpha[n]*acc[x,:] + mask_a[x]*v1[n,:] + (1-mask_a[x])*v2[n,:]
  *   dq[n,:,x] = (dqhat_x - qhat_x (qhat_x . dqhat_x)) * inv_norm[n,x]        ([B,C,P] f32)
- * alpha [B], v1 [B,C], v2 [B,C] (v2 may be NULL = zeros) carry the upstream gradient
- * and every rank-1 term; the caller computes them on [B,C] tensors.
+ * alpha [B], v1 [B,C], v2 [B,C] (v2 may be NULL = zeros) carry every rank-1 term (cp2_loss_combine
+ * writes them for a unit upstream gradient); gscale is NULL or a device scalar, the upstream
+ * gradient d L / d loss, multiplied into all three on load (no host read, no scaling pass).
  *   scratch_nl : [B, cp2_dense_pad(P)] f32 work space. */
 int cp2_dense_pad(int P);
 int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int32_t *key_count, const float *lse,
                    const float *mask_a, const float *mask_b, const float *inv_norm, const float *alpha,
-                   const float *v1, const float *v2, float *dq, float *scratch_nl, float inv_tau, int B,
-                   int C, int P, void *stream);
+                   const float *v1, const float *v2, const float *gscale, float *dq, float *scratch_nl,
+                   float inv_tau, int B, int C, int P, void *stream);
 
 /* K3 — global MoCo InfoNCE against the negative queue, forward and backward in one
  * pass over the queue.  Replaces builder.py:1396 (q_pos @ queue.clone()) and the
@@ -106,6 +110,26 @@ int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int32_t *key_co
 int64_t cp2_global_scratch_floats(int B, int C);
 int cp2_global_nce(const float *q_pos, const float *queue, float *z, float *g, float *scratch,
                    float inv_tau, int B, int C, int K, void *stream);
+
+/* a5/a7/a12 glue — the [B,C] / [B]-sized remainder of the CP2 loss in two launches.
+ * Replaces builder.py:1395 (l_pos), :1414-1418 (background logits), :1428 (cross entropy at the
+ * positive), :1431-1437 (rank-1 positive term and masked mean of the dense loss), :1439 (loss
+ * combination), the cross-image std meters (:1260-1285 stats) and, for the backward, the global loss's
+ * gradient pushed through the outer F.normalize of :1264,1268.
+ *   q_pos,k_pos,(q_neg,k_neg) : [B,C] unit pooled vectors (cp2_prep_features pos_unit / neg_unit);
+ *                               q_neg = k_neg = v2 = NULL when include_background is off
+ *   sq, sk   : [B,C] pooled sums before normalisation (pos_sum of the query / key side)
+ *   norms_q  : [B,2] (||sq||, ||neg_sum_q||) from cp2_prep_features
+ *   z, G     : [B], [B,C] from cp2_global_nce ; lse : [B,P] from cp2_dense_lse (compacted key order)
+ *   key_count: [B] int32 foreground keys per image ; mask_a : [B,P] f32
+ *   out      : [5] f32 = {loss, loss_ins, loss_dense, mean_c std_b(q_pos), mean_c std_b(k_pos)}
+ *   l_pos [B]; alpha [B], v1 [B,C], v2 [B,C] : inputs of cp2_dense_grad for upstream gradient 1
+ *   scratch  : [B,2] f32 */
+int cp2_loss_combine(const float *q_pos, const float *k_pos, const float *q_neg, const float *k_neg,
+                     const float *sq, const float *sk, const float *norms_q, const float *z, const float *G,
+                     const float *lse, const int32_t *key_count, const float *mask_a, float *out,
+                     float *l_pos, float *alpha, float *v1, float *v2, float *scratch, float inv_tau_global,
+                     float inv_tau_dense, float lmbd_dense, int B, int C, int P, void *stream);
 
 /* K4 — momentum (EMA) update of the key encoder, all parameters in one launch.
  * Replaces builder.py:557-567 (3 ATen kernels x ~183 tensors).

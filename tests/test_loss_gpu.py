@@ -66,9 +66,13 @@ def test_loss_vs_oracle(ops, B, C, hw, K, tl, bg):
     (r["loss"] * 1.7).backward()
     qd = q.cuda().requires_grad_(True)
     if C == 128:
-        loss, li, ld, k_pos, q_pos, _ = ops.cp2_loss(qd, k.cuda(), ma.cuda(), mb.cuda(), queue.cuda(), 0.2, tl,
-                                                     0.2, bg)
+        loss, li, ld, k_pos, q_pos, st = ops.cp2_loss(qd, k.cuda(), ma.cuda(), mb.cuda(), queue.cuda(), 0.2, tl,
+                                                      0.2, bg)
         (loss * 1.7).backward()
+        # the cross-image std meters (builder.py:1553-1563: q_pos.std(0).mean()) and l_pos come out of the same kernel
+        np.testing.assert_allclose(st["std_q_pos"].item(), r["q_pos"].detach().std(0).mean().item(), rtol=1e-4)
+        np.testing.assert_allclose(st["std_k_pos"].item(), r["k_pos"].std(0).mean().item(), rtol=1e-4)
+        assert torch.allclose(st["l_pos"].cpu(), (r["q_pos"].detach() * r["k_pos"]).sum(1), rtol=1e-4, atol=1e-6)
         np.testing.assert_allclose(loss.item(), r["loss"].item(), rtol=LOSS_RTOL)
         np.testing.assert_allclose(li.item(), r["loss_ins"].item(), rtol=LOSS_RTOL)
         np.testing.assert_allclose(ld.item(), r["loss_dense"].item(), rtol=LOSS_RTOL)
