@@ -278,6 +278,61 @@ def dense_sweep(args, peaks):
     return rows
 
 
+# ------------------------------------------------------------------ mirror-loss microbench
+def mirror_sweep(peaks, iters=20):
+    """configs[4] shapes (512x512 labels, Cls=2, decoder maps 32x32 = OS16 and 64x64 = OS8): the fused
+    resize + loss + backward kernel (cp2_mirror_loss_upsampled) and the full-resolution kernel
+    (cp2_mirror_loss) against the eager torch formulation of networks/mirror_network.py:47-63 +
+    segment_network.py:219-231 on the same GPU.  CUDA events, a 1 GiB memset between iterations flushes L2
+    and hides the host launch path."""
+    import torch
+    import torch.nn.functional as F
+    from cp2_b200 import ops
+    dev = torch.device("cuda")
+    flush = torch.empty(1 << 30, dtype=torch.uint8, device=dev)
+
+    def timeit(fn, n):
+        ts = []
+        for i in range(n + 3):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record()
+            torch.cuda.synchronize()
+            if i >= 3:
+                ts.append(a.elapsed_time(b) * 1e3)
+        return statistics.median(ts)
+
+    rows = []
+    for B, lo in ((8, 32), (8, 64), (32, 32), (32, 64)):
+        Cls, H = 2, 512
+        g = torch.Generator(device=dev).manual_seed(11)
+        s_lo = torch.randn(B, Cls, lo, lo, device=dev, generator=g).requires_grad_()
+        t_lo = torch.randn(B, Cls, lo, lo, device=dev, generator=g).requires_grad_()
+        masks = torch.randint(0, Cls, (B, H, H), device=dev, generator=g)
+        s_hi = F.interpolate(s_lo.detach(), size=(H, H), mode="bilinear", align_corners=False)
+        t_hi = F.interpolate(t_lo.detach(), size=(H, H), mode="bilinear", align_corners=False)
+
+        def eager():
+            s_lo.grad = t_lo.grad = None
+            s = F.interpolate(s_lo, size=(H, H), mode="bilinear", align_corners=False)
+            t = F.interpolate(t_lo, size=(H, H), mode="bilinear", align_corners=False)
+            cmp_ = F.cross_entropy(torch.softmax(s / 2.0, 1), torch.softmax(t / 2.0, 1))
+            cls_ = F.cross_entropy(torch.cat([s, t]), torch.cat([masks, masks]))
+            (cls_ + 0.01 * cmp_).backward()
+
+        up = timeit(lambda: ops.mirror_loss_upsampled_raw(s_lo.detach(), t_lo.detach(), masks, 0.01, 2.0, True), iters)
+        full = timeit(lambda: ops.mirror_loss_raw(s_hi, t_hi, masks, 0.01, 2.0, True), iters)
+        eag = timeit(eager, 5)
+        px = B * H * H
+        full_bytes = px * (8 + 16 * Cls)
+        rows.append({"B": B, "Cls": Cls, "logits": lo, "labels": H, "fused_resize_loss_bwd_us": round(up, 2),
+                     "label_bytes": px * 8, "full_res_loss_bwd_us": round(full, 2),
+                     "full_res_GBps": round(full_bytes / full / 1e3, 1),
+                     "full_res_frac_hbm": round(full_bytes / full / 1e3 / peaks["hbm_gbs"], 4),
+                     "eager_torch_us": round(eag, 1), "speedup_vs_eager": round(eag / up, 1)})
+    return rows
+
+
 # ------------------------------------------------------------------------------ own arm
 def algorithmic_work(batch, n_params, world):
     """Per-CALL algorithmic bytes / flops of each C-ABI entry point on the step."""
@@ -459,6 +514,7 @@ def own_arm(args):
         if not args.no_sweep:
             # free the training state first: the 56x56 / C=256 point needs ~3.5 GB
             line["dense_microbench"] = dense_sweep(args, peaks)
+            line["mirror_microbench"] = mirror_sweep(peaks)
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_leg()
     if rank == 0:
