@@ -84,7 +84,14 @@ global_nce_kernel(const __grid_constant__ CUtensorMap tm_queue, const float *__r
     mbar_init(e_empty, 1);
     mbar_init(d2_full, 1);
     fence_barrier_init();
-    prefetch_tmap(&tm_queue);
+    // the first NST stages are requested right here, by the thread that initialised the barriers: the DRAM
+    // round trip then overlaps the rest of the prologue (q_pos conversion, TMEM allocation, CTA barrier)
+    for (int i = 0; i < min(NST, my_tiles); ++i) {
+      const int nb = min(4, r1 - r0 - 4 * i);
+      const int k0 = (r0 + 4 * i) * 32;
+      mbar_expect_tx(&ffull[i], nb * FBOX);
+      for (int kq = 0; kq < nb; ++kq) tma_load_2d(sF + i * FSTAGE + kq * FBOX, &tm_queue, &ffull[i], k0 + kq * 32, 0);
+    }
   }
   if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
   // q_pos -> bf16 hi / lo operands (K-major, rows past B are zero)
@@ -108,7 +115,7 @@ global_nce_kernel(const __grid_constant__ CUtensorMap tm_queue, const float *__r
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      for (int i = 0; i < my_tiles; ++i) {
+      for (int i = NST; i < my_tiles; ++i) {           // tiles 0 .. NST-1 were requested in the prologue
         const int s = i % NST, ph = (i / NST) & 1;
         const int nb = min(4, r1 - r0 - 4 * i);
         const int k0 = (r0 + 4 * i) * 32;
