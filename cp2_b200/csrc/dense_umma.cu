@@ -519,7 +519,9 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       twait(&d_full[db], (it / ND) & 1, tr_a);
       tc_fence_after();
       const uint32_t tD = tmem_D + db * C + lane_off;
-      float dot = 0.f;
+      f2 dot2 = f2_pack(0.f, 0.f), ndot2 = dot2;
+      const f2 al2 = f2_pack(al, al), a2 = f2_pack(a, a), inr2 = f2_pack(inr, inr);
+      float *dq_row = dq + (long long)b * C * P + x;
 #pragma unroll 1
       for (int st2 = 0; st2 < NSTEP; st2 += 2) {
 #pragma unroll
@@ -538,6 +540,8 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
 #pragma unroll
           for (int i = 0; i < 32; ++i) r[i] = 0u;
         }
+        // packed fp32x2 arithmetic on channel pairs (c, c+1): the bf16 pair of Qhat is one word, the TMEM
+        // pair two adjacent registers, the rank-1 vectors come as float4 broadcasts
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           const uint4 qv = qb[sub][u];
@@ -546,16 +550,33 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
           for (int e4 = 0; e4 < 2; ++e4) {
             const float4 va = *reinterpret_cast<const float4 *>(sva + ch * 32 + u * 8 + e4 * 4);
             const float4 vb = *reinterpret_cast<const float4 *>(svb + ch * 32 + u * 8 + e4 * 4);
-            const float vaa[4] = {va.x, va.y, va.z, va.w}, vbb[4] = {vb.x, vb.y, vb.z, vb.w};
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int e = e4 * 4 + i, c = ch * 32 + u * 8 + e;
-              const float qh = __uint_as_float((e & 1) ? (qw[e >> 1] & 0xffff0000u) : (qw[e >> 1] << 16));
-              const float gq = fmaf(al, __uint_as_float(r[u * 8 + e]), fmaf(a, vaa[i], vbb[i]));
-              if (pass == 0) dot = fmaf(qh, gq, dot);
-              else if (valid) dq[((long long)b * C + c) * P + x] = (gq - qh * dot) * inr;
+            for (int h2 = 0; h2 < 2; ++h2) {
+              const int e = e4 * 4 + h2 * 2, c = ch * 32 + u * 8 + e;          // channels c, c+1
+              const uint32_t w = qw[e >> 1];
+              const f2 qh2 = f2_pack_u(w << 16, w & 0xffff0000u);
+              const f2 va2 = h2 == 0 ? f2_pack(va.x, va.y) : f2_pack(va.z, va.w);
+              const f2 vb2 = h2 == 0 ? f2_pack(vb.x, vb.y) : f2_pack(vb.z, vb.w);
+              const f2 gq2 = f2_fma(al2, f2_pack_u(r[u * 8 + e], r[u * 8 + e + 1]), f2_fma(a2, va2, vb2));
+              if (pass == 0) {
+                dot2 = f2_fma(qh2, gq2, dot2);
+              } else {
+                float o0, o1;
+                f2_unpack(f2_mul(f2_fma(qh2, ndot2, gq2), inr2), o0, o1);
+                if (valid) {
+                  float *dst = dq_row + (long long)c * P;
+                  dst[0] = o0;
+                  dst[P] = o1;
+                }
+              }
             }
           }
+        }
+        if (pass == 0 && ch == NCH - 1) {          // end of the first pass: dot = sum of the two lanes of dot2
+          float d0, d1;
+          f2_unpack(dot2, d0, d1);
+          const float dsum = d0 + d1;
+          ndot2 = f2_pack(-dsum, -dsum);
         }
       }
       }
