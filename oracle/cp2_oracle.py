@@ -122,7 +122,8 @@ def topk_accuracy(logits: torch.Tensor, topk=(1, 5)):
 
 # ------------------------------------------------------------------ a5+a6+a7+a12
 def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0,
-             lmbd_dense=0.2, include_background=False):
+             lmbd_dense=0.2, include_background=False, weights=None, negative_type="NONE",
+             negative_scale=2.0):
     """Everything `forward_cp2` does between the two encoder outputs and the scalar
     loss, for MappingType.CP2 / NegativeType.NONE.  builder.py:1260-1268, 1279-1292,
     1392-1397, 1414-1439.
@@ -137,7 +138,12 @@ def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0,
     q_hat, q_pos, q_neg = normalize_and_pool(q, mask_a)
     with torch.no_grad():
         k_hat, k_pos, k_neg = normalize_and_pool(k, mask_b)
-    loss_d = dense_infonce(q_hat, k_hat, mask_a, mask_b, temp_local)
+    if weights is None and negative_type == "NONE":
+        loss_d = dense_infonce(q_hat, k_hat, mask_a, mask_b, temp_local)
+    else:                                  # PROPOSED modes
+        w = torch.ones(()) if weights is None else weights
+        loss_d = dense_infonce_weighted(q_hat, k_hat, mask_a, mask_b, w, temp_local, negative_type,
+                                        negative_scale)
     loss_i, logits = global_infonce(q_pos, k_pos, queue.detach(), temp_global, q_neg, k_neg,
                                     include_background)
     loss = loss_i + loss_d * lmbd_dense
@@ -237,15 +243,48 @@ def cp2_corr_weights(pixel_ids_a, pixel_ids_b, region_ids_a, region_ids_b, mask_
                      w_pixel=1, w_region=1, w_not=1):
     """builder.py:1204-1243: region weight where region ids match (and both are known,
     i.e. non-zero), overridden by the pixel weight where pixel ids match, and the
-    "not" weight wherever the result is still zero.  All ones in CP2 mode."""
+    "not" weight wherever the result is still zero.  All ones in CP2 mode.  The dtype follows
+    the reference's `w_region * bool_tensor` (int64 for python ints, f32 for floats as main.py:75-77
+    passes them)."""
     b = mask_a.shape[0]
     pix = correlation_map(pixel_ids_a, pixel_ids_b)
     reg = correlation_map(region_ids_a, region_ids_b)
     known = (region_ids_a.reshape(b, -1)[:, :, None] * region_ids_b.reshape(b, -1)[:, None, :]) != 0
-    w = w_region * (reg & known).to(torch.int64)
+    w = w_region * (reg & known)
     w[pix] = w_pixel
-    w = w + (w == 0).to(w.dtype) * w_not
+    w = w + (w == 0) * w_not
     return w
+
+
+def negative_transform(logits, labels, negative_type: str, negative_scale: float):
+    """builder.py:1332-1386 on a copy: the non-label entries are squashed to
+    2*sigmoid(scale*(s - centre)) - 1 with centre 0 (FIXED) or the per-sample mean of the non-label
+    scores, detached (AVERAGE).  HARD leaves the logits untouched (its `*= 1.5` lands on a temporary,
+    SURVEY.md Appendix A.8); MEDIAN is not restated (per-sample nanquantile centre)."""
+    if negative_type in ("NONE", "HARD"):
+        return logits
+    neg = ~labels.bool()
+    if negative_type == "FIXED":
+        centre = torch.zeros(logits.shape[0], 1, 1)
+    elif negative_type == "AVERAGE":
+        centre = dense_loss_stats(logits, labels)["negative"]["average"].detach().reshape(-1, 1, 1)
+    else:
+        raise NotImplementedError(negative_type)
+    squashed = 2.0 / (1.0 + torch.exp((logits - centre) * -negative_scale)) - 1.0
+    return torch.where(neg, squashed, logits)
+
+
+def dense_infonce_weighted(q_hat, k_hat, mask_a, mask_b, weights, temp_local: float,
+                           negative_type: str = "NONE", negative_scale: float = 2.0):
+    """The dense loss of `forward_cp2` for the PROPOSED modes: builder.py:1289-1292, 1332-1392
+    (negative transform, then `* corr_weights`), 1431-1437."""
+    logits = dense_logits(q_hat, k_hat)
+    labels = torch.einsum("nx,ny->nxy", mask_a, mask_b)
+    logits = negative_transform(logits, labels, negative_type, negative_scale) * weights / temp_local
+    neg_log = -torch.log_softmax(logits, dim=1)
+    n = logits.shape[0]
+    num = (neg_log.reshape(n, -1) * labels.reshape(n, -1)).sum(dim=1)
+    return (num / labels.reshape(n, -1).sum(dim=1)).mean()
 
 
 def dense_loss_stats(logits, labels):

@@ -335,8 +335,77 @@ def gen_mirror():
     np.savez_compressed(os.path.join(OUT, "mirror.npz"), **out)
 
 
+def proposed_ids(batch, height, width, seed):
+    """Pixel / region id maps for the PROPOSED-mode fixtures: view b is view a shifted by a multiple
+    of the output stride (so pixel ids meet on the [OS/2::OS] lattice), out-of-view pixels get fresh
+    ids; regions are 64x64 blocks, a few of them "unknown" (id 0, builder.py:1221-1232)."""
+    g = torch.Generator().manual_seed(seed)
+    pa = torch.arange(1, height * width + 1, dtype=torch.int64).reshape(1, height, width).repeat(batch, 1, 1)
+    pb = torch.zeros_like(pa)
+    ra = torch.zeros_like(pa)
+    rb = torch.zeros_like(pa)
+    yy, xx = torch.meshgrid(torch.arange(height), torch.arange(width), indexing="ij")
+    for i in range(batch):
+        dy, dx = (int(v) * 16 for v in torch.randint(-3, 4, (2,), generator=g))
+        sy, sx = yy + dy, xx + dx
+        inside = (sy >= 0) & (sy < height) & (sx >= 0) & (sx < width)
+        fresh = height * width + 1 + yy * width + xx
+        pb[i] = torch.where(inside, pa[i][sy.clamp(0, height - 1), sx.clamp(0, width - 1)], fresh)
+        blocks = (yy // 64) * ((width + 63) // 64) + xx // 64          # block 0 is "unknown"
+        drop = torch.randint(1, int(blocks.max()) + 1, (2,), generator=g)
+        ra[i] = torch.where((blocks == drop[0]), torch.zeros_like(blocks), blocks)
+        rb_full = torch.where((blocks == drop[1]), torch.zeros_like(blocks), blocks)
+        rb[i] = torch.where(inside, rb_full[sy.clamp(0, height - 1), sx.clamp(0, width - 1)], torch.zeros_like(blocks))
+    return {"pixel_ids_a": pa, "pixel_ids_b": pb, "region_ids_a": ra, "region_ids_b": rb}
+
+
+def gen_weighted(tag, negative_type, temp_local, weights=(10.0, 2.0, 0.5), include_background=False):
+    """`forward_cp2` in PretrainType.PROPOSED / MappingType.PIXEL_REGION_ID (builder.py:1204-1243,
+    1332-1392) on given 14x14 feature maps -> tests/golden/cp2_weighted_<tag>.npz."""
+    torch.manual_seed(1)
+    B, C, h, K = 2, 128, 14, 1024
+    builder, model = rh.make_reference_model(
+        lambda: _FeatEncoder(B, C, h), K=K, dim=C, dense_logits_temp=temp_local,
+        include_background=include_background, pretrain_type=rh.import_reference().PretrainType.PROPOSED,
+        mapping_type=rh.import_reference().MappingType.PIXEL_REGION_ID,
+        negative_type=rh.import_reference().NegativeType[negative_type], negative_scale=2.0,
+        lmbd_pixel_corr_weight=weights[0], lmbd_region_corr_weight=weights[1], lmbd_not_corr_weight=weights[2])
+    cap = _Capture(model)
+    g = torch.Generator().manual_seed(11)
+    with torch.no_grad():
+        model.encoder_q.feat.copy_(torch.randn(B, C, h, h, generator=g))
+        model.encoder_k.feat.copy_(torch.randn(B, C, h, h, generator=g))
+    v = synth_views(B, 224, 224, 16, seed=43)
+    v.update(proposed_ids(B, 224, 224, seed=5))
+    sub = lambda t: t[:, 8::16, 8::16]
+    out = {"queue0": _np(model.queue), "temp_local": temp_local, "temp_global": 0.2, "lmbd": 0.2,
+           "include_background": include_background, "negative_type": negative_type, "negative_scale": 2.0,
+           "weights": np.asarray(weights, dtype=np.float32),
+           "bg0_ch0_zero": _np(v["bg0"][:, 0] == 0), "bg1_ch0_zero": _np(v["bg1"][:, 0] == 0)}
+    for name in ("pixel_ids_a", "pixel_ids_b", "region_ids_a", "region_ids_b"):
+        out[name + "_ds"] = _np(sub(v[name]))          # the [OS/2::OS] lattice is all the path reads
+    loss = model(visualize=False, step=0, new_epoch=False, **v)
+    loss.backward()
+    out["q"] = _np(cap.rec["q"])
+    out["k"] = _np(cap.rec["k_shuffled"][cap.rec["idx_unshuffle"]])
+    out["grad_q"] = _np(model.encoder_q.feat.grad)
+    out["loss"] = _np(loss)
+    out["loss_ins"] = np.float32(model.loss_i.val)
+    out["loss_dense"] = np.float32(model.loss_d.val)
+    out["iou"] = np.asarray(model.correlation_ious, dtype=np.float32)
+    out["iou_masked"] = np.asarray(model.masked_correlation_ious, dtype=np.float32)
+    np.savez_compressed(os.path.join(OUT, f"cp2_weighted_{tag}.npz"), **out)
+    print("cp2_weighted", tag, out["loss"], out["loss_ins"], out["loss_dense"])
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "weighted":
+        gen_weighted("none_t1", "NONE", 1.0)
+        gen_weighted("fixed_t05", "FIXED", 0.5)
+        gen_weighted("avg_t1_bg", "AVERAGE", 1.0, include_background=True)
+        gen_weighted("hard_t1", "HARD", 1.0, weights=(3.0, 1.0, 0.0))
+        sys.exit(0)
     gen_step_small()
     gen_loss_p196("t1", 1.0, False)
     gen_loss_p196("t02", 0.2, False)
@@ -345,3 +414,7 @@ if __name__ == "__main__":
     gen_enqueue()
     gen_corr()
     gen_mirror()
+    gen_weighted("none_t1", "NONE", 1.0)
+    gen_weighted("fixed_t05", "FIXED", 0.5)
+    gen_weighted("avg_t1_bg", "AVERAGE", 1.0, include_background=True)
+    gen_weighted("hard_t1", "HARD", 1.0, weights=(3.0, 1.0, 0.0))

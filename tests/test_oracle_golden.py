@@ -47,6 +47,47 @@ def test_loss_path_p196(tag):
     assert w.dtype == torch.int64 and bool((w == 1).all())
 
 
+WEIGHTED_TAGS = ["none_t1", "fixed_t05", "avg_t1_bg", "hard_t1"]
+
+
+def weighted_case(tag):
+    """Inputs of a PROPOSED-mode fixture (oracle/gen_golden.py:gen_weighted)."""
+    g = load_golden(f"cp2_weighted_{tag}.npz")
+    mask_a = O.stride_subsample(T(g["bg0_ch0_zero"]).float(), 16).reshape(2, -1)
+    mask_b = O.stride_subsample(T(g["bg1_ch0_zero"]).float(), 16).reshape(2, -1)
+    ids = {n: T(g[n + "_ds"]) for n in ("pixel_ids_a", "pixel_ids_b", "region_ids_a", "region_ids_b")}
+    return g, mask_a, mask_b, ids
+
+
+@pytest.mark.parametrize("tag", WEIGHTED_TAGS)
+def test_weighted_loss_path(tag):
+    """f3: PretrainType.PROPOSED / PIXEL_REGION_ID weights + NegativeType (builder.py:1204-1243, 1332-1392)."""
+    g, mask_a, mask_b, ids = weighted_case(tag)
+    wp, wr, wn = (float(x) for x in g["weights"])
+    w = O.cp2_corr_weights(ids["pixel_ids_a"], ids["pixel_ids_b"], ids["region_ids_a"], ids["region_ids_b"],
+                           mask_a, mask_b, wp, wr, wn)
+    assert w.dtype == torch.float32 and len(torch.unique(w)) == 3     # all three kinds of pair occur
+    q = T(g["q"]).requires_grad_(True)
+    r = O.cp2_loss(q, T(g["k"]), mask_a, mask_b, T(g["queue0"]), temp_global=float(g["temp_global"]),
+                   temp_local=float(g["temp_local"]), lmbd_dense=float(g["lmbd"]),
+                   include_background=bool(g["include_background"]), weights=w,
+                   negative_type=str(g["negative_type"]), negative_scale=float(g["negative_scale"]))
+    r["loss"].backward()
+    np.testing.assert_allclose(r["loss"].item(), g["loss"], rtol=1e-6)
+    np.testing.assert_allclose(r["loss_dense"].item(), g["loss_dense"], rtol=1e-6)
+    np.testing.assert_allclose(q.grad.numpy(), g["grad_q"], rtol=1e-4, atol=1e-9)
+    # the fixture is not the CP2-mode loss in disguise
+    q2 = T(g["q"]).requires_grad_(True)
+    r2 = O.cp2_loss(q2, T(g["k"]), mask_a, mask_b, T(g["queue0"]), temp_local=float(g["temp_local"]),
+                    include_background=bool(g["include_background"]))
+    r2["loss"].backward()
+    assert (q.grad - q2.grad).abs().max() > 2e-8 and abs(r2["loss_dense"].item() - float(g["loss_dense"])) > 1e-5
+    ra, rb = ids["region_ids_a"], ids["region_ids_b"]
+    mc = O.masked_correlation(ra, rb, mask_a.reshape(2, 14, 14), mask_b.reshape(2, 14, 14))
+    np.testing.assert_allclose(mc["iou"].numpy(), g["iou"])
+    np.testing.assert_allclose(mc["iou_masked"].numpy(), g["iou_masked"])
+
+
 def test_full_step_small():
     g = load_golden("cp2_step_small.npz")
     queue = T(g["queue0"]).clone()
