@@ -21,12 +21,15 @@ SIGNATURES = {
     "cp2_dense_lse": (c_int, [c_void_p] * 4 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_dense_pad": (c_int, [c_int]),
     "cp2_dense_grad": (c_int, [c_void_p] * 13 + [c_float] + [c_int] * 3 + [c_void_p]),
-    "cp2_loss_combine": (c_int, [c_void_p] * 18 + [c_float] * 3 + [c_int] * 3 + [c_void_p]),
+    "cp2_loss_combine": (c_int, [c_void_p] * 19 + [c_float] * 3 + [c_int] * 3 + [c_void_p]),
     "cp2_global_scratch_floats": (c_int64, [c_int, c_int]),
     "cp2_global_nce": (c_int, [c_void_p] * 5 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_ema": (c_int, [c_void_p] * 5 + [c_int, c_float, c_float, c_void_p]),
     "cp2_enqueue": (c_int, [c_void_p] * 3 + [c_int] * 3 + [c_void_p]),
     "cp2_id_iou": (c_int, [c_void_p] * 6 + [c_int] * 4 + [c_void_p]),
+    "cp2_dense_weighted_tiles": (c_int, [c_int]),
+    "cp2_dense_weighted_lse": (c_int, [c_void_p] * 17 + [c_float] * 3 + [c_int, c_float, c_float] + [c_int] * 6 + [c_void_p]),
+    "cp2_dense_weighted_grad": (c_int, [c_void_p] * 16 + [c_float] * 3 + [c_int, c_float, c_float] + [c_int] * 6 + [c_void_p]),
     "cp2_mirror_partials": (c_int, [c_int, c_int64]),
     "cp2_mirror_loss": (c_int, [c_void_p] * 8 + [c_float, c_float, c_int64, c_int, c_int, c_int64, c_void_p]),
     "cp2_mirror_up_partials": (c_int, [c_int] * 3),
@@ -41,7 +44,7 @@ DEBUG_SIGNATURES = {
 }
 
 EMA_CHUNK = 4096  # CP2_EMA_CHUNK
-ABI_VERSION = 5  # CP2_ABI_VERSION
+ABI_VERSION = 6  # CP2_ABI_VERSION
 
 _lib = None
 

@@ -8,8 +8,9 @@ interchange.  Everything between the encoder outputs and the scalar loss, plus t
 compositing, the EMA and the enqueue, runs in the sm_100a kernels of libcp2_b200.so
 (include/cp2_b200.h); torch supplies device memory, streams, autograd plumbing and NCCL.
 
-Scope: PretrainType.CP2 with MappingType.CP2 / NegativeType.NONE.  The
-other pre-training modes of the reference raise NotImplementedError here.
+Scope: `forward_cp2`, i.e. PretrainType.CP2 (MappingType.CP2 / NegativeType.NONE)
+and PretrainType.PROPOSED (pair weights from the id maps, NegativeType NONE / FIXED / AVERAGE / HARD;
+row f3).  The other pre-training modes of the reference raise NotImplementedError here.
 
 Deliberate, documented deviations from the reference (none changes the loss):
   * no `int(queue_ptr)` / `.item()` / `.cpu()` host syncs on the step: the queue pointer
@@ -17,9 +18,8 @@ Deliberate, documented deviations from the reference (none changes the loss):
   * no `queue.clone()` (builder.py:1396): the global kernel produces the backward's
     queue-weighted sum in the forward pass, so enqueue may overwrite the queue before
     `loss.backward()`;
-  * correlation-IoU bookkeeping and dense score quartiles (builder.py:1204-1257, 1298,
-    1401-1403) are loss-neutral in CP2 mode and are skipped (their torch restatements live in
-    the oracle; the IoU lists stay empty);
+  * the dense score quartiles (builder.py:1298, 1401-1403) are loss-neutral and skipped; the
+    correlation IoUs (builder.py:1252-1257) come from one kernel and stay on the device until read;
   * wandb logging is left to the caller (`rank` is stored, nothing is logged here).
 """
 from enum import Enum
@@ -208,6 +208,12 @@ class MODEL(nn.Module):
             assert lmbd_pixel_corr_weight == 1
             assert lmbd_region_corr_weight == 1
             assert lmbd_not_corr_weight == 1
+        elif mapping_type == MappingType.PIXEL_ID:
+            assert lmbd_region_corr_weight == 1
+            assert lmbd_pixel_corr_weight > 1
+        elif mapping_type == MappingType.REGION_ID:
+            assert lmbd_pixel_corr_weight == 1
+            assert lmbd_region_corr_weight > 1
         self.mapping_type = mapping_type
         self.lmbd_pixel_corr_weight = lmbd_pixel_corr_weight
         self.lmbd_region_corr_weight = lmbd_region_corr_weight
@@ -216,12 +222,21 @@ class MODEL(nn.Module):
         self.negative_type = negative_type
         self.negative_scale = negative_scale
         self.backbone_type = backbone_type
-        if pretrain_type != PretrainType.CP2:
+        if pretrain_type not in (PretrainType.CP2, PretrainType.PROPOSED):
             raise NotImplementedError(
-                f"cp2_b200 implements the CP2 pre-training path only ({pretrain_type = }); "
+                f"cp2_b200 implements forward_cp2 (PretrainType.CP2 / PROPOSED) only ({pretrain_type = }); "
                 "see SURVEY.md section 8(f) for the order in which the other modes follow")
-        assert negative_type == NegativeType.NONE       # builder.py:431-433
-        assert mapping_type == MappingType.CP2
+        if pretrain_type == PretrainType.CP2:
+            assert negative_type == NegativeType.NONE   # builder.py:431-433
+            assert mapping_type == MappingType.CP2
+        if negative_type == NegativeType.MEDIAN:
+            raise NotImplementedError("NegativeType.MEDIAN (per-sample nanquantile centre, builder.py:1358-1374) "
+                                      "is not built; NONE, FIXED, AVERAGE and HARD are")
+        # the PROPOSED modes that change the loss; all-ones weights with no
+        # negative squash are the CP2 loss and take the tensor-core path
+        self._weighted = not (lmbd_pixel_corr_weight == 1 and lmbd_region_corr_weight == 1
+                              and lmbd_not_corr_weight == 1
+                              and negative_type in (NegativeType.NONE, NegativeType.HARD))
         if backbone_type != BackboneType.DEEPLABV3 and encoder_factory is None:
             raise NotImplementedError(f"{backbone_type = } needs an encoder_factory (smp is not installed)")
 
@@ -387,11 +402,13 @@ class MODEL(nn.Module):
     # ---------------------------------------------------------- forward_cp2
     def forward_cp2(self, img_a, img_b, bg0, bg1, visualize=False, step=0, new_epoch=False,
                     pixel_ids_a=None, pixel_ids_b=None, region_ids_a=None, region_ids_b=None):
-        """builder.py:1124-1606 for MappingType.CP2 / NegativeType.NONE.
+        """builder.py:1124-1606.
 
-        The pixel / region id maps only feed loss-neutral bookkeeping in this mode (corr_weights is
-        all ones, builder.py:329-332, 1238-1243): the region-id IoUs the reference records per step
-        (builder.py:1252-1257) come from `cp2_id_iou`; the pixel-id maps are not needed.
+        MappingType.CP2 / NegativeType.NONE: the pixel / region id maps only feed loss-neutral bookkeeping
+        (corr_weights is all ones, builder.py:329-332, 1238-1243): the region-id IoUs the reference records
+        per step (builder.py:1252-1257) come from `cp2_id_iou`; the pixel-id maps are not needed.
+        PretrainType.PROPOSED with other weights or a NegativeType: the four id maps define the pair
+        weights and are read by the dense-loss kernels themselves (`cp2_dense_weighted_*`).
         """
         os_ = self.output_stride
         keep = bool(visualize) and self.rank == 0
@@ -417,9 +434,14 @@ class MODEL(nn.Module):
             k = self._batch_unshuffle_ddp(k, idx_unshuffle)
 
         # K2a/K2/K3 + autograd: builder.py:1261-1268, 1279-1292, 1392-1397, 1414-1439
+        pair_weights = None
+        if self._weighted:                                     # builder.py:1204-1243, 1332-1392
+            pair_weights = ops.PairWeights(pixel_ids_a, pixel_ids_b, region_ids_a, region_ids_b, os_,
+                                           self.lmbd_pixel_corr_weight, self.lmbd_region_corr_weight,
+                                           self.lmbd_not_corr_weight, self.negative_type, self.negative_scale)
         loss, loss_ins, loss_dense, k_pos, q_pos, stats = ops.cp2_loss(
             q, k, mask_a, mask_b, self.queue, self.temp_global, self.temp_local, self.lmbd_dense_loss,
-            self.include_background)
+            self.include_background, pair_weights)
         if self.track_accuracy:                                # uses the queue BEFORE this step's enqueue
             stats["acc_ins"], stats["acc_seg"] = self._accuracy_stats(q, k, mask_a, mask_b, q_pos, k_pos)
         self._dequeue_and_enqueue(k_pos)                       # builder.py:1426

@@ -37,7 +37,7 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
                     const float *__restrict__ norms_q, const float *__restrict__ z,
                     const float *__restrict__ G, const float *__restrict__ lse,
                     const int *__restrict__ key_count, const float *__restrict__ mask_a,
-                    float *__restrict__ terms, float *__restrict__ l_pos_out, float *__restrict__ alpha,
+                    const float *__restrict__ dense_n, float *__restrict__ terms, float *__restrict__ l_pos_out, float *__restrict__ alpha,
                     float *__restrict__ v1, float *__restrict__ v2, float inv_tg, float inv_tl, float lmbd,
                     int B, int C, int P) {
   __shared__ float red[6 * 4];
@@ -51,11 +51,11 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
     const float qp = q_pos[row + c];
     r1[0] = fmaf(qp, k_pos[row + c], r1[0]);
     if (bg) { r1[1] = fmaf(qp, q_neg[row + c], r1[1]); r1[2] = fmaf(qp, k_neg[row + c], r1[2]); }
-    r1[3] = fmaf(sq[row + c], sk[row + c], r1[3]);
+    if (!dense_n) r1[3] = fmaf(sq[row + c], sk[row + c], r1[3]);
   }
   for (int x = tid; x < P; x += 128) {
     r1[4] += mask_a[(long long)b * P + x];
-    if (x < cnt) r1[5] += lse[(long long)b * P + x];   // compacted keys: rows < cnt are the foreground ones
+    if (!dense_n && x < cnt) r1[5] += lse[(long long)b * P + x];   // compacted keys: rows < cnt are foreground
   }
   block_sum<6>(r1, red);
   const float l_pos = r1[0], A = r1[4], Bm = (float)cnt;
@@ -88,7 +88,8 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
     if (bg) num = fmaf(e_nq, q_neg[row + c], fmaf(e_nk, k_neg[row + c], num));
     const float dqpos = (num * rZ - kp) * invB * inv_tg;
     const float proj = nq > kEps ? dqpos - qp * r2[0] : dqpos;
-    v1[row + c] = proj * dq_d - lmbd * invB * sk[row + c] * dense_scale;
+    // dense_n given (PROPOSED modes): the dense loss has no rank-1 term, cp2_dense_weighted_grad does it all
+    v1[row + c] = dense_n ? proj * dq_d : proj * dq_d - lmbd * invB * sk[row + c] * dense_scale;
     if (bg) {
       const float qn = q_neg[row + c];
       const float dqneg = e_nq * rZ * qp * invB * inv_tg;
@@ -97,7 +98,7 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
   }
   if (tid == 0) {
     terms[2 * b] = logf(Z) + (1.f - l_pos) * inv_tg;                 // -log softmax at the positive
-    terms[2 * b + 1] = r1[5] / Bm - r1[3] * dense_scale;               // loss_dense of this image
+    terms[2 * b + 1] = dense_n ? dense_n[b] : r1[5] / Bm - r1[3] * dense_scale;   // loss_dense of this image
     l_pos_out[b] = l_pos;
     alpha[b] = lmbd * invB * inv_tl / Bm;
   }
@@ -147,18 +148,19 @@ loss_finalize_kernel(const float *__restrict__ terms, const float *__restrict__ 
 extern "C" int cp2_loss_combine(const float *q_pos, const float *k_pos, const float *q_neg, const float *k_neg,
                                 const float *sq, const float *sk, const float *norms_q, const float *z,
                                 const float *G, const float *lse, const int32_t *key_count,
-                                const float *mask_a, float *out, float *l_pos, float *alpha, float *v1,
+                                const float *mask_a, const float *dense_n, float *out, float *l_pos, float *alpha, float *v1,
                                 float *v2, float *scratch, float inv_tau_global, float inv_tau_dense,
                                 float lmbd_dense, int B, int C, int P, void *stream) {
   CP2_REQUIRE(B > 0 && C > 0 && P > 0, "cp2_loss_combine: bad shape B=%d C=%d P=%d", B, C, P);
-  CP2_REQUIRE(q_pos && k_pos && sq && sk && norms_q && z && G && lse && key_count && mask_a && out && l_pos &&
-              alpha && v1 && scratch, "cp2_loss_combine: null pointer");
+  CP2_REQUIRE(q_pos && k_pos && norms_q && z && G && key_count && mask_a && out && l_pos && alpha && v1 && scratch,
+              "cp2_loss_combine: null pointer");
+  CP2_REQUIRE(dense_n || (sq && sk && lse), "cp2_loss_combine: sq, sk and lse are needed unless dense_n is given");
   CP2_REQUIRE((q_neg == nullptr) == (k_neg == nullptr) && (q_neg == nullptr) == (v2 == nullptr),
               "cp2_loss_combine: q_neg, k_neg and v2 go together (include_background)");
   CP2_REQUIRE(inv_tau_global > 0.f && inv_tau_dense > 0.f, "cp2_loss_combine: bad temperature");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   loss_combine_kernel<<<B, 128, 0, st>>>(q_pos, k_pos, q_neg, k_neg, sq, sk, norms_q, z, G, lse, key_count, mask_a,
-                                         scratch, l_pos, alpha, v1, v2, inv_tau_global, inv_tau_dense, lmbd_dense,
+                                         dense_n, scratch, l_pos, alpha, v1, v2, inv_tau_global, inv_tau_dense, lmbd_dense,
                                          B, C, P);
   CP2_LAUNCH_CHECK();
   loss_finalize_kernel<<<1, 256, 0, st>>>(scratch, q_pos, k_pos, out, lmbd_dense, B, C);

@@ -238,12 +238,13 @@ def enqueue(keys_all, queue, queue_ptr):
 
 # ------------------------------------------------- fused loss (a5 + a6 + a7 + a12)
 def loss_combine(q_pos, k_pos, q_neg, k_neg, sq, sk, norms_q, z, G, lse, key_count, mask_a, temp_global,
-                 temp_local, lmbd_dense):
+                 temp_local, lmbd_dense, dense_n=None):
     """cp2_loss_combine: the [B,C]/[B]-sized remainder of the loss (2 launches).
     -> out [5] = (loss, loss_ins, loss_dense, std meter of q_pos, std meter of k_pos), l_pos [B],
-       alpha [B], v1 [B,C], v2 [B,C]|None (inputs of cp2_dense_grad for upstream gradient 1)."""
+       alpha [B], v1 [B,C], v2 [B,C]|None (inputs of cp2_dense_grad for upstream gradient 1).
+    dense_n [B] (PROPOSED modes): per-image dense losses from dense_weighted_lse; sq, sk, lse are then unused."""
     B, C = q_pos.shape
-    P = lse.shape[1]
+    P = mask_a.shape[1]
     dev = q_pos.device
     out = torch.empty((5,), device=dev, dtype=torch.float32)
     l_pos = torch.empty((B,), device=dev, dtype=torch.float32)
@@ -252,8 +253,8 @@ def loss_combine(q_pos, k_pos, q_neg, k_neg, sq, sk, norms_q, z, G, lse, key_cou
     v2 = torch.empty((B, C), device=dev, dtype=torch.float32) if q_neg is not None else None
     scratch = torch.empty((B, 2), device=dev, dtype=torch.float32)
     _call("cp2_loss_combine", 2, _lib.load().cp2_loss_combine, _ptr(q_pos), _ptr(k_pos), _ptr(q_neg), _ptr(k_neg),
-          _ptr(sq), _ptr(sk), _ptr(norms_q), _ptr(z), _ptr(G), _ptr(lse), _ptr(key_count), _ptr(mask_a), _ptr(out),
-          _ptr(l_pos), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(scratch), 1.0 / float(temp_global),
+          _ptr(sq), _ptr(sk), _ptr(norms_q), _ptr(z), _ptr(G), _ptr(lse), _ptr(key_count), _ptr(mask_a), _ptr(dense_n),
+          _ptr(out), _ptr(l_pos), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(scratch), 1.0 / float(temp_global),
           1.0 / float(temp_local), float(lmbd_dense), B, C, P, _stream())
     return out, l_pos, alpha, v1, v2
 
@@ -302,11 +303,110 @@ class CP2LossFunction(torch.autograd.Function):
         return dq.reshape(ctx.q_shape), None, None, None, None, None, None, None, None
 
 
+# ------------------------------------------------- f3: PROPOSED-mode dense loss
+NEGATIVE_CODES = {"NONE": 0, "FIXED": 1, "AVERAGE": 2, "HARD": 0}   # HARD: a no-op in the reference (Appendix A.8)
+
+
+class PairWeights:
+    """The id maps and scalars that define w[x,y] and the negative squash (builder.py:1204-1243, 1332-1386).
+    ids: four int64 maps [B,H,W] (full resolution, sub-sampled inside the kernels at `output_stride`)."""
+
+    def __init__(self, pixel_ids_a, pixel_ids_b, region_ids_a, region_ids_b, output_stride, w_pixel, w_region,
+                 w_not, negative_type="NONE", negative_scale=2.0):
+        name = getattr(negative_type, "name", negative_type)
+        if name not in NEGATIVE_CODES:
+            raise NotImplementedError(f"negative_type {name}: the per-sample nanquantile centre (builder.py:1358-1374) "
+                                      "is not built")
+        self.ids = []
+        for t in (pixel_ids_a, pixel_ids_b, region_ids_a, region_ids_b):
+            _need_cuda(t)
+            if t.dtype != torch.int64 or t.dim() != 3:
+                raise TypeError("id maps must be int64 [B,H,W]")
+            self.ids.append(t.contiguous())
+        self.h, self.w = self.ids[0].shape[1:]
+        self.os = int(output_stride)
+        self.scalars = (float(w_pixel), float(w_region), float(w_not), NEGATIVE_CODES[name], float(negative_scale))
+
+    def _args(self):
+        return [_ptr(t) for t in self.ids]
+
+    def _tail(self, inv_tau, B, C, P):
+        wp, wr, wn, code, scale = self.scalars
+        return (wp, wr, wn, code, scale, float(inv_tau), B, C, P, self.h, self.w, self.os, _stream())
+
+
+def dense_weighted_lse(qhat_t, khat_t, mask_a, mask_b, pw, pos_q, neg_q, pos_k, neg_k, inv_tau):
+    """cp2_dense_weighted_lse -> (lse [B,P], dense_n [B], wstats [B,3], key_count [B] int32)."""
+    B, P, C = qhat_t.shape
+    lib, dev = _lib.load(), qhat_t.device
+    lse = torch.empty((B, P), device=dev, dtype=torch.float32)
+    dense_n = torch.empty((B,), device=dev, dtype=torch.float32)
+    wstats = torch.empty((B, 3), device=dev, dtype=torch.float32)
+    count = torch.empty((B,), device=dev, dtype=torch.int32)
+    scratch = torch.empty((B, lib.cp2_dense_weighted_tiles(P)), device=dev, dtype=torch.float32)
+    _call("cp2_dense_weighted_lse", 3, lib.cp2_dense_weighted_lse, _ptr(qhat_t), _ptr(khat_t), _ptr(mask_a),
+          _ptr(mask_b), *pw._args(), _ptr(pos_q), _ptr(neg_q), _ptr(pos_k), _ptr(neg_k), _ptr(lse), _ptr(dense_n),
+          _ptr(wstats), _ptr(count), _ptr(scratch), *pw._tail(inv_tau, B, C, P))
+    return lse, dense_n, wstats, count
+
+
+def dense_weighted_grad(qhat_t, khat_t, mask_a, mask_b, pw, lse, wstats, inv_norm, alpha, v1, v2, inv_tau, gscale=None):
+    """cp2_dense_weighted_grad -> dq [B,C,P]."""
+    B, P, C = qhat_t.shape
+    dq = torch.empty((B, C, P), device=qhat_t.device, dtype=torch.float32)
+    _call("cp2_dense_weighted_grad", 1, _lib.load().cp2_dense_weighted_grad, _ptr(qhat_t), _ptr(khat_t), _ptr(mask_a),
+          _ptr(mask_b), *pw._args(), _ptr(lse), _ptr(wstats), _ptr(inv_norm), _ptr(alpha), _ptr(v1), _ptr(v2),
+          _ptr(gscale), _ptr(dq), *pw._tail(inv_tau, B, C, P))
+    return dq
+
+
+class CP2WeightedLossFunction(torch.autograd.Function):
+    """CP2LossFunction for the PROPOSED modes: same outputs, the dense loss with
+    pair weights and the negative squash.  Forward = cp2_prep_features x 2 (keys not compacted),
+    cp2_global_nce, cp2_dense_weighted_lse, cp2_loss_combine; backward = cp2_dense_weighted_grad."""
+
+    @staticmethod
+    def forward(ctx, q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense, include_background, pw):
+        B, C = q.shape[0], q.shape[1]
+        qf = _f32c(q.detach()).reshape(B, C, -1)
+        kf = _f32c(k.detach()).reshape(B, C, -1)
+        mask_a, mask_b = _f32c(mask_a), _f32c(mask_b)
+        tg, tl = float(temp_global), float(temp_local)
+        qh, q_inv, sq, nsq, _, q_pos, q_neg, norms_q = prep_features(qf, mask_a, unit=True)
+        kh, _, sk, nsk, _, k_pos, k_neg, _ = prep_features(kf, mask_b, unit=True)
+        z, G = global_nce(q_pos, queue, 1.0 / tg)
+        lse, dense_n, wstats, kcnt = dense_weighted_lse(qh, kh, mask_a, mask_b, pw, sq, nsq, sk, nsk, 1.0 / tl)
+        bg = bool(include_background)
+        out, l_pos, alpha, v1, v2 = loss_combine(q_pos, k_pos, q_neg if bg else None, k_neg if bg else None,
+                                                 None, None, norms_q, z, G, None, kcnt, mask_a, tg, tl, lmbd_dense,
+                                                 dense_n=dense_n)
+        ctx.save_for_backward(qh, kh, lse, mask_a, mask_b, wstats, q_inv, alpha, v1, v2)
+        ctx.inv_tl, ctx.pw, ctx.q_shape = 1.0 / tl, pw, q.shape
+        loss, loss_ins, loss_dense, meters = out[0], out[1], out[2], out[3:]
+        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters)
+        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters
+
+    @staticmethod
+    def backward(ctx, g_loss, *_unused):
+        qh, kh, lse, mask_a, mask_b, wstats, q_inv, alpha, v1, v2 = ctx.saved_tensors
+        g = g_loss.detach().reshape(1)
+        if g.dtype != torch.float32 or not g.is_contiguous():
+            g = g.float().contiguous()
+        dq = dense_weighted_grad(qh, kh, mask_a, mask_b, ctx.pw, lse, wstats, q_inv, alpha, v1, v2, ctx.inv_tl, gscale=g)
+        return (dq.reshape(ctx.q_shape),) + (None,) * 9
+
+
 def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_dense=0.2,
-             include_background=False):
-    """-> (loss, loss_ins, loss_dense, k_pos, q_pos, stats); only `loss` has a gradient (to q)."""
-    loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters = CP2LossFunction.apply(
-        q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense, include_background)
+             include_background=False, pair_weights=None):
+    """-> (loss, loss_ins, loss_dense, k_pos, q_pos, stats); only `loss` has a gradient (to q).
+    pair_weights: None (MappingType.CP2 / NegativeType.NONE, the tensor-core path) or a PairWeights."""
+    if pair_weights is None:
+        res = CP2LossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense,
+                                    include_background)
+    else:
+        res = CP2WeightedLossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense,
+                                            include_background, pair_weights)
+    loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters = res
     nan = float("nan")       # the arg-max / top-1 meters need the materialised logits: MODEL(track_accuracy=True)
     stats = {"l_pos": l_pos, "acc_ins": nan, "acc_seg": nan, "std_q_pos": meters[0], "std_k_pos": meters[1]}
     return loss, loss_ins, loss_dense, k_pos, q_pos, stats

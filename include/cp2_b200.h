@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CP2_ABI_VERSION 5
+#define CP2_ABI_VERSION 6
 
 #define CP2_OK 0
 #define CP2_E_INVALID (-1)      /* bad shape / null pointer / unsupported dim          */
@@ -122,13 +122,15 @@ int cp2_global_nce(const float *q_pos, const float *queue, float *z, float *g, f
  *   norms_q  : [B,2] (||sq||, ||neg_sum_q||) from cp2_prep_features
  *   z, G     : [B], [B,C] from cp2_global_nce ; lse : [B,P] from cp2_dense_lse (compacted key order)
  *   key_count: [B] int32 foreground keys per image ; mask_a : [B,P] f32
+ *   dense_n  : NULL, or [B] per-image dense losses from cp2_dense_weighted_lse (PROPOSED modes): then
+ *              sq, sk and lse are not read and v1 carries the global loss's gradient only
  *   out      : [5] f32 = {loss, loss_ins, loss_dense, mean_c std_b(q_pos), mean_c std_b(k_pos)}
  *   l_pos [B]; alpha [B], v1 [B,C], v2 [B,C] : inputs of cp2_dense_grad for upstream gradient 1
  *   scratch  : [B,2] f32 */
 int cp2_loss_combine(const float *q_pos, const float *k_pos, const float *q_neg, const float *k_neg,
                      const float *sq, const float *sk, const float *norms_q, const float *z, const float *G,
-                     const float *lse, const int32_t *key_count, const float *mask_a, float *out,
-                     float *l_pos, float *alpha, float *v1, float *v2, float *scratch, float inv_tau_global,
+                     const float *lse, const int32_t *key_count, const float *mask_a, const float *dense_n,
+                     float *out, float *l_pos, float *alpha, float *v1, float *v2, float *scratch, float inv_tau_global,
                      float inv_tau_dense, float lmbd_dense, int B, int C, int P, void *stream);
 
 /* K4 — momentum (EMA) update of the key encoder, all parameters in one launch.
@@ -202,6 +204,47 @@ int cp2_mirror_loss_upsampled(const float *s_lo, const float *t_lo, const int64_
                               float *partial, float *out, float *ds_lo, float *dt_lo,
                               float lmbd_compare, float inv_temp, int64_t n_valid, int B, int Cls,
                               int h, int w, int H, int W, void *stream);
+
+/* f3 — dense loss of forward_cp2 in the PROPOSED modes: per-pair correspondence weights from the id maps
+ * and the NegativeType squash, applied on the fly.  Replaces builder.py:1204-1243 (two
+ * get_masked_correlation_map calls, the known-region einsum, corr_weights), :1332-1392 (negative
+ * transform, `* corr_weights`) and :1431-1437 with their autograd — nothing [B,P,P]-sized is stored.
+ *   z[x,y]   = w[x,y] * t(S[x,y]) * inv_tau,  S = qhat_x . khat_y
+ *   w[x,y]   = w_pix if pixel ids agree, else w_reg if region ids agree and are non-zero, else 0;
+ *              then w_not wherever that is 0
+ *   t(s)     = s on label pairs (mask_a[x] != 0 and mask_b[y] != 0) or neg_type 0;
+ *              2/(1+exp(-neg_scale*(s - centre))) - 1 elsewhere, centre = 0 (neg_type 1, FIXED) or the
+ *              image's mean non-label S (neg_type 2, AVERAGE).  NegativeType.HARD is a no-op in the
+ *              reference: pass 0.  MEDIAN is not implemented.
+ *   lse[n,y] = log sum_x exp(z[x,y]);  dense_n[n] = sum_xy a_x b_y (lse_y - z[x,y]) / (sum a * sum b)
+ *   qhat_t, khat_t : [B,P,C] bf16 from cp2_prep_features, keys NOT compacted; masks [B,P] f32 (binary)
+ *   *_ids_*  : [B,ids_h,ids_w] int64 id maps; pixel p = (r,c) of the P = hs*ws lattice reads element
+ *              (r*os + os/2, c*os + os/2), the reference's [OS//2::OS] subsample (builder.py:1165-1186);
+ *              pass os = 1 for maps that are already subsampled
+ *   pos_*, neg_* : [B,C] pooled sums of cp2_prep_features (query / key side), for the AVERAGE centre
+ *   wstats   : [B,3] f32 out = {centre, sum mask_a, sum mask_b}; key_count [B] int32 out
+ *   scratch  : [B, cp2_dense_weighted_tiles(P)] f32.   C in {128, 256}. */
+int cp2_dense_weighted_tiles(int P);
+int cp2_dense_weighted_lse(const void *qhat_t, const void *khat_t, const float *mask_a, const float *mask_b,
+                           const int64_t *pixel_ids_a, const int64_t *pixel_ids_b, const int64_t *region_ids_a,
+                           const int64_t *region_ids_b, const float *pos_q, const float *neg_q,
+                           const float *pos_k, const float *neg_k, float *lse, float *dense_n, float *wstats,
+                           int32_t *key_count, float *scratch, float w_pix, float w_reg, float w_not,
+                           int neg_type, float neg_scale, float inv_tau, int B, int C, int P, int ids_h,
+                           int ids_w, int os, void *stream);
+
+/* f3 backward — d loss / d q for the PROPOSED modes, one launch (recomputes S):
+ *   acc[x,:]  = sum_y b_y (exp(z[x,y] - lse[y]) - a_x / sum a) * w[x,y] * t'(S[x,y]) * khat[y,:]
+ *   dqhat_x   = alpha[n]*acc[x,:] + mask_a[x]*v1[n,:] + (1-mask_a[x])*v2[n,:]
+ *   dq[n,:,x] = (dqhat_x - qhat_x (qhat_x . dqhat_x)) * inv_norm[n,x]         ([B,C,P] f32)
+ * alpha, v1, v2 from cp2_loss_combine called with dense_n; gscale as in cp2_dense_grad. */
+int cp2_dense_weighted_grad(const void *qhat_t, const void *khat_t, const float *mask_a, const float *mask_b,
+                            const int64_t *pixel_ids_a, const int64_t *pixel_ids_b, const int64_t *region_ids_a,
+                            const int64_t *region_ids_b, const float *lse, const float *wstats,
+                            const float *inv_norm, const float *alpha, const float *v1, const float *v2,
+                            const float *gscale, float *dq, float w_pix, float w_reg, float w_not, int neg_type,
+                            float neg_scale, float inv_tau, int B, int C, int P, int ids_h, int ids_w, int os,
+                            void *stream);
 
 #ifdef __cplusplus
 }
