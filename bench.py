@@ -333,6 +333,77 @@ def mirror_sweep(peaks, iters=20):
     return rows
 
 
+# ------------------------------------------------------------------ PROPOSED-mode dense loss microbench
+def weighted_sweep(peaks, iters=20):
+    """Row f3 at configs[1]'s shape (B=32, 14x14, C=128) and at 28x28: cp2_dense_weighted_lse +
+    cp2_dense_weighted_grad (pair weights 10/2/0.5, NegativeType.FIXED) against the eager torch formulation
+    of builder.py:1204-1243, 1289-1292, 1332-1392, 1431-1437 + autograd on the same GPU.  L2 flushed."""
+    import torch
+    import torch.nn.functional as F
+    from cp2_b200 import ops
+    dev = torch.device("cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def timeit(fn, n):
+        ts = []
+        for i in range(n + 3):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record()
+            torch.cuda.synchronize()
+            if i >= 3:
+                ts.append(a.elapsed_time(b) * 1e3)
+        return statistics.median(ts)
+
+    rows = []
+    for B, hw in ((32, 14), (32, 28)):
+        C, P, os_ = 128, hw * hw, 16
+        H = hw * os_
+        g = torch.Generator(device=dev).manual_seed(13)
+        q = torch.randn(B, C, P, device=dev, generator=g)
+        k = torch.randn(B, C, P, device=dev, generator=g)
+        ma = (torch.rand(B, P, device=dev, generator=g) < 0.65).float()
+        mb = (torch.rand(B, P, device=dev, generator=g) < 0.65).float()
+        pa = torch.arange(1, H * H + 1, device=dev).reshape(1, H, H).repeat(B, 1, 1)
+        pb = torch.roll(pa, shifts=(os_, os_), dims=(1, 2)).contiguous()
+        ra = (pa - 1) // (H * 64) * 4 + ((pa - 1) % H) // 64
+        rb = torch.roll(ra, shifts=(os_, os_), dims=(1, 2)).contiguous()
+        wts, scale, inv_tau = (10.0, 2.0, 0.5), 2.0, 1.0 / TAU_D
+        pw = ops.PairWeights(pa, pb, ra, rb, os_, *wts, "FIXED", scale)
+        alpha = torch.full((B,), 1.0 / B, device=dev)
+        v1 = torch.zeros(B, C, device=dev)
+        qh, q_inv, sq, nsq, _ = ops.prep_features(q, ma)
+        kh, _, sk, nsk, _ = ops.prep_features(k, mb)
+
+        def ours():
+            lse, dense_n, wstats, _ = ops.dense_weighted_lse(qh, kh, ma, mb, pw, sq, nsq, sk, nsk, inv_tau)
+            return ops.dense_weighted_grad(qh, kh, ma, mb, pw, lse, wstats, q_inv, alpha, v1, None, inv_tau)
+
+        sub = lambda t: t[:, os_ // 2::os_, os_ // 2::os_].reshape(B, -1)
+        qe = q.clone().requires_grad_()
+
+        def eager():
+            qe.grad = None
+            pix = sub(pa)[:, :, None] == sub(pb)[:, None, :]
+            reg = (sub(ra)[:, :, None] == sub(rb)[:, None, :]) & ((sub(ra)[:, :, None] * sub(rb)[:, None, :]) != 0)
+            w = wts[1] * reg
+            w[pix] = wts[0]
+            w = w + (w == 0) * wts[2]
+            logits = torch.einsum("ncx,ncy->nxy", F.normalize(qe, dim=1), F.normalize(k, dim=1))
+            labels = torch.einsum("nx,ny->nxy", ma, mb)
+            neg = labels == 0
+            logits = torch.where(neg, 2.0 / (1.0 + torch.exp(logits * -scale)) - 1.0, logits) * w * inv_tau
+            nl = -torch.log_softmax(logits, dim=1)
+            ((nl * labels).flatten(1).sum(1) / labels.flatten(1).sum(1)).mean().backward()
+
+        t_ours, t_eager = timeit(ours, iters), timeit(eager, 5)
+        rows.append({"B": B, "P": P, "C": C, "negative_type": "FIXED", "weights": list(wts),
+                     "weighted_lse_grad_us": round(t_ours, 2), "launches": 4, "eager_torch_us": round(t_eager, 1),
+                     "speedup_vs_eager": round(t_eager / t_ours, 1),
+                     "fp32_simt_tflops": round(6.0 * B * P * P * C / t_ours / 1e6, 2)})
+    return rows
+
+
 # ------------------------------------------------------------------------------ own arm
 def algorithmic_work(batch, n_params, world):
     """Per-CALL algorithmic bytes / flops of each C-ABI entry point on the step."""
@@ -515,6 +586,7 @@ def own_arm(args):
             # free the training state first: the 56x56 / C=256 point needs ~3.5 GB
             line["dense_microbench"] = dense_sweep(args, peaks)
             line["mirror_microbench"] = mirror_sweep(peaks)
+            line["weighted_microbench"] = weighted_sweep(peaks)
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_leg()
     if rank == 0:
