@@ -418,6 +418,9 @@ def algorithmic_work(batch, n_params, world):
         "cp2_enqueue": ("hbm", 2 * world * batch * C * 4),
         "cp2_loss_combine": ("hbm", batch * (9 * C + 2 * P) * 4),   # latency-bound: [B,C] / [B,P] operands once
         "cp2_id_iou": ("hbm", 2 * batch * P * (8 + 4)),       # latency-bound: 2P ids + masks per image
+        # f4 arg-max meters, fp32 CUDA cores: counted by the bytes they must read (features / queue once)
+        "cp2_dense_top1": ("hbm", 2 * batch * C * P * 4 + 2 * batch * P * 4),
+        "cp2_global_top1": ("hbm", 4 * C * QUEUE + 8 * batch * C),
     }
 
 

@@ -30,6 +30,10 @@ SIGNATURES = {
     "cp2_dense_weighted_tiles": (c_int, [c_int]),
     "cp2_dense_weighted_lse": (c_int, [c_void_p] * 17 + [c_float] * 3 + [c_int, c_float, c_float] + [c_int] * 6 + [c_void_p]),
     "cp2_dense_weighted_grad": (c_int, [c_void_p] * 16 + [c_float] * 3 + [c_int, c_float, c_float] + [c_int] * 6 + [c_void_p]),
+    "cp2_dense_top1_scratch_floats": (c_int64, [c_int, c_int]),
+    "cp2_dense_top1": (c_int, [c_void_p] * 7 + [c_int] * 3 + [c_void_p]),
+    "cp2_global_top1_scratch_floats": (c_int64, [c_int, c_int]),
+    "cp2_global_top1": (c_int, [c_void_p] * 8 + [c_int] * 3 + [c_void_p]),
     "cp2_mirror_partials": (c_int, [c_int, c_int64]),
     "cp2_mirror_loss": (c_int, [c_void_p] * 8 + [c_float, c_float, c_int64, c_int, c_int, c_int64, c_void_p]),
     "cp2_mirror_up_partials": (c_int, [c_int] * 3),

@@ -163,11 +163,12 @@ class MODEL(nn.Module):
     Extra keyword-only arguments (not in the reference):
       encoder_factory : callable returning one segmentor; replaces `build_segmentor(cfg.model)`
                         (mmseg/mmcv are not installable here).  Called twice (q, k).
-      track_accuracy  : also evaluate the loss-neutral `acc_ins` / `acc_seg` meters (builder.py:1441-1448)
-                        each step.  They need the arg-max over all P x P logits and the top-1 over the
-                        65537 global logits, which the fused kernels never materialise, so this opt-in
-                        branch materialises them with torch ops (the slow "stats"
-                        branch); off by default, the meters then read NaN.
+      track_accuracy  : evaluate the loss-neutral `acc_ins` / `acc_seg` meters (builder.py:1441-1448) each
+                        step, as the reference does.  They are the arg-max over all P x P dense logits
+                        and the top-1 over the 65537 global logits; two fp32 arg-max kernels
+                        (cp2_dense_top1, cp2_global_top1) give them without
+                        materialising either tensor and without a host sync.  On by default; False
+                        skips the four launches and the meters read NaN.
       output_stride   : skip the reference's CPU probe forward (builder.py:392-397) and use
                         this value.  When None the probe runs exactly as in the reference,
                         including its side effect on encoder_q's BN running statistics.
@@ -180,7 +181,7 @@ class MODEL(nn.Module):
                  backbone_type=BackboneType.DEEPLABV3, mapping_type=MappingType.CP2,
                  dense_logits_temp=1, unet_truncated_dec_blocks=2, use_predictor=False,
                  use_avgpool_global=False, use_symmetrical_loss=False, lmbd_coordinate=0,
-                 device=None, *, encoder_factory=None, output_stride=None, track_accuracy=False):
+                 device=None, *, encoder_factory=None, output_stride=None, track_accuracy=True):
         super().__init__()
         self.queue_len = K
         self.momentum = m
@@ -284,23 +285,17 @@ class MODEL(nn.Module):
         self.track_accuracy = bool(track_accuracy)
 
     @torch.no_grad()
-    def _accuracy_stats(self, q, k, mask_a, mask_b, q_pos, k_pos):
-        """builder.py:1441-1448 (+ :1395-1418 for the logits) with torch ops; opt-in, off the hot path."""
-        n = q.shape[0]
-        qh = F.normalize(q.detach().float().flatten(2), dim=1)
-        kh = F.normalize(k.detach().float().flatten(2), dim=1)
-        P = qh.shape[2]
-        idx = torch.einsum("ncx,ncy->nxy", qh, kh).reshape(n, -1).argmax(dim=1)
-        ar = torch.arange(n, device=q.device)
-        acc_seg = (mask_a[ar, idx // P] * mask_b[ar, idx % P]).float().mean() * 100.0
-        parts = [(q_pos * k_pos).sum(dim=1, keepdim=True), q_pos @ self.queue]
-        if self.include_background:
-            q_neg = F.normalize(torch.einsum("ncx,nx->nc", qh, 1.0 - mask_a), dim=1)
-            k_neg = F.normalize(torch.einsum("ncx,nx->nc", kh, 1.0 - mask_b), dim=1)
-            parts += [(q_pos * q_neg).sum(dim=1, keepdim=True), (q_pos * k_neg).sum(dim=1, keepdim=True)]
-        logits = torch.cat(parts, dim=1)
-        acc1 = self._accuracy(logits, torch.zeros(n, dtype=torch.long, device=q.device), topk=(1,))[0]
-        return acc1.reshape(()), acc_seg
+    def _accuracy_stats(self, q, k, mask_a, mask_b, q_pos, k_pos, stats):
+        """builder.py:1441-1448 (+ :1395-1418 for the logits) as two arg-max kernels (cp2_global_top1,
+        cp2_dense_top1): no [B,1+K] and no [B,P,P] tensor, no host sync.  In the PROPOSED modes the dense
+        arg-max would have to run on the weighted logits; that meter then reads NaN."""
+        bg = self.include_background
+        acc1, _ = ops.global_top1(q_pos, k_pos, self.queue, stats["q_neg"] if bg else None,
+                                  stats["k_neg"] if bg else None)
+        if self._weighted:
+            return acc1, float("nan")
+        acc_seg, _ = ops.dense_top1(q, k, mask_a, mask_b)
+        return acc1, acc_seg
 
     # ----------------------------------------------------------- a4 (metrics)
     # builder.py:1252-1257 extends two python lists with per-image IoUs every step, through a .cpu() sync.
@@ -443,7 +438,7 @@ class MODEL(nn.Module):
             q, k, mask_a, mask_b, self.queue, self.temp_global, self.temp_local, self.lmbd_dense_loss,
             self.include_background, pair_weights)
         if self.track_accuracy:                                # uses the queue BEFORE this step's enqueue
-            stats["acc_ins"], stats["acc_seg"] = self._accuracy_stats(q, k, mask_a, mask_b, q_pos, k_pos)
+            stats["acc_ins"], stats["acc_seg"] = self._accuracy_stats(q, k, mask_a, mask_b, q_pos, k_pos, stats)
         self._dequeue_and_enqueue(k_pos)                       # builder.py:1426
 
         if new_epoch and self.rank == 0:

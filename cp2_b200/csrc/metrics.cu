@@ -1,0 +1,262 @@
+// f4 — the two accuracy meters forward_cp2 logs every step, without materialising the logits:
+//   acc_seg (reference builder.py:1442-1448): arg-max of the [P*P] dense logits of each image, hit if
+//           that pair is a label pair (mask_a[x] * mask_b[y]);
+//   acc_ins (builder.py:1441, 1690-1706): top-1 of [l_pos, q_pos @ queue, (l_neg_q, l_neg_k)] is l_pos.
+// Both are arg-max decisions, so they are taken in fp32 on CUDA cores straight from the fp32 inputs
+// (bf16 operands could flip near-ties): ~0.3 + 0.5 GFLOP at configs[1], the queue is still L2-resident
+// from cp2_global_nce.  Positive scalings (1/tau, all-ones weights) do not move an arg-max and are skipped.
+#include "common.cuh"
+
+namespace {
+
+constexpr int MT = 256;                 // threads per CTA
+constexpr int YT = 32;                  // key pixels per CTA (lane = key)
+constexpr int XT = 64;                  // query pixels per chunk (warp w owns rows 8w..8w+7)
+constexpr float kEps = 1e-12f;          // F.normalize eps
+
+struct Best { float v; int i; };
+__device__ __forceinline__ void take(Best &a, float v, int i) {
+  if (v > a.v || (v == a.v && i < a.i)) { a.v = v; a.i = i; }     // first occurrence on ties
+}
+
+// rows [c][W] <- feat[b, c, p0 .. p0+W) (zero past P); feat is [B,C,P] f32
+template <int W>
+__device__ __forceinline__ void load_cols(const float *feat_b, int C, int P, int p0, float *dst) {
+  for (int i = threadIdx.x; i < C * W; i += MT) {
+    const int c = i / W, j = i - c * W;
+    dst[i] = p0 + j < P ? feat_b[(long long)c * P + p0 + j] : 0.f;
+  }
+}
+
+// One CTA = 32 key pixels of one image against all query pixels: best (value, flat index x*P+y) of the tile.
+__global__ void __launch_bounds__(MT)
+dense_top1_kernel(const float *__restrict__ q, const float *__restrict__ k, float *__restrict__ part_v,
+                  int *__restrict__ part_i, int C, int P) {
+  extern __shared__ __align__(16) float sm[];
+  float *ks = sm;                        // [C][32]
+  float *qs = sm + C * YT;               // [C][64]
+  __shared__ float invk_s[YT], invq_s[XT];
+  __shared__ float red_v[MT / 32];
+  __shared__ int red_i[MT / 32];
+  const int b = blockIdx.y, y0 = blockIdx.x * YT, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const float *qb = q + (long long)b * C * P, *kb = k + (long long)b * C * P;
+  load_cols<YT>(kb, C, P, y0, ks);
+  __syncthreads();
+  if (warp == 0) {
+    float s = 0.f;
+    for (int c = 0; c < C; ++c) s = fmaf(ks[c * YT + lane], ks[c * YT + lane], s);
+    invk_s[lane] = 1.f / fmaxf(sqrtf(s), kEps);
+  }
+  const int y = y0 + lane;
+  Best best{-INFINITY, 0x7fffffff};
+  for (int x0 = 0; x0 < P; x0 += XT) {
+    __syncthreads();
+    load_cols<XT>(qb, C, P, x0, qs);
+    __syncthreads();
+    if (threadIdx.x < XT) {
+      float s = 0.f;
+      for (int c = 0; c < C; ++c) s = fmaf(qs[c * XT + threadIdx.x], qs[c * XT + threadIdx.x], s);
+      invq_s[threadIdx.x] = 1.f / fmaxf(sqrtf(s), kEps);
+    }
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+    for (int c = 0; c < C; ++c) {
+      const float kv = ks[c * YT + lane];
+      const float4 a = *reinterpret_cast<const float4 *>(qs + c * XT + warp * 8);
+      const float4 d = *reinterpret_cast<const float4 *>(qs + c * XT + warp * 8 + 4);
+      acc[0] = fmaf(a.x, kv, acc[0]); acc[1] = fmaf(a.y, kv, acc[1]);
+      acc[2] = fmaf(a.z, kv, acc[2]); acc[3] = fmaf(a.w, kv, acc[3]);
+      acc[4] = fmaf(d.x, kv, acc[4]); acc[5] = fmaf(d.y, kv, acc[5]);
+      acc[6] = fmaf(d.z, kv, acc[6]); acc[7] = fmaf(d.w, kv, acc[7]);
+    }
+    __syncthreads();                     // invq_s written
+    if (y < P) {
+      const float ik = invk_s[lane];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int x = x0 + warp * 8 + i;
+        if (x < P) take(best, acc[i] * invq_s[warp * 8 + i] * ik, x * P + y);
+      }
+    }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    const float v = __shfl_down_sync(0xffffffffu, best.v, off);
+    const int i = __shfl_down_sync(0xffffffffu, best.i, off);
+    take(best, v, i);
+  }
+  if (lane == 0) { red_v[warp] = best.v; red_i[warp] = best.i; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < MT / 32; ++w) take(best, red_v[w], red_i[w]);
+    part_v[(long long)b * gridDim.x + blockIdx.x] = best.v;
+    part_i[(long long)b * gridDim.x + blockIdx.x] = best.i;
+  }
+}
+
+// hit[b] = mask_a[b, x*] * mask_b[b, y*] at the image's arg-max pair; acc = 100 * mean(hit).  One CTA.
+__global__ void __launch_bounds__(MT)
+dense_top1_finalize_kernel(const float *__restrict__ part_v, const int *__restrict__ part_i,
+                           const float *__restrict__ mask_a, const float *__restrict__ mask_b,
+                           float *__restrict__ hit, float *__restrict__ acc, int B, int P, int tiles) {
+  __shared__ float red[MT / 32];
+  float s = 0.f;
+  for (int b = threadIdx.x; b < B; b += MT) {
+    Best best{-INFINITY, 0x7fffffff};
+    for (int t = 0; t < tiles; ++t) take(best, part_v[(long long)b * tiles + t], part_i[(long long)b * tiles + t]);
+    float h = 0.f;
+    if (best.i != 0x7fffffff) {
+      const int x = best.i / P, y = best.i - x * P;
+      h = mask_a[(long long)b * P + x] * mask_b[(long long)b * P + y];
+    }
+    hit[b] = h;
+    s += h;
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < MT / 32; ++w) t += red[w];
+    acc[0] = t * (100.f / (float)B);
+  }
+}
+
+// max_k q_pos[r] . queue[:,k] over this CTA's 256-column blocks, 32 rows at a time (thread = column).
+__global__ void __launch_bounds__(MT)
+global_top1_kernel(const float *__restrict__ q_pos, const float *__restrict__ queue, float *__restrict__ part,
+                   int B, int C, int K) {
+  extern __shared__ __align__(16) float qT[];       // [C][32]
+  __shared__ float red[MT / 32][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nblk = (K + MT - 1) / MT;
+  for (int r0 = 0; r0 < B; r0 += 32) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < C * 32; i += MT) {
+      const int c = i >> 5, r = i & 31;
+      qT[i] = r0 + r < B ? q_pos[(long long)(r0 + r) * C + c] : 0.f;
+    }
+    __syncthreads();
+    float m[32];
+#pragma unroll
+    for (int r = 0; r < 32; ++r) m[r] = -INFINITY;
+    for (int blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+      const int col = blk * MT + threadIdx.x;
+      if (col >= K) continue;
+      float acc[32];
+#pragma unroll
+      for (int r = 0; r < 32; ++r) acc[r] = 0.f;
+#pragma unroll 2
+      for (int c = 0; c < C; ++c) {
+        const float kv = queue[(long long)c * K + col];
+#pragma unroll
+        for (int r4 = 0; r4 < 8; ++r4) {
+          const float4 qv = *reinterpret_cast<const float4 *>(qT + c * 32 + r4 * 4);
+          acc[4 * r4] = fmaf(qv.x, kv, acc[4 * r4]);
+          acc[4 * r4 + 1] = fmaf(qv.y, kv, acc[4 * r4 + 1]);
+          acc[4 * r4 + 2] = fmaf(qv.z, kv, acc[4 * r4 + 2]);
+          acc[4 * r4 + 3] = fmaf(qv.w, kv, acc[4 * r4 + 3]);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 32; ++r) m[r] = fmaxf(m[r], acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < 32; ++r) {
+      float v = m[r];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, off));
+      if (lane == 0) red[warp][r] = v;
+    }
+    __syncthreads();
+    if (warp == 0 && r0 + lane < B) {
+      float v = red[0][lane];
+      for (int w = 1; w < MT / 32; ++w) v = fmaxf(v, red[w][lane]);
+      part[(long long)blockIdx.x * B + r0 + lane] = v;
+    }
+  }
+}
+
+// hit[r] = l_pos > every other logit of row r; acc = 100 * mean(hit).  One CTA, one warp per row.
+__global__ void __launch_bounds__(MT)
+global_top1_finalize_kernel(const float *__restrict__ part, const float *__restrict__ q_pos,
+                            const float *__restrict__ k_pos, const float *__restrict__ q_neg,
+                            const float *__restrict__ k_neg, float *__restrict__ hit, float *__restrict__ acc,
+                            int B, int C, int nctas) {
+  __shared__ float red[MT / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float s = 0.f;
+  for (int r = warp; r < B; r += MT / 32) {
+    float lp = 0.f, lq = 0.f, lk = 0.f, mx = -INFINITY;
+    for (int c = lane; c < C; c += 32) {
+      const float qp = q_pos[(long long)r * C + c];
+      lp = fmaf(qp, k_pos[(long long)r * C + c], lp);
+      if (q_neg) { lq = fmaf(qp, q_neg[(long long)r * C + c], lq); lk = fmaf(qp, k_neg[(long long)r * C + c], lk); }
+    }
+    for (int t = lane; t < nctas; t += 32) mx = fmaxf(mx, part[(long long)t * B + r]);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      lp += __shfl_xor_sync(0xffffffffu, lp, off);
+      lq += __shfl_xor_sync(0xffffffffu, lq, off);
+      lk += __shfl_xor_sync(0xffffffffu, lk, off);
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    }
+    if (q_neg) mx = fmaxf(mx, fmaxf(lq, lk));
+    const float h = lp > mx ? 1.f : 0.f;
+    if (lane == 0) { hit[r] = h; s += h; }
+  }
+  if (lane == 0) red[warp] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < MT / 32; ++w) t += red[w];
+    acc[0] = t * (100.f / (float)B);
+  }
+}
+
+int top1_ctas(int K) {
+  const int nblk = cp2_cdiv(K, MT), cap = 2 * cp2_num_sms();
+  return nblk < cap ? nblk : cap;
+}
+
+}  // namespace
+
+extern "C" int64_t cp2_dense_top1_scratch_floats(int B, int P) { return 2LL * B * cp2_cdiv(P, YT); }
+
+extern "C" int cp2_dense_top1(const float *q, const float *k, const float *mask_a, const float *mask_b, float *hit,
+                              float *acc, float *scratch, int B, int C, int P, void *stream) {
+  CP2_REQUIRE(B > 0 && P > 0 && C > 0 && C <= 512 && (long long)P * P < 0x7fffffffLL,
+              "cp2_dense_top1: bad shape B=%d C=%d P=%d", B, C, P);
+  CP2_REQUIRE(q && k && mask_a && mask_b && hit && acc && scratch, "cp2_dense_top1: null pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int tiles = cp2_cdiv(P, YT);
+  float *part_v = scratch;
+  int *part_i = reinterpret_cast<int *>(scratch + (size_t)B * tiles);
+  const size_t smem = (size_t)C * (YT + XT) * sizeof(float);
+  CP2_CUDA(cudaFuncSetAttribute(dense_top1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dense_top1_kernel<<<dim3(tiles, B), MT, smem, st>>>(q, k, part_v, part_i, C, P);
+  CP2_LAUNCH_CHECK();
+  dense_top1_finalize_kernel<<<1, MT, 0, st>>>(part_v, part_i, mask_a, mask_b, hit, acc, B, P, tiles);
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}
+
+extern "C" int64_t cp2_global_top1_scratch_floats(int B, int K) { return (int64_t)B * top1_ctas(K); }
+
+extern "C" int cp2_global_top1(const float *q_pos, const float *k_pos, const float *q_neg, const float *k_neg,
+                               const float *queue, float *hit, float *acc, float *scratch, int B, int C, int K,
+                               void *stream) {
+  CP2_REQUIRE(B > 0 && K > 0 && C > 0 && C <= 1024, "cp2_global_top1: bad shape B=%d C=%d K=%d", B, C, K);
+  CP2_REQUIRE(q_pos && k_pos && queue && hit && acc && scratch, "cp2_global_top1: null pointer");
+  CP2_REQUIRE((q_neg == nullptr) == (k_neg == nullptr), "cp2_global_top1: q_neg and k_neg go together");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nctas = top1_ctas(K);
+  const size_t smem = (size_t)C * 32 * sizeof(float);
+  CP2_CUDA(cudaFuncSetAttribute(global_top1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  global_top1_kernel<<<nctas, MT, smem, st>>>(q_pos, queue, scratch, B, C, K);
+  CP2_LAUNCH_CHECK();
+  global_top1_finalize_kernel<<<1, MT, 0, st>>>(scratch, q_pos, k_pos, q_neg, k_neg, hit, acc, B, C, nctas);
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}

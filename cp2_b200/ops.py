@@ -290,8 +290,8 @@ class CP2LossFunction(torch.autograd.Function):
         ctx.inv_tl = 1.0 / tl
         ctx.q_shape = q.shape
         loss, loss_ins, loss_dense, meters = out[0], out[1], out[2], out[3:]
-        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters)
-        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters
+        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg)
+        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg
 
     @staticmethod
     def backward(ctx, g_loss, *_unused):
@@ -383,8 +383,8 @@ class CP2WeightedLossFunction(torch.autograd.Function):
         ctx.save_for_backward(qh, kh, lse, mask_a, mask_b, wstats, q_inv, alpha, v1, v2)
         ctx.inv_tl, ctx.pw, ctx.q_shape = 1.0 / tl, pw, q.shape
         loss, loss_ins, loss_dense, meters = out[0], out[1], out[2], out[3:]
-        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters)
-        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters
+        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg)
+        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg
 
     @staticmethod
     def backward(ctx, g_loss, *_unused):
@@ -406,10 +406,47 @@ def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_
     else:
         res = CP2WeightedLossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense,
                                             include_background, pair_weights)
-    loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters = res
+    loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg = res
     nan = float("nan")       # the arg-max / top-1 meters need the materialised logits: MODEL(track_accuracy=True)
-    stats = {"l_pos": l_pos, "acc_ins": nan, "acc_seg": nan, "std_q_pos": meters[0], "std_k_pos": meters[1]}
+    stats = {"l_pos": l_pos, "acc_ins": nan, "acc_seg": nan, "std_q_pos": meters[0], "std_k_pos": meters[1],
+             "q_neg": q_neg, "k_neg": k_neg}
     return loss, loss_ins, loss_dense, k_pos, q_pos, stats
+
+
+# ------------------------------------------------------------- f4: accuracy meters
+@torch.no_grad()
+def dense_top1(q, k, mask_a, mask_b):
+    """builder.py:1442-1448 -> (acc_seg 0-d, hit [B]).  q, k [B,C,P] or [B,C,h,w] f32 encoder outputs."""
+    _need_cuda(q, k, mask_a, mask_b)
+    B, C = q.shape[0], q.shape[1]
+    q, k = _f32c(q.detach()).reshape(B, C, -1), _f32c(k.detach()).reshape(B, C, -1)
+    mask_a, mask_b = _f32c(mask_a), _f32c(mask_b)
+    P = q.shape[2]
+    lib, dev = _lib.load(), q.device
+    hit = torch.empty((B,), device=dev, dtype=torch.float32)
+    acc = torch.empty((1,), device=dev, dtype=torch.float32)
+    scratch = torch.empty((lib.cp2_dense_top1_scratch_floats(B, P),), device=dev, dtype=torch.float32)
+    _call("cp2_dense_top1", 2, lib.cp2_dense_top1, _ptr(q), _ptr(k), _ptr(mask_a), _ptr(mask_b), _ptr(hit), _ptr(acc),
+          _ptr(scratch), B, C, P, _stream())
+    return acc[0], hit
+
+
+@torch.no_grad()
+def global_top1(q_pos, k_pos, queue, q_neg=None, k_neg=None):
+    """builder.py:1441 (top-1 of `_accuracy`) -> (acc_ins 0-d, hit [B]).  Call BEFORE the enqueue."""
+    _need_cuda(q_pos, k_pos, queue)
+    q_pos, k_pos = _f32c(q_pos), _f32c(k_pos)
+    B, C = q_pos.shape
+    assert queue.dtype == torch.float32 and queue.is_contiguous() and queue.shape[0] == C
+    K = queue.shape[1]
+    lib, dev = _lib.load(), q_pos.device
+    hit = torch.empty((B,), device=dev, dtype=torch.float32)
+    acc = torch.empty((1,), device=dev, dtype=torch.float32)
+    scratch = torch.empty((lib.cp2_global_top1_scratch_floats(B, K),), device=dev, dtype=torch.float32)
+    _call("cp2_global_top1", 2, lib.cp2_global_top1, _ptr(q_pos), _ptr(k_pos),
+          _ptr(_f32c(q_neg) if q_neg is not None else None), _ptr(_f32c(k_neg) if k_neg is not None else None),
+          _ptr(queue), _ptr(hit), _ptr(acc), _ptr(scratch), B, C, K, _stream())
+    return acc[0], hit
 
 
 # ------------------------------------------------------------- a2 + a4

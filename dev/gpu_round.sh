@@ -18,7 +18,7 @@ if [ "$1" != "nocu" ]; then
   echo "== ncu launch list exit $?"
   timeout 300 $STEP > gpurun_out/plain_step2.log 2>&1 &&
   timeout 900 ncu --profile-from-start off --set full --clock-control none --import-source on \
-      -k regex:'ema_kernel|global_nce_kernel|global_finalize|composite_kernel|prep_kernel|enqueue_kernel|dense_' -c 14 \
+      -k regex:'ema_kernel|global_nce_kernel|global_finalize|composite_kernel|prep_kernel|enqueue_kernel|dense_|top1' -c 20 \
       -o gpurun_out/prof_step -f $STEP > gpurun_out/ncu_step_full.log 2>&1
   echo "== ncu step full exit $?"
   unset CP2_BENCH_CUDA_PROFILER

@@ -246,6 +246,25 @@ int cp2_dense_weighted_grad(const void *qhat_t, const void *khat_t, const float 
                             float neg_scale, float inv_tau, int B, int C, int P, int ids_h, int ids_w, int os,
                             void *stream);
 
+/* f4 — acc_seg without the [B,P,P] logits.  Replaces builder.py:1442-1448:
+ *   hit[n] = mask_a[n,x*] * mask_b[n,y*] at (x*,y*) = argmax_{x,y} qhat_x . khat_y (first occurrence, flat
+ *   index x*P+y as the reference's reshape); acc[0] = 100 * mean_n hit[n].
+ * q, k: the encoder outputs [B,C,P] f32 (normalised inside, fp32 CUDA-core dot products so that near-ties
+ * fall as in the reference's fp32 einsum).  scratch: cp2_dense_top1_scratch_floats(B,P) f32. */
+int64_t cp2_dense_top1_scratch_floats(int B, int P);
+int cp2_dense_top1(const float *q, const float *k, const float *mask_a, const float *mask_b, float *hit,
+                   float *acc, float *scratch, int B, int C, int P, void *stream);
+
+/* f4 — acc_ins (top-1) without the [B,1+K] logits.  Replaces builder.py:1441 / _accuracy :1690-1706 for k=1:
+ *   hit[n] = 1 if q_pos[n].k_pos[n] > max(max_k q_pos[n].queue[:,k], q_pos[n].q_neg[n], q_pos[n].k_neg[n])
+ *   (the last two only when q_neg/k_neg are given: include_background); acc[0] = 100 * mean_n hit[n].
+ * Reads the queue BEFORE this step's enqueue, like the reference.  scratch:
+ * cp2_global_top1_scratch_floats(B,K) f32. */
+int64_t cp2_global_top1_scratch_floats(int B, int K);
+int cp2_global_top1(const float *q_pos, const float *k_pos, const float *q_neg, const float *k_neg,
+                    const float *queue, float *hit, float *acc, float *scratch, int B, int C, int K,
+                    void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -387,3 +387,52 @@ def test_id_iou_vs_oracle(ops, B, H, W, os_):
         iou, ioum = ops.id_iou(dev(ids_a), dev(ids_b), dev(ma), dev(mb), os_)
         assert torch.equal(iou.cpu(), ref["iou"]), kind
         assert torch.equal(ioum.cpu(), ref["iou_masked"]), kind
+
+
+# ------------------------------------------------------------------ f4: accuracy meters
+@pytest.mark.parametrize("B,C,hw", [(4, 128, 14), (3, 256, 9), (2, 128, 28), (5, 64, 7)])
+def test_dense_top1_vs_oracle(ops, B, C, hw):
+    """cp2_dense_top1 against builder.py:1442-1448 as restated by the oracle, image by image."""
+    g = torch.Generator().manual_seed(31 * hw + B)
+    P = hw * hw
+    q = torch.randn(B, C, P, generator=g)
+    k = torch.randn(B, C, P, generator=g)
+    ma = (torch.rand(B, P, generator=g) < 0.6).float()
+    mb = (torch.rand(B, P, generator=g) < 0.6).float()
+    acc, hit = ops.dense_top1(q.cuda(), k.cuda(), ma.cuda(), mb.cuda())
+    qh, kh = torch.nn.functional.normalize(q, dim=1), torch.nn.functional.normalize(k, dim=1)
+    want = [O.dense_accuracy(qh[i:i + 1], kh[i:i + 1], ma[i:i + 1], mb[i:i + 1]).item() / 100.0 for i in range(B)]
+    assert hit.cpu().tolist() == want
+    np.testing.assert_allclose(acc.item(), O.dense_accuracy(qh, kh, ma, mb).item(), rtol=1e-6)
+    # a planted maximum at a known pair, on a background key: miss; then on a foreground pair: hit
+    q2, k2 = q.clone(), k.clone()
+    x, y = P - 1, 3
+    k2[:, :, y] = q2[:, :, x] * 2.5                       # cosine 1 with query pixel x
+    ma2, mb2 = ma.clone(), mb.clone()
+    ma2[:, x], mb2[:, y] = 1.0, 0.0
+    _, hit2 = ops.dense_top1(q2.cuda(), k2.cuda(), ma2.cuda(), mb2.cuda())
+    assert hit2.cpu().tolist() == [0.0] * B
+    mb2[:, y] = 1.0
+    acc3, hit3 = ops.dense_top1(q2.cuda(), k2.cuda(), ma2.cuda(), mb2.cuda())
+    assert hit3.cpu().tolist() == [1.0] * B and acc3.item() == 100.0
+
+
+@pytest.mark.parametrize("B,K,bg", [(32, 65536, False), (4, 1000, True), (70, 4096, False)])
+def test_global_top1_vs_oracle(ops, B, K, bg):
+    """cp2_global_top1 against `_accuracy(logits_moco, 0, topk=(1,))` (builder.py:1441, 1690-1706)."""
+    g = torch.Generator().manual_seed(K + B)
+    C = 128
+    nrm = torch.nn.functional.normalize
+    queue = nrm(torch.randn(C, K, generator=g), dim=0)
+    q_pos = nrm(torch.randn(B, C, generator=g), dim=1)
+    # positives of graded quality: some beat every negative, some do not
+    k_pos = nrm(q_pos * torch.linspace(0.0, 1.2, B)[:, None] + torch.randn(B, C, generator=g) * 0.08, dim=1)
+    q_neg = nrm(torch.randn(B, C, generator=g), dim=1)
+    k_neg = nrm(q_pos * 0.6 + torch.randn(B, C, generator=g) * 0.08, dim=1)
+    logits = O.global_logits(q_pos, k_pos, queue, q_neg, k_neg, include_background=bg)
+    want = (logits.argmax(dim=1) == 0).float()
+    assert 0 < want.sum() < B
+    acc, hit = ops.global_top1(q_pos.cuda(), k_pos.cuda(), queue.cuda(), q_neg.cuda() if bg else None,
+                               k_neg.cuda() if bg else None)
+    assert torch.equal(hit.cpu(), want)
+    np.testing.assert_allclose(acc.item(), O.topk_accuracy(logits, topk=(1,))[0].item(), rtol=1e-6)

@@ -36,10 +36,17 @@ def test_loss_golden_p196(ops, tag):
     mask_a = O.stride_subsample(T(g["bg0_ch0_zero"]).float(), 16).reshape(2, -1)
     mask_b = O.stride_subsample(T(g["bg1_ch0_zero"]).float(), 16).reshape(2, -1)
     q = T(g["q"]).cuda().requires_grad_(True)
-    loss, li, ld, k_pos, q_pos, _ = ops.cp2_loss(
+    loss, li, ld, k_pos, q_pos, st = ops.cp2_loss(
         q, T(g["k"]).cuda(), mask_a.cuda(), mask_b.cuda(), T(g["queue0"]).cuda(),
         float(g["temp_global"]), float(g["temp_local"]), float(g["lmbd"]), bool(g["include_background"]))
     loss.backward()
+    # the reference's own accuracy meters (builder.py:1441-1448) from the two arg-max kernels
+    bg = bool(g["include_background"])
+    acc_ins, _ = ops.global_top1(q_pos, k_pos, T(g["queue0"]).cuda(), st["q_neg"] if bg else None,
+                                 st["k_neg"] if bg else None)
+    acc_seg, _ = ops.dense_top1(q.detach(), T(g["k"]).cuda(), mask_a.cuda(), mask_b.cuda())
+    np.testing.assert_allclose(acc_ins.item(), g["acc_ins"], atol=1e-3)
+    np.testing.assert_allclose(acc_seg.item(), g["acc_seg"], atol=1e-3)
     np.testing.assert_allclose(loss.item(), g["loss"], rtol=LOSS_RTOL)
     np.testing.assert_allclose(li.item(), g["loss_ins"], rtol=LOSS_RTOL)
     np.testing.assert_allclose(ld.item(), g["loss_dense"], rtol=LOSS_RTOL)
