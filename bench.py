@@ -376,7 +376,7 @@ def weighted_sweep(peaks, iters=20):
         kh, _, sk, nsk, _ = ops.prep_features(k, mb)
 
         def ours():
-            lse, dense_n, wstats, _ = ops.dense_weighted_lse(qh, kh, ma, mb, pw, sq, nsq, sk, nsk, inv_tau)
+            lse, dense_n, wstats, _, _ = ops.dense_weighted_lse(qh, kh, ma, mb, pw, sq, nsq, sk, nsk, inv_tau)
             return ops.dense_weighted_grad(qh, kh, ma, mb, pw, lse, wstats, q_inv, alpha, v1, None, inv_tau)
 
         sub = lambda t: t[:, os_ // 2::os_, os_ // 2::os_].reshape(B, -1)

@@ -9,8 +9,7 @@ compositing, the EMA and the enqueue, runs in the sm_100a kernels of libcp2_b200
 (include/cp2_b200.h); torch supplies device memory, streams, autograd plumbing and NCCL.
 
 Scope: `forward_cp2`, i.e. PretrainType.CP2 (MappingType.CP2 / NegativeType.NONE)
-and PretrainType.PROPOSED (pair weights from the id maps, NegativeType NONE / FIXED / AVERAGE / HARD;
-row f3).  The other pre-training modes of the reference raise NotImplementedError here.
+and PretrainType.PROPOSED (pair weights from the id maps, every NegativeType; row f3).  The other pre-training modes of the reference raise NotImplementedError here.
 
 Deliberate, documented deviations from the reference (none changes the loss):
   * no `int(queue_ptr)` / `.item()` / `.cpu()` host syncs on the step: the queue pointer
@@ -230,9 +229,6 @@ class MODEL(nn.Module):
         if pretrain_type == PretrainType.CP2:
             assert negative_type == NegativeType.NONE   # builder.py:431-433
             assert mapping_type == MappingType.CP2
-        if negative_type == NegativeType.MEDIAN:
-            raise NotImplementedError("NegativeType.MEDIAN (per-sample nanquantile centre, builder.py:1358-1374) "
-                                      "is not built; NONE, FIXED, AVERAGE and HARD are")
         # the PROPOSED modes that change the loss; all-ones weights with no
         # negative squash are the CP2 loss and take the tensor-core path
         self._weighted = not (lmbd_pixel_corr_weight == 1 and lmbd_region_corr_weight == 1
@@ -288,12 +284,12 @@ class MODEL(nn.Module):
     def _accuracy_stats(self, q, k, mask_a, mask_b, q_pos, k_pos, stats):
         """builder.py:1441-1448 (+ :1395-1418 for the logits) as two arg-max kernels (cp2_global_top1,
         cp2_dense_top1): no [B,1+K] and no [B,P,P] tensor, no host sync.  In the PROPOSED modes the dense
-        arg-max would have to run on the weighted logits; that meter then reads NaN."""
+        arg-max runs on the weighted logits inside cp2_dense_weighted_lse (stats["acc_seg"])."""
         bg = self.include_background
         acc1, _ = ops.global_top1(q_pos, k_pos, self.queue, stats["q_neg"] if bg else None,
                                   stats["k_neg"] if bg else None)
         if self._weighted:
-            return acc1, float("nan")
+            return acc1, stats["acc_seg"]
         acc_seg, _ = ops.dense_top1(q, k, mask_a, mask_b)
         return acc1, acc_seg
 

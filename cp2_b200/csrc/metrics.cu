@@ -147,9 +147,9 @@ global_top1_kernel(const float *__restrict__ q_pos, const float *__restrict__ qu
       float acc[32];
 #pragma unroll
       for (int r = 0; r < 32; ++r) acc[r] = 0.f;
-#pragma unroll 2
+#pragma unroll 8
       for (int c = 0; c < C; ++c) {
-        const float kv = queue[(long long)c * K + col];
+        const float kv = __ldg(queue + (long long)c * K + col);
 #pragma unroll
         for (int r4 = 0; r4 < 8; ++r4) {
           const float4 qv = *reinterpret_cast<const float4 *>(qT + c * 32 + r4 * 4);

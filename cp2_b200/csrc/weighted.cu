@@ -12,10 +12,11 @@ namespace {
 
 constexpr int WT = 32;                  // tile edge (pixels)
 constexpr int WTHREADS = 256;
+constexpr int SEL_INTS = 4 + 512;         // MEDIAN selection state per image
 
 struct WParams {
   float w_pix, w_reg, w_not, neg_scale, inv_tau;
-  int neg_type;                         // 0 none, 1 fixed (centre 0), 2 average (per-image centre)
+  int neg_type;                         // 0 none, 1 fixed (centre 0), 2 average, 3 median (per-image centre)
   int P, ws, ids_w, os;
   long long ids_hw;
 };
@@ -40,6 +41,11 @@ __device__ __forceinline__ void squash(float s, bool label, float centre, const 
   if (label || p.neg_type == 0) { t = s; dt = 1.f; return; }
   t = 2.f / (1.f + expf((s - centre) * -p.neg_scale)) - 1.f;
   dt = (1.f - t * t) * 0.5f * p.neg_scale;
+}
+
+struct Best { float v; int i; };
+__device__ __forceinline__ void take(Best &a, float v, int i) {
+  if (v > a.v || (v == a.v && i < a.i)) { a.v = v; a.i = i; }     // first occurrence on ties
 }
 
 // 8 bf16 -> 8 floats at dst
@@ -73,7 +79,8 @@ __global__ void __launch_bounds__(128)
 weighted_stats_kernel(const float *__restrict__ mask_a, const float *__restrict__ mask_b,
                       const float *__restrict__ pos_q, const float *__restrict__ neg_q,
                       const float *__restrict__ pos_k, const float *__restrict__ neg_k,
-                      float *__restrict__ wstats, int32_t *__restrict__ key_count, int C, int P) {
+                      float *__restrict__ wstats, int32_t *__restrict__ key_count, int *__restrict__ sel,
+                      int C, int P) {
   __shared__ float red[4][4];
   const int b = blockIdx.x, tid = threadIdx.x;
   float v[4] = {0.f, 0.f, 0.f, 0.f};                 // A, Bm, sum_all, sum_label
@@ -102,12 +109,114 @@ weighted_stats_kernel(const float *__restrict__ mask_a, const float *__restrict_
     wstats[3 * b + 1] = s[0];
     wstats[3 * b + 2] = s[1];
     key_count[b] = (int)(s[1] + 0.5f);
+    if (sel) {                           // NegativeType.MEDIAN: ranks of the two middle order statistics
+      const long long n = (long long)P * P - (long long)(s[0] + 0.5f) * (long long)(s[1] + 0.5f);
+      int *st = sel + (long long)b * SEL_INTS;
+      st[0] = st[1] = 0;                 // key prefixes
+      st[2] = (int)((n - 1) / 2);        // floor(0.5 (n-1))
+      st[3] = (int)(n / 2);              // ceil (0.5 (n-1))
+    }
+  }
+  if (sel)
+    for (int i = tid; i < 512; i += 128) sel[(long long)b * SEL_INTS + 4 + i] = 0;
+}
+
+// ---- NegativeType.MEDIAN (builder.py:1358-1374): the per-image median of the non-label similarities, i.e.
+// torch.nanquantile(q=0.5) = the mean of the two middle order statistics, found by a 4-pass radix select
+// (8 key bits per pass) that recomputes S instead of storing it.  sel[b] = {prefix0, prefix1, rank0, rank1,
+// hist0[256], hist1[256]}.
+__device__ __forceinline__ uint32_t sortable(float s) {
+  const uint32_t u = __float_as_uint(s);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float unsortable(uint32_t k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+template <int C>
+__global__ void __launch_bounds__(WTHREADS)
+weighted_select_kernel(const __nv_bfloat16 *__restrict__ qhat_t, const __nv_bfloat16 *__restrict__ khat_t,
+                       const float *__restrict__ mask_a, const float *__restrict__ mask_b, int *__restrict__ sel,
+                       int P, int pass) {
+  extern __shared__ __align__(16) float sm[];
+  float *ks = sm;
+  float *qs = sm + WT * (C + 4);
+  __shared__ float a_s[WT];
+  __shared__ int hist[2][256];
+  const int b = blockIdx.y, y0 = blockIdx.x * WT, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const __nv_bfloat16 *qb = qhat_t + (long long)b * P * C, *kb = khat_t + (long long)b * P * C;
+  int *st = sel + (long long)b * SEL_INTS;
+  for (int i = threadIdx.x; i < 512; i += WTHREADS) (&hist[0][0])[i] = 0;
+  load_rows<C>(kb, y0, P, ks, C + 1);
+  const int y = y0 + lane;
+  const bool vy = y < P;
+  const float by = vy ? mask_b[(long long)b * P + y] : 0.f;
+  const uint32_t pre0 = (uint32_t)st[0], pre1 = (uint32_t)st[1];
+  const int shift = 24 - 8 * pass;
+  for (int x0 = 0; x0 < P; x0 += WT) {
+    __syncthreads();
+    load_rows<C>(qb, x0, P, qs, C);
+    if (threadIdx.x < WT) a_s[threadIdx.x] = x0 + threadIdx.x < P ? mask_a[(long long)b * P + x0 + threadIdx.x] : 0.f;
+    __syncthreads();
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const float *kr = ks + lane * (C + 1);
+#pragma unroll 4
+    for (int c = 0; c < C; c += 4) {
+      const float k0 = kr[c], k1 = kr[c + 1], k2 = kr[c + 2], k3 = kr[c + 3];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 q4 = *reinterpret_cast<const float4 *>(qs + (warp * 4 + i) * C + c);
+        acc[i] = fmaf(q4.x, k0, fmaf(q4.y, k1, fmaf(q4.z, k2, fmaf(q4.w, k3, acc[i]))));
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int xl = warp * 4 + i;
+      if (vy && x0 + xl < P && !(a_s[xl] != 0.f && by != 0.f)) {       // non-label pairs only
+        const uint32_t key = sortable(acc[i]);
+        const uint32_t hi = pass == 0 ? 0u : key >> (shift + 8);
+        if (hi == pre0) atomicAdd(&hist[0][(key >> shift) & 255u], 1);
+        if (hi == pre1) atomicAdd(&hist[1][(key >> shift) & 255u], 1);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 512; i += WTHREADS) {
+    const int v = (&hist[0][0])[i];
+    if (v) atomicAdd(st + 4 + i, v);
+  }
+}
+
+// Picks the bin holding each target rank, extends the prefixes, clears the histograms; after the last pass
+// writes the centre = v0 + frac (v1 - v0) into wstats[b][0].
+__global__ void __launch_bounds__(32)
+weighted_pick_kernel(int *__restrict__ sel, float *__restrict__ wstats, int pass) {
+  int *st = sel + (long long)blockIdx.x * SEL_INTS;
+  const int lane = threadIdx.x;
+  if (lane < 2) {
+    const int *h = st + 4 + 256 * lane;
+    int rank = st[2 + lane], cum = 0, bin = 255;
+    for (int i = 0; i < 256; ++i) {
+      const int c = h[i];
+      if (rank < cum + c) { bin = i; break; }
+      cum += c;
+    }
+    st[lane] = (int)(((uint32_t)st[lane] << 8) | (uint32_t)bin);
+    st[2 + lane] = rank - cum;
+  }
+  __syncwarp();
+  for (int i = lane; i < 512; i += 32) st[4 + i] = 0;
+  __syncwarp();
+  if (pass == 3 && lane == 0) {
+    const float v0 = unsortable((uint32_t)st[0]), v1 = unsortable((uint32_t)st[1]);
+    wstats[3 * blockIdx.x] = v0 + 0.5f * (v1 - v0);     // identical ranks (odd count) give v0
   }
 }
 
 // Forward: CTA = 32 key pixels y of one image, all query pixels x in chunks of 32.  Thread (warp, lane):
 // key y0+lane, query rows 4*warp..4*warp+3 of the chunk.  lse[y] = log sum_x exp(z[x,y]) with
-// z = w*t(S)*inv_tau; partial[b,tile] = sum_y b_y (A lse_y - sum_x a_x z[x,y]).
+// z = w*t(S)*inv_tau; partial[b,tile] = sum_y b_y (A lse_y - sum_x a_x z[x,y]); best_v/best_i[b,tile] = the
+// tile's largest z and its flat index x*P+y (acc_seg, builder.py:1442-1448, on the weighted logits).
 template <int C>
 __global__ void __launch_bounds__(WTHREADS)
 weighted_lse_kernel(const __nv_bfloat16 *__restrict__ qhat_t, const __nv_bfloat16 *__restrict__ khat_t,
@@ -115,7 +224,7 @@ weighted_lse_kernel(const __nv_bfloat16 *__restrict__ qhat_t, const __nv_bfloat1
                     const long long *__restrict__ pid_a, const long long *__restrict__ pid_b,
                     const long long *__restrict__ rid_a, const long long *__restrict__ rid_b,
                     const float *__restrict__ wstats, float *__restrict__ lse, float *__restrict__ partial,
-                    WParams p) {
+                    float *__restrict__ best_v, int *__restrict__ best_i, WParams p) {
   extern __shared__ __align__(16) float sm[];
   float *ks = sm;                        // [32][C+1]
   float *qs = sm + WT * (C + 4);         // [32][C], 16-byte aligned rows
@@ -130,8 +239,9 @@ weighted_lse_kernel(const __nv_bfloat16 *__restrict__ qhat_t, const __nv_bfloat1
   const bool vy = y < P;
   const float by = vy ? mask_b[(long long)b * P + y] : 0.f;
   const long long pb = vy ? pid_b[id_index(p, b, y)] : 0, rb = vy ? rid_b[id_index(p, b, y)] : 0;
-  const float centre = p.neg_type == 2 ? wstats[3 * b] : 0.f, A = wstats[3 * b + 1];
+  const float centre = p.neg_type >= 2 ? wstats[3 * b] : 0.f, A = wstats[3 * b + 1];
   float m = -INFINITY, l = 0.f, pos = 0.f;
+  Best best{-INFINITY, 0x7fffffff};
   for (int x0 = 0; x0 < P; x0 += WT) {
     __syncthreads();
     load_rows<C>(qb, x0, P, qs, C);
@@ -165,6 +275,7 @@ weighted_lse_kernel(const __nv_bfloat16 *__restrict__ qhat_t, const __nv_bfloat1
         l = l * expf(m - mn) + expf(z - mn);
         m = mn;
         pos = fmaf(ax, z, pos);
+        take(best, z, (x0 + xl) * P + y);
       }
     }
   }
@@ -189,16 +300,54 @@ weighted_lse_kernel(const __nv_bfloat16 *__restrict__ qhat_t, const __nv_bfloat1
     for (int off = 16; off > 0; off >>= 1) contrib += __shfl_down_sync(0xffffffffu, contrib, off);
     if (lane == 0) partial[(long long)b * gridDim.x + blockIdx.x] = contrib;
   }
+  // arg-max of the tile
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    const float v = __shfl_down_sync(0xffffffffu, best.v, off);
+    const int i = __shfl_down_sync(0xffffffffu, best.i, off);
+    take(best, v, i);
+  }
+  __syncthreads();                       // red[] is free again
+  if (lane == 0) { red[0][warp][0] = best.v; red[1][warp][0] = __int_as_float(best.i); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < WTHREADS / 32; ++w) take(best, red[0][w][0], __float_as_int(red[1][w][0]));
+    best_v[(long long)b * gridDim.x + blockIdx.x] = best.v;
+    best_i[(long long)b * gridDim.x + blockIdx.x] = best.i;
+  }
 }
 
-// dense_n[b] = sum_tiles partial / (A * Bm): builder.py:1434-1437 for one image (0/0 -> NaN as the reference)
-__global__ void weighted_finalize_kernel(const float *__restrict__ partial, const float *__restrict__ wstats,
-                                         float *__restrict__ dense_n, int B, int tiles) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= B) return;
-  float s = 0.f;
-  for (int t = 0; t < tiles; ++t) s += partial[(long long)b * tiles + t];
-  dense_n[b] = s / (wstats[3 * b + 1] * wstats[3 * b + 2]);
+// dense_n[b] = sum_tiles partial / (A * Bm): builder.py:1434-1437 for one image (0/0 -> NaN as the reference);
+// acc_seg[0] = 100 * mean_b mask_a[x*] mask_b[y*] at the image's arg-max pair.  One CTA.
+__global__ void __launch_bounds__(WTHREADS)
+weighted_finalize_kernel(const float *__restrict__ partial, const float *__restrict__ best_v,
+                         const int *__restrict__ best_i, const float *__restrict__ wstats,
+                         const float *__restrict__ mask_a, const float *__restrict__ mask_b,
+                         float *__restrict__ dense_n, float *__restrict__ acc_seg, int B, int P, int tiles) {
+  __shared__ float red[WTHREADS / 32];
+  float hits = 0.f;
+  for (int b = threadIdx.x; b < B; b += WTHREADS) {
+    float s = 0.f;
+    Best best{-INFINITY, 0x7fffffff};
+    for (int t = 0; t < tiles; ++t) {
+      s += partial[(long long)b * tiles + t];
+      take(best, best_v[(long long)b * tiles + t], best_i[(long long)b * tiles + t]);
+    }
+    dense_n[b] = s / (wstats[3 * b + 1] * wstats[3 * b + 2]);
+    if (best.i != 0x7fffffff) {
+      const int x = best.i / P, y = best.i - x * P;
+      hits += mask_a[(long long)b * P + x] * mask_b[(long long)b * P + y];
+    }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) hits += __shfl_down_sync(0xffffffffu, hits, off);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = hits;
+  __syncthreads();
+  if (threadIdx.x == 0 && acc_seg) {
+    float t = 0.f;
+    for (int w = 0; w < WTHREADS / 32; ++w) t += red[w];
+    acc_seg[0] = t * (100.f / (float)B);
+  }
 }
 
 // Backward: CTA = 32 query pixels x of one image, all key pixels y in chunks of 32.
@@ -235,7 +384,7 @@ weighted_grad_kernel(const __nv_bfloat16 *__restrict__ qhat_t, const __nv_bfloat
     a_s[lane] = ax;
     inr_s[lane] = vx ? inv_norm[(long long)b * P + x] : 0.f;
   }
-  const float centre = p.neg_type == 2 ? wstats[3 * b] : 0.f, a_over_A = ax / wstats[3 * b + 1];
+  const float centre = p.neg_type >= 2 ? wstats[3 * b] : 0.f, a_over_A = ax / wstats[3 * b + 1];
   float acc[4][NJ];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -333,8 +482,8 @@ int make_params(WParams &p, float w_pix, float w_reg, float w_not, int neg_type,
   const int hs = (ids_h - os / 2 + os - 1) / os, ws = (ids_w - os / 2 + os - 1) / os;
   CP2_REQUIRE(hs * ws == P, "cp2_dense_weighted: id maps %dx%d at stride %d give %dx%d pixels, P=%d", ids_h, ids_w,
               os, hs, ws, P);
-  CP2_REQUIRE(neg_type >= 0 && neg_type <= 2, "cp2_dense_weighted: negative type %d (0 none, 1 fixed, 2 average)",
-              neg_type);
+  CP2_REQUIRE(neg_type >= 0 && neg_type <= 3,
+              "cp2_dense_weighted: negative type %d (0 none, 1 fixed, 2 average, 3 median)", neg_type);
   CP2_REQUIRE(inv_tau > 0.f, "cp2_dense_weighted: bad temperature");
   p = WParams{w_pix, w_reg, w_not, neg_scale, inv_tau, neg_type, P, ws, ids_w, os, (long long)ids_h * ids_w};
   return CP2_OK;
@@ -342,13 +491,14 @@ int make_params(WParams &p, float w_pix, float w_reg, float w_not, int neg_type,
 
 }  // namespace
 
-extern "C" int cp2_dense_weighted_tiles(int P) { return cp2_cdiv(P, WT); }
+extern "C" int cp2_dense_weighted_tiles(int P) { return 3 * cp2_cdiv(P, WT) + SEL_INTS; }
 
 extern "C" int cp2_dense_weighted_lse(const void *qhat_t, const void *khat_t, const float *mask_a, const float *mask_b,
                                       const int64_t *pixel_ids_a, const int64_t *pixel_ids_b,
                                       const int64_t *region_ids_a, const int64_t *region_ids_b, const float *pos_q,
                                       const float *neg_q, const float *pos_k, const float *neg_k, float *lse,
-                                      float *dense_n, float *wstats, int32_t *key_count, float *scratch,
+                                      float *dense_n, float *acc_seg, float *wstats, int32_t *key_count,
+                                      float *scratch,
                                       float w_pix, float w_reg, float w_not, int neg_type, float neg_scale,
                                       float inv_tau, int B, int C, int P, int ids_h, int ids_w, int os, void *stream) {
   CP2_REQUIRE(B > 0 && P > 0 && (C == 128 || C == 256), "cp2_dense_weighted_lse: bad shape B=%d C=%d P=%d", B, C, P);
@@ -362,18 +512,33 @@ extern "C" int cp2_dense_weighted_lse(const void *qhat_t, const void *khat_t, co
   const auto *pa = reinterpret_cast<const long long *>(pixel_ids_a), *pb = reinterpret_cast<const long long *>(pixel_ids_b);
   const auto *ra = reinterpret_cast<const long long *>(region_ids_a), *rb = reinterpret_cast<const long long *>(region_ids_b);
   const auto *q = static_cast<const __nv_bfloat16 *>(qhat_t), *k = static_cast<const __nv_bfloat16 *>(khat_t);
-  weighted_stats_kernel<<<B, 128, 0, st>>>(mask_a, mask_b, pos_q, neg_q, pos_k, neg_k, wstats, key_count, C, P);
+  int *sel = neg_type == 3 ? reinterpret_cast<int *>(scratch + 3 * (size_t)B * tiles) : nullptr;
+  weighted_stats_kernel<<<B, 128, 0, st>>>(mask_a, mask_b, pos_q, neg_q, pos_k, neg_k, wstats, key_count, sel, C, P);
   CP2_LAUNCH_CHECK();
   const dim3 grid(tiles, B);
+  if (sel) {
+    if (C == 128) CP2_CUDA(cudaFuncSetAttribute(weighted_select_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lse_smem(128)));
+    else CP2_CUDA(cudaFuncSetAttribute(weighted_select_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lse_smem(256)));
+    for (int pass = 0; pass < 4; ++pass) {
+      if (C == 128) weighted_select_kernel<128><<<grid, WTHREADS, lse_smem(128), st>>>(q, k, mask_a, mask_b, sel, P, pass);
+      else weighted_select_kernel<256><<<grid, WTHREADS, lse_smem(256), st>>>(q, k, mask_a, mask_b, sel, P, pass);
+      CP2_LAUNCH_CHECK();
+      weighted_pick_kernel<<<B, 32, 0, st>>>(sel, wstats, pass);
+      CP2_LAUNCH_CHECK();
+    }
+  }
+  float *bv = scratch + (size_t)B * tiles;
+  int *bi = reinterpret_cast<int *>(scratch + 2 * (size_t)B * tiles);
   if (C == 128) {
     CP2_CUDA(cudaFuncSetAttribute(weighted_lse_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lse_smem(128)));
-    weighted_lse_kernel<128><<<grid, WTHREADS, lse_smem(128), st>>>(q, k, mask_a, mask_b, pa, pb, ra, rb, wstats, lse, scratch, p);
+    weighted_lse_kernel<128><<<grid, WTHREADS, lse_smem(128), st>>>(q, k, mask_a, mask_b, pa, pb, ra, rb, wstats, lse, scratch, bv, bi, p);
   } else {
     CP2_CUDA(cudaFuncSetAttribute(weighted_lse_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lse_smem(256)));
-    weighted_lse_kernel<256><<<grid, WTHREADS, lse_smem(256), st>>>(q, k, mask_a, mask_b, pa, pb, ra, rb, wstats, lse, scratch, p);
+    weighted_lse_kernel<256><<<grid, WTHREADS, lse_smem(256), st>>>(q, k, mask_a, mask_b, pa, pb, ra, rb, wstats, lse, scratch, bv, bi, p);
   }
   CP2_LAUNCH_CHECK();
-  weighted_finalize_kernel<<<cp2_cdiv(B, 128), 128, 0, st>>>(scratch, wstats, dense_n, B, tiles);
+  weighted_finalize_kernel<<<1, WTHREADS, 0, st>>>(scratch, bv, bi, wstats, mask_a, mask_b, dense_n, acc_seg, B, P,
+                                                   tiles);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }

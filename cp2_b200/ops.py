@@ -304,7 +304,7 @@ class CP2LossFunction(torch.autograd.Function):
 
 
 # ------------------------------------------------- f3: PROPOSED-mode dense loss
-NEGATIVE_CODES = {"NONE": 0, "FIXED": 1, "AVERAGE": 2, "HARD": 0}   # HARD: a no-op in the reference (Appendix A.8)
+NEGATIVE_CODES = {"NONE": 0, "FIXED": 1, "AVERAGE": 2, "MEDIAN": 3, "HARD": 0}   # HARD: a no-op in the reference (Appendix A.8)
 
 
 class PairWeights:
@@ -315,8 +315,7 @@ class PairWeights:
                  w_not, negative_type="NONE", negative_scale=2.0):
         name = getattr(negative_type, "name", negative_type)
         if name not in NEGATIVE_CODES:
-            raise NotImplementedError(f"negative_type {name}: the per-sample nanquantile centre (builder.py:1358-1374) "
-                                      "is not built")
+            raise NotImplementedError(f"negative_type {name}")    # the reference's own fallthrough, builder.py:1386
         self.ids = []
         for t in (pixel_ids_a, pixel_ids_b, region_ids_a, region_ids_b):
             _need_cuda(t)
@@ -336,18 +335,19 @@ class PairWeights:
 
 
 def dense_weighted_lse(qhat_t, khat_t, mask_a, mask_b, pw, pos_q, neg_q, pos_k, neg_k, inv_tau):
-    """cp2_dense_weighted_lse -> (lse [B,P], dense_n [B], wstats [B,3], key_count [B] int32)."""
+    """cp2_dense_weighted_lse -> (lse [B,P], dense_n [B], wstats [B,3], key_count [B] int32, acc_seg [1])."""
     B, P, C = qhat_t.shape
     lib, dev = _lib.load(), qhat_t.device
     lse = torch.empty((B, P), device=dev, dtype=torch.float32)
     dense_n = torch.empty((B,), device=dev, dtype=torch.float32)
     wstats = torch.empty((B, 3), device=dev, dtype=torch.float32)
+    acc_seg = torch.empty((1,), device=dev, dtype=torch.float32)
     count = torch.empty((B,), device=dev, dtype=torch.int32)
     scratch = torch.empty((B, lib.cp2_dense_weighted_tiles(P)), device=dev, dtype=torch.float32)
     _call("cp2_dense_weighted_lse", 3, lib.cp2_dense_weighted_lse, _ptr(qhat_t), _ptr(khat_t), _ptr(mask_a),
           _ptr(mask_b), *pw._args(), _ptr(pos_q), _ptr(neg_q), _ptr(pos_k), _ptr(neg_k), _ptr(lse), _ptr(dense_n),
-          _ptr(wstats), _ptr(count), _ptr(scratch), *pw._tail(inv_tau, B, C, P))
-    return lse, dense_n, wstats, count
+          _ptr(acc_seg), _ptr(wstats), _ptr(count), _ptr(scratch), *pw._tail(inv_tau, B, C, P))
+    return lse, dense_n, wstats, count, acc_seg
 
 
 def dense_weighted_grad(qhat_t, khat_t, mask_a, mask_b, pw, lse, wstats, inv_norm, alpha, v1, v2, inv_tau, gscale=None):
@@ -375,7 +375,7 @@ class CP2WeightedLossFunction(torch.autograd.Function):
         qh, q_inv, sq, nsq, _, q_pos, q_neg, norms_q = prep_features(qf, mask_a, unit=True)
         kh, _, sk, nsk, _, k_pos, k_neg, _ = prep_features(kf, mask_b, unit=True)
         z, G = global_nce(q_pos, queue, 1.0 / tg)
-        lse, dense_n, wstats, kcnt = dense_weighted_lse(qh, kh, mask_a, mask_b, pw, sq, nsq, sk, nsk, 1.0 / tl)
+        lse, dense_n, wstats, kcnt, acc_seg = dense_weighted_lse(qh, kh, mask_a, mask_b, pw, sq, nsq, sk, nsk, 1.0 / tl)
         bg = bool(include_background)
         out, l_pos, alpha, v1, v2 = loss_combine(q_pos, k_pos, q_neg if bg else None, k_neg if bg else None,
                                                  None, None, norms_q, z, G, None, kcnt, mask_a, tg, tl, lmbd_dense,
@@ -383,8 +383,8 @@ class CP2WeightedLossFunction(torch.autograd.Function):
         ctx.save_for_backward(qh, kh, lse, mask_a, mask_b, wstats, q_inv, alpha, v1, v2)
         ctx.inv_tl, ctx.pw, ctx.q_shape = 1.0 / tl, pw, q.shape
         loss, loss_ins, loss_dense, meters = out[0], out[1], out[2], out[3:]
-        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg)
-        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg
+        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg, acc_seg)
+        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg, acc_seg
 
     @staticmethod
     def backward(ctx, g_loss, *_unused):
@@ -400,15 +400,17 @@ def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_
              include_background=False, pair_weights=None):
     """-> (loss, loss_ins, loss_dense, k_pos, q_pos, stats); only `loss` has a gradient (to q).
     pair_weights: None (MappingType.CP2 / NegativeType.NONE, the tensor-core path) or a PairWeights."""
+    nan = float("nan")       # the accuracy meters are separate launches: ops.global_top1 / ops.dense_top1
+    acc_seg = nan
     if pair_weights is None:
         res = CP2LossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense,
                                     include_background)
-    else:
-        res = CP2WeightedLossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense,
-                                            include_background, pair_weights)
+    else:                    # the weighted forward finds the arg-max of its own logits on the way
+        *res, acc_seg = CP2WeightedLossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local,
+                                                      lmbd_dense, include_background, pair_weights)
+        acc_seg = acc_seg[0]
     loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg = res
-    nan = float("nan")       # the arg-max / top-1 meters need the materialised logits: MODEL(track_accuracy=True)
-    stats = {"l_pos": l_pos, "acc_ins": nan, "acc_seg": nan, "std_q_pos": meters[0], "std_k_pos": meters[1],
+    stats = {"l_pos": l_pos, "acc_ins": nan, "acc_seg": acc_seg, "std_q_pos": meters[0], "std_k_pos": meters[1],
              "q_neg": q_neg, "k_neg": k_neg}
     return loss, loss_ins, loss_dense, k_pos, q_pos, stats
 

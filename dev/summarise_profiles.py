@@ -35,7 +35,9 @@ METRICS = [
 # ncu kernel name fragment -> C-ABI entry point (bench.py's kernel names)
 ENTRY = {"composite_kernel": "cp2_composite", "ema_kernel": "cp2_ema", "prep_kernel": "cp2_prep_features",
          "global_nce_kernel": "cp2_global_nce", "dense_lse_kernel": "cp2_dense_lse",
-         "dense_grad_kernel": "cp2_dense_grad", "enqueue_kernel": "cp2_enqueue"}
+         "dense_grad_kernel": "cp2_dense_grad", "enqueue_kernel": "cp2_enqueue",
+         "loss_combine_kernel": "cp2_loss_combine", "id_iou_kernel": "cp2_id_iou",
+         "dense_top1_kernel": "cp2_dense_top1", "global_top1_kernel": "cp2_global_top1"}
 UNIT = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0}
 
 
@@ -88,7 +90,8 @@ def summarise_launches(src, dst):
                 f"(cold-cache, serialised: compare shares)\n# total {T:.1f} us, {sum(cnt.values())} launches\n")
         f.write("# --- cp2_b200 kernels\n")
         for n, v in tot.most_common():
-            if any(k in n for k in list(ENTRY) + ["prep_reduce", "global_finalize", "advance_ptr"]):
+            if any(k in n for k in list(ENTRY) + ["prep_reduce", "global_finalize", "advance_ptr", "loss_finalize", "top1_finalize",
+                                                "dense_nl_kernel", "weighted_", "mirror_"]):
                 f.write(f"{v:10.1f} us {100 * v / T:6.2f}% x{cnt[n]:4d}  {n}\n")
         f.write("# --- top 25 overall (backbone = cuDNN / ATen, out of scope)\n")
         for n, v in tot.most_common(25):

@@ -214,22 +214,25 @@ int cp2_mirror_loss_upsampled(const float *s_lo, const float *t_lo, const int64_
  *              then w_not wherever that is 0
  *   t(s)     = s on label pairs (mask_a[x] != 0 and mask_b[y] != 0) or neg_type 0;
  *              2/(1+exp(-neg_scale*(s - centre))) - 1 elsewhere, centre = 0 (neg_type 1, FIXED) or the
- *              image's mean non-label S (neg_type 2, AVERAGE).  NegativeType.HARD is a no-op in the
- *              reference: pass 0.  MEDIAN is not implemented.
+ *              image's mean (neg_type 2, AVERAGE) or median (neg_type 3, MEDIAN: torch.nanquantile 0.5, by a
+ *              4-pass radix select that recomputes S; 8 more launches) of the non-label S.
+ *              NegativeType.HARD is a no-op in the reference: pass 0.
  *   lse[n,y] = log sum_x exp(z[x,y]);  dense_n[n] = sum_xy a_x b_y (lse_y - z[x,y]) / (sum a * sum b)
  *   qhat_t, khat_t : [B,P,C] bf16 from cp2_prep_features, keys NOT compacted; masks [B,P] f32 (binary)
  *   *_ids_*  : [B,ids_h,ids_w] int64 id maps; pixel p = (r,c) of the P = hs*ws lattice reads element
  *              (r*os + os/2, c*os + os/2), the reference's [OS//2::OS] subsample (builder.py:1165-1186);
  *              pass os = 1 for maps that are already subsampled
  *   pos_*, neg_* : [B,C] pooled sums of cp2_prep_features (query / key side), for the AVERAGE centre
+ *   acc_seg  : NULL or [1] f32 out: 100 * mean_n [arg-max pair of z[n] is a label pair] (builder.py:1442-1448
+ *              on the weighted logits; bf16 operands, so near-ties may fall differently from the reference)
  *   wstats   : [B,3] f32 out = {centre, sum mask_a, sum mask_b}; key_count [B] int32 out
  *   scratch  : [B, cp2_dense_weighted_tiles(P)] f32.   C in {128, 256}. */
 int cp2_dense_weighted_tiles(int P);
 int cp2_dense_weighted_lse(const void *qhat_t, const void *khat_t, const float *mask_a, const float *mask_b,
                            const int64_t *pixel_ids_a, const int64_t *pixel_ids_b, const int64_t *region_ids_a,
                            const int64_t *region_ids_b, const float *pos_q, const float *neg_q,
-                           const float *pos_k, const float *neg_k, float *lse, float *dense_n, float *wstats,
-                           int32_t *key_count, float *scratch, float w_pix, float w_reg, float w_not,
+                           const float *pos_k, const float *neg_k, float *lse, float *dense_n, float *acc_seg,
+                           float *wstats, int32_t *key_count, float *scratch, float w_pix, float w_reg, float w_not,
                            int neg_type, float neg_scale, float inv_tau, int B, int C, int P, int ids_h,
                            int ids_w, int os, void *stream);
 

@@ -259,8 +259,8 @@ def cp2_corr_weights(pixel_ids_a, pixel_ids_b, region_ids_a, region_ids_b, mask_
 def negative_transform(logits, labels, negative_type: str, negative_scale: float):
     """builder.py:1332-1386 on a copy: the non-label entries are squashed to
     2*sigmoid(scale*(s - centre)) - 1 with centre 0 (FIXED) or the per-sample mean of the non-label
-    scores, detached (AVERAGE).  HARD leaves the logits untouched (its `*= 1.5` lands on a temporary,
-    SURVEY.md Appendix A.8); MEDIAN is not restated (per-sample nanquantile centre)."""
+    scores (AVERAGE) or their per-sample median, `torch.nanquantile(q=0.5)` (MEDIAN), both detached.  HARD
+    leaves the logits untouched (its `*= 1.5` lands on a temporary)."""
     if negative_type in ("NONE", "HARD"):
         return logits
     neg = ~labels.bool()
@@ -268,6 +268,8 @@ def negative_transform(logits, labels, negative_type: str, negative_scale: float
         centre = torch.zeros(logits.shape[0], 1, 1)
     elif negative_type == "AVERAGE":
         centre = dense_loss_stats(logits, labels)["negative"]["average"].detach().reshape(-1, 1, 1)
+    elif negative_type == "MEDIAN":
+        centre = dense_loss_stats(logits, labels)["negative"]["quartiles"][1].detach().reshape(-1, 1, 1)
     else:
         raise NotImplementedError(negative_type)
     squashed = 2.0 / (1.0 + torch.exp((logits - centre) * -negative_scale)) - 1.0

@@ -405,6 +405,7 @@ if __name__ == "__main__":
         gen_weighted("fixed_t05", "FIXED", 0.5)
         gen_weighted("avg_t1_bg", "AVERAGE", 1.0, include_background=True)
         gen_weighted("hard_t1", "HARD", 1.0, weights=(3.0, 1.0, 0.0))
+        gen_weighted("median_t05", "MEDIAN", 0.5, weights=(5.0, 2.0, 1.0))
         sys.exit(0)
     gen_step_small()
     gen_loss_p196("t1", 1.0, False)
@@ -418,3 +419,4 @@ if __name__ == "__main__":
     gen_weighted("fixed_t05", "FIXED", 0.5)
     gen_weighted("avg_t1_bg", "AVERAGE", 1.0, include_background=True)
     gen_weighted("hard_t1", "HARD", 1.0, weights=(3.0, 1.0, 0.0))
+    gen_weighted("median_t05", "MEDIAN", 0.5, weights=(5.0, 2.0, 1.0))

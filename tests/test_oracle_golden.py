@@ -47,7 +47,7 @@ def test_loss_path_p196(tag):
     assert w.dtype == torch.int64 and bool((w == 1).all())
 
 
-WEIGHTED_TAGS = ["none_t1", "fixed_t05", "avg_t1_bg", "hard_t1"]
+WEIGHTED_TAGS = ["none_t1", "fixed_t05", "avg_t1_bg", "hard_t1", "median_t05"]
 
 
 def weighted_case(tag):

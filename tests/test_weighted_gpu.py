@@ -77,6 +77,8 @@ def _ids(B, hw, os_, gen):
     (2, 256, 7, 1, "NONE", 1.0, (10.0, 1.0, 1.0)),
     (2, 256, 12, 2, "AVERAGE", 0.2, (1.0, 4.0, 0.25)),
     (1, 128, 28, 2, "FIXED", 0.2, (5.0, 2.0, 1.0)),
+    (3, 128, 14, 2, "MEDIAN", 0.2, (10.0, 2.0, 0.5)),
+    (2, 256, 9, 1, "MEDIAN", 1.0, (2.0, 1.0, 1.0)),
 ])
 def test_weighted_dense_vs_oracle(ops, B, C, hw, os_, neg, tl, weights):
     gen = torch.Generator().manual_seed(100 * hw + C)
@@ -101,13 +103,20 @@ def test_weighted_dense_vs_oracle(ops, B, C, hw, os_, neg, tl, weights):
     qt, q_inv, sq, nsq, _ = ops.prep_features(qd, mad)
     kt, _, sk, nsk, _ = ops.prep_features(kd, mbd)
     pw = ops.PairWeights(pa.cuda(), pb.cuda(), ra.cuda(), rb.cuda(), os_, *weights, neg, 2.0)
-    lse, dense_n, wstats, cnt = ops.dense_weighted_lse(qt, kt, mad, mbd, pw, sq, nsq, sk, nsk, 1.0 / tl)
+    lse, dense_n, wstats, cnt, acc_seg = ops.dense_weighted_lse(qt, kt, mad, mbd, pw, sq, nsq, sk, nsk, 1.0 / tl)
     np.testing.assert_allclose(dense_n.mean().item(), ref.item(), rtol=LOSS_RTOL)
     assert torch.equal(cnt.cpu().long(), mb.sum(1).long())
+    # acc_seg on the weighted logits (builder.py:1442-1448)
+    z = O.negative_transform(torch.einsum("ncx,ncy->nxy", qh.detach(), kh), torch.einsum("nx,ny->nxy", ma, mb),
+                             neg, 2.0) * w / tl
+    idx = z.reshape(B, -1).argmax(dim=1)
+    want = (ma[torch.arange(B), idx // P] * mb[torch.arange(B), idx % P]).mean() * 100.0
+    np.testing.assert_allclose(acc_seg.item(), want.item(), rtol=1e-6)
     np.testing.assert_allclose(wstats[:, 1].cpu().numpy(), ma.sum(1).numpy())
-    if neg == "AVERAGE":
+    if neg in ("AVERAGE", "MEDIAN"):
         lab = torch.einsum("nx,ny->nxy", ma, mb)
-        centre = O.dense_loss_stats(torch.einsum("ncx,ncy->nxy", qh.detach(), kh), lab)["negative"]["average"]
+        st = O.dense_loss_stats(torch.einsum("ncx,ncy->nxy", qh.detach(), kh), lab)["negative"]
+        centre = st["average"] if neg == "AVERAGE" else st["quartiles"][1]
         np.testing.assert_allclose(wstats[:, 0].cpu().numpy(), centre.numpy(), rtol=2e-3, atol=2e-5)
     alpha = (1.0 / tl) / (B * mb.sum(1))
     v1 = torch.zeros(B, C)
@@ -144,7 +153,7 @@ def test_weighted_all_ones_equals_cp2_path(ops):
 def test_weighted_rejects_bad_arguments(ops):
     ids = torch.zeros(2, 14, 14, dtype=torch.int64, device="cuda")
     with pytest.raises(NotImplementedError):
-        ops.PairWeights(ids, ids, ids, ids, 1, 1, 1, 1, "MEDIAN")
+        ops.PairWeights(ids, ids, ids, ids, 1, 1, 1, 1, "SOFTEST")
     with pytest.raises(TypeError):
         ops.PairWeights(ids.int(), ids, ids, ids, 1, 1, 1, 1)
     pw = ops.PairWeights(ids, ids, ids, ids, 1, 1, 1, 1)           # 14x14 ids, but P = 49 below
@@ -164,7 +173,7 @@ class _Feat(nn.Module):
         return self.feat[: x.shape[0]] * 1.0
 
 
-@pytest.mark.parametrize("tag", ["fixed_t05", "avg_t1_bg"])
+@pytest.mark.parametrize("tag", ["fixed_t05", "avg_t1_bg", "median_t05"])
 def test_model_proposed_mode_golden(tag, monkeypatch):
     """MODEL(pretrain_type=PROPOSED, mapping_type=PIXEL_REGION_ID) against the reference's own forward_cp2."""
     from cp2_b200 import builder
