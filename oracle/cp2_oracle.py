@@ -158,6 +158,49 @@ def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0,
     }
 
 
+# ------------------------------------------------------------------ f2 (forward_densecl)
+def rows_infonce(rows, positives, queue, temp: float):
+    """`ContrastiveHead` (builder.py:150-176) for rows whose positive logit is rows . positives:
+    CE(cat([pos, rows @ queue]) / temp, 0), mean over the rows."""
+    pos = (rows * positives).sum(dim=1, keepdim=True)
+    logits = torch.cat([pos, rows @ queue], dim=1) / temp
+    return F.cross_entropy(logits, torch.zeros(rows.shape[0], dtype=torch.long))
+
+
+def densecl_match(embd_q, embd_k):
+    """builder.py:817-821: for every query pixel the key pixel with the most similar BACKBONE feature.
+    embd_* [B,Cb,P] unit columns -> idx [B,P]."""
+    return torch.einsum("ncx,ncy->nxy", embd_q, embd_k).max(dim=2)[1]
+
+
+def densecl_positive_keys(k_local, idx, pix_q, pix_k, lmbd_coordinate: float):
+    """The (detached) vector each query pixel is pulled towards, so that pos_local = q_local_x . kp_x:
+    the matched key pixel (builder.py:824-835), mixed with the sum of the key pixels sharing the query
+    pixel's id wherever there is one (builder.py:839-855).  k_local [B,C,P] -> kp [B,P,C]."""
+    b, c, p = k_local.shape
+    kp = torch.gather(k_local, 2, idx[:, None, :].expand(b, c, p)).permute(0, 2, 1)
+    corr = (pix_q.reshape(b, -1)[:, :, None] == pix_k.reshape(b, -1)[:, None, :])
+    overlap = corr.sum(-1) > 0
+    coord = torch.einsum("nxy,ncy->nxc", corr.to(k_local.dtype), k_local)
+    return torch.where(overlap[:, :, None], kp * (1 - lmbd_coordinate) + coord * lmbd_coordinate, kp)
+
+
+def densecl_loss(embd_q, embd_k, q_local, k_local, q_global, k_global, pix_q, pix_k, queue, queue2,
+                 temp_global=0.2, temp_local=0.2, lmbd_dense=0.5, lmbd_coordinate=0.0):
+    """One direction of `forward_densecl` between the feature extractors and the scalar loss
+    (builder.py:762-999): global InfoNCE on the pooled projections, local InfoNCE of every query pixel
+    against queue2 with the matched / coordinate-mixed key pixel as its positive.  All inputs are the unit
+    vectors `get_query_features` / `get_key_features` return (builder.py:700-760); keys detached."""
+    b, c, p = q_local.shape
+    loss_g = rows_infonce(q_global, k_global.detach(), queue.detach(), temp_global)
+    idx = densecl_match(embd_q.detach(), embd_k.detach())
+    kp = densecl_positive_keys(k_local.detach(), idx, pix_q, pix_k, lmbd_coordinate)
+    rows = q_local.permute(0, 2, 1).reshape(-1, c)
+    loss_l = rows_infonce(rows, kp.reshape(-1, c), queue2.detach(), temp_local)
+    return {"loss": (1 - lmbd_dense) * loss_g + lmbd_dense * loss_l, "loss_global": loss_g,
+            "loss_local": loss_l, "idx": idx}
+
+
 # --------------------------------------------------------------------------- a8
 def ema_update(params_q, params_k, m: float):
     """Momentum update of the key encoder, parameters only.  builder.py:557-567.

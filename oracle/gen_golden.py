@@ -398,8 +398,97 @@ def gen_weighted(tag, negative_type, temp_local, weights=(10.0, 2.0, 0.5), inclu
     print("cp2_weighted", tag, out["loss"], out["loss_ins"], out["loss_dense"])
 
 
+class _DenseCLEncoder(nn.Module):
+    """Stand-in segmentor for the DenseCL modes: `.backbone(img)[3]` is a 2048-channel stride-16 map
+    (DenseCLNeck's in_channels is hard-coded, builder.py:436-441), the module itself returns a 128-d map for
+    the output-stride probe (builder.py:392-402)."""
+
+    class _BB(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.proj = nn.Conv2d(3, 2048, 16, stride=16)
+
+        def forward(self, x):
+            y = self.proj(x)
+            return (y, y, y, y)
+
+        def init_weights(self):
+            pass
+
+    def __init__(self):
+        super().__init__()
+        self.backbone = _DenseCLEncoder._BB()
+        self.head = nn.Conv2d(2048, 128, 1)
+
+    def forward(self, x):
+        return self.head(self.backbone(x)[3])
+
+
+def gen_densecl(tag, pretrain_type, lmbd_coordinate, use_predictor=False):
+    """`forward_densecl` (builder.py:667-999) + backward on 96x96 views (S=6, P=36), K=512 ->
+    tests/golden/densecl_<tag>.npz: the unit features the loss consumes, loss values, gradients w.r.t. the
+    neck outputs, both queues after the step."""
+    torch.manual_seed(3)
+    B, H, K = 3, 96, 512
+    ref = rh.import_reference()
+    _, model = rh.make_reference_model(
+        _DenseCLEncoder, K=K, dim=128, pretrain_type=ref.PretrainType[pretrain_type], lmbd_cp2_dense_loss=0.5,
+        instance_logits_temp=0.2, dense_logits_temp=0.2, lmbd_coordinate=lmbd_coordinate,
+        use_predictor=use_predictor)
+    rec = {}
+
+    def neck_hook(side):
+        def hook(_m, _inp, out):
+            for name, t in out.items():
+                if side == "q" and t.requires_grad:
+                    t.retain_grad()
+                rec[f"{side}.{name}"] = t
+        return hook
+
+    def bb_hook(side):
+        def hook(_m, _inp, out):
+            rec[f"{side}.embd"] = out[3].detach().clone()
+        return hook
+
+    model.encoder_q.neck.register_forward_hook(neck_hook("q"))
+    model.encoder_k.neck.register_forward_hook(neck_hook("k"))
+    model.encoder_q.backbone.register_forward_hook(bb_hook("q"))
+    model.encoder_k.backbone.register_forward_hook(bb_hook("k"))
+    orig = model._batch_shuffle_ddp
+    model._batch_shuffle_ddp = lambda x: (lambda y, idx: (rec.__setitem__("idx_unshuffle", idx.clone()), (y, idx))[1])(*orig(x))
+    g = torch.Generator().manual_seed(21)
+    with torch.no_grad():                                  # make the two encoders differ
+        for p in model.encoder_q.parameters():
+            p.add_(0.02 * torch.randn(p.shape, generator=g))
+    v = synth_views(B, H, H, 16, seed=77)
+    # The reference raises IndexError at builder.py:861 (`.max(dim=2)` on a 2-d tensor) as soon as ONE pixel id
+    # is shared between the two lattices, so its own code can only be recorded on views without overlap.
+    v["pixel_ids_b"] = v["pixel_ids_a"] + H * H
+    out = {"queue0": _np(model.queue), "queue2_0": _np(model.queue2), "lmbd_coordinate": lmbd_coordinate,
+           "use_predictor": use_predictor, "pretrain_type": pretrain_type,
+           "pix_q": _np(v["pixel_ids_a"][:, 8::16, 8::16]), "pix_k": _np(v["pixel_ids_b"][:, 8::16, 8::16])}
+    loss = model(visualize=False, step=0, new_epoch=False, **v)
+    loss.backward()
+    un = rec["idx_unshuffle"]
+    ql = rec["q.x_local_pred"] if use_predictor else rec["q.x_local_proj"]
+    qg = rec["q.x_global_pred"] if use_predictor else rec["q.x_global_proj"]
+    out.update({"q_local_raw": _np(ql), "q_global_raw": _np(qg), "grad_q_local": _np(ql.grad),
+                "grad_q_global": _np(qg.grad), "embd_q": _np(rec["q.embd"]), "embd_k": _np(rec["k.embd"][un]),
+                "k_local_raw": _np(rec["k.x_local_proj"][un]), "k_global_raw": _np(rec["k.x_global_proj"][un]),
+                "k_pooled_raw": _np(rec["k.x_avgpool_local_proj"][un]),
+                "loss": _np(loss), "loss_global": np.float32(model.loss_i.val),
+                "loss_local": np.float32(model.loss_d.val), "queue1": _np(model.queue), "queue2_1": _np(model.queue2),
+                "queue_ptr1": _np(model.queue_ptr), "queue2_ptr1": _np(model.queue2_ptr)})
+    np.savez_compressed(os.path.join(OUT, f"densecl_{tag}.npz"), **out)
+    print("densecl", tag, out["loss"], out["loss_global"], out["loss_local"])
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "densecl":
+        gen_densecl("plain", "DENSECL", 0.0)
+        gen_densecl("v2_pred", "PROPOSED_V2", 0.3, use_predictor=True)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "weighted":
         gen_weighted("none_t1", "NONE", 1.0)
         gen_weighted("fixed_t05", "FIXED", 0.5)
@@ -420,3 +509,5 @@ if __name__ == "__main__":
     gen_weighted("avg_t1_bg", "AVERAGE", 1.0, include_background=True)
     gen_weighted("hard_t1", "HARD", 1.0, weights=(3.0, 1.0, 0.0))
     gen_weighted("median_t05", "MEDIAN", 0.5, weights=(5.0, 2.0, 1.0))
+    gen_densecl("plain", "DENSECL", 0.0)
+    gen_densecl("v2_pred", "PROPOSED_V2", 0.3, use_predictor=True)

@@ -181,3 +181,57 @@ def test_mirror_step_matches_reference(tag):
     if not none:
         np.testing.assert_allclose(cmp.item(), g[f"{tag}_compare"], rtol=1e-6)
         np.testing.assert_allclose(t_lo.grad.numpy(), g[f"{tag}_dt_lo"], rtol=1e-5, atol=1e-9)
+
+
+DENSECL_TAGS = ["plain", "v2_pred"]
+
+
+def densecl_case(tag):
+    """Inputs of a `forward_densecl` fixture (oracle/gen_golden.py:gen_densecl), normalised as
+    get_query_features / get_key_features do (builder.py:700-760)."""
+    g = load_golden(f"densecl_{tag}.npz")
+    nrm = torch.nn.functional.normalize
+    ql = T(g["q_local_raw"]).requires_grad_(True)
+    qg = T(g["q_global_raw"]).requires_grad_(True)
+    feats = {
+        "q_local_raw": ql, "q_global_raw": qg,
+        "q_local": nrm(ql.flatten(2), dim=1), "q_global": nrm(qg, dim=1),
+        "k_local": nrm(T(g["k_local_raw"]).flatten(2), dim=1), "k_global": nrm(T(g["k_global_raw"]), dim=1),
+        "k_pooled": nrm(T(g["k_pooled_raw"]), dim=1),
+        "embd_q": nrm(T(g["embd_q"]).flatten(2), dim=1), "embd_k": nrm(T(g["embd_k"]).flatten(2), dim=1),
+    }
+    return g, feats
+
+
+@pytest.mark.parametrize("tag", DENSECL_TAGS)
+def test_densecl_loss_path(tag):
+    """f2: forward_densecl (builder.py:762-999) between the feature extractors and the loss."""
+    g, f = densecl_case(tag)
+    r = O.densecl_loss(f["embd_q"], f["embd_k"], f["q_local"], f["k_local"], f["q_global"], f["k_global"],
+                       T(g["pix_q"]), T(g["pix_k"]), T(g["queue0"]), T(g["queue2_0"]), 0.2, 0.2, 0.5,
+                       float(g["lmbd_coordinate"]))
+    r["loss"].backward()
+    np.testing.assert_allclose(r["loss"].item(), g["loss"], rtol=1e-6)
+    np.testing.assert_allclose(r["loss_global"].item(), g["loss_global"], rtol=1e-6)
+    np.testing.assert_allclose(r["loss_local"].item(), g["loss_local"], rtol=1e-6)
+    np.testing.assert_allclose(f["q_local_raw"].grad.numpy(), g["grad_q_local"], rtol=1e-4, atol=1e-9)
+    np.testing.assert_allclose(f["q_global_raw"].grad.numpy(), g["grad_q_global"], rtol=1e-4, atol=1e-9)
+    queue, queue2 = T(g["queue0"]).clone(), T(g["queue2_0"]).clone()       # builder.py:975-976
+    assert O.dequeue_and_enqueue(queue, 0, f["k_global"]) == int(g["queue_ptr1"][0])
+    assert O.dequeue_and_enqueue(queue2, 0, f["k_pooled"]) == int(g["queue2_ptr1"][0])
+    np.testing.assert_allclose(queue.numpy(), g["queue1"], rtol=1e-6, atol=1e-8)
+    np.testing.assert_allclose(queue2.numpy(), g["queue2_1"], rtol=1e-6, atol=1e-8)
+
+
+def test_densecl_coordinate_mixing_formula():
+    """builder.py:839-855 on a hand-made case (the reference itself cannot run it: it raises at :861 as soon
+    as one pixel id is shared): overlap pixels mix the matched score with the sum over same-id key pixels."""
+    k_local = torch.nn.functional.normalize(torch.randn(1, 8, 4, generator=torch.Generator().manual_seed(0)), dim=1)
+    q_local = torch.nn.functional.normalize(torch.randn(1, 8, 4, generator=torch.Generator().manual_seed(1)), dim=1)
+    idx = torch.tensor([[2, 0, 1, 3]])
+    pix_q, pix_k = torch.tensor([[5, 6, 7, 8]]), torch.tensor([[7, 9, 7, 10]])
+    kp = O.densecl_positive_keys(k_local, idx, pix_q, pix_k, 0.25)
+    sim = torch.einsum("ncx,ncy->nxy", q_local, k_local)[0]
+    pos = torch.einsum("nxc,ncx->nx", kp, q_local)[0]
+    want = torch.stack([sim[0, 2], sim[1, 0], 0.75 * sim[2, 1] + 0.25 * (sim[2, 0] + sim[2, 2]), sim[3, 3]])
+    np.testing.assert_allclose(pos.numpy(), want.numpy(), rtol=1e-5, atol=1e-6)
