@@ -404,6 +404,63 @@ def weighted_sweep(peaks, iters=20):
     return rows
 
 
+# ------------------------------------------------------------------ forward_densecl loss microbench
+def densecl_sweep(peaks, iters=10):
+    """Row f2 at the DenseCL scripts' shape (B=32, 14x14 backbone map, 2048-d backbone features, dim 128,
+    K=65536, tau 0.2): ops.densecl_loss forward + backward (the backbone match is a cuBLAS bmm in both arms)
+    against the eager torch formulation of builder.py:762-931.  L2 flushed between iterations."""
+    import torch
+    import torch.nn.functional as F
+    from cp2_b200 import ops
+    dev = torch.device("cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    B, P, C, Cb, K, tau = 32, 196, DIM, 2048, QUEUE, 0.2
+    g = torch.Generator(device=dev).manual_seed(17)
+    nrm = F.normalize
+    embd_q = nrm(torch.randn(B, Cb, P, device=dev, generator=g), dim=1)
+    embd_k = nrm(torch.randn(B, Cb, P, device=dev, generator=g), dim=1)
+    q_local = nrm(torch.randn(B, C, P, device=dev, generator=g), dim=1).requires_grad_()
+    k_local = nrm(torch.randn(B, C, P, device=dev, generator=g), dim=1)
+    q_global = nrm(torch.randn(B, C, device=dev, generator=g), dim=1).requires_grad_()
+    k_global = nrm(torch.randn(B, C, device=dev, generator=g), dim=1)
+    queue = nrm(torch.randn(C, K, device=dev, generator=g), dim=0)
+    queue2 = nrm(torch.randn(C, K, device=dev, generator=g), dim=0)
+
+    def timeit(fn, n):
+        ts = []
+        for i in range(n + 2):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record()
+            torch.cuda.synchronize()
+            if i >= 2:
+                ts.append(a.elapsed_time(b) * 1e3)
+        return statistics.median(ts)
+
+    def ours():
+        q_local.grad = q_global.grad = None
+        ops.densecl_loss(embd_q, embd_k, q_local, k_local, q_global, k_global, queue, queue2, tau, tau, 0.5)[0].backward()
+
+    def head(pos, neg):
+        logits = torch.cat((pos, neg), dim=1) / tau
+        return F.cross_entropy(logits, torch.zeros(len(pos), dtype=torch.long, device=dev))
+
+    def eager():
+        q_local.grad = q_global.grad = None
+        lg = head((q_global * k_global).sum(1, keepdim=True), q_global @ queue.clone())
+        idx = torch.einsum("ncx,ncy->nxy", embd_q, embd_k).max(dim=2)[1]
+        pos = torch.gather(torch.einsum("ncx,ncy->nxy", q_local, k_local), 2, idx.unsqueeze(2)).reshape(-1, 1)
+        rows = q_local.permute(0, 2, 1).reshape(-1, C)
+        ll = head(pos, rows @ queue2.clone())
+        (0.5 * lg + 0.5 * ll).backward()
+
+    t_ours, t_eager = timeit(ours, iters), timeit(eager, 5)
+    return [{"B": B, "P": P, "C": C, "K": K, "rows": B * P, "densecl_loss_fwd_bwd_us": round(t_ours, 1),
+             "eager_torch_us": round(t_eager, 1), "speedup_vs_eager": round(t_eager / t_ours, 2),
+             "note": "local InfoNCE = cp2_global_nce re-run per 32 rows (196 queue passes): a many-row tcgen05 "
+                     "kernel is the open item of row f2"}]
+
+
 # ------------------------------------------------------------------------------ own arm
 def algorithmic_work(batch, n_params, world):
     """Per-CALL algorithmic bytes / flops of each C-ABI entry point on the step."""
@@ -590,6 +647,7 @@ def own_arm(args):
             line["dense_microbench"] = dense_sweep(args, peaks)
             line["mirror_microbench"] = mirror_sweep(peaks)
             line["weighted_microbench"] = weighted_sweep(peaks)
+            line["densecl_microbench"] = densecl_sweep(peaks)
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_leg()
     if rank == 0:

@@ -34,6 +34,8 @@ SIGNATURES = {
     "cp2_dense_top1": (c_int, [c_void_p] * 7 + [c_int] * 3 + [c_void_p]),
     "cp2_global_top1_scratch_floats": (c_int64, [c_int, c_int]),
     "cp2_global_top1": (c_int, [c_void_p] * 8 + [c_int] * 3 + [c_void_p]),
+    "cp2_rows_nce": (c_int, [c_void_p] * 7 + [c_float, c_int, c_int, c_void_p]),
+    "cp2_positive_keys": (c_int, [c_void_p] * 5 + [c_float] + [c_int] * 6 + [c_void_p]),
     "cp2_mirror_partials": (c_int, [c_int, c_int64]),
     "cp2_mirror_loss": (c_int, [c_void_p] * 8 + [c_float, c_float, c_int64, c_int, c_int, c_int64, c_void_p]),
     "cp2_mirror_up_partials": (c_int, [c_int] * 3),

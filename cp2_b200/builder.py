@@ -9,7 +9,8 @@ compositing, the EMA and the enqueue, runs in the sm_100a kernels of libcp2_b200
 (include/cp2_b200.h); torch supplies device memory, streams, autograd plumbing and NCCL.
 
 Scope: `forward_cp2`, i.e. PretrainType.CP2 (MappingType.CP2 / NegativeType.NONE)
-and PretrainType.PROPOSED (pair weights from the id maps, every NegativeType; row f3).  The other pre-training modes of the reference raise NotImplementedError here.
+and PretrainType.PROPOSED (pair weights from the id maps, every NegativeType; row f3), and `forward_densecl`
+(DENSECL / PROPOSED_V2; row f2).  MOCO / BYOL / PIXPRO raise NotImplementedError here.
 
 Deliberate, documented deviations from the reference (none changes the loss):
   * no `int(queue_ptr)` / `.item()` / `.cpu()` host syncs on the step: the queue pointer
@@ -156,6 +157,43 @@ def _default_encoder(cfg, dim):
 
 
 # ---------------------------------------------------------------------------- MODEL
+class DenseCLNeck(nn.Module):
+    """builder.py:179-276: the DenseCL neck (global fc-relu-fc, dense 1x1 conv-relu-conv, predictors on top),
+    same parameter names and initialisation.  Plain torch layers: cuDNN / cuBLAS, outside the loss path."""
+
+    def __init__(self, in_channels, hid_channels, out_channels, num_grid=None):
+        super().__init__()
+        self.avgpool_global = nn.AdaptiveAvgPool2d((1, 1))
+        self.global_projector = nn.Sequential(nn.Linear(in_channels, hid_channels), nn.ReLU(inplace=True),
+                                              nn.Linear(hid_channels, out_channels))
+        self.global_predictor = nn.Sequential(nn.Linear(out_channels, hid_channels), nn.ReLU(inplace=True),
+                                              nn.Linear(hid_channels, out_channels))
+        self.with_pool = num_grid is not None
+        if self.with_pool:
+            self.pool = nn.AdaptiveAvgPool2d((num_grid, num_grid))
+        self.local_projector = nn.Sequential(nn.Conv2d(in_channels, hid_channels, 1), nn.ReLU(inplace=True),
+                                             nn.Conv2d(hid_channels, out_channels, 1))
+        self.local_predictor = nn.Sequential(nn.Conv2d(out_channels, hid_channels, 1), nn.ReLU(inplace=True),
+                                             nn.Conv2d(hid_channels, out_channels, 1))
+        self.avgpool_local = nn.AdaptiveAvgPool2d((1, 1))
+        for m in self.modules():                                # builder.py:217-238
+            if isinstance(m, (nn.Conv2d, nn.Linear)):
+                nn.init.xavier_normal_(m.weight)
+                if m.bias is not None:
+                    nn.init.constant_(m.bias, 0)
+
+    def forward(self, x):                                       # builder.py:240-275
+        x_global_proj = self.global_projector(self.avgpool_global(x).flatten(1))
+        x_global_pred = self.global_predictor(x_global_proj)
+        if self.with_pool:
+            x = self.pool(x)
+        x_local_proj = self.local_projector(x)
+        x_local_pred = self.local_predictor(x_local_proj)
+        return {"x_global_proj": x_global_proj, "x_local_proj": x_local_proj, "x_global_pred": x_global_pred,
+                "x_local_pred": x_local_pred, "x_avgpool_local_pred": self.avgpool_local(x_local_pred).flatten(1),
+                "x_avgpool_local_proj": self.avgpool_local(x_local_proj).flatten(1)}
+
+
 class MODEL(nn.Module):
     """Drop-in for the reference's `builder.MODEL` (builder.py:277-1706), CP2 mode.
 
@@ -222,10 +260,19 @@ class MODEL(nn.Module):
         self.negative_type = negative_type
         self.negative_scale = negative_scale
         self.backbone_type = backbone_type
-        if pretrain_type not in (PretrainType.CP2, PretrainType.PROPOSED):
+        self._densecl = pretrain_type in (PretrainType.DENSECL, PretrainType.PROPOSED_V2)
+        if pretrain_type not in (PretrainType.CP2, PretrainType.PROPOSED) and not self._densecl:
             raise NotImplementedError(
-                f"cp2_b200 implements forward_cp2 (PretrainType.CP2 / PROPOSED) only ({pretrain_type = }); "
-                "see SURVEY.md section 8(f) for the order in which the other modes follow")
+                f"cp2_b200 implements forward_cp2 (PretrainType.CP2 / PROPOSED) and forward_densecl "
+                f"(DENSECL / PROPOSED_V2) only ({pretrain_type = })")
+        if self._densecl:                                       # builder.py:443-460
+            assert self.momentum == 0.999, f"{self.momentum = }"
+            assert self.lmbd_dense_loss == 0.5, f"{self.lmbd_dense_loss = }"
+            assert self.temp_global == 0.2, f"{self.temp_global = }"
+            assert self.temp_local == 0.2, f"{self.temp_local = }"
+        if pretrain_type == PretrainType.DENSECL:
+            assert not self.use_predictor and not self.use_avgpool_global
+            assert not self.use_symmetrical_loss and self.lmbd_coordinate == 0
         if pretrain_type == PretrainType.CP2:
             assert negative_type == NegativeType.NONE   # builder.py:431-433
             assert mapping_type == MappingType.CP2
@@ -255,6 +302,12 @@ class MODEL(nn.Module):
             test_sample = torch.rand(2, 3, 224, 224)
             shp = self.encoder_q.backbone(test_sample)[3].shape
             self.backbone_output_stride = int(test_sample.shape[2] / shp[2])
+
+        if self._densecl:                                       # builder.py:436-441, 452-457
+            if not hasattr(self.encoder_q, "backbone"):
+                raise NotImplementedError("the DenseCL modes need an encoder with a `.backbone` (4 stage outputs)")
+            self.encoder_q.neck = DenseCLNeck(in_channels=2048, hid_channels=2048, out_channels=self.dim)
+            self.encoder_k.neck = DenseCLNeck(in_channels=2048, hid_channels=2048, out_channels=self.dim)
 
         # builder.py:464-469: parameters only — BN buffers are not copied
         for param_q, param_k in zip(self.encoder_q.parameters(), self.encoder_k.parameters()):
@@ -388,7 +441,69 @@ class MODEL(nn.Module):
         return self._exchange_rows(x, perm_host)
 
     def forward(self, **kwargs):                               # builder.py:651-665
+        if self._densecl:
+            return self.forward_densecl(**kwargs)
         return self.forward_cp2(**kwargs)
+
+    # ------------------------------------------------------- forward_densecl (f2)
+    def _query_features(self, img):
+        """builder.py:700-720."""
+        embd = self.encoder_q.backbone(img)[3]
+        out = self.encoder_q.neck(embd)
+        tag = "pred" if self.use_predictor else "proj"
+        q_local, q_global = out[f"x_local_{tag}"], out[f"x_global_{tag}"]
+        if self.use_avgpool_global:
+            q_global = out[f"x_avgpool_local_{tag}"]
+        return (F.normalize(embd.detach().flatten(2), dim=1), F.normalize(q_local.flatten(2), dim=1),
+                F.normalize(q_global, dim=1))
+
+    @torch.no_grad()
+    def _key_features(self, img):
+        """builder.py:722-760: EMA, shuffle, key encoder, normalise, unshuffle."""
+        self._momentum_update_key_encoder()
+        img, idx_unshuffle = self._batch_shuffle_ddp(img)
+        embd = self.encoder_k.backbone(img)[3]
+        out = self.encoder_k.neck(embd)
+        pooled = out["x_avgpool_local_proj"]
+        k_global = pooled if self.use_avgpool_global else out["x_global_proj"]
+        feats = [F.normalize(embd.flatten(2), dim=1), F.normalize(out["x_local_proj"].flatten(2), dim=1),
+                 F.normalize(k_global, dim=1), F.normalize(pooled, dim=1)]
+        return [self._batch_unshuffle_ddp(t, idx_unshuffle) for t in feats]
+
+    def forward_densecl(self, img_a, img_b, bg0=None, bg1=None, visualize=False, step=0, new_epoch=False,
+                        pixel_ids_a=None, pixel_ids_b=None, region_ids_a=None, region_ids_b=None):
+        """builder.py:667-999 (DENSECL / PROPOSED_V2).  The images are used as they come (no compositing in this
+        mode); the losses run through `ops.densecl_loss`: no [N,1+K] logits, no [B,S^2,S^2] local similarity
+        matrix, no gather.  The reference's per-step wandb statistics (quartiles of the negatives, matching
+        rate) are logging only and are not computed; its IndexError at builder.py:861 on views that share a
+        pixel id is not reproduced."""
+        n = len(img_a)
+        bos = self.backbone_output_stride
+
+        def one_direction(x_q, x_k, ids_q, ids_k):
+            embd_q, q_local, q_global = self._query_features(x_q)
+            embd_k, k_local, k_global, k_pooled = self._key_features(x_k)
+            mix = self.lmbd_coordinate != 0 and ids_q is not None and ids_k is not None
+            loss, loss_g, loss_l = ops.densecl_loss(
+                embd_q, embd_k, q_local, k_local, q_global, k_global, self.queue, self.queue2, self.temp_global,
+                self.temp_local, self.lmbd_dense_loss, ids_q if mix else None, ids_k if mix else None, bos,
+                self.lmbd_coordinate)
+            return loss_g, loss_l, k_global, k_pooled
+
+        loss_global, loss_local, k_glob, k_loc = one_direction(img_a, img_b, pixel_ids_a, pixel_ids_b)
+        if self.use_symmetrical_loss:                          # builder.py:942-968
+            lg2, ll2, k_glob2, k_loc2 = one_direction(img_b, img_a, pixel_ids_b, pixel_ids_a)
+            loss_global, loss_local = loss_global + lg2, loss_local + ll2
+            if step % 2 == 0:
+                k_glob, k_loc = k_glob2, k_loc2
+        loss = (1 - self.lmbd_dense_loss) * loss_global + self.lmbd_dense_loss * loss_local
+        self._dequeue_and_enqueue(k_glob)                      # builder.py:975-976
+        self._dequeue_and_enqueue2(k_loc)
+        with torch.no_grad():
+            self.loss_o.update(loss, n)
+            self.loss_i.update(loss_global, n)
+            self.loss_d.update(loss_local, n)
+        return loss
 
     # ---------------------------------------------------------- forward_cp2
     def forward_cp2(self, img_a, img_b, bg0, bg1, visualize=False, step=0, new_epoch=False,

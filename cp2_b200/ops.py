@@ -4,6 +4,8 @@ torch is used for device memory, streams and autograd plumbing only; every op on
 hot path is a kernel of libcp2_b200.so.  All wrappers raise if their inputs are not
 CUDA tensors — there is no CPU path.
 """
+import math
+
 import torch
 
 from . import _lib
@@ -413,6 +415,126 @@ def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_
     stats = {"l_pos": l_pos, "acc_ins": nan, "acc_seg": acc_seg, "std_q_pos": meters[0], "std_k_pos": meters[1],
              "q_neg": q_neg, "k_neg": k_neg}
     return loss, loss_ins, loss_dense, k_pos, q_pos, stats
+
+
+# ------------------------------------------------- f2: forward_densecl losses
+def rows_nce(rows, pos_keys, z, G, inv_tau, want_grad=True):
+    """cp2_rows_nce -> (loss [1], terms [N], dq [N,C] | None)."""
+    N, C = rows.shape
+    dev = rows.device
+    loss = torch.empty((1,), device=dev, dtype=torch.float32)
+    terms = torch.empty((N,), device=dev, dtype=torch.float32)
+    dq = torch.empty((N, C), device=dev, dtype=torch.float32) if want_grad else None
+    _call("cp2_rows_nce", 2, _lib.load().cp2_rows_nce, _ptr(rows), _ptr(pos_keys), _ptr(z), _ptr(G), _ptr(loss),
+          _ptr(terms), _ptr(dq), float(inv_tau), N, C, _stream())
+    return loss, terms, dq
+
+
+TC_ROWS_MIN = 1024      # from this many rows on, the queue sums run on the dense-loss tensor-core kernels
+
+
+@torch.no_grad()
+def queue_sums_tc(rows, queue, inv_tau):
+    """z [N], G [N,C] as cp2_global_nce defines them (z = sum_k exp((l_k-1)/tau), G = sum_k exp((l_k-1)/tau) u_k),
+    for MANY rows, on the tcgen05 kernels of the dense loss instead of one queue pass per 32 rows: the queue is
+    cut into blocks of Pb = ceil128(N) entries, block n and the rows form "image" n of a [nb,Pb,Pb] problem;
+    cp2_dense_lse (queue entries on its summed axis) gives log sum exp per block and row, cp2_dense_grad
+    (rows as its query axis, lse := 1/tau, unit coefficients) gives the exp-weighted sums of queue entries.
+    Zero padding: padded queue entries add exp(-1/tau) each to z (subtracted) and nothing to G.
+    G comes back projected onto each row's tangent space (cp2_dense_grad's normalize backward with unit
+    norms); the F.normalize that produced the rows annihilates the missing component anyway."""
+    N, C = rows.shape
+    K = queue.shape[1]
+    dev = rows.device
+    Pb = (N + 127) // 128 * 128
+    nb = (K + Pb - 1) // Pb
+    pad = nb * Pb - K
+    ones_k = torch.ones((1, K), device=dev, dtype=torch.float32)
+    qt = prep_features(queue.unsqueeze(0), ones_k)[0]                    # [1,K,C] bf16 (columns re-normalised)
+    qblocks = torch.zeros((nb * Pb, C), device=dev, dtype=torch.bfloat16)
+    qblocks[:K] = qt[0]
+    qblocks = qblocks.view(nb, Pb, C)
+    rt = torch.zeros((Pb, C), device=dev, dtype=torch.bfloat16)
+    rt[:N] = rows
+    rblocks = rt.unsqueeze(0).expand(nb, Pb, C).contiguous()
+    lse = dense_lse(qblocks, rblocks, inv_tau)                          # [nb,Pb]: log sum over the block's entries
+    z = torch.exp(lse[:, :N] - inv_tau).sum(0) - pad * math.exp(-inv_tau)
+    shift = torch.full((nb, Pb), float(inv_tau), device=dev, dtype=torch.float32)
+    zeros_m = torch.zeros((nb, Pb), device=dev, dtype=torch.float32)
+    acc = dense_grad(rblocks, qblocks, shift, zeros_m, None, torch.ones_like(zeros_m),
+                     torch.ones((nb,), device=dev), torch.zeros((nb, C), device=dev), None, inv_tau)
+    G = acc.sum(0)[:, :N].t().contiguous()
+    return z, G
+
+
+class RowsInfoNCEFunction(torch.autograd.Function):
+    """`ContrastiveHead(pos, neg, temperature)` (builder.py:150-176) with pos = rows . pos_keys and
+    neg = rows @ queue, never materialising the [N,1+K] logits: the queue sums come from cp2_global_nce (few
+    rows: one pass over the queue per 32 rows) or from the dense loss's tensor-core kernels (`queue_sums_tc`,
+    N >= TC_ROWS_MIN), then cp2_rows_nce.  With the tensor-core path the gradient is the tangential one
+    (rows are unit vectors produced by F.normalize, whose backward drops the radial part anyway).  Gradient to `rows` only (keys and queue are
+    detached in the reference, builder.py:726, 768, 872)."""
+
+    @staticmethod
+    def forward(ctx, rows, pos_keys, queue, temp):
+        rows_c, pos_c = _f32c(rows.detach()), _f32c(pos_keys.detach())
+        if rows_c.shape[0] >= TC_ROWS_MIN:
+            z, G = queue_sums_tc(rows_c, queue, 1.0 / float(temp))
+        else:
+            z, G = global_nce(rows_c, queue, 1.0 / float(temp))
+        loss, _, dq = rows_nce(rows_c, pos_c, z, G, 1.0 / float(temp), want_grad=True)
+        ctx.save_for_backward(dq)
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        (dq,) = ctx.saved_tensors
+        return dq * g, None, None, None
+
+
+def rows_infonce(rows, pos_keys, queue, temp):
+    """rows, pos_keys [N,C] (rows unit vectors), queue [C,K] -> 0-d loss with a gradient to rows."""
+    return RowsInfoNCEFunction.apply(rows, pos_keys, queue, temp)
+
+
+@torch.no_grad()
+def positive_keys(k_local, idx, pix_q=None, pix_k=None, output_stride=1, lmbd_coordinate=0.0):
+    """builder.py:824-855 as vectors: k_local [B,C,P] unit columns, idx [B,P] -> kp [B*P,C]."""
+    _need_cuda(k_local, idx)
+    k_local = _f32c(k_local)
+    B, C, P = k_local.shape
+    idx = idx.contiguous()
+    assert idx.dtype == torch.int64 and tuple(idx.shape) == (B, P)
+    kp = torch.empty((B * P, C), device=k_local.device, dtype=torch.float32)
+    h = w = 1
+    if pix_q is not None:
+        assert pix_q.dtype == torch.int64 and pix_k.dtype == torch.int64 and pix_q.shape == pix_k.shape
+        pix_q, pix_k = pix_q.contiguous(), pix_k.contiguous()
+        h, w = pix_q.shape[1:]
+    _call("cp2_positive_keys", 1, _lib.load().cp2_positive_keys, _ptr(k_local), _ptr(idx), _ptr(pix_q), _ptr(pix_k),
+          _ptr(kp), float(lmbd_coordinate), B, C, P, h, w, int(output_stride), _stream())
+    return kp
+
+
+@torch.no_grad()
+def densecl_match(embd_q, embd_k):
+    """builder.py:817-821: idx[n,x] = argmax_y embd_q[n,:,x] . embd_k[n,:,y] on the 2048-d backbone features.
+    A plain batched library GEMM (cuBLAS through torch.bmm, fp32) + arg-max: the only [B,S^2,S^2] tensor
+    the path still writes (4.9 MB at configs[1])."""
+    return torch.bmm(embd_q.transpose(1, 2), embd_k).argmax(dim=2)
+
+
+def densecl_loss(embd_q, embd_k, q_local, k_local, q_global, k_global, queue, queue2, temp_global=0.2,
+                 temp_local=0.2, lmbd_dense=0.5, pix_q=None, pix_k=None, output_stride=1, lmbd_coordinate=0.0):
+    """One direction of forward_densecl (builder.py:762-931) on the unit features get_query_features /
+    get_key_features return: -> (loss, loss_global, loss_local), gradients to q_global and q_local."""
+    B, C, P = q_local.shape
+    loss_g = rows_infonce(q_global, k_global, queue, temp_global)
+    idx = densecl_match(embd_q.detach(), embd_k.detach())
+    kp = positive_keys(k_local.detach(), idx, pix_q, pix_k, output_stride, lmbd_coordinate)
+    rows = q_local.permute(0, 2, 1).reshape(B * P, C)
+    loss_l = rows_infonce(rows, kp, queue2, temp_local)
+    return (1 - lmbd_dense) * loss_g + lmbd_dense * loss_l, loss_g, loss_l
 
 
 # ------------------------------------------------------------- f4: accuracy meters

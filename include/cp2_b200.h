@@ -268,6 +268,27 @@ int cp2_global_top1(const float *q_pos, const float *k_pos, const float *q_neg, 
                     const float *queue, float *hit, float *acc, float *scratch, int B, int C, int K,
                     void *stream);
 
+/* f2 — ContrastiveHead (builder.py:150-176) for N rows against a queue, given cp2_global_nce's z [N], G [N,C]
+ * for those rows: the global loss of forward_densecl (builder.py:762-775; N = B) and its local loss
+ * (builder.py:866-873, 906-908; N = B*S^2, rows = q_local pixels, queue2).
+ *   l_r = rows[r].pos_keys[r];  terms[r] = log(z[r] + exp((l_r-1)/tau)) + (1-l_r)/tau;  loss[0] = mean_r terms
+ *   dq[r,:] = d loss / d rows[r,:] = ((G[r,:] + exp((l_r-1)/tau) pos_keys[r,:]) / Z_r - pos_keys[r,:]) / (N tau)
+ * rows, pos_keys [N,C] f32 (rows unit vectors); terms [N] scratch/out; dq may be NULL (no gradient wanted). */
+int cp2_rows_nce(const float *rows, const float *pos_keys, const float *z, const float *G, float *loss,
+                 float *terms, float *dq, float inv_tau, int N, int C, void *stream);
+
+/* f2 — the positive of every query pixel (builder.py:824-855), as a vector: kp[n*P+x,:] = k_local[n,:,idx[n,x]],
+ * and where key pixels share query pixel x's id: (1-lmbd) * that + lmbd * sum_{y: pix_k[y]==pix_q[x]} k_local[n,:,y]
+ * so that pos_local = q_local_x . kp_x without the [B,S^2,S^2] local similarity matrix.
+ *   k_local [B,C,P] f32 unit columns; idx [B,P] int64 (the backbone-feature match, builder.py:817-821);
+ *   pix_q, pix_k: [B,ids_h,ids_w] int64 id maps read at the [os//2::os] lattice (os = 1: already sub-sampled),
+ *   or both NULL (no coordinate mixing); kp [B*P,C] f32 out.
+ * Note: the reference itself raises IndexError at builder.py:861 whenever one id is shared; this implements the
+ * formula of :839-855. */
+int cp2_positive_keys(const float *k_local, const int64_t *idx, const int64_t *pix_q, const int64_t *pix_k,
+                      float *kp, float lmbd_coordinate, int B, int C, int P, int ids_h, int ids_w, int os,
+                      void *stream);
+
 #ifdef __cplusplus
 }
 #endif
