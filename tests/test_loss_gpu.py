@@ -174,3 +174,24 @@ def test_model_two_steps_against_reference_golden(monkeypatch):
     assert all(v == 1.0 for v in model.correlation_ious)
     model.reset_metrics()
     assert model.correlation_ious == [] and model.masked_correlation_ious == []
+
+
+def test_loss_nan_hazard_matches_reference(ops):
+    """a view without a foreground sample on the lattice gives `labels.sum() == 0`
+    and a NaN dense loss in the reference (builder.py:1434-1437); the kernels do not hide it, and the other
+    images of the batch are unaffected (their gradients stay finite and equal to the oracle's)."""
+    g = torch.Generator().manual_seed(9)
+    B, C, hw, K = 3, 128, 14, 512
+    q = torch.randn(B, C, hw, hw, generator=g)
+    k = torch.randn(B, C, hw, hw, generator=g)
+    ma = (torch.rand(B, hw * hw, generator=g) < 0.6).float()
+    mb = (torch.rand(B, hw * hw, generator=g) < 0.6).float()
+    mb[1] = 0.0                                            # image 1: no foreground key pixel
+    queue = torch.nn.functional.normalize(torch.randn(C, K, generator=g), dim=0)
+    qr = q.clone().requires_grad_(True)
+    r = O.cp2_loss(qr, k, ma, mb, queue, 0.2, 0.2, 0.2)
+    assert torch.isnan(r["loss"]) and torch.isnan(r["loss_dense"]) and torch.isfinite(r["loss_ins"])
+    qd = q.cuda().requires_grad_(True)
+    loss, li, ld, _, _, _ = ops.cp2_loss(qd, k.cuda(), ma.cuda(), mb.cuda(), queue.cuda(), 0.2, 0.2, 0.2)
+    assert torch.isnan(loss).item() and torch.isnan(ld).item()
+    np.testing.assert_allclose(li.item(), r["loss_ins"].item(), rtol=LOSS_RTOL)
