@@ -28,7 +28,8 @@ __device__ __forceinline__ void load_cols(const float *feat_b, int C, int P, int
   }
 }
 
-// One CTA = 32 key pixels of one image against all query pixels: best (value, flat index x*P+y) of the tile.
+// One CTA = 32 key pixels x 64 query pixels of one image (grid: key tiles, images, query chunks):
+// best (value, flat index x*P+y) of the tile.
 __global__ void __launch_bounds__(MT)
 dense_top1_kernel(const float *__restrict__ q, const float *__restrict__ k, float *__restrict__ part_v,
                   int *__restrict__ part_i, int C, int P) {
@@ -49,8 +50,8 @@ dense_top1_kernel(const float *__restrict__ q, const float *__restrict__ k, floa
   }
   const int y = y0 + lane;
   Best best{-INFINITY, 0x7fffffff};
-  for (int x0 = 0; x0 < P; x0 += XT) {
-    __syncthreads();
+  {
+    const int x0 = blockIdx.z * XT;
     load_cols<XT>(qb, C, P, x0, qs);
     __syncthreads();
     if (threadIdx.x < XT) {
@@ -89,8 +90,9 @@ dense_top1_kernel(const float *__restrict__ q, const float *__restrict__ k, floa
   __syncthreads();
   if (threadIdx.x == 0) {
     for (int w = 1; w < MT / 32; ++w) take(best, red_v[w], red_i[w]);
-    part_v[(long long)b * gridDim.x + blockIdx.x] = best.v;
-    part_i[(long long)b * gridDim.x + blockIdx.x] = best.i;
+    const long long slot = ((long long)b * gridDim.x + blockIdx.x) * gridDim.z + blockIdx.z;
+    part_v[slot] = best.v;
+    part_i[slot] = best.i;
   }
 }
 
@@ -123,17 +125,19 @@ dense_top1_finalize_kernel(const float *__restrict__ part_v, const int *__restri
   }
 }
 
-// max_k q_pos[r] . queue[:,k] over this CTA's 256-column blocks, 32 rows at a time (thread = column).
-__global__ void __launch_bounds__(MT)
+constexpr int GT = 128;                 // threads of global_top1_kernel: more, smaller CTAs keep more loads in flight
+
+// max_k q_pos[r] . queue[:,k] over this CTA's 128-column blocks, 32 rows at a time (thread = column).
+__global__ void __launch_bounds__(GT)
 global_top1_kernel(const float *__restrict__ q_pos, const float *__restrict__ queue, float *__restrict__ part,
                    int B, int C, int K) {
   extern __shared__ __align__(16) float qT[];       // [C][32]
-  __shared__ float red[MT / 32][32];
+  __shared__ float red[GT / 32][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int nblk = (K + MT - 1) / MT;
+  const int nblk = (K + GT - 1) / GT;
   for (int r0 = 0; r0 < B; r0 += 32) {
     __syncthreads();
-    for (int i = threadIdx.x; i < C * 32; i += MT) {
+    for (int i = threadIdx.x; i < C * 32; i += GT) {
       const int c = i >> 5, r = i & 31;
       qT[i] = r0 + r < B ? q_pos[(long long)(r0 + r) * C + c] : 0.f;
     }
@@ -142,7 +146,7 @@ global_top1_kernel(const float *__restrict__ q_pos, const float *__restrict__ qu
 #pragma unroll
     for (int r = 0; r < 32; ++r) m[r] = -INFINITY;
     for (int blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
-      const int col = blk * MT + threadIdx.x;
+      const int col = blk * GT + threadIdx.x;
       if (col >= K) continue;
       float acc[32];
 #pragma unroll
@@ -172,7 +176,7 @@ global_top1_kernel(const float *__restrict__ q_pos, const float *__restrict__ qu
     __syncthreads();
     if (warp == 0 && r0 + lane < B) {
       float v = red[0][lane];
-      for (int w = 1; w < MT / 32; ++w) v = fmaxf(v, red[w][lane]);
+      for (int w = 1; w < GT / 32; ++w) v = fmaxf(v, red[w][lane]);
       part[(long long)blockIdx.x * B + r0 + lane] = v;
     }
   }
@@ -216,13 +220,15 @@ global_top1_finalize_kernel(const float *__restrict__ part, const float *__restr
 }
 
 int top1_ctas(int K) {
-  const int nblk = cp2_cdiv(K, MT), cap = 2 * cp2_num_sms();
+  const int nblk = cp2_cdiv(K, GT), cap = 4 * cp2_num_sms();
   return nblk < cap ? nblk : cap;
 }
 
 }  // namespace
 
-extern "C" int64_t cp2_dense_top1_scratch_floats(int B, int P) { return 2LL * B * cp2_cdiv(P, YT); }
+extern "C" int64_t cp2_dense_top1_scratch_floats(int B, int P) {
+  return 2LL * B * cp2_cdiv(P, YT) * cp2_cdiv(P, XT);
+}
 
 extern "C" int cp2_dense_top1(const float *q, const float *k, const float *mask_a, const float *mask_b, float *hit,
                               float *acc, float *scratch, int B, int C, int P, void *stream) {
@@ -230,12 +236,13 @@ extern "C" int cp2_dense_top1(const float *q, const float *k, const float *mask_
               "cp2_dense_top1: bad shape B=%d C=%d P=%d", B, C, P);
   CP2_REQUIRE(q && k && mask_a && mask_b && hit && acc && scratch, "cp2_dense_top1: null pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int tiles = cp2_cdiv(P, YT);
+  const int ytiles = cp2_cdiv(P, YT), xchunks = cp2_cdiv(P, XT), tiles = ytiles * xchunks;
+  CP2_REQUIRE(xchunks <= 65535 && B <= 65535, "cp2_dense_top1: B=%d or P=%d too large for the grid", B, P);
   float *part_v = scratch;
   int *part_i = reinterpret_cast<int *>(scratch + (size_t)B * tiles);
   const size_t smem = (size_t)C * (YT + XT) * sizeof(float);
   CP2_CUDA(cudaFuncSetAttribute(dense_top1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dense_top1_kernel<<<dim3(tiles, B), MT, smem, st>>>(q, k, part_v, part_i, C, P);
+  dense_top1_kernel<<<dim3(ytiles, B, xchunks), MT, smem, st>>>(q, k, part_v, part_i, C, P);
   CP2_LAUNCH_CHECK();
   dense_top1_finalize_kernel<<<1, MT, 0, st>>>(part_v, part_i, mask_a, mask_b, hit, acc, B, P, tiles);
   CP2_LAUNCH_CHECK();
@@ -254,7 +261,7 @@ extern "C" int cp2_global_top1(const float *q_pos, const float *k_pos, const flo
   const int nctas = top1_ctas(K);
   const size_t smem = (size_t)C * 32 * sizeof(float);
   CP2_CUDA(cudaFuncSetAttribute(global_top1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  global_top1_kernel<<<nctas, MT, smem, st>>>(q_pos, queue, scratch, B, C, K);
+  global_top1_kernel<<<nctas, GT, smem, st>>>(q_pos, queue, scratch, B, C, K);
   CP2_LAUNCH_CHECK();
   global_top1_finalize_kernel<<<1, MT, 0, st>>>(scratch, q_pos, k_pos, q_neg, k_neg, hit, acc, B, C, nctas);
   CP2_LAUNCH_CHECK();
