@@ -10,7 +10,7 @@
 namespace {
 
 constexpr int MT = 256;                 // threads per CTA
-constexpr int YT = 32;                  // key pixels per CTA (lane = key)
+constexpr int YT = 64;                  // key pixels per CTA (lane = keys y0+lane and y0+32+lane)
 constexpr int XT = 64;                  // query pixels per chunk (warp w owns rows 8w..8w+7)
 constexpr float kEps = 1e-12f;          // F.normalize eps
 
@@ -19,16 +19,34 @@ __device__ __forceinline__ void take(Best &a, float v, int i) {
   if (v > a.v || (v == a.v && i < a.i)) { a.v = v; a.i = i; }     // first occurrence on ties
 }
 
-// rows [c][W] <- feat[b, c, p0 .. p0+W) (zero past P); feat is [B,C,P] f32
+// rows [c][W] <- feat[b, c, p0 .. p0+W) (zero past P); feat is [B,C,P] f32.  128-bit loads when the rows are
+// 16-byte aligned (P % 4 == 0), all of a thread's loads issued before the first store.
 template <int W>
 __device__ __forceinline__ void load_cols(const float *feat_b, int C, int P, int p0, float *dst) {
+  if ((P & 3) == 0) {
+    constexpr int W4 = W / 4;
+    const int n4 = C * W4;
+    for (int i0 = threadIdx.x; i0 < n4; i0 += 8 * MT) {
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * MT, c = i / W4, j = (i - c * W4) * 4;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < n4 && p0 + j < P) v[u] = *reinterpret_cast<const float4 *>(feat_b + (long long)c * P + p0 + j);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (i0 + u * MT < n4) *reinterpret_cast<float4 *>(dst + 4 * (i0 + u * MT)) = v[u];
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < C * W; i += MT) {
     const int c = i / W, j = i - c * W;
     dst[i] = p0 + j < P ? feat_b[(long long)c * P + p0 + j] : 0.f;
   }
 }
 
-// One CTA = 32 key pixels x 64 query pixels of one image (grid: key tiles, images, query chunks):
+// One CTA = 64 key pixels x 64 query pixels of one image (grid: key tiles, images, query chunks):
 // best (value, flat index x*P+y) of the tile.
 __global__ void __launch_bounds__(MT)
 dense_top1_kernel(const float *__restrict__ q, const float *__restrict__ k, float *__restrict__ part_v,
@@ -43,10 +61,10 @@ dense_top1_kernel(const float *__restrict__ q, const float *__restrict__ k, floa
   const float *qb = q + (long long)b * C * P, *kb = k + (long long)b * C * P;
   load_cols<YT>(kb, C, P, y0, ks);
   __syncthreads();
-  if (warp == 0) {
+  if (threadIdx.x < YT) {
     float s = 0.f;
-    for (int c = 0; c < C; ++c) s = fmaf(ks[c * YT + lane], ks[c * YT + lane], s);
-    invk_s[lane] = 1.f / fmaxf(sqrtf(s), kEps);
+    for (int c = 0; c < C; ++c) s = fmaf(ks[c * YT + threadIdx.x], ks[c * YT + threadIdx.x], s);
+    invk_s[threadIdx.x] = 1.f / fmaxf(sqrtf(s), kEps);
   }
   const int y = y0 + lane;
   Best best{-INFINITY, 0x7fffffff};
@@ -59,24 +77,30 @@ dense_top1_kernel(const float *__restrict__ q, const float *__restrict__ k, floa
       for (int c = 0; c < C; ++c) s = fmaf(qs[c * XT + threadIdx.x], qs[c * XT + threadIdx.x], s);
       invq_s[threadIdx.x] = 1.f / fmaxf(sqrtf(s), kEps);
     }
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    // two keys per thread: every 128-bit broadcast read of the query tile feeds 8 FMAs instead of 4
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, bcc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll 4
     for (int c = 0; c < C; ++c) {
-      const float kv = ks[c * YT + lane];
+      const float kv = ks[c * YT + lane], kw = ks[c * YT + 32 + lane];
       const float4 a = *reinterpret_cast<const float4 *>(qs + c * XT + warp * 8);
       const float4 d = *reinterpret_cast<const float4 *>(qs + c * XT + warp * 8 + 4);
       acc[0] = fmaf(a.x, kv, acc[0]); acc[1] = fmaf(a.y, kv, acc[1]);
       acc[2] = fmaf(a.z, kv, acc[2]); acc[3] = fmaf(a.w, kv, acc[3]);
       acc[4] = fmaf(d.x, kv, acc[4]); acc[5] = fmaf(d.y, kv, acc[5]);
       acc[6] = fmaf(d.z, kv, acc[6]); acc[7] = fmaf(d.w, kv, acc[7]);
+      bcc[0] = fmaf(a.x, kw, bcc[0]); bcc[1] = fmaf(a.y, kw, bcc[1]);
+      bcc[2] = fmaf(a.z, kw, bcc[2]); bcc[3] = fmaf(a.w, kw, bcc[3]);
+      bcc[4] = fmaf(d.x, kw, bcc[4]); bcc[5] = fmaf(d.y, kw, bcc[5]);
+      bcc[6] = fmaf(d.z, kw, bcc[6]); bcc[7] = fmaf(d.w, kw, bcc[7]);
     }
     __syncthreads();                     // invq_s written
-    if (y < P) {
-      const float ik = invk_s[lane];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int x = x0 + warp * 8 + i;
-        if (x < P) take(best, acc[i] * invq_s[warp * 8 + i] * ik, x * P + y);
+    for (int i = 0; i < 8; ++i) {
+      const int x = x0 + warp * 8 + i;
+      if (x < P) {
+        const float iq = invq_s[warp * 8 + i];
+        if (y < P) take(best, acc[i] * iq * invk_s[lane], x * P + y);
+        if (y + 32 < P) take(best, bcc[i] * iq * invk_s[32 + lane], x * P + y + 32);
       }
     }
   }
@@ -125,19 +149,17 @@ dense_top1_finalize_kernel(const float *__restrict__ part_v, const int *__restri
   }
 }
 
-constexpr int GT = 128;                 // threads of global_top1_kernel: more, smaller CTAs keep more loads in flight
-
-// max_k q_pos[r] . queue[:,k] over this CTA's 128-column blocks, 32 rows at a time (thread = column).
-__global__ void __launch_bounds__(GT)
+// max_k q_pos[r] . queue[:,k] over this CTA's 256-column blocks, 32 rows at a time (thread = column).
+__global__ void __launch_bounds__(MT)
 global_top1_kernel(const float *__restrict__ q_pos, const float *__restrict__ queue, float *__restrict__ part,
                    int B, int C, int K) {
   extern __shared__ __align__(16) float qT[];       // [C][32]
-  __shared__ float red[GT / 32][32];
+  __shared__ float red[MT / 32][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int nblk = (K + GT - 1) / GT;
+  const int nblk = (K + MT - 1) / MT;
   for (int r0 = 0; r0 < B; r0 += 32) {
     __syncthreads();
-    for (int i = threadIdx.x; i < C * 32; i += GT) {
+    for (int i = threadIdx.x; i < C * 32; i += MT) {
       const int c = i >> 5, r = i & 31;
       qT[i] = r0 + r < B ? q_pos[(long long)(r0 + r) * C + c] : 0.f;
     }
@@ -146,7 +168,7 @@ global_top1_kernel(const float *__restrict__ q_pos, const float *__restrict__ qu
 #pragma unroll
     for (int r = 0; r < 32; ++r) m[r] = -INFINITY;
     for (int blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
-      const int col = blk * GT + threadIdx.x;
+      const int col = blk * MT + threadIdx.x;
       if (col >= K) continue;
       float acc[32];
 #pragma unroll
@@ -176,7 +198,7 @@ global_top1_kernel(const float *__restrict__ q_pos, const float *__restrict__ qu
     __syncthreads();
     if (warp == 0 && r0 + lane < B) {
       float v = red[0][lane];
-      for (int w = 1; w < GT / 32; ++w) v = fmaxf(v, red[w][lane]);
+      for (int w = 1; w < MT / 32; ++w) v = fmaxf(v, red[w][lane]);
       part[(long long)blockIdx.x * B + r0 + lane] = v;
     }
   }
@@ -220,7 +242,7 @@ global_top1_finalize_kernel(const float *__restrict__ part, const float *__restr
 }
 
 int top1_ctas(int K) {
-  const int nblk = cp2_cdiv(K, GT), cap = 4 * cp2_num_sms();
+  const int nblk = cp2_cdiv(K, MT), cap = 2 * cp2_num_sms();
   return nblk < cap ? nblk : cap;
 }
 
@@ -232,7 +254,7 @@ extern "C" int64_t cp2_dense_top1_scratch_floats(int B, int P) {
 
 extern "C" int cp2_dense_top1(const float *q, const float *k, const float *mask_a, const float *mask_b, float *hit,
                               float *acc, float *scratch, int B, int C, int P, void *stream) {
-  CP2_REQUIRE(B > 0 && P > 0 && C > 0 && C <= 512 && (long long)P * P < 0x7fffffffLL,
+  CP2_REQUIRE(B > 0 && P > 0 && C > 0 && C <= 384 && (long long)P * P < 0x7fffffffLL,
               "cp2_dense_top1: bad shape B=%d C=%d P=%d", B, C, P);
   CP2_REQUIRE(q && k && mask_a && mask_b && hit && acc && scratch, "cp2_dense_top1: null pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -261,7 +283,7 @@ extern "C" int cp2_global_top1(const float *q_pos, const float *k_pos, const flo
   const int nctas = top1_ctas(K);
   const size_t smem = (size_t)C * 32 * sizeof(float);
   CP2_CUDA(cudaFuncSetAttribute(global_top1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  global_top1_kernel<<<nctas, GT, smem, st>>>(q_pos, queue, scratch, B, C, K);
+  global_top1_kernel<<<nctas, MT, smem, st>>>(q_pos, queue, scratch, B, C, K);
   CP2_LAUNCH_CHECK();
   global_top1_finalize_kernel<<<1, MT, 0, st>>>(scratch, q_pos, k_pos, q_neg, k_neg, hit, acc, B, C, nctas);
   CP2_LAUNCH_CHECK();
