@@ -50,6 +50,10 @@ def parse_args():
     ap.add_argument("--sweep-dims", default="128,256")
     ap.add_argument("--sweep-batch", type=int, default=256)
     ap.add_argument("--sweep-iters", type=int, default=10)
+    ap.add_argument("--cpu-budget", type=float, default=200.0, help="--impl reference: seconds of CPU work allowed")
+    ap.add_argument("--no-eager-baseline", action="store_true", help="skip the same-GPU eager (reference) legs")
+    ap.add_argument("--workload", default="cp2", choices=["cp2", "mirror"],
+                    help="cp2: configs[1] (the metric); mirror: configs[4] MirrorModule.shared_step at 512x512")
     return ap.parse_args()
 
 
@@ -60,8 +64,9 @@ def workload_config(batch, n_gpus, nchw=False):
                     "for the mmseg segmentor), 224x224 views (14x14 map), C=128, queue 65536",
         "batch_per_gpu": batch, "global_batch": batch * n_gpus, "image": IMG, "feature_map": IMG // OS_,
         "dim": DIM, "queue": QUEUE, "temp_global": TAU_G, "temp_dense": TAU_D, "lmbd_dense": LMBD,
-        "optimizer": "SGD(lr=1e-3, momentum=0.9, wd=1e-4)", "precision": "fp32 encoder (as the reference); "
-        "bf16 operands / fp32 accumulate in the two contraction kernels",
+        "optimizer": "SGD(lr=1e-3, momentum=0.9, wd=1e-4)", "precision": "fp32 parameters / activations; the "
+        "(out-of-scope) cuDNN convolutions run as TF32 tensor-op kernels (PyTorch's default, what the reference "
+        "gets too); bf16 operands / fp32 accumulate in the two contraction kernels of the loss",
         "parallelism": f"dp{n_gpus}",
         "l2": "no flush: one step streams >10 GB of activations and 0.8 GB of EMA traffic through the 126 MB L2",
     }
@@ -151,83 +156,184 @@ def synth_batch(batch, seed, pinned=False):
     return out
 
 
-# ----------------------------------------------------------------- CPU legs (oracle port)
-def _cpu_port(batch, seed=0):
-    """The reference's CPU path restated (oracle/cp2_oracle.py:CP2StepPort) on the same workload."""
+def feature_encoder(batch, dim, hw, seed):
+    """'Encoder' that returns a learnable stored feature map whatever the image: isolates the loss slice
+    (composite, id maps, normalise, both InfoNCE losses, enqueue, backward to the features) of either
+    implementation for the same-GPU comparison."""
+    import torch
+    import torch.nn as nn
+
+    class _BB(nn.Module):
+        def forward(self, x):
+            y = x.new_zeros(x.shape[0], 1, hw, hw)
+            return (y, y, y, y)
+
+        def init_weights(self):
+            pass
+
+    class FeatureEncoder(nn.Module):
+        def __init__(self):
+            super().__init__()
+            g = torch.Generator().manual_seed(seed)
+            self.feat = nn.Parameter(torch.randn(batch, dim, hw, hw, generator=g))
+            self.backbone = _BB()
+
+        def forward(self, x):
+            if x.shape[0] != self.feat.shape[0]:      # the constructor's 2-image stride probe (builder.py:392-402)
+                return x.new_zeros(x.shape[0], self.feat.shape[1], x.shape[2] // 16, x.shape[3] // 16)
+            return self.feat * 1.0
+
+    return FeatureEncoder()
+
+
+# ----------------------------------------------------------------- CPU legs (the reference's own code)
+def _host_threads():
+    """All host threads, set explicitly: torch.distributed.run exports OMP_NUM_THREADS=1, which would otherwise
+    pin the reference arm to one core at N > 1."""
+    import torch
+    n = os.cpu_count() or 1
+    try:
+        n = len(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        pass
+    torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
+def _reference_stepper(batch, device="cpu", channels_last=False, encoder="deeplab", seed=0):
+    """-> (step_fn(batch_dict) -> loss float, kind).  kind "_ref": the UNMODIFIED reference builder.MODEL
+    (source tree or oracle/_ref/*.pyc, through oracle/ref_harness.py) driven as main.py:590-644 drives it;
+    kind "port": oracle/cp2_oracle.CP2StepPort, only when no reference module is reachable (CPU only)."""
     import torch
     from cp2_b200.encoder import DeepLabV3Encoder
+    from oracle import ref_harness as rh
+    if encoder == "deeplab":
+        factory = lambda: DeepLabV3Encoder(dim=DIM)
+    else:
+        seeds = iter((11, 12))
+        factory = lambda: feature_encoder(batch, DIM, IMG // OS_, next(seeds))
+    if rh.reference_available():
+        from oracle.ref_step import ReferenceStep
+        ref = ReferenceStep(factory, device=device, dim=DIM, K=QUEUE, temp_global=TAU_G, temp_local=TAU_D,
+                            lmbd_dense=LMBD, lr=1e-3, seed=seed, channels_last=channels_last)
+        return ref.step, "_ref", ref
+    if device != "cpu":
+        return None, None, None
     from oracle import cp2_oracle as O
-    port = O.CP2StepPort(lambda: DeepLabV3Encoder(dim=DIM), dim=DIM, K=QUEUE, temp_global=TAU_G,
-                         temp_local=TAU_D, lmbd_dense=LMBD, output_stride=OS_, lr=1e-3, seed=seed)
-    b = synth_batch(batch, seed=1234)
-    return port, b, torch.get_num_threads()
-
-
-def cpu_baseline_leg(budget_s=20.0):
-    """Bounded sample for the own arm's `cpu_baseline` object: batch 8, 1 warm-up + up to 5 timed steps."""
-    batch = 8
-    port, b, threads = _cpu_port(batch)
-    t0 = time.perf_counter()
-    port.step(**b)
-    warm = time.perf_counter() - t0
-    n = max(1, min(5, int(budget_s / max(warm, 1e-3))))
-    t0 = time.perf_counter()
-    for _ in range(n):
-        port.step(**b)
-    dt = (time.perf_counter() - t0) / n
-    return {"value": batch / dt, "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"{n} timed steps (after 1 warm-up) of the full pre-training step at batch {batch} "
-                      f"(same model, queue {QUEUE}, 224x224), {dt * 1e3:.0f} ms/step; host has "
-                      f"{os.cpu_count()} logical CPUs, torch used {threads} threads"}
+    port = O.CP2StepPort(factory, dim=DIM, K=QUEUE, temp_global=TAU_G, temp_local=TAU_D, lmbd_dense=LMBD,
+                         output_stride=OS_, lr=1e-3, seed=seed)
+    return (lambda b: port.step(**b)), "port", port
 
 
 def reference_arm(args):
-    """--impl reference: the reference's own CPU implementation of the path (port), all host threads."""
+    """--impl reference: the reference's own CPU implementation of the step, all host threads, the FULL per-GPU
+    batch of configs[1] every step (the step COUNT is what shrinks when the budget would be exceeded)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    total = args.steps + args.warmup
-    # calibrate at batch 2 (BatchNorm needs > 1 sample), then size each step's sample so the run ends in minutes
-    port, b2, threads = _cpu_port(2)
+    threads = _host_threads()
+    step, kind, _ = _reference_stepper(args.batch)
+    b = synth_batch(args.batch, seed=1234)
+    budget = float(args.cpu_budget)
     t0 = time.perf_counter()
-    port.step(**b2)
-    port.step(**b2)
-    per_img = (time.perf_counter() - t0) / 4.0
-    budget = 150.0
-    batch = int(budget / max(total, 1) / max(per_img, 1e-4))
-    batch = max(2, min(args.batch, batch))
-    b = synth_batch(batch, seed=1234)
-    for _ in range(args.warmup):
-        port.step(**b)
+    step(b)                                             # warm-up 1 (also sizes the rest)
+    first = time.perf_counter() - t0
+    want = args.steps + args.warmup
+    fit = max(2, int(budget / max(first, 1e-3)))       # steps that fit the budget, incl. the one just run
+    warm = max(0, min(args.warmup, fit - 2) - 1)
+    timed = max(1, min(args.steps, fit - 1 - warm))
+    for _ in range(warm):
+        step(b)
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        port.step(**b)
-    dt = (time.perf_counter() - t0) / max(args.steps, 1)
-    value = batch / dt
-    sample = (f"each step = the full pre-training step on {batch} of the {args.batch} images of one GPU's batch "
-              f"(sized after a batch-2 calibration so that {total} steps fit in ~{budget:.0f} s); "
-              f"{os.cpu_count()} logical CPUs, torch threads {threads}")
+    for _ in range(timed):
+        step(b)
+    dt = (time.perf_counter() - t0) / timed
+    value = args.batch / dt
+    what = ("the unmodified reference builder.MODEL.forward_cp2 + backward + SGD (main.py:616-644) via "
+            "oracle/ref_harness.py" if kind == "_ref" else "oracle/cp2_oracle.CP2StepPort (reference modules not reachable)")
+    sample = (f"{timed} timed steps after {warm + 1} warm-up (asked {args.steps}+{args.warmup}; budget {budget:.0f} s) "
+              f"of the full pre-training step at the full per-GPU batch {args.batch}: {what}; segmentor = the same "
+              f"torchvision stand-in as the GPU arm; {dt * 1e3:.0f} ms/step; {os.cpu_count()} logical CPUs, "
+              f"torch threads {threads} (set explicitly; OMP_NUM_THREADS in env = {os.environ.get('OMP_NUM_THREADS')})")
     cfg = workload_config(args.batch, args.gpus)
-    cfg["sample_batch"] = batch
+    cfg["note"] = ("CPU arm: one process on rank 0's host cores runs ONE GPU's batch; at N > 1 the driver's ratio "
+                   "compares it with N GPUs' aggregate")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "steps": args.steps, "warmup": args.warmup, "steps_executed": timed, "ms_per_step": dt * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": cfg,
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads,
+                             "kind": "reference" if kind == "_ref" else "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
 
 
+def cpu_baseline_leg(batch, budget_s=25.0):
+    """`cpu_baseline` of the own arm: the reference arm in a child process (its `.cuda()` -> identity patch and
+    thread settings stay out of this process), bounded to ~budget_s of CPU work."""
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "5", "--warmup", "1",
+           "--batch", str(batch), "--cpu-budget", str(budget_s)]
+    env = dict(os.environ)
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "OMP_NUM_THREADS", "CUDA_VISIBLE_DEVICES"):
+        env.pop(k, None)
+    env["CUDA_VISIBLE_DEVICES"] = ""                    # host cores only
+    try:
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600, env=env)
+        for ln in reversed(r.stdout.strip().splitlines()):
+            if ln.startswith("{"):
+                return json.loads(ln)["cpu_baseline"]
+        return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "failed: " + r.stderr[-300:]}
+    except Exception as e:  # noqa: BLE001
+        return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"failed: {e}"}
+
+
 # ------------------------------------------------------------------ dense-loss microbench
-def dense_sweep(args, peaks):
+def _eager_dense_us(q, k, ma, mb, inv_tau, bf16, chunk, max_chunks=2):
+    """The eager torch formulation of the dense loss (builder.py:1261,1279,1289-1292,1431-1437) + autograd to q on
+    the same GPU, fp32 (`bf16=False`: what the reference runs, cuBLAS fp32/TF32 bmm + separate softmax kernels)
+    or with the bmm in bf16 (`bf16=True`).  The [b,P,P] tensors force chunking at 56x56: `max_chunks` chunks of
+    `chunk` images are timed and the figure is scaled to the whole batch."""
+    import torch
+    import torch.nn.functional as F
+    B = q.shape[0]
+    n = min(max_chunks, (B + chunk - 1) // chunk)
+    ts = []
+    for it in range(n + 1):
+        i0 = (it % n) * chunk
+        qs = q[i0:i0 + chunk].clone().requires_grad_()
+        ks, a, b = k[i0:i0 + chunk], ma[i0:i0 + chunk], mb[i0:i0 + chunk]
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        qh, kh = F.normalize(qs, dim=1), F.normalize(ks, dim=1)
+        if bf16:
+            logits = torch.bmm(qh.transpose(1, 2).to(torch.bfloat16), kh.to(torch.bfloat16)).float()
+        else:
+            logits = torch.einsum("ncx,ncy->nxy", qh, kh)
+        labels = torch.einsum("nx,ny->nxy", a, b)
+        nl = -torch.log_softmax(logits * inv_tau, dim=1)
+        loss = ((nl * labels).flatten(1).sum(1) / labels.flatten(1).sum(1)).mean()
+        loss.backward()
+        e1.record()
+        torch.cuda.synchronize()
+        if it > 0:
+            ts.append(e0.elapsed_time(e1) * 1e3)
+        del qs, logits, labels, nl, loss
+    return statistics.mean(ts) * (B / chunk), n * chunk
+
+
+def dense_sweep(args, peaks, eager=True):
     """configs[3]: dense pixel InfoNCE fwd+bwd at B=256 images/GPU, P in {14^2,28^2,56^2}, C in {128,256}.
     Algorithmic work 4*B*P^2*C FLOP (Q^T K forward + dQ backward; the backward's recomputation of Q^T K is
-    not counted, and background key columns skipped by the compaction are still counted: `frac` is the
-    dense-algorithmic figure, `executed_frac` = share of key columns actually visited).  Two mask variants
-    (SURVEY.md 8d): Bernoulli(0.65) fg masks (CP2's copy-paste masks are 50-80 % foreground) and all-ones
-    (nothing to skip).  `us` = cp2_dense_lse + cp2_dense_grad; `us_with_prep` adds the two
-    cp2_prep_features launches.  L2 is flushed between iterations."""
+    executed but not counted).  Two mask variants: all-ones (nothing can be skipped: the honest
+    roofline point) and Bernoulli(0.65) fg masks (CP2's copy-paste masks are 50-80 % foreground), where the
+    key compaction skips background key columns.  `frac` is the EXECUTED-work fraction of the bf16 burst peak
+    (counted FLOP x share of key columns actually visited); `frac_dense_algorithmic` counts the skipped columns
+    as if they had been computed.  `us` = cp2_dense_lse + cp2_dense_grad; `us_with_prep` adds the two
+    cp2_prep_features launches.  L2 is flushed between iterations.  `eager_*`: the eager torch formulation on
+    the same GPU (fp32 and bf16-bmm), chunked, scaled to B."""
     import torch
     from cp2_b200 import ops
     dev = torch.device("cuda")
@@ -242,7 +348,7 @@ def dense_sweep(args, peaks):
             alpha = torch.full((B,), 1.0 / B, device=dev)
             v1 = torch.zeros(B, C, device=dev)
             inv_tau = 1.0 / TAU_D
-            for variant in ("bernoulli(0.65)", "ones"):
+            for variant in ("ones", "bernoulli(0.65)"):
                 g8 = torch.Generator(device=dev).manual_seed(8)
                 if variant == "ones":
                     ma = torch.ones(B, P, device=dev)
@@ -258,8 +364,7 @@ def dense_sweep(args, peaks):
                     qh, q_inv, _, _, _ = ops.prep_features(q, ma)
                     kh, _, _, _, cnt = ops.prep_features(k, mb, compact=True)
                     e[1].record()
-                    lse = ops.dense_lse(qh, kh, inv_tau, cnt)
-                    dq = ops.dense_grad(qh, kh, lse, ma, None, q_inv, alpha, v1, None, inv_tau, key_count=cnt)
+                    lse, dq = ops.dense_fwd_bwd(qh, kh, cnt, ma, q_inv, alpha, v1, None, inv_tau)
                     e[2].record()
                     torch.cuda.synchronize()
                     if it >= 3:
@@ -268,14 +373,36 @@ def dense_sweep(args, peaks):
                 us, us_all = statistics.mean(t_core), statistics.mean(t_all)
                 flop = 4.0 * B * P * P * C
                 tf = flop / (us * 1e-6) / 1e12
-                rows.append({"P": P, "C": C, "B": B, "masks": variant, "us": round(us, 2),
-                             "us_with_prep": round(us_all, 2), "flop": flop, "tflops": round(tf, 2),
-                             "peak": peaks["tf_burst"], "frac": round(tf / peaks["tf_burst"], 4),
-                             "executed_frac": round(float(cnt.float().mean()) / P, 4),
-                             "finite": bool(torch.isfinite(dq).all())})
+                executed = float(cnt.float().mean()) / P
+                row = {"P": P, "C": C, "B": B, "masks": variant, "us": round(us, 2),
+                       "us_with_prep": round(us_all, 2), "flop": flop, "executed_frac": round(executed, 4),
+                       "tflops_executed": round(tf * executed, 2), "peak": peaks["tf_burst"],
+                       "frac": round(tf * executed / peaks["tf_burst"], 4),
+                       "frac_dense_algorithmic": round(tf / peaks["tf_burst"], 4),
+                       "finite": bool(torch.isfinite(dq).all())}
                 del qh, kh, dq, lse
+                if eager and variant == "ones":
+                    chunk = max(1, min(B, (1 << 31) // (P * P * 4 * 8)))      # ~8 live [b,P,P] f32 tensors <= 2 GiB
+                    for tag, bf in (("eager_fp32_us", False), ("eager_bf16_bmm_us", True)):
+                        t, n_img = _eager_dense_us(q, k, ma, mb, inv_tau, bf, chunk)
+                        row[tag] = round(t, 1)
+                        row[tag.replace("_us", "_timed_images")] = n_img
+                    row["speedup_vs_eager_fp32"] = round(row["eager_fp32_us"] / us_all, 1)
+                    row["speedup_vs_eager_bf16_bmm"] = round(row["eager_bf16_bmm_us"] / us_all, 1)
+                rows.append(row)
             del q, k
     return rows
+
+
+def headline_dense(rows):
+    """The north-star point (56x56, C=128, all-ones masks) as its own object."""
+    for r in rows:
+        if r["P"] == 3136 and r["C"] == 128 and r["masks"] == "ones":
+            return {"P": 3136, "C": 128, "B": r["B"], "masks": "ones", "fwd_bwd_us": r["us"],
+                    "tflops": r["tflops_executed"], "peak_tflops": r["peak"], "frac": r["frac"],
+                    "target_frac": 0.60, "eager_fp32_us": r.get("eager_fp32_us"),
+                    "eager_bf16_bmm_us": r.get("eager_bf16_bmm_us")}
+    return None
 
 
 # ------------------------------------------------------------------ mirror-loss microbench
@@ -465,11 +592,17 @@ def densecl_sweep(peaks, iters=10):
 def algorithmic_work(batch, n_params, world):
     """Per-CALL algorithmic bytes / flops of each C-ABI entry point on the step."""
     P, C, hw = (IMG // OS_) ** 2, DIM, IMG * IMG
+    comp = 3 * batch * 3 * hw * 4 + batch * P * 4
     return {
-        "cp2_composite": ("hbm", 3 * batch * 3 * hw * 4 + batch * P * 4),
+        "cp2_composite": ("hbm", comp),
+        "cp2_composite2": ("hbm", 2 * comp),
         "cp2_prep_features": ("hbm", 6 * batch * C * P + 4 * batch * P),
+        "cp2_prep_features2": ("hbm", 2 * (6 * batch * C * P + 4 * batch * P)),
         "cp2_dense_lse": ("tensor", 2.0 * batch * P * P * C),
         "cp2_dense_grad": ("tensor", 2.0 * batch * P * P * C),
+        "cp2_dense_small": ("tensor", 4.0 * batch * P * P * C),
+        "cp2_dense_epilogue": ("hbm", batch * P * C * (4 + 2 + 4)),
+        "cp2_dense_rescore": ("hbm", 2 * batch * C * P * 4),
         "cp2_global_nce": ("hbm", 4 * C * QUEUE + 8 * batch * C),
         "cp2_ema": ("hbm", 12 * n_params),
         "cp2_enqueue": ("hbm", 2 * world * batch * C * 4),
@@ -481,61 +614,174 @@ def algorithmic_work(batch, n_params, world):
     }
 
 
-def own_arm(args):
+def multi_rank_parity(model, dev, rank, world):
+    """World > 1, before the timed region: the NCCL paths against the CPU oracle (the untimed checker leg may
+    import oracle/).  3 enqueues through `_dequeue_and_enqueue` (all-gather + cp2_enqueue) and one
+    `_batch_shuffle_ddp` / `_batch_unshuffle_ddp` round trip (perm broadcast + all_to_all_single):
+      queue / queue_ptr equal on every rank and equal to oracle.dequeue_and_enqueue on the gathered keys,
+      the shuffled rows equal to oracle.batch_shuffle for every rank, the round trip the identity.
+    The model's queue and pointer are restored afterwards.  -> dict of booleans (identical on every rank)."""
     import torch
     import torch.distributed as dist
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the cp2_b200 path has no CPU fallback "
-                         "(use --impl reference for the CPU baseline)")
-    from cp2_b200 import _lib, ops
-    from cp2_b200.builder import MODEL
+    from oracle import cp2_oracle as O
+
+    def gather(t):
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t.contiguous())
+        return out
+
+    res = {}
+    with torch.no_grad():
+        queue0, ptr0 = model.queue.clone(), model.queue_ptr.clone()
+        B, C, K = 32, model.queue.shape[0], model.queue.shape[1]
+        model.queue_ptr.fill_(K - 2 * B * world - 5)            # the third enqueue wraps around
+        ref_q, ref_ptr = model.queue.cpu().clone(), int(model.queue_ptr.item())
+        for stp in range(3):
+            g = torch.Generator().manual_seed(1000 + 17 * stp + rank)
+            keys = torch.nn.functional.normalize(torch.randn(B, C, generator=g), dim=1).to(dev)
+            model._dequeue_and_enqueue(keys)
+            keys_all = torch.cat([t.cpu() for t in gather(keys)])
+            ref_ptr = O.dequeue_and_enqueue(ref_q, ref_ptr, keys_all)
+        qs, ps = gather(model.queue), gather(model.queue_ptr)
+        res["queue_equal_across_ranks"] = all(torch.equal(qs[0], t) for t in qs)
+        res["queue_ptr_equal_across_ranks"] = all(torch.equal(ps[0], t) for t in ps)
+        res["queue_matches_oracle"] = bool(torch.equal(model.queue.cpu(), ref_q))
+        res["queue_ptr_matches_oracle"] = int(model.queue_ptr.item()) == ref_ptr
+        model.queue.copy_(queue0)
+        model.queue_ptr.copy_(ptr0)
+        # shuffle / unshuffle: rows tagged with their global index
+        x = (torch.arange(B, device=dev, dtype=torch.float32) + rank * B).reshape(B, 1, 1, 1).expand(B, 3, 4, 4).contiguous()
+        x = x + torch.arange(3 * 16, device=dev, dtype=torch.float32).reshape(1, 3, 4, 4) / 64.0
+        y, idx_unshuffle = model._batch_shuffle_ddp(x)
+        z = model._batch_unshuffle_ddp(y, idx_unshuffle)
+        x_all = torch.cat([t.cpu() for t in gather(x)])
+        ys = [t.cpu() for t in gather(y)]
+        idx_shuffle = torch.argsort(idx_unshuffle).cpu()
+        res["shuffle_matches_oracle"] = all(torch.equal(ys[r], O.batch_shuffle(x_all, idx_shuffle, r, world))
+                                            for r in range(world))
+        perms = gather(idx_unshuffle)
+        res["perm_equal_across_ranks"] = all(torch.equal(perms[0], t) for t in perms)
+        res["unshuffle_roundtrip"] = bool(torch.equal(z, x))
+    flags = torch.tensor([int(bool(v)) for v in res.values()], device=dev)
+    dist.all_reduce(flags, op=dist.ReduceOp.MIN)                # a failure on any rank fails everywhere
+    return {k_: bool(f) for k_, f in zip(res.keys(), flags.tolist())}
+
+
+def ddp_weights_equal(model, dev, world):
+    import torch
+    import torch.distributed as dist
+    with torch.no_grad():
+        sig = torch.stack([p.detach().double().sum() for p in model.encoder_q.parameters()] +
+                          [p.detach().double().sum() for p in model.encoder_k.parameters()])
+    out = [torch.empty_like(sig) for _ in range(world)]
+    dist.all_gather(out, sig)
+    return all(torch.equal(out[0], t) for t in out)
+
+
+def collectives_summary(times, steps):
+    """model.collective_times -> {name: us per step}; device-side CUDA-event durations on the issuing stream
+    (host seconds for the gloo permutation broadcast)."""
+    import torch
+    torch.cuda.synchronize()
+    out = {}
+    for name, recs in times.items():
+        if name.endswith("_s"):
+            out[name[:-2] + "_us_per_step"] = round(1e6 * sum(recs) / max(steps, 1), 1)
+        else:
+            out[name + "_us_per_step"] = round(1e3 * sum(a.elapsed_time(b) for a, b in recs) / max(steps, 1), 1)
+    return out
+
+
+def gpu_eager_baseline(args, dev, own_step_ms, own_slice_fn):
+    """Same-GPU eager baselines: the UNMODIFIED reference builder.MODEL on this B200 through
+    its stock eager PyTorch path (cuBLAS bmm + separate softmax kernels + per-step host syncs), (a) the full step
+    with the same stand-in segmentor, as the reference runs it (NCHW) and with the backbone in channels_last
+    like the own arm, (b) the loss slice alone (a stored-feature 'encoder': composite x2, id maps, normalise,
+    both InfoNCE losses, enqueue, backward to the features) for both implementations, (c) the EMA over the full
+    66 M-parameter model.  CUDA events, 3 warm-up + 10 timed iterations each."""
+    import torch
+    from oracle import ref_harness as rh
+    if not rh.reference_available():
+        return {"unavailable": "reference modules not reachable (oracle/_ref not built)"}
+    B = args.batch
+    resident = {k: v.to(dev) for k, v in synth_batch(B, seed=1234).items()}
+
+    def timeit(fn, n=10, warm=3):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    out = {"what": "unmodified reference builder.MODEL (oracle/ref_harness.py), eager PyTorch on the same B200",
+           "batch": B}
+    for tag, cl in (("step_ms_nchw", False), ("step_ms_channels_last", True)):
+        step, kind, ref = _reference_stepper(B, device=str(dev), channels_last=cl)
+        out[tag] = round(timeit(lambda: step(resident)), 3)
+        if not cl:
+            m = ref.model
+            out["ema_eager_us"] = round(1e3 * timeit(m._momentum_update_key_encoder), 1)
+        del step, ref
+        torch.cuda.empty_cache()
+    out["own_step_ms"] = round(own_step_ms, 3)
+    out["speedup_vs_eager_gpu_step"] = round(out["step_ms_channels_last"] / own_step_ms, 3)
+    out["speedup_vs_eager_gpu_step_nchw_reference"] = round(out["step_ms_nchw"] / own_step_ms, 3)
+    step, kind, ref = _reference_stepper(B, device=str(dev), encoder="features")
+    out["loss_slice_eager_us"] = round(1e3 * timeit(lambda: step(resident)), 1)
+    del step, ref
+    torch.cuda.empty_cache()
+    out["loss_slice_own_us"] = round(1e3 * timeit(own_slice_fn(resident)), 1)
+    out["speedup_vs_eager_gpu_loss_slice"] = round(out["loss_slice_eager_us"] / out["loss_slice_own_us"], 2)
+    return out
+
+
+def mirror_arm(args, dev, rank, world, peaks):
+    """--workload mirror: BASELINE.json configs[4], one `MirrorModule.shared_step` training iteration
+    (mirror_pretrain.py:212-245, networks/mirror_network.py:40-63) per step: 512x512 source / target images,
+    B=8 per GPU, MirrorVariant.OUTPUT, Adam (segment_network.py:294-310), the segmentor = the same ResNet-50
+    DeepLabV3 stand-in with a 2-class head (OS16 -> 32x32 logits; the loss kernel upsamples on chip)."""
+    import torch
+    import torch.distributed as dist
+    from cp2_b200 import ops
     from cp2_b200.encoder import DeepLabV3Encoder
-    _lib.load()
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-    peaks = load_peaks()
-
-    if args.sweep_only:
-        if rank == 0:
-            print(json.dumps({"dense_microbench": dense_sweep(args, peaks)}), flush=True)
-        return 0
-
+    from cp2_b200.mirror_network import MirrorModule, MirrorVariant, Stage
     torch.manual_seed(0)
     torch.backends.cudnn.benchmark = True
-    model = MODEL(None, rank=rank, dim=DIM, K=QUEUE, m=0.999, instance_logits_temp=TAU_G,
-                  pretrain_from_scratch=True, lmbd_cp2_dense_loss=LMBD, dense_logits_temp=TAU_D, device=dev,
-                  encoder_factory=lambda: DeepLabV3Encoder(dim=DIM), output_stride=OS_).to(dev)
+    B, H, Cls = (8 if args.batch == 32 else args.batch), 512, 2
+    mod = MirrorModule(None, "RANDOM", 1e-4, 1e-4, Cls, (3, H, H), 0.01, 2.0, MirrorVariant.OUTPUT,
+                       segmentor_factory=lambda: DeepLabV3Encoder(dim=Cls)).to(dev)
     if not args.nchw:
-        # cuDNN's tensor-core convolutions are NHWC kernels: NCHW weights/activations cost an
-        # nchwToNhwc / nhwcToNchw transpose around every convolution (11 % of the r01b step)
-        model = model.to(memory_format=torch.channels_last)
-    n_params = sum(p.numel() for p in model.encoder_k.parameters())
-    net = model
-    if world > 1:
-        # queues are identical on every rank by construction -> no per-forward buffer broadcast
-        # conv_seg never receives a gradient in contrast mode (the reason the reference passes
-        # find_unused_parameters=True, main.py:456-461): freezing it is behaviour-neutral and spares DDP the
-        # per-step graph traversal; gradients are reduced in place in the buckets
-        for p in model.encoder_q.decode_head.conv_seg.parameters():
-            p.requires_grad_(False)
-        net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], find_unused_parameters=False,
-                                                        broadcast_buffers=False, gradient_as_bucket_view=True)
-    opt = torch.optim.SGD(model.encoder_q.parameters(), 1e-3, momentum=0.9, weight_decay=1e-4)
+        mod = mod.to(memory_format=torch.channels_last)
+    for p in mod.model.decode_head.conv_seg.parameters():      # unused head of the stand-in: no gradient ever
+        p.requires_grad_(False)
+    opt = mod.configure_optimizers()["optimizer"]
+    g = torch.Generator().manual_seed(4321 + rank)
+    host = [(torch.rand(B, 3, H, H, generator=g).pin_memory(), torch.rand(B, 3, H, H, generator=g).pin_memory(),
+             torch.randint(0, Cls, (B, H, H), generator=g).pin_memory()) for _ in range(2)]
+    resident = [tuple(t.to(dev) for t in hb) for hb in host]
+    h2d = sum(t.numel() * t.element_size() for t in host[0])
 
-    B = args.batch
-    host = [synth_batch(B, seed=1234 + rank + 100 * i, pinned=True) for i in range(2)]
-    resident = [{k: v.to(dev) for k, v in hb.items()} for hb in host]
-    h2d = sum(v.numel() * v.element_size() for v in host[0].values())
+    class _Wrap(torch.nn.Module):          # DDP drives forward(); route it to shared_step
+        def __init__(self, m):
+            super().__init__()
+            self.m = m
+
+        def forward(self, batch):
+            return self.m.shared_step(batch, Stage.TRAIN)
+
+    if world > 1:
+        net = torch.nn.parallel.DistributedDataParallel(_Wrap(mod), device_ids=[dev.index], gradient_as_bucket_view=True)
+        call = lambda b: net(b)
+    else:
+        call = lambda b: mod.shared_step(b, Stage.TRAIN)
 
     def step(batch):
-        loss = net(visualize=False, step=0, new_epoch=False, **batch)
+        loss = call(batch)
         opt.zero_grad(set_to_none=True)
         loss.backward()
         opt.step()
@@ -561,6 +807,139 @@ def own_arm(args):
 
     for i in range(max(args.warmup, 3)):
         step(resident[i % 2])
+    sampler = ClockSampler(dev.index)
+    sampler.start()
+    l0 = ops.LAUNCHES
+    with ops.KernelTimer() as kt:
+        ms_value = timed(lambda i: step(resident[i % 2]), args.steps)
+    launches = ops.LAUNCHES - l0
+    ksum = kt.summary()
+
+    def e2e_step(i):
+        batch = tuple(t.to(dev, non_blocking=True) for t in host[i % 2])
+        return step(batch).item()
+    e2e_step(0)
+    ms_e2e = timed(e2e_step, args.steps)
+    clocks = sampler.stop()
+    name = "cp2_mirror_loss_upsampled"
+    calls, us = ksum.get(name, (0, 0.0))
+    label_bytes = 8 * B * H * H + 4 * 2 * B * Cls * 32 * 32 * 4
+    roof = {"kernel": name, "bound": "hbm", "achieved": round(label_bytes / max(us, 1e-9) / 1e3, 2),
+            "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": round(label_bytes / max(us, 1e-9) / 1e3 / peaks["hbm_gbs"], 4),
+            "traffic": None, "algorithmic_per_launch": label_bytes, "us_per_launch": round(us, 2),
+            "peak_source": peaks["source"]}
+    line = {"metric": "mirror_pretrain_images_per_sec", "value": B * world * args.steps / (ms_value * 1e-3),
+            "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_value / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "BASELINE.json configs[4]: mirror_pretrain, MirrorModule.shared_step (OUTPUT "
+                                   "variant), 512x512 inputs, ResNet-50 DeepLabV3 stand-in (OS16, 32x32 logits), Adam",
+                       "batch_per_gpu": B, "global_batch": B * world, "classes": Cls, "lmbd_compare": 0.01,
+                       "softmax_temp": 2.0, "parallelism": f"dp{world}",
+                       "l2": "no flush: one step streams several GB of activations through L2"},
+            "e2e": {"value": B * world * args.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roof,
+            "kernels": {name: {"calls_per_step": calls / max(args.steps, 1), "us_per_call": round(us, 2)}}}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def own_arm(args):
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the cp2_b200 path has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    from cp2_b200 import _lib, ops
+    from cp2_b200.builder import MODEL
+    from cp2_b200.encoder import DeepLabV3Encoder
+    _lib.load()
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    peaks = load_peaks()
+
+    if args.sweep_only:
+        if rank == 0:
+            rows = dense_sweep(args, peaks, eager=not args.no_eager_baseline)
+            print(json.dumps({"dense_microbench": rows, "dense_loss": headline_dense(rows)}), flush=True)
+        return 0
+    if args.workload == "mirror":
+        return mirror_arm(args, dev, rank, world, peaks)
+
+    torch.manual_seed(0)
+    torch.backends.cudnn.benchmark = True
+
+    def build_model(factory):
+        m = MODEL(None, rank=rank, dim=DIM, K=QUEUE, m=0.999, instance_logits_temp=TAU_G,
+                  pretrain_from_scratch=True, lmbd_cp2_dense_loss=LMBD, dense_logits_temp=TAU_D, device=dev,
+                  encoder_factory=factory, output_stride=OS_).to(dev)
+        return m
+
+    model = build_model(lambda: DeepLabV3Encoder(dim=DIM))
+    if not args.nchw:
+        # cuDNN's tensor-core convolutions are NHWC kernels: NCHW weights/activations cost an
+        # nchwToNhwc / nhwcToNchw transpose around every convolution (11 % of the r01b step)
+        model = model.to(memory_format=torch.channels_last)
+    n_params = sum(p.numel() for p in model.encoder_k.parameters())
+    net = model
+    if world > 1:
+        # queues are identical on every rank by construction -> no per-forward buffer broadcast
+        # conv_seg never receives a gradient in contrast mode (the reason the reference passes
+        # find_unused_parameters=True, main.py:456-461): freezing it is behaviour-neutral and spares DDP the
+        # per-step graph traversal; gradients are reduced in place in the buckets
+        for p in model.encoder_q.decode_head.conv_seg.parameters():
+            p.requires_grad_(False)
+        net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], find_unused_parameters=False,
+                                                        broadcast_buffers=False, gradient_as_bucket_view=True)
+    opt = torch.optim.SGD(model.encoder_q.parameters(), 1e-3, momentum=0.9, weight_decay=1e-4)
+
+    B = args.batch
+    host = [synth_batch(B, seed=1234 + rank + 100 * i, pinned=True) for i in range(2)]
+    resident = [{k: v.to(dev) for k, v in hb.items()} for hb in host]
+    h2d = sum(v.numel() * v.element_size() for v in host[0].values())
+
+    def step(batch, module=None):
+        loss = (module or net)(visualize=False, step=0, new_epoch=False, **batch)
+        opt.zero_grad(set_to_none=True)
+        loss.backward()
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(n):
+            fn(i)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    parity = None
+    if world > 1:
+        parity = multi_rank_parity(model, dev, rank, world)
+
+    for i in range(max(args.warmup, 3)):
+        step(resident[i % 2])
     sampler = ClockSampler(local)
     sampler.start()
     launches0 = ops.LAUNCHES
@@ -574,7 +953,7 @@ def own_arm(args):
     launches = ops.LAUNCHES - launches0
     ksum = kt.summary()
 
-    # e2e: every step's inputs come from pinned host memory (77 MB per step) and the loss is read back.
+    # e2e: every step's inputs come from pinned host memory and the loss is read back.
     # As in a pin_memory data loader, the copy of step i+1 is issued on a copy stream before step i's loss
     # is waited for, so it overlaps the compute; each timed step still contains exactly one full H2D copy.
     copy_stream = torch.cuda.Stream(device=dev)
@@ -602,6 +981,30 @@ def own_arm(args):
     ms_e2e = timed(e2e_step, args.steps)
     clocks = sampler.stop()
 
+    # ---- N > 1: where the step time goes between ranks (untimed extra legs, device-side event timings)
+    collectives = None
+    if world > 1:
+        n_c = min(args.steps, 10)
+        model.collective_times = {}
+        timed(lambda i: step(resident[i % 2]), n_c)
+        collectives = collectives_summary(model.collective_times, n_c)
+        model.collective_times = None
+
+        def step_no_sync(i):                # same step without DDP's gradient all-reduce
+            with net.no_sync():
+                step(resident[i % 2])
+        ms_sync = timed(lambda i: step(resident[i % 2]), n_c) / n_c
+        ms_nosync = timed(step_no_sync, n_c) / n_c
+        model.overlap_exchange = False
+        ms_serial = timed(lambda i: step(resident[i % 2]), n_c) / n_c
+        model.overlap_exchange = True
+        collectives.update({"ddp_all_reduce_overhead_ms_per_step": round(ms_sync - ms_nosync, 3),
+                            "step_ms": round(ms_sync, 3), "step_ms_without_grad_all_reduce": round(ms_nosync, 3),
+                            "step_ms_with_serial_image_exchange": round(ms_serial, 3),
+                            "note": "all_to_all / all_gather: CUDA events on the issuing stream (the image exchange "
+                                    "runs on a side stream under encoder_q); all-reduce overhead from a no_sync() A/B"})
+        parity["ddp_weights_equal_across_ranks"] = ddp_weights_equal(model, dev, world)
+
     # ---- per-kernel figures from the CUDA events recorded inside the timed region
     work = algorithmic_work(B, n_params, world)
     traffic = {}
@@ -611,7 +1014,7 @@ def own_arm(args):
             traffic = json.load(f)
     kernels, per_step_us = {}, 0.0
     for name, (calls, us) in ksum.items():
-        bound, amount = work[name]
+        bound, amount = work.get(name, ("hbm", 0))
         per_step = us * calls / max(args.steps, 1)
         per_step_us += per_step
         if bound == "hbm":
@@ -637,24 +1040,54 @@ def own_arm(args):
         "data": "synthetic", "config": workload_config(B, world, args.nchw),
         "e2e": {"value": B * world * args.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
-        "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "kernels": kernels,
+        "gpu_launches": launches, "launches_per_step": launches / max(args.steps, 1), "clocks": clocks,
+        "roofline": roofline, "kernels": kernels,
         "cp2_kernels_us_per_step": round(per_step_us, 1),
         "backbone_and_optimizer_ms_per_step": round(ms_value / args.steps - per_step_us * 1e-3, 3),
     }
+    if parity is not None:
+        line["parity_check"] = parity
+    if collectives is not None:
+        line["collectives"] = collectives
     if world == 1:
+        own_ms = ms_value / args.steps
+        net = opt = None
+        if not args.no_eager_baseline:
+            def own_slice_fn(batch):
+                seeds = iter((11, 12))
+                m2 = build_model(lambda: feature_encoder(B, DIM, IMG // OS_, next(seeds)))
+                o2 = torch.optim.SGD(m2.encoder_q.parameters(), 1e-3, momentum=0.9, weight_decay=1e-4)
+
+                def run():
+                    loss = m2(visualize=False, step=0, new_epoch=False, **batch)
+                    o2.zero_grad(set_to_none=True)
+                    loss.backward()
+                    o2.step()
+                    return loss.item()
+                return run
+            try:
+                line["gpu_eager_baseline"] = gpu_eager_baseline(args, dev, own_ms, own_slice_fn)
+            except Exception as e:  # noqa: BLE001 - a baseline leg must not take the bench line down
+                line["gpu_eager_baseline"] = {"failed": f"{type(e).__name__}: {e}"[:400]}
+        model = None
+        torch.cuda.empty_cache()
         if not args.no_sweep:
-            # free the training state first: the 56x56 / C=256 point needs ~3.5 GB
-            line["dense_microbench"] = dense_sweep(args, peaks)
+            rows = dense_sweep(args, peaks, eager=not args.no_eager_baseline)
+            line["dense_loss"] = headline_dense(rows)
+            line["dense_microbench"] = rows
             line["mirror_microbench"] = mirror_sweep(peaks)
             line["weighted_microbench"] = weighted_sweep(peaks)
             line["densecl_microbench"] = densecl_sweep(peaks)
         if not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline_leg()
+            line["cpu_baseline"] = cpu_baseline_leg(B)
+    ok = parity is None or all(parity.values())
     if rank == 0:
         print(json.dumps(line), flush=True)
+        if not ok:
+            sys.stderr.write(f"bench.py: multi-rank parity check FAILED: {parity}\n")
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return 0 if ok else 3
 
 
 def main():

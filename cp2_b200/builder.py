@@ -18,10 +18,15 @@ Deliberate, documented deviations from the reference (none changes the loss):
   * no `queue.clone()` (builder.py:1396): the global kernel produces the backward's
     queue-weighted sum in the forward pass, so enqueue may overwrite the queue before
     `loss.backward()`;
-  * the dense score quartiles (builder.py:1298, 1401-1403) are loss-neutral and skipped; the
-    correlation IoUs (builder.py:1252-1257) come from one kernel and stay on the device until read;
-  * wandb logging is left to the caller (`rank` is stored, nothing is logged here).
+  * the correlation IoUs (builder.py:1252-1257) come from one kernel and stay on the device until read;
+  * the per-step / per-epoch wandb logs of rank 0 (builder.py:1450-1550, 1565-1604, 1608-1664) go through
+    `MODEL.logger` (default: `wandb.log` when a wandb run is active on rank 0, else nothing).  The score
+    statistics that only feed those logs (dense score means / quartiles, builder.py:1298; queue-logit
+    quartiles, builder.py:1401-1403) and the new-epoch heat-maps (builder.py:1489-1549) are computed by a
+    plain-torch branch off the hot path (`MODEL.dense_logits_for_visualisation`, `_step_score_stats`), taken
+    only when somebody logs: rank 0 with an active logger, as in the reference.
 """
+import time
 from enum import Enum
 
 import torch
@@ -197,6 +202,8 @@ class DenseCLNeck(nn.Module):
 class MODEL(nn.Module):
     """Drop-in for the reference's `builder.MODEL` (builder.py:277-1706), CP2 mode.
 
+    Supported range (validated in __init__): dim in {128, 256}, K % 4 == 0, both temperatures >= 1/16.
+
     Extra keyword-only arguments (not in the reference):
       encoder_factory : callable returning one segmentor; replaces `build_segmentor(cfg.model)`
                         (mmseg/mmcv are not installable here).  Called twice (q, k).
@@ -209,6 +216,15 @@ class MODEL(nn.Module):
       output_stride   : skip the reference's CPU probe forward (builder.py:392-397) and use
                         this value.  When None the probe runs exactly as in the reference,
                         including its side effect on encoder_q's BN running statistics.
+      backbone_output_stride : stride of `encoder.backbone(x)[3]` (builder.py:398-401), used by
+                        forward_densecl for the id lattice.  None: probed as in the reference when the
+                        encoder has a `.backbone` (also when `output_stride` is given), else = output_stride.
+      logger          : callable(dict) receiving what the reference hands to `wandb.log` on rank 0
+                        (builder.py:1450-1604, 1608-1664).  None: `wandb.log` if a wandb run is active on
+                        rank 0, otherwise nothing is logged and none of the log-only statistics is computed.
+      overlap_exchange: world > 1 only — issue the BN-shuffle image exchange (builder.py:609-630) on a side
+                        stream right after the compositing, so that it runs under `encoder_q` instead of
+                        between the two encoders.  The permutation, RNG draws and results are unchanged.
     """
 
     def __init__(self, cfg, rank, dim=128, K=65536, m=0.999, instance_logits_temp=0.2,
@@ -218,8 +234,18 @@ class MODEL(nn.Module):
                  backbone_type=BackboneType.DEEPLABV3, mapping_type=MappingType.CP2,
                  dense_logits_temp=1, unet_truncated_dec_blocks=2, use_predictor=False,
                  use_avgpool_global=False, use_symmetrical_loss=False, lmbd_coordinate=0,
-                 device=None, *, encoder_factory=None, output_stride=None, track_accuracy=True):
+                 device=None, *, encoder_factory=None, output_stride=None, backbone_output_stride=None,
+                 track_accuracy=True, logger=None, overlap_exchange=True):
         super().__init__()
+        # limits of the kernels, checked here instead of inside the first forward (include/cp2_b200.h)
+        if dim not in ops.SUPPORTED_DIMS:
+            raise ValueError(f"cp2_b200: dim={dim} unsupported; the tensor-core kernels take {ops.SUPPORTED_DIMS}")
+        if K <= 0 or K % 4 != 0:
+            raise ValueError(f"cp2_b200: K={K} must be a positive multiple of 4 (16-byte queue rows for TMA)")
+        for name, t in (("instance_logits_temp", instance_logits_temp), ("dense_logits_temp", dense_logits_temp)):
+            if not (t >= 1.0 / ops.MAX_INV_TAU):
+                raise ValueError(f"cp2_b200: {name}={t} must be >= {1.0 / ops.MAX_INV_TAU} (the kernels use a "
+                                 f"fixed soft-max shift, valid for 1/tau <= {ops.MAX_INV_TAU:g})")
         self.queue_len = K
         self.momentum = m
         self.temp_global = instance_logits_temp
@@ -297,11 +323,23 @@ class MODEL(nn.Module):
             self.output_stride = int(test_sample.shape[2] / self.encoder_q(test_sample).shape[2])
         else:
             self.output_stride = int(output_stride)
-        self.backbone_output_stride = self.output_stride
-        if output_stride is None and hasattr(self.encoder_q, "backbone"):
+        if backbone_output_stride is not None:
+            self.backbone_output_stride = int(backbone_output_stride)
+        elif hasattr(self.encoder_q, "backbone") and (output_stride is None or self._densecl):
+            # builder.py:398-401.  With `output_stride` given the probe is only run for the modes that use the
+            # value (forward_densecl), on the backbone alone and without touching BN statistics.
             test_sample = torch.rand(2, 3, 224, 224)
-            shp = self.encoder_q.backbone(test_sample)[3].shape
+            if output_stride is None:
+                shp = self.encoder_q.backbone(test_sample)[3].shape
+            else:
+                was_training = self.encoder_q.training
+                self.encoder_q.eval()
+                with torch.no_grad():
+                    shp = self.encoder_q.backbone(test_sample)[3].shape
+                self.encoder_q.train(was_training)
             self.backbone_output_stride = int(test_sample.shape[2] / shp[2])
+        else:
+            self.backbone_output_stride = self.output_stride
 
         if self._densecl:                                       # builder.py:436-441, 452-457
             if not hasattr(self.encoder_q, "backbone"):
@@ -330,8 +368,14 @@ class MODEL(nn.Module):
         self.cross_image_variance_source = AverageMeter("Cross_Image_Variance_Source", ":6.2f")
         self.cross_image_variance_target = AverageMeter("Cross_Image_Variance_Target", ":6.2f")
         self._iou_host, self._iou_dev = [[], []], [[], []]      # (all pixels, masked): lists + pending device chunks
+        self._iou_pending = [[], []]                            # (pinned host tensor, copy-done event) pairs
         self._ema_plan = None
         self.track_accuracy = bool(track_accuracy)
+        self._logger = logger
+        self.overlap_exchange = bool(overlap_exchange)
+        self._side_stream = None
+        self._cpu_group = None
+        self.collective_times = None        # bench.py: dict name -> [seconds | (event, event)] when not None
 
     @torch.no_grad()
     def _accuracy_stats(self, q, k, mask_a, mask_b, q_pos, k_pos, stats):
@@ -348,18 +392,35 @@ class MODEL(nn.Module):
 
     # ----------------------------------------------------------- a4 (metrics)
     # builder.py:1252-1257 extends two python lists with per-image IoUs every step, through a .cpu() sync.
-    # Here the per-step [B] results stay on the device and are only read back when the list is looked at
-    # (the reference does so once per epoch, builder.py:1455-1486).
+    # Here the per-step [B] results stay on the device; every _IOU_FLUSH steps they are copied to pinned host
+    # memory asynchronously (no sync, bounded device memory) and the lists are materialised when somebody looks
+    # at them (the reference does so once per epoch, builder.py:1455-1486).
+    _IOU_FLUSH = 64
+
+    def _iou_flush_async(self, which):
+        chunks, self._iou_dev[which] = self._iou_dev[which], []
+        if not chunks:
+            return
+        dev_t = torch.cat(chunks)
+        host_t = torch.empty(dev_t.shape, dtype=dev_t.dtype, pin_memory=True)
+        host_t.copy_(dev_t, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._iou_pending[which].append((host_t, ev, dev_t))     # dev_t kept alive until the copy is done
+
     def _iou_list(self, which):
-        if self._iou_dev[which]:
-            self._iou_host[which].extend(torch.cat(self._iou_dev[which]).cpu().numpy().tolist())
-            self._iou_dev[which] = []
+        self._iou_flush_async(which)
+        for host_t, ev, _dev_t in self._iou_pending[which]:
+            ev.synchronize()
+            self._iou_host[which].extend(host_t.numpy().tolist())
+        self._iou_pending[which] = []
         return self._iou_host[which]
 
-    correlation_ious = property(lambda self: self._iou_list(0),
-                                lambda self, v: (self._iou_dev.__setitem__(0, []), self._iou_host.__setitem__(0, list(v)))[0])
-    masked_correlation_ious = property(lambda self: self._iou_list(1),
-                                       lambda self, v: (self._iou_dev.__setitem__(1, []), self._iou_host.__setitem__(1, list(v)))[0])
+    def _iou_set(self, which, v):
+        self._iou_dev[which], self._iou_pending[which], self._iou_host[which] = [], [], list(v)
+
+    correlation_ious = property(lambda self: self._iou_list(0), lambda self, v: self._iou_set(0, v))
+    masked_correlation_ious = property(lambda self: self._iou_list(1), lambda self, v: self._iou_set(1, v))
 
     # ------------------------------------------------------------------ K4
     @torch.no_grad()
@@ -378,7 +439,7 @@ class MODEL(nn.Module):
     def _dequeue_and_enqueue(self, keys):
         """builder.py:569-587: all-gather, then transposed write at the device-side pointer
         with wrap-around.  No host sync."""
-        ops.enqueue(concat_all_gather(keys), self.queue, self.queue_ptr)
+        ops.enqueue(self._timed("nccl_all_gather_keys", lambda: concat_all_gather(keys)), self.queue, self.queue_ptr)
 
     @torch.no_grad()
     def _dequeue_and_enqueue2(self, keys):
@@ -408,25 +469,50 @@ class MODEL(nn.Module):
         inv[order] = torch.arange(B)
         return recv.index_select(0, inv.to(x.device, non_blocking=True))
 
+    def _timed(self, name, fn):
+        """Runs one collective; with `collective_times` set (bench.py) brackets it with CUDA events on the
+        issuing stream (device-side duration incl. the NCCL stream hand-over)."""
+        if self.collective_times is None:
+            return fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = fn()
+        e1.record()
+        self.collective_times.setdefault(name, []).append((e0, e1))
+        return out
+
+    def _broadcast_perm_host(self, idx_host):
+        """Rank 0's CPU permutation to every rank WITHOUT a device->host read: the 8*B*W bytes travel over a
+        gloo side group on the host (the device-side copy is broadcast separately by NCCL).  Falls back to the
+        default group when that already is a CPU backend."""
+        if self._cpu_group is None:
+            backend = dist.get_backend()
+            self._cpu_group = dist.group.WORLD if backend == "gloo" else dist.new_group(backend="gloo")
+        t0 = time.perf_counter()
+        dist.broadcast(idx_host, src=0, group=self._cpu_group)
+        if self.collective_times is not None:
+            self.collective_times.setdefault("gloo_broadcast_perm_host_s", []).append(time.perf_counter() - t0)
+        return idx_host
+
     @torch.no_grad()
     def _batch_shuffle_ddp(self, x):
-        """builder.py:609-630.  Same RNG contract: every rank draws a CPU `randperm`, rank 0's is
-        broadcast.  Returns (x_shuffled_for_this_rank, idx_unshuffle) like the reference; the rows
-        travel by all-to-all."""
+        """builder.py:609-630.  Same RNG contract: every rank draws a CPU `randperm`, rank 0's wins.
+        Returns (x_shuffled_for_this_rank, idx_unshuffle) like the reference; the rows travel by all-to-all
+        (SURVEY.md section 8 row f1).  No rank reads the permutation back from the device: rank 0's draw is
+        broadcast on the host (gloo) and uploaded by every rank."""
         batch_size_this = x.shape[0]
         W = _world()
         batch_size_all = batch_size_this * W
         idx_host = torch.randperm(batch_size_all)                # CPU generator, advanced on every rank
-        idx_shuffle = idx_host.to(x.device)
         if W > 1:
-            dist.broadcast(idx_shuffle, src=0)
-            if _rank() != 0:
-                idx_host = idx_shuffle.cpu()                     # rank 0 already holds the winning draw
-        idx_unshuffle = torch.argsort(idx_shuffle)
-        self._unshuffle_host = (idx_unshuffle, torch.argsort(idx_host))
+            idx_host = self._broadcast_perm_host(idx_host)
+        idx_shuffle = idx_host.to(x.device, non_blocking=True)
+        unshuffle_host = torch.argsort(idx_host)
+        idx_unshuffle = unshuffle_host.to(x.device, non_blocking=True)
+        self._unshuffle_host = (idx_unshuffle, unshuffle_host)
         if W == 1:
             return x[idx_shuffle], idx_unshuffle
-        return self._exchange_rows(x, idx_host), idx_unshuffle
+        return self._timed("nccl_all_to_all_shuffle", lambda: self._exchange_rows(x, idx_host)), idx_unshuffle
 
     @torch.no_grad()
     def _batch_unshuffle_ddp(self, x, idx_unshuffle):
@@ -438,7 +524,7 @@ class MODEL(nn.Module):
             perm_host = cached[1]                                # no second device->host read
         else:
             perm_host = idx_unshuffle.cpu()
-        return self._exchange_rows(x, perm_host)
+        return self._timed("nccl_all_to_all_unshuffle", lambda: self._exchange_rows(x, perm_host))
 
     def forward(self, **kwargs):                               # builder.py:651-665
         if self._densecl:
@@ -506,6 +592,29 @@ class MODEL(nn.Module):
         return loss
 
     # ---------------------------------------------------------- forward_cp2
+    def _shuffled_keys_input(self, img_b):
+        """builder.py:1274 `_batch_shuffle_ddp(img_b)`.  World > 1 with `overlap_exchange`: the exchange depends
+        only on the compositing kernel, so it is issued on a side stream and joined just before `encoder_k`
+        (it then runs under `encoder_q`).  -> (img_b_shuffled, idx_unshuffle, join) with join() to be called
+        on the compute stream before the result is used."""
+        if _world() == 1 or not self.overlap_exchange or not img_b.is_cuda:
+            out, idx = self._batch_shuffle_ddp(img_b)
+            return out, idx, (lambda: None)
+        cur = torch.cuda.current_stream()
+        if self._side_stream is None:
+            self._side_stream = torch.cuda.Stream(device=img_b.device)
+        side = self._side_stream
+        side.wait_stream(cur)                                  # the composited img_b is ready
+        with torch.cuda.stream(side):
+            out, idx = self._batch_shuffle_ddp(img_b)
+        img_b.record_stream(side)
+
+        def join():
+            cur.wait_stream(side)
+            out.record_stream(cur)
+            idx.record_stream(cur)
+        return out, idx, join
+
     def forward_cp2(self, img_a, img_b, bg0, bg1, visualize=False, step=0, new_epoch=False,
                     pixel_ids_a=None, pixel_ids_b=None, region_ids_a=None, region_ids_b=None):
         """builder.py:1124-1606.
@@ -518,24 +627,30 @@ class MODEL(nn.Module):
         """
         os_ = self.output_stride
         keep = bool(visualize) and self.rank == 0
-        # K1: builder.py:1146-1159 (+ the mask part of the [OS/2::OS] subsample)
-        img_a, mask_a, full_a = ops.composite(img_a, bg0, os_, want_full_mask=keep)
-        img_b, mask_b, full_b = ops.composite(img_b, bg1, os_, want_full_mask=keep)
+        # K1: builder.py:1146-1159 (+ the mask part of the [OS/2::OS] subsample), both views in one launch
+        (img_a, mask_a, full_a), (img_b, mask_b, full_b) = ops.composite_pair(img_a, bg0, img_b, bg1, os_,
+                                                                            want_full_mask=keep)
         if keep:
             self.last_visualization = {"img_a": img_a, "img_b": img_b, "mask_a": full_a, "mask_b": full_b}
         n = img_a.shape[0]
+        hidden_image_size = tuple(mask_a.shape[1:])
+        with torch.no_grad():                                  # builder.py:1271-1277, exchange started early
+            img_b, idx_unshuffle, join_exchange = self._shuffled_keys_input(img_b)
         if region_ids_a is not None and region_ids_b is not None:
             # a2 + a4: builder.py:1211-1217, 1252-1257 (the region-id IoUs are the ones the reference keeps)
             iou, iou_m = ops.id_iou(region_ids_a, region_ids_b, mask_a, mask_b, os_)
             self._iou_dev[0].append(iou)
             self._iou_dev[1].append(iou_m)
+            if len(self._iou_dev[0]) >= self._IOU_FLUSH:
+                self._iou_flush_async(0)
+                self._iou_flush_async(1)
         mask_a = mask_a.reshape(n, -1)
         mask_b = mask_b.reshape(n, -1)
 
         q = self.encoder_q(img_a)                              # builder.py:1260 (cuDNN, out of scope)
         with torch.no_grad():                                  # builder.py:1271-1277
             self._momentum_update_key_encoder()
-            img_b, idx_unshuffle = self._batch_shuffle_ddp(img_b)
+            join_exchange()
             k = self.encoder_k(img_b)
             k = self._batch_unshuffle_ddp(k, idx_unshuffle)
 
@@ -550,10 +665,14 @@ class MODEL(nn.Module):
             self.include_background, pair_weights)
         if self.track_accuracy:                                # uses the queue BEFORE this step's enqueue
             stats["acc_ins"], stats["acc_seg"] = self._accuracy_stats(q, k, mask_a, mask_b, q_pos, k_pos, stats)
+        log = self._active_logger()
+        score_stats = None
+        if log is not None:                                    # log-only statistics: queue BEFORE the enqueue
+            score_stats = self._step_score_stats(q, k, mask_a, mask_b, q_pos, k_pos, pair_weights)
         self._dequeue_and_enqueue(k_pos)                       # builder.py:1426
 
-        if new_epoch and self.rank == 0:
-            self.epoch += 1
+        if new_epoch:
+            self._new_epoch_branch(log, q, k, mask_a, mask_b, hidden_image_size, pair_weights)
         with torch.no_grad():                                  # builder.py:1553-1563, no syncs
             self.loss_o.update(loss, n)
             self.loss_i.update(loss_ins, n)
@@ -562,17 +681,193 @@ class MODEL(nn.Module):
             self.acc_seg.update(stats["acc_seg"], n)
             self.cross_image_variance_source.update(stats["std_q_pos"], n)    # q_pos.std(0).mean()
             self.cross_image_variance_target.update(stats["std_k_pos"], n)
+        if log is not None:
+            self._log_step(log, score_stats)
         return loss
 
-    def on_train_epoch_end(self, step):                        # builder.py:1608
-        return {"train/loss": self.loss_o.avg}
+    # ------------------------------------------------ a12: logging / visualisation (off the hot path)
+    def _active_logger(self):
+        """The callable that receives the reference's rank-0 `wandb.log` dicts, or None (nothing is logged and
+        none of the log-only statistics is computed)."""
+        if self.rank != 0:
+            return None
+        if self._logger is not None:
+            return self._logger
+        try:
+            import wandb
+        except Exception:
+            return None
+        return wandb.log if getattr(wandb, "run", None) is not None else None
 
-    def reset_metrics(self):
+    @torch.no_grad()
+    def dense_logits_for_visualisation(self, q, k, pair_weights=None, mask_a=None, mask_b=None):
+        """The materialised `logits_dense` [B,P,P] of builder.py:1289-1292 (/ tau_d at :1431 is NOT applied, as at
+        the point the reference slices it, :1493-1510), in plain torch.  Slow branch: only the new-epoch
+        heat-maps and the log-only score statistics use it.  PROPOSED modes: times the pair weights after the
+        NegativeType squash (builder.py:1332-1392) via the same torch formulation the tests use."""
+        B, C = q.shape[0], q.shape[1]
+        qh = F.normalize(q.detach().float().reshape(B, C, -1), dim=1)
+        kh = F.normalize(k.detach().float().reshape(B, C, -1), dim=1)
+        logits = torch.einsum("ncx,ncy->nxy", qh, kh)
+        if pair_weights is None or mask_a is None:
+            return logits
+        # PROPOSED modes (slow, visualisation only): squash of the non-label pairs, then the pair weights
+        labels = torch.einsum("nx,ny->nxy", mask_a, mask_b)
+        w_pix, w_reg, w_not, code, scale = pair_weights.scalars
+        if code != 0:
+            neg = labels == 0
+            if code == 1:                                      # FIXED
+                centre = logits.new_zeros(B, 1, 1)
+            else:
+                x = torch.where(neg, logits, torch.full_like(logits, float("nan"))).reshape(B, -1)
+                centre = (torch.nanmean(x, dim=1) if code == 2 else torch.nanquantile(x, 0.5, dim=1)).reshape(B, 1, 1)
+            logits = torch.where(neg, 2.0 / (1.0 + torch.exp((logits - centre) * -scale)) - 1.0, logits)
+        o, st = pair_weights.os // 2, pair_weights.os
+        pa, pb, ra, rb = (t[:, o::st, o::st].reshape(B, -1) for t in pair_weights.ids)
+        pix = pa[:, :, None] == pb[:, None, :]
+        reg = (ra[:, :, None] == rb[:, None, :]) & ((ra[:, :, None] * rb[:, None, :]) != 0)
+        w = w_reg * reg.to(logits.dtype)
+        w = torch.where(pix, torch.full_like(w, w_pix), w)
+        w = w + (w == 0) * w_not
+        return logits * w
+
+    @torch.no_grad()
+    def _step_score_stats(self, q, k, mask_a, mask_b, q_pos, k_pos, pair_weights):
+        """Log-only statistics of builder.py:1294-1303 (`calcuate_dense_loss_stats`,
+        tools/correlation_mapping.py:11-53) and :1399-1412 (queue-logit quartiles), plain torch."""
+        logits = self.dense_logits_for_visualisation(q, k)          # raw cosines: builder.py:1298 runs before the squash
+        labels = torch.einsum("nx,ny->nxy", mask_a, mask_b)
+        B = logits.shape[0]
+        qs = torch.tensor([0.25, 0.5, 0.75], device=logits.device)
+        out = {}
+        for name, sel in (("positive", labels == 1), ("negative", labels == 0)):
+            x = torch.where(sel, logits, torch.full_like(logits, float("nan"))).reshape(B, -1)
+            out[name] = {"average": torch.nanmean(x, dim=1), "quartiles": torch.nanquantile(x, qs, dim=1)}
+        l_neg = q_pos.detach() @ self.queue
+        out["instance_pos"] = (q_pos.detach() * k_pos.detach()).sum(1)
+        out["instance_neg_avg"] = l_neg.mean(dim=1)
+        out["instance_neg_q"] = torch.quantile(l_neg, qs, dim=1)
+        return out
+
+    def _log_step(self, log, st):
+        """builder.py:1565-1604 (rank 0).  Reads the meters' `.val` -> one device sync per logged step, as in
+        the reference."""
+        log({"train/loss_step": self.loss_o.val})
+        log({"train/acc_ins_step": self.acc_ins.val})
+        d = {"train/loss_ins_step": self.loss_i.val, "train/loss_dense_step": self.loss_d.val,
+             "train/acc_seg_step": self.acc_seg.val,
+             "train/cross_image_variance_source_step": self.cross_image_variance_source.val,
+             "train/cross_image_variance_target_step": self.cross_image_variance_target.val}
+        if st is not None:
+            pos, neg = st["positive"], st["negative"]
+            d.update({
+                "train/+ive_scores_step": float(pos["average"].mean()),
+                "train/-ive_scores_step": float(neg["average"].mean()),
+                "step/dense_per_sample_average_positive_scores": float(pos["average"].mean()),
+                "step/dense_per_sample_lower_positive_scores": float(pos["quartiles"][0].mean()),
+                "step/dense_per_sample_median_positive_scores": float(pos["quartiles"][1].mean()),
+                "step/dense_per_sample_upper_positive_scores": float(pos["quartiles"][2].mean()),
+                "step/dense_per_sample_average_negative_scores": float(neg["average"].mean()),
+                "step/dense_per_sample_lower_negative_scores": float(neg["quartiles"][0].mean()),
+                "step/dense_per_sample_median_negative_scores": float(neg["quartiles"][1].mean()),
+                "step/dense_per_sample_upper_negative_scores": float(neg["quartiles"][2].mean()),
+                "step/instance_average_positive_scores": float(st["instance_pos"].mean()),
+                "step/instance_average_negative_scores": float(st["instance_neg_avg"].mean()),
+                "step/instance_lower_negative_scores": float(st["instance_neg_q"][0].mean()),
+                "step/instance_median_negative_scores": float(st["instance_neg_q"][1].mean()),
+                "step/instance_upper_negative_scores": float(st["instance_neg_q"][2].mean()),
+            })
+        log(d)
+
+    @torch.no_grad()
+    def heatmap_grid(self, logits_dense, mask_a, mask_b, hidden_image_size):
+        """builder.py:1489-1532: per image the mean similarity of every key pixel to the foreground queries
+        (hm_b) and of every query pixel to the foreground keys (hm_a), laid out as [m_a, hm_a, m_b, hm_b] rows of
+        a 4-column grid, nearest-upscaled by 224 // h.  -> [H_grid, W_grid] float tensor (first channel)."""
+        B = logits_dense.shape[0]
+        a, b = mask_a.reshape(B, -1), mask_b.reshape(B, -1)
+        hm_b = torch.einsum("nxy,nx->ny", logits_dense, a) / a.sum(1, keepdim=True)
+        hm_a = torch.einsum("nxy,ny->nx", logits_dense, b) / b.sum(1, keepdim=True)
+        h, w = hidden_image_size
+        shape = (B, 1, h, w)
+        m_a, m_b = 2 * a.reshape(shape) - 1, 2 * b.reshape(shape) - 1
+        imgs = torch.stack([m_a, hm_a.reshape(shape), m_b, hm_b.reshape(shape)], dim=1).flatten(0, 1)
+        # torchvision.utils.make_grid(imgs, nrow=4): 2-pixel zero padding between / around the cells
+        nrow, pad = 4, 2
+        ncell = imgs.shape[0]
+        rows = (ncell + nrow - 1) // nrow
+        grid = imgs.new_zeros(rows * (h + pad) + pad, nrow * (w + pad) + pad)
+        for i in range(ncell):
+            r, c = divmod(i, nrow)
+            grid[pad + r * (h + pad): pad + r * (h + pad) + h, pad + c * (w + pad): pad + c * (w + pad) + w] = imgs[i, 0]
+        scale = max(1, 224 // h)
+        return grid.repeat_interleave(scale, dim=0).repeat_interleave(scale, dim=1)
+
+    def _new_epoch_branch(self, log, q, k, mask_a, mask_b, hidden_image_size, pair_weights):
+        """builder.py:1450-1550.  Rank 0 with a logger: IoU statistics + heat-maps, then the lists restart.
+        Every rank: the IoU lists restart (the reference leaks them on ranks != 0)."""
+        if log is not None:
+            import numpy as np
+            for which, tag in ((0, "feature_space"), (1, "feature_space_masked")):
+                vals = list(self._iou_list(which))
+                key = "iou" if which == 0 else "masked_iou"
+                nz = int(np.count_nonzero(vals))
+                log({f"feature_space_non_zero_{key}": nz})
+                log({f"feature_space_non_zero_{key}_ratio": nz / len(vals) if vals else float("nan")})
+                try:                                            # the histogram figure needs matplotlib + wandb.Image
+                    import matplotlib.pyplot as plt
+                    import wandb
+                    plt.figure(figsize=(10, 4))
+                    plt.hist(vals, bins="auto")
+                    plt.title("Histogram of IoU values" if which == 0 else "Histogram of Masked IoU values")
+                    plt.xlabel("IoU")
+                    plt.ylabel("Frequency")
+                    log({f"feature_space_{key}": wandb.Image(plt)})
+                except Exception:
+                    log({f"feature_space_{key}_histogram": np.histogram(vals, bins=10, range=(0, 1))[0].tolist()
+                         if vals else []})
+            grid = self.heatmap_grid(self.dense_logits_for_visualisation(q, k, pair_weights, mask_a, mask_b), mask_a, mask_b,
+                                     hidden_image_size)
+            self.last_heatmap_grid = grid
+            g = grid.detach().cpu().numpy()
+            try:                                                # viridis colour map as builder.py:1536-1547
+                import matplotlib
+                import matplotlib.cm as cm
+                import wandb
+                norm = matplotlib.colors.Normalize(vmin=g.min(), vmax=g.max(), clip=True)
+                rgb = cm.ScalarMappable(norm=norm, cmap="viridis").to_rgba(g)[:, :, :3]
+                log({"dense-heatmaps": wandb.Image(rgb)})
+            except Exception:
+                log({"dense-heatmaps": g})
+        if self.rank == 0:
+            self.epoch += 1
+        self.correlation_ious = []
+        self.masked_correlation_ious = []
+
+    def on_train_epoch_end(self, step):
+        """builder.py:1608-1664: rank 0 logs the epoch averages, every rank restarts the meters.  Returns the
+        logged dict (the reference returns None; main.py:656 ignores the value)."""
+        out = {"train/loss": self.loss_o.avg}
+        if self.pretrain_type in (PretrainType.CP2, PretrainType.PROPOSED):
+            out["train/acc_ins"] = self.acc_ins.avg
+        if self.pretrain_type in (PretrainType.DENSECL, PretrainType.PROPOSED_V2, PretrainType.CP2):
+            out["train/loss_ins"] = self.loss_i.avg
+            out["train/loss_dense"] = self.loss_d.avg
+        if self.pretrain_type == PretrainType.CP2:
+            out["train/acc_seg"] = self.acc_seg.avg
+        if self.pretrain_type in (PretrainType.PROPOSED_V2, PretrainType.CP2):
+            out["train/cross_image_variance_source"] = self.cross_image_variance_source.avg
+            out["train/cross_image_variance_target"] = self.cross_image_variance_target.avg
+        log = self._active_logger()
+        if log is not None:
+            log(out)
+        self.reset_metrics()
+        return out
+
+    def reset_metrics(self):                                   # builder.py:1666-1688 (the IoU lists are not touched)
         for mtr in (self.loss_o, self.loss_i, self.loss_d, self.acc_ins, self.acc_seg,
                     self.cross_image_variance_source, self.cross_image_variance_target):
             mtr.reset()
-        self.correlation_ious = []
-        self.masked_correlation_ious = []
 
     def _accuracy(self, output, target, topk=(1,)):            # builder.py:1690-1706
         with torch.no_grad():

@@ -11,6 +11,8 @@ import torch
 from . import _lib
 
 _EPS = 1e-12   # F.normalize eps
+SUPPORTED_DIMS = (128, 256)     # feature dims of the tcgen05 kernels (cp2_dense_*, cp2_global_nce)
+MAX_INV_TAU = 16.0              # fixed soft-max shift: |logit| <= 1/tau <= 16 keeps exp2 in range
 
 # ------------------------------------------------------------ launch accounting
 # Every C-ABI call goes through `_call`: it counts the kernels launched (bench.py's
@@ -96,6 +98,12 @@ def composite(img, bg, output_stride, want_full_mask=False, out=None):
     return out, mask_ds, mask_full
 
 
+def composite_pair(img_a, bg_a, img_b, bg_b, output_stride, want_full_mask=False):
+    """Both views of builder.py:1146-1159 -> ((out_a, mask_ds_a, full_a), (out_b, mask_ds_b, full_b))."""
+    return (composite(img_a, bg_a, output_stride, want_full_mask),
+            composite(img_b, bg_b, output_stride, want_full_mask))
+
+
 # ----------------------------------------------------------------- K2a
 def prep_features(feat, mask, compact=False, unit=False):
     """builder.py:1261-1268.  feat [B,C,P] f32, mask [B,P] -> (fhat_t bf16 [B,P,C], inv_norm [B,P],
@@ -148,6 +156,15 @@ def dense_grad(qhat_t, khat_t, lse, mask_a, mask_b, inv_norm, alpha, v1, v2, inv
           _ptr(mask_a), _ptr(mask_b), _ptr(inv_norm), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(gscale), _ptr(dq),
           _ptr(nl), float(inv_tau), B, C, P, _stream())
     return dq
+
+
+def dense_fwd_bwd(qhat_t, khat_t, key_count, mask_a, inv_norm, alpha, v1, v2, inv_tau, gscale=None):
+    """Column LSE + gradient w.r.t. the query features of the dense loss in one call -> (lse [B,P], dq [B,C,P]).
+    The configs[3] microbench unit: cp2_dense_lse + cp2_dense_grad."""
+    lse = dense_lse(qhat_t, khat_t, inv_tau, key_count)
+    dq = dense_grad(qhat_t, khat_t, lse, mask_a, None, inv_norm, alpha, v1, v2, inv_tau, key_count=key_count,
+                    gscale=gscale)
+    return lse, dq
 
 
 # ------------------------------------------------------------------ K3

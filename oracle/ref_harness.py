@@ -1,9 +1,14 @@
-"""TEST INFRASTRUCTURE ONLY — never imported by the product path (cp2_b200/).
+"""TEST / BASELINE INFRASTRUCTURE ONLY — never imported by the product path (cp2_b200/).
 
-Imports the *unmodified* reference (`/root/reference/builder.py`, read-only) in this
-dev container so that `oracle/gen_golden.py` can record golden vectors from the
-reference's own code.  The reference cannot travel to the GPU box, so nothing that
-runs there (`-m gpu` tests, `smoke()`, `bench.py`) may import this module.
+Imports the *unmodified* reference `builder.py`: from the read-only source tree
+(`/root/reference`) in this dev container, where `oracle/gen_golden.py` records golden
+vectors from the reference's own code, or — on the GPU box, where that tree does not
+exist — from the sourceless byte-compiled modules `oracle/build_ref.py` puts under
+`oracle/_ref/` (git-ignored build artefact, the Python analogue of a compiled
+`oracle/_ref/*.so`).  Users: `oracle/gen_golden.py`, `bench.py --impl reference` (the
+reference's own CPU path) and bench.py's `gpu_eager_baseline` leg (the reference's eager
+PyTorch path on the same B200).  The `-m gpu` tests and `smoke()` use the committed golden
+vectors and `oracle/cp2_oracle.py` only.
 
 Recipe: the reference imports several non-arithmetic
 packages at module level (`builder.py:7-27`, `networks/segment_network.py:3-9`,
@@ -20,11 +25,26 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-REFERENCE_ROOT = os.environ.get("CP2_REFERENCE_ROOT", "/root/reference")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _find_reference():
+    """(root, kind): the source tree if present, else the byte-compiled modules, else (None, None)."""
+    env = os.environ.get("CP2_REFERENCE_ROOT")
+    for root in ([env] if env else []) + ["/root/reference"]:
+        if os.path.isfile(os.path.join(root, "builder.py")):
+            return root, "source"
+    pyc = os.path.join(_HERE, "_ref")
+    if os.path.isfile(os.path.join(pyc, "builder.pyc")):
+        return pyc, "pyc"
+    return None, None
+
+
+REFERENCE_ROOT, REFERENCE_KIND = _find_reference()
 
 
 def reference_available() -> bool:
-    return os.path.isfile(os.path.join(REFERENCE_ROOT, "builder.py"))
+    return REFERENCE_ROOT is not None
 
 
 class PatchEncoder(nn.Module):
@@ -106,7 +126,8 @@ def _install_stubs():
 def import_reference():
     """Returns the reference's `builder` module (unmodified source)."""
     if not reference_available():
-        raise RuntimeError(f"reference not found under {REFERENCE_ROOT}")
+        raise RuntimeError("reference not found: neither /root/reference nor oracle/_ref/builder.pyc "
+                           "(run `python oracle/build_ref.py` where the reference tree exists)")
     _install_stubs()
     if REFERENCE_ROOT not in sys.path:
         sys.path.insert(0, REFERENCE_ROOT)
@@ -115,13 +136,17 @@ def import_reference():
     return builder
 
 
-def ensure_process_group():
+def ensure_process_group(backend="gloo"):
+    """The reference calls torch.distributed unconditionally (builder.py:612-649, 1710-1722): a
+    world-size-1 group (gloo for the CPU arm, nccl when the model runs on the GPU) through a private file
+    store (independent of MASTER_* / torchrun's env)."""
+    import tempfile
+
     import torch.distributed as dist
 
     if not dist.is_initialized():
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("MASTER_PORT", "29577")
-        dist.init_process_group("gloo", rank=0, world_size=1)
+        store = dist.FileStore(tempfile.NamedTemporaryFile(prefix="cp2_ref_pg_", delete=False).name, 1)
+        dist.init_process_group(backend, store=store, rank=0, world_size=1)
 
 
 class _Cfg:
@@ -131,14 +156,15 @@ class _Cfg:
         return None
 
 
-def make_reference_model(encoder_factory, **kwargs):
-    """Builds the reference `MODEL` (`builder.py:277`) on CPU with `encoder_factory()`
-    standing in for both segmentors.  rank=1 disables every wandb call (all gated on
-    rank==0)."""
+def make_reference_model(encoder_factory, cpu=True, **kwargs):
+    """Builds the reference `MODEL` (`builder.py:277`) with `encoder_factory()` standing in for both
+    segmentors.  rank=1 disables every wandb call (all gated on rank==0).  cpu=True: the model is meant
+    to run on the host (the caller keeps it there), so the reference's hard-coded `.cuda()` calls
+    (builder.py:175,618,1420) are made the identity FOR THIS PROCESS; cpu=False (GPU eager baseline):
+    nothing is patched and the caller moves the model to the device."""
     builder = import_reference()
-    ensure_process_group()
-    # the reference hard-codes `.cuda()` (builder.py:175,618,1420); identity on CPU
-    if not torch.cuda.is_available():
+    ensure_process_group("gloo" if cpu else "nccl")
+    if cpu:
         torch.Tensor.cuda = lambda self, *a, **k: self
     _encoder_factory[0] = encoder_factory
     kwargs.setdefault("pretrain_from_scratch", True)

@@ -1,0 +1,121 @@
+"""Host-side logic of cp2_b200.builder.MODEL that needs no GPU: constructor validation, the epoch-end
+logging / meter restart (reference builder.py:1608-1688), the new-epoch heat-map arithmetic
+(builder.py:1489-1532) and the log-only score statistics (tools/correlation_mapping.py:11-53)."""
+import pytest
+import torch
+import torch.nn as nn
+
+from oracle import cp2_oracle as O
+
+
+class _Tiny(nn.Module):
+    def __init__(self, dim=128):
+        super().__init__()
+        self.proj = nn.Conv2d(3, dim, 16, 16)
+
+    def forward(self, x):
+        return self.proj(x)
+
+
+def _model(**kw):
+    from cp2_b200.builder import MODEL
+    kw.setdefault("encoder_factory", _Tiny)
+    kw.setdefault("output_stride", 16)
+    kw.setdefault("K", 256)
+    return MODEL(None, kw.pop("rank", 0), **kw)
+
+
+def test_constructor_validates_kernel_limits():
+    with pytest.raises(ValueError, match="dim"):
+        _model(dim=64)
+    with pytest.raises(ValueError, match="multiple of 4"):
+        _model(K=1001)
+    with pytest.raises(ValueError, match="instance_logits_temp"):
+        _model(instance_logits_temp=0.01)
+    with pytest.raises(ValueError, match="dense_logits_temp"):
+        _model(dense_logits_temp=0.05)
+    m = _model(dim=256, encoder_factory=lambda: _Tiny(256))
+    assert m.queue.shape == (256, 256)
+
+
+def test_backbone_output_stride_kwarg():
+    m = _model(backbone_output_stride=32)
+    assert m.output_stride == 16 and m.backbone_output_stride == 32
+    assert _model().backbone_output_stride == 16
+
+
+def test_epoch_end_logs_and_restarts_meters():
+    logged = []
+    m = _model(logger=logged.append)
+    for epoch in range(2):
+        for step in range(3):
+            m.loss_o.update(torch.tensor(1.0 + epoch), 4)
+            m.loss_i.update(0.5 + epoch, 4)
+            m.loss_d.update(0.25, 4)
+            m.acc_ins.update(torch.tensor(50.0), 4)
+            m.acc_seg.update(25.0, 4)
+            m.cross_image_variance_source.update(0.1, 4)
+            m.cross_image_variance_target.update(0.2, 4)
+        out = m.on_train_epoch_end(step=3 * (epoch + 1))
+        # the second epoch's averages are the second epoch's only: the meters restarted
+        assert out["train/loss"] == pytest.approx(1.0 + epoch)
+        assert out["train/loss_ins"] == pytest.approx(0.5 + epoch)
+        assert out["train/acc_ins"] == pytest.approx(50.0) and out["train/acc_seg"] == pytest.approx(25.0)
+        assert m.loss_o.count == 0 and m.acc_seg.count == 0
+    assert len(logged) == 2 and set(logged[0]) == {
+        "train/loss", "train/acc_ins", "train/loss_ins", "train/loss_dense", "train/acc_seg",
+        "train/cross_image_variance_source", "train/cross_image_variance_target"}
+    # ranks != 0 never log (builder.py:1609) but still restart
+    quiet = _model(rank=1, logger=logged.append)
+    quiet.loss_o.update(3.0, 2)
+    quiet.on_train_epoch_end(1)
+    assert len(logged) == 2 and quiet.loss_o.count == 0
+
+
+def test_heatmap_grid_matches_reference_formula():
+    torchvision = pytest.importorskip("torchvision")
+    B, h, w = 3, 4, 5
+    g = torch.Generator().manual_seed(0)
+    logits = torch.randn(B, h * w, h * w, generator=g)
+    ma = (torch.rand(B, h * w, generator=g) < 0.6).float()
+    mb = (torch.rand(B, h * w, generator=g) < 0.6).float()
+    ma[:, 0] = 1
+    mb[:, 1] = 1
+    m = _model()
+    got = m.heatmap_grid(logits, ma, mb, (h, w))
+    # builder.py:1493-1532 restated
+    hm_a, hm_b = [], []
+    for i in range(B):
+        b_ = logits[i][ma[i].bool(), :]
+        a_ = logits[i][:, mb[i].bool()]
+        hm_b.append((b_.sum(0) / b_.shape[0]).reshape(h, w))
+        hm_a.append((a_.sum(1) / a_.shape[1]).reshape(h, w))
+    hm_a, hm_b = torch.stack(hm_a).unsqueeze(1), torch.stack(hm_b).unsqueeze(1)
+    m_a, m_b = 2 * ma.reshape(B, 1, h, w) - 1, 2 * mb.reshape(B, 1, h, w) - 1
+    imgs = torch.stack([m_a, hm_a, m_b, hm_b], dim=1).flatten(0, 1)
+    grid = torchvision.utils.make_grid(imgs, nrow=4)[0]
+    scale = 224 // h
+    ref = grid.repeat_interleave(scale, 0).repeat_interleave(scale, 1)     # NEAREST_EXACT at an integer factor
+    assert got.shape == ref.shape
+    assert torch.allclose(got, ref, atol=1e-6)
+
+
+def test_step_score_stats_match_oracle():
+    B, C, hw = 2, 128, 3
+    g = torch.Generator().manual_seed(1)
+    q, k = torch.randn(B, C, hw, hw, generator=g), torch.randn(B, C, hw, hw, generator=g)
+    ma = (torch.rand(B, hw * hw, generator=g) < 0.6).float()
+    mb = (torch.rand(B, hw * hw, generator=g) < 0.6).float()
+    ma[:, 0] = 1
+    mb[:, 0] = 1
+    m = _model()
+    qh, q_pos, _ = O.normalize_and_pool(q.reshape(B, C, -1), ma)
+    kh, k_pos, _ = O.normalize_and_pool(k.reshape(B, C, -1), mb)
+    st = m._step_score_stats(q, k, ma, mb, q_pos, k_pos, None)
+    ref = O.dense_loss_stats(O.dense_logits(qh, kh), torch.einsum("nx,ny->nxy", ma, mb))
+    for name in ("positive", "negative"):
+        assert torch.allclose(st[name]["average"], ref[name]["average"], atol=1e-6)
+        for i in range(3):
+            assert torch.allclose(st[name]["quartiles"][i], ref[name]["quartiles"][i], atol=1e-6)
+    l_neg = q_pos @ m.queue
+    assert torch.allclose(st["instance_neg_q"], torch.quantile(l_neg, torch.tensor([0.25, 0.5, 0.75]), dim=1))

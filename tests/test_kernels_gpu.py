@@ -220,19 +220,6 @@ def test_dense_lse_compact_count(ops):
     assert not got[2].any()
 
 
-def test_dense_lse_vs_simt_large(ops):
-    from cp2_b200 import _lib
-    lib = _lib.load()
-    B, C, P = 2, 128, 3136
-    qh, kh = dev(_unit_bf16(B, P, C, 3)), dev(_unit_bf16(B, P, C, 4))
-    got = ops.dense_lse(qh, kh, 5.0)
-    ref = torch.empty_like(got)
-    _lib.check(lib.cp2_dbg_dense_lse_simt(qh.data_ptr(), kh.data_ptr(), ref.data_ptr(), 5.0, B, C, P,
-                                          torch.cuda.current_stream().cuda_stream), "simt")
-    torch.cuda.synchronize()
-    assert torch.allclose(got, ref, rtol=0, atol=6e-5), float((got - ref).abs().max())
-
-
 # ------------------------------------------------------------------ K2 backward
 def _grad_ref(qh, kh, lse, ma, mb, inv_norm, alpha, v1, v2, inv_tau):
     """fp64 restatement of the cp2_dense_grad contract (include/cp2_b200.h)."""
@@ -296,27 +283,6 @@ def test_dense_grad_compact_equals_masked(ops, C, P):
     only_rank1 = _grad_ref(qh[1:2].float(), kh_full[1:2].float().cpu(), lse[1:2], ma[1:2], mb[1:2], inv_norm[1:2],
                            alpha[1:2] * 0, v1[1:2], None, 1.0 / tau)
     assert rel_l2(got[1:2], only_rank1) < 1e-5
-
-
-def test_dense_grad_vs_simt_large(ops):
-    from cp2_b200 import _lib
-    lib = _lib.load()
-    B, C, P = 1, 128, 3136
-    g = torch.Generator().manual_seed(11)
-    qh, kh = dev(_unit_bf16(B, P, C, 7)), dev(_unit_bf16(B, P, C, 8))
-    ma = dev((torch.rand(B, P, generator=g) < 0.6).float())
-    mb = dev((torch.rand(B, P, generator=g) < 0.6).float())
-    inv_norm = dev(torch.rand(B, P, generator=g) + 0.5)
-    alpha, v1 = dev(torch.rand(B, generator=g) + 0.1), dev(torch.randn(B, C, generator=g) * 0.01)
-    lse = ops.dense_lse(qh, kh, 5.0)
-    got = ops.dense_grad(qh, kh, lse, ma, mb, inv_norm, alpha, v1, None, 5.0)
-    ref = torch.empty_like(got)
-    st = torch.cuda.current_stream().cuda_stream
-    _lib.check(lib.cp2_dbg_dense_grad_simt(qh.data_ptr(), kh.data_ptr(), lse.data_ptr(), ma.data_ptr(),
-                                           mb.data_ptr(), inv_norm.data_ptr(), alpha.data_ptr(), v1.data_ptr(),
-                                           None, ref.data_ptr(), 5.0, B, C, P, st), "simt")
-    torch.cuda.synchronize()
-    assert rel_l2(got, ref) < 5e-3, rel_l2(got, ref)
 
 
 # --------------------------------------------------------------------------- K3
