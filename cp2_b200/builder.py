@@ -208,11 +208,11 @@ class MODEL(nn.Module):
       encoder_factory : callable returning one segmentor; replaces `build_segmentor(cfg.model)`
                         (mmseg/mmcv are not installable here).  Called twice (q, k).
       track_accuracy  : evaluate the loss-neutral `acc_ins` / `acc_seg` meters (builder.py:1441-1448) each
-                        step, as the reference does.  They are the arg-max over all P x P dense logits
-                        and the top-1 over the 65537 global logits; two fp32 arg-max kernels
-                        (cp2_dense_top1, cp2_global_top1) give them without
-                        materialising either tensor and without a host sync.  On by default; False
-                        skips the four launches and the meters read NaN.
+                        step, as the reference does.  They are the top-1 over the 65537 global logits —
+                        taken inside the loss's own queue pass (cp2_global_nce: candidates within the bf16
+                        error bound of l_pos are re-scored exactly in fp32) — and the arg-max over all P x P
+                        dense logits; neither tensor is materialised and nothing syncs
+                        the host.  On by default; False skips them and the meters read NaN.
       output_stride   : skip the reference's CPU probe forward (builder.py:392-397) and use
                         this value.  When None the probe runs exactly as in the reference,
                         including its side effect on encoder_q's BN running statistics.
@@ -370,6 +370,7 @@ class MODEL(nn.Module):
         self._iou_host, self._iou_dev = [[], []], [[], []]      # (all pixels, masked): lists + pending device chunks
         self._iou_pending = [[], []]                            # (pinned host tensor, copy-done event) pairs
         self._ema_plan = None
+        self._shadow, self._shadow2 = ops.QueueShadow(), ops.QueueShadow()   # bf16 operands of cp2_global_nce
         self.track_accuracy = bool(track_accuracy)
         self._logger = logger
         self.overlap_exchange = bool(overlap_exchange)
@@ -378,17 +379,13 @@ class MODEL(nn.Module):
         self.collective_times = None        # bench.py: dict name -> [seconds | (event, event)] when not None
 
     @torch.no_grad()
-    def _accuracy_stats(self, q, k, mask_a, mask_b, q_pos, k_pos, stats):
-        """builder.py:1441-1448 (+ :1395-1418 for the logits) as two arg-max kernels (cp2_global_top1,
-        cp2_dense_top1): no [B,1+K] and no [B,P,P] tensor, no host sync.  In the PROPOSED modes the dense
-        arg-max runs on the weighted logits inside cp2_dense_weighted_lse (stats["acc_seg"])."""
-        bg = self.include_background
-        acc1, _ = ops.global_top1(q_pos, k_pos, self.queue, stats["q_neg"] if bg else None,
-                                  stats["k_neg"] if bg else None)
+    def _dense_accuracy(self, q, k, mask_a, mask_b, stats):
+        """builder.py:1442-1448: arg-max over all P x P dense logits (cp2_dense_top1; no [B,P,P] tensor, no host
+        sync).  In the PROPOSED modes the arg-max runs on the weighted logits inside cp2_dense_weighted_lse
+        (stats["acc_seg"]).  acc_ins (builder.py:1441) comes out of the loss's own queue pass (cp2_global_nce)."""
         if self._weighted:
-            return acc1, stats["acc_seg"]
-        acc_seg, _ = ops.dense_top1(q, k, mask_a, mask_b)
-        return acc1, acc_seg
+            return stats["acc_seg"]
+        return ops.dense_top1(q, k, mask_a, mask_b)[0]
 
     # ----------------------------------------------------------- a4 (metrics)
     # builder.py:1252-1257 extends two python lists with per-image IoUs every step, through a .cpu() sync.
@@ -439,12 +436,13 @@ class MODEL(nn.Module):
     def _dequeue_and_enqueue(self, keys):
         """builder.py:569-587: all-gather, then transposed write at the device-side pointer
         with wrap-around.  No host sync."""
-        ops.enqueue(self._timed("nccl_all_gather_keys", lambda: concat_all_gather(keys)), self.queue, self.queue_ptr)
+        ops.enqueue(self._timed("nccl_all_gather_keys", lambda: concat_all_gather(keys)), self.queue, self.queue_ptr,
+                    self._shadow)
 
     @torch.no_grad()
     def _dequeue_and_enqueue2(self, keys):
         """builder.py:589-607."""
-        ops.enqueue(concat_all_gather(keys), self.queue2, self.queue2_ptr)
+        ops.enqueue(concat_all_gather(keys), self.queue2, self.queue2_ptr, self._shadow2)
 
     # ----------------------------------------------------------------- a11 / f1
     @staticmethod
@@ -573,7 +571,7 @@ class MODEL(nn.Module):
             loss, loss_g, loss_l = ops.densecl_loss(
                 embd_q, embd_k, q_local, k_local, q_global, k_global, self.queue, self.queue2, self.temp_global,
                 self.temp_local, self.lmbd_dense_loss, ids_q if mix else None, ids_k if mix else None, bos,
-                self.lmbd_coordinate)
+                self.lmbd_coordinate, shadow=self._shadow, shadow2=self._shadow2)
             return loss_g, loss_l, k_global, k_pooled
 
         loss_global, loss_local, k_glob, k_loc = one_direction(img_a, img_b, pixel_ids_a, pixel_ids_b)
@@ -662,9 +660,9 @@ class MODEL(nn.Module):
                                            self.lmbd_not_corr_weight, self.negative_type, self.negative_scale)
         loss, loss_ins, loss_dense, k_pos, q_pos, stats = ops.cp2_loss(
             q, k, mask_a, mask_b, self.queue, self.temp_global, self.temp_local, self.lmbd_dense_loss,
-            self.include_background, pair_weights)
-        if self.track_accuracy:                                # uses the queue BEFORE this step's enqueue
-            stats["acc_ins"], stats["acc_seg"] = self._accuracy_stats(q, k, mask_a, mask_b, q_pos, k_pos, stats)
+            self.include_background, pair_weights, queue_shadow=self._shadow, track_accuracy=self.track_accuracy)
+        if self.track_accuracy:                                # acc_ins came with the queue pass (before the enqueue)
+            stats["acc_seg"] = self._dense_accuracy(q, k, mask_a, mask_b, stats)
         log = self._active_logger()
         score_stats = None
         if log is not None:                                    # log-only statistics: queue BEFORE the enqueue

@@ -1,4 +1,5 @@
-// a5/a7/a12 glue — everything of the CP2 loss that lives on [B,C] / [B] tensors, in two launches:
+// a5/a7/a12 glue — everything of the CP2 loss that lives on [B,C] / [B] tensors, in ONE launch (the CTA of
+// the last image to finish sums the batch; done counter in a persistent, self-resetting scratch word):
 // the global InfoNCE's positive (and optional background) logits and its cross-entropy
 // (reference builder.py:1395, 1414-1418, 1428), the rank-1 positive term and the masked mean of the
 // dense loss (builder.py:1431-1437), the loss combination (builder.py:1439), and the per-image
@@ -29,6 +30,44 @@ __device__ __forceinline__ void block_sum(float (&v)[N], float *red /* [N][4] */
   for (int k = 0; k < N; ++k) v[k] = red[k * 4] + red[k * 4 + 1] + red[k * 4 + 2] + red[k * 4 + 3];
 }
 
+// out = {loss, loss_ins, loss_dense, mean_c std_b(q_pos), mean_c std_b(k_pos)}; fixed summation order.  128 threads.
+__device__ void loss_finalize(const float *terms, const float *__restrict__ q_pos, const float *__restrict__ k_pos,
+                              float *__restrict__ out, float lmbd, int B, int C, float *red /* >= 8 floats */) {
+  float sd[2] = {0.f, 0.f};
+  for (int c = threadIdx.x; c < C; c += 128) {
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+      const float *src = w == 0 ? q_pos : k_pos;
+      float m = 0.f;
+      for (int b = 0; b < B; ++b) m += src[(long long)b * C + c];
+      m /= (float)B;
+      float var = 0.f;
+      for (int b = 0; b < B; ++b) { const float d = src[(long long)b * C + c] - m; var = fmaf(d, d, var); }
+      sd[w] += sqrtf(var / (float)(B - 1));                             // torch.std: unbiased; B = 1 -> NaN
+    }
+  }
+#pragma unroll
+  for (int w = 0; w < 2; ++w)
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) sd[w] += __shfl_down_sync(0xffffffffu, sd[w], off);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) { red[wid] = sd[0]; red[4 + wid] = sd[1]; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, d = 0.f, s0 = 0.f, s1 = 0.f;
+    for (int b = 0; b < B; ++b) { a += __ldcg(terms + 2 * b); d += __ldcg(terms + 2 * b + 1); }
+    for (int w = 0; w < 4; ++w) { s0 += red[w]; s1 += red[4 + w]; }
+    a /= (float)B;
+    d /= (float)B;
+    out[0] = a + d * lmbd;
+    out[1] = a;
+    out[2] = d;
+    out[3] = s0 / (float)C;
+    out[4] = s1 / (float)C;
+  }
+}
+
 // One CTA (128 threads) per image.
 __global__ void __launch_bounds__(128)
 loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k_pos,
@@ -38,9 +77,11 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
                     const float *__restrict__ G, const float *__restrict__ lse,
                     const int *__restrict__ key_count, const float *__restrict__ mask_a,
                     const float *__restrict__ dense_n, float *__restrict__ terms, float *__restrict__ l_pos_out, float *__restrict__ alpha,
-                    float *__restrict__ v1, float *__restrict__ v2, float inv_tg, float inv_tl, float lmbd,
+                    float *__restrict__ v1, float *__restrict__ v2, float *__restrict__ out,
+                    unsigned int *__restrict__ counter, float inv_tg, float inv_tl, float lmbd,
                     int B, int C, int P) {
   __shared__ float red[6 * 4];
+  __shared__ int is_last;
   const int b = blockIdx.x, tid = threadIdx.x;
   const bool bg = q_neg != nullptr;
   const long long row = (long long)b * C;
@@ -101,45 +142,15 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
     terms[2 * b + 1] = dense_n ? dense_n[b] : r1[5] / Bm - r1[3] * dense_scale;   // loss_dense of this image
     l_pos_out[b] = l_pos;
     alpha[b] = lmbd * invB * inv_tl / Bm;
+    __threadfence();                      // this image's terms are visible before the done counter moves
+    const int last = atomicAdd(counter, 1u) == (unsigned)B - 1u;
+    if (last) *counter = 0u;
+    is_last = last;
   }
-}
-
-// out = {loss, loss_ins, loss_dense, mean_c std_b(q_pos), mean_c std_b(k_pos)}; fixed summation order.
-__global__ void __launch_bounds__(256)
-loss_finalize_kernel(const float *__restrict__ terms, const float *__restrict__ q_pos,
-                     const float *__restrict__ k_pos, float *__restrict__ out, float lmbd, int B, int C) {
-  __shared__ float red[2 * 4 * 2];
-  float sd[2] = {0.f, 0.f};
-  for (int c = threadIdx.x; c < C; c += 256) {
-#pragma unroll
-    for (int w = 0; w < 2; ++w) {
-      const float *src = w == 0 ? q_pos : k_pos;
-      float m = 0.f;
-      for (int b = 0; b < B; ++b) m += src[(long long)b * C + c];
-      m /= (float)B;
-      float var = 0.f;
-      for (int b = 0; b < B; ++b) { const float d = src[(long long)b * C + c] - m; var = fmaf(d, d, var); }
-      sd[w] += sqrtf(var / (float)(B - 1));                             // torch.std: unbiased; B = 1 -> NaN
-    }
-  }
-#pragma unroll
-  for (int w = 0; w < 2; ++w)
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) sd[w] += __shfl_down_sync(0xffffffffu, sd[w], off);
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  if (lane == 0) { red[wid] = sd[0]; red[8 + wid] = sd[1]; }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    float a = 0.f, d = 0.f, s0 = 0.f, s1 = 0.f;
-    for (int b = 0; b < B; ++b) { a += terms[2 * b]; d += terms[2 * b + 1]; }
-    for (int w = 0; w < 8; ++w) { s0 += red[w]; s1 += red[8 + w]; }
-    a /= (float)B;
-    d /= (float)B;
-    out[0] = a + d * lmbd;
-    out[1] = a;
-    out[2] = d;
-    out[3] = s0 / (float)C;
-    out[4] = s1 / (float)C;
+  if (is_last) {                          // the last image's CTA sums the batch in a fixed order
+    __threadfence();
+    loss_finalize(terms, q_pos, k_pos, out, lmbd, B, C, red);
   }
 }
 
@@ -149,10 +160,10 @@ extern "C" int cp2_loss_combine(const float *q_pos, const float *k_pos, const fl
                                 const float *sq, const float *sk, const float *norms_q, const float *z,
                                 const float *G, const float *lse, const int32_t *key_count,
                                 const float *mask_a, const float *dense_n, float *out, float *l_pos, float *alpha, float *v1,
-                                float *v2, float *scratch, float inv_tau_global, float inv_tau_dense,
-                                float lmbd_dense, int B, int C, int P, void *stream) {
+                                float *v2, float *scratch, void *scratch_counter, float inv_tau_global,
+                                float inv_tau_dense, float lmbd_dense, int B, int C, int P, void *stream) {
   CP2_REQUIRE(B > 0 && C > 0 && P > 0, "cp2_loss_combine: bad shape B=%d C=%d P=%d", B, C, P);
-  CP2_REQUIRE(q_pos && k_pos && norms_q && z && G && key_count && mask_a && out && l_pos && alpha && v1 && scratch,
+  CP2_REQUIRE(q_pos && k_pos && norms_q && z && G && key_count && mask_a && out && l_pos && alpha && v1 && scratch && scratch_counter,
               "cp2_loss_combine: null pointer");
   CP2_REQUIRE(dense_n || (sq && sk && lse), "cp2_loss_combine: sq, sk and lse are needed unless dense_n is given");
   CP2_REQUIRE((q_neg == nullptr) == (k_neg == nullptr) && (q_neg == nullptr) == (v2 == nullptr),
@@ -160,10 +171,9 @@ extern "C" int cp2_loss_combine(const float *q_pos, const float *k_pos, const fl
   CP2_REQUIRE(inv_tau_global > 0.f && inv_tau_dense > 0.f, "cp2_loss_combine: bad temperature");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   loss_combine_kernel<<<B, 128, 0, st>>>(q_pos, k_pos, q_neg, k_neg, sq, sk, norms_q, z, G, lse, key_count, mask_a,
-                                         dense_n, scratch, l_pos, alpha, v1, v2, inv_tau_global, inv_tau_dense, lmbd_dense,
-                                         B, C, P);
-  CP2_LAUNCH_CHECK();
-  loss_finalize_kernel<<<1, 256, 0, st>>>(scratch, q_pos, k_pos, out, lmbd_dense, B, C);
+                                         dense_n, scratch, l_pos, alpha, v1, v2, out,
+                                         static_cast<unsigned int *>(scratch_counter), inv_tau_global, inv_tau_dense,
+                                         lmbd_dense, B, C, P);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }

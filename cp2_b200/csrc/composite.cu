@@ -7,12 +7,22 @@
 
 namespace {
 
+struct CompositeView {
+  const float *img, *bg;
+  float *out, *mask_full, *mask_ds;
+};
+struct CompositeViews { CompositeView v[2]; };     // blockIdx.y selects the view (1 or 2 views per launch)
+
 template <bool kVec>
 __global__ void __launch_bounds__(256)
-composite_kernel(const float *__restrict__ img, const float *__restrict__ bg, float *__restrict__ out,
-                 float *__restrict__ mask_full, float *__restrict__ mask_ds, int B, int H, int W,
-                 int os, int hs, int ws) {
+composite_kernel(const CompositeViews views, int B, int H, int W, int os, int hs, int ws) {
   constexpr int V = kVec ? 4 : 1;
+  const CompositeView &vw = views.v[blockIdx.y];
+  const float *__restrict__ img = vw.img;
+  const float *__restrict__ bg = vw.bg;
+  float *__restrict__ out = vw.out;
+  float *__restrict__ mask_full = vw.mask_full;
+  float *__restrict__ mask_ds = vw.mask_ds;
   const long long plane = (long long)H * W;
   const long long groups_per_img = plane / V;
   const long long total = (long long)B * groups_per_img;
@@ -68,28 +78,53 @@ composite_kernel(const float *__restrict__ img, const float *__restrict__ bg, fl
 
 }  // namespace
 
+namespace {
+
+int launch_composite(const CompositeViews &views, int nviews, int B, int H, int W, int os, cudaStream_t st) {
+  const int o = os / 2;
+  const int hs = H > o ? (H - o + os - 1) / os : 0;
+  const int ws = W > o ? (W - o + os - 1) / os : 0;
+  auto aligned = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+  bool vec = (W % 4 == 0);
+  for (int i = 0; i < nviews; ++i) {
+    const CompositeView &v = views.v[i];
+    if (!(v.img && v.bg && v.out)) { cp2_set_error("cp2_composite: null pointer"); return CP2_E_INVALID; }
+    if (!(v.mask_ds || hs * ws == 0)) { cp2_set_error("cp2_composite: null mask_ds"); return CP2_E_INVALID; }
+    vec = vec && aligned(v.img) && aligned(v.bg) && aligned(v.out) && (v.mask_full == nullptr || aligned(v.mask_full));
+  }
+  const long long groups = (long long)B * H * W / (vec ? 4 : 1);
+  const int threads = 256;
+  long long blocks = (groups + threads - 1) / threads;
+  const long long cap = (long long)cp2_num_sms() * 16 / nviews;     // grid-stride; whole waves of 148 SMs
+  if (blocks > cap) blocks = cap;
+  dim3 grid((unsigned)blocks, nviews);
+  if (vec)
+    composite_kernel<true><<<grid, threads, 0, st>>>(views, B, H, W, os, hs, ws);
+  else
+    composite_kernel<false><<<grid, threads, 0, st>>>(views, B, H, W, os, hs, ws);
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}
+
+}  // namespace
+
 extern "C" int cp2_composite(const float *img, const float *bg, float *out, float *mask_full,
                              float *mask_ds, int B, int H, int W, int os, void *stream) {
   CP2_REQUIRE(B >= 0 && H > 0 && W > 0 && os > 0, "cp2_composite: bad shape B=%d H=%d W=%d os=%d", B, H, W, os);
   if (B == 0) return CP2_OK;                 // empty batch: pointers may be null
-  CP2_REQUIRE(img && bg && out, "cp2_composite: null pointer");
-  const int o = os / 2;
-  const int hs = H > o ? (H - o + os - 1) / os : 0;
-  const int ws = W > o ? (W - o + os - 1) / os : 0;
-  CP2_REQUIRE(mask_ds || hs * ws == 0, "cp2_composite: null mask_ds");
-  auto aligned = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
-  const bool vec = (W % 4 == 0) && aligned(img) && aligned(bg) && aligned(out) &&
-                   (mask_full == nullptr || aligned(mask_full));
-  const long long groups = (long long)B * H * W / (vec ? 4 : 1);
-  const int threads = 256;
-  long long blocks = (groups + threads - 1) / threads;
-  const long long cap = (long long)cp2_num_sms() * 16;     // grid-stride; whole waves of 148 SMs
-  if (blocks > cap) blocks = cap;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (vec)
-    composite_kernel<true><<<(unsigned)blocks, threads, 0, st>>>(img, bg, out, mask_full, mask_ds, B, H, W, os, hs, ws);
-  else
-    composite_kernel<false><<<(unsigned)blocks, threads, 0, st>>>(img, bg, out, mask_full, mask_ds, B, H, W, os, hs, ws);
-  CP2_LAUNCH_CHECK();
-  return CP2_OK;
+  CompositeViews views;
+  views.v[0] = CompositeView{img, bg, out, mask_full, mask_ds};
+  views.v[1] = views.v[0];
+  return launch_composite(views, 1, B, H, W, os, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int cp2_composite2(const float *img_a, const float *bg_a, float *out_a, float *mask_full_a,
+                              float *mask_ds_a, const float *img_b, const float *bg_b, float *out_b,
+                              float *mask_full_b, float *mask_ds_b, int B, int H, int W, int os, void *stream) {
+  CP2_REQUIRE(B >= 0 && H > 0 && W > 0 && os > 0, "cp2_composite2: bad shape B=%d H=%d W=%d os=%d", B, H, W, os);
+  if (B == 0) return CP2_OK;
+  CompositeViews views;
+  views.v[0] = CompositeView{img_a, bg_a, out_a, mask_full_a, mask_ds_a};
+  views.v[1] = CompositeView{img_b, bg_b, out_b, mask_full_b, mask_ds_b};
+  return launch_composite(views, 2, B, H, W, os, static_cast<cudaStream_t>(stream));
 }

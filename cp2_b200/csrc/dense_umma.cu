@@ -613,15 +613,27 @@ int make_feature_tmap(CUtensorMap *tm, const void *base, int B, int C, int P, in
   return CP2_OK;
 }
 
-long long *g_dense_trace = nullptr;    // test-only: set by cp2_dbg_dense_trace, read by the next cp2_dense_grad
-
-// share of the exponentials evaluated on the FMA pipe, in quarters (0..3); tunable for experiments
+// Tuning knobs and the wait-time trace exist only in the DEBUG build of this file (libcp2_b200_debug.so,
+// -DCP2_DEBUG_BUILD, loaded by tests / dev scripts); the product library has neither getenv on the launch path
+// nor a trace entry point.
+#ifdef CP2_DEBUG_BUILD
+long long *g_dense_trace = nullptr;    // set by cp2_dbg_dense_trace, read by the next cp2_dense_grad
+// share of the exponentials evaluated on the FMA pipe, in quarters (0..3)
 int poly_quarters(const char *env, int dflt) {
   const char *e = getenv(env);
   if (!e || !*e) return dflt;
   const int v = atoi(e);
   return v < 0 ? 0 : (v > 3 ? 3 : v);
 }
+bool fwd_nsw8() {
+  const char *e = getenv("CP2_DENSE_NSW_FWD");
+  return !(e && atoi(e) == 4);
+}
+#else
+constexpr long long *g_dense_trace = nullptr;
+constexpr int poly_quarters(const char *, int dflt) { return dflt; }
+constexpr bool fwd_nsw8() { return true; }
+#endif
 
 template <int C>
 constexpr size_t lse_smem(int nst) { return 1024 + (size_t)(C / 64) * TILE * 128 * (1 + nst) + 256 + TILE * 4; }
@@ -657,10 +669,12 @@ int launch_grad(const CUtensorMap &tq, const CUtensorMap &tk, const void *qhat, 
 
 }  // namespace
 
+#ifdef CP2_DEBUG_BUILD
 extern "C" int cp2_dbg_dense_trace(long long *buf) {   // [n_sms * 16] device counters or NULL (cp2_b200_debug.h)
   g_dense_trace = buf;
   return CP2_OK;
 }
+#endif
 
 extern "C" int cp2_dense_pad(int P) { return P > 0 ? cp2_cdiv(P, TILE) * TILE : 0; }
 
@@ -680,8 +694,7 @@ extern "C" int cp2_dense_lse(const void *qhat_t, const void *khat_t, const int *
   // measured on B200 (dev/tune_dense.py, P=3136): C=128 best at 8 softmax warps + 1/4 of the exponentials on
   // the FMA pipe; at C=256 (one CTA per SM, MMA twice as long per exponential) the plain MUFU stream wins
   const int pf = poly_quarters("CP2_DENSE_PF_FWD", C == 128 ? 1 : 0);
-  const char *nsw_env = getenv("CP2_DENSE_NSW_FWD");
-  const bool nsw8 = !(nsw_env && atoi(nsw_env) == 4);
+  const bool nsw8 = fwd_nsw8();
 #define CP2_LSE(CC, PFV) (nsw8 ? launch_lse<CC, PFV, 8>(tq, tk, key_count, lse, sl2, B, P, st) \
                                : launch_lse<CC, PFV, 4>(tq, tk, key_count, lse, sl2, B, P, st))
   if (C == 128) {

@@ -1,10 +1,9 @@
-// f4 — the two accuracy meters forward_cp2 logs every step, without materialising the logits:
+// f4 — the dense accuracy meter forward_cp2 logs every step, without materialising the logits:
 //   acc_seg (reference builder.py:1442-1448): arg-max of the [P*P] dense logits of each image, hit if
-//           that pair is a label pair (mask_a[x] * mask_b[y]);
-//   acc_ins (builder.py:1441, 1690-1706): top-1 of [l_pos, q_pos @ queue, (l_neg_q, l_neg_k)] is l_pos.
-// Both are arg-max decisions, so they are taken in fp32 on CUDA cores straight from the fp32 inputs
-// (bf16 operands could flip near-ties): ~0.3 + 0.5 GFLOP at configs[1], the queue is still L2-resident
-// from cp2_global_nce.  Positive scalings (1/tau, all-ones weights) do not move an arg-max and are skipped.
+//           that pair is a label pair (mask_a[x] * mask_b[y]).
+// An arg-max decision, taken in fp32 on CUDA cores straight from the fp32 inputs (bf16 operands could flip
+// near-ties).  Positive scalings (1/tau, all-ones weights) do not move an arg-max and are skipped.
+// (acc_ins, builder.py:1441, comes out of cp2_global_nce's single queue pass.)
 #include "common.cuh"
 
 namespace {
@@ -149,103 +148,6 @@ dense_top1_finalize_kernel(const float *__restrict__ part_v, const int *__restri
   }
 }
 
-// max_k q_pos[r] . queue[:,k] over this CTA's 256-column blocks, 32 rows at a time (thread = column).
-__global__ void __launch_bounds__(MT)
-global_top1_kernel(const float *__restrict__ q_pos, const float *__restrict__ queue, float *__restrict__ part,
-                   int B, int C, int K) {
-  extern __shared__ __align__(16) float qT[];       // [C][32]
-  __shared__ float red[MT / 32][32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int nblk = (K + MT - 1) / MT;
-  for (int r0 = 0; r0 < B; r0 += 32) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < C * 32; i += MT) {
-      const int c = i >> 5, r = i & 31;
-      qT[i] = r0 + r < B ? q_pos[(long long)(r0 + r) * C + c] : 0.f;
-    }
-    __syncthreads();
-    float m[32];
-#pragma unroll
-    for (int r = 0; r < 32; ++r) m[r] = -INFINITY;
-    for (int blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
-      const int col = blk * MT + threadIdx.x;
-      if (col >= K) continue;
-      float acc[32];
-#pragma unroll
-      for (int r = 0; r < 32; ++r) acc[r] = 0.f;
-#pragma unroll 8
-      for (int c = 0; c < C; ++c) {
-        const float kv = __ldg(queue + (long long)c * K + col);
-#pragma unroll
-        for (int r4 = 0; r4 < 8; ++r4) {
-          const float4 qv = *reinterpret_cast<const float4 *>(qT + c * 32 + r4 * 4);
-          acc[4 * r4] = fmaf(qv.x, kv, acc[4 * r4]);
-          acc[4 * r4 + 1] = fmaf(qv.y, kv, acc[4 * r4 + 1]);
-          acc[4 * r4 + 2] = fmaf(qv.z, kv, acc[4 * r4 + 2]);
-          acc[4 * r4 + 3] = fmaf(qv.w, kv, acc[4 * r4 + 3]);
-        }
-      }
-#pragma unroll
-      for (int r = 0; r < 32; ++r) m[r] = fmaxf(m[r], acc[r]);
-    }
-#pragma unroll
-    for (int r = 0; r < 32; ++r) {
-      float v = m[r];
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, off));
-      if (lane == 0) red[warp][r] = v;
-    }
-    __syncthreads();
-    if (warp == 0 && r0 + lane < B) {
-      float v = red[0][lane];
-      for (int w = 1; w < MT / 32; ++w) v = fmaxf(v, red[w][lane]);
-      part[(long long)blockIdx.x * B + r0 + lane] = v;
-    }
-  }
-}
-
-// hit[r] = l_pos > every other logit of row r; acc = 100 * mean(hit).  One CTA, one warp per row.
-__global__ void __launch_bounds__(MT)
-global_top1_finalize_kernel(const float *__restrict__ part, const float *__restrict__ q_pos,
-                            const float *__restrict__ k_pos, const float *__restrict__ q_neg,
-                            const float *__restrict__ k_neg, float *__restrict__ hit, float *__restrict__ acc,
-                            int B, int C, int nctas) {
-  __shared__ float red[MT / 32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float s = 0.f;
-  for (int r = warp; r < B; r += MT / 32) {
-    float lp = 0.f, lq = 0.f, lk = 0.f, mx = -INFINITY;
-    for (int c = lane; c < C; c += 32) {
-      const float qp = q_pos[(long long)r * C + c];
-      lp = fmaf(qp, k_pos[(long long)r * C + c], lp);
-      if (q_neg) { lq = fmaf(qp, q_neg[(long long)r * C + c], lq); lk = fmaf(qp, k_neg[(long long)r * C + c], lk); }
-    }
-    for (int t = lane; t < nctas; t += 32) mx = fmaxf(mx, part[(long long)t * B + r]);
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-      lp += __shfl_xor_sync(0xffffffffu, lp, off);
-      lq += __shfl_xor_sync(0xffffffffu, lq, off);
-      lk += __shfl_xor_sync(0xffffffffu, lk, off);
-      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-    }
-    if (q_neg) mx = fmaxf(mx, fmaxf(lq, lk));
-    const float h = lp > mx ? 1.f : 0.f;
-    if (lane == 0) { hit[r] = h; s += h; }
-  }
-  if (lane == 0) red[warp] = s;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    float t = 0.f;
-    for (int w = 0; w < MT / 32; ++w) t += red[w];
-    acc[0] = t * (100.f / (float)B);
-  }
-}
-
-int top1_ctas(int K) {
-  const int nblk = cp2_cdiv(K, MT), cap = 2 * cp2_num_sms();
-  return nblk < cap ? nblk : cap;
-}
-
 }  // namespace
 
 extern "C" int64_t cp2_dense_top1_scratch_floats(int B, int P) {
@@ -267,25 +169,6 @@ extern "C" int cp2_dense_top1(const float *q, const float *k, const float *mask_
   dense_top1_kernel<<<dim3(ytiles, B, xchunks), MT, smem, st>>>(q, k, part_v, part_i, C, P);
   CP2_LAUNCH_CHECK();
   dense_top1_finalize_kernel<<<1, MT, 0, st>>>(part_v, part_i, mask_a, mask_b, hit, acc, B, P, tiles);
-  CP2_LAUNCH_CHECK();
-  return CP2_OK;
-}
-
-extern "C" int64_t cp2_global_top1_scratch_floats(int B, int K) { return (int64_t)B * top1_ctas(K); }
-
-extern "C" int cp2_global_top1(const float *q_pos, const float *k_pos, const float *q_neg, const float *k_neg,
-                               const float *queue, float *hit, float *acc, float *scratch, int B, int C, int K,
-                               void *stream) {
-  CP2_REQUIRE(B > 0 && K > 0 && C > 0 && C <= 1024, "cp2_global_top1: bad shape B=%d C=%d K=%d", B, C, K);
-  CP2_REQUIRE(q_pos && k_pos && queue && hit && acc && scratch, "cp2_global_top1: null pointer");
-  CP2_REQUIRE((q_neg == nullptr) == (k_neg == nullptr), "cp2_global_top1: q_neg and k_neg go together");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int nctas = top1_ctas(K);
-  const size_t smem = (size_t)C * 32 * sizeof(float);
-  CP2_CUDA(cudaFuncSetAttribute(global_top1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  global_top1_kernel<<<nctas, MT, smem, st>>>(q_pos, queue, scratch, B, C, K);
-  CP2_LAUNCH_CHECK();
-  global_top1_finalize_kernel<<<1, MT, 0, st>>>(scratch, q_pos, k_pos, q_neg, k_neg, hit, acc, B, C, nctas);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }

@@ -80,6 +80,20 @@ def _f32c(t):
     return t if t.is_contiguous() else t.contiguous()
 
 
+# Persistent zero-initialised scratch (done counters / fixed-point accumulators): the kernels that use one
+# leave it all-zero again, so it is allocated and cleared once per (device, stream, tag, size).
+_scratch = {}
+
+
+def _persistent_zero(tag, nbytes, device):
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream, tag, int(nbytes))
+    t = _scratch.get(key)
+    if t is None:
+        t = torch.zeros((int(nbytes) + 7) // 8, device=device, dtype=torch.int64)
+        _scratch[key] = t
+    return t
+
+
 # ------------------------------------------------------------------ K1
 def composite(img, bg, output_stride, want_full_mask=False, out=None):
     """builder.py:1146-1159.  Returns (composited [B,3,H,W], mask_ds [B,hs,ws], mask_full|None)."""
@@ -99,9 +113,21 @@ def composite(img, bg, output_stride, want_full_mask=False, out=None):
 
 
 def composite_pair(img_a, bg_a, img_b, bg_b, output_stride, want_full_mask=False):
-    """Both views of builder.py:1146-1159 -> ((out_a, mask_ds_a, full_a), (out_b, mask_ds_b, full_b))."""
-    return (composite(img_a, bg_a, output_stride, want_full_mask),
-            composite(img_b, bg_b, output_stride, want_full_mask))
+    """Both views of builder.py:1146-1159 in ONE launch -> ((out_a, mask_ds_a, full_a), (out_b, mask_ds_b, full_b))."""
+    _need_cuda(img_a, bg_a, img_b, bg_b)
+    img_a, bg_a, img_b, bg_b = _f32c(img_a), _f32c(bg_a), _f32c(img_b), _f32c(bg_b)
+    B, ch, H, W = img_a.shape
+    assert ch == 3 and bg_a.shape == img_a.shape and img_b.shape == img_a.shape and bg_b.shape == img_a.shape
+    o = output_stride // 2
+    hs, ws = len(range(o, H, output_stride)), len(range(o, W, output_stride))
+    dev = img_a.device
+    outs = [torch.empty_like(img_a), torch.empty_like(img_b)]
+    mds = [torch.empty((B, hs, ws), device=dev, dtype=torch.float32) for _ in range(2)]
+    full = [torch.empty((B, H, W), device=dev, dtype=torch.float32) if want_full_mask else None for _ in range(2)]
+    _call("cp2_composite2", 1, _lib.load().cp2_composite2, _ptr(img_a), _ptr(bg_a), _ptr(outs[0]), _ptr(full[0]),
+          _ptr(mds[0]), _ptr(img_b), _ptr(bg_b), _ptr(outs[1]), _ptr(full[1]), _ptr(mds[1]), B, H, W, output_stride,
+          _stream())
+    return (outs[0], mds[0], full[0]), (outs[1], mds[1], full[1])
 
 
 # ----------------------------------------------------------------- K2a
@@ -125,11 +151,36 @@ def prep_features(feat, mask, compact=False, unit=False):
     pu = torch.empty((B, C), device=dev, dtype=torch.float32) if unit else None
     nu = torch.empty((B, C), device=dev, dtype=torch.float32) if unit else None
     norms = torch.empty((B, 2), device=dev, dtype=torch.float32) if unit else None
-    _call("cp2_prep_features", 2, lib.cp2_prep_features, _ptr(feat), _ptr(mask), _ptr(fhat_t), _ptr(inv_norm),
-          _ptr(pos), _ptr(neg), _ptr(scratch), _ptr(count), _ptr(pu), _ptr(nu), _ptr(norms), B, C, P, _stream())
+    _call("cp2_prep_features", 1, lib.cp2_prep_features, _ptr(feat), _ptr(mask), _ptr(fhat_t), _ptr(inv_norm),
+          _ptr(pos), _ptr(neg), _ptr(scratch), _ptr(count), _ptr(pu), _ptr(nu), _ptr(norms),
+          _ptr(_persistent_zero("prep", 4 * B, dev)), B, C, P, _stream())
     if unit:
         return fhat_t, inv_norm, pos, neg, count, pu, nu, norms
     return fhat_t, inv_norm, pos, neg, count
+
+
+def prep_features_pair(feat_q, mask_q, feat_k, mask_k):
+    """Query side and (compacted) key side of one step in ONE launch.  -> two tuples shaped like
+    prep_features(..., unit=True): (fhat_t, inv_norm, pos_sum, neg_sum, key_count|None, pos_unit, neg_unit, norms)."""
+    _need_cuda(feat_q, mask_q, feat_k, mask_k)
+    feat_q, mask_q, feat_k, mask_k = _f32c(feat_q), _f32c(mask_q), _f32c(feat_k), _f32c(mask_k)
+    B, C, P = feat_q.shape
+    assert feat_k.shape == feat_q.shape
+    lib, dev = _lib.load(), feat_q.device
+    f32 = dict(device=dev, dtype=torch.float32)
+    tiles = lib.cp2_prep_tiles(P)
+
+    def side():
+        return [torch.empty((B, P, C), device=dev, dtype=torch.bfloat16), torch.empty((B, P), **f32),
+                torch.empty((B, C), **f32), torch.empty((B, C), **f32), torch.empty((B, tiles, 2, C), **f32),
+                torch.empty((B, C), **f32), torch.empty((B, C), **f32), torch.empty((B, 2), **f32)]
+    q, k = side(), side()
+    count = torch.empty((B,), device=dev, dtype=torch.int32)
+    _call("cp2_prep_features2", 1, lib.cp2_prep_features2,
+          _ptr(feat_q), _ptr(mask_q), *[_ptr(t) for t in q],
+          _ptr(feat_k), _ptr(mask_k), *[_ptr(t) for t in k[:5]], _ptr(count), *[_ptr(t) for t in k[5:]],
+          _ptr(_persistent_zero("prep2", 8 * B, dev)), B, C, P, _stream())
+    return ((q[0], q[1], q[2], q[3], None, q[5], q[6], q[7]), (k[0], k[1], k[2], k[3], count, k[5], k[6], k[7]))
 
 
 # ------------------------------------------------------------------ K2
@@ -168,8 +219,43 @@ def dense_fwd_bwd(qhat_t, khat_t, key_count, mask_a, inv_norm, alpha, v1, v2, in
 
 
 # ------------------------------------------------------------------ K3
-def global_nce(q_pos, queue, inv_tau):
-    """One pass over the queue: z[b] = sum_k exp((l-1)/tau), g[b,:] = sum_k exp((l-1)/tau) queue[:,k]."""
+class QueueShadow:
+    """The bf16 entry-major [K,C] shadow of one fp32 [C,K] queue buffer that cp2_global_nce streams.
+    cp2_enqueue rewrites the rows it enqueues, so in steady state the shadow never needs a conversion pass;
+    it is rebuilt (cp2_queue_shadow, one transpose kernel) when the fp32 buffer was replaced or written by
+    anything else (torch in-place ops bump `queue._version`: load_state_dict, copy_, normalisation at init)."""
+
+    def __init__(self):
+        self.bf = None           # [K,C] view of the storage below
+        self._store = None       # [rows >= K, C]; rows past K stay zero (block padding of queue_sums_tc)
+        self._key = None
+
+    def _sig(self, queue):
+        return (queue.data_ptr(), queue._version, tuple(queue.shape))
+
+    def get(self, queue, min_rows=0):
+        _need_cuda(queue)
+        assert queue.dtype == torch.float32 and queue.is_contiguous() and queue.dim() == 2
+        C, K = queue.shape
+        if self.bf is None or self._key != self._sig(queue) or self._store.shape[0] < min_rows:
+            rows = max(K, int(min_rows), 0 if self._store is None else self._store.shape[0])
+            if self._store is None or self._store.shape != (rows, C) or self._store.device != queue.device:
+                self._store = torch.zeros((rows, C), device=queue.device, dtype=torch.bfloat16)
+            self.bf = self._store[:K]
+            _call("cp2_queue_shadow", 1, _lib.load().cp2_queue_shadow, _ptr(queue), _ptr(self.bf), C, K, _stream())
+            self._key = self._sig(queue)
+        return self.bf
+
+    def padded(self, queue, rows):
+        """[rows, C] view (rows >= K): the shadow followed by zero rows."""
+        self.get(queue, min_rows=rows)
+        return self._store[:rows]
+
+
+def global_nce(q_pos, queue, inv_tau, k_pos=None, q_neg=None, k_neg=None, shadow=None):
+    """One launch, one pass over the queue: z[b] = sum_k exp((l-1)/tau), g[b,:] = sum_k exp((l-1)/tau) queue[:,k]
+    and, with k_pos, the top-1 meter (hit [B], acc [1]).  -> (z, g, hit|None, acc|None).
+    shadow: a QueueShadow kept across steps (MODEL does); None converts the queue for this call."""
     _need_cuda(q_pos, queue)
     q_pos = _f32c(q_pos)
     B, C = q_pos.shape
@@ -177,12 +263,20 @@ def global_nce(q_pos, queue, inv_tau):
     K = queue.shape[1]
     lib = _lib.load()
     dev = q_pos.device
+    qbf = (shadow if shadow is not None else QueueShadow()).get(queue)
     z = torch.empty((B,), device=dev, dtype=torch.float32)
     g = torch.empty((B, C), device=dev, dtype=torch.float32)
-    scratch = torch.empty((max(1, lib.cp2_global_scratch_floats(B, C)),), device=dev, dtype=torch.float32)
-    _call("cp2_global_nce", 2, lib.cp2_global_nce, _ptr(q_pos), _ptr(queue), _ptr(z), _ptr(g), _ptr(scratch), float(inv_tau),
-                                  B, C, K, _stream())
-    return z, g
+    hit = acc = None
+    if k_pos is not None:
+        k_pos = _f32c(k_pos)
+        hit = torch.empty((B,), device=dev, dtype=torch.float32)
+        acc = torch.empty((1,), device=dev, dtype=torch.float32)
+    if q_neg is not None:
+        q_neg, k_neg = _f32c(q_neg), _f32c(k_neg)
+    scratch = _persistent_zero("global", lib.cp2_global_scratch_bytes(B, C), dev)
+    _call("cp2_global_nce", 1, lib.cp2_global_nce, _ptr(q_pos), _ptr(qbf), _ptr(queue), _ptr(k_pos), _ptr(q_neg),
+          _ptr(k_neg), _ptr(z), _ptr(g), _ptr(hit), _ptr(acc), _ptr(scratch), float(inv_tau), B, C, K, _stream())
+    return z, g, hit, acc
 
 
 # ------------------------------------------------------------------ K4
@@ -244,21 +338,23 @@ class EmaPlan:
 
 # ------------------------------------------------------------------ K5
 @torch.no_grad()
-def enqueue(keys_all, queue, queue_ptr):
-    """builder.py:574-587 on device: queue[:, (ptr+i) % K] = keys_all[i]; ptr = (ptr+n) % K."""
+def enqueue(keys_all, queue, queue_ptr, shadow=None):
+    """builder.py:574-587 on device, one launch: queue[:, (ptr+i) % K] = keys_all[i]; ptr = (ptr+n) % K.
+    shadow: the queue's QueueShadow; its rows (ptr+i) % K are rewritten too (it stays valid)."""
     _need_cuda(keys_all, queue, queue_ptr)
     keys_all = _f32c(keys_all)
     n, C = keys_all.shape
     assert queue.dtype == torch.float32 and queue.is_contiguous() and queue.shape[0] == C
     assert queue_ptr.dtype == torch.int64 and queue_ptr.numel() == 1
-    _call("cp2_enqueue", 2, _lib.load().cp2_enqueue, _ptr(keys_all), _ptr(queue), _ptr(queue_ptr), n, C, queue.shape[1],
-                                      _stream())
+    qbf = shadow.get(queue) if shadow is not None else None      # (re)built first if stale, then kept in step
+    _call("cp2_enqueue", 1, _lib.load().cp2_enqueue, _ptr(keys_all), _ptr(queue), _ptr(qbf), _ptr(queue_ptr),
+          _ptr(_persistent_zero("enqueue", 8, queue.device)), n, C, queue.shape[1], _stream())
 
 
 # ------------------------------------------------- fused loss (a5 + a6 + a7 + a12)
 def loss_combine(q_pos, k_pos, q_neg, k_neg, sq, sk, norms_q, z, G, lse, key_count, mask_a, temp_global,
                  temp_local, lmbd_dense, dense_n=None):
-    """cp2_loss_combine: the [B,C]/[B]-sized remainder of the loss (2 launches).
+    """cp2_loss_combine: the [B,C]/[B]-sized remainder of the loss (1 launch).
     -> out [5] = (loss, loss_ins, loss_dense, std meter of q_pos, std meter of k_pos), l_pos [B],
        alpha [B], v1 [B,C], v2 [B,C]|None (inputs of cp2_dense_grad for upstream gradient 1).
     dense_n [B] (PROPOSED modes): per-image dense losses from dense_weighted_lse; sq, sk, lse are then unused."""
@@ -271,9 +367,10 @@ def loss_combine(q_pos, k_pos, q_neg, k_neg, sq, sk, norms_q, z, G, lse, key_cou
     v1 = torch.empty((B, C), device=dev, dtype=torch.float32)
     v2 = torch.empty((B, C), device=dev, dtype=torch.float32) if q_neg is not None else None
     scratch = torch.empty((B, 2), device=dev, dtype=torch.float32)
-    _call("cp2_loss_combine", 2, _lib.load().cp2_loss_combine, _ptr(q_pos), _ptr(k_pos), _ptr(q_neg), _ptr(k_neg),
+    _call("cp2_loss_combine", 1, _lib.load().cp2_loss_combine, _ptr(q_pos), _ptr(k_pos), _ptr(q_neg), _ptr(k_neg),
           _ptr(sq), _ptr(sk), _ptr(norms_q), _ptr(z), _ptr(G), _ptr(lse), _ptr(key_count), _ptr(mask_a), _ptr(dense_n),
-          _ptr(out), _ptr(l_pos), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(scratch), 1.0 / float(temp_global),
+          _ptr(out), _ptr(l_pos), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(scratch),
+          _ptr(_persistent_zero("combine", 8, dev)), 1.0 / float(temp_global),
           1.0 / float(temp_local), float(lmbd_dense), B, C, P, _stream())
     return out, l_pos, alpha, v1, v2
 
@@ -283,34 +380,40 @@ class CP2LossFunction(torch.autograd.Function):
     1392-1397, 1414-1439), MappingType.CP2 / NegativeType.NONE.
 
     forward(q [B,C,h,w], k [B,C,h,w], mask_a [B,P], mask_b [B,P], queue [C,K], ...) ->
-        (loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters [2])
+        (loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters [2], q_neg, k_neg, acc_ins [1])
     Only `loss` carries a gradient, and only to q (keys and queue are detached in the
-    reference, builder.py:1271,1396).  Forward = cp2_prep_features x 2, cp2_global_nce, cp2_dense_lse,
-    cp2_loss_combine; backward = cp2_dense_grad alone, reading the upstream gradient from device memory.
+    reference, builder.py:1271,1396).  Forward = cp2_prep_features2, cp2_global_nce, cp2_dense_lse,
+    cp2_loss_combine (4 launches); backward = cp2_dense_grad alone, reading the upstream gradient from device memory.
     No ATen arithmetic in between: torch only allocates the buffers.
     """
 
     @staticmethod
-    def forward(ctx, q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense, include_background):
+    def forward(ctx, q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense, include_background,
+                queue_shadow, track_accuracy):
         B, C = q.shape[0], q.shape[1]
         qf = _f32c(q.detach()).reshape(B, C, -1)
         kf = _f32c(k.detach()).reshape(B, C, -1)
         mask_a, mask_b = _f32c(mask_a), _f32c(mask_b)
         tg, tl = float(temp_global), float(temp_local)
-        qh, q_inv, sq, _, _, q_pos, q_neg, norms_q = prep_features(qf, mask_a, unit=True)
-        # key side compacted: fg keys first, zero rows after
-        kh, _, sk, _, kcnt, k_pos, k_neg, _ = prep_features(kf, mask_b, compact=True, unit=True)
-        z, G = global_nce(q_pos, queue, 1.0 / tg)              # one pass over the queue: fwd + bwd sums
-        lse = dense_lse(qh, kh, 1.0 / tl, kcnt)                # column LSE on the tensor cores
+        # one launch for both sides; key side compacted: fg keys first, zero rows after
+        (qh, q_inv, sq, _, _, q_pos, q_neg, norms_q), (kh, _, sk, _, kcnt, k_pos, k_neg, _) = \
+            prep_features_pair(qf, mask_a, kf, mask_b)
         bg = bool(include_background)
+        # one pass over the queue: fwd + bwd sums (+ the acc_ins meter)
+        z, G, _, acc_ins = global_nce(q_pos, queue, 1.0 / tg, k_pos if track_accuracy else None,
+                                      q_neg if (bg and track_accuracy) else None,
+                                      k_neg if (bg and track_accuracy) else None, shadow=queue_shadow)
+        lse = dense_lse(qh, kh, 1.0 / tl, kcnt)                # column LSE on the tensor cores
         out, l_pos, alpha, v1, v2 = loss_combine(q_pos, k_pos, q_neg if bg else None, k_neg if bg else None,
                                                  sq, sk, norms_q, z, G, lse, kcnt, mask_a, tg, tl, lmbd_dense)
         ctx.save_for_backward(qh, kh, lse, mask_a, kcnt, q_inv, alpha, v1, v2)
         ctx.inv_tl = 1.0 / tl
         ctx.q_shape = q.shape
         loss, loss_ins, loss_dense, meters = out[0], out[1], out[2], out[3:]
-        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg)
-        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg
+        if acc_ins is None:
+            acc_ins = torch.full((1,), float("nan"), device=q.device)
+        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg, acc_ins)
+        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg, acc_ins
 
     @staticmethod
     def backward(ctx, g_loss, *_unused):
@@ -319,7 +422,7 @@ class CP2LossFunction(torch.autograd.Function):
         if g.dtype != torch.float32 or not g.is_contiguous():
             g = g.float().contiguous()
         dq = dense_grad(qh, kh, lse, mask_a, None, q_inv, alpha, v1, v2, ctx.inv_tl, key_count=kcnt, gscale=g)
-        return dq.reshape(ctx.q_shape), None, None, None, None, None, None, None, None
+        return (dq.reshape(ctx.q_shape),) + (None,) * 10
 
 
 # ------------------------------------------------- f3: PROPOSED-mode dense loss
@@ -385,7 +488,8 @@ class CP2WeightedLossFunction(torch.autograd.Function):
     cp2_global_nce, cp2_dense_weighted_lse, cp2_loss_combine; backward = cp2_dense_weighted_grad."""
 
     @staticmethod
-    def forward(ctx, q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense, include_background, pw):
+    def forward(ctx, q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense, include_background, pw,
+                queue_shadow, track_accuracy):
         B, C = q.shape[0], q.shape[1]
         qf = _f32c(q.detach()).reshape(B, C, -1)
         kf = _f32c(k.detach()).reshape(B, C, -1)
@@ -393,17 +497,21 @@ class CP2WeightedLossFunction(torch.autograd.Function):
         tg, tl = float(temp_global), float(temp_local)
         qh, q_inv, sq, nsq, _, q_pos, q_neg, norms_q = prep_features(qf, mask_a, unit=True)
         kh, _, sk, nsk, _, k_pos, k_neg, _ = prep_features(kf, mask_b, unit=True)
-        z, G = global_nce(q_pos, queue, 1.0 / tg)
-        lse, dense_n, wstats, kcnt, acc_seg = dense_weighted_lse(qh, kh, mask_a, mask_b, pw, sq, nsq, sk, nsk, 1.0 / tl)
         bg = bool(include_background)
+        z, G, _, acc_ins = global_nce(q_pos, queue, 1.0 / tg, k_pos if track_accuracy else None,
+                                      q_neg if (bg and track_accuracy) else None,
+                                      k_neg if (bg and track_accuracy) else None, shadow=queue_shadow)
+        lse, dense_n, wstats, kcnt, acc_seg = dense_weighted_lse(qh, kh, mask_a, mask_b, pw, sq, nsq, sk, nsk, 1.0 / tl)
         out, l_pos, alpha, v1, v2 = loss_combine(q_pos, k_pos, q_neg if bg else None, k_neg if bg else None,
                                                  None, None, norms_q, z, G, None, kcnt, mask_a, tg, tl, lmbd_dense,
                                                  dense_n=dense_n)
         ctx.save_for_backward(qh, kh, lse, mask_a, mask_b, wstats, q_inv, alpha, v1, v2)
         ctx.inv_tl, ctx.pw, ctx.q_shape = 1.0 / tl, pw, q.shape
         loss, loss_ins, loss_dense, meters = out[0], out[1], out[2], out[3:]
-        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg, acc_seg)
-        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg, acc_seg
+        if acc_ins is None:
+            acc_ins = torch.full((1,), float("nan"), device=q.device)
+        ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg, acc_ins, acc_seg)
+        return loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg, acc_ins, acc_seg
 
     @staticmethod
     def backward(ctx, g_loss, *_unused):
@@ -412,25 +520,28 @@ class CP2WeightedLossFunction(torch.autograd.Function):
         if g.dtype != torch.float32 or not g.is_contiguous():
             g = g.float().contiguous()
         dq = dense_weighted_grad(qh, kh, mask_a, mask_b, ctx.pw, lse, wstats, q_inv, alpha, v1, v2, ctx.inv_tl, gscale=g)
-        return (dq.reshape(ctx.q_shape),) + (None,) * 9
+        return (dq.reshape(ctx.q_shape),) + (None,) * 11
 
 
 def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_dense=0.2,
-             include_background=False, pair_weights=None):
+             include_background=False, pair_weights=None, queue_shadow=None, track_accuracy=False):
     """-> (loss, loss_ins, loss_dense, k_pos, q_pos, stats); only `loss` has a gradient (to q).
-    pair_weights: None (MappingType.CP2 / NegativeType.NONE, the tensor-core path) or a PairWeights."""
-    nan = float("nan")       # the accuracy meters are separate launches: ops.global_top1 / ops.dense_top1
+    pair_weights: None (MappingType.CP2 / NegativeType.NONE, the tensor-core path) or a PairWeights.
+    queue_shadow: the queue's QueueShadow (None: the queue is converted to bf16 for this call).
+    track_accuracy: stats["acc_ins"] from the same queue pass (builder.py:1441); acc_seg is ops.dense_top1's."""
+    nan = float("nan")
     acc_seg = nan
     if pair_weights is None:
         res = CP2LossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense,
-                                    include_background)
+                                    include_background, queue_shadow, bool(track_accuracy))
     else:                    # the weighted forward finds the arg-max of its own logits on the way
         *res, acc_seg = CP2WeightedLossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local,
-                                                      lmbd_dense, include_background, pair_weights)
+                                                      lmbd_dense, include_background, pair_weights, queue_shadow,
+                                                      bool(track_accuracy))
         acc_seg = acc_seg[0]
-    loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg = res
-    stats = {"l_pos": l_pos, "acc_ins": nan, "acc_seg": acc_seg, "std_q_pos": meters[0], "std_k_pos": meters[1],
-             "q_neg": q_neg, "k_neg": k_neg}
+    loss, loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg, acc_ins = res
+    stats = {"l_pos": l_pos, "acc_ins": acc_ins[0], "acc_seg": acc_seg, "std_q_pos": meters[0],
+             "std_k_pos": meters[1], "q_neg": q_neg, "k_neg": k_neg}
     return loss, loss_ins, loss_dense, k_pos, q_pos, stats
 
 
@@ -451,7 +562,7 @@ TC_ROWS_MIN = 1024      # from this many rows on, the queue sums run on the dens
 
 
 @torch.no_grad()
-def queue_sums_tc(rows, queue, inv_tau):
+def queue_sums_tc(rows, queue, inv_tau, shadow=None):
     """z [N], G [N,C] as cp2_global_nce defines them (z = sum_k exp((l_k-1)/tau), G = sum_k exp((l_k-1)/tau) u_k),
     for MANY rows, on the tcgen05 kernels of the dense loss instead of one queue pass per 32 rows: the queue is
     cut into blocks of Pb = ceil128(N) entries, block n and the rows form "image" n of a [nb,Pb,Pb] problem;
@@ -466,11 +577,8 @@ def queue_sums_tc(rows, queue, inv_tau):
     Pb = (N + 127) // 128 * 128
     nb = (K + Pb - 1) // Pb
     pad = nb * Pb - K
-    ones_k = torch.ones((1, K), device=dev, dtype=torch.float32)
-    qt = prep_features(queue.unsqueeze(0), ones_k)[0]                    # [1,K,C] bf16 (columns re-normalised)
-    qblocks = torch.zeros((nb * Pb, C), device=dev, dtype=torch.bfloat16)
-    qblocks[:K] = qt[0]
-    qblocks = qblocks.view(nb, Pb, C)
+    # the queue's bf16 entry-major shadow (kept in step by cp2_enqueue) followed by zero rows IS the block operand
+    qblocks = (shadow if shadow is not None else QueueShadow()).padded(queue, nb * Pb).view(nb, Pb, C)
     rt = torch.zeros((Pb, C), device=dev, dtype=torch.bfloat16)
     rt[:N] = rows
     rblocks = rt.unsqueeze(0).expand(nb, Pb, C).contiguous()
@@ -493,12 +601,12 @@ class RowsInfoNCEFunction(torch.autograd.Function):
     detached in the reference, builder.py:726, 768, 872)."""
 
     @staticmethod
-    def forward(ctx, rows, pos_keys, queue, temp):
+    def forward(ctx, rows, pos_keys, queue, temp, shadow):
         rows_c, pos_c = _f32c(rows.detach()), _f32c(pos_keys.detach())
         if rows_c.shape[0] >= TC_ROWS_MIN:
-            z, G = queue_sums_tc(rows_c, queue, 1.0 / float(temp))
+            z, G = queue_sums_tc(rows_c, queue, 1.0 / float(temp), shadow)
         else:
-            z, G = global_nce(rows_c, queue, 1.0 / float(temp))
+            z, G = global_nce(rows_c, queue, 1.0 / float(temp), shadow=shadow)[:2]
         loss, _, dq = rows_nce(rows_c, pos_c, z, G, 1.0 / float(temp), want_grad=True)
         ctx.save_for_backward(dq)
         return loss[0]
@@ -506,12 +614,12 @@ class RowsInfoNCEFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         (dq,) = ctx.saved_tensors
-        return dq * g, None, None, None
+        return dq * g, None, None, None, None
 
 
-def rows_infonce(rows, pos_keys, queue, temp):
+def rows_infonce(rows, pos_keys, queue, temp, shadow=None):
     """rows, pos_keys [N,C] (rows unit vectors), queue [C,K] -> 0-d loss with a gradient to rows."""
-    return RowsInfoNCEFunction.apply(rows, pos_keys, queue, temp)
+    return RowsInfoNCEFunction.apply(rows, pos_keys, queue, temp, shadow)
 
 
 @torch.no_grad()
@@ -542,15 +650,16 @@ def densecl_match(embd_q, embd_k):
 
 
 def densecl_loss(embd_q, embd_k, q_local, k_local, q_global, k_global, queue, queue2, temp_global=0.2,
-                 temp_local=0.2, lmbd_dense=0.5, pix_q=None, pix_k=None, output_stride=1, lmbd_coordinate=0.0):
+                 temp_local=0.2, lmbd_dense=0.5, pix_q=None, pix_k=None, output_stride=1, lmbd_coordinate=0.0,
+                 shadow=None, shadow2=None):
     """One direction of forward_densecl (builder.py:762-931) on the unit features get_query_features /
     get_key_features return: -> (loss, loss_global, loss_local), gradients to q_global and q_local."""
     B, C, P = q_local.shape
-    loss_g = rows_infonce(q_global, k_global, queue, temp_global)
+    loss_g = rows_infonce(q_global, k_global, queue, temp_global, shadow)
     idx = densecl_match(embd_q.detach(), embd_k.detach())
     kp = positive_keys(k_local.detach(), idx, pix_q, pix_k, output_stride, lmbd_coordinate)
     rows = q_local.permute(0, 2, 1).reshape(B * P, C)
-    loss_l = rows_infonce(rows, kp, queue2, temp_local)
+    loss_l = rows_infonce(rows, kp, queue2, temp_local, shadow2)
     return (1 - lmbd_dense) * loss_g + lmbd_dense * loss_l, loss_g, loss_l
 
 
@@ -573,20 +682,10 @@ def dense_top1(q, k, mask_a, mask_b):
 
 
 @torch.no_grad()
-def global_top1(q_pos, k_pos, queue, q_neg=None, k_neg=None):
-    """builder.py:1441 (top-1 of `_accuracy`) -> (acc_ins 0-d, hit [B]).  Call BEFORE the enqueue."""
-    _need_cuda(q_pos, k_pos, queue)
-    q_pos, k_pos = _f32c(q_pos), _f32c(k_pos)
-    B, C = q_pos.shape
-    assert queue.dtype == torch.float32 and queue.is_contiguous() and queue.shape[0] == C
-    K = queue.shape[1]
-    lib, dev = _lib.load(), q_pos.device
-    hit = torch.empty((B,), device=dev, dtype=torch.float32)
-    acc = torch.empty((1,), device=dev, dtype=torch.float32)
-    scratch = torch.empty((lib.cp2_global_top1_scratch_floats(B, K),), device=dev, dtype=torch.float32)
-    _call("cp2_global_top1", 2, lib.cp2_global_top1, _ptr(q_pos), _ptr(k_pos),
-          _ptr(_f32c(q_neg) if q_neg is not None else None), _ptr(_f32c(k_neg) if k_neg is not None else None),
-          _ptr(queue), _ptr(hit), _ptr(acc), _ptr(scratch), B, C, K, _stream())
+def global_top1(q_pos, k_pos, queue, q_neg=None, k_neg=None, shadow=None):
+    """builder.py:1441 (top-1 of `_accuracy`) -> (acc_ins 0-d, hit [B]): the meter part of cp2_global_nce on its
+    own (the training step gets it from the loss's queue pass).  Call BEFORE the enqueue."""
+    _, _, hit, acc = global_nce(q_pos, queue, 5.0, k_pos, q_neg, k_neg, shadow=shadow)
     return acc[0], hit
 
 

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CP2_ABI_VERSION 6
+#define CP2_ABI_VERSION 7
 
 #define CP2_OK 0
 #define CP2_E_INVALID (-1)      /* bad shape / null pointer / unsupported dim          */
@@ -43,6 +43,10 @@ const char *cp2_last_error(void);
  * Bit-exact with the reference. */
 int cp2_composite(const float *img, const float *bg, float *out, float *mask_full,
                   float *mask_ds, int B, int H, int W, int os, void *stream);
+/* Both views of one step in one launch (same contract per view as cp2_composite). */
+int cp2_composite2(const float *img_a, const float *bg_a, float *out_a, float *mask_full_a, float *mask_ds_a,
+                   const float *img_b, const float *bg_b, float *out_b, float *mask_full_b, float *mask_ds_b,
+                   int B, int H, int W, int os, void *stream);
 
 /* K2a — per-pixel L2 normalisation + masked pooling + bf16 transpose (+ key compaction).
  * Replaces builder.py:1261-1268 (query) / 1279-1285 (key): F.normalize(dim=1) and the
@@ -63,11 +67,23 @@ int cp2_composite(const float *img, const float *bg, float *out, float *mask_ful
  *   pos_unit, neg_unit, norms : all NULL, or OUT [B,C], [B,C], [B,2]: the outer F.normalize of the pooled
  *               vectors (builder.py:1264,1268,1282,1285), x / max(||x||, 1e-12), and the raw norms
  *               (||pos_sum||, ||neg_sum||) the normalisation's backward needs.
+ *   scratch_counters : B uint32, PERSISTENT (zero before the first call, left zero): done counters — the
+ *               last tile CTA of an image reduces the image's per-tile partial sums in a fixed order
+ *               (one launch, deterministic).
  * C must be a multiple of 64 and <= 256. */
 int cp2_prep_tiles(int P);
 int cp2_prep_features(const float *feat, const float *mask, void *fhat_t, float *inv_norm,
                       float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count,
-                      float *pos_unit, float *neg_unit, float *norms, int B, int C, int P, void *stream);
+                      float *pos_unit, float *neg_unit, float *norms, void *scratch_counters,
+                      int B, int C, int P, void *stream);
+/* Query side and key side (key side compacted through key_count) of one step in ONE launch; per side the
+ * contract of cp2_prep_features.  scratch_counters: 2*B uint32. */
+int cp2_prep_features2(const float *feat_q, const float *mask_q, void *qhat_t, float *inv_norm_q,
+                       float *pos_sum_q, float *neg_sum_q, float *scratch_q, float *pos_unit_q,
+                       float *neg_unit_q, float *norms_q, const float *feat_k, const float *mask_k,
+                       void *khat_t, float *inv_norm_k, float *pos_sum_k, float *neg_sum_k,
+                       float *scratch_k, int32_t *key_count, float *pos_unit_k, float *neg_unit_k,
+                       float *norms_k, void *scratch_counters, int B, int C, int P, void *stream);
 
 /* K2 forward — dense pixel InfoNCE, column log-sum-exp.
  * Replaces builder.py:1289 (einsum ncx,ncy->nxy), :1431 (/T) and the LogSoftmax(dim=1)
@@ -96,20 +112,32 @@ int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int32_t *key_co
                    const float *v1, const float *v2, const float *gscale, float *dq, float *scratch_nl,
                    float inv_tau, int B, int C, int P, void *stream);
 
-/* K3 — global MoCo InfoNCE against the negative queue, forward and backward in one
- * pass over the queue.  Replaces builder.py:1396 (q_pos @ queue.clone()) and the
- * queue part of F.cross_entropy at :1428 and its autograd:
+/* K3 — global MoCo InfoNCE against the negative queue: forward sums, backward sums and the top-1
+ * accuracy meter in one launch and one pass over the queue.  Replaces builder.py:1396
+ * (q_pos @ queue.clone()), the queue part of F.cross_entropy at :1428 and its autograd, and
+ * :1441 + _accuracy :1690-1706 (top-1 of logits_moco):
  *   z[b]   = sum_k exp((l[b,k] - 1) * inv_tau),      l = q_pos @ queue
  *   g[b,:] = sum_k exp((l[b,k] - 1) * inv_tau) * queue[:,k]
+ *   hit[b] = l_pos[b] > every l[b,k] (and > the two background logits when q_neg/k_neg are given),
+ *            l_pos = q_pos[b].k_pos[b];   acc[0] = 100 * mean(hit)
  * (fixed shift 1: |l| <= 1 for unit vectors, so no running max is needed.)
- *   q_pos   : [B,C] f32 unit rows (used as a bf16 hi+lo pair);
- *   queue   : [C,K] f32, read once by TMA and converted on chip to a bf16 operand image
- *   z : [B] f32; g : [B,C] f32
- *   scratch : cp2_global_scratch_floats(B,C) f32
- * C == 128, K % 4 == 0, queue 16-byte aligned. */
-int64_t cp2_global_scratch_floats(int B, int C);
-int cp2_global_nce(const float *q_pos, const float *queue, float *z, float *g, float *scratch,
-                   float inv_tau, int B, int C, int K, void *stream);
+ *   q_pos    : [B,C] f32 unit rows (used as a bf16 hi+lo pair)
+ *   queue_bf : [K,C] bf16, the entry-major SHADOW of the queue (cp2_queue_shadow / cp2_enqueue keep it in
+ *              step with the fp32 buffer); the only queue bytes the pass streams (TMA, 128-byte swizzle)
+ *   queue    : [C,K] f32 (the checkpointed buffer) — read only for the few entries whose bf16 logit lies
+ *              within 3e-3 of l_pos, which are re-scored exactly in fp32; may be NULL when k_pos is NULL
+ *   k_pos    : [B,C] f32 or NULL (no accuracy meter; hit / acc untouched)
+ *   q_neg, k_neg : [B,C] f32 or both NULL (include_background, builder.py:1414-1418)
+ *   z : [B] f32; g : [B,C] f32; hit : [B] f32; acc : [1] f32
+ *   scratch  : cp2_global_scratch_bytes(B,C) bytes, 8-byte aligned, PERSISTENT: all zero before the first
+ *              call and left all zero by every call (fixed-point accumulators of the deterministic
+ *              cross-CTA reduction + the done counter); one scratch per concurrently running stream.
+ * C in {128, 256}; any K > 0; 0 < inv_tau <= 16; queue_bf 16-byte aligned. */
+int64_t cp2_global_scratch_bytes(int B, int C);
+int cp2_queue_shadow(const float *queue, void *queue_bf, int C, int K, void *stream);
+int cp2_global_nce(const float *q_pos, const void *queue_bf, const float *queue, const float *k_pos,
+                   const float *q_neg, const float *k_neg, float *z, float *g, float *hit, float *acc,
+                   void *scratch, float inv_tau, int B, int C, int K, void *stream);
 
 /* a5/a7/a12 glue — the [B,C] / [B]-sized remainder of the CP2 loss in two launches.
  * Replaces builder.py:1395 (l_pos), :1414-1418 (background logits), :1428 (cross entropy at the
@@ -130,7 +158,7 @@ int cp2_global_nce(const float *q_pos, const float *queue, float *z, float *g, f
 int cp2_loss_combine(const float *q_pos, const float *k_pos, const float *q_neg, const float *k_neg,
                      const float *sq, const float *sk, const float *norms_q, const float *z, const float *G,
                      const float *lse, const int32_t *key_count, const float *mask_a, const float *dense_n,
-                     float *out, float *l_pos, float *alpha, float *v1, float *v2, float *scratch, float inv_tau_global,
+                     float *out, float *l_pos, float *alpha, float *v1, float *v2, float *scratch, void *scratch_counter, float inv_tau_global,
                      float inv_tau_dense, float lmbd_dense, int B, int C, int P, void *stream);
 
 /* K4 — momentum (EMA) update of the key encoder, all parameters in one launch.
@@ -145,14 +173,17 @@ int cp2_ema(const float *const *q_ptrs, float *const *k_ptrs, const int64_t *num
             const int32_t *chunk_tensor, const int32_t *chunk_index, int n_chunks, float m,
             float one_minus_m, void *stream);
 
-/* K5 — queue enqueue of the all-gathered keys with wrap-around, device-side pointer.
+/* K5 — queue enqueue of the all-gathered keys with wrap-around, device-side pointer, ONE launch.
  * Replaces builder.py:574-587 (int(queue_ptr) D2H sync, 1-2 transposed slice writes,
  * pointer update).  The all-gather itself (builder.py:1710-1722) is issued by the
  * caller as one ncclAllGather into keys_all on the same stream.
  *   keys_all : [n,C] f32 ; queue : [C,K] f32 ; queue_ptr : [1] int64 (read, then advanced)
- * Bit-exact with the reference (n <= K). */
-int cp2_enqueue(const float *keys_all, float *queue, int64_t *queue_ptr, int n, int C, int K,
-                void *stream);
+ *   queue_bf : NULL, or the [K,C] bf16 shadow cp2_global_nce streams: rows (ptr+i) mod K are rewritten too
+ *   scratch_counter : 4 bytes, PERSISTENT: zero before the first call, left zero by every call (done
+ *              counter of "the last CTA to have read the pointer advances it")
+ * queue and queue_ptr bit-exact with the reference (n <= K). */
+int cp2_enqueue(const float *keys_all, float *queue, void *queue_bf, int64_t *queue_ptr, void *scratch_counter,
+                int n, int C, int K, void *stream);
 
 /* a2 + a4 — sub-sampled id maps and their (masked) correlation IoU.
  * Replaces builder.py:1165-1186 (the `[OS/2::OS]` subsample of the id maps) and
@@ -257,16 +288,6 @@ int cp2_dense_weighted_grad(const void *qhat_t, const void *khat_t, const float 
 int64_t cp2_dense_top1_scratch_floats(int B, int P);
 int cp2_dense_top1(const float *q, const float *k, const float *mask_a, const float *mask_b, float *hit,
                    float *acc, float *scratch, int B, int C, int P, void *stream);
-
-/* f4 — acc_ins (top-1) without the [B,1+K] logits.  Replaces builder.py:1441 / _accuracy :1690-1706 for k=1:
- *   hit[n] = 1 if q_pos[n].k_pos[n] > max(max_k q_pos[n].queue[:,k], q_pos[n].q_neg[n], q_pos[n].k_neg[n])
- *   (the last two only when q_neg/k_neg are given: include_background); acc[0] = 100 * mean_n hit[n].
- * Reads the queue BEFORE this step's enqueue, like the reference.  scratch:
- * cp2_global_top1_scratch_floats(B,K) f32. */
-int64_t cp2_global_top1_scratch_floats(int B, int K);
-int cp2_global_top1(const float *q_pos, const float *k_pos, const float *q_neg, const float *k_neg,
-                    const float *queue, float *hit, float *acc, float *scratch, int B, int C, int K,
-                    void *stream);
 
 /* f2 — ContrastiveHead (builder.py:150-176) for N rows against a queue, given cp2_global_nce's z [N], G [N,C]
  * for those rows: the global loss of forward_densecl (builder.py:762-775; N = B) and its local loss

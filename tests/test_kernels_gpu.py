@@ -286,16 +286,17 @@ def test_dense_grad_compact_equals_masked(ops, C, P):
 
 
 # --------------------------------------------------------------------------- K3
-@pytest.mark.parametrize("B,K,tau", [(32, 65536, 0.2), (4, 4096, 0.2), (2, 1024, 0.07), (64, 8192, 0.2),
-                                     (100, 4096, 0.2), (7, 1000, 0.2), (1, 256, 1.0)])
-def test_global_nce_vs_oracle(ops, B, K, tau):
-    C = 128
+@pytest.mark.parametrize("B,K,tau,C", [(32, 65536, 0.2, 128), (4, 4096, 0.2, 128), (2, 1024, 0.07, 128),
+                                       (64, 8192, 0.2, 128), (100, 4096, 0.2, 128), (7, 1000, 0.2, 128),
+                                       (1, 256, 1.0, 128), (32, 65536, 0.2, 256), (5, 1000, 0.2, 256),
+                                       (40, 300, 0.2, 256), (3, 100, 0.2, 128)])
+def test_global_nce_vs_oracle(ops, B, K, tau, C):
     g = torch.Generator().manual_seed(B + K)
     qp = torch.nn.functional.normalize(torch.randn(B, C, generator=g), dim=1)
     queue = torch.nn.functional.normalize(torch.randn(C, K, generator=g), dim=0)
     e = torch.exp((qp.double() @ queue.double() - 1.0) / tau)
     z_ref, g_ref = e.sum(dim=1), e @ queue.double().T
-    z, gg = ops.global_nce(dev(qp), dev(queue), 1.0 / tau)
+    z, gg = ops.global_nce(dev(qp), dev(queue), 1.0 / tau)[:2]
     torch.cuda.synchronize()
     # TF32 operands (10-bit mantissa): logits off by <~1e-3 -> e off by <~1e-3/tau relative
     assert torch.allclose(z.double().cpu(), z_ref, rtol=2e-3 / tau * 0.2 + 1e-3), (z.cpu(), z_ref)
@@ -304,12 +305,12 @@ def test_global_nce_vs_oracle(ops, B, K, tau):
 
 def test_global_nce_vs_simt(ops):
     from cp2_b200 import _lib
-    lib = _lib.load()
+    lib = _lib.load_debug()
     B, C, K = 32, 128, 65536
     g = torch.Generator().manual_seed(0)
     qp = dev(torch.nn.functional.normalize(torch.randn(B, C, generator=g), dim=1))
     queue = dev(torch.nn.functional.normalize(torch.randn(C, K, generator=g), dim=0))
-    z, gg = ops.global_nce(qp, queue, 5.0)
+    z, gg = ops.global_nce(qp, queue, 5.0)[:2]
     z2, g2 = torch.empty_like(z), torch.empty_like(gg)
     _lib.check(lib.cp2_dbg_global_nce_simt(qp.data_ptr(), queue.data_ptr(), z2.data_ptr(), g2.data_ptr(), 5.0,
                                            B, C, K, torch.cuda.current_stream().cuda_stream), "simt")
@@ -402,3 +403,29 @@ def test_global_top1_vs_oracle(ops, B, K, bg):
                                k_neg.cuda() if bg else None)
     assert torch.equal(hit.cpu(), want)
     np.testing.assert_allclose(acc.item(), O.topk_accuracy(logits, topk=(1,))[0].item(), rtol=1e-6)
+
+
+def test_global_top1_near_ties_are_rescored_exactly(ops):
+    """Queue entries whose logit lies within the bf16 error band of l_pos (|l_k - l_pos| ~ 1e-5 .. 1e-3, on either
+    side) must be decided by their exact fp32 logits, not by the bf16 operand the tensor cores see."""
+    B, C, K = 16, 128, 4096
+    g = torch.Generator().manual_seed(3)
+    nrm = torch.nn.functional.normalize
+    queue = nrm(torch.randn(C, K, generator=g), dim=0) * 1.0
+    q_pos = nrm(torch.randn(B, C, generator=g), dim=1)
+    k_pos = nrm(q_pos * 2.0 + torch.randn(B, C, generator=g) * 0.1, dim=1)       # l_pos ~ 0.99 > every random negative
+    l_pos = (q_pos * k_pos).sum(1)
+    deltas = torch.tensor([3e-5, -3e-5, 2e-4, -2e-4, 8e-4, -8e-4, 2e-3, -2e-3] * 2)
+    for b in range(B):
+        # an entry u = unit vector with q_pos[b].u = l_pos[b] + delta: rotate k_pos[b] inside span(q, k)
+        target = float(l_pos[b] + deltas[b])
+        perp = nrm(k_pos[b] - l_pos[b] * q_pos[b], dim=0)
+        u = target * q_pos[b] + (1.0 - target * target) ** 0.5 * perp
+        queue[:, 37 + 101 * b] = u
+    logits = O.global_logits(q_pos.double(), k_pos.double(), queue.double())
+    want = (logits.argmax(dim=1) == 0).float()
+    assert 0 < want.sum() < B
+    margin = (logits[:, 1:].max(dim=1).values - logits[:, 0]).abs()
+    assert float(margin.min()) > 1e-5                       # decidable in fp32
+    acc, hit = ops.global_top1(q_pos.cuda(), k_pos.cuda(), queue.cuda())
+    assert torch.equal(hit.cpu(), want), (hit.cpu(), want, margin)

@@ -38,8 +38,10 @@ def test_loss_golden_p196(ops, tag):
     q = T(g["q"]).cuda().requires_grad_(True)
     loss, li, ld, k_pos, q_pos, st = ops.cp2_loss(
         q, T(g["k"]).cuda(), mask_a.cuda(), mask_b.cuda(), T(g["queue0"]).cuda(),
-        float(g["temp_global"]), float(g["temp_local"]), float(g["lmbd"]), bool(g["include_background"]))
+        float(g["temp_global"]), float(g["temp_local"]), float(g["lmbd"]), bool(g["include_background"]),
+        track_accuracy=True)
     loss.backward()
+    np.testing.assert_allclose(st["acc_ins"].item(), g["acc_ins"], atol=1e-3)   # from the loss's own queue pass
     # the reference's own accuracy meters (builder.py:1441-1448) from the two arg-max kernels
     bg = bool(g["include_background"])
     acc_ins, _ = ops.global_top1(q_pos, k_pos, T(g["queue0"]).cuda(), st["q_neg"] if bg else None,
@@ -72,23 +74,20 @@ def test_loss_vs_oracle(ops, B, C, hw, K, tl, bg):
     r = O.cp2_loss(qr, k, ma, mb, queue, 0.2, tl, 0.2, include_background=bg)
     (r["loss"] * 1.7).backward()
     qd = q.cuda().requires_grad_(True)
-    if C == 128:
-        loss, li, ld, k_pos, q_pos, st = ops.cp2_loss(qd, k.cuda(), ma.cuda(), mb.cuda(), queue.cuda(), 0.2, tl,
-                                                      0.2, bg)
-        (loss * 1.7).backward()
-        # the cross-image std meters (builder.py:1553-1563: q_pos.std(0).mean()) and l_pos come out of the same kernel
-        np.testing.assert_allclose(st["std_q_pos"].item(), r["q_pos"].detach().std(0).mean().item(), rtol=1e-4)
-        np.testing.assert_allclose(st["std_k_pos"].item(), r["k_pos"].std(0).mean().item(), rtol=1e-4)
-        assert torch.allclose(st["l_pos"].cpu(), (r["q_pos"].detach() * r["k_pos"]).sum(1), rtol=1e-4, atol=1e-6)
-        np.testing.assert_allclose(loss.item(), r["loss"].item(), rtol=LOSS_RTOL)
-        np.testing.assert_allclose(li.item(), r["loss_ins"].item(), rtol=LOSS_RTOL)
-        np.testing.assert_allclose(ld.item(), r["loss_dense"].item(), rtol=LOSS_RTOL)
-        assert torch.allclose(k_pos.cpu(), r["k_pos"], rtol=1e-5, atol=1e-6)
-        assert torch.allclose(q_pos.cpu(), r["q_pos"].detach(), rtol=1e-5, atol=1e-6)
-        assert rel_l2(qd.grad, qr.grad) < GRAD_REL_L2, rel_l2(qd.grad, qr.grad)
-    else:
-        with pytest.raises(RuntimeError):
-            ops.cp2_loss(qd, k.cuda(), ma.cuda(), mb.cuda(), queue.cuda(), 0.2, tl, 0.2, bg)
+    loss, li, ld, k_pos, q_pos, st = ops.cp2_loss(qd, k.cuda(), ma.cuda(), mb.cuda(), queue.cuda(), 0.2, tl,
+                                                  0.2, bg, track_accuracy=True)
+    (loss * 1.7).backward()
+    # the cross-image std meters (builder.py:1553-1563: q_pos.std(0).mean()) and l_pos come out of the same kernel
+    np.testing.assert_allclose(st["std_q_pos"].item(), r["q_pos"].detach().std(0).mean().item(), rtol=1e-4)
+    np.testing.assert_allclose(st["std_k_pos"].item(), r["k_pos"].std(0).mean().item(), rtol=1e-4)
+    assert torch.allclose(st["l_pos"].cpu(), (r["q_pos"].detach() * r["k_pos"]).sum(1), rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(loss.item(), r["loss"].item(), rtol=LOSS_RTOL)
+    np.testing.assert_allclose(li.item(), r["loss_ins"].item(), rtol=LOSS_RTOL)
+    np.testing.assert_allclose(ld.item(), r["loss_dense"].item(), rtol=LOSS_RTOL)
+    assert torch.allclose(k_pos.cpu(), r["k_pos"], rtol=1e-5, atol=1e-6)
+    assert torch.allclose(q_pos.cpu(), r["q_pos"].detach(), rtol=1e-5, atol=1e-6)
+    assert rel_l2(qd.grad, qr.grad) < GRAD_REL_L2, rel_l2(qd.grad, qr.grad)
+    np.testing.assert_allclose(st["acc_ins"].item(), r["acc1"].item(), atol=1e-3)   # meter of the same queue pass
 
 
 def test_dense_loss_linearity_full_size(ops):
