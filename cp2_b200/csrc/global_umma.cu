@@ -65,6 +65,8 @@ struct GlobalScratch {                  // views into the caller's persistent sc
   long long *acc_z;                     // [chunks*NB]
   long long *acc_g;                     // [chunks*NB*C]
   int *miss;                            // [chunks*NB]
+  float *lpos;                          // [chunks*NB] exact l_pos (written by the first CTA of a chunk; no zeroing needed)
+  float *lbg;                           // [chunks*NB] max of the two background logits (or -3e38)
   unsigned int *counter;                // [1]
 };
 
@@ -132,18 +134,31 @@ global_nce_kernel(const __grid_constant__ CUtensorMap tm_q, const float *__restr
   }
   // exact fp32 positive logits and the two decision thresholds of the top-1 test
   for (int r = warp; r < NB; r += NTHREADS / 32) {
-    float lp = 0.f;
-    if (want_acc && b0 + r < B)
-      for (int c = lane; c < C; c += 32)
-        lp = fmaf(q_pos[(long long)(b0 + r) * C + c], k_pos[(long long)(b0 + r) * C + c], lp);
+    float lp = 0.f, lq = 0.f, lk = 0.f;
+    const bool on = want_acc && b0 + r < B;
+    if (on) {
+      const long long ro = (long long)(b0 + r) * C;
+      for (int c = lane; c < C; c += 32) {
+        const float qv = q_pos[ro + c];
+        lp = fmaf(qv, k_pos[ro + c], lp);
+        if (q_neg) { lq = fmaf(qv, q_neg[ro + c], lq); lk = fmaf(qv, k_neg[ro + c], lk); }
+      }
+    }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) lp += __shfl_xor_sync(0xffffffffu, lp, o);
+    for (int o = 16; o > 0; o >>= 1) {
+      lp += __shfl_xor_sync(0xffffffffu, lp, o);
+      lq += __shfl_xor_sync(0xffffffffu, lq, o);
+      lk += __shfl_xor_sync(0xffffffffu, lk, o);
+    }
     if (lane == 0) {
-      const bool on = want_acc && b0 + r < B;
       lpos[r] = lp;
       lhi[r] = on ? lp + MARGIN : 3.0e38f;       // logit >= lhi: certainly >= l_pos
       llo[r] = on ? lp - MARGIN : 3.0e38f;       // logit <  llo: certainly <  l_pos
       miss_s[r] = 0;
+      if (on && cta == 0) {                      // published once per chunk for the last CTA's finalisation
+        sc.lpos[chunk * NB + r] = lp;
+        sc.lbg[chunk * NB + r] = q_neg ? fmaxf(lq, lk) : -3.0e38f;
+      }
     }
   }
   fence_proxy_async_smem();
@@ -309,33 +324,38 @@ global_nce_kernel(const __grid_constant__ CUtensorMap tm_q, const float *__restr
     if (*last_flag) {
       __threadfence();
       const int chunks = gridDim.y;
-      for (int idx = st; idx < chunks * NB * C; idx += 128) {
-        const int rr = idx / C, c = idx - rr * C;
-        const int b = (rr / NB) * ROWS + (rr % NB);
-        const long long v = __ldcg(sc.acc_g + idx);
-        sc.acc_g[idx] = 0;
-        if ((rr % NB) < ROWS && b < B) g[(long long)b * C + c] = __ll2float_rn(v) * UNFIX;
+      const int total = chunks * NB * C;
+      // batches of 8 independent L2 loads per thread: a handful of round trips instead of one per element
+      for (int base = 0; base < total; base += 128 * 8) {
+        long long v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int idx = base + u * 128 + st;
+          v[u] = idx < total ? __ldcg(sc.acc_g + idx) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int idx = base + u * 128 + st;
+          if (idx < total) {
+            const int rr = idx / C, c = idx - rr * C;
+            const int b = (rr / NB) * ROWS + (rr % NB);
+            sc.acc_g[idx] = 0;
+            if (b < B) g[(long long)b * C + c] = __ll2float_rn(v[u]) * UNFIX;
+          }
+        }
       }
       float hits = 0.f;
       for (int rr = st; rr < chunks * NB; rr += 128) {
         const int b = (rr / NB) * ROWS + (rr % NB);
         const long long v = __ldcg(sc.acc_z + rr);
         const int ms = __ldcg(sc.miss + rr);
+        const float lp = __ldcg(sc.lpos + rr), lb = __ldcg(sc.lbg + rr);
         sc.acc_z[rr] = 0;
         sc.miss[rr] = 0;
-        if ((rr % NB) < ROWS && b < B) {
+        if (b < B) {
           z[b] = __ll2float_rn(v) * UNFIX;
           if (want_acc) {
-            float lp = 0.f, lq = -3.0e38f, lk = -3.0e38f;
-            for (int c = 0; c < C; ++c) lp = fmaf(q_pos[(long long)b * C + c], k_pos[(long long)b * C + c], lp);
-            if (q_neg) {
-              lq = 0.f; lk = 0.f;
-              for (int c = 0; c < C; ++c) {
-                lq = fmaf(q_pos[(long long)b * C + c], q_neg[(long long)b * C + c], lq);
-                lk = fmaf(q_pos[(long long)b * C + c], k_neg[(long long)b * C + c], lk);
-              }
-            }
-            const float h = (!ms && lp > fmaxf(lq, lk)) ? 1.f : 0.f;
+            const float h = (!ms && lp > lb) ? 1.f : 0.f;
             hit[b] = h;
             hits += h;
           }
@@ -403,7 +423,9 @@ GlobalScratch carve_scratch(void *scratch, int chunks, int NB, int C) {
   sc.acc_z = static_cast<long long *>(scratch);
   sc.acc_g = sc.acc_z + (size_t)chunks * NB;
   sc.miss = reinterpret_cast<int *>(sc.acc_g + (size_t)chunks * NB * C);
-  sc.counter = reinterpret_cast<unsigned int *>(sc.miss + (size_t)chunks * NB);
+  sc.lpos = reinterpret_cast<float *>(sc.miss + (size_t)chunks * NB);
+  sc.lbg = sc.lpos + (size_t)chunks * NB;
+  sc.counter = reinterpret_cast<unsigned int *>(sc.lbg + (size_t)chunks * NB);
   return sc;
 }
 
@@ -425,7 +447,7 @@ int launch_global(const CUtensorMap &tq, const float *q_pos, const float *queue,
 extern "C" int64_t cp2_global_scratch_bytes(int B, int C) {
   if (B <= 0) return 16;
   const int64_t rows = (int64_t)cp2_cdiv(B, ROWS) * pick_nb(B);
-  return rows * 8 + rows * C * 8 + rows * 4 + 16;
+  return rows * 8 + rows * C * 8 + rows * 12 + 16;
 }
 
 extern "C" int cp2_queue_shadow(const float *queue, void *queue_bf, int C, int K, void *stream) {

@@ -2,7 +2,8 @@
 
 Build recipe for `oracle/_ref/`: byte-compiles the reference's own modules of the CP2
 pre-training path FROM THE SOURCES WHERE THEY LIE under /root/reference into sourceless
-`.pyc` files (the Python analogue of compiling a C reference into `oracle/_ref/*.so`).
+byte-code files `*.pycode` (a `.pyc` under another extension: the GPU-box snapshot drops `*.pyc`;
+the Python analogue of compiling a C reference into `oracle/_ref/*.so`).
 No reference source is copied into the repo; `oracle/_ref/` is git-ignored and is not
 gpurun-ignored, so the compiled modules travel to the GPU box, where
 `bench.py --impl reference` (CPU arm) and the `gpu_eager_baseline` leg import the
@@ -33,7 +34,7 @@ def build(reference_root="/root/reference", out=OUT, quiet=False):
         src = os.path.join(reference_root, rel)
         if not os.path.isfile(src):
             continue
-        dst = os.path.join(out, rel[:-3] + ".pyc")
+        dst = os.path.join(out, rel[:-3] + ".pycode")
         os.makedirs(os.path.dirname(dst), exist_ok=True)
         # unchecked-hash pyc: valid without the source file next to it (sourceless import)
         py_compile.compile(src, cfile=dst, dfile=rel, doraise=True,

@@ -35,9 +35,47 @@ def _find_reference():
         if os.path.isfile(os.path.join(root, "builder.py")):
             return root, "source"
     pyc = os.path.join(_HERE, "_ref")
-    if os.path.isfile(os.path.join(pyc, "builder.pyc")):
+    if os.path.isfile(os.path.join(pyc, "builder.pycode")):
         return pyc, "pyc"
     return None, None
+
+
+class _ByteCodeFinder:
+    """Meta-path finder for the sourceless byte-code modules of oracle/_ref (`<name>.pycode` =
+    a .pyc under another extension, packages as `<name>/__init__.pycode`, namespace dirs allowed)."""
+
+    def __init__(self, root):
+        self.root = root
+
+    def find_spec(self, fullname, path=None, target=None):
+        import importlib.machinery
+        import importlib.util
+        rel = os.path.join(self.root, *fullname.split("."))
+        if os.path.isfile(rel + ".pycode"):
+            return importlib.util.spec_from_loader(fullname, self, origin=rel + ".pycode")
+        if os.path.isfile(os.path.join(rel, "__init__.pycode")):
+            return importlib.util.spec_from_loader(fullname, self, origin=os.path.join(rel, "__init__.pycode"),
+                                                   is_package=True)
+        if os.path.isdir(rel) and any(f.endswith(".pycode") for f in os.listdir(rel)):
+            spec = importlib.machinery.ModuleSpec(fullname, self, is_package=True)      # namespace-like (tools/)
+            spec.origin = None
+            return spec
+        return None
+
+    def create_module(self, spec):
+        return None
+
+    def exec_module(self, module):
+        import marshal
+        origin = module.__spec__.origin
+        if module.__spec__.submodule_search_locations is not None:
+            module.__path__ = [os.path.join(self.root, *module.__name__.split("."))]
+        if origin is None:
+            return
+        with open(origin, "rb") as f:
+            data = f.read()
+        module.__file__ = origin
+        exec(marshal.loads(data[16:]), module.__dict__)                                # 16-byte pyc header
 
 
 REFERENCE_ROOT, REFERENCE_KIND = _find_reference()
@@ -126,10 +164,13 @@ def _install_stubs():
 def import_reference():
     """Returns the reference's `builder` module (unmodified source)."""
     if not reference_available():
-        raise RuntimeError("reference not found: neither /root/reference nor oracle/_ref/builder.pyc "
+        raise RuntimeError("reference not found: neither /root/reference nor oracle/_ref/builder.pycode "
                            "(run `python oracle/build_ref.py` where the reference tree exists)")
     _install_stubs()
-    if REFERENCE_ROOT not in sys.path:
+    if REFERENCE_KIND == "pyc":
+        if not any(isinstance(f, _ByteCodeFinder) for f in sys.meta_path):
+            sys.meta_path.insert(0, _ByteCodeFinder(REFERENCE_ROOT))
+    elif REFERENCE_ROOT not in sys.path:
         sys.path.insert(0, REFERENCE_ROOT)
     import builder  # the reference's builder.py
 

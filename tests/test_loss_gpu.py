@@ -168,11 +168,25 @@ def test_model_two_steps_against_reference_golden(monkeypatch):
         opt.step()
     assert model.loss_o.count == 2 * B and abs(model.loss_o.val - float(g["s1.loss"])) < 1e-3
     # region-id IoUs recorded per step (builder.py:1252-1257): identical id maps in both views -> IoU 1,
-    # one entry per image and step; reset_metrics clears them
+    # one entry per image and step; reset_metrics restarts the meters but, as in the reference
+    # (builder.py:1666-1688), not the IoU lists: those restart in the new-epoch branch (builder.py:1466,1486)
     assert len(model.correlation_ious) == 2 * B and len(model.masked_correlation_ious) == 2 * B
     assert all(v == 1.0 for v in model.correlation_ious)
     model.reset_metrics()
+    assert model.loss_o.count == 0 and len(model.correlation_ious) == 2 * B
+    logged = []
+    model.rank, model._logger = 0, logged.append            # rank 0 with a logger: the new-epoch branch logs
+    loss = model(img_a=T(g["s1.img_a"]).to(dev), img_b=T(g["s1.img_b"]).to(dev), bg0=T(g["s1.bg0"]).to(dev),
+                 bg1=T(g["s1.bg1"]).to(dev), visualize=False, step=2, new_epoch=True, pixel_ids_a=ids,
+                 pixel_ids_b=ids, region_ids_a=ids, region_ids_b=ids)
+    assert torch.isfinite(loss) and model.epoch == 1
     assert model.correlation_ious == [] and model.masked_correlation_ious == []
+    keys = set().union(*[set(d) for d in logged])
+    assert {"feature_space_non_zero_iou", "dense-heatmaps", "train/loss_step", "train/+ive_scores_step",
+            "step/instance_median_negative_scores"} <= keys, sorted(keys)
+    assert model.last_heatmap_grid.dim() == 2
+    out = model.on_train_epoch_end(3)
+    assert out["train/loss"] == pytest.approx(loss.item(), rel=1e-5) and model.loss_o.count == 0
 
 
 def test_loss_nan_hazard_matches_reference(ops):
