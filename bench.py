@@ -601,7 +601,7 @@ def algorithmic_work(batch, n_params, world):
         "cp2_dense_lse": ("tensor", 2.0 * batch * P * P * C),
         "cp2_dense_grad": ("tensor", 2.0 * batch * P * P * C),
         "cp2_dense_small": ("tensor", 4.0 * batch * P * P * C),
-        "cp2_dense_epilogue": ("hbm", batch * P * C * (4 + 2 + 4)),
+        "cp2_dense_small_bwd": ("hbm", batch * P * C * (4 + 2 + 4)),
         "cp2_dense_rescore": ("hbm", 2 * batch * C * P * 4),
         "cp2_global_nce": ("hbm", 4 * C * QUEUE + 8 * batch * C),
         "cp2_ema": ("hbm", 12 * n_params),

@@ -23,6 +23,9 @@ SIGNATURES = {
     "cp2_dense_lse": (c_int, [c_void_p] * 4 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_dense_pad": (c_int, [c_int]),
     "cp2_dense_grad": (c_int, [c_void_p] * 13 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_dense_small_ok": (c_int, [c_int, c_int]),
+    "cp2_dense_small": (c_int, [c_void_p] * 6 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_dense_small_bwd": (c_int, [c_void_p] * 10 + [c_int] * 3 + [c_void_p]),
     "cp2_loss_combine": (c_int, [c_void_p] * 20 + [c_float] * 3 + [c_int] * 3 + [c_void_p]),
     "cp2_global_scratch_bytes": (c_int64, [c_int, c_int]),
     "cp2_queue_shadow": (c_int, [c_void_p] * 2 + [c_int] * 2 + [c_void_p]),
@@ -53,7 +56,7 @@ DEBUG_SIGNATURES = {
 }
 
 EMA_CHUNK = 4096  # CP2_EMA_CHUNK
-ABI_VERSION = 7  # CP2_ABI_VERSION
+ABI_VERSION = 8  # CP2_ABI_VERSION
 
 _lib = None
 _dbg = None

@@ -121,43 +121,81 @@ global_nce_kernel(const __grid_constant__ CUtensorMap tm_q, const float *__restr
     }
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
-  // q_pos -> bf16 hi / lo operands (K-major, rows past B are zero)
-  for (int idx = threadIdx.x; idx < NB * (C / 2); idx += NTHREADS) {
-    const int row = idx / (C / 2), c = (idx % (C / 2)) * 2;
-    float2 v = make_float2(0.f, 0.f);
-    if (b0 + row < B) v = *reinterpret_cast<const float2 *>(q_pos + (long long)(b0 + row) * C + c);
-    const __nv_bfloat16 h0 = __float2bfloat16_rn(v.x), h1 = __float2bfloat16_rn(v.y);
-    const float l0 = v.x - __bfloat162float(h0), l1 = v.y - __bfloat162float(h1);
-    const uint32_t off = sw128_off(row, c, Cfg::QBOX);
-    *reinterpret_cast<uint32_t *>(sQh + off) = pack_bf16x2(__bfloat162float(h0), __bfloat162float(h1));
-    *reinterpret_cast<uint32_t *>(sQl + off) = pack_bf16x2(l0, l1);
-  }
-  // exact fp32 positive logits and the two decision thresholds of the top-1 test
-  for (int r = warp; r < NB; r += NTHREADS / 32) {
-    float lp = 0.f, lq = 0.f, lk = 0.f;
-    const bool on = want_acc && b0 + r < B;
-    if (on) {
-      const long long ro = (long long)(b0 + r) * C;
-      for (int c = lane; c < C; c += 32) {
-        const float qv = q_pos[ro + c];
-        lp = fmaf(qv, k_pos[ro + c], lp);
-        if (q_neg) { lq = fmaf(qv, q_neg[ro + c], lq); lk = fmaf(qv, k_neg[ro + c], lk); }
+  // q_pos -> bf16 hi / lo operands (K-major, rows past B are zero).  Every global load of the prologue is
+  // issued before the first use: one memory round trip instead of one per loop iteration.
+  {
+    constexpr int NPAIR = NB * (C / 2), NU = (NPAIR + NTHREADS - 1) / NTHREADS;
+    float2 v[NU];
+#pragma unroll
+    for (int u = 0; u < NU; ++u) {
+      const int idx = threadIdx.x + u * NTHREADS, row = idx / (C / 2), c = (idx % (C / 2)) * 2;
+      v[u] = make_float2(0.f, 0.f);
+      if (idx < NPAIR && b0 + row < B) v[u] = __ldg(reinterpret_cast<const float2 *>(q_pos + (long long)(b0 + row) * C + c));
+    }
+    // exact fp32 positive logits and the two decision thresholds of the top-1 test: item = (row, 32-channel
+    // segment), the segments of a row sit in adjacent lanes
+    constexpr int SEG = C / 32, NITEM = NB * SEG, NIT = (NITEM + NTHREADS - 1) / NTHREADS;
+    float lp[NIT], lq[NIT], lk[NIT];
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+      const int item = threadIdx.x + it * NTHREADS, r = item / SEG, seg = item % SEG;
+      lp[it] = lq[it] = lk[it] = 0.f;
+      if (want_acc && item < NITEM && b0 + r < B) {
+        const long long ro = (long long)(b0 + r) * C + seg * 32;
+        float4 a[8], bq[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          a[j] = __ldg(reinterpret_cast<const float4 *>(q_pos + ro) + j);
+          bq[j] = __ldg(reinterpret_cast<const float4 *>(k_pos + ro) + j);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          lp[it] = fmaf(a[j].x, bq[j].x, fmaf(a[j].y, bq[j].y, fmaf(a[j].z, bq[j].z, fmaf(a[j].w, bq[j].w, lp[it]))));
+        if (q_neg) {
+          float4 cq[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            bq[j] = __ldg(reinterpret_cast<const float4 *>(q_neg + ro) + j);
+            cq[j] = __ldg(reinterpret_cast<const float4 *>(k_neg + ro) + j);
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            lq[it] = fmaf(a[j].x, bq[j].x, fmaf(a[j].y, bq[j].y, fmaf(a[j].z, bq[j].z, fmaf(a[j].w, bq[j].w, lq[it]))));
+            lk[it] = fmaf(a[j].x, cq[j].x, fmaf(a[j].y, cq[j].y, fmaf(a[j].z, cq[j].z, fmaf(a[j].w, cq[j].w, lk[it]))));
+          }
+        }
       }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      lp += __shfl_xor_sync(0xffffffffu, lp, o);
-      lq += __shfl_xor_sync(0xffffffffu, lq, o);
-      lk += __shfl_xor_sync(0xffffffffu, lk, o);
+    for (int u = 0; u < NU; ++u) {
+      const int idx = threadIdx.x + u * NTHREADS, row = idx / (C / 2), c = (idx % (C / 2)) * 2;
+      if (idx < NPAIR) {
+        const __nv_bfloat16 h0 = __float2bfloat16_rn(v[u].x), h1 = __float2bfloat16_rn(v[u].y);
+        const float l0 = v[u].x - __bfloat162float(h0), l1 = v[u].y - __bfloat162float(h1);
+        const uint32_t off = sw128_off(row, c, Cfg::QBOX);
+        *reinterpret_cast<uint32_t *>(sQh + off) = pack_bf16x2(__bfloat162float(h0), __bfloat162float(h1));
+        *reinterpret_cast<uint32_t *>(sQl + off) = pack_bf16x2(l0, l1);
+      }
     }
-    if (lane == 0) {
-      lpos[r] = lp;
-      lhi[r] = on ? lp + MARGIN : 3.0e38f;       // logit >= lhi: certainly >= l_pos
-      llo[r] = on ? lp - MARGIN : 3.0e38f;       // logit <  llo: certainly <  l_pos
-      miss_s[r] = 0;
-      if (on && cta == 0) {                      // published once per chunk for the last CTA's finalisation
-        sc.lpos[chunk * NB + r] = lp;
-        sc.lbg[chunk * NB + r] = q_neg ? fmaxf(lq, lk) : -3.0e38f;
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+      const int item = threadIdx.x + it * NTHREADS, r = item / SEG, seg = item % SEG;
+#pragma unroll
+      for (int o = SEG / 2; o > 0; o >>= 1) {
+        lp[it] += __shfl_xor_sync(0xffffffffu, lp[it], o);
+        lq[it] += __shfl_xor_sync(0xffffffffu, lq[it], o);
+        lk[it] += __shfl_xor_sync(0xffffffffu, lk[it], o);
+      }
+      if (item < NITEM && seg == 0) {
+        const bool on = want_acc && b0 + r < B;
+        lpos[r] = lp[it];
+        lhi[r] = on ? lp[it] + MARGIN : 3.0e38f;       // logit >= lhi: certainly >= l_pos
+        llo[r] = on ? lp[it] - MARGIN : 3.0e38f;       // logit <  llo: certainly <  l_pos
+        miss_s[r] = 0;
+        if (on && cta == 0) {                          // published once per chunk for the last CTA's finalisation
+          sc.lpos[chunk * NB + r] = lp[it];
+          sc.lbg[chunk * NB + r] = q_neg ? fmaxf(lq[it], lk[it]) : -3.0e38f;
+        }
       }
     }
   }
@@ -325,16 +363,16 @@ global_nce_kernel(const __grid_constant__ CUtensorMap tm_q, const float *__restr
       __threadfence();
       const int chunks = gridDim.y;
       const int total = chunks * NB * C;
-      // batches of 8 independent L2 loads per thread: a handful of round trips instead of one per element
-      for (int base = 0; base < total; base += 128 * 8) {
-        long long v[8];
+      // batches of 16 independent L2 loads per thread: a handful of round trips instead of one per element
+      for (int base = 0; base < total; base += 128 * 16) {
+        long long v[16];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < 16; ++u) {
           const int idx = base + u * 128 + st;
           v[u] = idx < total ? __ldcg(sc.acc_g + idx) : 0;
         }
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < 16; ++u) {
           const int idx = base + u * 128 + st;
           if (idx < total) {
             const int rr = idx / C, c = idx - rr * C;
@@ -469,9 +507,10 @@ extern "C" int cp2_global_nce(const float *q_pos, const void *queue_bf, const fl
   CP2_REQUIRE(q_pos && queue_bf && z && g && scratch, "cp2_global_nce: null pointer");
   CP2_REQUIRE((k_pos == nullptr) || (queue && hit && acc), "cp2_global_nce: the top-1 meter needs queue, hit and acc");
   CP2_REQUIRE((q_neg == nullptr) == (k_neg == nullptr), "cp2_global_nce: q_neg and k_neg go together");
-  CP2_REQUIRE((reinterpret_cast<uintptr_t>(queue_bf) & 15u) == 0 && (reinterpret_cast<uintptr_t>(q_pos) & 7u) == 0 &&
-                  (reinterpret_cast<uintptr_t>(scratch) & 7u) == 0,
-              "cp2_global_nce: queue_bf must be 16-byte, q_pos and scratch 8-byte aligned");
+  CP2_REQUIRE((reinterpret_cast<uintptr_t>(queue_bf) & 15u) == 0 && (reinterpret_cast<uintptr_t>(q_pos) & 15u) == 0 &&
+                  (reinterpret_cast<uintptr_t>(k_pos) & 15u) == 0 && (reinterpret_cast<uintptr_t>(q_neg) & 15u) == 0 &&
+                  (reinterpret_cast<uintptr_t>(k_neg) & 15u) == 0 && (reinterpret_cast<uintptr_t>(scratch) & 7u) == 0,
+              "cp2_global_nce: queue_bf, q_pos, k_pos, q_neg, k_neg must be 16-byte, scratch 8-byte aligned");
   const int NB = pick_nb(B), chunks = cp2_cdiv(B, ROWS);
   CP2_REQUIRE(chunks <= 65535, "cp2_global_nce: B=%d too large", B);
   const int nctas = pick_nctas(K);

@@ -209,9 +209,42 @@ def dense_grad(qhat_t, khat_t, lse, mask_a, mask_b, inv_norm, alpha, v1, v2, inv
     return dq
 
 
+def dense_small_ok(C, P):
+    """True when the single-kernel path for maps that fit TMEM takes this shape (cp2_dense_small_ok)."""
+    return bool(_lib.load().cp2_dense_small_ok(int(C), int(P)))
+
+
+def dense_small(qhat_t, khat_t, inv_tau, key_count=None, mask_b=None):
+    """cp2_dense_small: column LSE and the P^2-sized part of the gradient in ONE launch (P <= 256).
+    -> (lse [B,P], acc [B,C,P]); acc[n,:,x] = sum_y on_y exp(S[x,y]/tau - lse[y]) khat[y,:]."""
+    _need_cuda(qhat_t, khat_t)
+    B, P, C = qhat_t.shape
+    dev = qhat_t.device
+    lse = torch.empty((B, P), device=dev, dtype=torch.float32)
+    acc = torch.empty((B, C, P), device=dev, dtype=torch.float32)
+    _call("cp2_dense_small", 1, _lib.load().cp2_dense_small, _ptr(qhat_t), _ptr(khat_t), _ptr(key_count), _ptr(mask_b),
+          _ptr(lse), _ptr(acc), float(inv_tau), B, C, P, _stream())
+    return lse, acc
+
+
+def dense_small_bwd(acc, qhat_t, mask_a, inv_norm, alpha, v1, v2, key_count=None, gscale=None):
+    """cp2_dense_small_bwd: rank-1 terms, upstream gradient (device scalar) and the F.normalize backward applied to
+    cp2_dense_small's acc -> dq [B,C,P] (what cp2_dense_grad's epilogue does)."""
+    B, P, C = qhat_t.shape
+    dq = torch.empty((B, C, P), device=qhat_t.device, dtype=torch.float32)
+    _call("cp2_dense_small_bwd", 1, _lib.load().cp2_dense_small_bwd, _ptr(acc), _ptr(qhat_t), _ptr(key_count),
+          _ptr(mask_a), _ptr(inv_norm), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(gscale), _ptr(dq), B, C, P, _stream())
+    return dq
+
+
 def dense_fwd_bwd(qhat_t, khat_t, key_count, mask_a, inv_norm, alpha, v1, v2, inv_tau, gscale=None):
     """Column LSE + gradient w.r.t. the query features of the dense loss in one call -> (lse [B,P], dq [B,C,P]).
-    The configs[3] microbench unit: cp2_dense_lse + cp2_dense_grad."""
+    The configs[3] microbench unit: cp2_dense_small + cp2_dense_small_bwd for maps that fit TMEM, else
+    cp2_dense_lse + cp2_dense_grad."""
+    B, P, C = qhat_t.shape
+    if dense_small_ok(C, P):
+        lse, acc = dense_small(qhat_t, khat_t, inv_tau, key_count)
+        return lse, dense_small_bwd(acc, qhat_t, mask_a, inv_norm, alpha, v1, v2, key_count=key_count, gscale=gscale)
     lse = dense_lse(qhat_t, khat_t, inv_tau, key_count)
     dq = dense_grad(qhat_t, khat_t, lse, mask_a, None, inv_norm, alpha, v1, v2, inv_tau, key_count=key_count,
                     gscale=gscale)
@@ -384,6 +417,8 @@ class CP2LossFunction(torch.autograd.Function):
     Only `loss` carries a gradient, and only to q (keys and queue are detached in the
     reference, builder.py:1271,1396).  Forward = cp2_prep_features2, cp2_global_nce, cp2_dense_lse,
     cp2_loss_combine (4 launches); backward = cp2_dense_grad alone, reading the upstream gradient from device memory.
+    Maps that fit TMEM (P <= 256): cp2_dense_small replaces cp2_dense_lse and already holds the P^2 part of the
+    gradient, the backward is the elementwise cp2_dense_small_bwd.
     No ATen arithmetic in between: torch only allocates the buffers.
     """
 
@@ -403,10 +438,14 @@ class CP2LossFunction(torch.autograd.Function):
         z, G, _, acc_ins = global_nce(q_pos, queue, 1.0 / tg, k_pos if track_accuracy else None,
                                       q_neg if (bg and track_accuracy) else None,
                                       k_neg if (bg and track_accuracy) else None, shadow=queue_shadow)
-        lse = dense_lse(qh, kh, 1.0 / tl, kcnt)                # column LSE on the tensor cores
+        ctx.small = dense_small_ok(C, qh.shape[1])
+        if ctx.small:                                          # map fits TMEM: LSE and the P^2 part of dq in one launch
+            lse, acc = dense_small(qh, kh, 1.0 / tl, kcnt)
+        else:
+            lse, acc = dense_lse(qh, kh, 1.0 / tl, kcnt), None  # column LSE on the tensor cores
         out, l_pos, alpha, v1, v2 = loss_combine(q_pos, k_pos, q_neg if bg else None, k_neg if bg else None,
                                                  sq, sk, norms_q, z, G, lse, kcnt, mask_a, tg, tl, lmbd_dense)
-        ctx.save_for_backward(qh, kh, lse, mask_a, kcnt, q_inv, alpha, v1, v2)
+        ctx.save_for_backward(qh, acc if ctx.small else kh, lse, mask_a, kcnt, q_inv, alpha, v1, v2)
         ctx.inv_tl = 1.0 / tl
         ctx.q_shape = q.shape
         loss, loss_ins, loss_dense, meters = out[0], out[1], out[2], out[3:]
@@ -421,7 +460,10 @@ class CP2LossFunction(torch.autograd.Function):
         g = g_loss.detach().reshape(1)
         if g.dtype != torch.float32 or not g.is_contiguous():
             g = g.float().contiguous()
-        dq = dense_grad(qh, kh, lse, mask_a, None, q_inv, alpha, v1, v2, ctx.inv_tl, key_count=kcnt, gscale=g)
+        if ctx.small:                                          # kh holds acc: nothing is recomputed
+            dq = dense_small_bwd(kh, qh, mask_a, q_inv, alpha, v1, v2, key_count=kcnt, gscale=g)
+        else:
+            dq = dense_grad(qh, kh, lse, mask_a, None, q_inv, alpha, v1, v2, ctx.inv_tl, key_count=kcnt, gscale=g)
         return (dq.reshape(ctx.q_shape),) + (None,) * 10
 
 

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CP2_ABI_VERSION 7
+#define CP2_ABI_VERSION 8
 
 #define CP2_OK 0
 #define CP2_E_INVALID (-1)      /* bad shape / null pointer / unsupported dim          */
@@ -111,6 +111,23 @@ int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int32_t *key_co
                    const float *mask_a, const float *mask_b, const float *inv_norm, const float *alpha,
                    const float *v1, const float *v2, const float *gscale, float *dq, float *scratch_nl,
                    float inv_tau, int B, int C, int P, void *stream);
+
+/* K2-small — the same loss for maps that fit one SM's tensor memory (P <= 256 at C = 128, P <= 128 at
+ * C = 256; 14x14 = 196 is the map configs[1] trains at): ONE launch gives the column log-sum-exp of the
+ * forward and the P^2-sized part of the gradient, so the backward recomputes nothing.
+ * Replaces builder.py:1289-1292, 1431-1437 and their autograd like cp2_dense_lse + cp2_dense_grad:
+ *   lse[n,y]   = log sum_x exp(S[x,y]*inv_tau)                               ([B,P] f32; 0 for y >= key_count[n])
+ *   acc[n,:,x] = sum_y on_y * exp(S[x,y]*inv_tau - lse[y]) * khat[y,:]        ([B,C,P] f32)
+ * cp2_dense_small_bwd then applies what cp2_dense_grad's epilogue applies (rank-1 terms, upstream
+ * gradient from device memory, F.normalize backward):
+ *   dq[n,:,x] = N_x( g * (alpha[n]*acc[n,:,x] + mask_a[x]*v1[n,:] + (1-mask_a[x])*v2[n,:]) )
+ * cp2_dense_small_ok(C, P) = 1 when the shape is taken by this path. */
+int cp2_dense_small_ok(int C, int P);
+int cp2_dense_small(const void *qhat_t, const void *khat_t, const int32_t *key_count, const float *mask_b,
+                    float *lse, float *acc, float inv_tau, int B, int C, int P, void *stream);
+int cp2_dense_small_bwd(const float *acc, const void *qhat_t, const int32_t *key_count, const float *mask_a,
+                        const float *inv_norm, const float *alpha, const float *v1, const float *v2,
+                        const float *gscale, float *dq, int B, int C, int P, void *stream);
 
 /* K3 — global MoCo InfoNCE against the negative queue: forward sums, backward sums and the top-1
  * accuracy meter in one launch and one pass over the queue.  Replaces builder.py:1396

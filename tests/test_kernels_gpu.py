@@ -285,6 +285,79 @@ def test_dense_grad_compact_equals_masked(ops, C, P):
     assert rel_l2(got[1:2], only_rank1) < 1e-5
 
 
+# ------------------------------------------------------------------ K2-small (maps that fit TMEM)
+@pytest.mark.parametrize("B,C,P,tau,bg", [(2, 128, 196, 0.2, False), (3, 128, 196, 1.0, True), (1, 128, 128, 0.2, True),
+                                          (2, 128, 50, 0.2, False), (2, 128, 256, 0.2, True), (1, 128, 129, 0.2, False),
+                                          (2, 128, 1, 0.2, False), (2, 256, 49, 0.2, True), (1, 256, 128, 1.0, False),
+                                          (33, 128, 196, 0.2, False)])
+def test_dense_small_vs_oracle(ops, B, C, P, tau, bg):
+    """cp2_dense_small + cp2_dense_small_bwd against the fp64 restatement of the lse / grad contracts."""
+    assert ops.dense_small_ok(C, P)
+    g = torch.Generator().manual_seed(P * 3 + C + B)
+    qh, kh = _unit_bf16(B, P, C, 50 + P), _unit_bf16(B, P, C, 51 + P)
+    ma = (torch.rand(B, P, generator=g) < 0.6).float()
+    mb = (torch.rand(B, P, generator=g) < 0.6).float()
+    inv_norm = torch.rand(B, P, generator=g) + 0.5
+    alpha = torch.rand(B, generator=g) + 0.1
+    v1 = torch.randn(B, C, generator=g) * 0.1
+    v2 = torch.randn(B, C, generator=g) * 0.1 if bg else None
+    lse_ref = _lse_ref(qh.float(), kh.float(), 1.0 / tau)
+    lse, acc = ops.dense_small(dev(qh), dev(kh), 1.0 / tau, mask_b=dev(mb))
+    gs = torch.tensor([0.75], device="cuda")
+    got = ops.dense_small_bwd(acc, dev(qh), dev(ma), dev(inv_norm), dev(alpha), dev(v1),
+                              None if v2 is None else dev(v2), gscale=gs)
+    torch.cuda.synchronize()
+    assert torch.allclose(lse.double().cpu(), lse_ref, rtol=0, atol=5e-5), float((lse.double().cpu() - lse_ref).abs().max())
+    ref = 0.75 * _grad_ref(qh.float(), kh.float(), lse_ref.float(), ma, mb, inv_norm, alpha, v1, v2, 1.0 / tau)
+    assert got.shape == (B, C, P)
+    err = rel_l2(got, ref)
+    assert err < 5e-3, err
+
+
+def test_dense_small_ok_shapes(ops):
+    assert ops.dense_small_ok(128, 196) and ops.dense_small_ok(128, 256) and ops.dense_small_ok(256, 128)
+    assert not ops.dense_small_ok(128, 257) and not ops.dense_small_ok(256, 196) and not ops.dense_small_ok(64, 100)
+
+
+@pytest.mark.parametrize("C,P", [(128, 196), (128, 250), (256, 100)])
+def test_dense_small_compact_matches_streaming_kernels(ops, C, P):
+    """Compacted keys + key_count: the single-kernel path equals cp2_dense_lse + cp2_dense_grad (same operands,
+    same bf16 rounding of P~) and the fp64 reference of the mask_b formulation; an image without foreground
+    keys keeps only the rank-1 terms."""
+    B, tau = 4, 0.2
+    g = torch.Generator().manual_seed(C + P)
+    feat_k = torch.randn(B, C, P, generator=g)
+    qh = _unit_bf16(B, P, C, 61)
+    ma = (torch.rand(B, P, generator=g) < 0.6).float()
+    mb = (torch.rand(B, P, generator=g) < 0.6).float()
+    mb[1] = 0.0                                           # no foreground key
+    mb[2] = 1.0                                           # every key
+    mb[3, 5:] = 0.0                                       # a handful of keys (one 16-row slice)
+    inv_norm = torch.rand(B, P, generator=g) + 0.5
+    alpha = torch.rand(B, generator=g) + 0.1
+    v1 = torch.randn(B, C, generator=g) * 0.1
+    v2 = torch.randn(B, C, generator=g) * 0.1
+    kh_full, _, _, _, _ = ops.prep_features(dev(feat_k), dev(mb))
+    kh_c, _, _, _, cnt = ops.prep_features(dev(feat_k), dev(mb), compact=True)
+    lse_s, acc = ops.dense_small(dev(qh), kh_c, 1.0 / tau, key_count=cnt)
+    got = ops.dense_small_bwd(acc, dev(qh), dev(ma), dev(inv_norm), dev(alpha), dev(v1), dev(v2), key_count=cnt)
+    lse_t = ops.dense_lse(dev(qh), kh_c, 1.0 / tau, cnt)
+    ref_t = ops.dense_grad(dev(qh), kh_c, lse_t, dev(ma), None, dev(inv_norm), dev(alpha), dev(v1), dev(v2),
+                           1.0 / tau, key_count=cnt)
+    torch.cuda.synchronize()
+    cn = cnt.cpu().tolist()
+    for b in range(B):
+        assert torch.allclose(lse_s[b, :cn[b]], lse_t[b, :cn[b]], rtol=0, atol=2e-5)
+        assert not lse_s[b, cn[b]:].any()
+    assert rel_l2(got, ref_t) < 2e-3, rel_l2(got, ref_t)
+    lse = _lse_ref(qh.float(), kh_full.float().cpu(), 1.0 / tau).float()
+    ref = _grad_ref(qh.float(), kh_full.float().cpu(), lse, ma, mb, inv_norm, alpha, v1, v2, 1.0 / tau)
+    assert rel_l2(got, ref) < 5e-3, rel_l2(got, ref)
+    only_rank1 = _grad_ref(qh[1:2].float(), kh_full[1:2].float().cpu(), lse[1:2], ma[1:2], mb[1:2], inv_norm[1:2],
+                           alpha[1:2] * 0, v1[1:2], v2[1:2], 1.0 / tau)
+    assert rel_l2(got[1:2], only_rank1) < 1e-5
+
+
 # --------------------------------------------------------------------------- K3
 @pytest.mark.parametrize("B,K,tau,C", [(32, 65536, 0.2, 128), (4, 4096, 0.2, 128), (2, 1024, 0.07, 128),
                                        (64, 8192, 0.2, 128), (100, 4096, 0.2, 128), (7, 1000, 0.2, 128),
