@@ -29,6 +29,19 @@ void cp2_set_error(const char *fmt, ...);
 
 #define CP2_LAUNCH_CHECK() CP2_CUDA(cudaGetLastError())
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is sticky per (function, device): set it on the first launch of a
+// kernel instantiation on each device instead of on every call (it is a driver round trip on the launch path).
+#define CP2_SMEM_ONCE(kern, bytes)                                                                        \
+  do {                                                                                                    \
+    static unsigned long long done_ = 0ull;                                                               \
+    int dev_ = 0;                                                                                         \
+    CP2_CUDA(cudaGetDevice(&dev_));                                                                       \
+    if (!((done_ >> (dev_ & 63)) & 1ull)) {                                                               \
+      CP2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)));    \
+      done_ |= 1ull << (dev_ & 63);                                                                       \
+    }                                                                                                     \
+  } while (0)
+
 static inline int cp2_cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 // SM count of the current device (cached per process; 148 on B200).

@@ -55,19 +55,8 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.y, xt = blockIdx.x;
-  const int cnt = key_count ? min(max(key_count[b], 0), P) : P;
-  const int nyt = (cnt + TILE - 1) / TILE;          // key tiles that carry loss terms (0, 1 or 2)
-  const int nch = (P + 31) / 32;                    // 32-column chunks of the query axis
-
-  if (nyt == 0) {                                   // no foreground key: no loss term, zero gradient part
-    if (xt == 0)
-      for (int y = threadIdx.x; y < P; y += SM_THREADS) lse[(long long)b * P + y] = 0.f;
-    const int x = xt * TILE + (threadIdx.x & 127);
-    if (threadIdx.x < 256 && x < P)
-      for (int c = threadIdx.x >> 7; c < C; c += 2) acc[((long long)b * C + c) * P + x] = 0.f;
-    return;
-  }
-
+  // both operand loads are requested before anything else (they do not depend on key_count): the memory round
+  // trip overlaps the key_count read, the TMEM allocation and the role dispatch
   if (threadIdx.x == 0) {
     mbar_init(bar_k, 1);
     mbar_init(bar_q, 1);
@@ -79,9 +68,28 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     mbar_init(&bar_p[1], 4);
     mbar_init(bar_d, 1);
     fence_barrier_init();
-    prefetch_tmap(&tm_q);
-    prefetch_tmap(&tm_k);
+    mbar_expect_tx(bar_k, oper);
+    for (int kb = 0; kb < C / 64; ++kb) tma_load_3d(sK + kb * box, &tm_k, bar_k, kb * 64, 0, b);
+    mbar_expect_tx(bar_q, oper);
+    for (int kb = 0; kb < C / 64; ++kb) tma_load_3d(sQ + kb * box, &tm_q, bar_q, kb * 64, 0, b);
   }
+  const int cnt = key_count ? min(max(key_count[b], 0), P) : P;
+  const int nyt = (cnt + TILE - 1) / TILE;          // key tiles that carry loss terms (0, 1 or 2)
+  const int nch = (P + 31) / 32;                    // 32-column chunks of the query axis
+
+  if (nyt == 0) {                                   // no foreground key: no loss term, zero gradient part
+    if (xt == 0)
+      for (int y = threadIdx.x; y < P; y += SM_THREADS) lse[(long long)b * P + y] = 0.f;
+    const int x = xt * TILE + (threadIdx.x & 127);
+    if (threadIdx.x < 256 && x < P)
+      for (int c = threadIdx.x >> 7; c < C; c += 2) acc[((long long)b * C + c) * P + x] = 0.f;
+    if (threadIdx.x == 0) {                         // the CTA's shared memory must outlive the copies in flight
+      mbar_wait(bar_k, 0);
+      mbar_wait(bar_q, 0);
+    }
+    return;
+  }
+
   if (warp == 1) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
@@ -91,12 +99,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   const int W = nyt * 64;                           // S2 columns per softmax-warp half
 
   if (warp == 0) {
-    if (lane == 0) {
-      mbar_expect_tx(bar_k, oper);
-      for (int kb = 0; kb < C / 64; ++kb) tma_load_3d(sK + kb * box, &tm_k, bar_k, kb * 64, 0, b);
-      mbar_expect_tx(bar_q, oper);
-      for (int kb = 0; kb < C / 64; ++kb) tma_load_3d(sQ + kb * box, &tm_q, bar_q, kb * 64, 0, b);
-    }
+    // (the two TMA loads were issued at the top of the kernel)
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     const uint32_t idesc1 = make_idesc(TILE, rows, FMT_BF16, FMT_BF16, MAJOR_K, MAJOR_K);
@@ -287,7 +290,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 }
 
 // Backward of the small path: dq[b,c,x] = F.normalize backward of  g * (alpha_b acc[b,c,x] + a_x (v1-v2)[c] + v2[c]).
-// CTA = 128 pixels x 4 channel groups; the per-pixel dot product goes through shared memory.
+// CTA = PX pixels x G groups of 32 channels (512 threads); the per-pixel dot product goes through shared memory.
 template <int C>
 __global__ void __launch_bounds__(512)
 dense_small_bwd_kernel(const float *__restrict__ acc, const __nv_bfloat16 *__restrict__ qhat,
@@ -295,54 +298,62 @@ dense_small_bwd_kernel(const float *__restrict__ acc, const __nv_bfloat16 *__res
                        const float *__restrict__ inv_norm, const float *__restrict__ alpha,
                        const float *__restrict__ v1, const float *__restrict__ v2,
                        const float *__restrict__ gscale, float *__restrict__ dq, int P) {
-  constexpr int CG = C / 4;
+  constexpr int CG = 32, G = C / CG, PX = 512 / G;
   __shared__ float sva[C], svb[C];
-  __shared__ float red[4][128];
-  const int b = blockIdx.y, px = threadIdx.x & 127, grp = threadIdx.x >> 7;
-  const int x = blockIdx.x * 128 + px;
+  __shared__ float red[G][PX];
+  const int b = blockIdx.y, px = threadIdx.x % PX, grp = threadIdx.x / PX;
+  const int x = blockIdx.x * PX + px;
   const bool valid = x < P;
-  const float gup = gscale ? __ldg(gscale) : 1.f;
-  const int cnt = key_count ? min(max(key_count[b], 0), P) : P;
-  const float al = cnt > 0 ? alpha[b] * gup : 0.f;
-  for (int c = threadIdx.x; c < C; c += 512) {
-    const float b2 = v2 ? v2[(long long)b * C + c] * gup : 0.f;
-    sva[c] = v1[(long long)b * C + c] * gup - b2;
-    svb[c] = b2;
-  }
-  __syncthreads();
-  const float a = valid ? mask_a[(long long)b * P + x] : 0.f;
-  const float inr = valid ? inv_norm[(long long)b * P + x] : 0.f;
+  // every global load of the thread is issued before the first barrier: one memory round trip
   const float *arow = acc + ((long long)b * C + grp * CG) * P + (valid ? x : 0);
   const uint4 *qrow = reinterpret_cast<const uint4 *>(qhat + ((long long)b * P + (valid ? x : 0)) * C + grp * CG);
-  float gq[CG];
+  float av[CG];
+  uint4 qv[CG / 8];
+#pragma unroll
+  for (int cl = 0; cl < CG; ++cl) av[cl] = __ldg(arow + (long long)cl * P);
+#pragma unroll
+  for (int u = 0; u < CG / 8; ++u) qv[u] = __ldg(qrow + u);
+  const float gup = gscale ? __ldg(gscale) : 1.f;
+  const int cnt = key_count ? min(max(__ldg(key_count + b), 0), P) : P;
+  const float al_raw = __ldg(alpha + b);
+  const float a = valid ? __ldg(mask_a + (long long)b * P + x) : 0.f;
+  const float inr = valid ? __ldg(inv_norm + (long long)b * P + x) : 0.f;
+  for (int c = threadIdx.x; c < C; c += 512) {
+    const float b2 = v2 ? __ldg(v2 + (long long)b * C + c) * gup : 0.f;
+    sva[c] = __ldg(v1 + (long long)b * C + c) * gup - b2;
+    svb[c] = b2;
+  }
+  const float al = cnt > 0 ? al_raw * gup : 0.f;
+  __syncthreads();
   float dot = 0.f;
 #pragma unroll
   for (int u = 0; u < CG / 8; ++u) {
-    const uint4 qv = __ldg(qrow + u);
-    const uint32_t qw[4] = {qv.x, qv.y, qv.z, qv.w};
+    const uint32_t qw[4] = {qv[u].x, qv[u].y, qv[u].z, qv[u].w};
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int cl = u * 8 + e, c = grp * CG + cl;
       const float qh = (e & 1) ? __uint_as_float(qw[e >> 1] & 0xffff0000u) : __uint_as_float(qw[e >> 1] << 16);
-      const float g = fmaf(al, valid ? __ldg(arow + (long long)cl * P) : 0.f, fmaf(a, sva[c], svb[c]));
-      gq[cl] = g;
+      const float g = fmaf(al, valid ? av[cl] : 0.f, fmaf(a, sva[c], svb[c]));
+      av[cl] = g;                                   // acc value is dead: keep the combined gradient in its place
       dot = fmaf(qh, g, dot);
     }
   }
   red[grp][px] = dot;
   __syncthreads();
-  const float ndot = -(red[0][px] + red[1][px] + red[2][px] + red[3][px]);
+  float dsum = 0.f;
+#pragma unroll
+  for (int k = 0; k < G; ++k) dsum += red[k][px];
+  const float ndot = -dsum;
   if (!valid) return;
   float *drow = dq + ((long long)b * C + grp * CG) * P + x;
 #pragma unroll
   for (int u = 0; u < CG / 8; ++u) {
-    const uint4 qv = __ldg(qrow + u);
-    const uint32_t qw[4] = {qv.x, qv.y, qv.z, qv.w};
+    const uint32_t qw[4] = {qv[u].x, qv[u].y, qv[u].z, qv[u].w};
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int cl = u * 8 + e;
       const float qh = (e & 1) ? __uint_as_float(qw[e >> 1] & 0xffff0000u) : __uint_as_float(qw[e >> 1] << 16);
-      drow[(long long)cl * P] = fmaf(qh, ndot, gq[cl]) * inr;
+      drow[(long long)cl * P] = fmaf(qh, ndot, av[cl]) * inr;
     }
   }
 }
@@ -371,11 +382,11 @@ extern "C" int cp2_dense_small(const void *qhat_t, const void *khat_t, const int
   dim3 grid(nxt, B);
   if (C == 128) {
     const size_t smem = SmallCfg<128>::smem(rows);
-    CP2_CUDA(cudaFuncSetAttribute(dense_small_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CP2_SMEM_ONCE(dense_small_kernel<128>, SmallCfg<128>::smem(256));
     dense_small_kernel<128><<<grid, SM_THREADS, smem, st>>>(tq, tk, key_count, mask_b, lse, acc, sl2, P, rows);
   } else {
     const size_t smem = SmallCfg<256>::smem(rows);
-    CP2_CUDA(cudaFuncSetAttribute(dense_small_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CP2_SMEM_ONCE(dense_small_kernel<256>, SmallCfg<256>::smem(128));
     dense_small_kernel<256><<<grid, SM_THREADS, smem, st>>>(tq, tk, key_count, mask_b, lse, acc, sl2, P, rows);
   }
   CP2_LAUNCH_CHECK();
@@ -390,7 +401,7 @@ extern "C" int cp2_dense_small_bwd(const float *acc, const void *qhat_t, const i
   if (B == 0) return CP2_OK;
   CP2_REQUIRE(acc && qhat_t && mask_a && inv_norm && alpha && v1 && dq, "cp2_dense_small_bwd: null pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  dim3 grid(cp2_cdiv(P, 128), B);
+  dim3 grid(cp2_cdiv(P, C == 128 ? 128 : 64), B);
   if (C == 128)
     dense_small_bwd_kernel<128><<<grid, 512, 0, st>>>(acc, static_cast<const __nv_bfloat16 *>(qhat_t), key_count,
                                                       mask_a, inv_norm, alpha, v1, v2, gscale, dq, P);

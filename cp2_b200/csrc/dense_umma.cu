@@ -518,7 +518,7 @@ int launch_lse(const CUtensorMap &tq, const CUtensorMap &tk, const int *key_coun
                int B, int P, cudaStream_t st) {
   constexpr int NST = 2;
   const size_t smem = lse_smem<C>(NST);
-  CP2_CUDA(cudaFuncSetAttribute(dense_lse_kernel<C, NST, PF, NSW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CP2_SMEM_ONCE((dense_lse_kernel<C, NST, PF, NSW>), smem);
   dim3 grid(cp2_cdiv(P, TILE), B);
   dense_lse_kernel<C, NST, PF, NSW><<<grid, 64 + 32 * NSW, smem, st>>>(tq, tk, key_count, lse, scale_log2, P);
   CP2_LAUNCH_CHECK();
@@ -532,7 +532,7 @@ int launch_grad(const CUtensorMap &tq, const CUtensorMap &tk, const void *qhat, 
                 int P_pad, cudaStream_t st) {
   using Cfg = GradCfg<C, TY, NST, NQ, ND>;
   auto kern = dense_grad_kernel<C, TY, NST, NQ, ND, PF>;
-  CP2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+  CP2_SMEM_ONCE(kern, Cfg::SMEM);
   const long long items = (long long)B * cp2_cdiv(P, TILE);
   const int grid = (int)(items < cp2_num_sms() ? items : cp2_num_sms());
   kern<<<grid, GRAD_THREADS, Cfg::SMEM, st>>>(tq, tk, static_cast<const __nv_bfloat16 *>(qhat), nl, key_count,

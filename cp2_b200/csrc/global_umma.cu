@@ -264,9 +264,9 @@ global_nce_kernel(const __grid_constant__ CUtensorMap tm_q, const float *__restr
     const int quad = warp & 3;
     const int row = quad * 32 + lane;               // tile row = queue entry within the tile
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
-    float zacc[NB];
+    float zacc[NB], thi[NB], tlo[NB];                // thresholds in registers: no loads / branches per element
 #pragma unroll
-    for (int j = 0; j < NB; ++j) zacc[j] = 0.f;
+    for (int j = 0; j < NB; ++j) { zacc[j] = 0.f; thi[j] = lhi[j]; tlo[j] = llo[j]; }
     for (int i = 0; i < my_tiles; ++i) {
       const int buf = i & 1, tph = (i >> 1) & 1, eb = i & 1;
       const int kg = (t0 + i) * KT + row;
@@ -289,12 +289,12 @@ global_nce_kernel(const __grid_constant__ CUtensorMap tm_q, const float *__restr
           e = kvalid ? e : 0.f;
           zacc[bb] += e;
           *reinterpret_cast<__nv_bfloat16 *>(sEb + sw128_off(bb, row, Cfg::QBOX)) = __float2bfloat16_rn(e);
-          if (kvalid) {
-            if (l >= lhi[bb]) certain |= 1u << bb;
-            else if (l >= llo[bb]) band |= 1u << bb;
-          }
+          certain |= (l >= thi[bb]) ? (1u << bb) : 0u;
+          band |= (l >= tlo[bb]) ? (1u << bb) : 0u;
         }
       }
+      if (!kvalid) certain = band = 0u;
+      band &= ~certain;
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
@@ -473,7 +473,7 @@ int launch_global(const CUtensorMap &tq, const float *q_pos, const float *queue,
                   void *scratch, float scale_log2, int B, int K, int nctas, int chunks, cudaStream_t st) {
   using Cfg = GCfg<C, NB>;
   auto kern = global_nce_kernel<C, NB>;
-  CP2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+  CP2_SMEM_ONCE(kern, Cfg::SMEM);
   kern<<<dim3(nctas, chunks), NTHREADS, Cfg::SMEM, st>>>(tq, q_pos, queue, k_pos, q_neg, k_neg, z, g, hit, acc,
                                                          carve_scratch(scratch, chunks, NB, C), scale_log2, B, K);
   CP2_LAUNCH_CHECK();

@@ -4,7 +4,7 @@
 // (algorithmic bytes 6*B*C*P).  A CTA owns 32 consecutive pixels of one image: the
 // loads are coalesced along P (128 B per warp per channel), the tile is transposed
 // through shared memory, and the stores are coalesced along C.  Pooled sums are
-// reduced per tile into scratch and summed over tiles by a second, tiny kernel in a
+// reduced per tile into scratch and summed over tiles by the last CTA of the image in a
 // fixed order (deterministic).
 #include "common.cuh"
 
@@ -29,6 +29,7 @@ __device__ void prep_reduce_image(const PrepSide &sd, int b, int C, int tiles, f
   for (int t = threadIdx.x; t < 2 * C; t += blockDim.x) {
     const float *p = sd.scratch + (long long)b * tiles * 2 * C + t;
     float s = 0.f;
+#pragma unroll 8
     for (int tl = 0; tl < tiles; ++tl) s += __ldcg(p + (long long)tl * 2 * C);
     sums[t] = s;
     if (t < C) { sd.pos_sum[(long long)b * C + t] = s; sq_pos = fmaf(s, s, sq_pos); }
@@ -127,18 +128,26 @@ prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, i
   }
   __syncthreads();
   {
-    const float d = den[lane], m = mk[lane];
+    const float d = den[lane];
+    for (int c = warp; c < C; c += 8) tile[c][lane] = tile[c][lane] / d;
+  }
+  __syncthreads();
+  {
+    // pooled sums of the tile: one thread per (channel, pos | neg) walks the 32 pixels in order (rows of `tile` are
+    // 33 floats apart: conflict-free), no shuffles
     float *__restrict__ part = scratch + ((long long)(b * tiles + tl) * 2) * C;
-    for (int c = warp; c < C; c += 8) {
-      const float v = tile[c][lane] / d;
-      tile[c][lane] = v;
-      float pos = v * m, neg = valid ? v * (1.0f - m) : 0.f;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        pos += __shfl_xor_sync(0xffffffffu, pos, o);
-        neg += __shfl_xor_sync(0xffffffffu, neg, o);
+    const int nv = min(PT, P - tl * PT);
+    for (int o = threadIdx.x; o < 2 * C; o += 256) {
+      const int c = o < C ? o : o - C;
+      float s = 0.f;
+      if (o < C) {
+#pragma unroll 8
+        for (int p = 0; p < nv; ++p) s = fmaf(tile[c][p], mk[p], s);
+      } else {
+#pragma unroll 8
+        for (int p = 0; p < nv; ++p) s = fmaf(tile[c][p], 1.0f - mk[p], s);
       }
-      if (lane == 0) { part[c] = pos; part[C + c] = neg; }
+      part[o] = s;
     }
   }
   __threadfence();                       // this tile's partial sums are visible before the done counter moves
