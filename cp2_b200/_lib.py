@@ -18,15 +18,15 @@ SIGNATURES = {
     "cp2_composite": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "cp2_composite2": (c_int, [c_void_p] * 10 + [c_int] * 4 + [c_void_p]),
     "cp2_prep_tiles": (c_int, [c_int]),
-    "cp2_prep_features": (c_int, [c_void_p] * 12 + [c_int] * 3 + [c_void_p]),
-    "cp2_prep_features2": (c_int, [c_void_p] * 22 + [c_int] * 3 + [c_void_p]),
+    "cp2_prep_features": (c_int, [c_void_p] * 13 + [c_int] * 3 + [c_void_p]),
+    "cp2_prep_features2": (c_int, [c_void_p] * 23 + [c_int] * 3 + [c_void_p]),
     "cp2_dense_lse": (c_int, [c_void_p] * 4 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_dense_pad": (c_int, [c_int]),
     "cp2_dense_grad": (c_int, [c_void_p] * 13 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_dense_small_ok": (c_int, [c_int, c_int]),
-    "cp2_dense_small": (c_int, [c_void_p] * 6 + [c_float] + [c_int] * 3 + [c_void_p]),
+    "cp2_dense_small": (c_int, [c_void_p] * 14 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_dense_small_bwd": (c_int, [c_void_p] * 10 + [c_int] * 3 + [c_void_p]),
-    "cp2_loss_combine": (c_int, [c_void_p] * 20 + [c_float] * 3 + [c_int] * 3 + [c_void_p]),
+    "cp2_loss_combine": (c_int, [c_void_p] * 21 + [c_float] * 3 + [c_int] * 3 + [c_void_p]),
     "cp2_global_scratch_bytes": (c_int64, [c_int, c_int]),
     "cp2_queue_shadow": (c_int, [c_void_p] * 2 + [c_int] * 2 + [c_void_p]),
     "cp2_global_nce": (c_int, [c_void_p] * 11 + [c_float] + [c_int] * 3 + [c_void_p]),

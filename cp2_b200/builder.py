@@ -380,10 +380,10 @@ class MODEL(nn.Module):
 
     @torch.no_grad()
     def _dense_accuracy(self, q, k, mask_a, mask_b, stats):
-        """builder.py:1442-1448: arg-max over all P x P dense logits (cp2_dense_top1; no [B,P,P] tensor, no host
-        sync).  In the PROPOSED modes the arg-max runs on the weighted logits inside cp2_dense_weighted_lse
-        (stats["acc_seg"]).  acc_ins (builder.py:1441) comes out of the loss's own queue pass (cp2_global_nce)."""
-        if self._weighted:
+        """builder.py:1442-1448: arg-max over all P x P dense logits (no [B,P,P] tensor, no host sync).  Maps that
+        fit TMEM: found by cp2_dense_small while S is on chip (stats["acc_seg"]); larger maps: cp2_dense_top1.
+        In the PROPOSED modes the arg-max runs on the weighted logits inside cp2_dense_weighted_lse.  acc_ins (builder.py:1441) comes out of the loss's own queue pass (cp2_global_nce)."""
+        if stats.get("acc_seg") is not None:                   # weighted modes / maps that fit TMEM: already there
             return stats["acc_seg"]
         return ops.dense_top1(q, k, mask_a, mask_b)[0]
 

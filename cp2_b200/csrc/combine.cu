@@ -30,9 +30,11 @@ __device__ __forceinline__ void block_sum(float (&v)[N], float *red /* [N][4] */
   for (int k = 0; k < N; ++k) v[k] = red[k * 4] + red[k * 4 + 1] + red[k * 4 + 2] + red[k * 4 + 3];
 }
 
-// out = {loss, loss_ins, loss_dense, mean_c std_b(q_pos), mean_c std_b(k_pos)}; fixed summation order.  128 threads.
+// out = {loss, loss_ins, loss_dense, mean_c std_b(q_pos), mean_c std_b(k_pos), acc_seg}; fixed summation order.
+// 128 threads.  acc_seg = 100 * mean(hit_seg) (builder.py:1442-1448) or NaN without hit_seg.
 __device__ void loss_finalize(const float *terms, const float *__restrict__ q_pos, const float *__restrict__ k_pos,
-                              float *__restrict__ out, float lmbd, int B, int C, float *red /* >= 8 floats */) {
+                              const float *hit_seg, float *__restrict__ out, float lmbd, int B, int C,
+                              float *red /* >= 8 floats */) {
   float sd[2] = {0.f, 0.f};
   for (int c = threadIdx.x; c < C; c += 128) {
 #pragma unroll
@@ -65,6 +67,13 @@ __device__ void loss_finalize(const float *terms, const float *__restrict__ q_po
     out[2] = d;
     out[3] = s0 / (float)C;
     out[4] = s1 / (float)C;
+    float hs = __int_as_float(0x7fc00000);
+    if (hit_seg) {
+      hs = 0.f;
+      for (int b = 0; b < B; ++b) hs += __ldcg(hit_seg + b);
+      hs *= 100.f / (float)B;
+    }
+    out[5] = hs;
   }
 }
 
@@ -76,7 +85,8 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
                     const float *__restrict__ norms_q, const float *__restrict__ z,
                     const float *__restrict__ G, const float *__restrict__ lse,
                     const int *__restrict__ key_count, const float *__restrict__ mask_a,
-                    const float *__restrict__ dense_n, float *__restrict__ terms, float *__restrict__ l_pos_out, float *__restrict__ alpha,
+                    const float *__restrict__ dense_n, const float *hit_seg, float *__restrict__ terms,
+                    float *__restrict__ l_pos_out, float *__restrict__ alpha,
                     float *__restrict__ v1, float *__restrict__ v2, float *__restrict__ out,
                     unsigned int *__restrict__ counter, float inv_tg, float inv_tl, float lmbd,
                     int B, int C, int P) {
@@ -150,7 +160,7 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
   __syncthreads();
   if (is_last) {                          // the last image's CTA sums the batch in a fixed order
     __threadfence();
-    loss_finalize(terms, q_pos, k_pos, out, lmbd, B, C, red);
+    loss_finalize(terms, q_pos, k_pos, hit_seg, out, lmbd, B, C, red);
   }
 }
 
@@ -159,7 +169,8 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
 extern "C" int cp2_loss_combine(const float *q_pos, const float *k_pos, const float *q_neg, const float *k_neg,
                                 const float *sq, const float *sk, const float *norms_q, const float *z,
                                 const float *G, const float *lse, const int32_t *key_count,
-                                const float *mask_a, const float *dense_n, float *out, float *l_pos, float *alpha, float *v1,
+                                const float *mask_a, const float *dense_n, const float *hit_seg, float *out,
+                                float *l_pos, float *alpha, float *v1,
                                 float *v2, float *scratch, void *scratch_counter, float inv_tau_global,
                                 float inv_tau_dense, float lmbd_dense, int B, int C, int P, void *stream) {
   CP2_REQUIRE(B > 0 && C > 0 && P > 0, "cp2_loss_combine: bad shape B=%d C=%d P=%d", B, C, P);
@@ -171,7 +182,7 @@ extern "C" int cp2_loss_combine(const float *q_pos, const float *k_pos, const fl
   CP2_REQUIRE(inv_tau_global > 0.f && inv_tau_dense > 0.f, "cp2_loss_combine: bad temperature");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   loss_combine_kernel<<<B, 128, 0, st>>>(q_pos, k_pos, q_neg, k_neg, sq, sk, norms_q, z, G, lse, key_count, mask_a,
-                                         dense_n, scratch, l_pos, alpha, v1, v2, out,
+                                         dense_n, hit_seg, scratch, l_pos, alpha, v1, v2, out,
                                          static_cast<unsigned int *>(scratch_counter), inv_tau_global, inv_tau_dense,
                                          lmbd_dense, B, C, P);
   CP2_LAUNCH_CHECK();

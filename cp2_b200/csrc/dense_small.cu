@@ -27,19 +27,35 @@ namespace {
 
 constexpr int SM_THREADS = 320;          // warp 0 TMA, warp 1 MMA + TMEM owner, warps 2-9 softmax / epilogue
 constexpr int PF_SMALL = 1;              // exponentials evaluated on the FMA pipe: 1 of every 4 column pairs
+constexpr float SEG_DELTA = 0.0078125f;  // acc_seg meter: candidate band below the bf16-operand maximum (2^-7)
+constexpr int SEG_MAXC = 64;             // ... and the most candidates re-scored per image
 
 template <int C>
 struct SmallCfg {
   static size_t smem(int rows) {
-    return 1024 + 2 * (size_t)(C / 64) * rows * 128 + 256 * 4 + 2 * 2 * 128 * 4 + 16 * 8 + 16;
+    return 1024 + 2 * (size_t)(C / 64) * rows * 128 + 256 * 4 + 2 * 2 * 128 * 4 + 16 * 8 + 16 + 32 * 4 + 16 +
+           SEG_MAXC * 4;
   }
+};
+
+// acc_seg meter (builder.py:1442-1448): arg-max over ALL pixel pairs of the image's similarity matrix, hit = label
+// of that pair.  The CTA xt = 0 of an image finds the largest bf16-operand S while it is in TMEM, collects every
+// pair within SEG_DELTA of it (the bound of the operands' bf16 rounding, both ways) and re-scores those exactly in
+// fp32 from the encoder outputs, so the decision is the fp32 reference's.
+struct SegMeter {
+  const float *q_f32, *k_f32;        // [B,C,P] encoder outputs (before normalisation)
+  const float *inv_q, *inv_k;        // [B,P] 1 / max(||.||, eps), pixel order
+  const int *perm_k;                 // [B,P] pixel of each key row, or NULL (rows in pixel order)
+  const float *mask_a, *mask_b;      // [B,P] labels' factors, pixel order
+  float *hit;                        // [B] OUT, NULL = meter off
 };
 
 template <int C>
 __global__ void __launch_bounds__(SM_THREADS, 1)
 dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                    const int *__restrict__ key_count, const float *__restrict__ mask_b,
-                   float *__restrict__ lse, float *__restrict__ acc, float scale_log2, int P, int rows) {
+                   float *__restrict__ lse, float *__restrict__ acc, const SegMeter seg, float scale_log2, int P,
+                   int rows) {
   const int box = rows * 128;                      // bytes of one (rows x 64 channels) swizzled TMA box
   const int oper = (C / 64) * box;
   extern __shared__ uint8_t smem_raw[];
@@ -52,6 +68,9 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   uint64_t *bar_k = bars, *bar_q = bars + 1, *bar_s1 = bars + 2 /* [2] */, *bar_free = bars + 4,
            *bar_s2 = bars + 5, *bar_p = bars + 6 /* [2] */, *bar_d = bars + 8;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16);
+  float *smax = reinterpret_cast<float *>(tmem_slot + 4);       // [8] per-warp maxima / [8][4] per-warp bests
+  int *ncand = reinterpret_cast<int *>(smax + 32);
+  int *cand = ncand + 4;                                        // [SEG_MAXC] (x << 16) | key row
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.y, xt = blockIdx.x;
@@ -67,6 +86,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     mbar_init(&bar_p[0], 4);
     mbar_init(&bar_p[1], 4);
     mbar_init(bar_d, 1);
+    *ncand = 0;
     fence_barrier_init();
     mbar_expect_tx(bar_k, oper);
     for (int kb = 0; kb < C / 64; ++kb) tma_load_3d(sK + kb * box, &tm_k, bar_k, kb * 64, 0, b);
@@ -84,6 +104,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     if (threadIdx.x < 256 && x < P)
       for (int c = threadIdx.x >> 7; c < C; c += 2) acc[((long long)b * C + c) * P + x] = 0.f;
     if (threadIdx.x == 0) {                         // the CTA's shared memory must outlive the copies in flight
+      if (seg.hit && xt == 0) seg.hit[b] = 0.f;     // every label of the image is 0
       mbar_wait(bar_k, 0);
       mbar_wait(bar_q, 0);
     }
@@ -97,6 +118,8 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   const uint32_t tmem = *tmem_slot;
   const uint32_t tmem_D = tmem + 256;
   const int W = nyt * 64;                           // S2 columns per softmax-warp half
+  const bool meter = seg.hit != nullptr && xt == 0;
+  const int nyt_s = meter ? rows / TILE : nyt;      // key tiles phase 1 looks at (the meter needs every key)
 
   if (warp == 0) {
     // (the two TMA loads were issued at the top of the kernel)
@@ -112,7 +135,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     mbar_wait(bar_q, 0);
     tc_fence_after();
     if (elect_one()) {
-      for (int yt = 0; yt < nyt; ++yt) {
+      for (int yt = 0; yt < nyt_s; ++yt) {
 #pragma unroll
         for (int kk = 0; kk < C / 16; ++kk) {
           const uint32_t off = (kk >> 2) * box + (kk & 3) * 32;
@@ -155,9 +178,9 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     const f2 scale2 = f2_pack(scale_log2, scale_log2);
     const int row = quad * 32 + lane;
     // ---- phase 1: units u = yt * nch + ch, first half of the list to half 0
-    const int U = nyt * nch, U0 = (U + 1) / 2;
+    const int U = nyt_s * nch, U0 = (U + 1) / 2;
     const int u_begin = half == 0 ? 0 : U0, u_end = half == 0 ? U0 : U;
-    float sum0 = 0.f, sum1 = 0.f;
+    float sum0 = 0.f, sum1 = 0.f, vmax = -INFINITY;
     {
       f2 acc_m = f2_pack(0.f, 0.f), acc_p = acc_m, acc_m2 = acc_m, acc_p2 = acc_m;
       float tail = 0.f;
@@ -177,7 +200,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
         const int yt = u / nch, ch = u - yt * nch;
         if (yt != cur) {
           flush();
-          if (cur == 0 && !freed) {                  // leaving key tile 0: its columns may be overwritten
+          if (cur == 0 && !freed && !meter) {        // leaving key tile 0: its columns may be overwritten
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_free);
@@ -198,16 +221,23 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
         const bool same_next = (u + 1 < u_end) && ((u + 1) / nch == yt);
         if (same_next) issue(u + 1, nxt);
         const int nvalid = min(32, P - ch * 32);
-        if (nvalid == 32) {
-          softmax_chunk_fwd<PF_SMALL>(now, scale2, acc_m, acc_m2, acc_p, acc_p2);
-        } else {
+        if (meter && yt * TILE + row < P) {          // running maximum of the raw similarities (valid pairs only)
 #pragma unroll
           for (int j = 0; j < 32; ++j)
-            if (j < nvalid) tail += ex2_approx(__uint_as_float(now[j]) * scale_log2);
+            if (j < nvalid) vmax = fmaxf(vmax, __uint_as_float(now[j]));
+        }
+        if (yt < nyt) {                              // tiles past the foreground keys only feed the meter
+          if (nvalid == 32) {
+            softmax_chunk_fwd<PF_SMALL>(now, scale2, acc_m, acc_m2, acc_p, acc_p2);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < nvalid) tail += ex2_approx(__uint_as_float(now[j]) * scale_log2);
+          }
         }
         if (!same_next && u + 1 < u_end) issue(u + 1, nxt);
       };
-      if (u_begin >= u_end || u_begin >= nch) {      // no unit of key tile 0 in this warp's share
+      if (!meter && (u_begin >= u_end || u_begin >= nch)) {   // no unit of key tile 0 in this warp's share
         if (lane == 0) mbar_arrive(bar_free);
         freed = true;
       }
@@ -217,7 +247,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
         if (u + 1 < u_end) step(u + 1, r1, r0);
       }
       flush();
-      if (!freed) {                                  // ended inside key tile 0, or had no unit of it
+      if (!freed && !meter) {                        // ended inside key tile 0, or had no unit of it
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_free);
@@ -225,7 +255,37 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     }
     part[(half * 2 + 0) * 128 + row] = sum0;
     part[(half * 2 + 1) * 128 + row] = sum1;
+    if (meter) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+      if (lane == 0) smax[warp - 2] = vmax;
+    }
     asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (meter) {
+      // second look at this warp's units (S^T is still in TMEM): every pair within SEG_DELTA of the maximum
+      float M = smax[0];
+#pragma unroll
+      for (int w = 1; w < 8; ++w) M = fmaxf(M, smax[w]);
+      const float thr = M - SEG_DELTA;
+      for (int u = u_begin; u < u_end; ++u) {
+        const int yt = u / nch, ch = u - yt * nch;
+        uint32_t rc[32];
+        tmem_ld32(tmem + lane_off + yt * 256 + ch * 32, rc);
+        tmem_wait_ld();
+        const int nvalid = min(32, P - ch * 32);
+        if (yt * TILE + row < P) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < nvalid && __uint_as_float(rc[j]) >= thr) {
+              const int slot = atomicAdd(ncand, 1);
+              if (slot < SEG_MAXC) cand[slot] = ((ch * 32 + j) << 16) | (yt * TILE + row);
+            }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_free);
+    }
     if (half < nyt) {                                // half h finishes key tile h
       const int y = half * 128 + row;
       const float lg = log2f(part[(0 * 2 + half) * 128 + row] + part[(1 * 2 + half) * 128 + row]);
@@ -281,6 +341,53 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) dst[(long long)(c0 + j) * P] = __uint_as_float(r[j]);
         }
+      }
+    }
+    // ---- acc_seg: exact fp32 score of the candidates (the list is complete: every warp passed the nl barrier)
+    if (meter) {
+      const int n = min(*reinterpret_cast<volatile int *>(ncand), SEG_MAXC);
+      float bestv = -INFINITY;
+      int bestf = 0x7fffffff, bestx = 0, besty = 0, bestr = 0;
+      for (int i = warp - 2; i < n; i += 8) {
+        const int x = cand[i] >> 16, yr = cand[i] & 0xffff;
+        const int y = seg.perm_k ? __ldg(seg.perm_k + (long long)b * P + yr) : yr;
+        const float *qp = seg.q_f32 + (long long)b * C * P + x, *kp = seg.k_f32 + (long long)b * C * P + y;
+        float qv[C / 32], kv[C / 32];
+#pragma unroll
+        for (int j = 0; j < C / 32; ++j) {
+          qv[j] = __ldg(qp + (long long)(lane + 32 * j) * P);
+          kv[j] = __ldg(kp + (long long)(lane + 32 * j) * P);
+        }
+        const float iq = __ldg(seg.inv_q + (long long)b * P + x), ik = __ldg(seg.inv_k + (long long)b * P + y);
+        float d = 0.f;
+#pragma unroll
+        for (int j = 0; j < C / 32; ++j) d = fmaf(qv[j] * iq, kv[j] * ik, d);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+        const int flat = x * P + y;
+        if (d > bestv || (d == bestv && flat < bestf)) { bestv = d; bestf = flat; bestx = x; besty = y; bestr = yr; }
+      }
+      if (lane == 0) {
+        smax[(warp - 2) * 4 + 0] = bestv;
+        smax[(warp - 2) * 4 + 1] = __int_as_float(bestf);
+        smax[(warp - 2) * 4 + 2] = __int_as_float(bestx);
+        smax[(warp - 2) * 4 + 3] = __int_as_float(seg.mask_b ? besty : (bestr < cnt ? -1 : -2));
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (threadIdx.x == 64) {
+        float bv = -INFINITY;
+        int bf = 0x7fffffff, bx = 0, by = -2;
+        for (int w = 0; w < 8; ++w) {
+          const float v = smax[w * 4];
+          const int f = __float_as_int(smax[w * 4 + 1]);
+          if (v > bv || (v == bv && f < bf)) { bv = v; bf = f; bx = __float_as_int(smax[w * 4 + 2]); by = __float_as_int(smax[w * 4 + 3]); }
+        }
+        float h = 0.f;
+        if (bf != 0x7fffffff) {
+          const float lb = by >= 0 ? seg.mask_b[(long long)b * P + by] : (by == -1 ? 1.f : 0.f);
+          h = seg.mask_a[(long long)b * P + bx] * lb;
+        }
+        seg.hit[b] = h;
       }
     }
   }
@@ -366,12 +473,19 @@ extern "C" int cp2_dense_small_ok(int C, int P) {
 }
 
 extern "C" int cp2_dense_small(const void *qhat_t, const void *khat_t, const int *key_count, const float *mask_b,
-                               float *lse, float *acc, float inv_tau, int B, int C, int P, void *stream) {
+                               float *lse, float *acc, const float *seg_q, const float *seg_k,
+                               const float *seg_inv_q, const float *seg_inv_k, const int *seg_perm_k,
+                               const float *seg_mask_a, const float *seg_mask_b, float *seg_hit, float inv_tau, int B,
+                               int C, int P, void *stream) {
   CP2_REQUIRE(cp2_dense_small_ok(C, P), "cp2_dense_small: unsupported shape C=%d P=%d (C=128: P<=256, C=256: P<=128)", C, P);
   CP2_REQUIRE(B >= 0 && B <= 65535, "cp2_dense_small: bad batch B=%d", B);
   CP2_REQUIRE(inv_tau > 0.f && inv_tau <= 16.f, "cp2_dense_small: 1/tau=%g outside (0, 16]", (double)inv_tau);
   if (B == 0) return CP2_OK;
   CP2_REQUIRE(qhat_t && khat_t && lse && acc, "cp2_dense_small: null pointer");
+  CP2_REQUIRE(seg_hit == nullptr || (seg_q && seg_k && seg_inv_q && seg_inv_k && seg_mask_a &&
+                                     (seg_mask_b || key_count)),
+              "cp2_dense_small: the acc_seg meter needs seg_q, seg_k, seg_inv_q, seg_inv_k, seg_mask_a and "
+              "seg_mask_b (or key_count)");
   const int nxt = cp2_cdiv(P, TILE), rows = nxt * TILE;
   CUtensorMap tq, tk;
   int rc;
@@ -379,15 +493,16 @@ extern "C" int cp2_dense_small(const void *qhat_t, const void *khat_t, const int
   if ((rc = make_feature_tmap(&tk, khat_t, B, C, P, rows)) != CP2_OK) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const float sl2 = inv_tau * LOG2E;
+  const SegMeter seg{seg_q, seg_k, seg_inv_q, seg_inv_k, seg_perm_k, seg_mask_a, seg_mask_b, seg_hit};
   dim3 grid(nxt, B);
   if (C == 128) {
     const size_t smem = SmallCfg<128>::smem(rows);
     CP2_SMEM_ONCE(dense_small_kernel<128>, SmallCfg<128>::smem(256));
-    dense_small_kernel<128><<<grid, SM_THREADS, smem, st>>>(tq, tk, key_count, mask_b, lse, acc, sl2, P, rows);
+    dense_small_kernel<128><<<grid, SM_THREADS, smem, st>>>(tq, tk, key_count, mask_b, lse, acc, seg, sl2, P, rows);
   } else {
     const size_t smem = SmallCfg<256>::smem(rows);
     CP2_SMEM_ONCE(dense_small_kernel<256>, SmallCfg<256>::smem(128));
-    dense_small_kernel<256><<<grid, SM_THREADS, smem, st>>>(tq, tk, key_count, mask_b, lse, acc, sl2, P, rows);
+    dense_small_kernel<256><<<grid, SM_THREADS, smem, st>>>(tq, tk, key_count, mask_b, lse, acc, seg, sl2, P, rows);
   }
   CP2_LAUNCH_CHECK();
   return CP2_OK;

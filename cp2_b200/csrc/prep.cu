@@ -16,7 +16,7 @@ struct PrepSide {
   const float *feat, *mask;
   __nv_bfloat16 *fhat_t;
   float *inv_norm, *scratch, *pos_sum, *neg_sum, *pos_unit, *neg_unit, *norms;
-  int32_t *key_count;
+  int32_t *key_count, *perm;
 };
 struct PrepSides { PrepSide s[2]; };        // blockIdx.z selects the side (query / key) of a fused launch
 
@@ -80,7 +80,7 @@ prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, i
   const bool valid = x < P;
   const float *__restrict__ src = feat + (long long)b * C * P + x;
   if (key_count != nullptr) {
-    // stable partition of the image's pixels: foreground rows first, background rows (zeroed) after
+    // stable partition of the image's pixels: foreground rows first, background rows after
     int before = 0, total = 0;
     for (int i = threadIdx.x; i < P; i += 256) {
       const int on = mask[(long long)b * P + i] != 0.f;
@@ -165,12 +165,12 @@ prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, i
     const int xx = tl * PT + p;
     if (xx < P) {
       const int row = key_count ? dest[p] : xx;
-      const float keep = (key_count && mk[p] == 0.f) ? 0.f : 1.f;
+      if (sd.perm && lane == 0) sd.perm[(long long)b * P + row] = xx;
       __nv_bfloat162 *dst = reinterpret_cast<__nv_bfloat162 *>(fhat_t + ((long long)b * P + row) * C);
 #pragma unroll
       for (int j = 0; j < C / 64; ++j) {
         const int c = j * 64 + lane * 2;
-        dst[c >> 1] = __floats2bfloat162_rn(tile[c][p] * keep, tile[c + 1][p] * keep);
+        dst[c >> 1] = __floats2bfloat162_rn(tile[c][p], tile[c + 1][p]);
       }
     }
   }
@@ -215,7 +215,7 @@ int launch_prep(const PrepSides &sides, int nsides, unsigned int *counters, int 
 }  // namespace
 
 extern "C" int cp2_prep_features(const float *feat, const float *mask, void *fhat_t, float *inv_norm,
-                                 float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count,
+                                 float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count, int32_t *perm,
                                  float *pos_unit, float *neg_unit, float *norms, void *scratch_counters,
                                  int B, int C, int P, void *stream) {
   CP2_REQUIRE(B >= 0 && P > 0 && B <= 65535, "cp2_prep_features: bad shape B=%d P=%d", B, P);
@@ -223,8 +223,9 @@ extern "C" int cp2_prep_features(const float *feat, const float *mask, void *fha
   if (B == 0) return CP2_OK;
   CP2_REQUIRE(scratch_counters, "cp2_prep_features: null scratch_counters");
   PrepSides sides;
+  CP2_REQUIRE(perm == nullptr || key_count != nullptr, "cp2_prep_features: perm needs key_count (compaction)");
   sides.s[0] = PrepSide{feat, mask, static_cast<__nv_bfloat16 *>(fhat_t), inv_norm, scratch, pos_sum, neg_sum,
-                        pos_unit, neg_unit, norms, key_count};
+                        pos_unit, neg_unit, norms, key_count, perm};
   sides.s[1] = sides.s[0];
   int rc = check_side(sides.s[0]);
   if (rc != CP2_OK) return rc;
@@ -235,17 +236,18 @@ extern "C" int cp2_prep_features2(const float *feat_q, const float *mask_q, void
                                   float *pos_sum_q, float *neg_sum_q, float *scratch_q, float *pos_unit_q,
                                   float *neg_unit_q, float *norms_q, const float *feat_k, const float *mask_k,
                                   void *khat_t, float *inv_norm_k, float *pos_sum_k, float *neg_sum_k,
-                                  float *scratch_k, int32_t *key_count, float *pos_unit_k, float *neg_unit_k,
-                                  float *norms_k, void *scratch_counters, int B, int C, int P, void *stream) {
+                                  float *scratch_k, int32_t *key_count, int32_t *perm_k, float *pos_unit_k,
+                                  float *neg_unit_k, float *norms_k, void *scratch_counters, int B, int C, int P,
+                                  void *stream) {
   CP2_REQUIRE(B >= 0 && P > 0 && B <= 65535, "cp2_prep_features2: bad shape B=%d P=%d", B, P);
   CP2_REQUIRE(C == 64 || C == 128 || C == 192 || C == 256, "cp2_prep_features2: C=%d unsupported (64,128,192,256)", C);
   if (B == 0) return CP2_OK;
   CP2_REQUIRE(scratch_counters, "cp2_prep_features2: null scratch_counters");
   PrepSides sides;
   sides.s[0] = PrepSide{feat_q, mask_q, static_cast<__nv_bfloat16 *>(qhat_t), inv_norm_q, scratch_q, pos_sum_q,
-                        neg_sum_q, pos_unit_q, neg_unit_q, norms_q, nullptr};
+                        neg_sum_q, pos_unit_q, neg_unit_q, norms_q, nullptr, nullptr};
   sides.s[1] = PrepSide{feat_k, mask_k, static_cast<__nv_bfloat16 *>(khat_t), inv_norm_k, scratch_k, pos_sum_k,
-                        neg_sum_k, pos_unit_k, neg_unit_k, norms_k, key_count};
+                        neg_sum_k, pos_unit_k, neg_unit_k, norms_k, key_count, perm_k};
   int rc = check_side(sides.s[0]);
   if (rc == CP2_OK) rc = check_side(sides.s[1]);
   if (rc != CP2_OK) return rc;

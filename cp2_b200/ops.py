@@ -131,10 +131,11 @@ def composite_pair(img_a, bg_a, img_b, bg_b, output_stride, want_full_mask=False
 
 
 # ----------------------------------------------------------------- K2a
-def prep_features(feat, mask, compact=False, unit=False):
+def prep_features(feat, mask, compact=False, unit=False, perm=None):
     """builder.py:1261-1268.  feat [B,C,P] f32, mask [B,P] -> (fhat_t bf16 [B,P,C], inv_norm [B,P],
     pos_sum [B,C], neg_sum [B,C], key_count).  compact=True (key side): fhat_t holds the foreground
-    rows first (pixel order) then zero rows, and key_count [B] int32 is their number; else None.
+    rows first (pixel order) then the background rows, and key_count [B] int32 is the number of foreground
+    rows; else None.  perm: optional [B,P] int32 OUT, the pixel stored in each row (compact only).
     unit=True appends (pos_unit [B,C], neg_unit [B,C], norms [B,2]): the outer F.normalize of the pooled
     vectors (builder.py:1264,1268) and the raw norms its backward needs."""
     _need_cuda(feat, mask)
@@ -152,16 +153,17 @@ def prep_features(feat, mask, compact=False, unit=False):
     nu = torch.empty((B, C), device=dev, dtype=torch.float32) if unit else None
     norms = torch.empty((B, 2), device=dev, dtype=torch.float32) if unit else None
     _call("cp2_prep_features", 1, lib.cp2_prep_features, _ptr(feat), _ptr(mask), _ptr(fhat_t), _ptr(inv_norm),
-          _ptr(pos), _ptr(neg), _ptr(scratch), _ptr(count), _ptr(pu), _ptr(nu), _ptr(norms),
+          _ptr(pos), _ptr(neg), _ptr(scratch), _ptr(count), _ptr(perm), _ptr(pu), _ptr(nu), _ptr(norms),
           _ptr(_persistent_zero("prep", 4 * B, dev)), B, C, P, _stream())
     if unit:
         return fhat_t, inv_norm, pos, neg, count, pu, nu, norms
     return fhat_t, inv_norm, pos, neg, count
 
 
-def prep_features_pair(feat_q, mask_q, feat_k, mask_k):
+def prep_features_pair(feat_q, mask_q, feat_k, mask_k, want_perm=False):
     """Query side and (compacted) key side of one step in ONE launch.  -> two tuples shaped like
-    prep_features(..., unit=True): (fhat_t, inv_norm, pos_sum, neg_sum, key_count|None, pos_unit, neg_unit, norms)."""
+    prep_features(..., unit=True): (fhat_t, inv_norm, pos_sum, neg_sum, key_count|None, pos_unit, neg_unit, norms);
+    want_perm appends perm_k [B,P] int32 (pixel of each compacted key row) to the key tuple."""
     _need_cuda(feat_q, mask_q, feat_k, mask_k)
     feat_q, mask_q, feat_k, mask_k = _f32c(feat_q), _f32c(mask_q), _f32c(feat_k), _f32c(mask_k)
     B, C, P = feat_q.shape
@@ -176,11 +178,13 @@ def prep_features_pair(feat_q, mask_q, feat_k, mask_k):
                 torch.empty((B, C), **f32), torch.empty((B, C), **f32), torch.empty((B, 2), **f32)]
     q, k = side(), side()
     count = torch.empty((B,), device=dev, dtype=torch.int32)
+    perm = torch.empty((B, P), device=dev, dtype=torch.int32) if want_perm else None
     _call("cp2_prep_features2", 1, lib.cp2_prep_features2,
           _ptr(feat_q), _ptr(mask_q), *[_ptr(t) for t in q],
-          _ptr(feat_k), _ptr(mask_k), *[_ptr(t) for t in k[:5]], _ptr(count), *[_ptr(t) for t in k[5:]],
+          _ptr(feat_k), _ptr(mask_k), *[_ptr(t) for t in k[:5]], _ptr(count), _ptr(perm), *[_ptr(t) for t in k[5:]],
           _ptr(_persistent_zero("prep2", 8 * B, dev)), B, C, P, _stream())
-    return ((q[0], q[1], q[2], q[3], None, q[5], q[6], q[7]), (k[0], k[1], k[2], k[3], count, k[5], k[6], k[7]))
+    kt = (k[0], k[1], k[2], k[3], count, k[5], k[6], k[7])
+    return ((q[0], q[1], q[2], q[3], None, q[5], q[6], q[7]), kt + (perm,) if want_perm else kt)
 
 
 # ------------------------------------------------------------------ K2
@@ -214,17 +218,26 @@ def dense_small_ok(C, P):
     return bool(_lib.load().cp2_dense_small_ok(int(C), int(P)))
 
 
-def dense_small(qhat_t, khat_t, inv_tau, key_count=None, mask_b=None):
+def dense_small(qhat_t, khat_t, inv_tau, key_count=None, mask_b=None, seg=None):
     """cp2_dense_small: column LSE and the P^2-sized part of the gradient in ONE launch (P <= 256).
-    -> (lse [B,P], acc [B,C,P]); acc[n,:,x] = sum_y on_y exp(S[x,y]/tau - lse[y]) khat[y,:]."""
+    -> (lse [B,P], acc [B,C,P]); acc[n,:,x] = sum_y on_y exp(S[x,y]/tau - lse[y]) khat[y,:].
+    seg = (q_f32 [B,C,P], k_f32 [B,C,P], inv_norm_q [B,P], inv_norm_k [B,P], perm_k [B,P] int32 | None,
+           mask_a [B,P], mask_b [B,P] | None) turns the acc_seg meter on (builder.py:1442-1448): a third result
+    hit [B] = label of the image's arg-max pixel pair, decided in fp32."""
     _need_cuda(qhat_t, khat_t)
     B, P, C = qhat_t.shape
     dev = qhat_t.device
     lse = torch.empty((B, P), device=dev, dtype=torch.float32)
     acc = torch.empty((B, C, P), device=dev, dtype=torch.float32)
+    segp, hit = [None] * 7, None
+    if seg is not None:
+        segp = list(seg)
+        for t in segp[:4] + segp[5:]:
+            assert t is None or (t.dtype == torch.float32 and t.is_contiguous())
+        hit = torch.empty((B,), device=dev, dtype=torch.float32)
     _call("cp2_dense_small", 1, _lib.load().cp2_dense_small, _ptr(qhat_t), _ptr(khat_t), _ptr(key_count), _ptr(mask_b),
-          _ptr(lse), _ptr(acc), float(inv_tau), B, C, P, _stream())
-    return lse, acc
+          _ptr(lse), _ptr(acc), *[_ptr(t) for t in segp], _ptr(hit), float(inv_tau), B, C, P, _stream())
+    return (lse, acc) if seg is None else (lse, acc, hit)
 
 
 def dense_small_bwd(acc, qhat_t, mask_a, inv_norm, alpha, v1, v2, key_count=None, gscale=None):
@@ -386,15 +399,15 @@ def enqueue(keys_all, queue, queue_ptr, shadow=None):
 
 # ------------------------------------------------- fused loss (a5 + a6 + a7 + a12)
 def loss_combine(q_pos, k_pos, q_neg, k_neg, sq, sk, norms_q, z, G, lse, key_count, mask_a, temp_global,
-                 temp_local, lmbd_dense, dense_n=None):
+                 temp_local, lmbd_dense, dense_n=None, hit_seg=None):
     """cp2_loss_combine: the [B,C]/[B]-sized remainder of the loss (1 launch).
-    -> out [5] = (loss, loss_ins, loss_dense, std meter of q_pos, std meter of k_pos), l_pos [B],
+    -> out [6] = (loss, loss_ins, loss_dense, std meter of q_pos, std meter of k_pos, acc_seg | NaN), l_pos [B],
        alpha [B], v1 [B,C], v2 [B,C]|None (inputs of cp2_dense_grad for upstream gradient 1).
     dense_n [B] (PROPOSED modes): per-image dense losses from dense_weighted_lse; sq, sk, lse are then unused."""
     B, C = q_pos.shape
     P = mask_a.shape[1]
     dev = q_pos.device
-    out = torch.empty((5,), device=dev, dtype=torch.float32)
+    out = torch.empty((6,), device=dev, dtype=torch.float32)
     l_pos = torch.empty((B,), device=dev, dtype=torch.float32)
     alpha = torch.empty((B,), device=dev, dtype=torch.float32)
     v1 = torch.empty((B, C), device=dev, dtype=torch.float32)
@@ -402,7 +415,7 @@ def loss_combine(q_pos, k_pos, q_neg, k_neg, sq, sk, norms_q, z, G, lse, key_cou
     scratch = torch.empty((B, 2), device=dev, dtype=torch.float32)
     _call("cp2_loss_combine", 1, _lib.load().cp2_loss_combine, _ptr(q_pos), _ptr(k_pos), _ptr(q_neg), _ptr(k_neg),
           _ptr(sq), _ptr(sk), _ptr(norms_q), _ptr(z), _ptr(G), _ptr(lse), _ptr(key_count), _ptr(mask_a), _ptr(dense_n),
-          _ptr(out), _ptr(l_pos), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(scratch),
+          _ptr(hit_seg), _ptr(out), _ptr(l_pos), _ptr(alpha), _ptr(v1), _ptr(v2), _ptr(scratch),
           _ptr(_persistent_zero("combine", 8, dev)), 1.0 / float(temp_global),
           1.0 / float(temp_local), float(lmbd_dense), B, C, P, _stream())
     return out, l_pos, alpha, v1, v2
@@ -430,25 +443,32 @@ class CP2LossFunction(torch.autograd.Function):
         kf = _f32c(k.detach()).reshape(B, C, -1)
         mask_a, mask_b = _f32c(mask_a), _f32c(mask_b)
         tg, tl = float(temp_global), float(temp_local)
-        # one launch for both sides; key side compacted: fg keys first, zero rows after
-        (qh, q_inv, sq, _, _, q_pos, q_neg, norms_q), (kh, _, sk, _, kcnt, k_pos, k_neg, _) = \
-            prep_features_pair(qf, mask_a, kf, mask_b)
+        ctx.small = dense_small_ok(C, qf.shape[2])
+        seg_on = bool(track_accuracy) and ctx.small
+        # one launch for both sides; key side compacted: fg keys first, bg keys after
+        (qh, q_inv, sq, _, _, q_pos, q_neg, norms_q), (kh, k_inv, sk, _, kcnt, k_pos, k_neg, _, *perm) = \
+            prep_features_pair(qf, mask_a, kf, mask_b, want_perm=seg_on)
         bg = bool(include_background)
         # one pass over the queue: fwd + bwd sums (+ the acc_ins meter)
         z, G, _, acc_ins = global_nce(q_pos, queue, 1.0 / tg, k_pos if track_accuracy else None,
                                       q_neg if (bg and track_accuracy) else None,
                                       k_neg if (bg and track_accuracy) else None, shadow=queue_shadow)
-        ctx.small = dense_small_ok(C, qh.shape[1])
+        hit_seg = None
         if ctx.small:                                          # map fits TMEM: LSE and the P^2 part of dq in one launch
-            lse, acc = dense_small(qh, kh, 1.0 / tl, kcnt)
+            if seg_on:                                         # ... and the acc_seg meter (builder.py:1442-1448)
+                lse, acc, hit_seg = dense_small(qh, kh, 1.0 / tl, kcnt,
+                                                seg=(qf, kf, q_inv, k_inv, perm[0], mask_a, mask_b))
+            else:
+                lse, acc = dense_small(qh, kh, 1.0 / tl, kcnt)
         else:
             lse, acc = dense_lse(qh, kh, 1.0 / tl, kcnt), None  # column LSE on the tensor cores
         out, l_pos, alpha, v1, v2 = loss_combine(q_pos, k_pos, q_neg if bg else None, k_neg if bg else None,
-                                                 sq, sk, norms_q, z, G, lse, kcnt, mask_a, tg, tl, lmbd_dense)
+                                                 sq, sk, norms_q, z, G, lse, kcnt, mask_a, tg, tl, lmbd_dense,
+                                                 hit_seg=hit_seg)
         ctx.save_for_backward(qh, acc if ctx.small else kh, lse, mask_a, kcnt, q_inv, alpha, v1, v2)
         ctx.inv_tl = 1.0 / tl
         ctx.q_shape = q.shape
-        loss, loss_ins, loss_dense, meters = out[0], out[1], out[2], out[3:]
+        loss, loss_ins, loss_dense, meters = out[0], out[1], out[2], out[3:]     # meters = (std q, std k, acc_seg | NaN)
         if acc_ins is None:
             acc_ins = torch.full((1,), float("nan"), device=q.device)
         ctx.mark_non_differentiable(loss_ins, loss_dense, k_pos, q_pos, l_pos, meters, q_neg, k_neg, acc_ins)
@@ -570,12 +590,14 @@ def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_
     """-> (loss, loss_ins, loss_dense, k_pos, q_pos, stats); only `loss` has a gradient (to q).
     pair_weights: None (MappingType.CP2 / NegativeType.NONE, the tensor-core path) or a PairWeights.
     queue_shadow: the queue's QueueShadow (None: the queue is converted to bf16 for this call).
-    track_accuracy: stats["acc_ins"] from the same queue pass (builder.py:1441); acc_seg is ops.dense_top1's."""
-    nan = float("nan")
-    acc_seg = nan
+    track_accuracy: stats["acc_ins"] from the same queue pass (builder.py:1441); stats["acc_seg"] from the dense
+    kernel itself when the map fits TMEM (P <= 256) or the weights are on, else None (ops.dense_top1 computes it)."""
+    acc_seg = None
     if pair_weights is None:
         res = CP2LossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense,
                                     include_background, queue_shadow, bool(track_accuracy))
+        if track_accuracy and dense_small_ok(q.shape[1], q[0, 0].numel()):
+            acc_seg = res[6][2]                      # came out of cp2_dense_small / cp2_loss_combine
     else:                    # the weighted forward finds the arg-max of its own logits on the way
         *res, acc_seg = CP2WeightedLossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local,
                                                       lmbd_dense, include_background, pair_weights, queue_shadow,

@@ -59,11 +59,14 @@ int cp2_composite2(const float *img_a, const float *bg_a, float *out_a, float *m
  *   pos_sum   : [B,C] f32, sum_x mask_x * fhat_x      (fp32 values, not the bf16 copy)
  *   neg_sum   : [B,C] f32, sum_x (1-mask_x) * fhat_x
  *   scratch   : [B, cp2_prep_tiles(P), 2, C] f32 work space (per-tile partial sums)
- *   key_count : NULL, or [B] int32 OUT.  When given, fhat_t is written COMPACTED: the unit vectors of
- *               the foreground pixels (mask != 0) first, in pixel order, then zero rows;
- *               key_count[n] = number of foreground pixels.  Only the key side is compacted:
- *               background keys have label 0 for every query (builder.py:1291-1292,1435), so they
- *               enter neither the loss nor the gradient.  inv_norm / pos_sum / neg_sum are unaffected.
+ *   key_count : NULL, or [B] int32 OUT.  When given, fhat_t is written COMPACTED (a stable partition): the
+ *               unit vectors of the foreground pixels (mask != 0) first, in pixel order, then those of the
+ *               background pixels, in pixel order; key_count[n] = number of foreground pixels.  Only the
+ *               key side is compacted: background keys have label 0 for every query
+ *               (builder.py:1291-1292,1435), so they enter neither the loss nor the gradient and K2 skips
+ *               the rows past key_count (they are still there for the arg-max meter, builder.py:1442).
+ *               inv_norm / pos_sum / neg_sum are unaffected (pixel order).
+ *   perm      : NULL, or [B,P] int32 OUT (needs key_count): perm[n,row] = the pixel stored in row `row`.
  *   pos_unit, neg_unit, norms : all NULL, or OUT [B,C], [B,C], [B,2]: the outer F.normalize of the pooled
  *               vectors (builder.py:1264,1268,1282,1285), x / max(||x||, 1e-12), and the raw norms
  *               (||pos_sum||, ||neg_sum||) the normalisation's backward needs.
@@ -73,17 +76,18 @@ int cp2_composite2(const float *img_a, const float *bg_a, float *out_a, float *m
  * C must be a multiple of 64 and <= 256. */
 int cp2_prep_tiles(int P);
 int cp2_prep_features(const float *feat, const float *mask, void *fhat_t, float *inv_norm,
-                      float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count,
+                      float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count, int32_t *perm,
                       float *pos_unit, float *neg_unit, float *norms, void *scratch_counters,
                       int B, int C, int P, void *stream);
 /* Query side and key side (key side compacted through key_count) of one step in ONE launch; per side the
- * contract of cp2_prep_features.  scratch_counters: 2*B uint32. */
+ * contract of cp2_prep_features (perm_k may be NULL).  scratch_counters: 2*B uint32. */
 int cp2_prep_features2(const float *feat_q, const float *mask_q, void *qhat_t, float *inv_norm_q,
                        float *pos_sum_q, float *neg_sum_q, float *scratch_q, float *pos_unit_q,
                        float *neg_unit_q, float *norms_q, const float *feat_k, const float *mask_k,
                        void *khat_t, float *inv_norm_k, float *pos_sum_k, float *neg_sum_k,
-                       float *scratch_k, int32_t *key_count, float *pos_unit_k, float *neg_unit_k,
-                       float *norms_k, void *scratch_counters, int B, int C, int P, void *stream);
+                       float *scratch_k, int32_t *key_count, int32_t *perm_k, float *pos_unit_k,
+                       float *neg_unit_k, float *norms_k, void *scratch_counters, int B, int C, int P,
+                       void *stream);
 
 /* K2 forward — dense pixel InfoNCE, column log-sum-exp.
  * Replaces builder.py:1289 (einsum ncx,ncy->nxy), :1431 (/T) and the LogSoftmax(dim=1)
@@ -121,10 +125,19 @@ int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int32_t *key_co
  * cp2_dense_small_bwd then applies what cp2_dense_grad's epilogue applies (rank-1 terms, upstream
  * gradient from device memory, F.normalize backward):
  *   dq[n,:,x] = N_x( g * (alpha[n]*acc[n,:,x] + mask_a[x]*v1[n,:] + (1-mask_a[x])*v2[n,:]) )
+ * The acc_seg meter of builder.py:1442-1448 (label of the arg-max over all pixel pairs) comes out of the same
+ * launch when seg_hit is given: the largest similarity is found while S is in TMEM, every pair within 2^-7 of it
+ * (the bound of the operands' bf16 rounding) is re-scored exactly in fp32:
+ *   seg_q, seg_k : [B,C,P] f32 encoder outputs; seg_inv_q, seg_inv_k : [B,P] (cp2_prep_features inv_norm);
+ *   seg_perm_k   : [B,P] int32 pixel of each key row (cp2_prep_features perm) or NULL (keys in pixel order);
+ *   seg_mask_a, seg_mask_b : [B,P] f32 masks in pixel order (seg_mask_b NULL: label = row < key_count);
+ *   seg_hit      : [B] f32 OUT = mask_a[x*] * mask_b[y*]   (NULL: meter off, the other seg_* are ignored).
  * cp2_dense_small_ok(C, P) = 1 when the shape is taken by this path. */
 int cp2_dense_small_ok(int C, int P);
 int cp2_dense_small(const void *qhat_t, const void *khat_t, const int32_t *key_count, const float *mask_b,
-                    float *lse, float *acc, float inv_tau, int B, int C, int P, void *stream);
+                    float *lse, float *acc, const float *seg_q, const float *seg_k, const float *seg_inv_q,
+                    const float *seg_inv_k, const int32_t *seg_perm_k, const float *seg_mask_a,
+                    const float *seg_mask_b, float *seg_hit, float inv_tau, int B, int C, int P, void *stream);
 int cp2_dense_small_bwd(const float *acc, const void *qhat_t, const int32_t *key_count, const float *mask_a,
                         const float *inv_norm, const float *alpha, const float *v1, const float *v2,
                         const float *gscale, float *dq, int B, int C, int P, void *stream);
@@ -169,13 +182,15 @@ int cp2_global_nce(const float *q_pos, const void *queue_bf, const float *queue,
  *   key_count: [B] int32 foreground keys per image ; mask_a : [B,P] f32
  *   dense_n  : NULL, or [B] per-image dense losses from cp2_dense_weighted_lse (PROPOSED modes): then
  *              sq, sk and lse are not read and v1 carries the global loss's gradient only
- *   out      : [5] f32 = {loss, loss_ins, loss_dense, mean_c std_b(q_pos), mean_c std_b(k_pos)}
+ *   hit_seg  : NULL or [B] f32 (cp2_dense_small's seg_hit): out[5] = 100 * mean(hit_seg), the acc_seg meter
+ *   out      : [6] f32 = {loss, loss_ins, loss_dense, mean_c std_b(q_pos), mean_c std_b(k_pos), acc_seg | NaN}
  *   l_pos [B]; alpha [B], v1 [B,C], v2 [B,C] : inputs of cp2_dense_grad for upstream gradient 1
  *   scratch  : [B,2] f32 */
 int cp2_loss_combine(const float *q_pos, const float *k_pos, const float *q_neg, const float *k_neg,
                      const float *sq, const float *sk, const float *norms_q, const float *z, const float *G,
                      const float *lse, const int32_t *key_count, const float *mask_a, const float *dense_n,
-                     float *out, float *l_pos, float *alpha, float *v1, float *v2, float *scratch, void *scratch_counter, float inv_tau_global,
+                     const float *hit_seg, float *out, float *l_pos, float *alpha, float *v1, float *v2,
+                     float *scratch, void *scratch_counter, float inv_tau_global,
                      float inv_tau_dense, float lmbd_dense, int B, int C, int P, void *stream);
 
 /* K4 — momentum (EMA) update of the key encoder, all parameters in one launch.

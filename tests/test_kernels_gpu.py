@@ -164,8 +164,8 @@ def test_prep_features(ops, B, C, P):
 
 @pytest.mark.parametrize("B,C,P", [(2, 128, 196), (2, 256, 50), (1, 128, 3136), (3, 128, 33)])
 def test_prep_features_compact_keys(ops, B, C, P):
-    """compact=True: foreground rows first (pixel order), zero rows after, key_count = #fg; everything
-    else identical to the plain call."""
+    """compact=True: foreground rows first (pixel order), background rows after (pixel order), key_count = #fg,
+    perm = the pixel of each row; everything else identical to the plain call."""
     g = torch.Generator().manual_seed(P + 1)
     feat = torch.randn(B, C, P, generator=g)
     mask = (torch.rand(B, P, generator=g) < 0.6).float()
@@ -173,13 +173,17 @@ def test_prep_features_compact_keys(ops, B, C, P):
     if B > 1:
         mask[1] = 0.0                                     # no foreground at all
     fh, inv, ps, ns, _ = ops.prep_features(dev(feat), dev(mask))
-    fc, inv2, ps2, ns2, cnt = ops.prep_features(dev(feat), dev(mask), compact=True)
+    perm = torch.full((B, P), -1, dtype=torch.int32, device="cuda")
+    fc, inv2, ps2, ns2, cnt = ops.prep_features(dev(feat), dev(mask), compact=True, perm=perm)
     assert torch.equal(inv, inv2) and torch.equal(ps, ps2) and torch.equal(ns, ns2)
     assert cnt.dtype == torch.int32 and torch.equal(cnt.cpu().long(), mask.sum(1).long())
     for b in range(B):
         n = int(cnt[b])
-        assert torch.equal(fc[b, :n], fh[b][mask[b].bool().cuda()])
-        assert not fc[b, n:].any()
+        fg = mask[b].bool().cuda()
+        assert torch.equal(fc[b, :n], fh[b][fg])
+        assert torch.equal(fc[b, n:], fh[b][~fg])
+        want = torch.cat([torch.nonzero(fg).flatten(), torch.nonzero(~fg).flatten()]).int()
+        assert torch.equal(perm[b], want)
 
 
 # ------------------------------------------------------------------- K2 forward
@@ -455,6 +459,59 @@ def test_dense_top1_vs_oracle(ops, B, C, hw):
     mb2[:, y] = 1.0
     acc3, hit3 = ops.dense_top1(q2.cuda(), k2.cuda(), ma2.cuda(), mb2.cuda())
     assert hit3.cpu().tolist() == [1.0] * B and acc3.item() == 100.0
+
+
+def _seg_hits(ops, q, k, ma, mb, tau=0.2):
+    """acc_seg out of the dense kernel itself, the way the step calls it: compacted keys + perm."""
+    B, C, P = q.shape
+    qd, kd, mad, mbd = q.cuda(), k.cuda(), ma.cuda(), mb.cuda()
+    (qh, q_inv, *_), (kh, k_inv, _, _, cnt, _, _, _, perm) = ops.prep_features_pair(qd, mad, kd, mbd, want_perm=True)
+    _, _, hit = ops.dense_small(qh, kh, 1.0 / tau, cnt, seg=(qd, kd, q_inv, k_inv, perm, mad, mbd))
+    torch.cuda.synchronize()
+    return hit.cpu()
+
+
+@pytest.mark.parametrize("B,C,hw", [(4, 128, 14), (6, 128, 16), (3, 128, 9), (3, 256, 9), (5, 128, 11), (40, 128, 14)])
+def test_dense_small_acc_seg_vs_oracle(ops, B, C, hw):
+    """The acc_seg meter found by cp2_dense_small while S is in TMEM (bf16-operand maximum, candidates within 2^-7
+    re-scored in fp32) against builder.py:1442-1448 as restated by the oracle, image by image, incl. planted
+    maxima and a near-tie that bf16 rounding alone would decide wrongly."""
+    g = torch.Generator().manual_seed(17 * hw + B)
+    P = hw * hw
+    q = torch.randn(B, C, P, generator=g)
+    k = torch.randn(B, C, P, generator=g)
+    ma = (torch.rand(B, P, generator=g) < 0.6).float()
+    mb = (torch.rand(B, P, generator=g) < 0.6).float()
+    if B > 2:
+        mb[1] = 0.0                                       # no foreground key at all
+        mb[2] = 1.0
+    qh, kh = torch.nn.functional.normalize(q, dim=1), torch.nn.functional.normalize(k, dim=1)
+    want = [O.dense_accuracy(qh[i:i + 1], kh[i:i + 1], ma[i:i + 1], mb[i:i + 1]).item() / 100.0 for i in range(B)]
+    assert _seg_hits(ops, q, k, ma, mb).tolist() == want
+    # a planted maximum at a known pair, on a background key: miss; then on a foreground pair: hit
+    q2, k2 = q.clone(), k.clone()
+    x, y = P - 1, 3
+    k2[:, :, y] = q2[:, :, x] * 2.5                       # cosine 1 with query pixel x
+    ma2, mb2 = ma.clone(), mb.clone()
+    ma2[:, x], mb2[:, y] = 1.0, 0.0
+    assert _seg_hits(ops, q2, k2, ma2, mb2).tolist() == [0.0] * B
+    mb2[:, y] = 1.0
+    assert _seg_hits(ops, q2, k2, ma2, mb2).tolist() == [1.0] * B
+    # near-tie: a second pair 2e-4 below the planted maximum in fp32 (far inside the bf16 rounding of the operands),
+    # with the opposite label: the fp32 re-scoring has to pick the planted one, whatever bf16 says
+    q3, k3 = q2.clone(), k2.clone()
+    x2, y2 = 1, P - 2
+    v = q3[:, :, x2] / q3[:, :, x2].norm(dim=1, keepdim=True)
+    r = torch.randn(B, C, generator=g)
+    r = r - (r * v).sum(1, keepdim=True) * v
+    r = r / r.norm(dim=1, keepdim=True)
+    k3[:, :, y2] = v * (1 - 2e-4) + r * (1 - (1 - 2e-4) ** 2) ** 0.5     # cosine 1 - 2e-4 with query pixel x2
+    ma3, mb3 = ma2.clone(), mb2.clone()
+    ma3[:, x2], mb3[:, y2] = 1.0, 0.0                     # runner-up is a non-label pair, winner a label pair
+    qh3, kh3 = torch.nn.functional.normalize(q3, dim=1), torch.nn.functional.normalize(k3, dim=1)
+    want3 = [O.dense_accuracy(qh3[i:i + 1], kh3[i:i + 1], ma3[i:i + 1], mb3[i:i + 1]).item() / 100.0 for i in range(B)]
+    assert want3 == [1.0] * B
+    assert _seg_hits(ops, q3, k3, ma3, mb3).tolist() == want3
 
 
 @pytest.mark.parametrize("B,K,bg", [(32, 65536, False), (4, 1000, True), (70, 4096, False)])

@@ -42,6 +42,7 @@ def test_loss_golden_p196(ops, tag):
         track_accuracy=True)
     loss.backward()
     np.testing.assert_allclose(st["acc_ins"].item(), g["acc_ins"], atol=1e-3)   # from the loss's own queue pass
+    np.testing.assert_allclose(st["acc_seg"].item(), g["acc_seg"], atol=1e-3)   # from the dense kernel itself (P=196)
     # the reference's own accuracy meters (builder.py:1441-1448) from the two arg-max kernels
     bg = bool(g["include_background"])
     acc_ins, _ = ops.global_top1(q_pos, k_pos, T(g["queue0"]).cuda(), st["q_neg"] if bg else None,
