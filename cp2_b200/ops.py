@@ -218,6 +218,23 @@ def dense_small_ok(C, P):
     return bool(_lib.load().cp2_dense_small_ok(int(C), int(P)))
 
 
+_SM_COUNT = {}
+
+
+def dense_small_preferred(B, C, P, device=None):
+    """The single-kernel path runs one CTA per SM (all of TMEM, both operands of the image in shared memory): it
+    wins while the batch fits one wave (B * ceil(P/128) <= SM count; measured at P=196: 27 us vs 30 us at B=32,
+    65 us vs 52 us at B=256), beyond that the streaming pair (2 CTAs per SM in the forward) has the throughput."""
+    if not dense_small_ok(C, P):
+        return False
+    dev = None if device is None else torch.device(device).index
+    if dev is None:
+        dev = torch.cuda.current_device()
+    if dev not in _SM_COUNT:
+        _SM_COUNT[dev] = torch.cuda.get_device_properties(dev).multi_processor_count
+    return B * ((P + 127) // 128) <= _SM_COUNT[dev]
+
+
 def dense_small(qhat_t, khat_t, inv_tau, key_count=None, mask_b=None, seg=None):
     """cp2_dense_small: column LSE and the P^2-sized part of the gradient in ONE launch (P <= 256).
     -> (lse [B,P], acc [B,C,P]); acc[n,:,x] = sum_y on_y exp(S[x,y]/tau - lse[y]) khat[y,:].
@@ -255,7 +272,7 @@ def dense_fwd_bwd(qhat_t, khat_t, key_count, mask_a, inv_norm, alpha, v1, v2, in
     The configs[3] microbench unit: cp2_dense_small + cp2_dense_small_bwd for maps that fit TMEM, else
     cp2_dense_lse + cp2_dense_grad."""
     B, P, C = qhat_t.shape
-    if dense_small_ok(C, P):
+    if dense_small_preferred(B, C, P, qhat_t.device):
         lse, acc = dense_small(qhat_t, khat_t, inv_tau, key_count)
         return lse, dense_small_bwd(acc, qhat_t, mask_a, inv_norm, alpha, v1, v2, key_count=key_count, gscale=gscale)
     lse = dense_lse(qhat_t, khat_t, inv_tau, key_count)
@@ -443,7 +460,7 @@ class CP2LossFunction(torch.autograd.Function):
         kf = _f32c(k.detach()).reshape(B, C, -1)
         mask_a, mask_b = _f32c(mask_a), _f32c(mask_b)
         tg, tl = float(temp_global), float(temp_local)
-        ctx.small = dense_small_ok(C, qf.shape[2])
+        ctx.small = dense_small_preferred(B, C, qf.shape[2], qf.device)
         seg_on = bool(track_accuracy) and ctx.small
         # one launch for both sides; key side compacted: fg keys first, bg keys after
         (qh, q_inv, sq, _, _, q_pos, q_neg, norms_q), (kh, k_inv, sk, _, kcnt, k_pos, k_neg, _, *perm) = \
@@ -591,12 +608,13 @@ def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_
     pair_weights: None (MappingType.CP2 / NegativeType.NONE, the tensor-core path) or a PairWeights.
     queue_shadow: the queue's QueueShadow (None: the queue is converted to bf16 for this call).
     track_accuracy: stats["acc_ins"] from the same queue pass (builder.py:1441); stats["acc_seg"] from the dense
-    kernel itself when the map fits TMEM (P <= 256) or the weights are on, else None (ops.dense_top1 computes it)."""
+    kernel itself when the single-kernel path is taken (map fits TMEM, batch fits one wave: dense_small_preferred)
+    or the weights are on, else None (ops.dense_top1 computes it)."""
     acc_seg = None
     if pair_weights is None:
         res = CP2LossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense,
                                     include_background, queue_shadow, bool(track_accuracy))
-        if track_accuracy and dense_small_ok(q.shape[1], q[0, 0].numel()):
+        if track_accuracy and dense_small_preferred(q.shape[0], q.shape[1], q[0, 0].numel(), q.device):
             acc_seg = res[6][2]                      # came out of cp2_dense_small / cp2_loss_combine
     else:                    # the weighted forward finds the arg-max of its own logits on the way
         *res, acc_seg = CP2WeightedLossFunction.apply(q, k, mask_a, mask_b, queue, temp_global, temp_local,
