@@ -7,41 +7,15 @@
 // pair on the same bf16 operands: forward = column log-sum-exp + the label-weighted positive sum,
 // backward = recomputation + the second contraction + the per-pixel normalize backward, one launch.
 #include "common.cuh"
+#include "weighted_common.cuh"
+
+using namespace weighted;
 
 namespace {
 
 constexpr int WT = 32;                  // tile edge (pixels)
 constexpr int WTHREADS = 256;
 constexpr int SEL_INTS = 4 + 512;         // MEDIAN selection state per image
-
-struct WParams {
-  float w_pix, w_reg, w_not, neg_scale, inv_tau;
-  int neg_type;                         // 0 none, 1 fixed (centre 0), 2 average, 3 median (per-image centre)
-  int P, ws, ids_w, os;
-  long long ids_hw;
-};
-
-__device__ __forceinline__ long long id_index(const WParams &p, int b, int pix) {
-  const int r = pix / p.ws, c = pix - r * p.ws;
-  return (long long)b * p.ids_hw + (long long)(r * p.os + p.os / 2) * p.ids_w + c * p.os + p.os / 2;
-}
-
-// builder.py:1234-1243: region weight where the region ids agree and are both known (non-zero),
-// overridden by the pixel weight where the pixel ids agree, the "not" weight where still zero.
-__device__ __forceinline__ float pair_weight(long long pa, long long pb, long long ra, long long rb,
-                                             const WParams &p) {
-  float w = (ra == rb && ra != 0) ? p.w_reg : 0.f;
-  if (pa == pb) w = p.w_pix;
-  if (w == 0.f) w = p.w_not;
-  return w;
-}
-
-// builder.py:1332-1375: t = s on label pairs, 2*sigmoid(scale*(s-centre))-1 elsewhere; dt = dt/ds.
-__device__ __forceinline__ void squash(float s, bool label, float centre, const WParams &p, float &t, float &dt) {
-  if (label || p.neg_type == 0) { t = s; dt = 1.f; return; }
-  t = 2.f / (1.f + expf((s - centre) * -p.neg_scale)) - 1.f;
-  dt = (1.f - t * t) * 0.5f * p.neg_scale;
-}
 
 struct Best { float v; int i; };
 __device__ __forceinline__ void take(Best &a, float v, int i) {
@@ -476,20 +450,31 @@ weighted_grad_kernel(const __nv_bfloat16 *__restrict__ qhat_t, const __nv_bfloat
 size_t lse_smem(int C) { return (size_t)(WT * (C + 4) + WT * C) * sizeof(float); }
 size_t grad_smem(int C) { return (size_t)(WT * (C + 4) + (WT + 1) * C + WT * (WT + 1)) * sizeof(float); }
 
-int make_params(WParams &p, float w_pix, float w_reg, float w_not, int neg_type, float neg_scale, float inv_tau,
-                int P, int ids_h, int ids_w, int os) {
-  CP2_REQUIRE(os >= 1 && ids_h >= 1 && ids_w >= 1, "cp2_dense_weighted: bad id map %dx%d stride %d", ids_h, ids_w, os);
-  const int hs = (ids_h - os / 2 + os - 1) / os, ws = (ids_w - os / 2 + os - 1) / os;
-  CP2_REQUIRE(hs * ws == P, "cp2_dense_weighted: id maps %dx%d at stride %d give %dx%d pixels, P=%d", ids_h, ids_w,
-              os, hs, ws, P);
-  CP2_REQUIRE(neg_type >= 0 && neg_type <= 3,
-              "cp2_dense_weighted: negative type %d (0 none, 1 fixed, 2 average, 3 median)", neg_type);
-  CP2_REQUIRE(inv_tau > 0.f, "cp2_dense_weighted: bad temperature");
-  p = WParams{w_pix, w_reg, w_not, neg_scale, inv_tau, neg_type, P, ws, ids_w, os, (long long)ids_h * ids_w};
+}  // namespace
+
+// Pre-pass shared by the SIMT and the tensor-core forward: wstats / key_count, and for NegativeType.MEDIAN the
+// 4-pass radix select of the centre.  scratch: [B, cp2_dense_weighted_tiles(P)] floats.
+int weighted::prepass(const __nv_bfloat16 *q, const __nv_bfloat16 *k, const float *mask_a, const float *mask_b,
+                      const float *pos_q, const float *neg_q, const float *pos_k, const float *neg_k, float *wstats,
+                      int32_t *key_count, float *scratch, int neg_type, int B, int C, int P, cudaStream_t st) {
+  const int tiles = cp2_cdiv(P, WT);
+  int *sel = neg_type == 3 ? reinterpret_cast<int *>(scratch + 3 * (size_t)B * tiles) : nullptr;
+  weighted_stats_kernel<<<B, 128, 0, st>>>(mask_a, mask_b, pos_q, neg_q, pos_k, neg_k, wstats, key_count, sel, C, P);
+  CP2_LAUNCH_CHECK();
+  const dim3 grid(tiles, B);
+  if (sel) {
+    if (C == 128) CP2_CUDA(cudaFuncSetAttribute(weighted_select_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lse_smem(128)));
+    else CP2_CUDA(cudaFuncSetAttribute(weighted_select_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lse_smem(256)));
+    for (int pass = 0; pass < 4; ++pass) {
+      if (C == 128) weighted_select_kernel<128><<<grid, WTHREADS, lse_smem(128), st>>>(q, k, mask_a, mask_b, sel, P, pass);
+      else weighted_select_kernel<256><<<grid, WTHREADS, lse_smem(256), st>>>(q, k, mask_a, mask_b, sel, P, pass);
+      CP2_LAUNCH_CHECK();
+      weighted_pick_kernel<<<B, 32, 0, st>>>(sel, wstats, pass);
+      CP2_LAUNCH_CHECK();
+    }
+  }
   return CP2_OK;
 }
-
-}  // namespace
 
 extern "C" int cp2_dense_weighted_tiles(int P) { return 3 * cp2_cdiv(P, WT) + SEL_INTS; }
 
@@ -512,21 +497,9 @@ extern "C" int cp2_dense_weighted_lse(const void *qhat_t, const void *khat_t, co
   const auto *pa = reinterpret_cast<const long long *>(pixel_ids_a), *pb = reinterpret_cast<const long long *>(pixel_ids_b);
   const auto *ra = reinterpret_cast<const long long *>(region_ids_a), *rb = reinterpret_cast<const long long *>(region_ids_b);
   const auto *q = static_cast<const __nv_bfloat16 *>(qhat_t), *k = static_cast<const __nv_bfloat16 *>(khat_t);
-  int *sel = neg_type == 3 ? reinterpret_cast<int *>(scratch + 3 * (size_t)B * tiles) : nullptr;
-  weighted_stats_kernel<<<B, 128, 0, st>>>(mask_a, mask_b, pos_q, neg_q, pos_k, neg_k, wstats, key_count, sel, C, P);
-  CP2_LAUNCH_CHECK();
+  if (int rc = weighted::prepass(q, k, mask_a, mask_b, pos_q, neg_q, pos_k, neg_k, wstats, key_count, scratch, neg_type, B, C, P, st))
+    return rc;
   const dim3 grid(tiles, B);
-  if (sel) {
-    if (C == 128) CP2_CUDA(cudaFuncSetAttribute(weighted_select_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lse_smem(128)));
-    else CP2_CUDA(cudaFuncSetAttribute(weighted_select_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lse_smem(256)));
-    for (int pass = 0; pass < 4; ++pass) {
-      if (C == 128) weighted_select_kernel<128><<<grid, WTHREADS, lse_smem(128), st>>>(q, k, mask_a, mask_b, sel, P, pass);
-      else weighted_select_kernel<256><<<grid, WTHREADS, lse_smem(256), st>>>(q, k, mask_a, mask_b, sel, P, pass);
-      CP2_LAUNCH_CHECK();
-      weighted_pick_kernel<<<B, 32, 0, st>>>(sel, wstats, pass);
-      CP2_LAUNCH_CHECK();
-    }
-  }
   float *bv = scratch + (size_t)B * tiles;
   int *bi = reinterpret_cast<int *>(scratch + 2 * (size_t)B * tiles);
   if (C == 128) {

@@ -551,6 +551,22 @@ def dense_weighted_lse(qhat_t, khat_t, mask_a, mask_b, pw, pos_q, neg_q, pos_k, 
     return lse, dense_n, wstats, count, acc_seg
 
 
+def dense_weighted_small(qhat_t, khat_t, mask_a, mask_b, pw, pos_q, neg_q, pos_k, neg_k, inv_tau):
+    """cp2_dense_weighted_small (maps that fit TMEM) -> (lse [B,P], dense_n [B], wstats [B,3], key_count [B] int32,
+    hit [B], acc [B,C,P]): the PROPOSED-mode dense loss on the tensor cores; acc feeds dense_small_bwd."""
+    B, P, C = qhat_t.shape
+    lib, dev = _lib.load(), qhat_t.device
+    f32 = dict(device=dev, dtype=torch.float32)
+    lse, dense_n, wstats = torch.empty((B, P), **f32), torch.empty((B,), **f32), torch.empty((B, 3), **f32)
+    hit, acc = torch.empty((B,), **f32), torch.empty((B, C, P), **f32)
+    count = torch.empty((B,), device=dev, dtype=torch.int32)
+    scratch = torch.empty((B, lib.cp2_dense_weighted_tiles(P)), **f32)
+    _call("cp2_dense_weighted_small", 2, lib.cp2_dense_weighted_small, _ptr(qhat_t), _ptr(khat_t), _ptr(mask_a),
+          _ptr(mask_b), *pw._args(), _ptr(pos_q), _ptr(neg_q), _ptr(pos_k), _ptr(neg_k), _ptr(lse), _ptr(dense_n),
+          _ptr(hit), _ptr(wstats), _ptr(count), _ptr(scratch), _ptr(acc), *pw._tail(inv_tau, B, C, P))
+    return lse, dense_n, wstats, count, hit, acc
+
+
 def dense_weighted_grad(qhat_t, khat_t, mask_a, mask_b, pw, lse, wstats, inv_norm, alpha, v1, v2, inv_tau, gscale=None):
     """cp2_dense_weighted_grad -> dq [B,C,P]."""
     B, P, C = qhat_t.shape
@@ -564,7 +580,8 @@ def dense_weighted_grad(qhat_t, khat_t, mask_a, mask_b, pw, lse, wstats, inv_nor
 class CP2WeightedLossFunction(torch.autograd.Function):
     """CP2LossFunction for the PROPOSED modes: same outputs, the dense loss with
     pair weights and the negative squash.  Forward = cp2_prep_features x 2 (keys not compacted),
-    cp2_global_nce, cp2_dense_weighted_lse, cp2_loss_combine; backward = cp2_dense_weighted_grad."""
+    cp2_global_nce, cp2_dense_weighted_lse, cp2_loss_combine; backward = cp2_dense_weighted_grad.  Maps that fit
+    TMEM: cp2_dense_weighted_small (tcgen05) in the forward, cp2_dense_small_bwd in the backward."""
 
     @staticmethod
     def forward(ctx, q, k, mask_a, mask_b, queue, temp_global, temp_local, lmbd_dense, include_background, pw,
@@ -580,11 +597,21 @@ class CP2WeightedLossFunction(torch.autograd.Function):
         z, G, _, acc_ins = global_nce(q_pos, queue, 1.0 / tg, k_pos if track_accuracy else None,
                                       q_neg if (bg and track_accuracy) else None,
                                       k_neg if (bg and track_accuracy) else None, shadow=queue_shadow)
-        lse, dense_n, wstats, kcnt, acc_seg = dense_weighted_lse(qh, kh, mask_a, mask_b, pw, sq, nsq, sk, nsk, 1.0 / tl)
+        ctx.small = dense_small_preferred(B, C, qh.shape[1], qh.device)
+        if ctx.small:                    # map fits TMEM: the tensor-core kernel, which also leaves the P^2 part of dq
+            lse, dense_n, wstats, kcnt, hit, acc = dense_weighted_small(qh, kh, mask_a, mask_b, pw, sq, nsq, sk, nsk,
+                                                                        1.0 / tl)
+            acc_seg = None
+        else:
+            lse, dense_n, wstats, kcnt, acc_seg = dense_weighted_lse(qh, kh, mask_a, mask_b, pw, sq, nsq, sk, nsk,
+                                                                     1.0 / tl)
+            hit = acc = None
         out, l_pos, alpha, v1, v2 = loss_combine(q_pos, k_pos, q_neg if bg else None, k_neg if bg else None,
                                                  None, None, norms_q, z, G, None, kcnt, mask_a, tg, tl, lmbd_dense,
-                                                 dense_n=dense_n)
-        ctx.save_for_backward(qh, kh, lse, mask_a, mask_b, wstats, q_inv, alpha, v1, v2)
+                                                 dense_n=dense_n, hit_seg=hit)
+        if ctx.small:
+            acc_seg = out[5:6]
+        ctx.save_for_backward(qh, acc if ctx.small else kh, lse, mask_a, mask_b, wstats, q_inv, alpha, v1, v2, kcnt)
         ctx.inv_tl, ctx.pw, ctx.q_shape = 1.0 / tl, pw, q.shape
         loss, loss_ins, loss_dense, meters = out[0], out[1], out[2], out[3:]
         if acc_ins is None:
@@ -594,11 +621,15 @@ class CP2WeightedLossFunction(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_loss, *_unused):
-        qh, kh, lse, mask_a, mask_b, wstats, q_inv, alpha, v1, v2 = ctx.saved_tensors
+        qh, kh, lse, mask_a, mask_b, wstats, q_inv, alpha, v1, v2, kcnt = ctx.saved_tensors
         g = g_loss.detach().reshape(1)
         if g.dtype != torch.float32 or not g.is_contiguous():
             g = g.float().contiguous()
-        dq = dense_weighted_grad(qh, kh, mask_a, mask_b, ctx.pw, lse, wstats, q_inv, alpha, v1, v2, ctx.inv_tl, gscale=g)
+        if ctx.small:                    # kh holds acc
+            dq = dense_small_bwd(kh, qh, mask_a, q_inv, alpha, v1, v2, key_count=kcnt, gscale=g)
+        else:
+            dq = dense_weighted_grad(qh, kh, mask_a, mask_b, ctx.pw, lse, wstats, q_inv, alpha, v1, v2, ctx.inv_tl,
+                                     gscale=g)
         return (dq.reshape(ctx.q_shape),) + (None,) * 11
 
 

@@ -312,6 +312,20 @@ int cp2_dense_weighted_grad(const void *qhat_t, const void *khat_t, const float 
                             float neg_scale, float inv_tau, int B, int C, int P, int ids_h, int ids_w, int os,
                             void *stream);
 
+/* f3 on the tensor cores — cp2_dense_weighted_lse for maps that fit TMEM (cp2_dense_small_ok(C, P)): the
+ * statistics pre-pass, then ONE tcgen05 launch gives lse, the per-image loss dense_n, the label of the arg-max
+ * pair hit [B] (acc_seg = 100 * mean(hit); may be NULL) and
+ *   acc[n,:,x] = sum_y b_y (exp(z[x,y] - lse_y) - a_x/A) w[x,y] t'(S[x,y]) khat[y,:]            ([B,C,P] f32)
+ * so that the backward is cp2_dense_small_bwd (alpha * acc + rank-1 terms, normalize backward) instead of
+ * cp2_dense_weighted_grad.  Other arguments as cp2_dense_weighted_lse. */
+int cp2_dense_weighted_small(const void *qhat_t, const void *khat_t, const float *mask_a, const float *mask_b,
+                             const int64_t *pixel_ids_a, const int64_t *pixel_ids_b, const int64_t *region_ids_a,
+                             const int64_t *region_ids_b, const float *pos_q, const float *neg_q, const float *pos_k,
+                             const float *neg_k, float *lse, float *dense_n, float *hit, float *wstats,
+                             int32_t *key_count, float *scratch, float *acc, float w_pix, float w_reg, float w_not,
+                             int neg_type, float neg_scale, float inv_tau, int B, int C, int P, int ids_h, int ids_w,
+                             int os, void *stream);
+
 /* f4 — acc_seg without the [B,P,P] logits.  Replaces builder.py:1442-1448:
  *   hit[n] = mask_a[n,x*] * mask_b[n,y*] at (x*,y*) = argmax_{x,y} qhat_x . khat_y (first occurrence, flat
  *   index x*P+y as the reference's reshape); acc[0] = 100 * mean_n hit[n].

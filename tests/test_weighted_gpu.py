@@ -126,6 +126,17 @@ def test_weighted_dense_vs_oracle(ops, B, C, hw, os_, neg, tl, weights):
     dq3 = ops.dense_weighted_grad(qt, kt, mad, mbd, pw, lse, wstats, q_inv, alpha.cuda(), v1.cuda(), None, 1.0 / tl,
                                   gscale=torch.tensor([3.0], device="cuda"))
     assert rel_l2(dq3, 3.0 * dq) < 1e-5
+    # the tensor-core implementation for maps that fit TMEM: same contract, acc instead of a second P^2 pass
+    if ops.dense_small_ok(C, P):
+        lse2, dn2, ws2, cnt2, hit, acc = ops.dense_weighted_small(qt, kt, mad, mbd, pw, sq, nsq, sk, nsk, 1.0 / tl)
+        np.testing.assert_allclose(dn2.mean().item(), ref.item(), rtol=LOSS_RTOL)
+        np.testing.assert_allclose(dn2.cpu().numpy(), dense_n.cpu().numpy(), rtol=2e-5)
+        np.testing.assert_allclose(hit.mean().item() * 100.0, want.item(), rtol=1e-6)
+        assert torch.equal(cnt2, cnt) and torch.equal(ws2, wstats)
+        assert torch.allclose(lse2, lse, rtol=0, atol=1e-4), float((lse2 - lse).abs().max())
+        dq2 = ops.dense_small_bwd(acc, qt, mad, q_inv, alpha.cuda(), v1.cuda(), None)
+        assert rel_l2(dq2, qr.grad) < GRAD_REL_L2, rel_l2(dq2, qr.grad)
+        assert rel_l2(dq2, dq) < 6e-3, rel_l2(dq2, dq)          # g is rounded to bf16 for the tensor cores
 
 
 def test_weighted_all_ones_equals_cp2_path(ops):
