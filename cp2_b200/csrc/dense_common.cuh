@@ -27,9 +27,9 @@ __device__ __forceinline__ uint64_t kmajor_desc(uint32_t tile_addr, int kk, int 
 // One 32-column chunk of the backward softmax: P~ = exp2(S*scale + nl) packed to bf16 pairs.  Software
 // pipeline over four 8-column groups in explicit program order: X(k) = scale/offset (FFMA2), E(k) = the
 // exponentials (MUFU, or the FMA-pipe polynomial for the first PF pairs of a group), C(k) = bf16 pack.
-template <int PF>
+template <int PF, bool ZS = false>
 __device__ __forceinline__ void softmax_chunk_bwd(const uint32_t (&r)[32], uint32_t nl_saddr, f2 scale2,
-                                                  uint32_t (&pk)[16]) {
+                                                  uint32_t (&pk)[16], f2 *zsum = nullptr) {
   float4 n[8];
 #pragma unroll
   for (int u = 0; u < 8; ++u) n[u] = lds_f4(nl_saddr + u * 16);
@@ -62,6 +62,7 @@ __device__ __forceinline__ void softmax_chunk_bwd(const uint32_t (&r)[32], uint3
     for (int p = 0; p < 4; ++p) {
       const int j = 4 * k + p;
       float a, c;
+      if constexpr (ZS) *zsum = f2_add(*zsum, x[j]);      // fp32 row sums of P~ (queue-sums mode)
       f2_unpack(x[j], a, c);
       pk[j] = pack_bf16x2_v(a, c);
     }

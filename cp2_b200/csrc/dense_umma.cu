@@ -196,7 +196,13 @@ struct GradCfg {
   static_assert(2 * TY + ND * C <= 512, "TMEM budget");
 };
 
-template <int C, int TY, int NST, int NQ, int ND, int PF>
+// MODE 0: the dense loss's backward (items = (image, 128 query pixels), keys = the image's key pixels).
+// MODE 1: queue sums of an InfoNCE with MANY rows (f2, builder.py:866-873): one "image", queries = the N rows,
+//         keys = the K queue entries cut into B = nsplit contiguous ranges of `tps` key tiles; items = (range, 128
+//         rows).  nl holds -log2(e)/tau for real entries (NL_MASKED past K), so P~ = exp((l-1)/tau); the softmax
+//         warps also keep fp32 row sums of P~ (z), and the epilogue writes the raw accumulator:
+//           dq[(s*P + r)*C + c] = sum_{k in range s} P~[r,k] u_k[c],   zp[(2s+half)*P_pad + r] = partial z.
+template <int C, int TY, int NST, int NQ, int ND, int PF, int MODE = 0>
 __global__ void __launch_bounds__(GRAD_THREADS, 1)
 dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                   const __nv_bfloat16 *__restrict__ qhat, const float *__restrict__ nl,
@@ -204,7 +210,8 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
                   const float *__restrict__ inv_norm, const float *__restrict__ alpha,
                   const float *__restrict__ v1, const float *__restrict__ v2,
                   const float *__restrict__ gscale, float *__restrict__ dq,
-                  float scale_log2, int B, int P, int P_pad, long long *__restrict__ trace) {
+                  float scale_log2, int B, int P, int P_pad, long long *__restrict__ trace,
+                  float *__restrict__ zp, int tps, int ktiles) {
   using Cfg = GradCfg<C, TY, NST, NQ, ND>;
   // optional per-CTA wait-time accounting (test-only; cp2_dbg_dense_trace): slot k of trace[blockIdx.x*16+k]
   long long tr_a = 0, tr_b = 0, tr_c = 0, tr_d = 0;
@@ -251,9 +258,13 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
   const uint32_t tmem_D = tmem + 2 * TY;
 
   auto key_tiles = [&](int b) {
+    if constexpr (MODE == 1) return max(0, min(tps, ktiles - b * tps));
     const int cnt = key_count ? min(max(key_count[b], 0), P) : P;
     return (cnt + TY - 1) / TY;
   };
+  // MODE 1: the operands are single "images" (batch coordinate 0), the key tiles of range b start at b * tps
+  auto img = [&](int b) { return MODE == 1 ? 0 : b; };
+  auto tile0 = [&](int b) { return MODE == 1 ? b * tps : 0; };
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
@@ -265,14 +276,15 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
         twait(&q_empty[qb], ((it / NQ) & 1) ^ 1, tr_a);
         mbar_expect_tx(&q_full[qb], Cfg::OPER_Q);
         for (int kb = 0; kb < C / 64; ++kb)
-          tma_load_3d(sQ + qb * Cfg::OPER_Q + kb * Cfg::QBOX, &tm_q, &q_full[qb], kb * 64, x0, b);
+          tma_load_3d(sQ + qb * Cfg::OPER_Q + kb * Cfg::QBOX, &tm_q, &q_full[qb], kb * 64, x0, img(b));
         for (int j = 0; j < ny; ++j, ++g) {
           const int s = g % NST;
           twait(&kempty[s], ((g / NST) & 1) ^ 1, tr_b);
           mbar_expect_tx(&kfull[s], Cfg::OPER_K + TY * 4);
           for (int kb = 0; kb < C / 64; ++kb)
-            tma_load_3d(sK + s * Cfg::OPER_K + kb * Cfg::KBOX, &tm_k, &kfull[s], kb * 64, j * TY, b);
-          bulk_load_1d(nlbuf + s * TY, nl + (long long)b * P_pad + j * TY, TY * 4, &kfull[s]);
+            tma_load_3d(sK + s * Cfg::OPER_K + kb * Cfg::KBOX, &tm_k, &kfull[s], kb * 64, (tile0(b) + j) * TY, img(b));
+          bulk_load_1d(nlbuf + s * TY, nl + (MODE == 1 ? 0 : (long long)b * P_pad) + (long long)(tile0(b) + j) * TY,
+                       TY * 4, &kfull[s]);
         }
       }
     }
@@ -349,6 +361,7 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
     int g = 0;
     for (int w = blockIdx.x; w < items; w += gridDim.x) {
       const int ny = key_tiles(w / nxt);
+      f2 zsum = f2_pack(0.f, 0.f);
       for (int j = 0; j < ny; ++j, ++g) {
         const int s = g % NST;
         const uint32_t tS = tmem + (g & 1) * TY + lane_off + half * W;
@@ -364,13 +377,19 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
           tmem_wait_ld();
           if (ch + 1 < W / 32) tmem_ld32(tS + (ch + 1) * 32, rb[(ch + 1) & 1]);
           const uint32_t(&r)[32] = rb[ch & 1];
-          softmax_chunk_bwd<PF>(r, nl_saddr + ch * 128, scale2, pk);
+          softmax_chunk_bwd<PF, MODE == 1>(r, nl_saddr + ch * 128, scale2, pk, &zsum);
           tmem_st16(tS + ch * 16, pk);
         }
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[g & 1]);
+      }
+      if constexpr (MODE == 1) {
+        float z0, z1;
+        f2_unpack(zsum, z0, z1);
+        const int x = (w % nxt) * TILE + quad * 32 + lane;
+        zp[(long long)(2 * (w / nxt) + half) * P_pad + x] = z0 + z1;
       }
     }
   } else {
@@ -385,6 +404,33 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       const int db = it % ND;
       const int x = x0 + row;
       const bool valid = x < P;
+      if constexpr (MODE == 1) {                     // queue sums: the raw accumulator row, 512 B per thread
+        twait(&d_full[db], (it / ND) & 1, tr_a);
+        tc_fence_after();
+        const uint32_t tDq = tmem_D + db * C + lane_off;
+        float4 *dst = reinterpret_cast<float4 *>(dq + ((long long)b * P + (valid ? x : 0)) * C);
+#pragma unroll 1
+        for (int ch = 0; ch < C / 32; ++ch) {
+          uint32_t r[32];
+          if (ny > 0) {
+            tmem_ld32(tDq + ch * 32, r);
+            tmem_wait_ld();
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) r[i] = 0u;
+          }
+          if (valid) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+              dst[ch * 8 + u] = make_float4(__uint_as_float(r[4 * u]), __uint_as_float(r[4 * u + 1]),
+                                            __uint_as_float(r[4 * u + 2]), __uint_as_float(r[4 * u + 3]));
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&d_empty[db]);
+        continue;
+      }
       const float a = valid ? mask_a[(long long)b * P + x] : 0.f;
       const float inr = valid ? inv_norm[(long long)b * P + x] : 0.f;
       const float al = (ny > 0) ? alpha[b] * gup : 0.f;
@@ -537,12 +583,50 @@ int launch_grad(const CUtensorMap &tq, const CUtensorMap &tk, const void *qhat, 
   const int grid = (int)(items < cp2_num_sms() ? items : cp2_num_sms());
   kern<<<grid, GRAD_THREADS, Cfg::SMEM, st>>>(tq, tk, static_cast<const __nv_bfloat16 *>(qhat), nl, key_count,
                                               mask_a, inv_norm, alpha, v1, v2, gscale, dq, scale_log2, B, P, P_pad,
-                                              g_dense_trace);
+                                              g_dense_trace, nullptr, 0, 0);
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}
+
+// f2: queue sums on the backward kernel (MODE 1).  C = 128.
+int launch_queue_sums(const CUtensorMap &tq, const CUtensorMap &tk, const float *nl, float *zp, float *gacc,
+                      float scale_log2, int nsplit, int N, int N_pad, int tps, int ktiles, cudaStream_t st) {
+  using Cfg = GradCfg<128, 128, 5, 1, 2>;
+  auto kern = dense_grad_kernel<128, 128, 5, 1, 2, 1, 1>;
+  CP2_SMEM_ONCE(kern, Cfg::SMEM);
+  const long long items = (long long)nsplit * cp2_cdiv(N, TILE);
+  const int grid = (int)(items < cp2_num_sms() ? items : cp2_num_sms());
+  kern<<<grid, GRAD_THREADS, Cfg::SMEM, st>>>(tq, tk, nullptr, nl, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                                              nullptr, gacc, scale_log2, nsplit, N, N_pad, nullptr, zp, tps, ktiles);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }
 
 }  // namespace
+
+// ranges the queue is cut into so that (ranges x row tiles) fills the SMs
+extern "C" int cp2_queue_sums_split(int N, int K) {
+  if (N <= 0 || K <= 0) return 1;
+  const int nxt = cp2_cdiv(N, TILE), ktiles = cp2_cdiv(K, 128);
+  int s = cp2_num_sms() / nxt;
+  s = s < 1 ? 1 : (s > 8 ? 8 : s);
+  return s < ktiles ? s : ktiles;
+}
+
+extern "C" int cp2_queue_sums(const void *rows_bf, const void *queue_bf, const float *nl, float *zp, float *gacc,
+                              float inv_tau, int N, int C, int K, void *stream) {
+  CP2_REQUIRE(C == 128, "cp2_queue_sums: C=%d unsupported (128)", C);
+  CP2_REQUIRE(N > 0 && K > 0, "cp2_queue_sums: bad shape N=%d K=%d", N, K);
+  CP2_REQUIRE(inv_tau > 0.f && inv_tau <= 16.f, "cp2_queue_sums: 1/tau=%g outside (0, 16]", (double)inv_tau);
+  CP2_REQUIRE(rows_bf && queue_bf && nl && zp && gacc, "cp2_queue_sums: null pointer");
+  const int nsplit = cp2_queue_sums_split(N, K), ktiles = cp2_cdiv(K, 128), tps = cp2_cdiv(ktiles, nsplit);
+  CUtensorMap tq, tk;
+  int rc;
+  if ((rc = make_feature_tmap(&tq, rows_bf, 1, C, N, TILE)) != CP2_OK) return rc;
+  if ((rc = make_feature_tmap(&tk, queue_bf, 1, C, K, 128)) != CP2_OK) return rc;
+  return launch_queue_sums(tq, tk, nl, zp, gacc, inv_tau * LOG2E, nsplit, N, cp2_dense_pad(N), tps, ktiles,
+                           static_cast<cudaStream_t>(stream));
+}
 
 #ifdef CP2_DEBUG_BUILD
 extern "C" int cp2_dbg_dense_trace(long long *buf) {   // [n_sms * 16] device counters or NULL (cp2_b200_debug.h)

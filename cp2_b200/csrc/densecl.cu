@@ -18,21 +18,27 @@ constexpr int RT = 256;                 // threads: 8 rows per CTA, one warp per
 __global__ void __launch_bounds__(RT)
 rows_nce_kernel(const float *__restrict__ rows, const float *__restrict__ pos_keys, const float *__restrict__ z,
                 const float *__restrict__ G, float *__restrict__ terms, float *__restrict__ dq, float inv_tau,
-                int N, int C) {
+                int N, int C, int nz, long long zstride, int ng, long long gstride) {
+  // z and G may arrive as partial sums (cp2_queue_sums): z[r] = sum_i z[i*zstride + r], G[r,:] likewise (fixed order)
   const int lane = threadIdx.x & 31, r = blockIdx.x * (RT / 32) + (threadIdx.x >> 5);
   if (r >= N) return;
   const float *q = rows + (long long)r * C, *kp = pos_keys + (long long)r * C, *g = G + (long long)r * C;
+  float zr = 0.f;
+  for (int i = 0; i < nz; ++i) zr += z[(long long)i * zstride + r];
   float lp = 0.f;
   for (int c = lane; c < C; c += 32) lp = fmaf(q[c], kp[c], lp);
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) lp += __shfl_xor_sync(0xffffffffu, lp, off);
   // shift 1 as in cp2_global_nce: z = sum_k exp((l_k - 1) / tau)
   const float e_pos = expf((lp - 1.f) * inv_tau);
-  const float Z = z[r] + e_pos, rZ = 1.f / Z, scale = inv_tau / (float)N;
+  const float Z = zr + e_pos, rZ = 1.f / Z, scale = inv_tau / (float)N;
   if (lane == 0) terms[r] = logf(Z) + (1.f - lp) * inv_tau;
   if (dq)
-    for (int c = lane; c < C; c += 32)
-      dq[(long long)r * C + c] = (fmaf(e_pos, kp[c], g[c]) * rZ - kp[c]) * scale;
+    for (int c = lane; c < C; c += 32) {
+      float gc = 0.f;
+      for (int i = 0; i < ng; ++i) gc += g[(long long)i * gstride + c];
+      dq[(long long)r * C + c] = (fmaf(e_pos, kp[c], gc) * rZ - kp[c]) * scale;
+    }
 }
 
 // loss[0] = mean(terms), fixed summation order.  One CTA.
@@ -88,12 +94,15 @@ positive_keys_kernel(const float *__restrict__ k_local, const long long *__restr
 }  // namespace
 
 extern "C" int cp2_rows_nce(const float *rows, const float *pos_keys, const float *z, const float *G, float *loss,
-                            float *terms, float *dq, float inv_tau, int N, int C, void *stream) {
+                            float *terms, float *dq, float inv_tau, int N, int C, int nz, int64_t zstride, int ng,
+                            int64_t gstride, void *stream) {
   CP2_REQUIRE(N > 0 && C > 0, "cp2_rows_nce: bad shape N=%d C=%d", N, C);
   CP2_REQUIRE(rows && pos_keys && z && G && loss && terms, "cp2_rows_nce: null pointer");
   CP2_REQUIRE(inv_tau > 0.f, "cp2_rows_nce: bad temperature");
+  CP2_REQUIRE(nz >= 1 && ng >= 1, "cp2_rows_nce: bad partial counts nz=%d ng=%d", nz, ng);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  rows_nce_kernel<<<cp2_cdiv(N, RT / 32), RT, 0, st>>>(rows, pos_keys, z, G, terms, dq, inv_tau, N, C);
+  rows_nce_kernel<<<cp2_cdiv(N, RT / 32), RT, 0, st>>>(rows, pos_keys, z, G, terms, dq, inv_tau, N, C, nz,
+                                                      (long long)zstride, ng, (long long)gstride);
   CP2_LAUNCH_CHECK();
   rows_mean_kernel<<<1, RT, 0, st>>>(terms, loss, N);
   CP2_LAUNCH_CHECK();

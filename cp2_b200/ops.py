@@ -660,64 +660,69 @@ def cp2_loss(q, k, mask_a, mask_b, queue, temp_global=0.2, temp_local=1.0, lmbd_
 
 # ------------------------------------------------- f2: forward_densecl losses
 def rows_nce(rows, pos_keys, z, G, inv_tau, want_grad=True):
-    """cp2_rows_nce -> (loss [1], terms [N], dq [N,C] | None)."""
+    """cp2_rows_nce -> (loss [1], terms [N], dq [N,C] | None).  z [N] / G [N,C], or partial sums
+    z [nz, stride >= N] / G [ng, N, C] from queue_sums_tc (added inside the kernel, fixed order)."""
     N, C = rows.shape
     dev = rows.device
     loss = torch.empty((1,), device=dev, dtype=torch.float32)
     terms = torch.empty((N,), device=dev, dtype=torch.float32)
     dq = torch.empty((N, C), device=dev, dtype=torch.float32) if want_grad else None
+    nz, zs = (z.shape[0], z.stride(0)) if z.dim() == 2 else (1, 0)
+    ng, gs = (G.shape[0], G.stride(0)) if G.dim() == 3 else (1, 0)
     _call("cp2_rows_nce", 2, _lib.load().cp2_rows_nce, _ptr(rows), _ptr(pos_keys), _ptr(z), _ptr(G), _ptr(loss),
-          _ptr(terms), _ptr(dq), float(inv_tau), N, C, _stream())
+          _ptr(terms), _ptr(dq), float(inv_tau), N, C, nz, zs, ng, gs, _stream())
     return loss, terms, dq
 
 
-TC_ROWS_MIN = 1024      # from this many rows on, the queue sums run on the dense-loss tensor-core kernels
+TC_ROWS_MIN = 1024      # from this many rows on, the queue sums run on the dense loss's tensor-core kernel
+_NL_CACHE = {}
+
+
+def _queue_nl(K, inv_tau, device):
+    """nl operand of cp2_queue_sums: -log2(e)/tau per real queue entry, -80 for the padding up to a multiple of
+    128.  Built once per (K, tau, device)."""
+    key = (int(K), float(inv_tau), str(device))
+    if key not in _NL_CACHE:
+        kp = (K + 127) // 128 * 128
+        nl = torch.full((kp,), -float(inv_tau) * 1.4426950408889634, device=device, dtype=torch.float32)
+        nl[K:] = -80.0
+        _NL_CACHE[key] = nl
+    return _NL_CACHE[key]
 
 
 @torch.no_grad()
-def queue_sums_tc(rows, queue, inv_tau, shadow=None):
-    """z [N], G [N,C] as cp2_global_nce defines them (z = sum_k exp((l_k-1)/tau), G = sum_k exp((l_k-1)/tau) u_k),
-    for MANY rows, on the tcgen05 kernels of the dense loss instead of one queue pass per 32 rows: the queue is
-    cut into blocks of Pb = ceil128(N) entries, block n and the rows form "image" n of a [nb,Pb,Pb] problem;
-    cp2_dense_lse (queue entries on its summed axis) gives log sum exp per block and row, cp2_dense_grad
-    (rows as its query axis, lse := 1/tau, unit coefficients) gives the exp-weighted sums of queue entries.
-    Zero padding: padded queue entries add exp(-1/tau) each to z (subtracted) and nothing to G.
-    G comes back projected onto each row's tangent space (cp2_dense_grad's normalize backward with unit
-    norms); the F.normalize that produced the rows annihilates the missing component anyway."""
-    N, C = rows.shape
+def queue_sums_tc(rows_bf, queue, inv_tau, shadow=None):
+    """Partial sums of z [N] = sum_k exp((l_k-1)/tau) and G [N,C] = sum_k exp((l_k-1)/tau) u_k (cp2_global_nce's
+    definitions) for MANY rows in ONE launch of the dense loss's backward kernel in its rectangular mode
+    (cp2_queue_sums): queries = rows_bf [N,C] bf16 unit rows, keys = the queue's bf16 shadow.
+    -> (zp [2*split, pad128(N)], gacc [split, N, C]) for rows_nce; no ATen arithmetic."""
+    N, C = rows_bf.shape
     K = queue.shape[1]
-    dev = rows.device
-    Pb = (N + 127) // 128 * 128
-    nb = (K + Pb - 1) // Pb
-    pad = nb * Pb - K
-    # the queue's bf16 entry-major shadow (kept in step by cp2_enqueue) followed by zero rows IS the block operand
-    qblocks = (shadow if shadow is not None else QueueShadow()).padded(queue, nb * Pb).view(nb, Pb, C)
-    rt = torch.zeros((Pb, C), device=dev, dtype=torch.bfloat16)
-    rt[:N] = rows
-    rblocks = rt.unsqueeze(0).expand(nb, Pb, C).contiguous()
-    lse = dense_lse(qblocks, rblocks, inv_tau)                          # [nb,Pb]: log sum over the block's entries
-    z = torch.exp(lse[:, :N] - inv_tau).sum(0) - pad * math.exp(-inv_tau)
-    shift = torch.full((nb, Pb), float(inv_tau), device=dev, dtype=torch.float32)
-    zeros_m = torch.zeros((nb, Pb), device=dev, dtype=torch.float32)
-    acc = dense_grad(rblocks, qblocks, shift, zeros_m, None, torch.ones_like(zeros_m),
-                     torch.ones((nb,), device=dev), torch.zeros((nb, C), device=dev), None, inv_tau)
-    G = acc.sum(0)[:, :N].t().contiguous()
-    return z, G
+    dev = rows_bf.device
+    lib = _lib.load()
+    qbf = (shadow if shadow is not None else QueueShadow()).get(queue)
+    split = lib.cp2_queue_sums_split(N, K)
+    zp = torch.empty((2 * split, lib.cp2_dense_pad(N)), device=dev, dtype=torch.float32)
+    gacc = torch.empty((split, N, C), device=dev, dtype=torch.float32)
+    _call("cp2_queue_sums", 1, lib.cp2_queue_sums, _ptr(rows_bf), _ptr(qbf), _ptr(_queue_nl(K, inv_tau, dev)), _ptr(zp),
+          _ptr(gacc), float(inv_tau), N, C, K, _stream())
+    return zp, gacc
 
 
 class RowsInfoNCEFunction(torch.autograd.Function):
     """`ContrastiveHead(pos, neg, temperature)` (builder.py:150-176) with pos = rows . pos_keys and
     neg = rows @ queue, never materialising the [N,1+K] logits: the queue sums come from cp2_global_nce (few
-    rows: one pass over the queue per 32 rows) or from the dense loss's tensor-core kernels (`queue_sums_tc`,
-    N >= TC_ROWS_MIN), then cp2_rows_nce.  With the tensor-core path the gradient is the tangential one
-    (rows are unit vectors produced by F.normalize, whose backward drops the radial part anyway).  Gradient to `rows` only (keys and queue are
-    detached in the reference, builder.py:726, 768, 872)."""
+    rows: one pass over the queue per 32 rows) or from the dense loss's tensor-core backward kernel in its
+    rectangular mode (`queue_sums_tc` / cp2_queue_sums, N >= TC_ROWS_MIN, one launch), then cp2_rows_nce.
+    Gradient to `rows` only (keys and queue are detached in the reference, builder.py:726, 768, 872)."""
 
     @staticmethod
-    def forward(ctx, rows, pos_keys, queue, temp, shadow):
+    def forward(ctx, rows, pos_keys, queue, temp, shadow, rows_bf=None):
         rows_c, pos_c = _f32c(rows.detach()), _f32c(pos_keys.detach())
-        if rows_c.shape[0] >= TC_ROWS_MIN:
-            z, G = queue_sums_tc(rows_c, queue, 1.0 / float(temp), shadow)
+        if rows_c.shape[0] >= TC_ROWS_MIN and rows_c.shape[1] == 128:
+            if rows_bf is None:
+                rows_bf = rows_c.to(torch.bfloat16)
+            z, G = queue_sums_tc(rows_bf, queue, 1.0 / float(temp), shadow)
         else:
             z, G = global_nce(rows_c, queue, 1.0 / float(temp), shadow=shadow)[:2]
         loss, _, dq = rows_nce(rows_c, pos_c, z, G, 1.0 / float(temp), want_grad=True)
@@ -727,12 +732,13 @@ class RowsInfoNCEFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         (dq,) = ctx.saved_tensors
-        return dq * g, None, None, None, None
+        return dq * g, None, None, None, None, None
 
 
-def rows_infonce(rows, pos_keys, queue, temp, shadow=None):
-    """rows, pos_keys [N,C] (rows unit vectors), queue [C,K] -> 0-d loss with a gradient to rows."""
-    return RowsInfoNCEFunction.apply(rows, pos_keys, queue, temp, shadow)
+def rows_infonce(rows, pos_keys, queue, temp, shadow=None, rows_bf=None):
+    """rows, pos_keys [N,C] (rows unit vectors), queue [C,K] -> 0-d loss with a gradient to rows.
+    rows_bf: the rows as a bf16 [N,C] tensor if the caller already has it (cp2_prep_features' operand)."""
+    return RowsInfoNCEFunction.apply(rows, pos_keys, queue, temp, shadow, rows_bf)
 
 
 @torch.no_grad()
@@ -772,7 +778,11 @@ def densecl_loss(embd_q, embd_k, q_local, k_local, q_global, k_global, queue, qu
     idx = densecl_match(embd_q.detach(), embd_k.detach())
     kp = positive_keys(k_local.detach(), idx, pix_q, pix_k, output_stride, lmbd_coordinate)
     rows = q_local.permute(0, 2, 1).reshape(B * P, C)
-    loss_l = rows_infonce(rows, kp, queue2, temp_local, shadow2)
+    rows_bf = None
+    if B * P >= TC_ROWS_MIN and C == 128:       # bf16 [B,P,C] operand of the tensor-core queue sums (mask unused)
+        rows_bf = prep_features(q_local.detach(), _persistent_zero("densecl_mask", 4 * B * P, q_local.device)
+                                .view(torch.float32)[: B * P].view(B, P))[0].view(B * P, C)
+    loss_l = rows_infonce(rows, kp, queue2, temp_local, shadow2, rows_bf)
     return (1 - lmbd_dense) * loss_g + lmbd_dense * loss_l, loss_g, loss_l
 
 

@@ -340,9 +340,26 @@ int cp2_dense_top1(const float *q, const float *k, const float *mask_a, const fl
  * (builder.py:866-873, 906-908; N = B*S^2, rows = q_local pixels, queue2).
  *   l_r = rows[r].pos_keys[r];  terms[r] = log(z[r] + exp((l_r-1)/tau)) + (1-l_r)/tau;  loss[0] = mean_r terms
  *   dq[r,:] = d loss / d rows[r,:] = ((G[r,:] + exp((l_r-1)/tau) pos_keys[r,:]) / Z_r - pos_keys[r,:]) / (N tau)
- * rows, pos_keys [N,C] f32 (rows unit vectors); terms [N] scratch/out; dq may be NULL (no gradient wanted). */
+ * rows, pos_keys [N,C] f32 (rows unit vectors); terms [N] scratch/out; dq may be NULL (no gradient wanted).
+ * z / G may be given as nz / ng partial sums, zstride / gstride floats apart (cp2_queue_sums); 1, 0 otherwise. */
 int cp2_rows_nce(const float *rows, const float *pos_keys, const float *z, const float *G, float *loss,
-                 float *terms, float *dq, float inv_tau, int N, int C, void *stream);
+                 float *terms, float *dq, float inv_tau, int N, int C, int nz, int64_t zstride, int ng,
+                 int64_t gstride, void *stream);
+
+/* f2 — the queue sums z, G of cp2_global_nce for MANY rows (the local InfoNCE of forward_densecl has
+ * N = B*S^2 = 6272 rows against the 65536-entry queue2: builder.py:866-873) on the tensor cores: the dense
+ * loss's backward kernel in its rectangular mode (queries = the rows, keys = the queue entries, cut into
+ * cp2_queue_sums_split(N,K) contiguous ranges so that ranges x 128-row tiles fill the SMs).  PARTIAL sums come
+ * back; cp2_rows_nce adds them in a fixed order (nz = 2*split, zstride = cp2_dense_pad(N); ng = split,
+ * gstride = N*C):
+ *   zp   [2*split, cp2_dense_pad(N)] f32:  sum_i zp[i,r]   = sum_k exp((rows[r].u_k - 1)/tau)
+ *   gacc [split, N, C] f32:                sum_s gacc[s,r] = sum_k exp((rows[r].u_k - 1)/tau) u_k
+ *   rows_bf  [N,C] bf16 unit rows (cp2_prep_features' operand layout); queue_bf [K,C] bf16 (the queue's shadow);
+ *   nl [ceil128(K)] f32 = -log2(e)/tau for k < K, -80 for the padding (built once per (K, tau)).
+ * C = 128; 0 < inv_tau <= 16. */
+int cp2_queue_sums_split(int N, int K);
+int cp2_queue_sums(const void *rows_bf, const void *queue_bf, const float *nl, float *zp, float *gacc,
+                   float inv_tau, int N, int C, int K, void *stream);
 
 /* f2 — the positive of every query pixel (builder.py:824-855), as a vector: kp[n*P+x,:] = k_local[n,:,idx[n,x]],
  * and where key pixels share query pixel x's id: (1-lmbd) * that + lmbd * sum_{y: pix_k[y]==pix_q[x]} k_local[n,:,y]
