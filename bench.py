@@ -541,7 +541,7 @@ def weighted_sweep(peaks, iters=20):
 # ------------------------------------------------------------------ forward_densecl loss microbench
 def densecl_sweep(peaks, iters=10):
     """Row f2 at the DenseCL scripts' shape (B=32, 14x14 backbone map, 2048-d backbone features, dim 128,
-    K=65536, tau 0.2): ops.densecl_loss forward + backward (the backbone match is a cuBLAS bmm in both arms)
+    K=65536, tau 0.2): ops.densecl_loss forward + backward (backbone match = cp2_densecl_match)
     against the eager torch formulation of builder.py:762-931.  L2 flushed between iterations."""
     import torch
     import torch.nn.functional as F
@@ -591,8 +591,9 @@ def densecl_sweep(peaks, iters=10):
     t_ours, t_eager = timeit(ours, iters), timeit(eager, 5)
     return [{"B": B, "P": P, "C": C, "K": K, "rows": B * P, "densecl_loss_fwd_bwd_us": round(t_ours, 1),
              "eager_torch_us": round(t_eager, 1), "speedup_vs_eager": round(t_eager / t_ours, 2),
-             "note": "queue sums of the 6272-row local InfoNCE on the dense-loss tcgen05 kernels (11 blocks of "
-                     "6272 queue entries), global InfoNCE on cp2_global_nce, backbone match = cuBLAS bmm in both arms"}]
+             "note": "queue sums of the 6272-row local InfoNCE in one launch of the dense loss's tcgen05 backward "
+                     "kernel (cp2_queue_sums, rectangular mode), global InfoNCE on cp2_global_nce, backbone match = "
+                     "cp2_densecl_match (tcgen05, bf16 hi+lo split of the fp32 features); eager arm: cuBLAS bmm"}]
 
 
 # ------------------------------------------------------------------------------ own arm

@@ -763,9 +763,17 @@ def positive_keys(k_local, idx, pix_q=None, pix_k=None, output_stride=1, lmbd_co
 @torch.no_grad()
 def densecl_match(embd_q, embd_k):
     """builder.py:817-821: idx[n,x] = argmax_y embd_q[n,:,x] . embd_k[n,:,y] on the 2048-d backbone features.
-    A plain batched library GEMM (cuBLAS through torch.bmm, fp32) + arg-max: the only [B,S^2,S^2] tensor
-    the path still writes (4.9 MB at configs[1])."""
-    return torch.bmm(embd_q.transpose(1, 2), embd_k).argmax(dim=2)
+    cp2_densecl_match: one tcgen05 kernel (fp32 operands split into bf16 hi + lo on chip, the [B,S^2,S^2]
+    similarities stay in TMEM).  Maps above 256 pixels or channel counts off the 32-grid: torch.bmm + argmax."""
+    _need_cuda(embd_q, embd_k)
+    B, Cb, P = embd_q.shape
+    if P > 256 or Cb % 32 != 0:
+        return torch.bmm(embd_q.transpose(1, 2), embd_k).argmax(dim=2)
+    embd_q, embd_k = _f32c(embd_q), _f32c(embd_k)
+    idx = torch.empty((B, P), device=embd_q.device, dtype=torch.int64)
+    _call("cp2_densecl_match", 1, _lib.load().cp2_densecl_match, _ptr(embd_q), _ptr(embd_k), _ptr(idx), B, Cb, P,
+          _stream())
+    return idx
 
 
 def densecl_loss(embd_q, embd_k, q_local, k_local, q_global, k_global, queue, queue2, temp_global=0.2,

@@ -373,6 +373,13 @@ int cp2_positive_keys(const float *k_local, const int64_t *idx, const int64_t *p
                       float *kp, float lmbd_coordinate, int B, int C, int P, int ids_h, int ids_w, int os,
                       void *stream);
 
+/* f2 — the backbone match of forward_densecl (builder.py:817-821) in one tcgen05 kernel:
+ *   idx[n,x] = argmax_y sum_c embd_q[n,c,x] * embd_k[n,c,y]        (first largest y)
+ * embd_q, embd_k : [B,Cb,P] f32 (the backbone feature maps, pixel axis contiguous), 16-byte aligned;
+ * idx : [B,P] int64.  Each fp32 value enters as two bf16 terms (hi + lo; three products per pair), i.e. the
+ * similarity to ~2^-16 relative; the [B,P,P] matrix exists only in TMEM.  P <= 256, Cb a multiple of 32. */
+int cp2_densecl_match(const float *embd_q, const float *embd_k, int64_t *idx, int B, int Cb, int P, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

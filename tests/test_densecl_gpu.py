@@ -78,6 +78,36 @@ def test_rows_infonce_vs_oracle(ops, N, K, tau):
     assert rel_l2(rd.grad, rr.grad) < GRAD_REL_L2, rel_l2(rd.grad, rr.grad)
 
 
+@pytest.mark.parametrize("B,Cb,P", [(4, 2048, 196), (2, 256, 49), (3, 64, 128), (2, 512, 256), (1, 2048, 50),
+                                    (2, 96, 131)])
+def test_densecl_match_vs_oracle(ops, B, Cb, P):
+    """cp2_densecl_match (tcgen05, bf16 hi+lo operands) against the fp64 arg-max of builder.py:817-821, on
+    post-ReLU-like (non-negative) and signed features; planted winners; exact duplicates keep the first index."""
+    gen = torch.Generator().manual_seed(Cb + P)
+    for signed in (False, True):
+        eq = torch.randn(B, Cb, P, generator=gen)
+        ek = torch.randn(B, Cb, P, generator=gen)
+        if not signed:
+            eq, ek = eq.relu(), ek.relu()
+        eq, ek = F.normalize(eq, dim=1), F.normalize(ek, dim=1)
+        ek[:, :, 3] = eq[:, :, P - 1] * 1.5                  # planted: query P-1 matches key 3
+        if P > 10:
+            ek[:, :, 7] = ek[:, :, 5]                        # exact duplicate columns: the first one must win
+        sim = torch.einsum("ncx,ncy->nxy", eq.double(), ek.double())
+        want = sim.argmax(dim=2)
+        got = ops.densecl_match(eq.cuda(), ek.cuda()).cpu()
+        assert got.dtype == torch.int64 and got.shape == (B, P)
+        assert (got[:, P - 1] == 3).all()
+        assert not (got == 7).any() or P <= 10
+        bad = got != want
+        if bad.any():                                        # only ties below the stated 2^-16 resolution may differ
+            top = sim.gather(2, want.unsqueeze(2)).squeeze(2)
+            alt = sim.gather(2, got.unsqueeze(2)).squeeze(2)
+            scale = eq.double().norm(dim=1) * ek.double().norm(dim=1).max(dim=1, keepdim=True).values
+            assert ((top - alt)[bad] <= 2.0 ** -15 * scale[bad]).all(), float((top - alt)[bad].max())
+            assert bad.float().mean() < 0.01
+
+
 @pytest.mark.parametrize("B,C,hw,os_,lmbd", [(3, 128, 6, 2, 0.3), (2, 128, 14, 1, 0.5), (2, 64, 5, 4, 0.0)])
 def test_positive_keys_vs_oracle(ops, B, C, hw, os_, lmbd):
     gen = torch.Generator().manual_seed(hw * 10 + B)
