@@ -1,0 +1,42 @@
+"""GPU: one call of each round-2 kernel outside the step (f3 tensor-core path, f2 queue sums + backbone match) at the
+bench shapes, for `ncu` captures.  Usage: python dev/prof_f2f3.py [iters]"""
+import os
+import sys
+
+import torch
+import torch.nn.functional as F
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from cp2_b200 import ops  # noqa: E402
+
+iters = int(sys.argv[1]) if len(sys.argv) > 1 else 3
+dev = torch.device("cuda")
+g = torch.Generator(device=dev).manual_seed(5)
+B, C, hw, os_, K = 32, 128, 14, 16, 65536
+P, H = hw * hw, hw * 16
+q = torch.randn(B, C, P, device=dev, generator=g)
+k = torch.randn(B, C, P, device=dev, generator=g)
+ma = (torch.rand(B, P, device=dev, generator=g) < 0.65).float()
+mb = (torch.rand(B, P, device=dev, generator=g) < 0.65).float()
+pa = torch.arange(1, H * H + 1, device=dev).reshape(1, H, H).repeat(B, 1, 1)
+pb = torch.roll(pa, shifts=(os_, os_), dims=(1, 2)).contiguous()
+ra = (pa - 1) // (H * 64) * 4 + ((pa - 1) % H) // 64
+rb = torch.roll(ra, shifts=(os_, os_), dims=(1, 2)).contiguous()
+pw = ops.PairWeights(pa, pb, ra, rb, os_, 10.0, 2.0, 0.5, "FIXED", 2.0)
+alpha = torch.full((B,), 1.0 / B, device=dev)
+v1 = torch.zeros(B, C, device=dev)
+qh, q_inv, sq, nsq, _ = ops.prep_features(q, ma)
+kh, _, sk, nsk, _ = ops.prep_features(k, mb)
+queue2 = F.normalize(torch.randn(C, K, device=dev, generator=g), dim=0)
+shadow = ops.QueueShadow()
+rows_bf = qh.view(B * P, C)
+eq = F.normalize(torch.randn(B, 2048, P, device=dev, generator=g).relu(), dim=1)
+ek = F.normalize(torch.randn(B, 2048, P, device=dev, generator=g).relu(), dim=1)
+torch.cuda.synchronize()
+for _ in range(iters):
+    _, _, _, cnt, _, acc = ops.dense_weighted_small(qh, kh, ma, mb, pw, sq, nsq, sk, nsk, 5.0)
+    ops.dense_small_bwd(acc, qh, ma, q_inv, alpha, v1, None, key_count=cnt)
+    zp, gacc = ops.queue_sums_tc(rows_bf, queue2, 5.0, shadow)
+    idx = ops.densecl_match(eq, ek)
+torch.cuda.synchronize()
+print("ok", float(zp.sum()), int(idx.sum()))
