@@ -66,7 +66,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   float *part = nl + 256;                                       // [2 halves][2 key tiles][128]
   uint64_t *bars = reinterpret_cast<uint64_t *>(part + 512);
   uint64_t *bar_k = bars, *bar_q = bars + 1, *bar_s1 = bars + 2 /* [2] */, *bar_free = bars + 4,
-           *bar_s2 = bars + 5, *bar_p = bars + 6 /* [2] */, *bar_d = bars + 8;
+           *bar_s2 = bars + 5, *bar_p = bars + 6 /* [2] */, *bar_d = bars + 8, *bar_cand = bars + 9;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16);
   float *smax = reinterpret_cast<float *>(tmem_slot + 4);       // [8] per-warp maxima / [8][4] per-warp bests
   int *ncand = reinterpret_cast<int *>(smax + 32);
@@ -86,6 +86,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     mbar_init(&bar_p[0], 4);
     mbar_init(&bar_p[1], 4);
     mbar_init(bar_d, 1);
+    mbar_init(bar_cand, 8);
     *ncand = 0;
     fence_barrier_init();
     mbar_expect_tx(bar_k, oper);
@@ -123,6 +124,40 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 
   if (warp == 0) {
     // (the two TMA loads were issued at the top of the kernel)
+    // acc_seg: this otherwise idle warp scores the candidates exactly in fp32 while the others run phase 2
+    if (meter) {
+      mbar_wait(bar_cand, 0);                        // every softmax warp has finished its scan: the list is complete
+      const int n = min(*reinterpret_cast<volatile int *>(ncand), SEG_MAXC);
+      float bestv = -INFINITY;
+      int bestf = 0x7fffffff, bestx = 0, besty = 0, bestr = 0;
+      for (int i = 0; i < n; ++i) {
+        const int x = cand[i] >> 16, yr = cand[i] & 0xffff;
+        const int y = seg.perm_k ? __ldg(seg.perm_k + (long long)b * P + yr) : yr;
+        const float *qp = seg.q_f32 + (long long)b * C * P + x, *kp = seg.k_f32 + (long long)b * C * P + y;
+        float qv[C / 32], kv[C / 32];
+#pragma unroll
+        for (int j = 0; j < C / 32; ++j) {
+          qv[j] = __ldg(qp + (long long)(lane + 32 * j) * P);
+          kv[j] = __ldg(kp + (long long)(lane + 32 * j) * P);
+        }
+        const float iq = __ldg(seg.inv_q + (long long)b * P + x), ik = __ldg(seg.inv_k + (long long)b * P + y);
+        float d = 0.f;
+#pragma unroll
+        for (int j = 0; j < C / 32; ++j) d = fmaf(qv[j] * iq, kv[j] * ik, d);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+        const int flat = x * P + y;
+        if (d > bestv || (d == bestv && flat < bestf)) { bestv = d; bestf = flat; bestx = x; besty = y; bestr = yr; }
+      }
+      if (lane == 0) {
+        float h = 0.f;
+        if (bestf != 0x7fffffff) {
+          const float lb = seg.mask_b ? seg.mask_b[(long long)b * P + besty] : (bestr < cnt ? 1.f : 0.f);
+          h = seg.mask_a[(long long)b * P + bestx] * lb;
+        }
+        seg.hit[b] = h;
+      }
+    }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     const uint32_t idesc1 = make_idesc(TILE, rows, FMT_BF16, FMT_BF16, MAJOR_K, MAJOR_K);
@@ -284,7 +319,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_free);
+      if (lane == 0) { mbar_arrive(bar_free); mbar_arrive(bar_cand); }
     }
     if (half < nyt) {                                // half h finishes key tile h
       const int y = half * 128 + row;
@@ -341,53 +376,6 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) dst[(long long)(c0 + j) * P] = __uint_as_float(r[j]);
         }
-      }
-    }
-    // ---- acc_seg: exact fp32 score of the candidates (the list is complete: every warp passed the nl barrier)
-    if (meter) {
-      const int n = min(*reinterpret_cast<volatile int *>(ncand), SEG_MAXC);
-      float bestv = -INFINITY;
-      int bestf = 0x7fffffff, bestx = 0, besty = 0, bestr = 0;
-      for (int i = warp - 2; i < n; i += 8) {
-        const int x = cand[i] >> 16, yr = cand[i] & 0xffff;
-        const int y = seg.perm_k ? __ldg(seg.perm_k + (long long)b * P + yr) : yr;
-        const float *qp = seg.q_f32 + (long long)b * C * P + x, *kp = seg.k_f32 + (long long)b * C * P + y;
-        float qv[C / 32], kv[C / 32];
-#pragma unroll
-        for (int j = 0; j < C / 32; ++j) {
-          qv[j] = __ldg(qp + (long long)(lane + 32 * j) * P);
-          kv[j] = __ldg(kp + (long long)(lane + 32 * j) * P);
-        }
-        const float iq = __ldg(seg.inv_q + (long long)b * P + x), ik = __ldg(seg.inv_k + (long long)b * P + y);
-        float d = 0.f;
-#pragma unroll
-        for (int j = 0; j < C / 32; ++j) d = fmaf(qv[j] * iq, kv[j] * ik, d);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
-        const int flat = x * P + y;
-        if (d > bestv || (d == bestv && flat < bestf)) { bestv = d; bestf = flat; bestx = x; besty = y; bestr = yr; }
-      }
-      if (lane == 0) {
-        smax[(warp - 2) * 4 + 0] = bestv;
-        smax[(warp - 2) * 4 + 1] = __int_as_float(bestf);
-        smax[(warp - 2) * 4 + 2] = __int_as_float(bestx);
-        smax[(warp - 2) * 4 + 3] = __int_as_float(seg.mask_b ? besty : (bestr < cnt ? -1 : -2));
-      }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (threadIdx.x == 64) {
-        float bv = -INFINITY;
-        int bf = 0x7fffffff, bx = 0, by = -2;
-        for (int w = 0; w < 8; ++w) {
-          const float v = smax[w * 4];
-          const int f = __float_as_int(smax[w * 4 + 1]);
-          if (v > bv || (v == bv && f < bf)) { bv = v; bf = f; bx = __float_as_int(smax[w * 4 + 2]); by = __float_as_int(smax[w * 4 + 3]); }
-        }
-        float h = 0.f;
-        if (bf != 0x7fffffff) {
-          const float lb = by >= 0 ? seg.mask_b[(long long)b * P + by] : (by == -1 ? 1.f : 0.f);
-          h = seg.mask_a[(long long)b * P + bx] * lb;
-        }
-        seg.hit[b] = h;
       }
     }
   }

@@ -3,9 +3,10 @@
 // as ONE kernel on the tensor cores; the [B,S^2,S^2] similarity matrix lives only in TMEM.
 //
 // The operands are the fp32 backbone feature maps as cuDNN leaves them, [B,Cb,P] with the pixel axis contiguous.
-// CTA = (image, 128 query pixels).  Per 32-channel slab, 8 converter warps read the fp32 values (coalesced along
-// P), split each into two bf16 terms (hi = RN(v), lo = RN(v - hi)) and write them as MN-major, 128-byte-swizzled
-// tcgen05 operand tiles (3 slabs in flight); the MMA warp accumulates  S += q_hi k_hi + q_hi k_lo + q_lo k_hi  in
+// CTA = (image, 128 query pixels).  Per 16-channel slab, 8 converter warps bring the fp32 values into a shared-
+// memory ring with cp.async (4 slabs in flight per SM: the kernel is a stream over 2 x 1.6 MB per image), split
+// each into two bf16 terms (hi = RN(v), lo = RN(v - hi)) and write them as MN-major, 128-byte-swizzled tcgen05
+// operand tiles (3 stages); the MMA warp accumulates  S += q_hi k_hi + q_hi k_lo + q_lo k_hi  in
 // TMEM (fp32), i.e. the similarity to ~2^-16 relative — ties closer than that are below the noise of the
 // reference's own fp32 summation order on 2048 channels.  After the last slab four warps scan their TMEM lane
 // (one query pixel each) for the first largest column.  P <= 256.
@@ -17,18 +18,20 @@ using namespace umma;
 namespace {
 
 constexpr int MT_THREADS = 288;          // warp 0: MMA issuer + TMEM owner; warps 1-8: converters (1-4 also arg-max)
-constexpr int KS = 32;                   // channels per slab (two K = 16 MMA slices)
-constexpr int NS = 3;                    // slabs in flight
-constexpr int A_BYTES = 2 * KS * 128;    // one bf16 term of the query slab: 2 chunks of 64 pixels x 32 channel rows
+constexpr int KS = 16;                   // channels per slab (one K = 16 MMA slice)
+constexpr int NS = 3;                    // bf16 operand stages
+constexpr int ND = 4;                    // fp32 slabs in flight (cp.async ring)
+constexpr int A_BYTES = 2 * KS * 128;    // one bf16 term of the query slab: 2 chunks of 64 pixels x 16 channel rows
 constexpr int B_BYTES = 4 * KS * 128;    // one bf16 term of the key slab: 4 chunks of 64 pixels
 constexpr int STAGE = 2 * A_BYTES + 2 * B_BYTES;
-constexpr size_t MT_SMEM = 1024 + (size_t)NS * STAGE + 2 * NS * 8 + 8 + 16;
+constexpr int RING = 6 * 256 * 16;       // one fp32 slab: 6 16-byte pieces per converter thread, piece-major
+constexpr size_t MT_SMEM = 1024 + (size_t)NS * STAGE + (size_t)ND * RING + 2 * NS * 8 + 8 + 16;
 
 __device__ __forceinline__ uint8_t *align1024m(uint8_t *p) {
   return reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(p) + 1023) & ~uintptr_t(1023));
 }
 
-// 8 consecutive pixels of channel row `c` (0..31) starting at pixel 8*unit: byte offset inside an MN-major
+// 8 consecutive pixels of channel row `c` (0..15) starting at pixel 8*unit: byte offset inside an MN-major
 // operand term whose 64-pixel chunks are KS*128 bytes apart (LBO) and whose 8-row groups are 1024 bytes apart (SBO)
 __device__ __forceinline__ uint32_t mn_off(int c, int unit) {
   return (uint32_t)((unit >> 3) * (KS * 128) + (c >> 3) * 1024 + (c & 7) * 128 + (((unit & 7) ^ (c & 7)) << 4));
@@ -47,15 +50,18 @@ __device__ __forceinline__ void split8(const float (&v)[8], uint4 &hi, uint4 &lo
   lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
-// 8 consecutive pixels p0..p0+7 of one channel row (zeros past P); vec: rows are 16-byte aligned (P % 4 == 0)
-__device__ __forceinline__ void load8(const float *__restrict__ row, int p0, int P, bool vec, float (&v)[8]) {
+// One unit (8 consecutive pixels p0..p0+7 of a channel row) into two 16-byte ring pieces: cp.async when the row
+// is 16-byte aligned and the unit lies inside the map, plain loads / zeros otherwise (map edge, P % 4 != 0).
+__device__ __forceinline__ void stage8(const float *__restrict__ row, int p0, int P, bool vec, uint8_t *d0, uint8_t *d1) {
   if (vec && p0 + 8 <= P) {
-    const float4 a = __ldg(reinterpret_cast<const float4 *>(row + p0));
-    const float4 b = __ldg(reinterpret_cast<const float4 *>(row + p0 + 4));
-    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(d0)), "l"(row + p0) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(d1)), "l"(row + p0 + 4) : "memory");
   } else {
+    float v[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] = (p0 + i < P) ? __ldg(row + p0 + i) : 0.f;
+    *reinterpret_cast<float4 *>(d0) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4 *>(d1) = make_float4(v[4], v[5], v[6], v[7]);
   }
 }
 
@@ -64,7 +70,8 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
                      int Cb, int P, int ncols) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = align1024m(smem_raw);
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + NS * STAGE);
+  uint8_t *ring = smem + NS * STAGE;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(ring + ND * RING);
   uint64_t *full = bars, *empty = bars + NS, *done = bars + 2 * NS;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(done + 1);
 
@@ -92,14 +99,11 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
       if (elect_one()) {
         const uint32_t base = smem_u32(smem + s * STAGE);
         const uint32_t aH = base, aL = base + A_BYTES, bH = base + 2 * A_BYTES, bL = bH + B_BYTES;
-#pragma unroll
-        for (int kk = 0; kk < KS / 16; ++kk) {            // 16 channel rows (2 KB) per slice
-          const uint64_t dAh = make_sdesc(aH + kk * 2048, KS * 128, 1024), dAl = make_sdesc(aL + kk * 2048, KS * 128, 1024);
-          const uint64_t dBh = make_sdesc(bH + kk * 2048, KS * 128, 1024), dBl = make_sdesc(bL + kk * 2048, KS * 128, 1024);
-          mma_f16_ss(tmem, dAh, dBh, idesc, (i > 0 || kk > 0) ? 1u : 0u);
-          mma_f16_ss(tmem, dAh, dBl, idesc, 1u);
-          mma_f16_ss(tmem, dAl, dBh, idesc, 1u);
-        }
+        const uint64_t dAh = make_sdesc(aH, KS * 128, 1024), dAl = make_sdesc(aL, KS * 128, 1024);
+        const uint64_t dBh = make_sdesc(bH, KS * 128, 1024), dBl = make_sdesc(bL, KS * 128, 1024);
+        mma_f16_ss(tmem, dAh, dBh, idesc, i > 0 ? 1u : 0u);
+        mma_f16_ss(tmem, dAh, dBl, idesc, 1u);
+        mma_f16_ss(tmem, dAl, dBh, idesc, 1u);
         mma_commit(&empty[s]);
         if (i == nslab - 1) mma_commit(done);
       }
@@ -110,50 +114,49 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
     const int t = threadIdx.x - 32;                      // 0..255
     const bool vec = (P & 3) == 0;
     const float *qb = eq + (long long)b * Cb * P, *kb = ek + (long long)b * Cb * P;
-    // thread -> (channel row c, 8-pixel unit): query slab 32 x 16 units (2 per thread), key slab 32 x 32 (4)
-    const int c = t >> 3;                                // 0..31
-    const int u0 = t & 7;                                // units u0 + 8*j
-    // register double buffer: the loads of slab i+1 are in flight while slab i is split and stored
-    float vqa[2][8], vka[4][8], vqb[2][8], vkb[4][8];
-    auto fetch = [&](int i, float (&vq)[2][8], float (&vk)[4][8]) {
+    // thread -> channel row c, one 8-pixel unit of the query slab (16 x 16 units) and two of the key slab (16 x 32);
+    // a thread converts exactly what it copied, so the fp32 ring needs no barrier, only cp.async.wait_group
+    const int c = t >> 4;                                // 0..15
+    const int ua = t & 15, ub0 = t & 15, ub1 = (t & 15) + 16;
+    auto piece = [&](int slot, int pc) { return ring + slot * RING + (pc * 256 + t) * 16; };
+    auto fetch = [&](int i) {
+      const int slot = i % ND;
       const float *qrow = qb + (long long)(i * KS + c) * P, *krow = kb + (long long)(i * KS + c) * P;
-#pragma unroll
-      for (int j = 0; j < 2; ++j) load8(qrow, x0 + (u0 + 8 * j) * 8, P, vec, vq[j]);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) load8(krow, (u0 + 8 * j) * 8, P, vec, vk[j]);
+      stage8(qrow, x0 + ua * 8, P, vec, piece(slot, 0), piece(slot, 1));
+      stage8(krow, ub0 * 8, P, vec, piece(slot, 2), piece(slot, 3));
+      stage8(krow, ub1 * 8, P, vec, piece(slot, 4), piece(slot, 5));
     };
-    auto emit = [&](int i, const float (&vq)[2][8], const float (&vk)[4][8]) {
-      const int s = i % NS, ph = (i / NS) & 1;
+    auto take8 = [&](int slot, int pc, float (&v)[8]) {
+      const float4 a = *reinterpret_cast<const float4 *>(piece(slot, pc));
+      const float4 d = *reinterpret_cast<const float4 *>(piece(slot, pc + 1));
+      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = d.x; v[5] = d.y; v[6] = d.z; v[7] = d.w;
+    };
+    for (int i = 0; i < ND - 1; ++i) {                   // prologue: ND-1 slabs in flight
+      if (i < nslab) fetch(i);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    for (int i = 0; i < nslab; ++i) {
+      if (i + ND - 1 < nslab) fetch(i + ND - 1);         // its ring slot was converted in iteration i-1
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group %0;" ::"n"(ND - 1) : "memory");   // slab i has landed (this thread's pieces)
+      const int slot = i % ND, s = i % NS, ph = (i / NS) & 1;
+      float v[8];
+      uint4 hq, lq, hk0, lk0, hk1, lk1;
+      take8(slot, 0, v); split8(v, hq, lq);
+      take8(slot, 2, v); split8(v, hk0, lk0);
+      take8(slot, 4, v); split8(v, hk1, lk1);
       mbar_wait(&empty[s], ph ^ 1);                      // the MMAs that read this stage have completed
       uint8_t *st = smem + s * STAGE;
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        uint4 hi, lo;
-        split8(vq[j], hi, lo);
-        const uint32_t off = mn_off(c, u0 + 8 * j);
-        *reinterpret_cast<uint4 *>(st + off) = hi;
-        *reinterpret_cast<uint4 *>(st + A_BYTES + off) = lo;
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        uint4 hi, lo;
-        split8(vk[j], hi, lo);
-        const uint32_t off = mn_off(c, u0 + 8 * j);
-        *reinterpret_cast<uint4 *>(st + 2 * A_BYTES + off) = hi;
-        *reinterpret_cast<uint4 *>(st + 2 * A_BYTES + B_BYTES + off) = lo;
-      }
+      const uint32_t oa = mn_off(c, ua), o0 = mn_off(c, ub0), o1 = mn_off(c, ub1);
+      *reinterpret_cast<uint4 *>(st + oa) = hq;
+      *reinterpret_cast<uint4 *>(st + A_BYTES + oa) = lq;
+      *reinterpret_cast<uint4 *>(st + 2 * A_BYTES + o0) = hk0;
+      *reinterpret_cast<uint4 *>(st + 2 * A_BYTES + B_BYTES + o0) = lk0;
+      *reinterpret_cast<uint4 *>(st + 2 * A_BYTES + o1) = hk1;
+      *reinterpret_cast<uint4 *>(st + 2 * A_BYTES + B_BYTES + o1) = lk1;
       fence_proxy_async_smem();                          // generic-proxy writes -> visible to the tensor core
       __syncwarp();
       if (lane == 0) mbar_arrive(&full[s]);
-    };
-    fetch(0, vqa, vka);
-    for (int i = 0; i < nslab; i += 2) {
-      if (i + 1 < nslab) fetch(i + 1, vqb, vkb);
-      emit(i, vqa, vka);
-      if (i + 1 < nslab) {
-        if (i + 2 < nslab) fetch(i + 2, vqa, vka);
-        emit(i + 1, vqb, vkb);
-      }
     }
     // ------------------------------------------------------------------ arg-max (warps 1-4, one TMEM lane each)
     if (warp <= 4) {

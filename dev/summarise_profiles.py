@@ -37,7 +37,9 @@ ENTRY = {"composite_kernel": "cp2_composite", "ema_kernel": "cp2_ema", "prep_ker
          "global_nce_kernel": "cp2_global_nce", "dense_lse_kernel": "cp2_dense_lse",
          "dense_grad_kernel": "cp2_dense_grad", "enqueue_kernel": "cp2_enqueue",
          "loss_combine_kernel": "cp2_loss_combine", "id_iou_kernel": "cp2_id_iou",
-         "dense_top1_kernel": "cp2_dense_top1", "global_top1_kernel": "cp2_global_top1"}
+         "dense_top1_kernel": "cp2_dense_top1", "global_top1_kernel": "cp2_global_top1",
+         "dense_small_kernel": "cp2_dense_small", "dense_small_bwd_kernel": "cp2_dense_small_bwd",
+         "dense_wsmall_kernel": "cp2_dense_weighted_small", "densecl_match_kernel": "cp2_densecl_match"}
 UNIT = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0}
 
 
@@ -103,7 +105,7 @@ def main():
     os.makedirs(DST, exist_ok=True)
     tpath = os.path.join(DST, "traffic.json")
     traffic = json.load(open(tpath)) if os.path.isfile(tpath) else {}
-    for name in ("prof_step", "prof_dense", "prof_global", "prof_mirror"):
+    for name in ("prof_step", "prof_dense", "prof_global", "prof_mirror", "prof_f2f3", "prof_small"):
         rep = os.path.join(SRC, name + ".ncu-rep")
         if os.path.isfile(rep):
             summarise_rep(rep, os.path.join(DST, f"{tag}_ncu_{name[5:]}.csv"), traffic if name == "prof_step" else {})
