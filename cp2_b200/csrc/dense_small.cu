@@ -213,8 +213,10 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     const f2 scale2 = f2_pack(scale_log2, scale_log2);
     const int row = quad * 32 + lane;
     // ---- phase 1: units u = yt * nch + ch, first half of the list to half 0
-    const int U = nyt_s * nch, U0 = (U + 1) / 2;
-    const int u_begin = half == 0 ? 0 : U0, u_end = half == 0 ? U0 : U;
+    // units of this half: the chunks ch = half, half + 2, ... of key tile 0, then those of key tile 1 (both halves
+    // get the same share of every tile, so the exponentials stay balanced when tile 1 only feeds the meter)
+    const int nch_h = (nch - half + 1) / 2;
+    const int u_begin = 0, u_end = nyt_s * nch_h;
     float sum0 = 0.f, sum1 = 0.f, vmax = -INFINITY;
     {
       f2 acc_m = f2_pack(0.f, 0.f), acc_p = acc_m, acc_m2 = acc_m, acc_p2 = acc_m;
@@ -232,7 +234,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
       };
       uint32_t r0[32], r1[32];
       auto issue = [&](int u, uint32_t (&dst)[32]) {
-        const int yt = u / nch, ch = u - yt * nch;
+        const int yt = u / nch_h, ch = 2 * (u - yt * nch_h) + half;
         if (yt != cur) {
           flush();
           if (cur == 0 && !freed && !meter) {        // leaving key tile 0: its columns may be overwritten
@@ -251,9 +253,9 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
       // before the exponentials when it stays in the same key tile (a tile switch flushes the running sums, so it
       // has to wait for this unit; it happens at most once per warp).
       auto step = [&](int u, uint32_t (&now)[32], uint32_t (&nxt)[32]) {
-        const int yt = u / nch, ch = u - yt * nch;
+        const int yt = u / nch_h, ch = 2 * (u - yt * nch_h) + half;
         tmem_wait_ld();
-        const bool same_next = (u + 1 < u_end) && ((u + 1) / nch == yt);
+        const bool same_next = (u + 1 < u_end) && ((u + 1) / nch_h == yt);
         if (same_next) issue(u + 1, nxt);
         const int nvalid = min(32, P - ch * 32);
         if (meter && yt * TILE + row < P) {          // running maximum of the raw similarities (valid pairs only)
@@ -272,7 +274,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
         }
         if (!same_next && u + 1 < u_end) issue(u + 1, nxt);
       };
-      if (!meter && (u_begin >= u_end || u_begin >= nch)) {   // no unit of key tile 0 in this warp's share
+      if (!meter && u_begin >= u_end) {              // no unit at all in this warp's share (nch = 1, half 1)
         if (lane == 0) mbar_arrive(bar_free);
         freed = true;
       }
@@ -303,7 +305,7 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
       for (int w = 1; w < 8; ++w) M = fmaxf(M, smax[w]);
       const float thr = M - SEG_DELTA;
       for (int u = u_begin; u < u_end; ++u) {
-        const int yt = u / nch, ch = u - yt * nch;
+        const int yt = u / nch_h, ch = 2 * (u - yt * nch_h) + half;
         uint32_t rc[32];
         tmem_ld32(tmem + lane_off + yt * 256 + ch * 32, rc);
         tmem_wait_ld();

@@ -50,18 +50,27 @@ __device__ __forceinline__ void split8(const float (&v)[8], uint4 &hi, uint4 &lo
   lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
-// One unit (8 consecutive pixels p0..p0+7 of a channel row) into two 16-byte ring pieces: cp.async when the row
-// is 16-byte aligned and the unit lies inside the map, plain loads / zeros otherwise (map edge, P % 4 != 0).
+// One unit (8 consecutive pixels p0..p0+7 of a channel row) into two 16-byte ring pieces, asynchronously in every
+// case (a synchronous load on the map edge would put one memory round trip per slab on the critical path):
+// 16-byte cp.async when the rows are 16-byte aligned (P % 4 == 0: a piece is then entirely inside or outside the
+// map), 4-byte cp.async per pixel otherwise; pieces / pixels past P are zero-filled (src-size 0 reads nothing).
 __device__ __forceinline__ void stage8(const float *__restrict__ row, int p0, int P, bool vec, uint8_t *d0, uint8_t *d1) {
-  if (vec && p0 + 8 <= P) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(d0)), "l"(row + p0) : "memory");
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(d1)), "l"(row + p0 + 4) : "memory");
-  } else {
-    float v[8];
+  if (vec) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = (p0 + i < P) ? __ldg(row + p0 + i) : 0.f;
-    *reinterpret_cast<float4 *>(d0) = make_float4(v[0], v[1], v[2], v[3]);
-    *reinterpret_cast<float4 *>(d1) = make_float4(v[4], v[5], v[6], v[7]);
+    for (int h = 0; h < 2; ++h) {
+      const int p = p0 + 4 * h;
+      const uint32_t n = p < P ? 16u : 0u;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(h ? d1 : d0)),
+                   "l"(row + (p < P ? p : 0)), "r"(n) : "memory");
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int p = p0 + i;
+      const uint32_t n = p < P ? 4u : 0u;
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32((i < 4 ? d0 : d1) + 4 * (i & 3))),
+                   "l"(row + (p < P ? p : 0)), "r"(n) : "memory");
+    }
   }
 }
 

@@ -9,7 +9,7 @@ import torch.nn.functional as F
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from cp2_b200 import ops  # noqa: E402
 
-iters = int(sys.argv[1]) if len(sys.argv) > 1 else 3
+iters = int(sys.argv[1]) if len(sys.argv) > 1 else 9
 dev = torch.device("cuda")
 g = torch.Generator(device=dev).manual_seed(5)
 B, C, hw, os_, K = 32, 128, 14, 16, 65536
@@ -33,10 +33,34 @@ rows_bf = qh.view(B * P, C)
 eq = F.normalize(torch.randn(B, 2048, P, device=dev, generator=g).relu(), dim=1)
 ek = F.normalize(torch.randn(B, 2048, P, device=dev, generator=g).relu(), dim=1)
 torch.cuda.synchronize()
-for _ in range(iters):
-    _, _, _, cnt, _, acc = ops.dense_weighted_small(qh, kh, ma, mb, pw, sq, nsq, sk, nsk, 5.0)
-    ops.dense_small_bwd(acc, qh, ma, q_inv, alpha, v1, None, key_count=cnt)
-    zp, gacc = ops.queue_sums_tc(rows_bf, queue2, 5.0, shadow)
-    idx = ops.densecl_match(eq, ek)
-torch.cuda.synchronize()
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+
+def timed(name, fn, n=iters):
+    ts = []
+    for i in range(n + 2):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 2:
+            ts.append(e0.elapsed_time(e1) * 1e3)
+    ts.sort()
+    print(f"{name:28s} {ts[len(ts) // 2]:9.1f} us (median of {n}, L2 flushed)", flush=True)
+    return out
+
+
+_, _, _, cnt, _, acc = timed("dense_weighted_small", lambda: ops.dense_weighted_small(qh, kh, ma, mb, pw, sq, nsq, sk, nsk, 5.0))
+timed("dense_small_bwd", lambda: ops.dense_small_bwd(acc, qh, ma, q_inv, alpha, v1, None, key_count=cnt))
+zp, gacc = timed("queue_sums_tc", lambda: ops.queue_sums_tc(rows_bf, queue2, 5.0, shadow))
+idx = timed("densecl_match", lambda: ops.densecl_match(eq, ek))
+(qh2, q_inv2, *_), (kh2, k_inv2, _, _, cnt2, _, _, _, perm2) = ops.prep_features_pair(q, ma, k, mb, want_perm=True)
+timed("dense_small (no meter)", lambda: ops.dense_small(qh2, kh2, 5.0, cnt2))
+timed("dense_small (acc_seg)", lambda: ops.dense_small(qh2, kh2, 5.0, cnt2, seg=(q, k, q_inv2, k_inv2, perm2, ma, mb)))
+qpos = F.normalize(torch.randn(B, C, device=dev, generator=g), dim=1)
+kpos = F.normalize(torch.randn(B, C, device=dev, generator=g), dim=1)
+timed("global_nce (acc_ins)", lambda: ops.global_nce(qpos, queue2, 5.0, k_pos=kpos, shadow=shadow))
+timed("prep_features_pair", lambda: ops.prep_features_pair(q, ma, k, mb))
 print("ok", float(zp.sum()), int(idx.sum()))
