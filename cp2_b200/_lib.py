@@ -43,7 +43,8 @@ SIGNATURES = {
     "cp2_queue_sums_split": (c_int, [c_int, c_int]),
     "cp2_queue_sums": (c_int, [c_void_p] * 5 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_positive_keys": (c_int, [c_void_p] * 5 + [c_float] + [c_int] * 6 + [c_void_p]),
-    "cp2_densecl_match": (c_int, [c_void_p] * 3 + [c_int] * 3 + [c_void_p]),
+    "cp2_densecl_match_scratch_bytes": (c_int64, [c_int, c_int]),
+    "cp2_densecl_match": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p]),
     "cp2_mirror_partials": (c_int, [c_int, c_int64]),
     "cp2_mirror_loss": (c_int, [c_void_p] * 8 + [c_float, c_float, c_int64, c_int, c_int, c_int64, c_void_p]),
     "cp2_mirror_up_partials": (c_int, [c_int] * 3),

@@ -3,13 +3,16 @@
 // as ONE kernel on the tensor cores; the [B,S^2,S^2] similarity matrix lives only in TMEM.
 //
 // The operands are the fp32 backbone feature maps as cuDNN leaves them, [B,Cb,P] with the pixel axis contiguous.
-// CTA = (image, 128 query pixels).  Per 16-channel slab, 8 converter warps bring the fp32 values into a shared-
-// memory ring with cp.async (4 slabs in flight per SM: the kernel is a stream over 2 x 1.6 MB per image), split
-// each into two bf16 terms (hi = RN(v), lo = RN(v - hi)) and write them as MN-major, 128-byte-swizzled tcgen05
-// operand tiles (3 stages); the MMA warp accumulates  S += q_hi k_hi + q_hi k_lo + q_lo k_hi  in
-// TMEM (fp32), i.e. the similarity to ~2^-16 relative — ties closer than that are below the noise of the
-// reference's own fp32 summation order on 2048 channels.  After the last slab four warps scan their TMEM lane
-// (one query pixel each) for the first largest column.  P <= 256.
+// The kernel is a stream over them (2 x 1.6 MB per image at configs[1]), so it is laid out for bytes in flight:
+// CTA = (image, 128 query pixels, 128 key pixels) — 4 CTAs per 14x14 image, 128 at B = 32 — and per 16-channel
+// slab 8 converter warps bring the fp32 values into a shared-memory ring with cp.async (7 slabs = 112 KB in flight
+// per SM), split each into two bf16 terms (hi = RN(v), lo = RN(v - hi)) and write them as MN-major,
+// 128-byte-swizzled tcgen05 operand tiles (3 stages); the MMA warp accumulates
+// S += q_hi k_hi + q_hi k_lo + q_lo k_hi in TMEM (fp32), i.e. the similarity to ~2^-16 relative — ties closer than
+// that are below the noise of the reference's own fp32 summation order on 2048 channels.  After the last slab four
+// warps scan their TMEM lane (one query pixel each) for the first largest column of the tile and publish
+// (value, column) with one 64-bit atomicMax per query pixel (order-preserving key, smaller column wins ties:
+// deterministic); the last CTA of an image decodes the winners into idx and re-zeroes the scratch.  P <= 256.
 #include "common.cuh"
 #include "umma.cuh"
 
@@ -20,12 +23,11 @@ namespace {
 constexpr int MT_THREADS = 288;          // warp 0: MMA issuer + TMEM owner; warps 1-8: converters (1-4 also arg-max)
 constexpr int KS = 16;                   // channels per slab (one K = 16 MMA slice)
 constexpr int NS = 3;                    // bf16 operand stages
-constexpr int ND = 4;                    // fp32 slabs in flight (cp.async ring)
-constexpr int A_BYTES = 2 * KS * 128;    // one bf16 term of the query slab: 2 chunks of 64 pixels x 16 channel rows
-constexpr int B_BYTES = 4 * KS * 128;    // one bf16 term of the key slab: 4 chunks of 64 pixels
-constexpr int STAGE = 2 * A_BYTES + 2 * B_BYTES;
-constexpr int RING = 6 * 256 * 16;       // one fp32 slab: 6 16-byte pieces per converter thread, piece-major
-constexpr size_t MT_SMEM = 1024 + (size_t)NS * STAGE + (size_t)ND * RING + 2 * NS * 8 + 8 + 16;
+constexpr int ND = 8;                    // fp32 slabs in the cp.async ring (ND - 1 in flight)
+constexpr int T_BYTES = 2 * KS * 128;    // one bf16 term of a 128-pixel slab: 2 chunks of 64 pixels x 16 channel rows
+constexpr int STAGE = 4 * T_BYTES;       // q_hi, q_lo, k_hi, k_lo
+constexpr int RING = 4 * 256 * 16;       // one fp32 slab: 4 16-byte pieces per converter thread, piece-major
+constexpr size_t MT_SMEM = 1024 + (size_t)NS * STAGE + (size_t)ND * RING + 2 * NS * 8 + 8 + 32;
 
 __device__ __forceinline__ uint8_t *align1024m(uint8_t *p) {
   return reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(p) + 1023) & ~uintptr_t(1023));
@@ -74,25 +76,33 @@ __device__ __forceinline__ void stage8(const float *__restrict__ row, int p0, in
   }
 }
 
+// order-preserving 32-bit key of a float (larger float <-> larger unsigned)
+__device__ __forceinline__ uint32_t orderable(float v) {
+  const uint32_t u = __float_as_uint(v);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
 __global__ void __launch_bounds__(MT_THREADS, 1)
 densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek, long long *__restrict__ idx,
-                     int Cb, int P, int ncols) {
+                     unsigned long long *__restrict__ best, unsigned int *__restrict__ counters, int Cb, int P) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = align1024m(smem_raw);
   uint8_t *ring = smem + NS * STAGE;
   uint64_t *bars = reinterpret_cast<uint64_t *>(ring + ND * RING);
   uint64_t *full = bars, *empty = bars + NS, *done = bars + 2 * NS;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(done + 1);
+  int *is_last = reinterpret_cast<int *>(tmem_slot + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b = blockIdx.y, x0 = blockIdx.x * 128;
+  const int b = blockIdx.z, x0 = blockIdx.x * 128, y0 = blockIdx.y * 128;
   const int nslab = Cb / KS;
+  const int ncols = min(128, ((P - y0 + 31) / 32) * 32);   // MMA N: every 32-column chunk the arg-max reads is written
   if (threadIdx.x == 0) {
     for (int s = 0; s < NS; ++s) { mbar_init(&full[s], 8); mbar_init(&empty[s], 1); }
     mbar_init(done, 1);
     fence_barrier_init();
   }
-  if (warp == 0) tmem_alloc(tmem_slot, 256);
+  if (warp == 0) tmem_alloc(tmem_slot, 128);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -107,9 +117,8 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
       tc_fence_after();
       if (elect_one()) {
         const uint32_t base = smem_u32(smem + s * STAGE);
-        const uint32_t aH = base, aL = base + A_BYTES, bH = base + 2 * A_BYTES, bL = bH + B_BYTES;
-        const uint64_t dAh = make_sdesc(aH, KS * 128, 1024), dAl = make_sdesc(aL, KS * 128, 1024);
-        const uint64_t dBh = make_sdesc(bH, KS * 128, 1024), dBl = make_sdesc(bL, KS * 128, 1024);
+        const uint64_t dAh = make_sdesc(base, KS * 128, 1024), dAl = make_sdesc(base + T_BYTES, KS * 128, 1024);
+        const uint64_t dBh = make_sdesc(base + 2 * T_BYTES, KS * 128, 1024), dBl = make_sdesc(base + 3 * T_BYTES, KS * 128, 1024);
         mma_f16_ss(tmem, dAh, dBh, idesc, i > 0 ? 1u : 0u);
         mma_f16_ss(tmem, dAh, dBl, idesc, 1u);
         mma_f16_ss(tmem, dAl, dBh, idesc, 1u);
@@ -123,17 +132,14 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
     const int t = threadIdx.x - 32;                      // 0..255
     const bool vec = (P & 3) == 0;
     const float *qb = eq + (long long)b * Cb * P, *kb = ek + (long long)b * Cb * P;
-    // thread -> channel row c, one 8-pixel unit of the query slab (16 x 16 units) and two of the key slab (16 x 32);
-    // a thread converts exactly what it copied, so the fp32 ring needs no barrier, only cp.async.wait_group
-    const int c = t >> 4;                                // 0..15
-    const int ua = t & 15, ub0 = t & 15, ub1 = (t & 15) + 16;
+    // thread -> channel row c and 8-pixel unit u of both 16 x 128 slabs; a thread converts exactly what it copied,
+    // so the fp32 ring needs no barrier, only cp.async.wait_group
+    const int c = t >> 4, u = t & 15;
     auto piece = [&](int slot, int pc) { return ring + slot * RING + (pc * 256 + t) * 16; };
     auto fetch = [&](int i) {
       const int slot = i % ND;
-      const float *qrow = qb + (long long)(i * KS + c) * P, *krow = kb + (long long)(i * KS + c) * P;
-      stage8(qrow, x0 + ua * 8, P, vec, piece(slot, 0), piece(slot, 1));
-      stage8(krow, ub0 * 8, P, vec, piece(slot, 2), piece(slot, 3));
-      stage8(krow, ub1 * 8, P, vec, piece(slot, 4), piece(slot, 5));
+      stage8(qb + (long long)(i * KS + c) * P, x0 + u * 8, P, vec, piece(slot, 0), piece(slot, 1));
+      stage8(kb + (long long)(i * KS + c) * P, y0 + u * 8, P, vec, piece(slot, 2), piece(slot, 3));
     };
     auto take8 = [&](int slot, int pc, float (&v)[8]) {
       const float4 a = *reinterpret_cast<const float4 *>(piece(slot, pc));
@@ -144,25 +150,22 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
       if (i < nslab) fetch(i);
       asm volatile("cp.async.commit_group;" ::: "memory");
     }
+    const uint32_t off = mn_off(c, u);
     for (int i = 0; i < nslab; ++i) {
       if (i + ND - 1 < nslab) fetch(i + ND - 1);         // its ring slot was converted in iteration i-1
       asm volatile("cp.async.commit_group;" ::: "memory");
       asm volatile("cp.async.wait_group %0;" ::"n"(ND - 1) : "memory");   // slab i has landed (this thread's pieces)
       const int slot = i % ND, s = i % NS, ph = (i / NS) & 1;
       float v[8];
-      uint4 hq, lq, hk0, lk0, hk1, lk1;
+      uint4 hq, lq, hk, lk;
       take8(slot, 0, v); split8(v, hq, lq);
-      take8(slot, 2, v); split8(v, hk0, lk0);
-      take8(slot, 4, v); split8(v, hk1, lk1);
+      take8(slot, 2, v); split8(v, hk, lk);
       mbar_wait(&empty[s], ph ^ 1);                      // the MMAs that read this stage have completed
-      uint8_t *st = smem + s * STAGE;
-      const uint32_t oa = mn_off(c, ua), o0 = mn_off(c, ub0), o1 = mn_off(c, ub1);
-      *reinterpret_cast<uint4 *>(st + oa) = hq;
-      *reinterpret_cast<uint4 *>(st + A_BYTES + oa) = lq;
-      *reinterpret_cast<uint4 *>(st + 2 * A_BYTES + o0) = hk0;
-      *reinterpret_cast<uint4 *>(st + 2 * A_BYTES + B_BYTES + o0) = lk0;
-      *reinterpret_cast<uint4 *>(st + 2 * A_BYTES + o1) = hk1;
-      *reinterpret_cast<uint4 *>(st + 2 * A_BYTES + B_BYTES + o1) = lk1;
+      uint8_t *st = smem + s * STAGE + off;
+      *reinterpret_cast<uint4 *>(st) = hq;
+      *reinterpret_cast<uint4 *>(st + T_BYTES) = lq;
+      *reinterpret_cast<uint4 *>(st + 2 * T_BYTES) = hk;
+      *reinterpret_cast<uint4 *>(st + 3 * T_BYTES) = lk;
       fence_proxy_async_smem();                          // generic-proxy writes -> visible to the tensor core
       __syncwarp();
       if (lane == 0) mbar_arrive(&full[s]);
@@ -173,7 +176,7 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
       tc_fence_after();
       const int quad = warp & 3, x = x0 + quad * 32 + lane;
       const uint32_t lane_base = tmem + (uint32_t(quad * 32) << 16);
-      float best = -INFINITY;
+      float bv = -INFINITY;
       int bi = 0;
       for (int ch = 0; ch * 32 < ncols; ++ch) {
         uint32_t r[32];
@@ -181,32 +184,55 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
         tmem_wait_ld();
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          const int y = ch * 32 + j;
+          const int y = y0 + ch * 32 + j;
           const float v = __uint_as_float(r[j]);
-          if (y < P && v > best) { best = v; bi = y; }   // strict: the first largest column wins
+          if (y < P && v > bv) { bv = v; bi = y; }       // strict: the first largest column of the tile wins
         }
       }
-      if (x < P) idx[(long long)b * P + x] = bi;
+      if (x < P)                                         // across key tiles: larger value, then smaller column
+        atomicMax(best + (long long)b * P + x, ((unsigned long long)orderable(bv) << 32) | (0xFFFFFFFFu - (uint32_t)bi));
     }
   }
   tc_fence_before();
+  __threadfence();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 256);
+  if (warp == 0) tmem_dealloc(tmem, 128);
+  // the last CTA of the image decodes the winners and leaves the scratch zeroed for the next call
+  if (threadIdx.x == 0) {
+    const unsigned int total = gridDim.x * gridDim.y;
+    const int last = atomicAdd(counters + b, 1u) == total - 1u;
+    if (last) counters[b] = 0u;
+    *is_last = last;
+  }
+  __syncthreads();
+  if (*is_last) {
+    __threadfence();
+    for (int x = threadIdx.x; x < P; x += MT_THREADS) {
+      const unsigned long long key = __ldcg(best + (long long)b * P + x);
+      best[(long long)b * P + x] = 0ull;
+      idx[(long long)b * P + x] = (long long)(0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull));
+    }
+  }
 }
 
 }  // namespace
 
-extern "C" int cp2_densecl_match(const float *embd_q, const float *embd_k, int64_t *idx, int B, int Cb, int P,
-                                 void *stream) {
+extern "C" int64_t cp2_densecl_match_scratch_bytes(int B, int P) { return (int64_t)B * P * 8 + (int64_t)B * 4 + 16; }
+
+extern "C" int cp2_densecl_match(const float *embd_q, const float *embd_k, int64_t *idx, void *scratch, int B, int Cb,
+                                 int P, void *stream) {
   CP2_REQUIRE(B > 0 && B <= 65535 && P > 0 && P <= 256, "cp2_densecl_match: bad shape B=%d P=%d (P <= 256)", B, P);
   CP2_REQUIRE(Cb > 0 && Cb % KS == 0, "cp2_densecl_match: Cb=%d must be a positive multiple of %d", Cb, KS);
-  CP2_REQUIRE(embd_q && embd_k && idx, "cp2_densecl_match: null pointer");
-  CP2_REQUIRE((reinterpret_cast<uintptr_t>(embd_q) & 15u) == 0 && (reinterpret_cast<uintptr_t>(embd_k) & 15u) == 0,
-              "cp2_densecl_match: embd_q / embd_k must be 16-byte aligned");
-  const int ncols = ((P + 31) / 32) * 32;              // MMA N: every 32-column chunk the arg-max reads is written
+  CP2_REQUIRE(embd_q && embd_k && idx && scratch, "cp2_densecl_match: null pointer");
+  CP2_REQUIRE((reinterpret_cast<uintptr_t>(embd_q) & 15u) == 0 && (reinterpret_cast<uintptr_t>(embd_k) & 15u) == 0 &&
+                  (reinterpret_cast<uintptr_t>(scratch) & 7u) == 0,
+              "cp2_densecl_match: embd_q / embd_k must be 16-byte, scratch 8-byte aligned");
+  auto *best = static_cast<unsigned long long *>(scratch);
+  auto *counters = reinterpret_cast<unsigned int *>(best + (size_t)B * P);
   CP2_SMEM_ONCE(densecl_match_kernel, MT_SMEM);
-  densecl_match_kernel<<<dim3(cp2_cdiv(P, 128), B), MT_THREADS, MT_SMEM, static_cast<cudaStream_t>(stream)>>>(
-      embd_q, embd_k, reinterpret_cast<long long *>(idx), Cb, P, ncols);
+  const int nt = cp2_cdiv(P, 128);
+  densecl_match_kernel<<<dim3(nt, nt, B), MT_THREADS, MT_SMEM, static_cast<cudaStream_t>(stream)>>>(
+      embd_q, embd_k, reinterpret_cast<long long *>(idx), best, counters, Cb, P);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }

@@ -764,14 +764,16 @@ def positive_keys(k_local, idx, pix_q=None, pix_k=None, output_stride=1, lmbd_co
 def densecl_match(embd_q, embd_k):
     """builder.py:817-821: idx[n,x] = argmax_y embd_q[n,:,x] . embd_k[n,:,y] on the 2048-d backbone features.
     cp2_densecl_match: one tcgen05 kernel (fp32 operands split into bf16 hi + lo on chip, the [B,S^2,S^2]
-    similarities stay in TMEM).  Maps above 256 pixels or channel counts off the 32-grid: torch.bmm + argmax."""
+    similarities stay in TMEM).  Maps above 256 pixels or channel counts off the 16-grid: torch.bmm + argmax."""
     _need_cuda(embd_q, embd_k)
     B, Cb, P = embd_q.shape
-    if P > 256 or Cb % 32 != 0:
+    if P > 256 or Cb % 16 != 0:
         return torch.bmm(embd_q.transpose(1, 2), embd_k).argmax(dim=2)
     embd_q, embd_k = _f32c(embd_q), _f32c(embd_k)
+    lib = _lib.load()
     idx = torch.empty((B, P), device=embd_q.device, dtype=torch.int64)
-    _call("cp2_densecl_match", 1, _lib.load().cp2_densecl_match, _ptr(embd_q), _ptr(embd_k), _ptr(idx), B, Cb, P,
+    scratch = _persistent_zero("match", lib.cp2_densecl_match_scratch_bytes(B, P), embd_q.device)
+    _call("cp2_densecl_match", 1, lib.cp2_densecl_match, _ptr(embd_q), _ptr(embd_k), _ptr(idx), _ptr(scratch), B, Cb, P,
           _stream())
     return idx
 

@@ -377,8 +377,14 @@ int cp2_positive_keys(const float *k_local, const int64_t *idx, const int64_t *p
  *   idx[n,x] = argmax_y sum_c embd_q[n,c,x] * embd_k[n,c,y]        (first largest y)
  * embd_q, embd_k : [B,Cb,P] f32 (the backbone feature maps, pixel axis contiguous), 16-byte aligned;
  * idx : [B,P] int64.  Each fp32 value enters as two bf16 terms (hi + lo; three products per pair), i.e. the
- * similarity to ~2^-16 relative; the [B,P,P] matrix exists only in TMEM.  P <= 256, Cb a multiple of 32. */
-int cp2_densecl_match(const float *embd_q, const float *embd_k, int64_t *idx, int B, int Cb, int P, void *stream);
+ * similarity to ~2^-16 relative; the [B,P,P] matrix exists only in TMEM.
+ *   scratch : cp2_densecl_match_scratch_bytes(B,P) bytes, 8-byte aligned, PERSISTENT: all zero before the first call
+ *             and left all zero by every call (per-pixel 64-bit arg-max keys combined across key tiles + per-image
+ *             done counters).
+ * P <= 256, Cb a multiple of 16. */
+int64_t cp2_densecl_match_scratch_bytes(int B, int P);
+int cp2_densecl_match(const float *embd_q, const float *embd_k, int64_t *idx, void *scratch, int B, int Cb, int P,
+                      void *stream);
 
 #ifdef __cplusplus
 }
