@@ -5,9 +5,10 @@
 // The operands are the fp32 backbone feature maps as cuDNN leaves them, [B,Cb,P] with the pixel axis contiguous.
 // The kernel is a stream over them (2 x 1.6 MB per image at configs[1]), so it is laid out for bytes in flight:
 // CTA = (image, 128 query pixels, 128 key pixels) — 4 CTAs per 14x14 image, 128 at B = 32 — and per 16-channel
-// slab 8 converter warps bring the fp32 values into a shared-memory ring with cp.async (7 slabs = 112 KB in flight
-// per SM), split each into two bf16 terms (hi = RN(v), lo = RN(v - hi)) and write them as MN-major,
-// 128-byte-swizzled tcgen05 operand tiles (3 stages); the MMA warp accumulates
+// slab a group of 2 converter warps (4 groups, each owning every 4th slab so that their per-slab fixed costs
+// overlap) brings the fp32 values into a shared-memory ring with cp.async, splits each into two bf16 terms
+// (hi = RN(v), lo = RN(v - hi)) and writes them as MN-major, 128-byte-swizzled tcgen05 operand tiles (6 stages);
+// the MMA warp accumulates
 // S += q_hi k_hi + q_hi k_lo + q_lo k_hi in TMEM (fp32), i.e. the similarity to ~2^-16 relative — ties closer than
 // that are below the noise of the reference's own fp32 summation order on 2048 channels.  After the last slab four
 // warps scan their TMEM lane (one query pixel each) for the first largest column of the tile and publish
@@ -22,11 +23,13 @@ namespace {
 
 constexpr int MT_THREADS = 288;          // warp 0: MMA issuer + TMEM owner; warps 1-8: converters (1-4 also arg-max)
 constexpr int KS = 16;                   // channels per slab (one K = 16 MMA slice)
-constexpr int NS = 3;                    // bf16 operand stages
-constexpr int ND = 8;                    // fp32 slabs in the cp.async ring (ND - 1 in flight)
+constexpr int NG = 4;                    // converter groups (2 warps each); group g owns the slabs i = g (mod NG), so the
+                                         // per-slab fixed costs (waits, proxy fence, barrier hand-over) of the groups overlap
+constexpr int NS = 6;                    // bf16 operand stages
+constexpr int ND = 8;                    // fp32 slabs in the cp.async ring (ND / NG per group, all but one in flight)
 constexpr int T_BYTES = 2 * KS * 128;    // one bf16 term of a 128-pixel slab: 2 chunks of 64 pixels x 16 channel rows
 constexpr int STAGE = 4 * T_BYTES;       // q_hi, q_lo, k_hi, k_lo
-constexpr int RING = 4 * 256 * 16;       // one fp32 slab: 4 16-byte pieces per converter thread, piece-major
+constexpr int RING = 16 * 64 * 16;       // one fp32 slab: 16 16-byte pieces per thread of the owning group, piece-major
 constexpr size_t MT_SMEM = 1024 + (size_t)NS * STAGE + (size_t)ND * RING + 2 * NS * 8 + 8 + 32;
 
 __device__ __forceinline__ uint8_t *align1024m(uint8_t *p) {
@@ -98,7 +101,7 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
   const int nslab = Cb / KS;
   const int ncols = min(128, ((P - y0 + 31) / 32) * 32);   // MMA N: every 32-column chunk the arg-max reads is written
   if (threadIdx.x == 0) {
-    for (int s = 0; s < NS; ++s) { mbar_init(&full[s], 8); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < NS; ++s) { mbar_init(&full[s], 256 / 32 / NG); mbar_init(&empty[s], 1); }
     mbar_init(done, 1);
     fence_barrier_init();
   }
@@ -132,40 +135,52 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
     const int t = threadIdx.x - 32;                      // 0..255
     const bool vec = (P & 3) == 0;
     const float *qb = eq + (long long)b * Cb * P, *kb = ek + (long long)b * Cb * P;
-    // thread -> channel row c and 8-pixel unit u of both 16 x 128 slabs; a thread converts exactly what it copied,
-    // so the fp32 ring needs no barrier, only cp.async.wait_group
-    const int c = t >> 4, u = t & 15;
-    auto piece = [&](int slot, int pc) { return ring + slot * RING + (pc * 256 + t) * 16; };
+    // group g = t / 64 converts the slabs i = g, g + NG, ...; inside the group thread tg -> channel row c and the
+    // 8-pixel units u0 + 4j (j < 4) of both 16 x 128 slabs.  A thread converts exactly what it copied, so the fp32
+    // ring needs no barrier, only cp.async.wait_group.
+    constexpr int DG = ND / NG;                          // ring slots per group
+    const int grp = t >> 6, tg = t & 63;
+    const int c = tg >> 2, u0 = tg & 3;
+    auto piece = [&](int slot, int pc) { return ring + slot * RING + (pc * 64 + tg) * 16; };
     auto fetch = [&](int i) {
       const int slot = i % ND;
-      stage8(qb + (long long)(i * KS + c) * P, x0 + u * 8, P, vec, piece(slot, 0), piece(slot, 1));
-      stage8(kb + (long long)(i * KS + c) * P, y0 + u * 8, P, vec, piece(slot, 2), piece(slot, 3));
+      const float *qrow = qb + (long long)(i * KS + c) * P, *krow = kb + (long long)(i * KS + c) * P;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        stage8(qrow, x0 + (u0 + 4 * j) * 8, P, vec, piece(slot, 2 * j), piece(slot, 2 * j + 1));
+        stage8(krow, y0 + (u0 + 4 * j) * 8, P, vec, piece(slot, 8 + 2 * j), piece(slot, 9 + 2 * j));
+      }
     };
     auto take8 = [&](int slot, int pc, float (&v)[8]) {
       const float4 a = *reinterpret_cast<const float4 *>(piece(slot, pc));
       const float4 d = *reinterpret_cast<const float4 *>(piece(slot, pc + 1));
       v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = d.x; v[5] = d.y; v[6] = d.z; v[7] = d.w;
     };
-    for (int i = 0; i < ND - 1; ++i) {                   // prologue: ND-1 slabs in flight
-      if (i < nslab) fetch(i);
+    for (int k = 0; k < DG - 1; ++k) {                   // prologue: DG-1 of the group's slabs in flight
+      if (grp + k * NG < nslab) fetch(grp + k * NG);
       asm volatile("cp.async.commit_group;" ::: "memory");
     }
-    const uint32_t off = mn_off(c, u);
-    for (int i = 0; i < nslab; ++i) {
-      if (i + ND - 1 < nslab) fetch(i + ND - 1);         // its ring slot was converted in iteration i-1
+    for (int i = grp; i < nslab; i += NG) {
+      if (i + (DG - 1) * NG < nslab) fetch(i + (DG - 1) * NG);   // its ring slot was converted one round ago
       asm volatile("cp.async.commit_group;" ::: "memory");
-      asm volatile("cp.async.wait_group %0;" ::"n"(ND - 1) : "memory");   // slab i has landed (this thread's pieces)
+      asm volatile("cp.async.wait_group %0;" ::"n"(DG - 1) : "memory");   // slab i has landed (this thread's pieces)
       const int slot = i % ND, s = i % NS, ph = (i / NS) & 1;
-      float v[8];
-      uint4 hq, lq, hk, lk;
-      take8(slot, 0, v); split8(v, hq, lq);
-      take8(slot, 2, v); split8(v, hk, lk);
+      uint4 hq[4], lq[4], hk[4], lk[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float v[8];
+        take8(slot, 2 * j, v); split8(v, hq[j], lq[j]);
+        take8(slot, 8 + 2 * j, v); split8(v, hk[j], lk[j]);
+      }
       mbar_wait(&empty[s], ph ^ 1);                      // the MMAs that read this stage have completed
-      uint8_t *st = smem + s * STAGE + off;
-      *reinterpret_cast<uint4 *>(st) = hq;
-      *reinterpret_cast<uint4 *>(st + T_BYTES) = lq;
-      *reinterpret_cast<uint4 *>(st + 2 * T_BYTES) = hk;
-      *reinterpret_cast<uint4 *>(st + 3 * T_BYTES) = lk;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint8_t *st = smem + s * STAGE + mn_off(c, u0 + 4 * j);
+        *reinterpret_cast<uint4 *>(st) = hq[j];
+        *reinterpret_cast<uint4 *>(st + T_BYTES) = lq[j];
+        *reinterpret_cast<uint4 *>(st + 2 * T_BYTES) = hk[j];
+        *reinterpret_cast<uint4 *>(st + 3 * T_BYTES) = lk[j];
+      }
       fence_proxy_async_smem();                          // generic-proxy writes -> visible to the tensor core
       __syncwarp();
       if (lane == 0) mbar_arrive(&full[s]);
