@@ -5,9 +5,10 @@
 // The operands are the fp32 backbone feature maps as cuDNN leaves them, [B,Cb,P] with the pixel axis contiguous.
 // The kernel is a stream over them (2 x 1.6 MB per image at configs[1]), so it is laid out for bytes in flight:
 // CTA = (image, 128 query pixels, 128 key pixels) — 4 CTAs per 14x14 image, 128 at B = 32 — and per 16-channel
-// slab a group of 2 converter warps (4 groups, each owning every 4th slab so that their per-slab fixed costs
-// overlap) brings the fp32 values into a shared-memory ring with cp.async, splits each into two bf16 terms
-// (hi = RN(v), lo = RN(v - hi)) and writes them as MN-major, 128-byte-swizzled tcgen05 operand tiles (6 stages);
+// slab a group of 4 converter warps (2 groups owning alternate slabs, so that their per-slab fixed costs overlap;
+// 3 slabs of each group in flight) brings the fp32 values into a shared-memory ring with cp.async, splits each
+// into two bf16 terms (hi = RN(v), lo = RN(v - hi)) and writes them as MN-major, 128-byte-swizzled tcgen05
+// operand tiles (4 stages);
 // the MMA warp accumulates
 // S += q_hi k_hi + q_hi k_lo + q_lo k_hi in TMEM (fp32), i.e. the similarity to ~2^-16 relative — ties closer than
 // that are below the noise of the reference's own fp32 summation order on 2048 channels.  After the last slab four
@@ -23,13 +24,16 @@ namespace {
 
 constexpr int MT_THREADS = 288;          // warp 0: MMA issuer + TMEM owner; warps 1-8: converters (1-4 also arg-max)
 constexpr int KS = 16;                   // channels per slab (one K = 16 MMA slice)
-constexpr int NG = 4;                    // converter groups (2 warps each); group g owns the slabs i = g (mod NG), so the
+constexpr int NG = 2;                    // converter groups (4 warps each); group g owns the slabs i = g (mod NG), so the
                                          // per-slab fixed costs (waits, proxy fence, barrier hand-over) of the groups overlap
-constexpr int NS = 6;                    // bf16 operand stages
+constexpr int NS = 4;                    // bf16 operand stages
 constexpr int ND = 8;                    // fp32 slabs in the cp.async ring (ND / NG per group, all but one in flight)
 constexpr int T_BYTES = 2 * KS * 128;    // one bf16 term of a 128-pixel slab: 2 chunks of 64 pixels x 16 channel rows
 constexpr int STAGE = 4 * T_BYTES;       // q_hi, q_lo, k_hi, k_lo
-constexpr int RING = 16 * 64 * 16;       // one fp32 slab: 16 16-byte pieces per thread of the owning group, piece-major
+constexpr int TG = 256 / NG;             // threads per converter group
+constexpr int UW = TG / 16;              // 8-pixel units of one channel row taken by neighbouring threads
+constexpr int UPT = 16 / UW;             // units per thread and operand
+constexpr int RING = 16 * 1024;          // one fp32 slab: 4 * UPT 16-byte pieces per thread of the owning group, piece-major
 constexpr size_t MT_SMEM = 1024 + (size_t)NS * STAGE + (size_t)ND * RING + 2 * NS * 8 + 8 + 32;
 
 __device__ __forceinline__ uint8_t *align1024m(uint8_t *p) {
@@ -42,14 +46,14 @@ __device__ __forceinline__ uint32_t mn_off(int c, int unit) {
   return (uint32_t)((unit >> 3) * (KS * 128) + (c >> 3) * 1024 + (c & 7) * 128 + (((unit & 7) ^ (c & 7)) << 4));
 }
 
-// 8 fp32 -> hi / lo bf16 x 8 (two 16-byte vectors)
+// 8 fp32 -> hi / lo bf16 x 8 (two 16-byte vectors).  hi pairs come from one packed conversion (cvt.rn.bf16x2.f32),
+// their fp32 values back by shift / mask: no quarter-rate scalar F2F on the path.
 __device__ __forceinline__ void split8(const float (&v)[8], uint4 &hi, uint4 &lo) {
   uint32_t h[4], l[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const __nv_bfloat16 h0 = __float2bfloat16_rn(v[2 * i]), h1 = __float2bfloat16_rn(v[2 * i + 1]);
-    h[i] = pack_bf16x2(__bfloat162float(h0), __bfloat162float(h1));
-    l[i] = pack_bf16x2(v[2 * i] - __bfloat162float(h0), v[2 * i + 1] - __bfloat162float(h1));
+    h[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+    l[i] = pack_bf16x2(v[2 * i] - __uint_as_float(h[i] << 16), v[2 * i + 1] - __uint_as_float(h[i] & 0xffff0000u));
   }
   hi = make_uint4(h[0], h[1], h[2], h[3]);
   lo = make_uint4(l[0], l[1], l[2], l[3]);
@@ -135,20 +139,20 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
     const int t = threadIdx.x - 32;                      // 0..255
     const bool vec = (P & 3) == 0;
     const float *qb = eq + (long long)b * Cb * P, *kb = ek + (long long)b * Cb * P;
-    // group g = t / 64 converts the slabs i = g, g + NG, ...; inside the group thread tg -> channel row c and the
-    // 8-pixel units u0 + 4j (j < 4) of both 16 x 128 slabs.  A thread converts exactly what it copied, so the fp32
+    // group g = t / TG converts the slabs i = g, g + NG, ...; inside the group thread tg -> channel row c and the
+    // 8-pixel units u0 + UW*j (j < UPT) of both 16 x 128 slabs.  A thread converts exactly what it copied, so the fp32
     // ring needs no barrier, only cp.async.wait_group.
     constexpr int DG = ND / NG;                          // ring slots per group
-    const int grp = t >> 6, tg = t & 63;
-    const int c = tg >> 2, u0 = tg & 3;
-    auto piece = [&](int slot, int pc) { return ring + slot * RING + (pc * 64 + tg) * 16; };
+    const int grp = t / TG, tg = t % TG;
+    const int c = tg / UW, u0 = tg % UW;
+    auto piece = [&](int slot, int pc) { return ring + slot * RING + (pc * TG + tg) * 16; };
     auto fetch = [&](int i) {
       const int slot = i % ND;
       const float *qrow = qb + (long long)(i * KS + c) * P, *krow = kb + (long long)(i * KS + c) * P;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        stage8(qrow, x0 + (u0 + 4 * j) * 8, P, vec, piece(slot, 2 * j), piece(slot, 2 * j + 1));
-        stage8(krow, y0 + (u0 + 4 * j) * 8, P, vec, piece(slot, 8 + 2 * j), piece(slot, 9 + 2 * j));
+      for (int j = 0; j < UPT; ++j) {
+        stage8(qrow, x0 + (u0 + UW * j) * 8, P, vec, piece(slot, 2 * j), piece(slot, 2 * j + 1));
+        stage8(krow, y0 + (u0 + UW * j) * 8, P, vec, piece(slot, 2 * UPT + 2 * j), piece(slot, 2 * UPT + 2 * j + 1));
       }
     };
     auto take8 = [&](int slot, int pc, float (&v)[8]) {
@@ -165,17 +169,17 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
       asm volatile("cp.async.commit_group;" ::: "memory");
       asm volatile("cp.async.wait_group %0;" ::"n"(DG - 1) : "memory");   // slab i has landed (this thread's pieces)
       const int slot = i % ND, s = i % NS, ph = (i / NS) & 1;
-      uint4 hq[4], lq[4], hk[4], lk[4];
+      uint4 hq[UPT], lq[UPT], hk[UPT], lk[UPT];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
+      for (int j = 0; j < UPT; ++j) {
         float v[8];
         take8(slot, 2 * j, v); split8(v, hq[j], lq[j]);
-        take8(slot, 8 + 2 * j, v); split8(v, hk[j], lk[j]);
+        take8(slot, 2 * UPT + 2 * j, v); split8(v, hk[j], lk[j]);
       }
       mbar_wait(&empty[s], ph ^ 1);                      // the MMAs that read this stage have completed
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        uint8_t *st = smem + s * STAGE + mn_off(c, u0 + 4 * j);
+      for (int j = 0; j < UPT; ++j) {
+        uint8_t *st = smem + s * STAGE + mn_off(c, u0 + UW * j);
         *reinterpret_cast<uint4 *>(st) = hq[j];
         *reinterpret_cast<uint4 *>(st + T_BYTES) = lq[j];
         *reinterpret_cast<uint4 *>(st + 2 * T_BYTES) = hk[j];
