@@ -665,7 +665,7 @@ def multi_rank_parity(model, dev, rank, world):
         x_all = torch.cat([t.cpu() for t in gather(x)])
         ys = [t.cpu() for t in gather(y)]
         idx_shuffle = torch.argsort(idx_unshuffle).cpu()
-        res["shuffle_matches_oracle"] = all(torch.equal(ys[r], O.batch_shuffle(x_all, idx_shuffle, r, world))
+        res["shuffle_matches_oracle"] = all(torch.equal(ys[r], O.batch_shuffle(x_all, idx_shuffle, r, world)[0])
                                             for r in range(world))
         perms = gather(idx_unshuffle)
         res["perm_equal_across_ranks"] = all(torch.equal(perms[0], t) for t in perms)
