@@ -992,6 +992,9 @@ def own_arm(args):
     # ---- N > 1: where the step time goes between ranks (untimed extra legs, device-side event timings)
     collectives = None
     if world > 1:
+        # after warm-up + both timed regions of all-reduced steps, and BEFORE the no_sync() A/B below, which steps the
+        # optimizer on rank-local gradients and lets the replicas drift on purpose
+        parity["ddp_weights_equal_across_ranks"] = ddp_weights_equal(model, dev, world)
         n_c = min(args.steps, 10)
         model.collective_times = {}
         timed(lambda i: step(resident[i % 2]), n_c)
@@ -1011,7 +1014,6 @@ def own_arm(args):
                             "step_ms_with_serial_image_exchange": round(ms_serial, 3),
                             "note": "all_to_all / all_gather: CUDA events on the issuing stream (the image exchange "
                                     "runs on a side stream under encoder_q); all-reduce overhead from a no_sync() A/B"})
-        parity["ddp_weights_equal_across_ranks"] = ddp_weights_equal(model, dev, world)
 
     # ---- per-kernel figures from the CUDA events recorded inside the timed region
     work = algorithmic_work(B, n_params, world)
