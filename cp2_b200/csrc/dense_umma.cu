@@ -182,7 +182,10 @@ __global__ void dense_nl_kernel(const float *__restrict__ lse, const float *__re
   nl[(long long)b * P_pad + y] = v;
 }
 
-constexpr int GRAD_THREADS = 448;   // warp 0 TMA, warp 1 MMA + TMEM owner, warps 2-9 softmax, 10-13 epilogue
+// warp 0 TMA, warp 1 MMA + TMEM owner, then 4*NSG softmax warps (NSG column groups x 4 TMEM lane quadrants), then 4
+// epilogue warps.  NSG = 2: 448 threads (TY = 128: two 64-column groups); NSG = 3: 576 threads (TY = 192).
+constexpr int grad_threads(int nsg) { return 64 + 128 * nsg + 128; }
+constexpr int GRAD_THREADS = grad_threads(2);
 
 template <int C, int TY, int NST, int NQ, int ND>
 struct GradCfg {
@@ -202,8 +205,8 @@ struct GradCfg {
 //         rows).  nl holds -log2(e)/tau for real entries (NL_MASKED past K), so P~ = exp((l-1)/tau); the softmax
 //         warps also keep fp32 row sums of P~ (z), and the epilogue writes the raw accumulator:
 //           dq[(s*P + r)*C + c] = sum_{k in range s} P~[r,k] u_k[c],   zp[(2s+half)*P_pad + r] = partial z.
-template <int C, int TY, int NST, int NQ, int ND, int PF, int MODE = 0>
-__global__ void __launch_bounds__(GRAD_THREADS, 1)
+template <int C, int TY, int NST, int NQ, int ND, int PF, int MODE = 0, int NSG = 2>
+__global__ void __launch_bounds__(grad_threads(NSG), 1)
 dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                   const __nv_bfloat16 *__restrict__ qhat, const float *__restrict__ nl,
                   const int *__restrict__ key_count, const float *__restrict__ mask_a,
@@ -225,7 +228,8 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       mbar_wait(bar, parity);
     }
   };
-  constexpr int W = TY / 2;                              // S columns per softmax warp
+  constexpr int W = TY / NSG;                            // S columns per softmax warp
+  static_assert(W % 32 == 0, "softmax column groups are whole 32-column chunks");
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = align1024(smem_raw);
   uint8_t *sQ = smem;
@@ -244,7 +248,7 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
   if (threadIdx.x == 0) {
     for (int i = 0; i < NQ; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&kfull[s], 1); mbar_init(&kempty[s], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 8); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 4 * NSG); }
     for (int i = 0; i < ND; ++i) { mbar_init(&d_full[i], 1); mbar_init(&d_empty[i], 4); }
     fence_barrier_init();
     prefetch_tmap(&tm_q);
@@ -353,7 +357,7 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       if (elect_one()) mma_commit(&d_full[db]);
       __syncwarp();
     }
-  } else if (warp < 10) {
+  } else if (warp < 2 + 4 * NSG) {
     // ------------------------------------------------ softmax warps: S -> P~ (bf16, in place)
     const int quad = warp & 3, half = (warp - 2) >> 2;
     const uint32_t lane_off = uint32_t(quad * 32) << 16;
@@ -389,6 +393,7 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
         float z0, z1;
         f2_unpack(zsum, z0, z1);
         const int x = (w % nxt) * TILE + quad * 32 + lane;
+        static_assert(MODE == 0 || NSG == 2, "queue-sums mode: two column groups");
         zp[(long long)(2 * (w / nxt) + half) * P_pad + x] = z0 + z1;
       }
     }
@@ -436,7 +441,7 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
       const float al = (ny > 0) ? alpha[b] * gup : 0.f;
       const uint4 *qrow = reinterpret_cast<const uint4 *>(qhat + ((long long)b * P + (valid ? x : 0)) * C);
       // rank-1 vectors of this image -> shared memory: sva = v1 - v2, svb = v2 (read back as broadcasts)
-      const int et = threadIdx.x - 320;                        // 0..127 among the epilogue threads
+      const int et = threadIdx.x - (64 + 128 * NSG);           // 0..127 among the epilogue threads
       asm volatile("bar.sync 1, 128;" ::: "memory");           // everyone is done with the previous item's copy
       for (int c = et; c < C; c += 128) {
         const float b2 = v2 ? v2[(long long)b * C + c] * gup : 0.f;
@@ -550,7 +555,12 @@ bool fwd_nsw8() {
   const char *e = getenv("CP2_DENSE_NSW_FWD");
   return !(e && atoi(e) == 4);
 }
+int bwd_variant(int dflt) {
+  const char *e = getenv("CP2_DENSE_BWD_VARIANT");
+  return (e && *e) ? atoi(e) : dflt;
+}
 #else
+constexpr int bwd_variant(int dflt) { return dflt; }
 constexpr long long *g_dense_trace = nullptr;
 constexpr int poly_quarters(const char *, int dflt) { return dflt; }
 constexpr bool fwd_nsw8() { return true; }
@@ -571,17 +581,17 @@ int launch_lse(const CUtensorMap &tq, const CUtensorMap &tk, const int *key_coun
   return CP2_OK;
 }
 
-template <int C, int TY, int NST, int NQ, int ND, int PF>
+template <int C, int TY, int NST, int NQ, int ND, int PF, int NSG = 2>
 int launch_grad(const CUtensorMap &tq, const CUtensorMap &tk, const void *qhat, const float *nl,
                 const int *key_count, const float *mask_a, const float *inv_norm, const float *alpha,
                 const float *v1, const float *v2, const float *gscale, float *dq, float scale_log2, int B, int P,
                 int P_pad, cudaStream_t st) {
   using Cfg = GradCfg<C, TY, NST, NQ, ND>;
-  auto kern = dense_grad_kernel<C, TY, NST, NQ, ND, PF>;
+  auto kern = dense_grad_kernel<C, TY, NST, NQ, ND, PF, 0, NSG>;
   CP2_SMEM_ONCE(kern, Cfg::SMEM);
   const long long items = (long long)B * cp2_cdiv(P, TILE);
   const int grid = (int)(items < cp2_num_sms() ? items : cp2_num_sms());
-  kern<<<grid, GRAD_THREADS, Cfg::SMEM, st>>>(tq, tk, static_cast<const __nv_bfloat16 *>(qhat), nl, key_count,
+  kern<<<grid, grad_threads(NSG), Cfg::SMEM, st>>>(tq, tk, static_cast<const __nv_bfloat16 *>(qhat), nl, key_count,
                                               mask_a, inv_norm, alpha, v1, v2, gscale, dq, scale_log2, B, P, P_pad,
                                               g_dense_trace, nullptr, 0, 0);
   CP2_LAUNCH_CHECK();
@@ -635,7 +645,8 @@ extern "C" int cp2_dbg_dense_trace(long long *buf) {   // [n_sms * 16] device co
 }
 #endif
 
-extern "C" int cp2_dense_pad(int P) { return P > 0 ? cp2_cdiv(P, TILE) * TILE : 0; }
+// row length of the nl scratch: whole key tiles of either backward variant (128 / 192 rows)
+extern "C" int cp2_dense_pad(int P) { return P > 0 ? cp2_cdiv(P, 384) * 384 : 0; }
 
 extern "C" int cp2_dense_lse(const void *qhat_t, const void *khat_t, const int *key_count, float *lse,
                              float inv_tau, int B, int C, int P, void *stream) {
@@ -675,7 +686,10 @@ extern "C" int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int 
   if (B == 0) return CP2_OK;
   CP2_REQUIRE(qhat_t && khat_t && lse && mask_a && inv_norm && alpha && v1 && dq && scratch_nl,
               "cp2_dense_grad: null pointer");
-  const int TY = (C == 128) ? 128 : 64;
+  // C = 128 variants: 0 = key tiles of 128 rows, 8 softmax warps, double-buffered accumulator;
+  //                   1 = key tiles of 192 rows, 12 softmax warps (3 column groups of 64), single accumulator
+  const int variant = (C == 128) ? bwd_variant(0) : 0;
+  const int TY = (C == 128) ? (variant == 1 ? 192 : 128) : 64;
   CUtensorMap tq, tk;
   int rc;
   if ((rc = make_feature_tmap(&tq, qhat_t, B, C, P, TILE)) != CP2_OK) return rc;
@@ -689,6 +703,12 @@ extern "C" int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int 
 #define CP2_GRAD(CC, TYV, NSTV, NQV, NDV, PFV)                                                                     \
   launch_grad<CC, TYV, NSTV, NQV, NDV, PFV>(tq, tk, qhat_t, scratch_nl, key_count, mask_a, inv_norm, alpha, v1, \
                                          v2, gscale, dq, sl2, B, P, P_pad, st)
+  if (C == 128 && variant == 1) {
+    return pf == 0 ? launch_grad<128, 192, 3, 1, 1, 0, 3>(tq, tk, qhat_t, scratch_nl, key_count, mask_a, inv_norm, alpha,
+                                                           v1, v2, gscale, dq, sl2, B, P, P_pad, st)
+                   : launch_grad<128, 192, 3, 1, 1, 1, 3>(tq, tk, qhat_t, scratch_nl, key_count, mask_a, inv_norm, alpha,
+                                                           v1, v2, gscale, dq, sl2, B, P, P_pad, st);
+  }
   if (C == 128) {
     switch (pf) { case 0: return CP2_GRAD(128, 128, 5, 1, 2, 0); case 1: return CP2_GRAD(128, 128, 5, 1, 2, 1);
                   case 2: return CP2_GRAD(128, 128, 5, 1, 2, 2); default: return CP2_GRAD(128, 128, 5, 1, 2, 3); }
