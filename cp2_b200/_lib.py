@@ -61,7 +61,7 @@ DEBUG_SIGNATURES = {
 }
 
 EMA_CHUNK = 4096  # CP2_EMA_CHUNK
-ABI_VERSION = 8  # CP2_ABI_VERSION
+ABI_VERSION = 9  # CP2_ABI_VERSION
 
 _lib = None
 _dbg = None

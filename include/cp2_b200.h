@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CP2_ABI_VERSION 8
+#define CP2_ABI_VERSION 9
 
 #define CP2_OK 0
 #define CP2_E_INVALID (-1)      /* bad shape / null pointer / unsupported dim          */
@@ -109,7 +109,7 @@ int cp2_dense_lse(const void *qhat_t, const void *khat_t, const int32_t *key_cou
  * alpha [B], v1 [B,C], v2 [B,C] (v2 may be NULL = zeros) carry every rank-1 term (cp2_loss_combine
  * writes them for a unit upstream gradient); gscale is NULL or a device scalar, the upstream
  * gradient d L / d loss, multiplied into all three on load (no host read, no scaling pass).
- *   scratch_nl : [B, cp2_dense_pad(P)] f32 work space. */
+ *   scratch_nl : [B, cp2_dense_pad(P)] f32 work space (cp2_dense_pad: P rounded up to whole key tiles, a multiple of 384). */
 int cp2_dense_pad(int P);
 int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int32_t *key_count, const float *lse,
                    const float *mask_a, const float *mask_b, const float *inv_norm, const float *alpha,
