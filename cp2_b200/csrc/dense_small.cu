@@ -28,7 +28,7 @@ namespace {
 constexpr int SM_THREADS = 320;          // warp 0 TMA, warp 1 MMA + TMEM owner, warps 2-9 softmax / epilogue
 constexpr int PF_SMALL = 1;              // exponentials evaluated on the FMA pipe: 1 of every 4 column pairs
 constexpr float SEG_DELTA = 0.0078125f;  // acc_seg meter: candidate band below the bf16-operand maximum (2^-7)
-constexpr int SEG_MAXC = 64;             // ... and the most candidates re-scored per image
+constexpr int SEG_MAXC = 32;             // ... and the most candidates re-scored per image
 
 template <int C>
 struct SmallCfg {
@@ -130,24 +130,41 @@ dense_small_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
       const int n = min(*reinterpret_cast<volatile int *>(ncand), SEG_MAXC);
       float bestv = -INFINITY;
       int bestf = 0x7fffffff, bestx = 0, besty = 0, bestr = 0;
-      for (int i = 0; i < n; ++i) {
-        const int x = cand[i] >> 16, yr = cand[i] & 0xffff;
-        const int y = seg.perm_k ? __ldg(seg.perm_k + (long long)b * P + yr) : yr;
-        const float *qp = seg.q_f32 + (long long)b * C * P + x, *kp = seg.k_f32 + (long long)b * C * P + y;
-        float qv[C / 32], kv[C / 32];
+      // four candidates per round: their index reads, then their 2 x C/32 feature reads per lane, are in flight
+      // together (two memory round trips per FOUR candidates instead of per candidate)
+      for (int i0 = 0; i0 < n; i0 += 4) {
+        int xs[4], yrs[4], ys[4];
 #pragma unroll
-        for (int j = 0; j < C / 32; ++j) {
-          qv[j] = __ldg(qp + (long long)(lane + 32 * j) * P);
-          kv[j] = __ldg(kp + (long long)(lane + 32 * j) * P);
+        for (int u = 0; u < 4; ++u) {
+          const int i = min(i0 + u, n - 1);
+          xs[u] = cand[i] >> 16;
+          yrs[u] = cand[i] & 0xffff;
+          ys[u] = seg.perm_k ? __ldg(seg.perm_k + (long long)b * P + yrs[u]) : yrs[u];
         }
-        const float iq = __ldg(seg.inv_q + (long long)b * P + x), ik = __ldg(seg.inv_k + (long long)b * P + y);
-        float d = 0.f;
+        float qv[4][C / 32], kv[4][C / 32], iq[4], ik[4];
 #pragma unroll
-        for (int j = 0; j < C / 32; ++j) d = fmaf(qv[j] * iq, kv[j] * ik, d);
+        for (int u = 0; u < 4; ++u) {
+          const float *qp = seg.q_f32 + (long long)b * C * P + xs[u], *kp = seg.k_f32 + (long long)b * C * P + ys[u];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
-        const int flat = x * P + y;
-        if (d > bestv || (d == bestv && flat < bestf)) { bestv = d; bestf = flat; bestx = x; besty = y; bestr = yr; }
+          for (int j = 0; j < C / 32; ++j) {
+            qv[u][j] = __ldg(qp + (long long)(lane + 32 * j) * P);
+            kv[u][j] = __ldg(kp + (long long)(lane + 32 * j) * P);
+          }
+          iq[u] = __ldg(seg.inv_q + (long long)b * P + xs[u]);
+          ik[u] = __ldg(seg.inv_k + (long long)b * P + ys[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          float d = 0.f;
+#pragma unroll
+          for (int j = 0; j < C / 32; ++j) d = fmaf(qv[u][j] * iq[u], kv[u][j] * ik[u], d);
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+          const int flat = xs[u] * P + ys[u];
+          if (i0 + u < n && (d > bestv || (d == bestv && flat < bestf))) {
+            bestv = d; bestf = flat; bestx = xs[u]; besty = ys[u]; bestr = yrs[u];
+          }
+        }
       }
       if (lane == 0) {
         float h = 0.f;
