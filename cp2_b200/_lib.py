@@ -37,6 +37,9 @@ SIGNATURES = {
     "cp2_dense_weighted_lse": (c_int, [c_void_p] * 18 + [c_float] * 3 + [c_int, c_float, c_float] + [c_int] * 6 + [c_void_p]),
     "cp2_dense_weighted_grad": (c_int, [c_void_p] * 16 + [c_float] * 3 + [c_int, c_float, c_float] + [c_int] * 6 + [c_void_p]),
     "cp2_dense_weighted_small": (c_int, [c_void_p] * 19 + [c_float] * 3 + [c_int, c_float, c_float] + [c_int] * 6 + [c_void_p]),
+    "cp2_dense_weighted_stream_ids_bytes": (c_int64, [c_int, c_int]),
+    "cp2_dense_weighted_stream": (c_int, [c_void_p] * 20 + [c_float] * 3 + [c_int, c_float, c_float] + [c_int] * 6 + [c_void_p]),
+    "cp2_dense_weighted_stream_grad": (c_int, [c_void_p] * 15 + [c_float] * 3 + [c_int, c_float, c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_dense_top1_scratch_floats": (c_int64, [c_int, c_int]),
     "cp2_dense_top1": (c_int, [c_void_p] * 7 + [c_int] * 3 + [c_void_p]),
     "cp2_rows_nce": (c_int, [c_void_p] * 7 + [c_float, c_int, c_int, c_int, c_int64, c_int, c_int64, c_void_p]),

@@ -28,6 +28,7 @@
 #include "cp2_b200_debug.h"
 #include "umma.cuh"
 #include "dense_common.cuh"
+#include "weighted_common.cuh"
 
 using namespace umma;
 using namespace dense;
@@ -196,7 +197,16 @@ struct GradCfg {
   static constexpr int NBARS = 2 * NQ + 2 * NST + 4 + 2 * ND;
   static constexpr size_t SMEM = 1024 + (size_t)NQ * OPER_Q + (size_t)NST * OPER_K + (size_t)NST * TY * 4 +
                                  2 * C * 4 + NBARS * 8 + 16;
+  static constexpr size_t W_EXTRA = (size_t)NST * TY * 20;   // MODE 2: per-stage b (f32), pixel ids, region ids (int64) of the key tile
   static_assert(2 * TY + ND * C <= 512, "TMEM budget");
+};
+
+// MODE 2 (f3, PROPOSED modes on maps that do not fit TMEM): what the weighted soft-max needs besides the operands
+struct GradW {
+  const long long *ids;        // [4][B][P_pad] pid_a, pid_b, rid_a, rid_b gathered at the lattice (zero past P)
+  const float *b_pad;          // [B][P_pad] key-side mask (zero past P)
+  const float *wstats;         // [B][3] centre, A, Bm
+  weighted::WParams p;
 };
 
 // MODE 0: the dense loss's backward (items = (image, 128 query pixels), keys = the image's key pixels).
@@ -205,6 +215,9 @@ struct GradCfg {
 //         rows).  nl holds -log2(e)/tau for real entries (NL_MASKED past K), so P~ = exp((l-1)/tau); the softmax
 //         warps also keep fp32 row sums of P~ (z), and the epilogue writes the raw accumulator:
 //           dq[(s*P + r)*C + c] = sum_{k in range s} P~[r,k] u_k[c],   zp[(2s+half)*P_pad + r] = partial z.
+// MODE 2: MODE 0 with the PROPOSED-mode pair weights and NegativeType squash (builder.py:1204-1243, 1332-1386):
+//         the softmax warps write g[x,y] = b_y (exp(z - lse_y) - a_x/A) w t'(S) instead of P~; the key tile's mask and
+//         ids travel with the tile (bulk copies into the stage), the query pixel's own sit in registers.
 template <int C, int TY, int NST, int NQ, int ND, int PF, int MODE = 0, int NSG = 2>
 __global__ void __launch_bounds__(grad_threads(NSG), 1)
 dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
@@ -214,7 +227,7 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
                   const float *__restrict__ v1, const float *__restrict__ v2,
                   const float *__restrict__ gscale, float *__restrict__ dq,
                   float scale_log2, int B, int P, int P_pad, long long *__restrict__ trace,
-                  float *__restrict__ zp, int tps, int ktiles) {
+                  float *__restrict__ zp, int tps, int ktiles, const GradW gw) {
   using Cfg = GradCfg<C, TY, NST, NQ, ND>;
   // optional per-CTA wait-time accounting (test-only; cp2_dbg_dense_trace): slot k of trace[blockIdx.x*16+k]
   long long tr_a = 0, tr_b = 0, tr_c = 0, tr_d = 0;
@@ -236,7 +249,10 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
   uint8_t *sK = sQ + NQ * Cfg::OPER_Q;
   float *nlbuf = reinterpret_cast<float *>(sK + NST * Cfg::OPER_K);      // [NST][TY]
   float *sva = nlbuf + NST * TY, *svb = sva + C;                          // [C] each (epilogue)
-  uint64_t *bars = reinterpret_cast<uint64_t *>(svb + C);
+  long long *pbbuf = reinterpret_cast<long long *>(svb + C);              // MODE 2: [NST][TY] each
+  long long *rbbuf = pbbuf + (MODE == 2 ? NST * TY : 0);
+  float *bbuf = reinterpret_cast<float *>(rbbuf + (MODE == 2 ? NST * TY : 0));
+  uint64_t *bars = reinterpret_cast<uint64_t *>(bbuf + (MODE == 2 ? NST * TY : 0));
   uint64_t *q_full = bars, *q_empty = q_full + NQ, *kfull = q_empty + NQ, *kempty = kfull + NST,
            *s_full = kempty + NST, *p_full = s_full + 2, *d_full = p_full + 2, *d_empty = d_full + ND;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(d_empty + ND);
@@ -284,11 +300,17 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
         for (int j = 0; j < ny; ++j, ++g) {
           const int s = g % NST;
           twait(&kempty[s], ((g / NST) & 1) ^ 1, tr_b);
-          mbar_expect_tx(&kfull[s], Cfg::OPER_K + TY * 4);
+          mbar_expect_tx(&kfull[s], Cfg::OPER_K + TY * 4 + (MODE == 2 ? TY * 20 : 0));
           for (int kb = 0; kb < C / 64; ++kb)
             tma_load_3d(sK + s * Cfg::OPER_K + kb * Cfg::KBOX, &tm_k, &kfull[s], kb * 64, (tile0(b) + j) * TY, img(b));
           bulk_load_1d(nlbuf + s * TY, nl + (MODE == 1 ? 0 : (long long)b * P_pad) + (long long)(tile0(b) + j) * TY,
                        TY * 4, &kfull[s]);
+          if constexpr (MODE == 2) {
+            const long long o = (long long)b * P_pad + j * TY, plane = (long long)B * P_pad;
+            bulk_load_1d(bbuf + s * TY, gw.b_pad + o, TY * 4, &kfull[s]);
+            bulk_load_1d(pbbuf + s * TY, gw.ids + plane + o, TY * 8, &kfull[s]);
+            bulk_load_1d(rbbuf + s * TY, gw.ids + 3 * plane + o, TY * 8, &kfull[s]);
+          }
         }
       }
     }
@@ -366,6 +388,20 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
     for (int w = blockIdx.x; w < items; w += gridDim.x) {
       const int ny = key_tiles(w / nxt);
       f2 zsum = f2_pack(0.f, 0.f);
+      // MODE 2: this lane's query pixel
+      float w_ax = 0.f, w_aoa = 0.f, w_centre = 0.f;
+      long long w_pa = 0, w_ra = 0;
+      bool w_vx = false;
+      if constexpr (MODE == 2) {
+        const int wb = w / nxt, x = (w % nxt) * TILE + quad * 32 + lane;
+        w_vx = x < P;
+        const long long o = (long long)wb * P_pad + (w_vx ? x : 0);
+        w_ax = w_vx ? mask_a[(long long)wb * P + x] : 0.f;
+        w_pa = w_vx ? gw.ids[o] : 0;
+        w_ra = w_vx ? gw.ids[2ll * B * P_pad + o] : 0;
+        w_aoa = w_ax / gw.wstats[3 * wb + 1];
+        w_centre = gw.p.neg_type >= 2 ? gw.wstats[3 * wb] : 0.f;
+      }
       for (int j = 0; j < ny; ++j, ++g) {
         const int s = g % NST;
         const uint32_t tS = tmem + (g & 1) * TY + lane_off + half * W;
@@ -381,7 +417,28 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
           tmem_wait_ld();
           if (ch + 1 < W / 32) tmem_ld32(tS + (ch + 1) * 32, rb[(ch + 1) & 1]);
           const uint32_t(&r)[32] = rb[ch & 1];
-          softmax_chunk_bwd<PF, MODE == 1>(r, nl_saddr + ch * 128, scale2, pk, &zsum);
+          if constexpr (MODE == 2) {
+            const int c0 = s * TY + half * W + ch * 32;          // first key of the chunk inside the stage buffers
+#pragma unroll
+            for (int jj = 0; jj < 32; jj += 2) {
+              float g2[2];
+#pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                const float by = bbuf[c0 + jj + e];              // 0 past P
+                float gv = 0.f;
+                if (by != 0.f && w_vx) {
+                  float z2, wd;
+                  weighted::pair_eval(__uint_as_float(r[jj + e]), w_ax != 0.f, w_pa, pbbuf[c0 + jj + e], w_ra,
+                                      rbbuf[c0 + jj + e], w_centre, gw.p, scale_log2, z2, wd);
+                  gv = by * (ex2_approx(z2 + nlbuf[c0 + jj + e]) - w_aoa) * wd;
+                }
+                g2[e] = gv;
+              }
+              pk[jj >> 1] = pack_bf16x2(g2[0], g2[1]);
+            }
+          } else {
+            softmax_chunk_bwd<PF, MODE == 1>(r, nl_saddr + ch * 128, scale2, pk, &zsum);
+          }
           tmem_st16(tS + ch * 16, pk);
         }
         tmem_wait_st();
@@ -593,7 +650,7 @@ int launch_grad(const CUtensorMap &tq, const CUtensorMap &tk, const void *qhat, 
   const int grid = (int)(items < cp2_num_sms() ? items : cp2_num_sms());
   kern<<<grid, grad_threads(NSG), Cfg::SMEM, st>>>(tq, tk, static_cast<const __nv_bfloat16 *>(qhat), nl, key_count,
                                               mask_a, inv_norm, alpha, v1, v2, gscale, dq, scale_log2, B, P, P_pad,
-                                              g_dense_trace, nullptr, 0, 0);
+                                              g_dense_trace, nullptr, 0, 0, GradW{});
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }
@@ -607,12 +664,62 @@ int launch_queue_sums(const CUtensorMap &tq, const CUtensorMap &tk, const float 
   const long long items = (long long)nsplit * cp2_cdiv(N, TILE);
   const int grid = (int)(items < cp2_num_sms() ? items : cp2_num_sms());
   kern<<<grid, GRAD_THREADS, Cfg::SMEM, st>>>(tq, tk, nullptr, nl, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
-                                              nullptr, gacc, scale_log2, nsplit, N, N_pad, nullptr, zp, tps, ktiles);
+                                              nullptr, gacc, scale_log2, nsplit, N, N_pad, nullptr, zp, tps, ktiles,
+                                              GradW{});
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}
+
+
+// f3 backward on the streaming kernel (MODE 2).  C = 128.
+int launch_grad_weighted(const CUtensorMap &tq, const CUtensorMap &tk, const void *qhat, const float *nl,
+                         const float *mask_a, const float *inv_norm, const float *alpha, const float *v1,
+                         const float *v2, const float *gscale, float *dq, float scale_log2, int B, int P, int P_pad,
+                         const GradW &gw, cudaStream_t st) {
+  using Cfg = GradCfg<128, 128, 5, 1, 2>;
+  auto kern = dense_grad_kernel<128, 128, 5, 1, 2, 0, 2>;
+  const size_t smem = Cfg::SMEM + Cfg::W_EXTRA;
+  CP2_SMEM_ONCE(kern, smem);
+  const long long items = (long long)B * cp2_cdiv(P, TILE);
+  const int grid = (int)(items < cp2_num_sms() ? items : cp2_num_sms());
+  kern<<<grid, GRAD_THREADS, smem, st>>>(tq, tk, static_cast<const __nv_bfloat16 *>(qhat), nl, nullptr, mask_a, inv_norm,
+                                         alpha, v1, v2, gscale, dq, scale_log2, B, P, P_pad, nullptr, nullptr, 0, 0, gw);
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }
 
 }  // namespace
+
+extern "C" int cp2_dense_weighted_stream_grad(const void *qhat_t, const void *khat_t, const float *mask_a,
+                                              const float *mask_b, const float *lse, const void *ids_pad,
+                                              const float *b_pad, const float *wstats, const float *inv_norm,
+                                              const float *alpha, const float *v1, const float *v2,
+                                              const float *gscale, float *dq, float *scratch_nl, float w_pix,
+                                              float w_reg, float w_not, int neg_type, float neg_scale, float inv_tau,
+                                              int B, int C, int P, void *stream) {
+  CP2_REQUIRE(C == 128, "cp2_dense_weighted_stream_grad: C=%d unsupported (128)", C);
+  CP2_REQUIRE(B > 0 && P > 0 && B <= 65535, "cp2_dense_weighted_stream_grad: bad shape B=%d P=%d", B, P);
+  CP2_REQUIRE(inv_tau > 0.f && inv_tau <= 16.f, "cp2_dense_weighted_stream_grad: 1/tau=%g outside (0, 16]", (double)inv_tau);
+  CP2_REQUIRE(neg_type >= 0 && neg_type <= 3, "cp2_dense_weighted_stream_grad: negative type %d", neg_type);
+  CP2_REQUIRE(qhat_t && khat_t && mask_a && mask_b && lse && ids_pad && b_pad && wstats && inv_norm && alpha && v1 && dq &&
+              scratch_nl, "cp2_dense_weighted_stream_grad: null pointer");
+  CUtensorMap tq, tk;
+  int rc;
+  if ((rc = make_feature_tmap(&tq, qhat_t, B, C, P, TILE)) != CP2_OK) return rc;
+  if ((rc = make_feature_tmap(&tk, khat_t, B, C, P, 128)) != CP2_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int P_pad = cp2_dense_pad(P);
+  dense_nl_kernel<<<dim3(cp2_cdiv(P_pad, 256), B), 256, 0, st>>>(lse, mask_b, nullptr, scratch_nl, P, P_pad);
+  CP2_LAUNCH_CHECK();
+  GradW gw;
+  gw.ids = static_cast<const long long *>(ids_pad);
+  gw.b_pad = b_pad;
+  gw.wstats = wstats;
+  gw.p = weighted::WParams{w_pix, w_reg, w_not, neg_scale, inv_tau, neg_type, P, 0, 0, 0, 0};
+  return launch_grad_weighted(tq, tk, qhat_t, scratch_nl, mask_a, inv_norm, alpha, v1, v2, gscale, dq, inv_tau * LOG2E, B,
+                              P, P_pad, gw, st);
+}
+
 
 // ranges the queue is cut into so that (ranges x row tiles) fills the SMs
 extern "C" int cp2_queue_sums_split(int N, int K) {

@@ -40,20 +40,6 @@ struct WSmem {                           // after the two operand images
 template <int C>
 size_t ws_smem(int rows) { return 1024 + 2 * (size_t)(C / 64) * rows * 128 + sizeof(WSmem) + 16; }
 
-// one pixel pair: base-2 logit z2 = w * t(s) * (log2(e) / tau) and wd = w * dt/ds
-__device__ __forceinline__ void pair_eval(float s, bool label, long long pa, long long pb, long long ra, long long rb,
-                                          float centre, const WParams &p, float sl2, float &z2, float &wd) {
-  float t = s, dt = 1.f;
-  if (p.neg_type != 0 && !label) {
-    const float e = ex2_approx((s - centre) * (-p.neg_scale * LOG2E));
-    t = __fdividef(2.f, 1.f + e) - 1.f;
-    dt = (1.f - t * t) * 0.5f * p.neg_scale;
-  }
-  const float w = pair_weight(pa, pb, ra, rb, p);
-  z2 = w * t * sl2;
-  wd = w * dt;
-}
-
 template <int C>
 __global__ void __launch_bounds__(WS_THREADS, 1)
 dense_wsmall_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,

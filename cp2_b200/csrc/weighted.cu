@@ -476,6 +476,15 @@ int weighted::prepass(const __nv_bfloat16 *q, const __nv_bfloat16 *k, const floa
   return CP2_OK;
 }
 
+int weighted::finalize(const float *partial, const float *best_v, const int *best_i, const float *wstats,
+                       const float *mask_a, const float *mask_b, float *dense_n, float *acc_seg, int B, int P, int tiles,
+                       cudaStream_t st) {
+  weighted_finalize_kernel<<<1, WTHREADS, 0, st>>>(partial, best_v, best_i, wstats, mask_a, mask_b, dense_n, acc_seg, B, P,
+                                                   tiles);
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}
+
 extern "C" int cp2_dense_weighted_tiles(int P) { return 3 * cp2_cdiv(P, WT) + SEL_INTS; }
 
 extern "C" int cp2_dense_weighted_lse(const void *qhat_t, const void *khat_t, const float *mask_a, const float *mask_b,

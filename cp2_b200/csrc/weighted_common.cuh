@@ -36,6 +36,23 @@ __device__ __forceinline__ void squash(float s, bool label, float centre, const 
 }
 
 
+// One pixel pair for the tensor-core implementations: base-2 logit z2 = w * t(s) * sl2 (sl2 = log2(e) / tau) and
+// wd = w * dt/ds; the squash's exponential and division on the MUFU (ex2 / rcp approximations, rel. error ~2^-22).
+__device__ __forceinline__ void pair_eval(float s, bool label, long long pa, long long pb, long long ra, long long rb,
+                                          float centre, const WParams &p, float sl2, float &z2, float &wd) {
+  float t = s, dt = 1.f;
+  if (p.neg_type != 0 && !label) {
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"((s - centre) * (-p.neg_scale * 1.4426950408889634f)));
+    t = __fdividef(2.f, 1.f + e) - 1.f;
+    dt = (1.f - t * t) * 0.5f * p.neg_scale;
+  }
+  const float w = pair_weight(pa, pb, ra, rb, p);
+  z2 = w * t * sl2;
+  wd = w * dt;
+}
+
+
 inline int make_params(WParams &p, float w_pix, float w_reg, float w_not, int neg_type, float neg_scale, float inv_tau,
                 int P, int ids_h, int ids_w, int os) {
   CP2_REQUIRE(os >= 1 && ids_h >= 1 && ids_w >= 1, "cp2_dense_weighted: bad id map %dx%d stride %d", ids_h, ids_w, os);
@@ -49,6 +66,10 @@ inline int make_params(WParams &p, float w_pix, float w_reg, float w_not, int ne
   return CP2_OK;
 }
 
+
+// dense_n[b] / acc_seg from the per-(image, key tile) partial results of a forward kernel (weighted.cu)
+int finalize(const float *partial, const float *best_v, const int *best_i, const float *wstats, const float *mask_a,
+             const float *mask_b, float *dense_n, float *acc_seg, int B, int P, int tiles, cudaStream_t st);
 
 int prepass(const __nv_bfloat16 *q, const __nv_bfloat16 *k, const float *mask_a, const float *mask_b,
             const float *pos_q, const float *neg_q, const float *pos_k, const float *neg_k, float *wstats,

@@ -567,6 +567,46 @@ def dense_weighted_small(qhat_t, khat_t, mask_a, mask_b, pw, pos_q, neg_q, pos_k
     return lse, dense_n, wstats, count, hit, acc
 
 
+def dense_weighted_stream_ok(C, P, inv_tau):
+    """Shapes the streaming tensor-core pair of the PROPOSED modes takes (any map size; used when the single-kernel
+    path does not apply: maps above 256 pixels, batches beyond one wave)."""
+    return C == 128 and P >= 1 and 0.0 < inv_tau <= MAX_INV_TAU
+
+
+def dense_weighted_stream(qhat_t, khat_t, mask_a, mask_b, pw, pos_q, neg_q, pos_k, neg_k, inv_tau):
+    """cp2_dense_weighted_stream -> (lse [B,P], dense_n [B], wstats [B,3], key_count [B] int32, acc_seg [1],
+    ids_pad, b_pad): cp2_dense_weighted_lse's results on the tensor cores + what the streaming backward needs."""
+    B, P, C = qhat_t.shape
+    lib, dev = _lib.load(), qhat_t.device
+    f32 = dict(device=dev, dtype=torch.float32)
+    lse, dense_n, wstats = torch.empty((B, P), **f32), torch.empty((B,), **f32), torch.empty((B, 3), **f32)
+    acc_seg = torch.empty((1,), **f32)
+    count = torch.empty((B,), device=dev, dtype=torch.int32)
+    scratch = torch.empty((B, lib.cp2_dense_weighted_tiles(P)), **f32)
+    ids_pad = torch.empty((lib.cp2_dense_weighted_stream_ids_bytes(B, P) // 8,), device=dev, dtype=torch.int64)
+    b_pad = torch.empty((B, lib.cp2_dense_pad(P)), **f32)
+    _call("cp2_dense_weighted_stream", 4, lib.cp2_dense_weighted_stream, _ptr(qhat_t), _ptr(khat_t), _ptr(mask_a),
+          _ptr(mask_b), *pw._args(), _ptr(pos_q), _ptr(neg_q), _ptr(pos_k), _ptr(neg_k), _ptr(lse), _ptr(dense_n),
+          _ptr(acc_seg), _ptr(wstats), _ptr(count), _ptr(scratch), _ptr(ids_pad), _ptr(b_pad),
+          *pw._tail(inv_tau, B, C, P))
+    return lse, dense_n, wstats, count, acc_seg, ids_pad, b_pad
+
+
+def dense_weighted_stream_grad(qhat_t, khat_t, mask_a, mask_b, pw, lse, wstats, ids_pad, b_pad, inv_norm, alpha, v1, v2,
+                               inv_tau, gscale=None):
+    """cp2_dense_weighted_stream_grad -> dq [B,C,P] (the weighted backward on the dense backward kernel)."""
+    B, P, C = qhat_t.shape
+    lib = _lib.load()
+    dq = torch.empty((B, C, P), device=qhat_t.device, dtype=torch.float32)
+    nl = torch.empty((B, lib.cp2_dense_pad(P)), device=qhat_t.device, dtype=torch.float32)
+    wp, wr, wn, code, scale = pw.scalars
+    _call("cp2_dense_weighted_stream_grad", 2, lib.cp2_dense_weighted_stream_grad, _ptr(qhat_t), _ptr(khat_t),
+          _ptr(mask_a), _ptr(mask_b), _ptr(lse), _ptr(ids_pad), _ptr(b_pad), _ptr(wstats), _ptr(inv_norm), _ptr(alpha),
+          _ptr(v1), _ptr(v2), _ptr(gscale), _ptr(dq), _ptr(nl), wp, wr, wn, code, scale, float(inv_tau), B, C, P,
+          _stream())
+    return dq
+
+
 def dense_weighted_grad(qhat_t, khat_t, mask_a, mask_b, pw, lse, wstats, inv_norm, alpha, v1, v2, inv_tau, gscale=None):
     """cp2_dense_weighted_grad -> dq [B,C,P]."""
     B, P, C = qhat_t.shape
@@ -598,10 +638,16 @@ class CP2WeightedLossFunction(torch.autograd.Function):
                                       q_neg if (bg and track_accuracy) else None,
                                       k_neg if (bg and track_accuracy) else None, shadow=queue_shadow)
         ctx.small = dense_small_preferred(B, C, qh.shape[1], qh.device)
+        ctx.stream_extra = None
         if ctx.small:                    # map fits TMEM: the tensor-core kernel, which also leaves the P^2 part of dq
             lse, dense_n, wstats, kcnt, hit, acc = dense_weighted_small(qh, kh, mask_a, mask_b, pw, sq, nsq, sk, nsk,
                                                                         1.0 / tl)
             acc_seg = None
+        elif dense_weighted_stream_ok(C, qh.shape[1], 1.0 / tl):      # larger maps: the streaming tensor-core pair
+            lse, dense_n, wstats, kcnt, acc_seg, ids_pad, b_pad = dense_weighted_stream(qh, kh, mask_a, mask_b, pw, sq,
+                                                                                        nsq, sk, nsk, 1.0 / tl)
+            hit = acc = None
+            ctx.stream_extra = (ids_pad, b_pad)
         else:
             lse, dense_n, wstats, kcnt, acc_seg = dense_weighted_lse(qh, kh, mask_a, mask_b, pw, sq, nsq, sk, nsk,
                                                                      1.0 / tl)
@@ -627,6 +673,9 @@ class CP2WeightedLossFunction(torch.autograd.Function):
             g = g.float().contiguous()
         if ctx.small:                    # kh holds acc
             dq = dense_small_bwd(kh, qh, mask_a, q_inv, alpha, v1, v2, key_count=kcnt, gscale=g)
+        elif ctx.stream_extra is not None:
+            dq = dense_weighted_stream_grad(qh, kh, mask_a, mask_b, ctx.pw, lse, wstats, *ctx.stream_extra, q_inv, alpha,
+                                            v1, v2, ctx.inv_tl, gscale=g)
         else:
             dq = dense_weighted_grad(qh, kh, mask_a, mask_b, ctx.pw, lse, wstats, q_inv, alpha, v1, v2, ctx.inv_tl,
                                      gscale=g)

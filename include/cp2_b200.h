@@ -326,6 +326,28 @@ int cp2_dense_weighted_small(const void *qhat_t, const void *khat_t, const float
                              int neg_type, float neg_scale, float inv_tau, int B, int C, int P, int ids_h, int ids_w,
                              int os, void *stream);
 
+/* f3 on the tensor cores for maps that do not fit TMEM (P > 256, C = 128; e.g. 28x28): the streaming tcgen05
+ * pair.  cp2_dense_weighted_stream = cp2_dense_weighted_lse (same outputs: lse, dense_n, acc_seg, wstats,
+ * key_count) and additionally leaves the ids gathered at the lattice and the padded key mask for the backward:
+ *   ids_pad : cp2_dense_weighted_stream_ids_bytes(B,P) bytes = [4][B][cp2_dense_pad(P)] int64 (pid_a, pid_b, rid_a, rid_b)
+ *   b_pad   : [B][cp2_dense_pad(P)] f32
+ * cp2_dense_weighted_stream_grad = cp2_dense_weighted_grad on the tensor cores (dense backward kernel, weighted
+ * soft-max in place in TMEM); scratch_nl [B, cp2_dense_pad(P)] f32.  0 < inv_tau <= 16. */
+int64_t cp2_dense_weighted_stream_ids_bytes(int B, int P);
+int cp2_dense_weighted_stream(const void *qhat_t, const void *khat_t, const float *mask_a, const float *mask_b,
+                              const int64_t *pixel_ids_a, const int64_t *pixel_ids_b, const int64_t *region_ids_a,
+                              const int64_t *region_ids_b, const float *pos_q, const float *neg_q, const float *pos_k,
+                              const float *neg_k, float *lse, float *dense_n, float *acc_seg, float *wstats,
+                              int32_t *key_count, float *scratch, void *ids_pad, float *b_pad, float w_pix,
+                              float w_reg, float w_not, int neg_type, float neg_scale, float inv_tau, int B, int C,
+                              int P, int ids_h, int ids_w, int os, void *stream);
+int cp2_dense_weighted_stream_grad(const void *qhat_t, const void *khat_t, const float *mask_a, const float *mask_b,
+                                   const float *lse, const void *ids_pad, const float *b_pad, const float *wstats,
+                                   const float *inv_norm, const float *alpha, const float *v1, const float *v2,
+                                   const float *gscale, float *dq, float *scratch_nl, float w_pix, float w_reg,
+                                   float w_not, int neg_type, float neg_scale, float inv_tau, int B, int C, int P,
+                                   void *stream);
+
 /* f4 — acc_seg without the [B,P,P] logits.  Replaces builder.py:1442-1448:
  *   hit[n] = mask_a[n,x*] * mask_b[n,y*] at (x*,y*) = argmax_{x,y} qhat_x . khat_y (first occurrence, flat
  *   index x*P+y as the reference's reshape); acc[0] = 100 * mean_n hit[n].

@@ -139,6 +139,52 @@ def test_weighted_dense_vs_oracle(ops, B, C, hw, os_, neg, tl, weights):
         assert rel_l2(dq2, dq) < 6e-3, rel_l2(dq2, dq)          # g is rounded to bf16 for the tensor cores
 
 
+@pytest.mark.parametrize("B,hw,os_,neg,tl,weights", [
+    (2, 28, 2, "FIXED", 0.2, (5.0, 2.0, 1.0)),
+    (3, 14, 2, "AVERAGE", 0.2, (10.0, 2.0, 0.5)),
+    (2, 23, 1, "MEDIAN", 0.5, (3.0, 1.0, 0.25)),
+    (1, 18, 2, "NONE", 1.0, (10.0, 1.0, 1.0)),
+])
+def test_weighted_stream_vs_oracle_and_simt(ops, B, hw, os_, neg, tl, weights):
+    """The streaming tensor-core pair of the PROPOSED modes (cp2_dense_weighted_stream / _stream_grad) against the
+    oracle and against the fp32 SIMT pair it replaces on maps that do not fit TMEM."""
+    C = 128
+    gen = torch.Generator().manual_seed(7 * hw + B)
+    P = hw * hw
+    q = torch.randn(B, C, P, generator=gen)
+    k = q.roll(1, dims=2) * 0.7 + torch.randn(B, C, P, generator=gen) * 0.7
+    ma = (torch.rand(B, P, generator=gen) < 0.65).float()
+    mb = (torch.rand(B, P, generator=gen) < 0.65).float()
+    pa, pb, ra, rb = _ids(B, hw, os_, gen)
+    sub = lambda t: O.stride_subsample(t, os_) if os_ > 1 else t
+    w = O.cp2_corr_weights(sub(pa), sub(pb), sub(ra), sub(rb), ma, mb, *weights)
+    qr = q.clone().requires_grad_(True)
+    qh = F.normalize(qr, dim=1)
+    qh = qh + (qh.bfloat16().float() - qh).detach()
+    kh = F.normalize(k, dim=1).bfloat16().float()
+    ref = O.dense_infonce_weighted(qh, kh, ma, mb, w, tl, neg, 2.0)
+    ref.backward()
+    assert ops.dense_weighted_stream_ok(C, P, 1.0 / tl)
+    qd, kd, mad, mbd = q.cuda(), k.cuda(), ma.cuda(), mb.cuda()
+    qt, q_inv, sq, nsq, _ = ops.prep_features(qd, mad)
+    kt, _, sk, nsk, _ = ops.prep_features(kd, mbd)
+    pw = ops.PairWeights(pa.cuda(), pb.cuda(), ra.cuda(), rb.cuda(), os_, *weights, neg, 2.0)
+    lse0, dn0, ws0, cnt0, acc0 = ops.dense_weighted_lse(qt, kt, mad, mbd, pw, sq, nsq, sk, nsk, 1.0 / tl)
+    lse, dn, ws, cnt, acc_seg, ids_pad, b_pad = ops.dense_weighted_stream(qt, kt, mad, mbd, pw, sq, nsq, sk, nsk, 1.0 / tl)
+    np.testing.assert_allclose(dn.mean().item(), ref.item(), rtol=LOSS_RTOL)
+    np.testing.assert_allclose(dn.cpu().numpy(), dn0.cpu().numpy(), rtol=3e-5)
+    assert torch.equal(cnt, cnt0) and torch.equal(ws, ws0)
+    assert torch.allclose(lse, lse0, rtol=0, atol=1e-4), float((lse - lse0).abs().max())
+    np.testing.assert_allclose(acc_seg.item(), acc0.item(), rtol=1e-6)
+    alpha = (1.0 / tl) / (B * mb.sum(1))
+    v1 = torch.zeros(B, C)
+    dq0 = ops.dense_weighted_grad(qt, kt, mad, mbd, pw, lse0, ws0, q_inv, alpha.cuda(), v1.cuda(), None, 1.0 / tl)
+    dq = ops.dense_weighted_stream_grad(qt, kt, mad, mbd, pw, lse, ws, ids_pad, b_pad, q_inv, alpha.cuda(), v1.cuda(), None,
+                                        1.0 / tl, gscale=torch.tensor([1.0], device="cuda"))
+    assert rel_l2(dq, qr.grad) < GRAD_REL_L2, rel_l2(dq, qr.grad)
+    assert rel_l2(dq, dq0) < 6e-3, rel_l2(dq, dq0)                 # g is rounded to bf16 for the tensor cores
+
+
 def test_weighted_all_ones_equals_cp2_path(ops):
     """w = 1 everywhere and no squash is the CP2 loss: the SIMT pair must agree with the tensor-core path."""
     gen = torch.Generator().manual_seed(3)
