@@ -504,10 +504,21 @@ def weighted_sweep(peaks, iters=20):
 
         small = ops.dense_small_preferred(B, C, P, dev)          # maps that fit TMEM: the tcgen05 kernel
 
+        stream = (not small) and ops.dense_weighted_stream_ok(C, P, inv_tau)    # larger maps: streaming tcgen05 pair
+
         def ours():
             if small:
                 _, _, _, cnt, _, acc = ops.dense_weighted_small(qh, kh, ma, mb, pw, sq, nsq, sk, nsk, inv_tau)
                 return ops.dense_small_bwd(acc, qh, ma, q_inv, alpha, v1, None, key_count=cnt)
+            if stream:
+                lse, _, wstats, _, _, ids_pad, b_pad = ops.dense_weighted_stream(qh, kh, ma, mb, pw, sq, nsq, sk, nsk,
+                                                                                 inv_tau)
+                return ops.dense_weighted_stream_grad(qh, kh, ma, mb, pw, lse, wstats, ids_pad, b_pad, q_inv, alpha, v1,
+                                                      None, inv_tau)
+            lse, dense_n, wstats, _, _ = ops.dense_weighted_lse(qh, kh, ma, mb, pw, sq, nsq, sk, nsk, inv_tau)
+            return ops.dense_weighted_grad(qh, kh, ma, mb, pw, lse, wstats, q_inv, alpha, v1, None, inv_tau)
+
+        def simt():
             lse, dense_n, wstats, _, _ = ops.dense_weighted_lse(qh, kh, ma, mb, pw, sq, nsq, sk, nsk, inv_tau)
             return ops.dense_weighted_grad(qh, kh, ma, mb, pw, lse, wstats, q_inv, alpha, v1, None, inv_tau)
 
@@ -528,11 +539,13 @@ def weighted_sweep(peaks, iters=20):
             nl = -torch.log_softmax(logits, dim=1)
             ((nl * labels).flatten(1).sum(1) / labels.flatten(1).sum(1)).mean().backward()
 
-        t_ours, t_eager = timeit(ours, iters), timeit(eager, 5)
+        t_ours, t_eager, t_simt = timeit(ours, iters), timeit(eager, 5), timeit(simt, iters)
         rows.append({"B": B, "P": P, "C": C, "negative_type": "FIXED", "weights": list(wts),
-                     "weighted_lse_grad_us": round(t_ours, 2), "launches": 3 if small else 4,
+                     "weighted_lse_grad_us": round(t_ours, 2), "launches": 3 if small else (6 if stream else 4),
                      "path": "tcgen05 (cp2_dense_weighted_small + cp2_dense_small_bwd)" if small
+                             else "tcgen05 streaming (cp2_dense_weighted_stream + cp2_dense_weighted_stream_grad)" if stream
                              else "fp32 SIMT (cp2_dense_weighted_lse + cp2_dense_weighted_grad)",
+                     "fp32_simt_pair_us": round(t_simt, 2),
                      "eager_torch_us": round(t_eager, 1), "speedup_vs_eager": round(t_eager / t_ours, 1),
                      "executed_tflops": round(6.0 * B * P * P * C / t_ours / 1e6, 2)})
     return rows

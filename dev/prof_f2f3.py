@@ -63,4 +63,21 @@ qpos = F.normalize(torch.randn(B, C, device=dev, generator=g), dim=1)
 kpos = F.normalize(torch.randn(B, C, device=dev, generator=g), dim=1)
 timed("global_nce (acc_ins)", lambda: ops.global_nce(qpos, queue2, 5.0, k_pos=kpos, shadow=shadow))
 timed("prep_features_pair", lambda: ops.prep_features_pair(q, ma, k, mb))
+# f3 at 28x28: the streaming tensor-core pair vs the SIMT pair
+hw2, P2, H2 = 28, 784, 28 * 16
+q2 = torch.randn(B, C, P2, device=dev, generator=g)
+k2 = torch.randn(B, C, P2, device=dev, generator=g)
+ma2 = (torch.rand(B, P2, device=dev, generator=g) < 0.65).float()
+mb2 = (torch.rand(B, P2, device=dev, generator=g) < 0.65).float()
+pa2 = torch.arange(1, H2 * H2 + 1, device=dev).reshape(1, H2, H2).repeat(B, 1, 1)
+pb2 = torch.roll(pa2, shifts=(os_, os_), dims=(1, 2)).contiguous()
+ra2 = (pa2 - 1) // (H2 * 64) * 4 + ((pa2 - 1) % H2) // 64
+rb2 = torch.roll(ra2, shifts=(os_, os_), dims=(1, 2)).contiguous()
+pw2 = ops.PairWeights(pa2, pb2, ra2, rb2, os_, 10.0, 2.0, 0.5, "FIXED", 2.0)
+qh2b, q_inv2b, sq2, nsq2, _ = ops.prep_features(q2, ma2)
+kh2b, _, sk2, nsk2, _ = ops.prep_features(k2, mb2)
+lse_s, _, ws_s, _, _, ids_pad, b_pad = timed("weighted_stream fwd (28x28)", lambda: ops.dense_weighted_stream(qh2b, kh2b, ma2, mb2, pw2, sq2, nsq2, sk2, nsk2, 5.0))
+timed("weighted_stream bwd (28x28)", lambda: ops.dense_weighted_stream_grad(qh2b, kh2b, ma2, mb2, pw2, lse_s, ws_s, ids_pad, b_pad, q_inv2b, alpha, v1, None, 5.0))
+lse_m, _, ws_m, _, _ = timed("weighted SIMT fwd (28x28)", lambda: ops.dense_weighted_lse(qh2b, kh2b, ma2, mb2, pw2, sq2, nsq2, sk2, nsk2, 5.0))
+timed("weighted SIMT bwd (28x28)", lambda: ops.dense_weighted_grad(qh2b, kh2b, ma2, mb2, pw2, lse_m, ws_m, q_inv2b, alpha, v1, None, 5.0))
 print("ok", float(zp.sum()), int(idx.sum()))
