@@ -96,13 +96,31 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
   const bool bg = q_neg != nullptr;
   const long long row = (long long)b * C;
   const int cnt = min(max(key_count[b], 0), P);
+  // every operand of this image is read ONCE, up front (C <= 256: two channels per thread), so the kernel is one
+  // memory round trip + two block reductions instead of three dependent passes over global memory
+  constexpr int NC = 2;
+  float qp[NC], kp[NC], qn[NC], kn[NC], Gv[NC], sqv[NC], skv[NC];
+#pragma unroll
+  for (int i = 0; i < NC; ++i) {
+    const int c = tid + 128 * i;
+    const bool v = c < C;
+    qp[i] = v ? q_pos[row + c] : 0.f;
+    kp[i] = v ? k_pos[row + c] : 0.f;
+    Gv[i] = v ? G[row + c] : 0.f;
+    qn[i] = (v && bg) ? q_neg[row + c] : 0.f;
+    kn[i] = (v && bg) ? k_neg[row + c] : 0.f;
+    sqv[i] = (v && !dense_n) ? sq[row + c] : 0.f;
+    skv[i] = (v && !dense_n) ? sk[row + c] : 0.f;
+  }
+  const float zb = z[b], nq = norms_q[2 * b], nnq = norms_q[2 * b + 1];
   // ---- round 1: the dot products and the [P]-sized sums
   float r1[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};     // l_pos, q_pos.q_neg, q_pos.k_neg, sq.sk, A, sum lse
-  for (int c = tid; c < C; c += 128) {
-    const float qp = q_pos[row + c];
-    r1[0] = fmaf(qp, k_pos[row + c], r1[0]);
-    if (bg) { r1[1] = fmaf(qp, q_neg[row + c], r1[1]); r1[2] = fmaf(qp, k_neg[row + c], r1[2]); }
-    if (!dense_n) r1[3] = fmaf(sq[row + c], sk[row + c], r1[3]);
+#pragma unroll
+  for (int i = 0; i < NC; ++i) {
+    r1[0] = fmaf(qp[i], kp[i], r1[0]);
+    r1[1] = fmaf(qp[i], qn[i], r1[1]);
+    r1[2] = fmaf(qp[i], kn[i], r1[2]);
+    r1[3] = fmaf(sqv[i], skv[i], r1[3]);
   }
   for (int x = tid; x < P; x += 128) {
     r1[4] += mask_a[(long long)b * P + x];
@@ -112,7 +130,7 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
   const float l_pos = r1[0], A = r1[4], Bm = (float)cnt;
   // shift 1 as in cp2_global_nce: |l| <= 1 for unit vectors
   const float e_pos = expf((l_pos - 1.f) * inv_tg);
-  float Z = z[b] + e_pos, e_nq = 0.f, e_nk = 0.f;
+  float Z = zb + e_pos, e_nq = 0.f, e_nk = 0.f;
   if (bg) {
     e_nq = expf((r1[1] - 1.f) * inv_tg);
     e_nk = expf((r1[2] - 1.f) * inv_tg);
@@ -121,30 +139,28 @@ loss_combine_kernel(const float *__restrict__ q_pos, const float *__restrict__ k
   const float rZ = 1.f / Z, invB = 1.f / (float)B;
   const float dense_scale = inv_tl / (A * Bm);       // 1 / (tau_d * A * Bm); 0/0 -> NaN as the reference
   // ---- round 2: projections of the outer-normalize backward
-  const float nq = norms_q[2 * b], nnq = norms_q[2 * b + 1];
-  float r2[2] = {0.f, 0.f};
-  for (int c = tid; c < C; c += 128) {
-    const float qp = q_pos[row + c], kp = k_pos[row + c];
-    float num = fmaf(e_pos, kp, G[row + c]);
-    if (bg) num = fmaf(e_nq, q_neg[row + c], fmaf(e_nk, k_neg[row + c], num));
-    const float dqpos = (num * rZ - kp) * invB * inv_tg;
-    r2[0] = fmaf(qp, dqpos, r2[0]);
-    if (bg) r2[1] = fmaf(q_neg[row + c], e_nq * rZ * qp * invB * inv_tg, r2[1]);
+  float dqpos[NC], r2[2] = {0.f, 0.f};
+#pragma unroll
+  for (int i = 0; i < NC; ++i) {
+    float num = fmaf(e_pos, kp[i], Gv[i]);
+    if (bg) num = fmaf(e_nq, qn[i], fmaf(e_nk, kn[i], num));
+    dqpos[i] = (num * rZ - kp[i]) * invB * inv_tg;
+    r2[0] = fmaf(qp[i], dqpos[i], r2[0]);
+    if (bg) r2[1] = fmaf(qn[i], e_nq * rZ * qp[i] * invB * inv_tg, r2[1]);
   }
   block_sum<2>(r2, red);
   const float dq_d = 1.f / fmaxf(nq, kEps), dn_d = 1.f / fmaxf(nnq, kEps);
-  for (int c = tid; c < C; c += 128) {
-    const float qp = q_pos[row + c], kp = k_pos[row + c];
-    float num = fmaf(e_pos, kp, G[row + c]);
-    if (bg) num = fmaf(e_nq, q_neg[row + c], fmaf(e_nk, k_neg[row + c], num));
-    const float dqpos = (num * rZ - kp) * invB * inv_tg;
-    const float proj = nq > kEps ? dqpos - qp * r2[0] : dqpos;
-    // dense_n given (PROPOSED modes): the dense loss has no rank-1 term, cp2_dense_weighted_grad does it all
-    v1[row + c] = dense_n ? proj * dq_d : proj * dq_d - lmbd * invB * sk[row + c] * dense_scale;
-    if (bg) {
-      const float qn = q_neg[row + c];
-      const float dqneg = e_nq * rZ * qp * invB * inv_tg;
-      v2[row + c] = (nnq > kEps ? dqneg - qn * r2[1] : dqneg) * dn_d;
+#pragma unroll
+  for (int i = 0; i < NC; ++i) {
+    const int c = tid + 128 * i;
+    if (c < C) {
+      const float proj = nq > kEps ? dqpos[i] - qp[i] * r2[0] : dqpos[i];
+      // dense_n given (PROPOSED modes): the dense loss has no rank-1 term, cp2_dense_weighted_grad does it all
+      v1[row + c] = dense_n ? proj * dq_d : proj * dq_d - lmbd * invB * skv[i] * dense_scale;
+      if (bg) {
+        const float dqneg = e_nq * rZ * qp[i] * invB * inv_tg;
+        v2[row + c] = (nnq > kEps ? dqneg - qn[i] * r2[1] : dqneg) * dn_d;
+      }
     }
   }
   if (tid == 0) {
@@ -173,7 +189,7 @@ extern "C" int cp2_loss_combine(const float *q_pos, const float *k_pos, const fl
                                 float *l_pos, float *alpha, float *v1,
                                 float *v2, float *scratch, void *scratch_counter, float inv_tau_global,
                                 float inv_tau_dense, float lmbd_dense, int B, int C, int P, void *stream) {
-  CP2_REQUIRE(B > 0 && C > 0 && P > 0, "cp2_loss_combine: bad shape B=%d C=%d P=%d", B, C, P);
+  CP2_REQUIRE(B > 0 && C > 0 && C <= 256 && P > 0, "cp2_loss_combine: bad shape B=%d C=%d P=%d (C <= 256)", B, C, P);
   CP2_REQUIRE(q_pos && k_pos && norms_q && z && G && key_count && mask_a && out && l_pos && alpha && v1 && scratch && scratch_counter,
               "cp2_loss_combine: null pointer");
   CP2_REQUIRE(dense_n || (sq && sk && lse), "cp2_loss_combine: sq, sk and lse are needed unless dense_n is given");

@@ -312,9 +312,19 @@ global_nce_kernel(const __grid_constant__ CUtensorMap tm_q, const float *__restr
         if (*reinterpret_cast<volatile int *>(&miss_s[bb])) continue;
         const float *qr = q_pos + (long long)(b0 + bb) * C;
         const float *qc = queue_f32 + kg;
+        // 32 queue loads (one sector each, strided by K) in flight per round trip; q_pos as 128-bit broadcasts
         float exact = 0.f;
-#pragma unroll 8
-        for (int c = 0; c < C; ++c) exact = fmaf(__ldg(qr + c), __ldg(qc + (long long)c * K), exact);
+#pragma unroll 1
+        for (int c0 = 0; c0 < C; c0 += 32) {
+          float qv[32];
+#pragma unroll
+          for (int c = 0; c < 32; ++c) qv[c] = __ldg(qc + (long long)(c0 + c) * K);
+#pragma unroll
+          for (int c = 0; c < 32; c += 4) {
+            const float4 q4 = __ldg(reinterpret_cast<const float4 *>(qr + c0 + c));
+            exact = fmaf(q4.x, qv[c], fmaf(q4.y, qv[c + 1], fmaf(q4.z, qv[c + 2], fmaf(q4.w, qv[c + 3], exact))));
+          }
+        }
         if (exact >= lpos[bb]) miss_s[bb] = 1;
       }
     }
