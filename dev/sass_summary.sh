@@ -7,7 +7,7 @@ out=../../profiles/sass_summary.txt
 {
   echo "# cuobjdump -sass <object> | grep -c <mnemonic>   (nvcc $(nvcc --version | grep -o 'release [0-9.]*'), -gencode arch=compute_100a,code=sm_100a)"
   printf "%-22s %8s %8s %8s %8s %8s %10s %8s\n" object UTCHMMA UTMALDG LDTM STTM UTCBAR SYNCS.ARR MUFU.EX2
-  for o in dense_umma.o dense_small.o global_umma.o weighted.o metrics.o prep.o composite.o ema.o enqueue.o combine.o ids.o mirror.o densecl.o; do
+  for o in dense_umma.o dense_small.o dense_wsmall.o dense_wstream.o densecl_match.o global_umma.o weighted.o metrics.o prep.o composite.o ema.o enqueue.o combine.o ids.o mirror.o densecl.o; do
     [ -f $o ] || continue
     s=$(cuobjdump -sass $o)
     c() { echo "$s" | grep -c "$1"; }
@@ -15,7 +15,7 @@ out=../../profiles/sass_summary.txt
   done
   echo
   echo "# per kernel (entry symbol) of the tensor-core objects"
-  for o in dense_umma.o dense_small.o global_umma.o; do
+  for o in dense_umma.o dense_small.o dense_wsmall.o dense_wstream.o densecl_match.o global_umma.o; do
     [ -f $o ] || continue
     cuobjdump -sass $o | awk -v obj=$o '
       /Function :/ { name=$3 }
