@@ -123,28 +123,18 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
     const f2 scale2 = f2_pack(scale_log2, scale_log2);
     f2 acc_m = f2_pack(0.f, 0.f), acc_p = f2_pack(0.f, 0.f), acc_m2 = acc_m, acc_p2 = acc_m;
     float tail = 0.f;
-    // software pipeline over chunks AND tiles: the TMEM load of chunk ch+1 is in flight while chunk ch is
-    // exponentiated, and the first chunk of tile i+1 (other accumulator buffer, usually long since complete) is
-    // requested before the last chunk of tile i is processed, so no tile starts with an exposed barrier wait +
-    // tcgen05.ld round trip
-    uint32_t r[2][32];
-    static_assert((CW / 32) % 2 == 0, "chunk count per tile is even: the prefetch lands in r[0]");
-    mbar_wait(&tfull[0], 0);
-    tc_fence_after();
-    tmem_ld32(lane_base, r[0]);
     for (int i = 0; i < nx; ++i) {
-      const int buf = i & 1;
+      const int buf = i & 1, tph = (i >> 1) & 1;
+      mbar_wait(&tfull[buf], tph);
+      tc_fence_after();
       const int nvalid = min(CW, P - i * TILE - c0);     // valid columns of this warp's slice (may be <= 0)
+      // software pipeline: the TMEM load of chunk ch+1 is in flight while chunk ch is exponentiated
+      uint32_t r[2][32];
+      tmem_ld32(lane_base + buf * TILE, r[0]);
 #pragma unroll
       for (int ch = 0; ch < CW / 32; ++ch) {
         tmem_wait_ld();
-        if (ch + 1 < CW / 32) {
-          if ((ch + 1) * 32 < nvalid) tmem_ld32(lane_base + buf * TILE + (ch + 1) * 32, r[(ch + 1) & 1]);
-        } else if (i + 1 < nx) {
-          mbar_wait(&tfull[buf ^ 1], ((i + 1) >> 1) & 1);
-          tc_fence_after();
-          tmem_ld32(lane_base + (buf ^ 1) * TILE, r[0]);
-        }
+        if (ch + 1 < CW / 32 && (ch + 1) * 32 < nvalid) tmem_ld32(lane_base + buf * TILE + (ch + 1) * 32, r[(ch + 1) & 1]);
         if (ch * 32 < nvalid) {                    // warp-uniform
           const uint32_t(&rc)[32] = r[ch & 1];
           if ((ch + 1) * 32 <= nvalid) {
@@ -156,7 +146,6 @@ dense_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant
           }
         }
       }
-      // every load of THIS tile has completed (the prefetch above reads the other buffer and stays in flight)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[buf]);
@@ -413,36 +402,20 @@ dense_grad_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constan
         w_aoa = w_ax / gw.wstats[3 * wb + 1];
         w_centre = gw.p.neg_type >= 2 ? gw.wstats[3 * wb] : 0.f;
       }
-      uint32_t rb[2][32];
-      bool pre = false;                                  // rb[0] already receives chunk 0 of the coming tile
-      constexpr bool kPrefetch = (W / 32) % 2 == 0;       // even chunk count per tile: the prefetch lands in rb[0]
       for (int j = 0; j < ny; ++j, ++g) {
         const int s = g % NST;
         const uint32_t tS = tmem + (g & 1) * TY + lane_off + half * W;
         twait(&kfull[s], (g / NST) & 1, tr_a);           // nl slice of this tile landed (bulk copy)
-        if (!pre) {
-          twait(&s_full[g & 1], (g >> 1) & 1, tr_b);
-          tc_fence_after();
-          tmem_ld32(tS, rb[0]);
-        }
-        pre = false;
+        twait(&s_full[g & 1], (g >> 1) & 1, tr_b);
+        tc_fence_after();
         const uint32_t nl_saddr = smem_u32(nlbuf + s * TY + half * W);
+        uint32_t rb[2][32];
+        tmem_ld32(tS, rb[0]);
 #pragma unroll
         for (int ch = 0; ch < W / 32; ++ch) {
           uint32_t pk[16];
           tmem_wait_ld();
-          if (ch + 1 < W / 32) {
-            tmem_ld32(tS + (ch + 1) * 32, rb[(ch + 1) & 1]);
-          } else if (kPrefetch && j + 1 < ny) {
-            // S of the next key tile sits in the other buffer: if it is already complete, request its first chunk
-            // now, so that the next tile does not start with a barrier wait + tcgen05.ld round trip (never block
-            // here: P~ of THIS tile is what the tensor pipe waits for)
-            if (__all_sync(0xffffffffu, mbar_try_wait(&s_full[(g + 1) & 1], ((g + 1) >> 1) & 1))) {
-              tc_fence_after();
-              tmem_ld32(tmem + ((g + 1) & 1) * TY + lane_off + half * W, rb[0]);
-              pre = true;
-            }
-          }
+          if (ch + 1 < W / 32) tmem_ld32(tS + (ch + 1) * 32, rb[(ch + 1) & 1]);
           const uint32_t(&r)[32] = rb[ch & 1];
           if constexpr (MODE == 2) {
             const int c0 = s * TY + half * W + ch * 32;          // first key of the chunk inside the stage buffers
