@@ -699,6 +699,53 @@ def ddp_weights_equal(model, dev, world):
     return all(torch.equal(out[0], t) for t in out)
 
 
+def gpu_busy_breakdown(step_fn, n, dev):
+    """Where one step's wall time goes on this rank's GPU (torch.profiler / CUPTI over n steps, untimed leg):
+    union of all kernel intervals (GPU busy), the NCCL kernels' share, and what is left (GPU idle: host-bound
+    launch gaps and waits on peers).  -> dict, or {"unavailable": why}."""
+    import torch
+    try:
+        from torch.profiler import ProfilerActivity, profile
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            e0.record()
+            for i in range(n):
+                step_fn(i)
+            e1.record()
+            torch.cuda.synchronize(dev)
+        wall_ms = e0.elapsed_time(e1) / n
+        iv, nccl_us, memcpy_us = [], 0.0, 0.0
+        for ev in prof.events():
+            if str(getattr(ev, "device_type", "")).endswith("CUDA") and ev.time_range is not None:
+                t0, t1 = ev.time_range.start, ev.time_range.end
+                if t1 <= t0:
+                    continue
+                iv.append((t0, t1))
+                if "nccl" in ev.name.lower():
+                    nccl_us += t1 - t0
+                if "memcpy" in ev.name.lower() or "memset" in ev.name.lower():
+                    memcpy_us += t1 - t0
+        if not iv:
+            return {"unavailable": "profiler returned no device events"}
+        iv.sort()
+        busy, cs, ce = 0.0, iv[0][0], iv[0][1]
+        for a, b in iv[1:]:
+            if a > ce:
+                busy += ce - cs
+                cs, ce = a, b
+            else:
+                ce = max(ce, b)
+        busy += ce - cs
+        return {"step_ms": round(wall_ms, 3), "gpu_busy_ms_per_step": round(busy / n / 1e3, 3),
+                "gpu_idle_ms_per_step": round(wall_ms - busy / n / 1e3, 3),
+                "nccl_kernels_ms_per_step": round(nccl_us / n / 1e3, 3),
+                "memcpy_memset_ms_per_step": round(memcpy_us / n / 1e3, 3), "kernels_per_step": len(iv) // n,
+                "how": "torch.profiler (CUPTI) over %d steps on rank 0's GPU: union of all kernel / copy intervals" % n}
+    except Exception as e:                                    # profiler not usable on this box: say so, do not fail
+        return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+
+
 def collectives_summary(times, steps):
     """model.collective_times -> {name: us per step}; device-side CUDA-event durations on the issuing stream
     (host seconds for the gloo permutation broadcast)."""
@@ -1022,11 +1069,15 @@ def own_arm(args):
         model.overlap_exchange = False
         ms_serial = timed(lambda i: step(resident[i % 2]), n_c) / n_c
         model.overlap_exchange = True
+        collectives["gpu_busy"] = gpu_busy_breakdown(lambda i: step(resident[i % 2]), 3, dev)
         collectives.update({"ddp_all_reduce_overhead_ms_per_step": round(ms_sync - ms_nosync, 3),
                             "step_ms": round(ms_sync, 3), "step_ms_without_grad_all_reduce": round(ms_nosync, 3),
                             "step_ms_with_serial_image_exchange": round(ms_serial, 3),
                             "note": "all_to_all / all_gather: CUDA events on the issuing stream (the image exchange "
                                     "runs on a side stream under encoder_q); all-reduce overhead from a no_sync() A/B"})
+
+    if world == 1 and os.environ.get("CP2_BENCH_BREAKDOWN"):          # same breakdown at N=1, for comparison
+        collectives = {"gpu_busy": gpu_busy_breakdown(lambda i: step(resident[i % 2]), 3, dev)}
 
     # ---- per-kernel figures from the CUDA events recorded inside the timed region
     work = algorithmic_work(B, n_params, world)

@@ -249,6 +249,13 @@ __device__ __forceinline__ f2 f2_mul(f2 a, f2 b) {
   return r;
 }
 
+// p + (t << 23) as ONE integer multiply-add (ptxas emits SHF.L + IADD3 for the shift-add form)
+__device__ __forceinline__ uint32_t exp_splice(uint32_t p, uint32_t t) {
+  uint32_t r;
+  asm("mad.lo.u32 %0, %1, 8388608, %2;" : "=r"(r) : "r"(t), "r"(p));
+  return r;
+}
+
 // 2^x for a pair on the FMA/ALU pipes (no MUFU): Cody-Waite split x = n + f, |f| <= 0.5 by the
 // 1.5*2^23 rounding trick, minimax polynomial of degree DEG for 2^f (max rel. error 1.7e-3 / 7.6e-5 /
 // 2.7e-6 for DEG 2 / 3 / 4), exponent spliced in with one shift-add.  Requires -126 <= x <= 126.
@@ -274,7 +281,7 @@ __device__ __forceinline__ f2 exp2_poly2(f2 x) {
   uint32_t p0, p1, t0, t1;
   f2_unpack_u(p, p0, p1);
   f2_unpack_u(t, t0, t1);
-  return f2_pack_u(p0 + (t0 << 23), p1 + (t1 << 23));
+  return f2_pack_u(exp_splice(p0, t0), exp_splice(p1, t1));
 }
 
 // 2^(r*scale) for a pair, the scale folded into the range reduction (saves the separate multiply).
@@ -300,7 +307,7 @@ __device__ __forceinline__ f2 exp2_poly2_scaled(f2 r, f2 scale) {
   uint32_t p0, p1, t0, t1;
   f2_unpack_u(p, p0, p1);
   f2_unpack_u(t, t0, t1);
-  return f2_pack_u(p0 + (t0 << 23), p1 + (t1 << 23));
+  return f2_pack_u(exp_splice(p0, t0), exp_splice(p1, t1));
 }
 
 __device__ __forceinline__ float ex2_approx(float x) {
