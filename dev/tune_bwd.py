@@ -53,8 +53,20 @@ for masks in ("ones", "bern"):
     kh, _, _, _, cnt = ops.prep_features(k, mb, compact=True)
     lse = ops.dense_lse(qh, kh, 5.0, cnt)
     ref = None
-    for variant in (0, 1):
-        for pf in (0, 1):
+    for nsw in (8, 4):
+        for pf in (0, 1, 2, 3):
+            os.environ["CP2_DENSE_NSW_FWD"] = str(nsw)
+            os.environ["CP2_DENSE_PF_FWD"] = str(pf)
+            lse_t = torch.empty((B, P), device=dev, dtype=torch.float32)
+
+            def fwd():
+                rc = dbg.cp2_dense_lse(ptr(qh), ptr(kh), ptr(cnt), ptr(lse_t), 5.0, B, C, P, st())
+                assert rc == 0, dbg.cp2_last_error()
+                return lse_t
+            t, out = timed(fwd)
+            print(f"P={P} B={B} masks={masks} fwd nsw={nsw} pf={pf}: lse {t:8.1f} us   max|d lse| {float((out - lse).abs().max()):.2e}", flush=True)
+    for variant in (0,):
+        for pf in (0, 1, 2, 3):
             os.environ["CP2_DENSE_BWD_VARIANT"] = str(variant)
             os.environ["CP2_DENSE_PF_BWD"] = str(pf)
             t, dq = timed(lambda: grad(qh, kh, lse, ma, q_inv, cnt))
