@@ -584,9 +584,12 @@ def densecl_sweep(peaks, iters=10):
                 ts.append(a.elapsed_time(b) * 1e3)
         return statistics.median(ts)
 
+    sh1, sh2 = ops.QueueShadow(), ops.QueueShadow()      # as MODEL keeps them: the bf16 shadows persist across steps
+
     def ours():
         q_local.grad = q_global.grad = None
-        ops.densecl_loss(embd_q, embd_k, q_local, k_local, q_global, k_global, queue, queue2, tau, tau, 0.5)[0].backward()
+        ops.densecl_loss(embd_q, embd_k, q_local, k_local, q_global, k_global, queue, queue2, tau, tau, 0.5,
+                         shadow=sh1, shadow2=sh2)[0].backward()
 
     def head(pos, neg):
         logits = torch.cat((pos, neg), dim=1) / tau
