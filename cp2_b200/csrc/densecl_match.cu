@@ -31,9 +31,8 @@ constexpr int ND = 8;                    // fp32 slabs in the cp.async ring (ND 
 constexpr int T_BYTES = 2 * KS * 128;    // one bf16 term of a 128-pixel slab: 2 chunks of 64 pixels x 16 channel rows
 constexpr int STAGE = 4 * T_BYTES;       // q_hi, q_lo, k_hi, k_lo
 constexpr int TG = 256 / NG;             // threads per converter group
-constexpr int UW = TG / 16;              // 8-pixel units of one channel row taken by neighbouring threads
-constexpr int UPT = 16 / UW;             // units per thread and operand
-constexpr int RING = 16 * 1024;          // one fp32 slab: 4 * UPT 16-byte pieces per thread of the owning group, piece-major
+constexpr int RPT = KS / (TG / 32);      // channel rows per warp and operand: a warp copies whole 512-byte rows
+constexpr int RING = 16 * 1024;          // one fp32 slab: 2 * RPT 16-byte pieces per thread of the owning group, piece-major
 constexpr size_t MT_SMEM = 1024 + (size_t)NS * STAGE + (size_t)ND * RING + 2 * NS * 8 + 8 + 32;
 
 __device__ __forceinline__ uint8_t *align1024m(uint8_t *p) {
@@ -46,39 +45,32 @@ __device__ __forceinline__ uint32_t mn_off(int c, int unit) {
   return (uint32_t)((unit >> 3) * (KS * 128) + (c >> 3) * 1024 + (c & 7) * 128 + (((unit & 7) ^ (c & 7)) << 4));
 }
 
-// 8 fp32 -> hi / lo bf16 x 8 (two 16-byte vectors).  hi pairs come from one packed conversion (cvt.rn.bf16x2.f32),
+// 4 fp32 -> hi / lo bf16 x 4 (two 8-byte vectors).  hi pairs come from one packed conversion (cvt.rn.bf16x2.f32),
 // their fp32 values back by shift / mask: no quarter-rate scalar F2F on the path.
-__device__ __forceinline__ void split8(const float (&v)[8], uint4 &hi, uint4 &lo) {
-  uint32_t h[4], l[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    h[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
-    l[i] = pack_bf16x2(v[2 * i] - __uint_as_float(h[i] << 16), v[2 * i + 1] - __uint_as_float(h[i] & 0xffff0000u));
-  }
-  hi = make_uint4(h[0], h[1], h[2], h[3]);
-  lo = make_uint4(l[0], l[1], l[2], l[3]);
+__device__ __forceinline__ void split4(const float4 v, uint2 &hi, uint2 &lo) {
+  hi.x = pack_bf16x2(v.x, v.y);
+  hi.y = pack_bf16x2(v.z, v.w);
+  lo.x = pack_bf16x2(v.x - __uint_as_float(hi.x << 16), v.y - __uint_as_float(hi.x & 0xffff0000u));
+  lo.y = pack_bf16x2(v.z - __uint_as_float(hi.y << 16), v.w - __uint_as_float(hi.y & 0xffff0000u));
 }
 
-// One unit (8 consecutive pixels p0..p0+7 of a channel row) into two 16-byte ring pieces, asynchronously in every
-// case (a synchronous load on the map edge would put one memory round trip per slab on the critical path):
-// 16-byte cp.async when the rows are 16-byte aligned (P % 4 == 0: a piece is then entirely inside or outside the
-// map), 4-byte cp.async per pixel otherwise; pieces / pixels past P are zero-filled (src-size 0 reads nothing).
-__device__ __forceinline__ void stage8(const float *__restrict__ row, int p0, int P, bool vec, uint8_t *d0, uint8_t *d1) {
+// Four consecutive pixels p0..p0+3 of a channel row into one 16-byte ring piece, asynchronously in every case (a
+// synchronous load on the map edge would put one memory round trip per slab on the critical path): one 16-byte
+// cp.async when the rows are 16-byte aligned (P % 4 == 0: a piece is then entirely inside or outside the map),
+// 4-byte cp.async per pixel otherwise; pixels past P are zero-filled (src-size 0 reads nothing).  The 32 lanes of a
+// warp take consecutive pieces: 512 contiguous bytes of one row per instruction.
+__device__ __forceinline__ void stage4(const float *__restrict__ row, int p0, int P, bool vec, uint8_t *d) {
   if (vec) {
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int p = p0 + 4 * h;
-      const uint32_t n = p < P ? 16u : 0u;
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(h ? d1 : d0)),
-                   "l"(row + (p < P ? p : 0)), "r"(n) : "memory");
-    }
+    const uint32_t n = p0 < P ? 16u : 0u;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(d)), "l"(row + (p0 < P ? p0 : 0)), "r"(n)
+                 : "memory");
   } else {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < 4; ++i) {
       const int p = p0 + i;
       const uint32_t n = p < P ? 4u : 0u;
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32((i < 4 ? d0 : d1) + 4 * (i & 3))),
-                   "l"(row + (p < P ? p : 0)), "r"(n) : "memory");
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(d + 4 * i)), "l"(row + (p < P ? p : 0)),
+                   "r"(n) : "memory");
     }
   }
 }
@@ -139,26 +131,21 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
     const int t = threadIdx.x - 32;                      // 0..255
     const bool vec = (P & 3) == 0;
     const float *qb = eq + (long long)b * Cb * P, *kb = ek + (long long)b * Cb * P;
-    // group g = t / TG converts the slabs i = g, g + NG, ...; inside the group thread tg -> channel row c and the
-    // 8-pixel units u0 + UW*j (j < UPT) of both 16 x 128 slabs.  A thread converts exactly what it copied, so the fp32
-    // ring needs no barrier, only cp.async.wait_group.
+    // group g = t / TG converts the slabs i = g, g + NG, ...; inside the group warp wg takes the channel rows
+    // wg + (TG/32) j (j < RPT) of both 16 x 128 slabs, lane l the pixels 4l..4l+3 of the row (coalesced 512-byte
+    // copies).  A thread converts exactly what it copied, so the fp32 ring needs no barrier, only
+    // cp.async.wait_group.
     constexpr int DG = ND / NG;                          // ring slots per group
-    const int grp = t / TG, tg = t % TG;
-    const int c = tg / UW, u0 = tg % UW;
+    const int grp = t / TG, tg = t % TG, wg = tg >> 5;
     auto piece = [&](int slot, int pc) { return ring + slot * RING + (pc * TG + tg) * 16; };
     auto fetch = [&](int i) {
       const int slot = i % ND;
-      const float *qrow = qb + (long long)(i * KS + c) * P, *krow = kb + (long long)(i * KS + c) * P;
 #pragma unroll
-      for (int j = 0; j < UPT; ++j) {
-        stage8(qrow, x0 + (u0 + UW * j) * 8, P, vec, piece(slot, 2 * j), piece(slot, 2 * j + 1));
-        stage8(krow, y0 + (u0 + UW * j) * 8, P, vec, piece(slot, 2 * UPT + 2 * j), piece(slot, 2 * UPT + 2 * j + 1));
+      for (int j = 0; j < RPT; ++j) {
+        const long long ro = (long long)(i * KS + wg + (TG / 32) * j) * P;
+        stage4(qb + ro, x0 + 4 * lane, P, vec, piece(slot, j));
+        stage4(kb + ro, y0 + 4 * lane, P, vec, piece(slot, RPT + j));
       }
-    };
-    auto take8 = [&](int slot, int pc, float (&v)[8]) {
-      const float4 a = *reinterpret_cast<const float4 *>(piece(slot, pc));
-      const float4 d = *reinterpret_cast<const float4 *>(piece(slot, pc + 1));
-      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = d.x; v[5] = d.y; v[6] = d.z; v[7] = d.w;
     };
     for (int k = 0; k < DG - 1; ++k) {                   // prologue: DG-1 of the group's slabs in flight
       if (grp + k * NG < nslab) fetch(grp + k * NG);
@@ -169,21 +156,21 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
       asm volatile("cp.async.commit_group;" ::: "memory");
       asm volatile("cp.async.wait_group %0;" ::"n"(DG - 1) : "memory");   // slab i has landed (this thread's pieces)
       const int slot = i % ND, s = i % NS, ph = (i / NS) & 1;
-      uint4 hq[UPT], lq[UPT], hk[UPT], lk[UPT];
+      uint2 hq[RPT], lq[RPT], hk[RPT], lk[RPT];
 #pragma unroll
-      for (int j = 0; j < UPT; ++j) {
-        float v[8];
-        take8(slot, 2 * j, v); split8(v, hq[j], lq[j]);
-        take8(slot, 2 * UPT + 2 * j, v); split8(v, hk[j], lk[j]);
+      for (int j = 0; j < RPT; ++j) {
+        split4(*reinterpret_cast<const float4 *>(piece(slot, j)), hq[j], lq[j]);
+        split4(*reinterpret_cast<const float4 *>(piece(slot, RPT + j)), hk[j], lk[j]);
       }
       mbar_wait(&empty[s], ph ^ 1);                      // the MMAs that read this stage have completed
 #pragma unroll
-      for (int j = 0; j < UPT; ++j) {
-        uint8_t *st = smem + s * STAGE + mn_off(c, u0 + UW * j);
-        *reinterpret_cast<uint4 *>(st) = hq[j];
-        *reinterpret_cast<uint4 *>(st + T_BYTES) = lq[j];
-        *reinterpret_cast<uint4 *>(st + 2 * T_BYTES) = hk[j];
-        *reinterpret_cast<uint4 *>(st + 3 * T_BYTES) = lk[j];
+      for (int j = 0; j < RPT; ++j) {
+        // 8-pixel unit lane/2 of channel row c, its lower / upper four pixels
+        uint8_t *st = smem + s * STAGE + mn_off(wg + (TG / 32) * j, lane >> 1) + (lane & 1) * 8;
+        *reinterpret_cast<uint2 *>(st) = hq[j];
+        *reinterpret_cast<uint2 *>(st + T_BYTES) = lq[j];
+        *reinterpret_cast<uint2 *>(st + 2 * T_BYTES) = hk[j];
+        *reinterpret_cast<uint2 *>(st + 3 * T_BYTES) = lk[j];
       }
       fence_proxy_async_smem();                          // generic-proxy writes -> visible to the tensor core
       __syncwarp();
