@@ -5,10 +5,10 @@
 // The operands are the fp32 backbone feature maps as cuDNN leaves them, [B,Cb,P] with the pixel axis contiguous.
 // The kernel is a stream over them (2 x 1.6 MB per image at configs[1]), so it is laid out for bytes in flight:
 // CTA = (image, 128 query pixels, 128 key pixels) — 4 CTAs per 14x14 image, 128 at B = 32 — and per 16-channel
-// slab a group of 4 converter warps (2 groups owning alternate slabs, so that their per-slab fixed costs overlap;
-// 3 slabs of each group in flight) brings the fp32 values into a shared-memory ring with cp.async, splits each
-// into two bf16 terms (hi = RN(v), lo = RN(v - hi)) and writes them as MN-major, 128-byte-swizzled tcgen05
-// operand tiles (4 stages);
+// slab a group of 2 converter warps (4 groups, each owning every 4th slab so that their per-slab fixed costs
+// overlap) brings the fp32 values into a shared-memory ring with cp.async (warp-wide, coalesced 512-byte row
+// copies), splits each into two bf16 terms (hi = RN(v), lo = RN(v - hi)) and writes them as MN-major,
+// 128-byte-swizzled tcgen05 operand tiles (6 stages);
 // the MMA warp accumulates
 // S += q_hi k_hi + q_hi k_lo + q_lo k_hi in TMEM (fp32), i.e. the similarity to ~2^-16 relative — ties closer than
 // that are below the noise of the reference's own fp32 summation order on 2048 channels.  After the last slab four
@@ -23,24 +23,27 @@ using namespace umma;
 namespace {
 
 constexpr int MT_THREADS = 288;          // warp 0: MMA issuer + TMEM owner; warps 1-8: converters (1-4 also arg-max)
-constexpr int KS = 16;                   // channels per slab (one K = 16 MMA slice)
-constexpr int NG = 2;                    // converter groups (4 warps each); group g owns the slabs i = g (mod NG), so the
-                                         // per-slab fixed costs (waits, proxy fence, barrier hand-over) of the groups overlap
-constexpr int NS = 4;                    // bf16 operand stages
-constexpr int ND = 8;                    // fp32 slabs in the cp.async ring (ND / NG per group, all but one in flight)
-constexpr int T_BYTES = 2 * KS * 128;    // one bf16 term of a 128-pixel slab: 2 chunks of 64 pixels x 16 channel rows
-constexpr int STAGE = 4 * T_BYTES;       // q_hi, q_lo, k_hi, k_lo
-constexpr int TG = 256 / NG;             // threads per converter group
-constexpr int RPT = KS / (TG / 32);      // channel rows per warp and operand: a warp copies whole 512-byte rows
-constexpr int RING = 16 * 1024;          // one fp32 slab: 2 * RPT 16-byte pieces per thread of the owning group, piece-major
-constexpr size_t MT_SMEM = 1024 + (size_t)NS * STAGE + (size_t)ND * RING + 2 * NS * 8 + 8 + 32;
+// Tunables (template parameters of the kernel): KS channels per slab (K = 16 MMA slices: KS / 16), NG converter
+// groups (256 / NG threads each; group g owns the slabs i = g (mod NG), so the per-slab fixed costs of the groups
+// overlap), ND fp32 slabs in the cp.async ring (ND / NG per group, all but one in flight), NS bf16 operand stages.
+template <int KS, int NG, int ND, int NS>
+struct MatchCfg {
+  static constexpr int TG = 256 / NG;                   // threads per converter group
+  static constexpr int RPT = KS / (TG / 32);            // channel rows per warp and operand: a warp copies whole 512-byte rows
+  static constexpr int T_BYTES = 2 * KS * 128;          // one bf16 term of a 128-pixel slab: 2 chunks of 64 pixels x KS channel rows
+  static constexpr int STAGE = 4 * T_BYTES;             // q_hi, q_lo, k_hi, k_lo
+  static constexpr int RING = 2 * KS * 512;             // one fp32 slab (query + key rows), piece-major per owning group
+  static constexpr size_t SMEM = 1024 + (size_t)NS * STAGE + (size_t)ND * RING + 2 * NS * 8 + 8 + 32;
+  static_assert(ND % NG == 0 && KS % 16 == 0 && KS % (TG / 32) == 0, "bad match configuration");
+};
 
 __device__ __forceinline__ uint8_t *align1024m(uint8_t *p) {
   return reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(p) + 1023) & ~uintptr_t(1023));
 }
 
-// 8 consecutive pixels of channel row `c` (0..15) starting at pixel 8*unit: byte offset inside an MN-major
+// 8 consecutive pixels of channel row `c` (0..KS-1) starting at pixel 8*unit: byte offset inside an MN-major
 // operand term whose 64-pixel chunks are KS*128 bytes apart (LBO) and whose 8-row groups are 1024 bytes apart (SBO)
+template <int KS>
 __device__ __forceinline__ uint32_t mn_off(int c, int unit) {
   return (uint32_t)((unit >> 3) * (KS * 128) + (c >> 3) * 1024 + (c & 7) * 128 + (((unit & 7) ^ (c & 7)) << 4));
 }
@@ -81,9 +84,12 @@ __device__ __forceinline__ uint32_t orderable(float v) {
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
+template <int KS, int NG, int ND, int NS>
 __global__ void __launch_bounds__(MT_THREADS, 1)
 densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek, long long *__restrict__ idx,
                      unsigned long long *__restrict__ best, unsigned int *__restrict__ counters, int Cb, int P) {
+  using Cfg = MatchCfg<KS, NG, ND, NS>;
+  constexpr int TG = Cfg::TG, RPT = Cfg::RPT, T_BYTES = Cfg::T_BYTES, STAGE = Cfg::STAGE, RING = Cfg::RING;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = align1024m(smem_raw);
   uint8_t *ring = smem + NS * STAGE;
@@ -97,7 +103,7 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
   const int nslab = Cb / KS;
   const int ncols = min(128, ((P - y0 + 31) / 32) * 32);   // MMA N: every 32-column chunk the arg-max reads is written
   if (threadIdx.x == 0) {
-    for (int s = 0; s < NS; ++s) { mbar_init(&full[s], 256 / 32 / NG); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < NS; ++s) { mbar_init(&full[s], TG / 32); mbar_init(&empty[s], 1); }
     mbar_init(done, 1);
     fence_barrier_init();
   }
@@ -116,11 +122,15 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
       tc_fence_after();
       if (elect_one()) {
         const uint32_t base = smem_u32(smem + s * STAGE);
-        const uint64_t dAh = make_sdesc(base, KS * 128, 1024), dAl = make_sdesc(base + T_BYTES, KS * 128, 1024);
-        const uint64_t dBh = make_sdesc(base + 2 * T_BYTES, KS * 128, 1024), dBl = make_sdesc(base + 3 * T_BYTES, KS * 128, 1024);
-        mma_f16_ss(tmem, dAh, dBh, idesc, i > 0 ? 1u : 0u);
-        mma_f16_ss(tmem, dAh, dBl, idesc, 1u);
-        mma_f16_ss(tmem, dAl, dBh, idesc, 1u);
+#pragma unroll
+        for (int kk = 0; kk < KS / 16; ++kk) {             // 16 channel rows (2 KB) per slice
+          const uint32_t o = base + kk * 2048;
+          const uint64_t dAh = make_sdesc(o, KS * 128, 1024), dAl = make_sdesc(o + T_BYTES, KS * 128, 1024);
+          const uint64_t dBh = make_sdesc(o + 2 * T_BYTES, KS * 128, 1024), dBl = make_sdesc(o + 3 * T_BYTES, KS * 128, 1024);
+          mma_f16_ss(tmem, dAh, dBh, idesc, (i > 0 || kk > 0) ? 1u : 0u);
+          mma_f16_ss(tmem, dAh, dBl, idesc, 1u);
+          mma_f16_ss(tmem, dAl, dBh, idesc, 1u);
+        }
         mma_commit(&empty[s]);
         if (i == nslab - 1) mma_commit(done);
       }
@@ -166,7 +176,7 @@ densecl_match_kernel(const float *__restrict__ eq, const float *__restrict__ ek,
 #pragma unroll
       for (int j = 0; j < RPT; ++j) {
         // 8-pixel unit lane/2 of channel row c, its lower / upper four pixels
-        uint8_t *st = smem + s * STAGE + mn_off(wg + (TG / 32) * j, lane >> 1) + (lane & 1) * 8;
+        uint8_t *st = smem + s * STAGE + mn_off<KS>(wg + (TG / 32) * j, lane >> 1) + (lane & 1) * 8;
         *reinterpret_cast<uint2 *>(st) = hq[j];
         *reinterpret_cast<uint2 *>(st + T_BYTES) = lq[j];
         *reinterpret_cast<uint2 *>(st + 2 * T_BYTES) = hk[j];
@@ -228,17 +238,26 @@ extern "C" int64_t cp2_densecl_match_scratch_bytes(int B, int P) { return (int64
 extern "C" int cp2_densecl_match(const float *embd_q, const float *embd_k, int64_t *idx, void *scratch, int B, int Cb,
                                  int P, void *stream) {
   CP2_REQUIRE(B > 0 && B <= 65535 && P > 0 && P <= 256, "cp2_densecl_match: bad shape B=%d P=%d (P <= 256)", B, P);
-  CP2_REQUIRE(Cb > 0 && Cb % KS == 0, "cp2_densecl_match: Cb=%d must be a positive multiple of %d", Cb, KS);
+  CP2_REQUIRE(Cb > 0 && Cb % 16 == 0, "cp2_densecl_match: Cb=%d must be a positive multiple of 16", Cb);
   CP2_REQUIRE(embd_q && embd_k && idx && scratch, "cp2_densecl_match: null pointer");
   CP2_REQUIRE((reinterpret_cast<uintptr_t>(embd_q) & 15u) == 0 && (reinterpret_cast<uintptr_t>(embd_k) & 15u) == 0 &&
                   (reinterpret_cast<uintptr_t>(scratch) & 7u) == 0,
               "cp2_densecl_match: embd_q / embd_k must be 16-byte, scratch 8-byte aligned");
   auto *best = static_cast<unsigned long long *>(scratch);
   auto *counters = reinterpret_cast<unsigned int *>(best + (size_t)B * P);
-  CP2_SMEM_ONCE(densecl_match_kernel, MT_SMEM);
   const int nt = cp2_cdiv(P, 128);
-  densecl_match_kernel<<<dim3(nt, nt, B), MT_THREADS, MT_SMEM, static_cast<cudaStream_t>(stream)>>>(
-      embd_q, embd_k, reinterpret_cast<long long *>(idx), best, counters, Cb, P);
+  const dim3 grid(nt, nt, B);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define CP2_MATCH(KSV, NGV, NDV, NSV)                                                                              \
+  do {                                                                                                             \
+    CP2_SMEM_ONCE((densecl_match_kernel<KSV, NGV, NDV, NSV>), (MatchCfg<KSV, NGV, NDV, NSV>::SMEM));              \
+    densecl_match_kernel<KSV, NGV, NDV, NSV><<<grid, MT_THREADS, MatchCfg<KSV, NGV, NDV, NSV>::SMEM, st>>>(       \
+        embd_q, embd_k, reinterpret_cast<long long *>(idx), best, counters, Cb, P);                                \
+  } while (0)
+  // measured on B200 at B=32, P=196, Cb=2048 (ncu, isolated): (KS, NG, ND, NS) = (16,4,8,6) 60 us, (32,2,4,3) 62 us,
+  // (32,4,4,3) 64 us, (16,2,8,4) 67 us, (16,1,8,4) 75 us
+  CP2_MATCH(16, 4, 8, 6);
+#undef CP2_MATCH
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }
