@@ -24,7 +24,8 @@ using namespace weighted;
 namespace {
 
 constexpr int WL_THREADS = 320;          // warp 0 TMA, warp 1 MMA + TMEM owner, warps 2-9 softmax
-constexpr int WL_NST = 2;
+constexpr int WL_NST = 1;              // one query stage: two CTAs fit one SM up to P = 896 (16 softmax warps hide the
+                                       // latency of the CUDA-core epilogue better than a second stage does)
 
 // ids[0..3][b][pix] = pid_a, pid_b, rid_a, rid_b at the lattice point of pixel pix, b_pad[b][pix] = mask_b; rows are
 // P_pad long (whole key tiles of the backward), zero past P
@@ -49,7 +50,7 @@ size_t wl_smem(int P) {
   return 1024 + (size_t)(1 + WL_NST) * 2 * TILE * 128 + pp * 20 + 5 * 128 * 4 + 3 * 4 * 4 + 16 * 8 + 32;
 }
 
-__global__ void __launch_bounds__(WL_THREADS, 1)
+__global__ void __launch_bounds__(WL_THREADS, 2)
 wstream_lse_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                    const float *__restrict__ mask_a, const float *__restrict__ b_pad,
                    const long long *__restrict__ ids, const float *__restrict__ wstats, float *__restrict__ lse,
