@@ -1008,6 +1008,13 @@ def own_arm(args):
     parity = None
     if world > 1:
         parity = multi_rank_parity(model, dev, rank, world)
+        # ... and the replicas after real all-reduced steps: 4 full training steps (forward through both encoders,
+        # loss, backward with DDP's gradient all-reduce, SGD), then every parameter of both encoders must be
+        # bit-identical on all ranks.  (Untimed checker leg; it also lets NCCL, DDP's bucket rebuild and the cuDNN
+        # autotuner settle on every rank before the W warm-up steps.)
+        for i in range(4):
+            step(resident[i % 2])
+        parity["ddp_weights_equal_after_4_steps"] = ddp_weights_equal(model, dev, world)
 
     for i in range(max(args.warmup, 3)):
         step(resident[i % 2])
