@@ -88,10 +88,15 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
-        self.index, self.proc = index, None
+    def __init__(self, index, enabled=True):
+        # enabled: rank 0 only.  One `nvidia-smi -lms` poller per rank (8 on an 8-GPU box, every query taking the
+        # driver's lock) cost 4.7 ms/step at N=8 (29.1 vs 24.4 ms/step with and without them, r02d); rank 0's GPU
+        # stands for the box: all ranks run the same step behind the same barrier.
+        self.index, self.proc, self.enabled = index, None, enabled
 
     def start(self):
+        if not self.enabled:
+            return
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
@@ -100,6 +105,8 @@ class ClockSampler:
             self.proc = None
 
     def stop(self):
+        if not self.enabled:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["sampled on rank 0 only"]}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -878,7 +885,7 @@ def mirror_arm(args, dev, rank, world, peaks):
 
     for i in range(max(args.warmup, 3)):
         step(resident[i % 2])
-    sampler = ClockSampler(dev.index)
+    sampler = ClockSampler(dev.index, enabled=(rank == 0))
     sampler.start()
     l0 = ops.LAUNCHES
     with ops.KernelTimer() as kt:
@@ -1018,7 +1025,7 @@ def own_arm(args):
 
     for i in range(max(args.warmup, 3)):
         step(resident[i % 2])
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local, enabled=(rank == 0))
     sampler.start()
     launches0 = ops.LAUNCHES
     ncu_range = os.environ.get("CP2_BENCH_CUDA_PROFILER") == "1"    # ncu --profile-from-start off
