@@ -127,7 +127,8 @@ int cp2_dense_grad(const void *qhat_t, const void *khat_t, const int32_t *key_co
  *   dq[n,:,x] = N_x( g * (alpha[n]*acc[n,:,x] + mask_a[x]*v1[n,:] + (1-mask_a[x])*v2[n,:]) )
  * The acc_seg meter of builder.py:1442-1448 (label of the arg-max over all pixel pairs) comes out of the same
  * launch when seg_hit is given: the largest similarity is found while S is in TMEM, every pair within 2^-7 of it
- * (the bound of the operands' bf16 rounding) is re-scored exactly in fp32:
+ * (the bound of the operands' bf16 rounding) is re-scored exactly in fp32 (at most 32 such pairs per image; an image
+ * with more — e.g. collapsed features — is decided among the first 32 collected):
  *   seg_q, seg_k : [B,C,P] f32 encoder outputs; seg_inv_q, seg_inv_k : [B,P] (cp2_prep_features inv_norm);
  *   seg_perm_k   : [B,P] int32 pixel of each key row (cp2_prep_features perm) or NULL (keys in pixel order);
  *   seg_mask_a, seg_mask_b : [B,P] f32 masks in pixel order (seg_mask_b NULL: label = row < key_count);
