@@ -57,13 +57,20 @@ __device__ void prep_reduce_image(const PrepSide &sd, int b, int C, int tiles, f
   if (threadIdx.x == 0) { sd.norms[2 * b] = np; sd.norms[2 * b + 1] = nn; }
 }
 
+// Thread (warp w, lane l) owns pixel l of the tile and the channel pairs (2j, 2j+1), j = w + 8i: every global load
+// is a coalesced 128-byte row piece, the normalisation is one multiply per register, and adjacent channels convert to
+// one packed bf16 word.  Two smem images of the tile: fp32 [C][33] for the pooled sums (thread per channel walks the
+// pixels, conflict-free) and packed bf16 [32][C/2+1] for the transposed store (conflict-free both ways).
 template <int C>
 __global__ void __launch_bounds__(256)
-prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, int tiles) {
-  __shared__ float tile[C][PT + 1];
+prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, int tiles, int nt) {
+  constexpr int NP = C / 16;         // channel pairs per thread
+  constexpr int TW = C / 2 + 1;      // words per pixel row of the packed tile (odd: conflict-free)
+  extern __shared__ __align__(16) unsigned char prep_dyn[];
+  float (*tile)[PT + 1] = reinterpret_cast<float (*)[PT + 1]>(prep_dyn);
+  uint32_t (*tile_t)[TW] = reinterpret_cast<uint32_t (*)[TW]>(prep_dyn + sizeof(float) * C * (PT + 1));
   __shared__ float ssq[8][PT];
-  __shared__ float den[PT];
-  __shared__ float mk[PT];
+  __shared__ __align__(16) float2 wts[PT];   // (a_x, 1 - a_x) of the tile's pixels
   __shared__ int dest[PT];          // compact mode: destination row of each pixel of the tile
   __shared__ int cnt_s[2][8];
   __shared__ int is_last;
@@ -74,18 +81,29 @@ prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, i
   float *__restrict__ inv_norm = sd.inv_norm;
   float *__restrict__ scratch = sd.scratch;
   int32_t *__restrict__ key_count = sd.key_count;
-  const int b = blockIdx.y, tl = blockIdx.x;
+  const int b = blockIdx.y;
+  const int tl0 = blockIdx.x * nt, tl1 = min(tiles, tl0 + nt);      // this CTA's run of 32-pixel tiles
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int x = tl * PT + lane;
-  const bool valid = x < P;
-  const float *__restrict__ src = feat + (long long)b * C * P + x;
+  const float *__restrict__ src = feat + (long long)b * C * P + lane;
+  // all C/8 loads of a thread are issued before the first use (one DRAM round trip per tile), and the loads of
+  // tile t+1 are issued before the reductions of tile t: a CTA always has 32*C*4 bytes in flight
+  float v[2 * NP];
+  {
+    const bool valid = tl0 * PT + lane < P;
+#pragma unroll
+    for (int i = 0; i < NP; ++i) {
+      const float *r = src + tl0 * PT + (long long)(2 * (warp + 8 * i)) * P;
+      v[2 * i] = valid ? __ldcs(r) : 0.f;
+      v[2 * i + 1] = valid ? __ldcs(r + P) : 0.f;
+    }
+  }
+  int before = 0, total = 0;        // warp 0: foreground pixels before the current tile / in the image
   if (key_count != nullptr) {
     // stable partition of the image's pixels: foreground rows first, background rows after
-    int before = 0, total = 0;
     for (int i = threadIdx.x; i < P; i += 256) {
       const int on = mask[(long long)b * P + i] != 0.f;
       total += on;
-      before += on && (i < tl * PT);
+      before += on && (i < tl0 * PT);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -94,88 +112,104 @@ prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, i
     }
     if (lane == 0) { cnt_s[0][warp] = before; cnt_s[1][warp] = total; }
     __syncthreads();
-    if (warp == 0) {
-      before = 0; total = 0;
+    before = 0; total = 0;
 #pragma unroll
-      for (int w = 0; w < 8; ++w) { before += cnt_s[0][w]; total += cnt_s[1][w]; }
-      const bool on = valid && mask[(long long)b * P + x] != 0.f;
-      const unsigned fgm = __ballot_sync(0xffffffffu, on);
-      const int fg_lt = __popc(fgm & ((1u << lane) - 1u));
-      dest[lane] = on ? (before + fg_lt) : (total + (x - before - fg_lt));
-      if (tl == 0 && lane == 0) key_count[b] = total;
+    for (int w = 0; w < 8; ++w) { before += cnt_s[0][w]; total += cnt_s[1][w]; }
+    if (blockIdx.x == 0 && threadIdx.x == 0) key_count[b] = total;
+  }
+  for (int tl = tl0; tl < tl1; ++tl) {
+    const int x = tl * PT + lane;
+    const bool valid = x < P;
+    float f[2 * NP];
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < 2 * NP; ++i) {
+      f[i] = v[i];
+      sum = fmaf(f[i], f[i], sum);
     }
-  }
-  // all C/8 loads of a thread are issued before the first use: one DRAM round trip per CTA instead of four
-  float sum = 0.f;
-  float v[C / 8];
+    ssq[warp][lane] = sum;
+    if (tl + 1 < tl1) {
+      const bool nvalid = x + PT < P;
 #pragma unroll
-  for (int i = 0; i < C / 8; ++i) v[i] = valid ? __ldcs(src + (long long)(warp + 8 * i) * P) : 0.f;
-#pragma unroll
-  for (int i = 0; i < C / 8; ++i) {
-    tile[warp + 8 * i][lane] = v[i];
-    sum = fmaf(v[i], v[i], sum);
-  }
-  ssq[warp][lane] = sum;
-  __syncthreads();
-  if (warp == 0) {
-    float tot = 0.f;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) tot += ssq[w][lane];
-    const float d = fmaxf(sqrtf(tot), 1e-12f);       // F.normalize eps
-    den[lane] = d;
-    mk[lane] = valid ? mask[(long long)b * P + x] : 0.f;
-    if (valid) inv_norm[(long long)b * P + x] = 1.0f / d;
-  }
-  __syncthreads();
-  {
-    const float d = den[lane];
-    for (int c = warp; c < C; c += 8) tile[c][lane] = tile[c][lane] / d;
-  }
-  __syncthreads();
-  {
-    // pooled sums of the tile: one thread per (channel, pos | neg) walks the 32 pixels in order (rows of `tile` are
-    // 33 floats apart: conflict-free), no shuffles
-    float *__restrict__ part = scratch + ((long long)(b * tiles + tl) * 2) * C;
-    const int nv = min(PT, P - tl * PT);
-    for (int o = threadIdx.x; o < 2 * C; o += 256) {
-      const int c = o < C ? o : o - C;
-      float s = 0.f;
-      if (o < C) {
-#pragma unroll 8
-        for (int p = 0; p < nv; ++p) s = fmaf(tile[c][p], mk[p], s);
-      } else {
-#pragma unroll 8
-        for (int p = 0; p < nv; ++p) s = fmaf(tile[c][p], 1.0f - mk[p], s);
+      for (int i = 0; i < NP; ++i) {
+        const float *r = src + (tl + 1) * PT + (long long)(2 * (warp + 8 * i)) * P;
+        v[2 * i] = nvalid ? __ldcs(r) : 0.f;
+        v[2 * i + 1] = nvalid ? __ldcs(r + P) : 0.f;
       }
-      part[o] = s;
     }
+    __syncthreads();
+    {
+      // every thread sums the eight partial squares of its own pixel (same order everywhere: same value)
+      float tot = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) tot += ssq[w][lane];
+      const float rd = 1.0f / fmaxf(sqrtf(tot), 1e-12f);       // F.normalize eps
+      if (warp == 0) {
+        const float m = valid ? mask[(long long)b * P + x] : 0.f;
+        wts[lane] = make_float2(m, 1.0f - m);
+        if (valid) inv_norm[(long long)b * P + x] = rd;
+        if (key_count != nullptr) {
+          const bool on = valid && m != 0.f;
+          const unsigned fgm = __ballot_sync(0xffffffffu, on);
+          const int fg_lt = __popc(fgm & ((1u << lane) - 1u));
+          dest[lane] = on ? (before + fg_lt) : (total + (x - before - fg_lt));
+          before += __popc(fgm);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < NP; ++i) {
+        const int j = warp + 8 * i;
+        const float a = f[2 * i] * rd, c = f[2 * i + 1] * rd;
+        tile[2 * j][lane] = a;
+        tile[2 * j + 1][lane] = c;
+        const __nv_bfloat162 h = __floats2bfloat162_rn(a, c);
+        tile_t[lane][j] = *reinterpret_cast<const uint32_t *>(&h);
+      }
+    }
+    __syncthreads();
+    // pooled sums of the tile: one thread per channel walks the 32 pixels in order for both sums (pixels beyond P
+    // hold zeros), no shuffles
+    for (int c = threadIdx.x; c < C; c += 256) {
+      float sp0 = 0.f, sn0 = 0.f, sp1 = 0.f, sn1 = 0.f;      // even / odd pixels: two short FMA chains each
+#pragma unroll
+      for (int p = 0; p < PT; p += 2) {
+        const float4 w = *reinterpret_cast<const float4 *>(&wts[p]);
+        const float x0 = tile[c][p], x1 = tile[c][p + 1];
+        sp0 = fmaf(x0, w.x, sp0);
+        sn0 = fmaf(x0, w.y, sn0);
+        sp1 = fmaf(x1, w.z, sp1);
+        sn1 = fmaf(x1, w.w, sn1);
+      }
+      float *__restrict__ part = scratch + ((long long)(b * tiles + tl) * 2) * C;
+      part[c] = sp0 + sp1;
+      part[C + c] = sn0 + sn1;
+    }
+    // transposed store: warp w writes pixels w*4..w*4+3, 64 channels (128 B) per pass
+#pragma unroll
+    for (int pp = 0; pp < PT / 8; ++pp) {
+      const int p = warp * (PT / 8) + pp;
+      const int xx = tl * PT + p;
+      if (xx < P) {
+        const int row = key_count ? dest[p] : xx;
+        if (sd.perm && lane == 0) sd.perm[(long long)b * P + row] = xx;
+        uint32_t *dst = reinterpret_cast<uint32_t *>(fhat_t + ((long long)b * P + row) * C);
+#pragma unroll
+        for (int j = 0; j < C / 64; ++j) dst[j * 32 + lane] = tile_t[p][j * 32 + lane];
+      }
+    }
+    // no barrier here: the next iteration writes ssq before its first barrier (last read before this iteration's
+    // second one) and the tiles / wts / dest after it (last read above)
   }
-  __threadfence();                       // this tile's partial sums are visible before the done counter moves
+  __threadfence();                       // this CTA's partial sums are visible before the done counter moves
   __syncthreads();
   if (threadIdx.x == 0) {
     unsigned int *cnt = counters + blockIdx.z * gridDim.y + b;
-    const int last = atomicAdd(cnt, 1u) == (unsigned)tiles - 1u;
+    const int last = atomicAdd(cnt, 1u) == gridDim.x - 1u;
     if (last) *cnt = 0u;
     is_last = last;
   }
-  // transposed store: warp w writes pixels w*4..w*4+3, 64 channels (128 B) per pass
-#pragma unroll
-  for (int pp = 0; pp < PT / 8; ++pp) {
-    const int p = warp * (PT / 8) + pp;
-    const int xx = tl * PT + p;
-    if (xx < P) {
-      const int row = key_count ? dest[p] : xx;
-      if (sd.perm && lane == 0) sd.perm[(long long)b * P + row] = xx;
-      __nv_bfloat162 *dst = reinterpret_cast<__nv_bfloat162 *>(fhat_t + ((long long)b * P + row) * C);
-#pragma unroll
-      for (int j = 0; j < C / 64; ++j) {
-        const int c = j * 64 + lane * 2;
-        dst[c >> 1] = __floats2bfloat162_rn(tile[c][p], tile[c + 1][p]);
-      }
-    }
-  }
   __syncthreads();
-  if (is_last) {                         // block-uniform: the image's last tile reduces the partial sums
+  if (is_last) {                         // block-uniform: the image's last CTA reduces the partial sums
     __threadfence();
     prep_reduce_image(sd, b, C, tiles, &tile[0][0], reinterpret_cast<float (*)[8]>(&ssq[0][0]));
   }
@@ -199,14 +233,26 @@ int check_side(const PrepSide &sd) {
   return CP2_OK;
 }
 
+// fp32 tile [C][33] + packed bf16 tile [32][C/2+1]
+size_t prep_smem(int C) { return sizeof(float) * C * (PT + 1) + sizeof(uint32_t) * PT * (C / 2 + 1); }
+
 int launch_prep(const PrepSides &sides, int nsides, unsigned int *counters, int B, int C, int P, cudaStream_t st) {
   const int tiles = cp2_prep_tiles(P);
-  dim3 grid(tiles, B, nsides);
+  // tiles per CTA: 1 while every CTA is resident at once (the pre-training step: latency-bound, widest grid);
+  // beyond that a CTA walks a run of tiles with the next tile's loads in flight (HBM-bound sizes)
+  const long long ctas = (long long)B * nsides * tiles, resident = 8LL * cp2_num_sms();
+  int nt = 1;
+  if (ctas > resident) nt = (int)std::min<long long>(8, std::max<long long>(2, ctas / (2 * resident)));
+  dim3 grid(cp2_cdiv(tiles, nt), B, nsides);
+  const size_t smem = prep_smem(C);
   switch (C) {
-    case 64: prep_kernel<64><<<grid, 256, 0, st>>>(sides, counters, P, tiles); break;
-    case 128: prep_kernel<128><<<grid, 256, 0, st>>>(sides, counters, P, tiles); break;
-    case 192: prep_kernel<192><<<grid, 256, 0, st>>>(sides, counters, P, tiles); break;
-    default: prep_kernel<256><<<grid, 256, 0, st>>>(sides, counters, P, tiles); break;
+    case 64: prep_kernel<64><<<grid, 256, smem, st>>>(sides, counters, P, tiles, nt); break;
+    case 128: prep_kernel<128><<<grid, 256, smem, st>>>(sides, counters, P, tiles, nt); break;
+    case 192: prep_kernel<192><<<grid, 256, smem, st>>>(sides, counters, P, tiles, nt); break;
+    default:
+      CP2_SMEM_ONCE(prep_kernel<256>, smem);       // 50.3 KB: above the 48 KB default
+      prep_kernel<256><<<grid, 256, smem, st>>>(sides, counters, P, tiles, nt);
+      break;
   }
   CP2_LAUNCH_CHECK();
   return CP2_OK;
