@@ -84,17 +84,20 @@ prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, i
   const int b = blockIdx.y;
   const int tl0 = blockIdx.x * nt, tl1 = min(tiles, tl0 + nt);      // this CTA's run of 32-pixel tiles
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const float *__restrict__ src = feat + (long long)b * C * P + lane;
+  // row pointer of this thread's first channel pair; pixels beyond P re-read pixel P-1 (their weights are zero and
+  // their rows are never stored), so no load is predicated
+  const float *__restrict__ src = feat + (long long)b * C * P + (long long)(2 * warp) * P;
+  const long long pair_stride = 16LL * P;             // channel pairs j and j+8
   // all C/8 loads of a thread are issued before the first use (one DRAM round trip per tile), and the loads of
   // tile t+1 are issued before the reductions of tile t: a CTA always has 32*C*4 bytes in flight
   float v[2 * NP];
   {
-    const bool valid = tl0 * PT + lane < P;
+    const float *r = src + min(tl0 * PT + lane, P - 1);
 #pragma unroll
     for (int i = 0; i < NP; ++i) {
-      const float *r = src + tl0 * PT + (long long)(2 * (warp + 8 * i)) * P;
-      v[2 * i] = valid ? __ldcs(r) : 0.f;
-      v[2 * i + 1] = valid ? __ldcs(r + P) : 0.f;
+      v[2 * i] = __ldcs(r);
+      v[2 * i + 1] = __ldcs(r + P);
+      r += pair_stride;
     }
   }
   int before = 0, total = 0;        // warp 0: foreground pixels before the current tile / in the image
@@ -117,6 +120,8 @@ prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, i
     for (int w = 0; w < 8; ++w) { before += cnt_s[0][w]; total += cnt_s[1][w]; }
     if (blockIdx.x == 0 && threadIdx.x == 0) key_count[b] = total;
   }
+  uint32_t *__restrict__ out_rows = reinterpret_cast<uint32_t *>(fhat_t + (long long)b * P * C);
+  int32_t *__restrict__ perm_rows = sd.perm ? sd.perm + (long long)b * P : nullptr;
   for (int tl = tl0; tl < tl1; ++tl) {
     const int x = tl * PT + lane;
     const bool valid = x < P;
@@ -129,12 +134,12 @@ prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, i
     }
     ssq[warp][lane] = sum;
     if (tl + 1 < tl1) {
-      const bool nvalid = x + PT < P;
+      const float *r = src + min(x + PT, P - 1);
 #pragma unroll
       for (int i = 0; i < NP; ++i) {
-        const float *r = src + (tl + 1) * PT + (long long)(2 * (warp + 8 * i)) * P;
-        v[2 * i] = nvalid ? __ldcs(r) : 0.f;
-        v[2 * i + 1] = nvalid ? __ldcs(r + P) : 0.f;
+        v[2 * i] = __ldcs(r);
+        v[2 * i + 1] = __ldcs(r + P);
+        r += pair_stride;
       }
     }
     __syncthreads();
@@ -143,10 +148,10 @@ prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, i
       float tot = 0.f;
 #pragma unroll
       for (int w = 0; w < 8; ++w) tot += ssq[w][lane];
-      const float rd = 1.0f / fmaxf(sqrtf(tot), 1e-12f);       // F.normalize eps
+      const float rd = tot >= 1e-24f ? rsqrtf(tot) : 1e12f;    // 1 / max(||x||, 1e-12): F.normalize eps
       if (warp == 0) {
         const float m = valid ? mask[(long long)b * P + x] : 0.f;
-        wts[lane] = make_float2(m, 1.0f - m);
+        wts[lane] = valid ? make_float2(m, 1.0f - m) : make_float2(0.f, 0.f);
         if (valid) inv_norm[(long long)b * P + x] = rd;
         if (key_count != nullptr) {
           const bool on = valid && m != 0.f;
@@ -168,7 +173,7 @@ prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, i
     }
     __syncthreads();
     // pooled sums of the tile: one thread per channel walks the 32 pixels in order for both sums (pixels beyond P
-    // hold zeros), no shuffles
+    // carry zero weights), no shuffles
     for (int c = threadIdx.x; c < C; c += 256) {
       float sp0 = 0.f, sn0 = 0.f, sp1 = 0.f, sn1 = 0.f;      // even / odd pixels: two short FMA chains each
 #pragma unroll
@@ -191,10 +196,10 @@ prep_kernel(const PrepSides sides, unsigned int *__restrict__ counters, int P, i
       const int xx = tl * PT + p;
       if (xx < P) {
         const int row = key_count ? dest[p] : xx;
-        if (sd.perm && lane == 0) sd.perm[(long long)b * P + row] = xx;
-        uint32_t *dst = reinterpret_cast<uint32_t *>(fhat_t + ((long long)b * P + row) * C);
+        if (perm_rows && lane == 0) perm_rows[row] = xx;
+        uint32_t *dst = out_rows + (size_t)row * (C / 2) + lane;
 #pragma unroll
-        for (int j = 0; j < C / 64; ++j) dst[j * 32 + lane] = tile_t[p][j * 32 + lane];
+        for (int j = 0; j < C / 64; ++j) dst[j * 32] = tile_t[p][j * 32 + lane];
       }
     }
     // no barrier here: the next iteration writes ssq before its first barrier (last read before this iteration's
