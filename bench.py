@@ -19,6 +19,7 @@ its CPU path is restated in oracle/cp2_oracle.py (CP2StepPort, kind "port") and 
 """
 import argparse
 import json
+import math
 import os
 import statistics
 import subprocess
@@ -1051,6 +1052,23 @@ def own_arm(args):
             ev.record(copy_stream)
         pending["next"] = (b, ev)
 
+    def e2e_step_sync(i):
+        batch, ev = pending.pop("next")
+        cur = torch.cuda.current_stream()
+        cur.wait_event(ev)
+        for t in batch.values():
+            t.record_stream(cur)
+        prefetch(i + 1)
+        return step(batch).item()           # device -> host read of the step's loss, blocking (main.py:644-660)
+
+    # The same step with the read-back a training loop that does not want to stall uses: every step's loss is copied
+    # into pinned host memory by an asynchronous D2H copy issued in that step and consumed on the host one step later,
+    # so the host keeps queueing work while the GPU finishes the step.  Every step still moves its own inputs H2D and
+    # its own loss D2H inside the timed region (the last copy completes before the closing event).
+    loss_host = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+    loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
+    seen = []
+
     def e2e_step(i):
         batch, ev = pending.pop("next")
         cur = torch.cuda.current_stream()
@@ -1058,12 +1076,20 @@ def own_arm(args):
         for t in batch.values():
             t.record_stream(cur)
         prefetch(i + 1)
-        return step(batch).item()           # device -> host read of the step's loss
+        loss = step(batch)
+        loss_host[i % 2].copy_(loss.detach(), non_blocking=True)
+        loss_ev[i % 2].record(cur)
+        if i > 0:
+            loss_ev[(i - 1) % 2].synchronize()
+            seen.append(float(loss_host[(i - 1) % 2]))
 
     prefetch(0)
     for i in range(2):
-        e2e_step(i)
+        e2e_step_sync(i)
+    ms_e2e_sync = timed(e2e_step_sync, args.steps)
     ms_e2e = timed(e2e_step, args.steps)
+    seen.append(float(loss_host[(args.steps - 1) % 2]))
+    assert len(seen) == args.steps and all(math.isfinite(v) for v in seen), "e2e: a step's loss did not come back"
     clocks = sampler.stop()
 
     # ---- N > 1: where the step time goes between ranks (untimed extra legs, device-side event timings)
@@ -1130,7 +1156,9 @@ def own_arm(args):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32+bf16",
         "data": "synthetic", "config": workload_config(B, world, args.nchw),
         "e2e": {"value": B * world * args.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
+                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps,
+                "readback": "async D2H into pinned memory, consumed one step later",
+                "blocking_item_value": B * world * args.steps / (ms_e2e_sync * 1e-3)},
         "gpu_launches": launches, "launches_per_step": launches / max(args.steps, 1), "clocks": clocks,
         "roofline": roofline, "kernels": kernels,
         "cp2_kernels_us_per_step": round(per_step_us, 1),
