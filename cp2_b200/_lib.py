@@ -19,6 +19,7 @@ SIGNATURES = {
     "cp2_composite2": (c_int, [c_void_p] * 10 + [c_int] * 4 + [c_void_p]),
     "cp2_prep_tiles": (c_int, [c_int]),
     "cp2_prep_features": (c_int, [c_void_p] * 13 + [c_int] * 3 + [c_void_p]),
+    "cp2_prep_features_static": (c_int, [c_void_p] * 11 + [c_int] * 3 + [c_void_p]),
     "cp2_prep_features2": (c_int, [c_void_p] * 23 + [c_int] * 3 + [c_void_p]),
     "cp2_dense_lse": (c_int, [c_void_p] * 4 + [c_float] + [c_int] * 3 + [c_void_p]),
     "cp2_dense_pad": (c_int, [c_int]),
@@ -64,7 +65,7 @@ DEBUG_SIGNATURES = {
 }
 
 EMA_CHUNK = 4096  # CP2_EMA_CHUNK
-ABI_VERSION = 9  # CP2_ABI_VERSION
+ABI_VERSION = 10  # CP2_ABI_VERSION
 
 _lib = None
 _dbg = None

@@ -7,6 +7,7 @@
 // reduced per tile into scratch and summed over tiles by the last CTA of the image in a
 // fixed order (deterministic).
 #include "common.cuh"
+#include <mutex>
 
 namespace {
 
@@ -303,4 +304,73 @@ extern "C" int cp2_prep_features2(const float *feat_q, const float *mask_q, void
   if (rc == CP2_OK) rc = check_side(sides.s[1]);
   if (rc != CP2_OK) return rc;
   return launch_prep(sides, 2, static_cast<unsigned int *>(scratch_counters), B, C, P, static_cast<cudaStream_t>(stream));
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// cp2_prep_features_static — cp2_prep_features for callers that cannot allocate (CUDA graph capture, serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The work space cp2_prep_features takes from the caller (per-tile partial sums + per-image done
+// counters) lives in ONE file-scope device array instead; every GPU that loads the library holds its
+// CP2_PREP_STATIC_BYTES until the process exits.  All calls on a device share it: calls that overlap on the GPU
+// (different streams, no ordering between them) race on it.
+namespace {
+
+constexpr size_t kStaticCounterBytes = (size_t)CP2_PREP_STATIC_MAX_B * sizeof(unsigned int);   // 16 KB, first
+constexpr size_t kStaticSumBytes = (size_t)CP2_PREP_STATIC_BYTES - kStaticCounterBytes;        // partial sums after
+static_assert(kStaticCounterBytes % 256 == 0, "the partial sums start on a 256-byte boundary");
+
+static __device__ __align__(256) unsigned char g_prep_static[CP2_PREP_STATIC_BYTES];
+
+// In host code `g_prep_static` is a host-side stand-in, not a device address: the address the kernel may use
+// comes from cudaGetSymbolAddress, asked once per device with that device current.
+int prep_static_base(unsigned char **base) {
+  static std::mutex mu;
+  static unsigned char *cached[64] = {nullptr};
+  int dev = 0;
+  CP2_CUDA(cudaGetDevice(&dev));
+  CP2_REQUIRE(dev >= 0 && dev < 64, "cp2_prep_features_static: device ordinal %d unsupported (< 64)", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (cached[dev] == nullptr) {
+    unsigned char *p = nullptr;
+    CP2_CUDA(cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_prep_static));
+    CP2_REQUIRE(p != nullptr, "cp2_prep_features_static: cudaGetSymbolAddress returned a null address");
+    cached[dev] = p;
+  }
+  *base = cached[dev];
+  return CP2_OK;
+}
+
+}  // namespace
+
+extern "C" int cp2_prep_features_static(const float *feat, const float *mask, void *fhat_t, float *inv_norm,
+                                        float *pos_sum, float *neg_sum, int32_t *key_count, int32_t *perm,
+                                        float *pos_unit, float *neg_unit, float *norms, int B, int C, int P,
+                                        void *stream) {
+  CP2_REQUIRE(B >= 0 && P > 0, "cp2_prep_features_static: bad shape B=%d P=%d", B, P);
+  CP2_REQUIRE(C == 64 || C == 128 || C == 192 || C == 256,
+              "cp2_prep_features_static: C=%d unsupported (64,128,192,256)", C);
+  if (B == 0) return CP2_OK;
+  CP2_REQUIRE(B <= CP2_PREP_STATIC_MAX_B, "cp2_prep_features_static: B=%d exceeds the static limit of %d images",
+              B, (int)CP2_PREP_STATIC_MAX_B);
+  const unsigned long long need = 1ull * B * cp2_prep_tiles(P) * 2ull * C * sizeof(float);
+  CP2_REQUIRE(need <= kStaticSumBytes,
+              "cp2_prep_features_static: B=%d C=%d P=%d needs %llu bytes of work space, the static array holds %llu "
+              "(use cp2_prep_features with caller-owned scratch)",
+              B, C, P, need, (unsigned long long)kStaticSumBytes);
+  CP2_REQUIRE(perm == nullptr || key_count != nullptr, "cp2_prep_features_static: perm needs key_count (compaction)");
+  unsigned char *base = nullptr;
+  int rc = prep_static_base(&base);
+  if (rc != CP2_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  PrepSides sides;
+  sides.s[0] = PrepSide{feat, mask, static_cast<__nv_bfloat16 *>(fhat_t), inv_norm,
+                        reinterpret_cast<float *>(base + kStaticCounterBytes), pos_sum, neg_sum,
+                        pos_unit, neg_unit, norms, key_count, perm};
+  sides.s[1] = sides.s[0];
+  rc = check_side(sides.s[0]);
+  if (rc != CP2_OK) return rc;
+  // the array keeps the last call's contents.  The partial sums are all written before they are read; the done
+  // counters must start at zero (a completed call leaves them zero, an aborted one might not): clear them in-stream.
+  CP2_CUDA(cudaMemsetAsync(base, 0, (size_t)B * sizeof(unsigned int), st));
+  return launch_prep(sides, 1, reinterpret_cast<unsigned int *>(base), B, C, P, st);
 }

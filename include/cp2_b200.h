@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CP2_ABI_VERSION 9
+#define CP2_ABI_VERSION 10
 
 #define CP2_OK 0
 #define CP2_E_INVALID (-1)      /* bad shape / null pointer / unsupported dim          */
@@ -79,6 +79,24 @@ int cp2_prep_features(const float *feat, const float *mask, void *fhat_t, float 
                       float *pos_sum, float *neg_sum, float *scratch, int32_t *key_count, int32_t *perm,
                       float *pos_unit, float *neg_unit, float *norms, void *scratch_counters,
                       int B, int C, int P, void *stream);
+/* cp2_prep_features without caller-owned work space, for callers that cannot allocate (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in the reference.
+ * Same inputs, outputs and results as cp2_prep_features; the
+ * `scratch` / `scratch_counters` arguments are gone: both live in one file-scope `static __device__` array of
+ * CP2_PREP_STATIC_BYTES (8 MiB) that every GPU which loads the library holds until the process exits.  The call
+ * allocates nothing (no cudaMalloc / cudaFree, no allocating library routine): one cudaMemsetAsync of the done
+ * counters and one kernel launch on `stream`.
+ * Limits (CP2_E_INVALID with a message beyond them): B <= CP2_PREP_STATIC_MAX_B (4096) and
+ *   B * cp2_prep_tiles(P) * 2 * C * 4 <= CP2_PREP_STATIC_BYTES - 4 * CP2_PREP_STATIC_MAX_B   (8 372 224 bytes;
+ *   configs[1], B=32, P=196, C=128: 229 376; B=256, P=784, C=128: 6 553 600; B=256, P=3136 does not fit).
+ * Every call on a device shares the array, which keeps the previous call's contents (the entry clears what must
+ * start at zero): calls that OVERLAP on the GPU — different streams without an ordering between them — race on
+ * it; calls on one stream, or ordered by events, are safe. */
+#define CP2_PREP_STATIC_BYTES (8u << 20)
+#define CP2_PREP_STATIC_MAX_B 4096
+int cp2_prep_features_static(const float *feat, const float *mask, void *fhat_t, float *inv_norm,
+                             float *pos_sum, float *neg_sum, int32_t *key_count, int32_t *perm,
+                             float *pos_unit, float *neg_unit, float *norms, int B, int C, int P, void *stream);
 /* Query side and key side (key side compacted through key_count) of one step in ONE launch; per side the
  * contract of cp2_prep_features (perm_k may be NULL).  scratch_counters: 2*B uint32. */
 int cp2_prep_features2(const float *feat_q, const float *mask_q, void *qhat_t, float *inv_norm_q,

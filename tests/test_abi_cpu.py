@@ -44,7 +44,7 @@ def test_every_declared_symbol_is_exported(lib):
 
 def test_abi_version_and_host_helpers(lib):
     from cp2_b200 import _lib
-    assert lib.cp2_abi_version() == _lib.ABI_VERSION == 9
+    assert lib.cp2_abi_version() == _lib.ABI_VERSION == 10
     assert lib.cp2_mirror_up_partials(2, 512, 512) == 2 * 32 * 4 and lib.cp2_mirror_partials(0, 16) == 1
     assert lib.cp2_prep_tiles(196) == 7 and lib.cp2_prep_tiles(32) == 1
     assert lib.cp2_global_scratch_bytes(32, 128) == 32 * 8 + 32 * 128 * 8 + 32 * 12 + 16
