@@ -483,18 +483,223 @@ mirror_up_kernel(const float *__restrict__ s_lo, const float *__restrict__ t_lo,
   block_partials<kUpTW>(cls_sum, cmp_sum, n_valid, partial + 3 * cta);
 }
 
+// ------------------------------------------------- fused bilinear upsample, two classes (the polyp masks)
+// With two classes every term of the loss depends on the logits only through their DIFFERENCE a = s1 - s0,
+// b = t1 - t0, and bilinear interpolation is linear: the kernel interpolates the difference maps (half the patch,
+// half the lerps), evaluates one pixel in ~70 arithmetic instructions (mirror_pixel2d) and accumulates ONE gradient
+// per network (d/ds1 = -d/ds0 = d/da): half the segmented reductions and shared-memory atomics.  A CTA walks
+// th = 16, 32 or 64 rows in batches of 16 labels, so the per-CTA set-up (patch, reduction plan, block sums, gradient
+// write-back) is paid once per 64 rows on large batches; the per-row vertical weights come from a table in smem.
+constexpr int kUpMaxTH = 64;
+
+// a, b: interpolated logit differences; label in {0, 1} or -1 (ignored).  lm = 1 for live lanes, 0 for lanes past W.
+// cls_sum / cmp_sum gain the un-normalised loss terms; ga, gb = d loss / d a, d loss / d b (normalised).
+template <bool HAS_T, bool GRAD>
+__device__ __forceinline__ void mirror_pixel2d(float a, float b, int label, float w_cls, float k2, float kcmp,
+                                               float lm, float &cls_sum, float &cmp_sum, float &n_valid,
+                                               float &ga, float &gb) {
+  constexpr float kL2E = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
+  const float lv = label >= 0 ? 1.f : 0.f;
+  const float sgn = label > 0 ? -1.f : 1.f;                // d = logit(other) - logit(label) = sgn * (x1 - x0)
+  const float gsc = sgn * (lv * w_cls);
+  // class CE = softplus(d); d/dx = sgn * sigmoid(d)
+  auto class_ce = [&](float x, float &g) -> float {
+    const float d = sgn * x;
+    const float e = ex2_fast(-fabsf(d) * kL2E);
+    const float o = 1.f + e;
+    const float term = fmaf(kLn2, lg2_fast(o), fmaxf(d, 0.f));
+    if constexpr (GRAD) {
+      const float r = rcp_fast(o);
+      g = gsc * (d >= 0.f ? r : e * r);
+    }
+    return term;
+  };
+  float term = class_ce(a, ga);
+  if constexpr (HAS_T) {
+    term += class_ce(b, gb);
+    // softmax(x / T) over two logits = (big, small) = (r, e r), e = exp(-|x| / T), the big one on the side of sign(x)
+    const float es = ex2_fast(-fabsf(a) * k2), rs = rcp_fast(1.f + es), ss = es * rs;     // u   = softmax(s / T)
+    const float et = ex2_fast(-fabsf(b) * k2), rt = rcp_fast(1.f + et), st = et * rt;     // tau = softmax(t / T)
+    // CE with u as the LOGITS and tau as the target: lse(u) - sum_c tau_c u_c;  |u1 - u0| = rs - ss
+    const float dus = rs - ss;
+    const float e2 = ex2_fast(-dus * kL2E), o2 = 1.f + e2;
+    const float lse2 = fmaf(kLn2, lg2_fast(o2), rs);
+    const bool same = (__float_as_int(a) ^ __float_as_int(b)) >= 0;       // big entries in the same class
+    const float x = same ? rt : st, y = same ? st : rt;
+    const float tu = fmaf(rs, x, ss * y);
+    cmp_sum = fmaf(lm, lse2 - tu, cmp_sum);
+    if constexpr (GRAD) {
+      // d/da = (u0 u1 / T) ((q1 - q0) - (tau1 - tau0)),  q = softmax(u);   d/db = -(tau0 tau1 / T) (u1 - u0)
+      const float r2 = rcp_fast(o2), dq = fmaf(-e2, r2, r2);               // |q1 - q0|, sign(a)
+      const float dts = rt - st;                                           // |tau1 - tau0|, sign(b)
+      const float inner = dq - (same ? dts : -dts);                        // in units of sign(a)
+      const unsigned sa = __float_as_uint(a) & 0x80000000u;
+      const float ca = kcmp * (rs * ss) * inner, cb = kcmp * (rt * st) * dus;
+      ga += __uint_as_float(__float_as_uint(ca) ^ sa);
+      gb -= __uint_as_float(__float_as_uint(cb) ^ sa);
+    }
+  }
+  cls_sum = fmaf(lv, term, cls_sum);
+  n_valid += lv;
+}
+
+// s_lo,t_lo,ds_lo,dt_lo: [B,2,h,w]; labels [B,H,W].  CTA = th x kUpTW output pixels of one image, thread = one
+// output column.  Shared memory: the low-resolution patch of logit DIFFERENCES the tile reads ([NS][PH][PW]) and,
+// with GRAD, a same-shaped accumulator of d loss / d difference.
+template <bool HAS_T, bool GRAD>
+__global__ void __launch_bounds__(kUpTW)
+mirror_up2_kernel(const float *__restrict__ s_lo, const float *__restrict__ t_lo,
+                  const long long *__restrict__ labels, float *__restrict__ partial,
+                  float *__restrict__ ds_lo, float *__restrict__ dt_lo, MirrorScale sc, int h, int w,
+                  int H, int W, float ry, float rx, int PH, int PW, int th) {
+  extern __shared__ float smem[];
+  __shared__ int row_i[kUpMaxTH];          // (patch row of iy0) * 2 + (iy1 - iy0) of every output row of the tile
+  __shared__ float row_l[kUpMaxTH];        // l1y
+  constexpr int NS = HAS_T ? 2 : 1;
+  const int cell = PH * PW;
+  float *val = smem;                       // [NS][PH][PW]
+  float *acc = smem + NS * cell;           // [NS][PH][PW]  (GRAD only)
+  const int b = blockIdx.z, tid = threadIdx.x, lane = tid & 31;
+  const int x_tile = blockIdx.x * kUpTW, y_tile = blockIdx.y * th;
+  const int rows = min(th, H - y_tile);
+  const long long plane = (long long)h * w;
+
+  int py0, px0, tmp;
+  float f0, f1;
+  bilinear_src(y_tile, ry, h, py0, tmp, f0, f1);
+  bilinear_src(x_tile, rx, w, px0, tmp, f0, f1);
+  for (int i = tid; i < NS * cell; i += kUpTW) {
+    const int k = i / cell, rem = i - k * cell, pi = rem / PW, pj = rem - pi * PW;
+    const int yy = py0 + pi, xx = px0 + pj;
+    const float *src = ((k == 0) ? s_lo : t_lo) + ((long long)b * 2 * h + yy) * w + xx;
+    val[i] = (yy < h && xx < w) ? __ldg(src + plane) - __ldg(src) : 0.f;
+    if constexpr (GRAD) acc[i] = 0.f;
+  }
+  if (tid < th) {
+    int i0, i1;
+    float l0, l1;
+    bilinear_src(min(y_tile + tid, H - 1), ry, h, i0, i1, l0, l1);
+    row_i[tid] = ((i0 - py0) << 1) | (i1 - i0);
+    row_l[tid] = l1;
+  }
+
+  const int x = x_tile + tid;
+  const bool live = x < W;
+  const int xc = live ? x : W - 1;          // dead lanes keep a sorted key and contribute zeros
+  int ix0, ix1;
+  float l0x, l1x;
+  bilinear_src(xc, rx, w, ix0, ix1, l0x, l1x);
+  ix0 -= px0; ix1 -= px0;
+  // segmented-reduction plan over the (sorted) key ix0 within the warp
+  unsigned same = 0;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const int other = __shfl_down_sync(0xffffffffu, ix0, 1 << i);
+    if (lane + (1 << i) < 32 && other == ix0) same |= 1u << i;
+  }
+  const int prev = __shfl_up_sync(0xffffffffu, ix0, 1);
+  const bool head = lane == 0 || prev != ix0;
+  __syncthreads();
+
+  constexpr float kL2E = 1.4426950408889634f;
+  const float lm = live ? 1.f : 0.f;
+  const float k2 = kL2E * sc.inv_temp, kcmp = live ? sc.w_cmp * sc.inv_temp : 0.f, w_cls = sc.w_cls;
+  float top[NS], bot[NS], a_top[NS], a_bot[NS];
+  int cur = -1, cur0 = 0, cur1 = 0;
+  float cls_sum = 0.f, cmp_sum = 0.f, n_valid = 0.f;
+
+  auto flush = [&]() {
+    if constexpr (GRAD) {
+#pragma unroll
+      for (int k = 0; k < NS; ++k)
+#pragma unroll
+        for (int tb = 0; tb < 2; ++tb) {
+          const float a = tb == 0 ? a_top[k] : a_bot[k];
+          float v0 = l0x * a, v1 = l1x * a;
+#pragma unroll
+          for (int i = 0; i < 5; ++i) {
+            const float o0 = __shfl_down_sync(0xffffffffu, v0, 1 << i);
+            const float o1 = __shfl_down_sync(0xffffffffu, v1, 1 << i);
+            if (same & (1u << i)) { v0 += o0; v1 += o1; }
+          }
+          if (head) {
+            float *row = acc + k * cell + (tb == 0 ? cur0 : cur1) * PW;
+            atomicAdd(row + ix0, v0);
+            atomicAdd(row + ix1, v1);
+          }
+        }
+    }
+  };
+
+  const long long *lab_col = labels + ((long long)b * H + y_tile) * W + x;
+#pragma unroll 1
+  for (int r0 = 0; r0 < rows; r0 += kUpTH) {          // CTA-uniform trip counts and branches throughout
+    // labels of this thread's column for 16 rows: all loads issued before the first use, then packed to 2-bit
+    // codes (label + 1; 0 = ignored) so that the row loop needs no unrolling
+    long long lab[kUpTH];
+#pragma unroll
+    for (int r = 0; r < kUpTH; ++r)
+      lab[r] = (live && r0 + r < rows) ? __ldcs(lab_col + (long long)(r0 + r) * W) : kIgnoreIndex;
+    unsigned codes = 0;
+#pragma unroll
+    for (int r = 0; r < kUpTH; ++r) codes |= (unsigned)(mirror_label(lab[r], 2) + 1) << (2 * r);
+    const int rend = min(r0 + kUpTH, rows);
+#pragma unroll 1
+    for (int r = r0; r < rend; ++r) {
+      const int ri = row_i[r];
+      const float l1y = row_l[r], l0y = 1.f - l1y;
+      if (ri != cur) {
+        if (cur >= 0) flush();
+        cur = ri; cur0 = ri >> 1; cur1 = cur0 + (ri & 1);
+#pragma unroll
+        for (int k = 0; k < NS; ++k) {
+          const float *p = val + k * cell;
+          top[k] = l0x * p[cur0 * PW + ix0] + l1x * p[cur0 * PW + ix1];
+          bot[k] = l0x * p[cur1 * PW + ix0] + l1x * p[cur1 * PW + ix1];
+          a_top[k] = 0.f; a_bot[k] = 0.f;
+        }
+      }
+      const float a = l0y * top[0] + l1y * bot[0];
+      const float bb = HAS_T ? l0y * top[NS - 1] + l1y * bot[NS - 1] : 0.f;
+      const int label = (int)((codes >> (2 * (r - r0))) & 3u) - 1;       // -1: ignored / dead lane
+      float ga = 0.f, gb = 0.f;
+      mirror_pixel2d<HAS_T, GRAD>(a, bb, label, w_cls, k2, kcmp, lm, cls_sum, cmp_sum, n_valid, ga, gb);
+      if constexpr (GRAD) {
+        a_top[0] = fmaf(l0y, ga, a_top[0]); a_bot[0] = fmaf(l1y, ga, a_bot[0]);
+        if constexpr (HAS_T) { a_top[1] = fmaf(l0y, gb, a_top[1]); a_bot[1] = fmaf(l1y, gb, a_bot[1]); }
+      }
+    }
+  }
+  if (cur >= 0) flush();
+  if constexpr (GRAD) {
+    __syncthreads();
+    for (int i = tid; i < NS * cell; i += kUpTW) {
+      const int k = i / cell, rem = i - k * cell, pi = rem / PW, pj = rem - pi * PW;
+      const int yy = py0 + pi, xx = px0 + pj;
+      const float v = acc[i];
+      if (yy < h && xx < w && v != 0.f) {
+        float *dst = (k == 0 ? ds_lo : dt_lo) + ((long long)b * 2 * h + yy) * w + xx;
+        atomicAdd(dst + plane, v);           // d/d logit(1) = d/d difference
+        atomicAdd(dst, -v);                  // d/d logit(0) = -d/d difference
+      }
+    }
+  }
+  const long long cta = ((long long)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  block_partials<kUpTW>(cls_sum, cmp_sum, n_valid, partial + 3 * cta);
+}
+
 struct UpGeom { int gx, gy, PH, PW; };
 
-UpGeom up_geometry(int h, int w, int H, int W) {
+UpGeom up_geometry(int h, int w, int H, int W, int th = kUpTH) {
   UpGeom g;
   g.gx = cp2_cdiv(W, kUpTW);
-  g.gy = cp2_cdiv(H, kUpTH);
+  g.gy = cp2_cdiv(H, th);
   const float ry = (float)h / (float)H, rx = (float)w / (float)W;
   g.PH = 1; g.PW = 1;
   int a0, a1, b0, b1; float f0, f1;
   for (int ty = 0; ty < g.gy; ++ty) {
-    bilinear_src(ty * kUpTH, ry, h, a0, a1, f0, f1);
-    const int last = (ty * kUpTH + kUpTH - 1 < H) ? ty * kUpTH + kUpTH - 1 : H - 1;
+    bilinear_src(ty * th, ry, h, a0, a1, f0, f1);
+    const int last = (ty * th + th - 1 < H) ? ty * th + th - 1 : H - 1;
     bilinear_src(last, ry, h, b0, b1, f0, f1);
     if (b1 - a0 + 1 > g.PH) g.PH = b1 - a0 + 1;
   }
@@ -563,6 +768,38 @@ int launch_up(const float *s, const float *t, const long long *labels, float *pa
   if (has_t) { if (grad) CP2_UP(true, true); else CP2_UP(true, false); }
   else       { if (grad) CP2_UP(false, true); else CP2_UP(false, false); }
 #undef CP2_UP
+  CP2_LAUNCH_CHECK();
+  return CP2_OK;
+}
+
+// Two classes: the difference kernel.  Rows per CTA: 16 while the grid is small (occupancy first), 32 / 64 once
+// there are enough CTAs to keep every SM full (amortises the per-CTA set-up and gradient write-back).
+int up2_rows_per_cta(int B, int H, int W) {
+  const long long ctas16 = (long long)B * cp2_cdiv(H, kUpTH) * cp2_cdiv(W, kUpTW);
+  const long long wave = 8LL * cp2_num_sms();
+  return ctas16 >= 3 * wave ? 64 : ctas16 >= 3 * wave / 2 ? 32 : 16;
+}
+
+int launch_up2(const float *s, const float *t, const long long *labels, float *partial, float *ds,
+               float *dt, MirrorScale sc, int B, int h, int w, int H, int W, const UpGeom &g, int th,
+               cudaStream_t st) {
+  const bool has_t = t != nullptr, grad = ds != nullptr;
+  const size_t smem = sizeof(float) * (size_t)(has_t ? 2 : 1) * g.PH * g.PW * (grad ? 2 : 1);
+  CP2_REQUIRE(smem <= 200 * 1024, "cp2_mirror_loss_upsampled: low-resolution patch of %zu bytes per tile "
+              "does not fit shared memory (h=%d w=%d H=%d W=%d)", smem, h, w, H, W);
+  const float ry = (float)h / (float)H, rx = (float)w / (float)W;
+  const dim3 grid(g.gx, g.gy, B);
+#define CP2_UP2(HT, GR)                                                                           \
+  do {                                                                                            \
+    if (smem > 48 * 1024)                                                                         \
+      CP2_CUDA(cudaFuncSetAttribute(mirror_up2_kernel<HT, GR>,                                    \
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));     \
+    mirror_up2_kernel<HT, GR><<<grid, kUpTW, smem, st>>>(s, t, labels, partial, ds, dt, sc, h, w, \
+                                                         H, W, ry, rx, g.PH, g.PW, th);           \
+  } while (0)
+  if (has_t) { if (grad) CP2_UP2(true, true); else CP2_UP2(true, false); }
+  else       { if (grad) CP2_UP2(false, true); else CP2_UP2(false, false); }
+#undef CP2_UP2
   CP2_LAUNCH_CHECK();
   return CP2_OK;
 }
@@ -651,13 +888,14 @@ extern "C" int cp2_mirror_loss_upsampled(const float *s_lo, const float *t_lo, c
   const size_t lo_bytes = sizeof(float) * (size_t)B * Cls * h * w;
   if (ds_lo) CP2_CUDA(cudaMemsetAsync(ds_lo, 0, lo_bytes, st));
   if (dt_lo && has_t) CP2_CUDA(cudaMemsetAsync(dt_lo, 0, lo_bytes, st));
-  const UpGeom g = up_geometry(h, w, H, W);
+  const int th = Cls == 2 ? up2_rows_per_cta(B, H, W) : kUpTH;
+  const UpGeom g = up_geometry(h, w, H, W, th);
   const MirrorScale sc = make_scale(has_t, n_pix, n_valid, lmbd_compare, inv_temp);
   const long long *lab = reinterpret_cast<const long long *>(labels);
   int rc = CP2_OK;
 #define CP2_CALL_UP(N) launch_up<N>(s_lo, t_lo, lab, partial, ds_lo, dt_lo, sc, B, h, w, H, W, g, st)
   switch (Cls) {
-    case 2: rc = CP2_CALL_UP(2); break;
+    case 2: rc = launch_up2(s_lo, t_lo, lab, partial, ds_lo, dt_lo, sc, B, h, w, H, W, g, th, st); break;
     case 3: rc = CP2_CALL_UP(3); break;
     case 4: rc = CP2_CALL_UP(4); break;
     case 5: rc = CP2_CALL_UP(5); break;

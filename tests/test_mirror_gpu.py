@@ -76,7 +76,11 @@ def test_golden_full_resolution(ops, tag):
 @pytest.mark.parametrize("B,Cls,h,w,H,W", [(8, 2, 32, 32, 512, 512),      # BASELINE configs[4] at OS16
                                             (2, 2, 64, 64, 512, 512),      # ... and the OS8 64x64 map
                                             (3, 4, 14, 14, 224, 224), (1, 8, 9, 5, 131, 77),
-                                            (2, 2, 16, 16, 16, 16), (2, 3, 20, 12, 30, 50)])
+                                            (2, 2, 16, 16, 16, 16), (2, 3, 20, 12, 30, 50),
+                                            # two-class difference kernel with 32 / 64 rows per CTA: ragged last
+                                            # row tile and dead lanes in the last column tile; the B=32 bench shape
+                                            (20, 2, 16, 16, 500, 390), (32, 2, 32, 32, 512, 512),
+                                            (1, 2, 7, 5, 45, 131)])
 def test_upsampled_vs_oracle(ops, B, Cls, h, w, H, W):
     gen = torch.Generator().manual_seed(B * 100 + Cls * 10 + h)
     s_lo = 2.5 * torch.randn(B, Cls, h, w, generator=gen)
@@ -126,6 +130,36 @@ def test_ignore_index_and_valid_count(ops):
     loss2, aux2 = ops.mirror_loss(s_hi, t_hi, masks.cuda(), 0.2, 1.0, n_valid=n_valid)
     np.testing.assert_allclose(loss2.item(), ref.item(), rtol=1e-4)
     assert int(aux2[2].item()) == n_valid
+
+
+def test_two_class_ignore_index_large_batch(ops):
+    """The two-class kernel (logit differences, 64 rows per CTA at this size) with ignored labels,
+    a strong compare weight and T != 1; and without a teacher."""
+    gen = torch.Generator().manual_seed(9)
+    B, Cls, h, w, H, W = 40, 2, 12, 10, 384, 300
+    s_lo = 3.0 * torch.randn(B, Cls, h, w, generator=gen)
+    t_lo = 3.0 * torch.randn(B, Cls, h, w, generator=gen)
+    masks = torch.randint(0, Cls, (B, H, W), generator=gen)
+    masks[torch.rand(B, H, W, generator=gen) < 0.25] = -100
+    n_valid = int((masks >= 0).sum())
+    so, to = s_lo.clone().requires_grad_(True), t_lo.clone().requires_grad_(True)
+    ref, _, _ = O.mirror_step(so, to, masks, 0.7, 0.5)
+    ref.backward()
+    sg, tg = s_lo.cuda().requires_grad_(True), t_lo.cuda().requires_grad_(True)
+    loss, aux = ops.mirror_loss_upsampled(sg, tg, masks.cuda(), 0.7, 0.5, n_valid=n_valid)
+    loss.backward()
+    assert int(aux[2].item()) == n_valid
+    np.testing.assert_allclose(loss.item(), ref.item(), rtol=1e-4)
+    close_grad(sg.grad, so.grad)
+    close_grad(tg.grad, to.grad)
+    # no teacher: class CE only (mirror_network.py:47-52 with one network)
+    out, ds, dt = ops.mirror_loss_upsampled_raw(s_lo.cuda(), None, masks.cuda(), 0.7, 0.5, True, n_valid=n_valid)
+    assert dt is None
+    s2 = s_lo.clone().requires_grad_(True)
+    ce = torch.nn.functional.cross_entropy(O.mirror_resize(s2, (H, W)), masks)
+    ce.backward()
+    np.testing.assert_allclose(out[0].item(), ce.item(), rtol=1e-4)
+    close_grad(ds, s2.grad)
 
 
 def test_mirror_module_shared_step(ops):
