@@ -491,6 +491,7 @@ mirror_up_kernel(const float *__restrict__ s_lo, const float *__restrict__ t_lo,
 // th = 16, 32 or 64 rows in batches of 16 labels, so the per-CTA set-up (patch, reduction plan, block sums, gradient
 // write-back) is paid once per 64 rows on large batches; the per-row vertical weights come from a table in smem.
 constexpr int kUpMaxTH = 64;
+constexpr int kUpLB = 8;          // labels a thread has in flight (batch of rows)
 
 // a, b: interpolated logit differences; label in {0, 1} or -1 (ignored).  lm = 1 for live lanes, 0 for lanes past W.
 // cls_sum / cmp_sum gain the un-normalised loss terms; ga, gb = d loss / d a, d loss / d b (normalised).
@@ -633,17 +634,20 @@ mirror_up2_kernel(const float *__restrict__ s_lo, const float *__restrict__ t_lo
 
   const long long *lab_col = labels + ((long long)b * H + y_tile) * W + x;
 #pragma unroll 1
-  for (int r0 = 0; r0 < rows; r0 += kUpTH) {          // CTA-uniform trip counts and branches throughout
-    // labels of this thread's column for 16 rows: all loads issued before the first use, then packed to 2-bit
+  for (int r0 = 0; r0 < rows; r0 += kUpLB) {          // CTA-uniform trip counts and branches throughout
+    // labels of this thread's column for kUpLB rows: all loads issued before the first use, then packed to 2-bit
     // codes (label + 1; 0 = ignored) so that the row loop needs no unrolling
-    long long lab[kUpTH];
+    const int rend = min(r0 + kUpLB, rows);
+    const int nlab = live ? rend - r0 : 0;
+    unsigned long long lab[kUpLB];
 #pragma unroll
-    for (int r = 0; r < kUpTH; ++r)
-      lab[r] = (live && r0 + r < rows) ? __ldcs(lab_col + (long long)(r0 + r) * W) : kIgnoreIndex;
+    for (int r = 0; r < kUpLB; ++r) {
+      lab[r] = r < nlab ? (unsigned long long)__ldcs(lab_col) : ~0ull;
+      lab_col += W;
+    }
     unsigned codes = 0;
 #pragma unroll
-    for (int r = 0; r < kUpTH; ++r) codes |= (unsigned)(mirror_label(lab[r], 2) + 1) << (2 * r);
-    const int rend = min(r0 + kUpTH, rows);
+    for (int r = 0; r < kUpLB; ++r) codes |= (lab[r] < 2ull ? (unsigned)lab[r] + 1u : 0u) << (2 * r);
 #pragma unroll 1
     for (int r = r0; r < rend; ++r) {
       const int ri = row_i[r];
@@ -886,8 +890,12 @@ extern "C" int cp2_mirror_loss_upsampled(const float *s_lo, const float *t_lo, c
   if (n_valid <= 0) n_valid = n_pix;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t lo_bytes = sizeof(float) * (size_t)B * Cls * h * w;
-  if (ds_lo) CP2_CUDA(cudaMemsetAsync(ds_lo, 0, lo_bytes, st));
-  if (dt_lo && has_t) CP2_CUDA(cudaMemsetAsync(dt_lo, 0, lo_bytes, st));
+  if (ds_lo && dt_lo && has_t && dt_lo == ds_lo + (size_t)B * Cls * h * w) {
+    CP2_CUDA(cudaMemsetAsync(ds_lo, 0, 2 * lo_bytes, st));        // adjacent gradients: one memset node
+  } else {
+    if (ds_lo) CP2_CUDA(cudaMemsetAsync(ds_lo, 0, lo_bytes, st));
+    if (dt_lo && has_t) CP2_CUDA(cudaMemsetAsync(dt_lo, 0, lo_bytes, st));
+  }
   const int th = Cls == 2 ? up2_rows_per_cta(B, H, W) : kUpTH;
   const UpGeom g = up_geometry(h, w, H, W, th);
   const MirrorScale sc = make_scale(has_t, n_pix, n_valid, lmbd_compare, inv_temp);

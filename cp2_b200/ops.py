@@ -932,9 +932,13 @@ def mirror_loss_upsampled_raw(s_lo, t_lo, labels, lmbd_compare, softmax_temp, wa
     dev = s.device
     partial = torch.empty((lib.cp2_mirror_up_partials(B, H, W), 3), device=dev, dtype=torch.float32)
     out = torch.empty((4,), device=dev, dtype=torch.float32)
-    ds = torch.empty_like(s) if want_grads else None
-    dt = torch.empty_like(s) if (want_grads and t is not None) else None
-    n_launch = 2 + (1 if ds is not None else 0) + (1 if dt is not None else 0)     # + memsets of the grads
+    ds = dt = None
+    if want_grads and t is not None:
+        both = torch.empty((2,) + tuple(s.shape), device=dev, dtype=torch.float32)   # adjacent: ONE memset
+        ds, dt = both[0], both[1]
+    elif want_grads:
+        ds = torch.empty_like(s)
+    n_launch = 2 + (1 if ds is not None else 0)                                    # + memset of the grads
     _call("cp2_mirror_loss_upsampled", n_launch, lib.cp2_mirror_loss_upsampled, _ptr(s), _ptr(t), _ptr(labels),
           _ptr(partial), _ptr(out), _ptr(ds), _ptr(dt), float(lmbd_compare), 1.0 / float(softmax_temp),
           int(n_valid) if n_valid else 0, B, Cls, h, w, H, W, _stream())

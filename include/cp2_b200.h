@@ -279,7 +279,10 @@ int cp2_mirror_loss(const float *s_logits, const float *t_logits, const int64_t 
  *   s_lo, t_lo   : [B,Cls,h,w] f32 (t_lo == NULL: MirrorVariant.NONE); labels : [B,H,W] int64
  *   partial      : [cp2_mirror_up_partials(B,H,W), 3] f32 work space; out : [4] f32 as above
  *   ds_lo, dt_lo : NULL or [B,Cls,h,w] f32 OUT (zeroed here, then accumulated with fp32 atomics:
- *                  last-bit run-to-run differences, as ATen's own upsample backward)
+ *                  last-bit run-to-run differences, as ATen's own upsample backward); when dt_lo directly
+ *                  follows ds_lo in memory both are cleared by one memset
+ * Two classes (Cls == 2, the polyp masks of mirror_pretrain.py) run a specialised kernel on the logit
+ * DIFFERENCES s1 - s0, t1 - t0 (every term of the loss depends on them alone); other class counts the generic one.
  * Gradients are for upstream gradient 1 (they are tiny: scale them on the caller's side). */
 int cp2_mirror_up_partials(int B, int H, int W);
 int cp2_mirror_loss_upsampled(const float *s_lo, const float *t_lo, const int64_t *labels,
