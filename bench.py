@@ -44,6 +44,8 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=32, help="images per GPU (configs[1]: 32)")
     ap.add_argument("--nchw", action="store_true",
                     help="keep the (out-of-scope) cuDNN backbone in NCHW instead of channels_last (NHWC)")
+    ap.add_argument("--no-graphs", action="store_true",
+                    help="launch the (out-of-scope) encoders kernel by kernel instead of from CUDA graphs")
     ap.add_argument("--no-sweep", action="store_true", help="skip the dense-loss microbench sweep")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sweep-only", action="store_true", help="run only the dense-loss sweep (profiling)")
@@ -971,6 +973,19 @@ def own_arm(args):
         # nchwToNhwc / nhwcToNchw transpose around every convolution (11 % of the r01b step)
         model = model.to(memory_format=torch.channels_last)
     n_params = sum(p.numel() for p in model.encoder_k.parameters())
+    # The ~1100 cuDNN / ATen launches of the two encoders are the host-bound part of the step: capture them in CUDA
+    # graphs (MODEL.graph_encoders).  Under DDP the query encoder is captured stage by stage (one autograd node per
+    # stage): a single graph would serialise the gradient all-reduce behind the whole backward.
+    graphs = {"encoder_q": False, "encoder_k": False}
+    if not args.no_graphs:
+        try:
+            model.graph_encoders((args.batch, 3, IMG, IMG), query=True, key=True,
+                                 query_stages=model.encoder_q.graph_stages() if world > 1 else None)
+            graphs = dict(model.graphed)
+        except Exception as e:                                   # noqa: BLE001 - eager launches are the fallback
+            graphs["error"] = f"{type(e).__name__}: {e}"[:300]
+            print(f"[bench] CUDA-graph capture of the encoders failed, running them eagerly: {graphs['error']}",
+                  file=sys.stderr)
     net = model
     if world > 1:
         # queues are identical on every rank by construction -> no per-forward buffer broadcast
@@ -1154,7 +1169,7 @@ def own_arm(args):
         "metric": METRIC, "value": B * world * args.steps / (ms_value * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_value / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32+bf16",
-        "data": "synthetic", "config": workload_config(B, world, args.nchw),
+        "data": "synthetic", "config": dict(workload_config(B, world, args.nchw), encoder_cuda_graphs=graphs),
         "e2e": {"value": B * world * args.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps,
                 "readback": "async D2H into pinned memory, consumed one step later",

@@ -376,6 +376,8 @@ class MODEL(nn.Module):
         self.overlap_exchange = bool(overlap_exchange)
         self._side_stream = None
         self._cpu_group = None
+        self._key_graph = None                 # (CUDAGraph, static_in, static_out) of graph_encoders()
+        self.graphed = {"encoder_q": False, "encoder_k": False}
         self.collective_times = None        # bench.py: dict name -> [seconds | (event, event)] when not None
 
     @torch.no_grad()
@@ -524,6 +526,83 @@ class MODEL(nn.Module):
             perm_host = idx_unshuffle.cpu()
         return self._timed("nccl_all_to_all_unshuffle", lambda: self._exchange_rows(x, perm_host))
 
+    def graph_encoders(self, image_shape, *, query=True, key=True, warmup=3, query_stages=None):
+        """Capture the encoders for ONE input shape in CUDA graphs (no counterpart in the reference, which launches
+        every convolution / BN / ReLU kernel from Python: ~1100 launches per step, the host-bound part of the step).
+
+        * `encoder_q`: forward and backward, through `torch.cuda.make_graphed_callables` (its forward becomes one
+          graph launch, its backward another; parameters keep their storage, so the EMA kernel, the optimizer and
+          DDP see the same tensors).  Call BEFORE wrapping the model in DistributedDataParallel.  The whole backward
+          is then ONE autograd node: DDP's gradient hooks fire at its end, so the all-reduce no longer overlaps
+          the backward.  `query_stages` (a list of sub-modules that `encoder_q.forward` calls one after the other,
+          each on the previous one's output tensor) captures every stage on its own instead: autograd sees one node
+          per stage and DDP's buckets start reducing while the earlier stages are still in their backward.
+        * `encoder_k`: the no-grad forward of `forward_cp2` in one `torch.cuda.CUDAGraph` (static input / output).
+        Only used while the module is in training mode and the input has `image_shape`; any other call runs the
+        eager path.  The warm-up forwards run on zeros: BatchNorm running statistics of both encoders are
+        restored afterwards, so capturing does not change the model."""
+        dev = self.queue.device
+        assert dev.type == "cuda", "graph_encoders needs the model on a CUDA device"
+        assert self.training, "capture in training mode (the graphs replay train-mode BatchNorm)"
+        image_shape = tuple(int(v) for v in image_shape)
+
+        def with_buffers_restored(module, fn):
+            saved = [b.detach().clone() for b in module.buffers()]
+            try:
+                return fn()
+            finally:
+                with torch.no_grad():
+                    for b, v in zip(module.buffers(), saved):
+                        b.copy_(v)
+
+        if query and not self.graphed["encoder_q"]:
+            sample = torch.zeros(image_shape, device=dev, dtype=torch.float32)
+            if query_stages:
+                stages, samples, x = tuple(query_stages), [], sample
+
+                def capture_stages():
+                    nonlocal x
+                    with torch.no_grad():                        # shapes of the tensors handed from stage to stage
+                        for i, st in enumerate(stages):
+                            samples.append((torch.zeros_like(x).requires_grad_(i > 0),))
+                            x = st(x)
+                    torch.cuda.make_graphed_callables(stages, tuple(samples), num_warmup_iters=warmup,
+                                                      allow_unused_input=True)
+                with_buffers_restored(self.encoder_q, capture_stages)
+                self.graphed["encoder_q"] = f"{len(stages)} stages"
+            else:
+                with_buffers_restored(self.encoder_q, lambda: torch.cuda.make_graphed_callables(
+                    self.encoder_q, (sample,), num_warmup_iters=warmup, allow_unused_input=True))
+                self.graphed["encoder_q"] = True
+        if key and self._key_graph is None:
+            static_in = torch.zeros(image_shape, device=dev, dtype=torch.float32)
+
+            def capture():
+                side = torch.cuda.Stream(device=dev)
+                side.wait_stream(torch.cuda.current_stream(dev))
+                with torch.cuda.stream(side), torch.no_grad():
+                    for _ in range(max(1, warmup)):             # cuDNN algorithm search happens outside the capture
+                        self.encoder_k(static_in)
+                torch.cuda.current_stream(dev).wait_stream(side)
+                graph = torch.cuda.CUDAGraph()
+                with torch.no_grad(), torch.cuda.graph(graph):
+                    static_out = self.encoder_k(static_in)
+                return graph, static_out
+            graph, static_out = with_buffers_restored(self.encoder_k, capture)
+            self._key_graph = (graph, static_in, static_out)
+            self.graphed["encoder_k"] = True
+        return self
+
+    def _encode_keys(self, img_b):
+        """builder.py:1275 `k = self.encoder_k(img_b)` (inside no_grad)."""
+        kg = self._key_graph
+        if kg is None or not self.training or tuple(img_b.shape) != tuple(kg[1].shape) or not img_b.is_cuda:
+            return self.encoder_k(img_b)
+        graph, static_in, static_out = kg
+        static_in.copy_(img_b)
+        graph.replay()
+        return static_out                          # read by this step's loss before the next replay overwrites it
+
     def forward(self, **kwargs):                               # builder.py:651-665
         if self._densecl:
             return self.forward_densecl(**kwargs)
@@ -649,7 +728,7 @@ class MODEL(nn.Module):
         with torch.no_grad():                                  # builder.py:1271-1277
             self._momentum_update_key_encoder()
             join_exchange()
-            k = self.encoder_k(img_b)
+            k = self._encode_keys(img_b)
             k = self._batch_unshuffle_ddp(k, idx_unshuffle)
 
         # K2a/K2/K3 + autograd: builder.py:1261-1268, 1279-1292, 1392-1397, 1414-1439

@@ -73,3 +73,8 @@ class DeepLabV3Encoder(nn.Module):
 
     def forward(self, x):
         return self.decode_head(self.backbone(x)[3])
+
+    def graph_stages(self):
+        """The chain forward() runs, stage by stage (for MODEL.graph_encoders(query_stages=...))."""
+        b = self.backbone
+        return [b.stem, b.layer1, b.layer2, b.layer3, b.layer4, self.decode_head]

@@ -209,3 +209,77 @@ def test_loss_nan_hazard_matches_reference(ops):
     loss, li, ld, _, _, _ = ops.cp2_loss(qd, k.cuda(), ma.cuda(), mb.cuda(), queue.cuda(), 0.2, 0.2, 0.2)
     assert torch.isnan(loss).item() and torch.isnan(ld).item()
     np.testing.assert_allclose(li.item(), r["loss_ins"].item(), rtol=LOSS_RTOL)
+
+
+# ------------------------------------------------------------------------ CUDA-graph capture of the encoders
+class _ConvBN(nn.Module):
+    """Small segmentor with BatchNorm (running statistics are part of what the graphs must reproduce)."""
+
+    def __init__(self, dim=128):
+        super().__init__()
+        self.stem = nn.Sequential(nn.Conv2d(3, 16, 4, stride=4, bias=False), nn.BatchNorm2d(16), nn.ReLU(inplace=True))
+        self.body = nn.Sequential(nn.Conv2d(16, 32, 4, stride=4, bias=False), nn.BatchNorm2d(32), nn.ReLU(inplace=True))
+        self.proj = nn.Conv2d(32, dim, 1)
+
+    def forward(self, x):
+        return self.proj(self.body(self.stem(x)))
+
+
+def test_graph_encoders_matches_eager():
+    """MODEL.graph_encoders: three training steps with both encoders replayed from CUDA graphs give the losses,
+    parameters, BatchNorm statistics and queue of the same steps launched eagerly; capture itself leaves the model
+    (BN running statistics included) untouched; eval mode and other shapes fall back to the eager path."""
+    from cp2_b200.builder import MODEL
+    dev = torch.device("cuda:0")
+    B, H, C, K = 8, 224, 128, 256
+
+    def make():
+        torch.manual_seed(3)
+        m = MODEL(None, rank=1, dim=C, K=K, dense_logits_temp=0.2, device=dev, pretrain_from_scratch=True,
+                  encoder_factory=lambda: _ConvBN(C), output_stride=16).to(dev)
+        return m, torch.optim.SGD(m.encoder_q.parameters(), lr=0.05, momentum=0.9)
+
+    eager, opt_e = make()
+    graphed, opt_g = make()
+    staged, opt_s = make()
+    before = {k: v.clone() for k, v in graphed.state_dict().items()}
+    graphed.graph_encoders((B, 3, H, H))
+    assert graphed.graphed == {"encoder_q": True, "encoder_k": True}
+    # one graph pair per stage of the query encoder (what bench.py uses under DDP)
+    staged.graph_encoders((B, 3, H, H), query_stages=[staged.encoder_q.stem, staged.encoder_q.body,
+                                                       staged.encoder_q.proj])
+    assert staged.graphed == {"encoder_q": "3 stages", "encoder_k": True}
+    for k, v in staged.state_dict().items():
+        assert torch.equal(v, before[k]), f"staged capture changed {k}"
+    for k, v in graphed.state_dict().items():
+        assert torch.equal(v, before[k]), f"capture changed {k}"
+    g = torch.Generator().manual_seed(5)
+    for s in range(3):
+        img_a, img_b = torch.rand(B, 3, H, H, generator=g).to(dev), torch.rand(B, 3, H, H, generator=g).to(dev)
+        bg0, bg1 = torch.rand(B, 3, H, H, generator=g), torch.rand(B, 3, H, H, generator=g)
+        bg0[:, :, 30:200, 20:150] = 0.0
+        bg1[:, :, 50:220, 60:224] = 0.0
+        losses = []
+        for m, opt in ((eager, opt_e), (graphed, opt_g), (staged, opt_s)):
+            torch.manual_seed(100 + s)                      # the batch shuffle draws a CPU randperm
+            opt.zero_grad(set_to_none=True)
+            loss = m(img_a=img_a, img_b=img_b, bg0=bg0.to(dev), bg1=bg1.to(dev), visualize=False, step=s,
+                     new_epoch=False)
+            loss.backward()
+            opt.step()
+            losses.append(loss.item())
+        np.testing.assert_allclose(losses[1], losses[0], rtol=1e-5)
+        np.testing.assert_allclose(losses[2], losses[0], rtol=1e-5)
+    se, sg = eager.state_dict(), graphed.state_dict()
+    assert se.keys() == sg.keys()
+    for other in (sg, staged.state_dict()):
+        for k in se:
+            a, b = se[k].float(), other[k].float()
+            assert torch.allclose(a, b, rtol=1e-4, atol=1e-6), (k, float((a - b).abs().max()))
+    assert int(sg["encoder_k.stem.1.num_batches_tracked"]) == 3 and int(sg["encoder_q.stem.1.num_batches_tracked"]) == 3
+    # eval mode and another batch size run the eager path
+    graphed.eval()
+    with torch.no_grad():
+        out = graphed.encoder_q(torch.rand(2, 3, H, H, device=dev))
+        assert out.shape == (2, C, H // 16, H // 16)
+        assert graphed._encode_keys(torch.rand(2, 3, H, H, device=dev)).shape == (2, C, H // 16, H // 16)
