@@ -111,7 +111,7 @@ def main():
             summarise_rep(rep, os.path.join(DST, f"{tag}_ncu_{name[5:]}.csv"), traffic if name == "prof_step" else {})
     if os.path.isfile(os.path.join(SRC, "launches_step.csv")):
         summarise_launches(os.path.join(SRC, "launches_step.csv"), os.path.join(DST, f"{tag}_launches_step.txt"))
-    for name in ("bench.json", "bench_ref.json"):
+    for name in ("bench.json", "bench_ref.json", "bench_nographs.json", "mirror_times.log"):
         if os.path.isfile(os.path.join(SRC, name)) and os.path.getsize(os.path.join(SRC, name)) > 0:
             shutil.copy(os.path.join(SRC, name), os.path.join(DST, f"{tag}_{name}"))
     with open(tpath, "w") as f:
