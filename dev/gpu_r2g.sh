@@ -3,8 +3,11 @@
 # ncu launch list of the step and full captures of the step kernels, the 56x56 dense pair and the f2 / f3 kernels.
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,driver_version,clocks.max.sm --format=csv > gpurun_out/gpu.txt 2>&1
+rc=0
+if [ "$SKIP_TESTS" != "1" ]; then
 timeout 900 python -m pytest tests -m gpu -q --tb=short -p no:cacheprovider > gpurun_out/test_gpu.log 2>&1; rc=$?
 echo "== pytest exit $rc"; tail -n 8 gpurun_out/test_gpu.log
+fi
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "== smoke exit $?"; tail -n 3 gpurun_out/smoke.log
 timeout 400 python bench.py --impl reference --steps 4 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "== ref exit $?"
 timeout 1200 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "== bench exit $?"
@@ -51,4 +54,10 @@ if [ "$1" != "nocu" ]; then
   bash dev/gpu_ncu_mirror.sh full > gpurun_out/mirror_times.log 2>&1; tail -n 12 gpurun_out/mirror_times.log
   timeout 300 python bench.py --steps 10 --warmup 3 --no-sweep --no-cpu-baseline --no-eager-baseline --no-graphs > gpurun_out/bench_nographs.json 2> gpurun_out/bench_nographs.err; echo "== bench --no-graphs exit $?"
 fi
+# gpurun_out/ comes back only below 64 MiB: summarise the captures HERE and leave the .ncu-rep files behind
+mkdir -p gpurun_out/profiles_box
+cp profiles/traffic.json gpurun_out/profiles_box/ 2>/dev/null
+CP2_PROFILES_DST=gpurun_out/profiles_box python dev/summarise_profiles.py ${TAG:-r02g} > gpurun_out/summarise.log 2>&1; echo "== summarise exit $?"
+rm -f gpurun_out/*.ncu-rep
+du -sh gpurun_out
 exit $rc

@@ -18,7 +18,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SRC = os.path.join(ROOT, "gpurun_out")
-DST = os.path.join(ROOT, "profiles")
+DST = os.environ.get("CP2_PROFILES_DST") or os.path.join(ROOT, "profiles")   # on the GPU box: a directory under gpurun_out/
 
 METRICS = [
     "gpu__time_duration.sum", "sm__cycles_elapsed.max", "launch__grid_size", "launch__block_size",
