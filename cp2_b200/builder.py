@@ -539,7 +539,8 @@ class MODEL(nn.Module):
           per stage and DDP's buckets start reducing while the earlier stages are still in their backward.
         * `encoder_k`: the no-grad forward of `forward_cp2` in one `torch.cuda.CUDAGraph` (static input / output).
         Only used while the module is in training mode and the input has `image_shape`; any other call runs the
-        eager path.  The warm-up forwards run on zeros: BatchNorm running statistics of both encoders are
+        eager path.  The graphs hold the parameters' and buffers' addresses: load_state_dict / optimizer steps /
+        the EMA kernel (all in place) are fine, `.to(...)`, `.half()` or re-creating parameters afterwards are not.  The warm-up forwards run on zeros: BatchNorm running statistics of both encoders are
         restored afterwards, so capturing does not change the model."""
         dev = self.queue.device
         assert dev.type == "cuda", "graph_encoders needs the model on a CUDA device"
