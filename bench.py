@@ -44,6 +44,10 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=32, help="images per GPU (configs[1]: 32)")
     ap.add_argument("--nchw", action="store_true",
                     help="keep the (out-of-scope) cuDNN backbone in NCHW instead of channels_last (NHWC)")
+    ap.add_argument("--no-fold", action="store_true",
+                    help="run the ASPP's dilated 3x3 convolutions as cuDNN runs them instead of tap by tap on the "
+                         "windows where a tap sees data (MODEL.fold_dilated_convs)")
+    ap.add_argument("--fold-cover", type=float, default=0.15)
     ap.add_argument("--no-graphs", action="store_true",
                     help="launch the (out-of-scope) encoders kernel by kernel instead of from CUDA graphs")
     ap.add_argument("--no-sweep", action="store_true", help="skip the dense-loss microbench sweep")
@@ -976,12 +980,13 @@ def own_arm(args):
     # The ~1100 cuDNN / ATen launches of the two encoders are the host-bound part of the step: capture them in CUDA
     # graphs (MODEL.graph_encoders).  Under DDP the query encoder is captured stage by stage (one autograd node per
     # stage): a single graph would serialise the gradient all-reduce behind the whole backward.
-    graphs = {"encoder_q": False, "encoder_k": False}
+    folded = 0 if args.no_fold else model.fold_dilated_convs(args.fold_cover)
+    graphs = {"encoder_q": False, "encoder_k": False, "folded_dilated_convs": folded}
     if not args.no_graphs:
         try:
             model.graph_encoders((args.batch, 3, IMG, IMG), query=True, key=True,
                                  query_stages=model.encoder_q.graph_stages() if world > 1 else None)
-            graphs = dict(model.graphed)
+            graphs.update(model.graphed)
         except Exception as e:                                   # noqa: BLE001 - eager launches are the fallback
             graphs["error"] = f"{type(e).__name__}: {e}"[:300]
             print(f"[bench] CUDA-graph capture of the encoders failed, running them eagerly: {graphs['error']}",

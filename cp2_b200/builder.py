@@ -526,6 +526,16 @@ class MODEL(nn.Module):
             perm_host = idx_unshuffle.cpu()
         return self._timed("nccl_all_to_all_unshuffle", lambda: self._exchange_rows(x, perm_host))
 
+    def fold_dilated_convs(self, max_cover=0.15):
+        """Exact rewrite of the encoders' strongly dilated 3x3 convolutions (the ASPP branches) for small feature
+        maps: every tap is applied as a 1x1 convolution on the window where it reads data instead of padding
+        (`cp2_b200.encoder.fold_dilated_convs`; at the 14x14 map of 224x224 views the dilation-18 branch is a 1x1
+        convolution; the default `max_cover` keeps the dilation-12 branch, which touches 2-pixel borders, on cuDNN's
+        kernel because that measured faster).  Same parameters, same sums; maps that are too
+        large for it to pay run the stock convolution.  Call before `graph_encoders`.  -> convolutions patched."""
+        from .encoder import fold_dilated_convs
+        return fold_dilated_convs(self.encoder_q, max_cover) + fold_dilated_convs(self.encoder_k, max_cover)
+
     def graph_encoders(self, image_shape, *, query=True, key=True, warmup=3, query_stages=None):
         """Capture the encoders for ONE input shape in CUDA graphs (no counterpart in the reference, which launches
         every convolution / BN / ReLU kernel from Python: ~1100 launches per step, the host-bound part of the step).

@@ -78,3 +78,69 @@ class DeepLabV3Encoder(nn.Module):
         """The chain forward() runs, stage by stage (for MODEL.graph_encoders(query_stages=...))."""
         b = self.backbone
         return [b.stem, b.layer1, b.layer2, b.layer3, b.layer4, self.decode_head]
+
+
+# ------------------------------------------------------------------------------------------------------------
+# Exact rewrite of strongly dilated 3x3 convolutions on small feature maps (no counterpart in the reference).
+# A 3x3 convolution with dilation d and padding d reads, for the tap (ky, kx), the input at offset
+# ((ky-1)*d, (kx-1)*d): on an H x W map that offset lands in the zero padding for every output position outside
+# a (H - |dy|) x (W - |dx|) window, and for |dy| >= H or |dx| >= W the tap never sees data at all.  At the 14 x 14
+# map CP2 trains at (224 x 224 views, output stride 16) the ASPP branch with dilation 18 IS a 1x1 convolution
+# with the centre weights, and the dilation-12 branch touches 2-pixel borders only (the degeneration the DeepLabv3
+# paper describes for large rates) — yet cuDNN runs both as full 3x3 implicit GEMMs (118 GFLOP each at B=32).
+# folded_dilated_conv2d applies every tap as a 1x1 convolution on exactly the window where it sees data:
+# the same sums (taps that would multiply zeros are the only ones dropped), the same parameters / checkpoint keys,
+# gradients to the full 3x3 weight included.
+def _tap_windows(H, W, d):
+    """[(ky, kx, y0, y1, x0, x1)]: output window [y0:y1, x0:x1] on which tap (ky, kx) reads inside the map."""
+    out = []
+    for ky in range(3):
+        for kx in range(3):
+            dy, dx = (ky - 1) * d, (kx - 1) * d
+            y0, y1, x0, x1 = max(0, -dy), min(H, H - dy), max(0, -dx), min(W, W - dx)
+            if y1 > y0 and x1 > x0:
+                out.append((ky, kx, y0, y1, x0, x1))
+    return out
+
+
+def folded_dilated_conv2d(x, weight, d, max_cover=0.15):
+    """conv2d(x, weight [O,I,3,3], stride 1, padding d, dilation d) computed tap by tap on the windows where a tap
+    sees data.  Returns None when the taps cover more than `max_cover` of the 9*H*W products (the plain
+    convolution is the better kernel then).  Measured on a B200 at B=32, 2048 -> 512 channels, 14 x 14: dilation 18
+    (cover 0.11: the centre tap alone) 1.84 ms per training step faster than cuDNN's 3x3 kernel; dilation 12 (cover
+    0.18: eight extra 2-pixel windows) 0.47 ms SLOWER tap by tap, dilation 6 (0.51) slower still: hence 0.15."""
+    H, W = x.shape[-2:]
+    wins = _tap_windows(H, W, d)
+    if sum((y1 - y0) * (x1 - x0) for _, _, y0, y1, x0, x1 in wins) > max_cover * 9 * H * W:
+        return None
+    import torch.nn.functional as F
+    out = F.conv2d(x, weight[:, :, 1:2, 1:2])                 # the centre tap sees the whole map
+    for ky, kx, y0, y1, x0, x1 in wins:
+        if ky == 1 and kx == 1:
+            continue
+        dy, dx = (ky - 1) * d, (kx - 1) * d
+        out[:, :, y0:y1, x0:x1] += F.conv2d(x[:, :, y0 + dy:y1 + dy, x0 + dx:x1 + dx], weight[:, :, ky:ky + 1, kx:kx + 1])
+    return out
+
+
+def fold_dilated_convs(module, max_cover=0.15):
+    """Patch every eligible nn.Conv2d below `module` (3x3, stride 1, groups 1, padding == dilation > 1, zero
+    padding) so that its forward uses folded_dilated_conv2d whenever the input map is small enough for it to
+    pay; other inputs run the stock convolution.  Parameters and state_dict are untouched.  -> number of
+    patched convolutions."""
+    import types
+    n = 0
+    for m in module.modules():
+        if (isinstance(m, nn.Conv2d) and m.kernel_size == (3, 3) and m.stride == (1, 1) and m.groups == 1
+                and m.dilation[0] == m.dilation[1] and m.dilation[0] > 1 and m.padding == m.dilation
+                and m.padding_mode == "zeros" and not hasattr(m, "_cp2_stock_forward")):
+            m._cp2_stock_forward = m.forward
+
+            def forward(self, x, _cover=max_cover):
+                y = folded_dilated_conv2d(x, self.weight, self.dilation[0], _cover) if x.dim() == 4 else None
+                if y is None:
+                    return self._cp2_stock_forward(x)
+                return y if self.bias is None else y + self.bias.view(1, -1, 1, 1)
+            m.forward = types.MethodType(forward, m)
+            n += 1
+    return n

@@ -119,3 +119,42 @@ def test_step_score_stats_match_oracle():
             assert torch.allclose(st[name]["quartiles"][i], ref[name]["quartiles"][i], atol=1e-6)
     l_neg = q_pos @ m.queue
     assert torch.allclose(st["instance_neg_q"], torch.quantile(l_neg, torch.tensor([0.25, 0.5, 0.75]), dim=1))
+
+
+def test_fold_dilated_convs_is_exact():
+    """MODEL.fold_dilated_convs / encoder.fold_dilated_convs: a 3x3 convolution with padding == dilation applied tap
+    by tap on the windows where a tap sees data equals the stock convolution (fp64: to rounding), output and all
+    three gradients; parameters and state_dict keys are untouched; large maps keep the stock kernel."""
+    import copy
+    import torch.nn as nn
+    from cp2_b200.encoder import ASPPContrastHead, fold_dilated_convs, folded_dilated_conv2d
+    torch.manual_seed(0)
+    for H, W, d, bias in [(14, 14, 18, False), (14, 14, 12, False), (9, 20, 7, True), (32, 32, 18, False), (7, 7, 12, True)]:
+        conv = nn.Conv2d(8, 12, 3, padding=d, dilation=d, bias=bias).double()
+        ref = copy.deepcopy(conv)
+        assert fold_dilated_convs(conv, max_cover=0.5) == 1 and fold_dilated_convs(conv) == 0     # idempotent
+        x = torch.randn(2, 8, H, W, dtype=torch.double, requires_grad=True)
+        x2 = x.detach().clone().requires_grad_(True)
+        assert folded_dilated_conv2d(x, conv.weight, d, 0.5) is not None                  # the folded path runs
+        y, yr = conv(x), ref(x2)
+        g = torch.randn_like(y)
+        y.backward(g)
+        yr.backward(g)
+        assert torch.allclose(y, yr, rtol=0, atol=1e-12)
+        assert torch.allclose(x.grad, x2.grad, rtol=0, atol=1e-12)
+        assert torch.allclose(conv.weight.grad, ref.weight.grad, rtol=0, atol=1e-11)
+        if bias:
+            assert torch.allclose(conv.bias.grad, ref.bias.grad, rtol=0, atol=1e-11)
+        assert list(conv.state_dict()) == list(ref.state_dict())
+    # a map too large for the rewrite to pay (taps cover > 50 % of the products) runs the stock convolution
+    assert folded_dilated_conv2d(torch.randn(1, 8, 64, 64), torch.randn(4, 8, 3, 3), 6, 0.5) is None
+    # default threshold: the centre-tap-only case folds, the 2-pixel-border case stays on the stock kernel
+    assert folded_dilated_conv2d(torch.randn(1, 8, 14, 14), torch.randn(4, 8, 3, 3), 18) is not None
+    assert folded_dilated_conv2d(torch.randn(1, 8, 14, 14), torch.randn(4, 8, 3, 3), 12) is None
+    # the stand-in head at the 14x14 map of 224x224 views: dilation 18 folds, 6 and 12 run the stock kernel
+    head = ASPPContrastHead(in_channels=16, channels=8, dim=4).double()
+    ref = copy.deepcopy(head)
+    assert fold_dilated_convs(head) == 3                      # 3x3 branches with dilation 6, 12, 18
+    x = torch.randn(2, 16, 14, 14, dtype=torch.double)
+    head.eval(), ref.eval()
+    assert torch.allclose(head(x), ref(x), rtol=0, atol=1e-12)
