@@ -158,3 +158,44 @@ def test_fold_dilated_convs_is_exact():
     x = torch.randn(2, 16, 14, 14, dtype=torch.double)
     head.eval(), ref.eval()
     assert torch.allclose(head(x), ref(x), rtol=0, atol=1e-12)
+
+
+class _TinyAspp(nn.Module):
+    """Patch embedding + two dilated 3x3 branches (dilation 18 folds at 14x14, dilation 2 never does)."""
+
+    def __init__(self, dim=128):
+        super().__init__()
+        self.proj = nn.Conv2d(3, 8, 16, 16)
+        self.far = nn.Conv2d(8, dim, 3, padding=18, dilation=18, bias=False)
+        self.near = nn.Conv2d(8, dim, 3, padding=2, dilation=2)
+
+    def forward(self, x):
+        x = self.proj(x)
+        return self.far(x) + self.near(x)
+
+
+def test_model_fold_dilated_convs_patches_both_encoders():
+    """MODEL.fold_dilated_convs: both encoders are patched, their outputs and the checkpoint keys stay the same,
+    and gradients still reach the full 3x3 weight (zero on the taps that only ever read padding)."""
+    torch.manual_seed(1)
+    m = _model(encoder_factory=_TinyAspp)
+    keys = list(m.state_dict())
+    x = torch.randn(2, 3, 224, 224)
+    with torch.no_grad():
+        want_q, want_k = m.encoder_q(x), m.encoder_k(x)
+    assert m.fold_dilated_convs() == 4 and m.fold_dilated_convs() == 0        # 2 eligible convs per encoder
+    with torch.no_grad():
+        assert torch.allclose(m.encoder_q(x), want_q, rtol=1e-5, atol=1e-6)
+        assert torch.allclose(m.encoder_k(x), want_k, rtol=1e-5, atol=1e-6)
+    assert list(m.state_dict()) == keys
+    m.encoder_q(x).square().sum().backward()
+    g = m.encoder_q.far.weight.grad
+    assert g.shape == (128, 8, 3, 3) and float(g[:, :, 1, 1].abs().sum()) > 0
+    off_centre = g.clone()
+    off_centre[:, :, 1, 1] = 0
+    assert float(off_centre.abs().max()) == 0.0             # those taps multiply zero padding everywhere
+    # a larger map (448 x 448 views -> 28 x 28): the dilation-18 taps see data, the stock convolution runs
+    with torch.no_grad():
+        big = torch.randn(1, 3, 448, 448)
+        ref = nn.functional.conv2d(m.encoder_q.proj(big), m.encoder_q.far.weight, padding=18, dilation=18)
+        assert torch.allclose(m.encoder_q.far(m.encoder_q.proj(big)), ref, rtol=1e-5, atol=1e-6)
