@@ -980,7 +980,12 @@ def own_arm(args):
     # The ~1100 cuDNN / ATen launches of the two encoders are the host-bound part of the step: capture them in CUDA
     # graphs (MODEL.graph_encoders).  Under DDP the query encoder is captured stage by stage (one autograd node per
     # stage): a single graph would serialise the gradient all-reduce behind the whole backward.
-    folded = 0 if args.no_fold else model.fold_dilated_convs(args.fold_cover)
+    folded = 0
+    if not args.no_fold:
+        try:
+            folded = model.fold_dilated_convs(args.fold_cover)
+        except Exception as e:                                   # noqa: BLE001 - the stock convolutions are the fallback
+            print(f"[bench] fold_dilated_convs failed, stock convolutions kept: {type(e).__name__}: {e}", file=sys.stderr)
     graphs = {"encoder_q": False, "encoder_k": False, "folded_dilated_convs": folded}
     if not args.no_graphs:
         try:
